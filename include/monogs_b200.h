@@ -1,0 +1,165 @@
+/*
+ * monogs_b200.h — C-ABI of the B200-native differentiable Gaussian-splatting rasterizer.
+ *
+ * Every entry point takes plain device pointers, explicit sizes, a caller-owned workspace and the
+ * caller's CUDA stream (passed as void* so the header needs no CUDA include).  No torch type crosses
+ * this boundary.  All functions return 0 on success or a negative MGS_E* code; the message of the
+ * last failure on the calling thread is available from mgs_last_error_string().
+ *
+ * Paths below are relative to /root/reference/submodules/diff-gaussian-rasterization unless noted.
+ * Matrices are 16 floats in the reference's memory order (element [4*col+row], auxiliary.h:58-76).
+ */
+#ifndef MONOGS_B200_H_
+#define MONOGS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MGS_OK 0
+#define MGS_EINVAL (-1)    /* bad argument (null pointer, negative size, unsupported combination) */
+#define MGS_ENOSPC (-2)    /* workspace too small for (P, W, H, R_cap) */
+#define MGS_ECUDA (-3)     /* a CUDA runtime call failed; see mgs_last_error_string() */
+#define MGS_EOVERFLOW (-4) /* num_rendered exceeded R_cap (only reported by the synchronous entry) */
+
+/* gradient-request bits for mgs_raster_backward (the autograd wrapper sets them from needs_input_grad) */
+#define MGS_GRAD_MEANS3D 1u
+#define MGS_GRAD_COLOR 2u     /* dL_dsh or dL_dcolors_precomp */
+#define MGS_GRAD_OPACITY 4u
+#define MGS_GRAD_COV 8u       /* dL_dscales + dL_drotations, or dL_dcov3D_precomp */
+#define MGS_GRAD_TAU 16u      /* camera pose tangent (rho, theta) */
+#define MGS_GRAD_MEANS2D 32u  /* screen-space gradient sink used for densification statistics */
+#define MGS_GRAD_ALL 63u
+
+/* Per-view constants; mirrors GaussianRasterizationSettings (diff_gaussian_rasterization/__init__.py:392-405)
+ * and the scalar arguments of _C.rasterize_gaussians (rasterize_points.h:18-39). */
+typedef struct mgs_view {
+  int32_t image_height, image_width;
+  float tanfovx, tanfovy;
+  float scale_modifier;
+  int32_t sh_degree;      /* active degree D */
+  int32_t sh_coeffs;      /* M = coefficients per channel in the shs tensor; 0 when colors_precomp is used */
+  int32_t prefiltered;
+  const float* bg;             /* device f32[3] */
+  const float* viewmatrix;     /* device f32[16] */
+  const float* projmatrix;     /* device f32[16] */
+  const float* projmatrix_raw; /* device f32[16]; read only by backward (backward.cu:497-501) */
+  const float* campos;         /* device; first three floats used (forward.cu:245) */
+} mgs_view;
+
+const char* mgs_last_error_string(void);
+int mgs_version(void);
+
+/* ---- rasterizer forward: replaces _C.rasterize_gaussians (ext.cpp:46, rasterize_points.cu:35-127,
+ *      cuda_rasterizer/rasterizer_impl.cu:198-344).  The three growable torch arenas of the reference
+ *      become one caller-owned workspace that forward fills and backward reads. ---- */
+
+/* Bytes of workspace needed for P Gaussians, a W x H image and room for R_cap tile instances. */
+size_t mgs_raster_workspace_bytes(int32_t P, int32_t W, int32_t H, int64_t R_cap);
+
+/* Stage 1 (forward.cu:157-258 + the InclusiveSum at rasterizer_impl.cu:280): per-Gaussian projection,
+ * conic, radius, tile rect, SH->RGB and the inclusive scan of tiles touched.  Writes radii[P] and leaves
+ * num_rendered in the workspace; if num_rendered_out is non-null it also receives the value through an
+ * async copy on `stream` (device or pinned host pointer).  Optional inputs are null exactly where the
+ * reference receives empty tensors (__init__.py:433-447). */
+int mgs_raster_preprocess(const mgs_view* view, int32_t P,
+                          const float* means3D, const float* opacities,
+                          const float* shs, const float* colors_precomp,
+                          const float* scales, const float* rotations, const float* cov3D_precomp,
+                          int32_t* radii, void* workspace, size_t workspace_bytes,
+                          int32_t* num_rendered_out, void* stream);
+
+/* Stage 2 (rasterizer_impl.cu:286-341): key generation, 64-bit (tile|depth) stable sort, tile ranges,
+ * packed per-instance records and the alpha blend.  R_cap is the capacity the workspace was sized for;
+ * if the device-side num_rendered exceeds it the overflow flag in the workspace is set and only the first
+ * R_cap instances (in Gaussian order) are rendered.  Never synchronises.  out_* and n_touched are fully
+ * written (n_touched is zeroed first), so the caller need not pre-fill them. */
+int mgs_raster_render(const mgs_view* view, int32_t P, const float* colors_precomp, const int32_t* radii,
+                      void* workspace, size_t workspace_bytes, int64_t R_cap,
+                      float* out_color, float* out_depth, float* out_opacity, int32_t* n_touched,
+                      void* stream);
+
+/* Reads (num_rendered, overflow) back from a workspace; synchronises `stream`. */
+int mgs_raster_query(const void* workspace, int32_t* num_rendered, int32_t* overflow, void* stream);
+
+/* ---- rasterizer backward: replaces _C.rasterize_gaussians_backward (ext.cpp:47,
+ *      rasterize_points.cu:150-254, rasterizer_impl.cu:348-470, backward.cu).  Gradient outputs whose
+ *      request bit is clear may be null.  All requested outputs are fully overwritten (no pre-zeroing
+ *      needed).  dL_dtau_sum is f32[6] = sum over Gaussians of the reference's dL_dtau[P,6]
+ *      (__init__.py:339-342: rho = [0:3], theta = [3:6]); dL_dtau_per_gaussian (f32[P,6]) is optional. ---- */
+int mgs_raster_backward(const mgs_view* view, int32_t P, uint32_t grad_mask,
+                        const float* means3D, const float* shs, const float* colors_precomp,
+                        const float* scales, const float* rotations, const float* cov3D_precomp,
+                        const int32_t* radii, const void* workspace, size_t workspace_bytes,
+                        void* scratch, size_t scratch_bytes,
+                        const float* dL_dout_color, const float* dL_dout_depth,
+                        float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors_or_sh,
+                        float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                        float* dL_dtau_sum, float* dL_dtau_per_gaussian, void* stream);
+size_t mgs_raster_backward_scratch_bytes(int32_t P);
+
+/* ---- sketch-Jacobian backward: replaces _C.rasterize_gaussians_backward_sketch_jacobian (ext.cpp:48,
+ *      rasterize_points.cu:256-378, backward_sketch_jacobian.cu).  Produces SJ[d,6] = for each sketch row
+ *      i the pose tangent of sum over pixels with sketch_indices==i of (dL_dout . out), i.e. the quantity
+ *      the wrapper keeps (__init__.py:253) without materialising the [P,d,...] buffers. ---- */
+int mgs_raster_backward_sketch(const mgs_view* view, int32_t P, int32_t sketch_dim,
+                               const int32_t* sketch_indices /* i32[H,W], -1 = unused */,
+                               const float* means3D, const float* shs, const float* colors_precomp,
+                               const float* scales, const float* rotations, const float* cov3D_precomp,
+                               const int32_t* radii, const void* workspace, size_t workspace_bytes,
+                               void* scratch, size_t scratch_bytes,
+                               const float* dL_dout_color, const float* dL_dout_depth,
+                               float* sketch_dtau /* f32[d,6] */, void* stream);
+size_t mgs_raster_backward_sketch_scratch_bytes(int32_t P, int32_t sketch_dim);
+
+/* ---- markVisible: replaces _C.mark_visible (ext.cpp:49, rasterizer_impl.cu:54-66,141-153) ---- */
+int mgs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream);
+
+/* ---- fused tracking / mapping loss (utils/slam_utils.py:83-113,188-253 and HuberLoss :58-75 of the
+ *      MonoGS tree).  One pass computes the scalar loss and dL/d(image), dL/d(depth), dL/d(a), dL/d(b). ---- */
+#define MGS_LOSS_TRACK_L1 0     /* get_loss_tracking_rgb / _rgbd: mean |opacity*(img_ab*m - gt*m)| */
+#define MGS_LOSS_TRACK_HUBER 1  /* per-pixel residual -> Huber(delta) -> L2 norm (slam_frontend.py:506,596-598) */
+#define MGS_LOSS_MAP_L1 2       /* get_loss_mapping_rgb / _rgbd */
+typedef struct mgs_loss_args {
+  int32_t mode, H, W, use_depth;
+  float rgb_boundary_threshold; /* 0.01 */
+  float alpha;                  /* rgbd mixing weight, 0.95 */
+  float huber_delta;            /* 0.01 */
+  float loss_scale;             /* multiplies the loss and all gradients (upstream grad of the scalar) */
+  const float* image;    /* f32[3,H,W] rendered */
+  const float* depth;    /* f32[1,H,W] rendered, null unless use_depth */
+  const float* opacity;  /* f32[1,H,W] rendered */
+  const float* gt_image; /* f32[3,H,W] */
+  const float* gt_depth; /* f32[1,H,W] or null */
+  const float* grad_mask;/* f32[1,H,W] (Camera.grad_mask) or null = all ones */
+  const float* exposure_a; /* device f32[1] */
+  const float* exposure_b; /* device f32[1] */
+} mgs_loss_args;
+/* out_loss: device f32[1]; out_dab: device f32[2] (dL/da, dL/db); grads may be null to skip backward. */
+int mgs_loss_fwd_bwd(const mgs_loss_args* args, float* out_loss, float* out_dab,
+                     float* dL_dimage, float* dL_ddepth, void* scratch, size_t scratch_bytes, void* stream);
+size_t mgs_loss_scratch_bytes(int32_t H, int32_t W);
+
+/* ---- fused Adam (torch.optim.Adam as configured at gaussian_splatting/scene/gaussian_model.py:285,
+ *      utils/slam_frontend.py:453): multi-tensor, per-group lr, eps outside the bias-corrected sqrt. ---- */
+typedef struct mgs_adam_group {
+  float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+  int64_t numel; float lr;
+} mgs_adam_group;
+int mgs_adam_step(const mgs_adam_group* groups /* host array */, int32_t n_groups, int32_t step /* t>=1 */,
+                  float beta1, float beta2, float eps, void* stream);
+
+/* ---- simple-knn: replaces simple_knn._C.distCUDA2 (submodules/simple-knn/spatial.cu:15-26,
+ *      simple_knn.cu:46-222): mean squared distance to the three nearest other points. ---- */
+size_t mgs_knn_workspace_bytes(int32_t P);
+int mgs_knn_dist2(int32_t P, const float* points /* f32[P,3] */, float* mean_dist2 /* f32[P] */,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MONOGS_B200_H_ */

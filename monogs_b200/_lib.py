@@ -1,0 +1,104 @@
+"""ctypes binding of libmonogs_b200.so (include/monogs_b200.h).
+
+The library is the product; there is no CPU or eager fallback.  Importing this module on a machine where
+the shared object has not been built raises, and every call maps a non-zero status to RuntimeError with
+the library's own message (the reference raises RuntimeError through AT_ERROR,
+submodules/diff-gaussian-rasterization/rasterize_points.cu:58-65).
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libmonogs_b200.so")
+
+GRAD_MEANS3D, GRAD_COLOR, GRAD_OPACITY, GRAD_COV, GRAD_TAU, GRAD_MEANS2D = 1, 2, 4, 8, 16, 32
+GRAD_ALL = 63
+LOSS_TRACK_L1, LOSS_TRACK_HUBER, LOSS_MAP_L1 = 0, 1, 2
+
+
+class MgsView(C.Structure):
+    _fields_ = [
+        ("image_height", C.c_int32), ("image_width", C.c_int32),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float),
+        ("sh_degree", C.c_int32), ("sh_coeffs", C.c_int32), ("prefiltered", C.c_int32),
+        ("bg", C.c_void_p), ("viewmatrix", C.c_void_p), ("projmatrix", C.c_void_p),
+        ("projmatrix_raw", C.c_void_p), ("campos", C.c_void_p),
+    ]
+
+
+class MgsLossArgs(C.Structure):
+    _fields_ = [
+        ("mode", C.c_int32), ("H", C.c_int32), ("W", C.c_int32), ("use_depth", C.c_int32),
+        ("rgb_boundary_threshold", C.c_float), ("alpha", C.c_float), ("huber_delta", C.c_float),
+        ("loss_scale", C.c_float),
+        ("image", C.c_void_p), ("depth", C.c_void_p), ("opacity", C.c_void_p), ("gt_image", C.c_void_p),
+        ("gt_depth", C.c_void_p), ("grad_mask", C.c_void_p), ("exposure_a", C.c_void_p), ("exposure_b", C.c_void_p),
+    ]
+
+
+class MgsAdamGroup(C.Structure):
+    _fields_ = [
+        ("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+        ("numel", C.c_int64), ("lr", C.c_float),
+    ]
+
+
+_P, _I32, _I64, _U32, _F, _SZ = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_float, C.c_size_t
+_VP = C.POINTER(MgsView)
+
+# name -> (restype, argtypes); the not-gpu tests check this table against the header's declarations
+SIGNATURES = {
+    "mgs_last_error_string": (C.c_char_p, []),
+    "mgs_version": (C.c_int, []),
+    "mgs_raster_workspace_bytes": (_SZ, [_I32, _I32, _I32, _I64]),
+    "mgs_raster_preprocess": (C.c_int, [_VP, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P, _P]),
+    "mgs_raster_render": (C.c_int, [_VP, _I32, _P, _P, _P, _SZ, _I64, _P, _P, _P, _P, _P]),
+    "mgs_raster_query": (C.c_int, [_P, C.POINTER(_I32), C.POINTER(_I32), _P]),
+    "mgs_raster_backward": (C.c_int, [_VP, _I32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _P,
+                                      _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "mgs_raster_backward_scratch_bytes": (_SZ, [_I32]),
+    "mgs_raster_backward_pose": (C.c_int, [_VP, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _P,
+                                           _P, _P, _P]),
+    "mgs_raster_backward_pose_scratch_bytes": (_SZ, [_I32, _I32, _I32]),
+    "mgs_sketch_reduce": (C.c_int, [_P, _I32, _I32, _I32, _I32, _P, _P, _P]),
+    "mgs_mark_visible": (C.c_int, [_I32, _P, _P, _P, _P, _P]),
+    "mgs_loss_fwd_bwd": (C.c_int, [C.POINTER(MgsLossArgs), _P, _P, _P, _P, _P, _SZ, _P]),
+    "mgs_loss_scratch_bytes": (_SZ, [_I32, _I32]),
+    "mgs_adam_step": (C.c_int, [C.POINTER(MgsAdamGroup), _I32, _I32, _F, _F, _F, _P]),
+    "mgs_knn_workspace_bytes": (_SZ, [_I32]),
+    "mgs_knn_dist2": (C.c_int, [_I32, _P, _P, _P, _SZ, _P]),
+    "mgs_pose_update": (C.c_int, [_P, _P, _P, _P, _F, _P]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load the shared object once; fail loudly if it is missing (no fallback path exists)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a).  monogs_b200 has no CPU or eager fallback.")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            if os.environ.get("MGS_DEV_PARTIAL") and not hasattr(L, name):
+                continue
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().mgs_last_error_string().decode("utf-8", "replace")
+        raise RuntimeError(f"{what} failed (status {rc}): {msg}")
+
+
+def ptr(t):
+    """data pointer of a torch tensor, or None (-> NULL) for an absent / empty optional."""
+    if t is None or t.numel() == 0:
+        return None
+    return C.c_void_p(t.data_ptr())

@@ -1,0 +1,142 @@
+// Per-tile alpha blend, forward (replaces renderCUDA, forward.cu:263-392).
+//
+// One CTA per 16x16 tile, 256 threads, each warp owns an 8x4 pixel patch so that a small splat touches
+// few warps.  The tile's packed 48-B records are contiguous after the sort, so batches of 256 records
+// (12 KB) are streamed global->shared with cp.async.bulk (TMA 1-D, UBLKCP) into a two-stage ring tracked
+// by mbarriers; one elected thread issues the copies.  Early termination is decided per warp with a
+// ballot and per CTA with __syncthreads_count, like the reference's block vote.
+#include "launchers.h"
+
+namespace mgs {
+
+constexpr int FWD_BATCH = 256;
+constexpr int FWD_STAGES = 2;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+
+__global__ void __launch_bounds__(256)
+blend_forward_kernel(const int W, const int H, const int gx,
+                     const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
+                     const float* __restrict__ bg,
+                     float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
+                     float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
+                     int32_t* __restrict__ n_touched) {
+  __shared__ __align__(128) SplatRec stage[FWD_STAGES][FWD_BATCH];
+  __shared__ __align__(8) uint64_t full_bar[FWD_STAGES];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tile = blockIdx.x;
+  const int tx = tile % gx, ty = tile / gx;
+  const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
+  const int py = ty * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = px < W && py < H;
+  const float pxf = (float)px, pyf = (float)py;
+
+  const uint2 range = ranges[tile];
+  const int n = (int)(range.y - range.x);
+  const int rounds = (n + FWD_BATCH - 1) / FWD_BATCH;
+  const SplatRec* src = recs + range.x;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < FWD_STAGES; s++) mbar_init(&full_bar[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid == 0 && rounds > 0) {
+    const uint32_t bytes = (uint32_t)min(n, FWD_BATCH) * sizeof(SplatRec);
+    mbar_expect_tx(&full_bar[0], bytes);
+    bulk_g2s(&stage[0][0], src, bytes, &full_bar[0]);
+  }
+
+  bool done = !inside;
+  float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
+  uint32_t last_contributor = 0;
+
+  for (int i = 0; i < rounds; i++) {
+    // CTA vote; also guarantees every warp left the stage that the next copy overwrites
+    if (__syncthreads_count(done) == TILE_PIX) {
+      if (tid == 0) mbar_wait(&full_bar[i & 1], (i >> 1) & 1);  // never exit with a bulk copy in flight
+      break;
+    }
+    if (tid == 0 && i + 1 < rounds) {
+      const int s = (i + 1) & 1;
+      const uint32_t bytes = (uint32_t)min(n - (i + 1) * FWD_BATCH, FWD_BATCH) * sizeof(SplatRec);
+      mbar_expect_tx(&full_bar[s], bytes);
+      bulk_g2s(&stage[s][0], src + (size_t)(i + 1) * FWD_BATCH, bytes, &full_bar[s]);
+    }
+    mbar_wait(&full_bar[i & 1], (i >> 1) & 1);
+    const float4* rec4 = reinterpret_cast<const float4*>(&stage[i & 1][0]);
+    const int cnt = min(FWD_BATCH, n - i * FWD_BATCH);
+    const uint32_t base = (uint32_t)i * FWD_BATCH;
+    for (int j = 0; j < cnt; j++) {
+      if (__ballot_sync(0xffffffffu, !done) == 0u) break;
+      const float4 g0 = rec4[3 * j + 0];  // x, y, depth, id
+      const float4 g1 = rec4[3 * j + 1];  // conic xyz, opacity
+      const float dx = g0.x - pxf, dy = g0.y - pyf;
+      const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
+      bool valid = !done && !(power > 0.0f);
+      const float alpha = min(0.99f, g1.w * expf(power));
+      valid = valid && !(alpha < 1.0f / 255.0f);
+      const float test_T = T * (1 - alpha);
+      if (valid && test_T < 0.0001f) { done = true; valid = false; }
+      const unsigned touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
+      if (valid) {
+        const float4 g2 = rec4[3 * j + 2];
+        C0 += g2.x * alpha * T;
+        C1 += g2.y * alpha * T;
+        C2 += g2.z * alpha * T;
+        D += g0.z * alpha * T;
+        T = test_T;
+        last_contributor = base + j + 1;
+      }
+      if (touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
+    }
+  }
+
+  if (inside) {
+    const size_t pix = (size_t)py * W + px;
+    const size_t plane = (size_t)W * H;
+    final_T[pix] = T;
+    n_contrib[pix] = last_contributor;
+    out_color[pix] = C0 + T * bg[0];
+    out_color[plane + pix] = C1 + T * bg[1];
+    out_color[2 * plane + pix] = C2 + T * bg[2];
+    out_depth[pix] = D;
+    out_opacity[pix] = 1 - T;
+  }
+}
+
+int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
+                         float* out_opacity, int32_t* n_touched, cudaStream_t s) {
+  const int tiles = v.gx * v.gy;
+  blend_forward_kernel<<<tiles, 256, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges),
+                                             ws_ptr<SplatRec>(ws, L.records), v.bg,
+                                             ws_ptr<float>(ws, L.final_T), ws_ptr<uint32_t>(ws, L.n_contrib),
+                                             out_color, out_depth, out_opacity, n_touched);
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
+}
+
+}  // namespace mgs

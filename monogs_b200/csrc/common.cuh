@@ -1,0 +1,159 @@
+// Shared device helpers, the workspace layout and error plumbing for libmonogs_b200.
+// Reference paths are relative to /root/reference/submodules/diff-gaussian-rasterization/cuda_rasterizer.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include "../../include/monogs_b200.h"
+
+namespace mgs {
+
+constexpr int TILE_X = 16;   // config.h:16-17 — the tile size is part of the parity contract (keys, ranges)
+constexpr int TILE_Y = 16;
+constexpr int TILE_PIX = TILE_X * TILE_Y;
+
+// ---- error plumbing -------------------------------------------------------------------------
+void set_error(const char* fmt, ...);
+#define MGS_CUDA_TRY(expr)                                                              \
+  do {                                                                                  \
+    cudaError_t e__ = (expr);                                                           \
+    if (e__ != cudaSuccess) {                                                           \
+      mgs::set_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__,               \
+                     cudaGetErrorString(e__));                                          \
+      return MGS_ECUDA;                                                                 \
+    }                                                                                   \
+  } while (0)
+#define MGS_LAUNCH_CHECK() MGS_CUDA_TRY(cudaGetLastError())
+
+// ---- per-instance record: what a tile's blend loop consumes, contiguous per tile after the sort ----
+// 48 B, 16-B aligned so a tile's list [start,end) is one legal cp.async.bulk source.
+struct __align__(16) SplatRec {
+  float x, y, depth; uint32_t id;       // pixel-space mean, view depth (forward.cu:254), Gaussian index
+  float cx, cy, cz, opacity;            // conic (inverse 2D covariance) + opacity (forward.cu:257)
+  float r, g, b, pad;                   // colour after SH evaluation / precomputed
+};
+static_assert(sizeof(SplatRec) == 48, "SplatRec must stay 48 bytes");
+
+struct WsHeader {
+  uint32_t num_rendered;   // last element of the inclusive scan (rasterizer_impl.cu:284)
+  uint32_t overflow;       // 1 when num_rendered > R_cap
+  uint32_t r_used;         // min(num_rendered, R_cap): instances actually binned
+  uint32_t pad[61];
+};
+static_assert(sizeof(WsHeader) == 256, "header is one 256-B slot");
+
+// Host-side view of the workspace.  Everything backward needs lives at offsets that do not depend on
+// R_cap (header, per-Gaussian state, image state, then the records), so backward never needs R_cap.
+struct WsLayout {
+  size_t header, depths, means2D, conic_opacity, rgb4, tiles_touched, point_offsets;
+  size_t final_T, n_contrib, ranges, records;
+  size_t keys_in, keys_out, vals_in, vals_out, scan_tmp, sort_tmp;
+  size_t scan_tmp_bytes, sort_tmp_bytes;
+  size_t total;
+};
+// needs a CUDA device only for the two CUB size queries
+int ws_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, WsLayout* out);
+
+template <typename T> __host__ __device__ inline T* ws_ptr(void* base, size_t off) {
+  return reinterpret_cast<T*>(reinterpret_cast<char*>(base) + off);
+}
+template <typename T> __host__ __device__ inline const T* ws_ptr(const void* base, size_t off) {
+  return reinterpret_cast<const T*>(reinterpret_cast<const char*>(base) + off);
+}
+
+// ---- small column-major 3x3 (m[c][r]); the product and transpose follow the exact expression order of
+//      the matrix type the reference kernels use, so fp32 contraction yields the same bits ----
+struct M3 {
+  float m[3][3];
+  __device__ __forceinline__ float* operator[](int c) { return m[c]; }
+  __device__ __forceinline__ const float* operator[](int c) const { return m[c]; }
+};
+__device__ __forceinline__ M3 m3_cols(float a0, float a1, float a2, float b0, float b1, float b2,
+                                      float c0, float c1, float c2) {
+  M3 r;
+  r.m[0][0] = a0; r.m[0][1] = a1; r.m[0][2] = a2;
+  r.m[1][0] = b0; r.m[1][1] = b1; r.m[1][2] = b2;
+  r.m[2][0] = c0; r.m[2][1] = c1; r.m[2][2] = c2;
+  return r;
+}
+__device__ __forceinline__ M3 m3_mul(const M3& A, const M3& B) {
+  M3 R;
+#pragma unroll
+  for (int c = 0; c < 3; c++)
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+      R.m[c][r] = A.m[0][r] * B.m[c][0] + A.m[1][r] * B.m[c][1] + A.m[2][r] * B.m[c][2];
+  return R;
+}
+__device__ __forceinline__ M3 m3_t(const M3& A) {
+  M3 R;
+#pragma unroll
+  for (int c = 0; c < 3; c++)
+#pragma unroll
+    for (int r = 0; r < 3; r++) R.m[c][r] = A.m[r][c];
+  return R;
+}
+
+// ---- point transforms with the reference's accumulation order (auxiliary.h:58-87) ----
+__device__ __forceinline__ float3 xform4x3(const float3& p, const float* __restrict__ mat) {
+  float3 t = {
+      mat[0] * p.x + mat[4] * p.y + mat[8] * p.z + mat[12],
+      mat[1] * p.x + mat[5] * p.y + mat[9] * p.z + mat[13],
+      mat[2] * p.x + mat[6] * p.y + mat[10] * p.z + mat[14],
+  };
+  return t;
+}
+__device__ __forceinline__ float4 xform4x4(const float3& p, const float* __restrict__ mat) {
+  float4 t = {
+      mat[0] * p.x + mat[4] * p.y + mat[8] * p.z + mat[12],
+      mat[1] * p.x + mat[5] * p.y + mat[9] * p.z + mat[13],
+      mat[2] * p.x + mat[6] * p.y + mat[10] * p.z + mat[14],
+      mat[3] * p.x + mat[7] * p.y + mat[11] * p.z + mat[15]};
+  return t;
+}
+
+// NDC -> pixel; evaluated in double like the reference (auxiliary.h:41-44).
+__device__ __forceinline__ float ndc_to_pix(float v, int S) { return ((v + 1.0) * S - 1.0) * 0.5; }
+
+// Tile rectangle of a splat (auxiliary.h:46-56): float division, truncation, clamp to the grid.
+__device__ __forceinline__ void tile_rect(float2 p, int max_radius, int gx, int gy, uint2& rmin, uint2& rmax) {
+  rmin.x = min(gx, max(0, (int)((p.x - max_radius) / TILE_X)));
+  rmin.y = min(gy, max(0, (int)((p.y - max_radius) / TILE_Y)));
+  rmax.x = min(gx, max(0, (int)((p.x + max_radius + TILE_X - 1) / TILE_X)));
+  rmax.y = min(gy, max(0, (int)((p.y + max_radius + TILE_Y - 1) / TILE_Y)));
+}
+
+// SH basis constants (auxiliary.h:21-39)
+__device__ constexpr float kSH0 = 0.28209479177387814f;
+__device__ constexpr float kSH1 = 0.4886025119029199f;
+__device__ constexpr float kSH2[5] = {1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f,
+                                      -1.0925484305920792f, 0.5462742152960396f};
+__device__ constexpr float kSH3[7] = {-0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f,
+                                      0.3731763325901154f, -0.4570457994644658f, 1.445305721320277f,
+                                      -0.5900435899266435f};
+
+struct ViewConst {  // by-value kernel parameter: scalars + the pointers of mgs_view
+  int W, H, gx, gy;
+  float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
+  int D, M, prefiltered;
+  const float* bg; const float* view; const float* proj; const float* proj_raw; const float* campos;
+};
+inline ViewConst make_view_const(const mgs_view* v) {
+  ViewConst c;
+  c.W = v->image_width; c.H = v->image_height;
+  c.gx = (c.W + TILE_X - 1) / TILE_X; c.gy = (c.H + TILE_Y - 1) / TILE_Y;
+  c.tanfovx = v->tanfovx; c.tanfovy = v->tanfovy;
+  c.focal_y = c.H / (2.0f * v->tanfovy);   // rasterizer_impl.cu:225-226
+  c.focal_x = c.W / (2.0f * v->tanfovx);
+  c.scale_modifier = v->scale_modifier;
+  c.D = v->sh_degree; c.M = v->sh_coeffs; c.prefiltered = v->prefiltered;
+  c.bg = v->bg; c.view = v->viewmatrix; c.proj = v->projmatrix; c.proj_raw = v->projmatrix_raw;
+  c.campos = v->campos;
+  return c;
+}
+
+// number of significant bits of the tile id (rasterizer_impl.cu:35-50)
+// — the reference's bisection returns the bit length of n (and 1 for n == 0).
+inline uint32_t tile_id_bits(uint32_t n) { return n ? 32u - (uint32_t)__builtin_clz(n) : 1u; }
+
+}  // namespace mgs

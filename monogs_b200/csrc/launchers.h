@@ -1,0 +1,31 @@
+// Host-side launch functions shared between the translation units of libmonogs_b200.
+#pragma once
+#include "common.cuh"
+
+namespace mgs {
+
+const char* get_error();
+
+int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
+                      const float* colors_precomp, const float* scales, const float* rotations,
+                      const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s);
+int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
+                   const WsLayout& L, int64_t R_cap, cudaStream_t s);
+int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
+                         float* out_opacity, int32_t* n_touched, cudaStream_t s);
+
+struct BackwardArgs {
+  ViewConst v; int P; uint32_t grad_mask;
+  const float *means3D, *shs, *colors_precomp, *scales, *rotations, *cov3D_precomp;
+  const int32_t* radii; const void* ws; WsLayout L;
+  void* scratch; size_t scratch_bytes;
+  const float *dL_dcolor_img, *dL_ddepth_img;
+  float *dL_dmeans3D, *dL_dmeans2D, *dL_dcolors_or_sh, *dL_dopacity, *dL_dscales, *dL_drotations, *dL_dcov3D;
+  float *dL_dtau_sum, *dL_dtau_pg;
+  // sketch mode (sketch_dim > 0): per-pixel row routing, output sketch_dtau[d,6]
+  int sketch_dim; const int32_t* sketch_indices; float* sketch_dtau;
+};
+int launch_backward(const BackwardArgs& a, cudaStream_t s);
+size_t backward_scratch_bytes(int P, int sketch_dim);
+
+}  // namespace mgs

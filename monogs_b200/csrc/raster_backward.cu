@@ -1,0 +1,344 @@
+// Full backward of the rasterizer (mapping path: every Gaussian gradient + pose tangent).
+// Replaces BACKWARD::render (backward.cu:800-1027) and BACKWARD::preprocess (backward.cu:154-361,433-567).
+//
+// blend_backward_full: one CTA per tile, warp = 8x4 pixel patch, back-to-front over the tile's packed
+// records (streamed with cp.async.bulk).  The reference pays >=11 block barriers per Gaussian per tile for
+// a 256-thread tree reduction; here each warp that has at least one contributing lane reduces its 12
+// partials with a 17-shuffle transposing butterfly, lanes add the warp totals into a per-batch shared
+// accumulator, and after the batch every thread flushes one Gaussian with three 16-byte vector atomics.
+// Two block barriers per 256 Gaussians.
+#include "launchers.h"
+#include "gaussian_backward.cuh"
+
+namespace mgs {
+
+// per-Gaussian screen-space gradient accumulator (scratch, zeroed per call): 3 x float4
+struct __align__(16) G2DGrad {
+  float mx, my, cx, cy;     // dL/dmean2D (ndc-scaled, backward.cu:877-878), dL/dconic xx, xy
+  float cw, op, dd, pad0;   // dL/dconic yy, dL/dopacity, dL/ddepth
+  float r, g, b, pad1;      // dL/dcolor
+};
+static_assert(sizeof(G2DGrad) == 48, "G2DGrad is 48 bytes");
+
+constexpr int BWD_BATCH = 256;
+
+__device__ __forceinline__ uint32_t smem_u32b(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init_b(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32b(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx_b(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32b(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_b(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(smem_u32b(dst)), "l"(src), "r"(bytes), "r"(smem_u32b(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_b(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAITB_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONEB_%=;\n"
+      "bra WAITB_%=;\n"
+      "DONEB_%=:\n"
+      "}\n" ::"r"(smem_u32b(bar)), "r"(parity) : "memory");
+}
+
+// Sum 16 per-lane values across the warp; afterwards lane l (both lanes of each pair) holds the total of
+// value index l>>1.  8+4+2+1+1 = 16 shuffles instead of 16*5.
+__device__ __forceinline__ float warp_reduce16_transpose(float (&v)[16], int lane) {
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const bool hi = lane & 16;
+    const float keep = hi ? v[i + 8] : v[i], send = hi ? v[i] : v[i + 8];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const bool hi = lane & 8;
+    const float keep = hi ? v[i + 4] : v[i], send = hi ? v[i] : v[i + 4];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+  }
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    const bool hi = lane & 4;
+    const float keep = hi ? v[i + 2] : v[i], send = hi ? v[i] : v[i + 2];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+  }
+  {
+    const bool hi = lane & 2;
+    const float keep = hi ? v[1] : v[0], send = hi ? v[0] : v[1];
+    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+  }
+  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+
+__global__ void __launch_bounds__(256)
+blend_backward_full_kernel(const int W, const int H, const int gx,
+                           const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
+                           const float* __restrict__ bg, const float* __restrict__ final_T,
+                           const uint32_t* __restrict__ n_contrib,
+                           const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth,
+                           G2DGrad* __restrict__ g2d) {
+  __shared__ __align__(128) SplatRec stage[2][BWD_BATCH];
+  __shared__ __align__(16) float acc[BWD_BATCH * 12];
+  __shared__ __align__(8) uint64_t full_bar[2];
+  __shared__ int s_max_contrib;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tile = blockIdx.x;
+  const int tx = tile % gx, ty = tile / gx;
+  const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
+  const int py = ty * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = px < W && py < H;
+  const size_t pix = (size_t)py * W + px, plane = (size_t)W * H;
+  const float pxf = (float)px, pyf = (float)py;
+  const uint2 range = ranges[tile];
+
+  const float T_final = inside ? final_T[pix] : 0.f;
+  const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+  float dpx0 = 0.f, dpx1 = 0.f, dpx2 = 0.f, dpd = 0.f;
+  if (inside) {
+    dpx0 = dL_dpix[pix]; dpx1 = dL_dpix[plane + pix]; dpx2 = dL_dpix[2 * plane + pix];
+    dpd = dL_dpix_depth[pix];
+  }
+  if (tid == 0) {
+    s_max_contrib = 0;
+    mbar_init_b(&full_bar[0], 1); mbar_init_b(&full_bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  {
+    int m = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0 && m > 0) atomicMax(&s_max_contrib, m);
+  }
+  __syncthreads();
+  // nothing behind the deepest contributor of this tile can receive gradient (it would be skipped by
+  // `contributor >= last_contributor`, backward.cu:919), so the walk starts there
+  const int n = min(s_max_contrib, (int)(range.y - range.x));
+  const int rounds = (n + BWD_BATCH - 1) / BWD_BATCH;
+  const SplatRec* src = recs + range.x;
+
+  auto issue = [&](int i) {  // batch i covers list positions [lo, hi), walked from hi-1 down to lo
+    const int hi = n - i * BWD_BATCH, lo = max(0, hi - BWD_BATCH);
+    const uint32_t bytes = (uint32_t)(hi - lo) * sizeof(SplatRec);
+    mbar_expect_tx_b(&full_bar[i & 1], bytes);
+    bulk_g2s_b(&stage[i & 1][0], src + lo, bytes, &full_bar[i & 1]);
+  };
+  if (tid == 0 && rounds > 0) issue(0);
+
+  float T = T_final;
+  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ard = 0.f;       // accum_rec colour / depth
+  float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f, last_alpha = 0.f;
+  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+  const float bg_dot_dpixel = bg[0] * dpx0 + bg[1] * dpx1 + bg[2] * dpx2;
+
+  for (int i = 0; i < rounds; i++) {
+    // zero this thread's accumulator slot; the barrier also retires all reads of the other stage
+#pragma unroll
+    for (int k = 0; k < 3; k++) reinterpret_cast<float4*>(acc)[tid * 3 + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    __syncthreads();
+    if (tid == 0 && i + 1 < rounds) issue(i + 1);
+    mbar_wait_b(&full_bar[i & 1], (i >> 1) & 1);
+    const int hi = n - i * BWD_BATCH, lo = max(0, hi - BWD_BATCH);
+    const int cnt = hi - lo;
+    const float4* rec4 = reinterpret_cast<const float4*>(&stage[i & 1][0]);
+    for (int j = cnt - 1; j >= 0; j--) {
+      const int contributor = lo + j;  // list position of this Gaussian
+      const float4 g0 = rec4[3 * j + 0];
+      const float4 g1 = rec4[3 * j + 1];
+      const float dx = g0.x - pxf, dy = g0.y - pyf;
+      const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
+      const float G = expf(power);
+      const float alpha = min(0.99f, g1.w * G);
+      const bool skip = !inside || contributor >= last_contributor || power > 0.0f || alpha < 1.0f / 255.0f;
+      if (__ballot_sync(0xffffffffu, !skip) == 0u) continue;
+      float v[16];
+#pragma unroll
+      for (int k = 0; k < 16; k++) v[k] = 0.f;
+      if (!skip) {
+        const float4 g2 = rec4[3 * j + 2];
+        T = T / (1.f - alpha);
+        const float dchannel_dcolor = alpha * T;
+        float dL_dalpha = 0.0f;
+        ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = g2.x; dL_dalpha += (g2.x - ar0) * dpx0;
+        ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = g2.y; dL_dalpha += (g2.y - ar1) * dpx1;
+        ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = g2.z; dL_dalpha += (g2.z - ar2) * dpx2;
+        ard = last_alpha * ld + (1.f - last_alpha) * ard; ld = g0.z; dL_dalpha += (g0.z - ard) * dpd;
+        dL_dalpha *= T;
+        last_alpha = alpha;
+        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+        const float dL_dG = g1.w * dL_dalpha;   // clamp at 0.99 deliberately ignored (Q6)
+        const float gdx = G * dx, gdy = G * dy;
+        const float dG_ddelx = -gdx * g1.x - gdy * g1.y;
+        const float dG_ddely = -gdy * g1.z - gdx * g1.y;
+        v[0] = dL_dG * dG_ddelx * ddelx_dx;
+        v[1] = dL_dG * dG_ddely * ddely_dy;
+        v[2] = -0.5f * gdx * dx * dL_dG;
+        v[3] = -0.5f * gdx * dy * dL_dG;
+        v[4] = -0.5f * gdy * dy * dL_dG;
+        v[5] = G * dL_dalpha;
+        v[6] = dchannel_dcolor * dpd;
+        v[8] = dchannel_dcolor * dpx0;
+        v[9] = dchannel_dcolor * dpx1;
+        v[10] = dchannel_dcolor * dpx2;
+      }
+      const float tot = warp_reduce16_transpose(v, lane);
+      if (!(lane & 1) && lane < 24) atomicAdd(&acc[j * 12 + (lane >> 1)], tot);
+    }
+    __syncthreads();
+    if (tid < cnt) {
+      const float4 a0 = reinterpret_cast<const float4*>(acc)[tid * 3 + 0];
+      const float4 a1 = reinterpret_cast<const float4*>(acc)[tid * 3 + 1];
+      const float4 a2 = reinterpret_cast<const float4*>(acc)[tid * 3 + 2];
+      const uint32_t id = __float_as_uint(rec4[3 * tid + 0].w);
+      float4* dst = reinterpret_cast<float4*>(g2d + id);
+      if (a0.x != 0.f || a0.y != 0.f || a0.z != 0.f || a0.w != 0.f) atomicAdd(dst + 0, a0);
+      if (a1.x != 0.f || a1.y != 0.f || a1.z != 0.f) atomicAdd(dst + 1, a1);
+      if (a2.x != 0.f || a2.y != 0.f || a2.z != 0.f) atomicAdd(dst + 2, a2);
+    }
+    // the next iteration's zeroing touches only this thread's own slot, and its barrier orders the flush
+    // reads of rec4 before stage reuse two iterations later
+  }
+}
+
+
+// Block-wide sum of a 6-vector, one atomicAdd per block per component.
+__device__ __forceinline__ void block_add6(float (&t)[6], float* __restrict__ out6) {
+  __shared__ float part[8][6];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    float x = t[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) part[warp][k] = x;
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    float x = 0.f;
+    const int nw = (blockDim.x + 31) >> 5;
+    for (int w = 0; w < nw; w++) x += part[w][threadIdx.x];
+    if (x != 0.f) atomicAdd(&out6[threadIdx.x], x);
+  }
+}
+
+// K9 + K10 fused: one thread per Gaussian, screen-space gradients -> all parameter gradients + pose tangent.
+__global__ void __launch_bounds__(256)
+preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
+                           const float* __restrict__ means3D, const float* __restrict__ shs,
+                           const float* __restrict__ colors_precomp, const float* __restrict__ scales,
+                           const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
+                           const int32_t* __restrict__ radii, const float4* __restrict__ rgb4,
+                           const G2DGrad* __restrict__ g2d,
+                           float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dmeans2D,
+                           float* __restrict__ dL_dcolors_or_sh, float* __restrict__ dL_dopacity,
+                           float* __restrict__ dL_dscales, float* __restrict__ dL_drotations,
+                           float* __restrict__ dL_dcov3D, float* __restrict__ tau_sum, float* __restrict__ tau_pg) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (idx < P) {
+    const bool vis = radii[idx] > 0;
+    float3 dmean = {0.f, 0.f, 0.f}, dscale = {0.f, 0.f, 0.f};
+    float4 drot = {0.f, 0.f, 0.f, 0.f};
+    float dcov6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    G2DGrad gg;
+    gg.mx = gg.my = gg.cx = gg.cy = gg.cw = gg.op = gg.dd = gg.r = gg.g = gg.b = 0.f;
+    const int Msh = v.M;
+    float* dsh = (shs != nullptr && (mask & MGS_GRAD_COLOR)) ? dL_dcolors_or_sh + (size_t)idx * Msh * 3 : nullptr;
+    if (vis) {
+      const float4* src = reinterpret_cast<const float4*>(g2d + idx);
+      const float4 a0 = src[0], a1 = src[1], a2 = src[2];
+      gg.mx = a0.x; gg.my = a0.y; gg.cx = a0.z; gg.cy = a0.w; gg.cw = a1.x; gg.op = a1.y; gg.dd = a1.z;
+      gg.r = a2.x; gg.g = a2.y; gg.b = a2.z;
+      const float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+      GaussCtx g;
+      if (cov3D_precomp != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) g.cov6[k] = cov3D_precomp[6 * (size_t)idx + k];
+      } else cov3d_from_scale_rot_b(scales, rotations, idx, v.scale_modifier, g.cov6);
+      gauss_ctx_init(g, v, p);
+      ConicChainOut cc;
+      conic_chain(g, v, gg.cx, gg.cy, gg.cw, cc);
+#pragma unroll
+      for (int k = 0; k < 6; k++) { tau[k] = cc.tau[k]; dcov6[k] = cc.dcov6[k]; }
+      dmean = cc.dmean;
+      ProjCtx q;
+      proj_ctx_init(q, v, p);
+      const float3 dm2 = mean2d_to_mean3d(q, v.proj, gg.mx, gg.my);
+      dmean.x += dm2.x; dmean.y += dm2.y; dmean.z += dm2.z;
+      float jx[6], jy[6];
+      mean2d_tau_jac(q, v.proj_raw, jx, jy);
+#pragma unroll
+      for (int k = 0; k < 6; k++) tau[k] += gg.mx * jx[k] + gg.my * jy[k];
+      // depth gradient (backward.cu:546-556)
+      dmean.x += gg.dd * v.view[2]; dmean.y += gg.dd * v.view[6]; dmean.z += gg.dd * v.view[10];
+      tau[2] += gg.dd;
+      tau[3] += gg.dd * q.pC.y;
+      tau[4] += gg.dd * -q.pC.x;
+      if (shs != nullptr) {
+        const uint32_t cm = __float_as_uint(rgb4[idx].w);
+        const float3 dcol = {(cm & 1u) ? 0.f : gg.r, (cm & 2u) ? 0.f : gg.g, (cm & 4u) ? 0.f : gg.b};
+        const float3 dms = sh_backward(v.D, Msh, p, v.campos, shs + (size_t)idx * Msh * 3, dcol, dsh);
+        dmean.x += dms.x; dmean.y += dms.y; dmean.z += dms.z;
+        tau[0] += -dms.x; tau[1] += -dms.y; tau[2] += -dms.z;
+      }
+      if (scales != nullptr && (mask & MGS_GRAD_COV)) cov3d_backward(scales, rotations, idx, v.scale_modifier, dcov6, dscale, drot);
+    } else if (dsh != nullptr) {
+      for (int k = 0; k < 3 * Msh; k++) dsh[k] = 0.f;
+    }
+    if (mask & MGS_GRAD_MEANS3D) { dL_dmeans3D[3 * idx] = dmean.x; dL_dmeans3D[3 * idx + 1] = dmean.y; dL_dmeans3D[3 * idx + 2] = dmean.z; }
+    if (mask & MGS_GRAD_MEANS2D) { dL_dmeans2D[3 * idx] = gg.mx; dL_dmeans2D[3 * idx + 1] = gg.my; dL_dmeans2D[3 * idx + 2] = 0.f; }
+    if (mask & MGS_GRAD_OPACITY) dL_dopacity[idx] = gg.op;
+    if ((mask & MGS_GRAD_COLOR) && shs == nullptr) {
+      dL_dcolors_or_sh[3 * idx] = gg.r; dL_dcolors_or_sh[3 * idx + 1] = gg.g; dL_dcolors_or_sh[3 * idx + 2] = gg.b;
+    }
+    if (mask & MGS_GRAD_COV) {
+      if (scales != nullptr) {
+        dL_dscales[3 * idx] = dscale.x; dL_dscales[3 * idx + 1] = dscale.y; dL_dscales[3 * idx + 2] = dscale.z;
+        reinterpret_cast<float4*>(dL_drotations)[idx] = drot;
+      }
+      if (dL_dcov3D != nullptr) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) dL_dcov3D[6 * (size_t)idx + k] = dcov6[k];
+      }
+    }
+    if (tau_pg != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) tau_pg[6 * (size_t)idx + k] = tau[k];
+    }
+  }
+  if (tau_sum != nullptr) block_add6(tau, tau_sum);
+}
+
+size_t backward_scratch_bytes(int P, int sketch_dim) {
+  (void)sketch_dim;
+  return ((size_t)(P > 0 ? P : 1) * sizeof(G2DGrad) + 255) / 256 * 256 + 256;
+}
+
+int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
+  const ViewConst& v = a.v;
+  const int P = a.P;
+  const size_t need = backward_scratch_bytes(P, 0);
+  if (a.scratch == nullptr || a.scratch_bytes < need) { set_error("backward scratch too small: %zu < %zu", a.scratch_bytes, need); return MGS_ENOSPC; }
+  G2DGrad* g2d = reinterpret_cast<G2DGrad*>(a.scratch);
+  MGS_CUDA_TRY(cudaMemsetAsync(g2d, 0, (size_t)P * sizeof(G2DGrad), s));
+  if (a.dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
+  const int tiles = v.gx * v.gy;
+  blend_backward_full_kernel<<<tiles, 256, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges),
+                                                   ws_ptr<SplatRec>(a.ws, a.L.records), v.bg,
+                                                   ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib),
+                                                   a.dL_dcolor_img, a.dL_ddepth_img, g2d);
+  MGS_LAUNCH_CHECK();
+  preprocess_backward_kernel<<<(P + 255) / 256, 256, 0, s>>>(
+      v, P, a.grad_mask, a.means3D, a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp, a.radii,
+      ws_ptr<float4>(a.ws, a.L.rgb4), g2d, a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dcolors_or_sh, a.dL_dopacity,
+      a.dL_dscales, a.dL_drotations, a.dL_dcov3D, a.dL_dtau_sum, a.dL_dtau_pg);
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
+}
+
+}  // namespace mgs
