@@ -101,19 +101,30 @@ int mgs_raster_backward(const mgs_view* view, int32_t P, uint32_t grad_mask,
                         float* dL_dtau_sum, float* dL_dtau_per_gaussian, void* stream);
 size_t mgs_raster_backward_scratch_bytes(int32_t P);
 
-/* ---- sketch-Jacobian backward: replaces _C.rasterize_gaussians_backward_sketch_jacobian (ext.cpp:48,
- *      rasterize_points.cu:256-378, backward_sketch_jacobian.cu).  Produces SJ[d,6] = for each sketch row
- *      i the pose tangent of sum over pixels with sketch_indices==i of (dL_dout . out), i.e. the quantity
- *      the wrapper keeps (__init__.py:253) without materialising the [P,d,...] buffers. ---- */
-int mgs_raster_backward_sketch(const mgs_view* view, int32_t P, int32_t sketch_dim,
-                               const int32_t* sketch_indices /* i32[H,W], -1 = unused */,
-                               const float* means3D, const float* shs, const float* colors_precomp,
-                               const float* scales, const float* rotations, const float* cov3D_precomp,
-                               const int32_t* radii, const void* workspace, size_t workspace_bytes,
-                               void* scratch, size_t scratch_bytes,
-                               const float* dL_dout_color, const float* dL_dout_depth,
-                               float* sketch_dtau /* f32[d,6] */, void* stream);
-size_t mgs_raster_backward_sketch_scratch_bytes(int32_t P, int32_t sketch_dim);
+/* ---- pose-only backward (tracking) and sketch-Jacobian backward.  Replaces the tracking use of
+ *      _C.rasterize_gaussians_backward (only grad_theta / grad_rho are consumed there because the frontend's
+ *      Gaussians are detached, utils/slam_frontend.py:1799-1800) and
+ *      _C.rasterize_gaussians_backward_sketch_jacobian (ext.cpp:48, rasterize_points.cu:256-378,
+ *      backward_sketch_jacobian.cu).  The screen-space-gradient -> pose-tangent map is linear per Gaussian, so
+ *      each pixel accumulates its own 6-vector: tau_image[k,y,x] (f32[6,H,W], optional) is the pose tangent
+ *      of that pixel's term dL_dout[:,y,x] . out[:,y,x]; dL_dtau_sum (f32[6], optional) is its sum over the
+ *      image = sum over Gaussians of the reference's dL_dtau[P,6] (__init__.py:339-342). ---- */
+int mgs_raster_backward_pose(const mgs_view* view, int32_t P,
+                             const float* means3D, const float* shs, const float* colors_precomp,
+                             const float* scales, const float* rotations, const float* cov3D_precomp,
+                             const int32_t* radii, const void* workspace, size_t workspace_bytes,
+                             void* scratch, size_t scratch_bytes,
+                             const float* dL_dout_color, const float* dL_dout_depth,
+                             float* tau_image, float* dL_dtau_sum, void* stream);
+size_t mgs_raster_backward_pose_scratch_bytes(int32_t P, int32_t W, int32_t H);
+
+/* Sketch rows from a tau image: sketch_dtau[j,i,:] = sum over pixels with sketch_indices[j,y,x] == i of
+ * tau_image[:,y,x]; indices outside [0, sketch_dim) (the reference uses -1) are ignored.  This equals
+ * sum over Gaussians of df_dtau[P,d,6] that the reference wrapper forms per stack j (__init__.py:216-253);
+ * one tau image serves all n_stacks stacks because only the pixel->row routing differs between them. */
+int mgs_sketch_reduce(const float* tau_image, int32_t H, int32_t W, int32_t n_stacks, int32_t sketch_dim,
+                      const int32_t* sketch_indices /* i32[n_stacks,H,W] */,
+                      float* sketch_dtau /* f32[n_stacks,sketch_dim,6] */, void* stream);
 
 /* ---- markVisible: replaces _C.mark_visible (ext.cpp:49, rasterizer_impl.cu:54-66,141-153) ---- */
 int mgs_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -158,6 +169,13 @@ int mgs_adam_step(const mgs_adam_group* groups /* host array */, int32_t n_group
 size_t mgs_knn_workspace_bytes(int32_t P);
 int mgs_knn_dist2(int32_t P, const float* points /* f32[P,3] */, float* mean_dist2 /* f32[P] */,
                   void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- on-device pose update: replaces update_pose (utils/pose_utils.py:88-98, lietorch.SE3.exp).
+ *      T_w2c (f32[4,4] row-major, in/out) <- Exp(rho, theta) @ T_w2c; rho and theta are zeroed; converged_out
+ *      (optional) = |tau|^2 < threshold^2.  Optional outputs: viewmatrix = T^T (utils/camera_utils.py:94-96) and
+ *      projmatrix = viewmatrix @ proj_raw (:98-104), so a tracking iteration needs no host round trip. ---- */
+int mgs_pose_update(float* T_w2c, float* rho, float* theta, const float* proj_raw, float* viewmatrix_out,
+                    float* projmatrix_out, int32_t* converged_out, float converged_threshold, void* stream);
 
 #ifdef __cplusplus
 }

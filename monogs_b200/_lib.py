@@ -67,7 +67,7 @@ SIGNATURES = {
     "mgs_adam_step": (C.c_int, [C.POINTER(MgsAdamGroup), _I32, _I32, _F, _F, _F, _P]),
     "mgs_knn_workspace_bytes": (_SZ, [_I32]),
     "mgs_knn_dist2": (C.c_int, [_I32, _P, _P, _P, _SZ, _P]),
-    "mgs_pose_update": (C.c_int, [_P, _P, _P, _P, _F, _P]),
+    "mgs_pose_update": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _F, _P]),
 }
 
 _lib = None

@@ -9,6 +9,8 @@ namespace mgs {
 int launch_backward_full(const BackwardArgs& a, cudaStream_t s);
 int launch_backward_pose(const BackwardArgs& a, cudaStream_t s);
 size_t backward_pose_scratch_bytes(int P, int W, int H);
+int launch_sketch_reduce(const float* tau_image, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,
+                         float* sketch_dtau, cudaStream_t s);
 }
 
 static int check_view(const mgs_view* v, bool need_raw) {
@@ -163,6 +165,49 @@ int mgs_raster_backward(const mgs_view* view, int32_t P, uint32_t grad_mask, con
   a.dL_dtau_sum = (grad_mask & MGS_GRAD_TAU) ? dL_dtau_sum : nullptr;
   a.dL_dtau_pg = (grad_mask & MGS_GRAD_TAU) ? dL_dtau_per_gaussian : nullptr;
   return launch_backward_full(a, s);
+}
+
+
+size_t mgs_raster_backward_pose_scratch_bytes(int32_t P, int32_t W, int32_t H) { return backward_pose_scratch_bytes(P, W, H); }
+
+int mgs_raster_backward_pose(const mgs_view* view, int32_t P, const float* means3D, const float* shs,
+                             const float* colors_precomp, const float* scales, const float* rotations,
+                             const float* cov3D_precomp, const int32_t* radii, const void* workspace,
+                             size_t workspace_bytes, void* scratch, size_t scratch_bytes, const float* dL_dout_color,
+                             const float* dL_dout_depth, float* tau_image, float* dL_dtau_sum, void* stream) {
+  int rc = check_view(view, true);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (P < 0) { set_error("P < 0"); return MGS_EINVAL; }
+  if (!tau_image && !dL_dtau_sum) { set_error("backward_pose: no output requested"); return MGS_EINVAL; }
+  const size_t npix = (size_t)view->image_width * view->image_height;
+  if (P == 0) {
+    if (dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(dL_dtau_sum, 0, 6 * sizeof(float), s));
+    if (tau_image) MGS_CUDA_TRY(cudaMemsetAsync(tau_image, 0, 6 * npix * sizeof(float), s));
+    return MGS_OK;
+  }
+  if (!means3D || !radii || !workspace || !dL_dout_color || !dL_dout_depth) { set_error("null required input"); return MGS_EINVAL; }
+  if ((rc = check_options(view, shs, colors_precomp, scales, rotations, cov3D_precomp))) return rc;
+  BackwardArgs a;
+  memset(&a, 0, sizeof(a));
+  a.v = make_view_const(view); a.P = P; a.grad_mask = MGS_GRAD_TAU;
+  a.means3D = means3D; a.shs = shs; a.colors_precomp = colors_precomp; a.scales = scales; a.rotations = rotations;
+  a.cov3D_precomp = cov3D_precomp; a.radii = radii; a.ws = workspace;
+  if ((rc = ws_layout(P, view->image_width, view->image_height, 0, &a.L))) return rc;
+  if (workspace_bytes < a.L.total) { set_error("workspace too small"); return MGS_ENOSPC; }
+  a.scratch = scratch; a.scratch_bytes = scratch_bytes;
+  a.dL_dcolor_img = dL_dout_color; a.dL_ddepth_img = dL_dout_depth;
+  a.dL_dtau_sum = dL_dtau_sum; a.sketch_dtau = tau_image;
+  return launch_backward_pose(a, s);
+}
+
+int mgs_sketch_reduce(const float* tau_image, int32_t H, int32_t W, int32_t n_stacks, int32_t sketch_dim,
+                      const int32_t* sketch_indices, float* sketch_dtau, void* stream) {
+  if (!tau_image || !sketch_indices || !sketch_dtau || H <= 0 || W <= 0 || n_stacks <= 0 || sketch_dim <= 0) {
+    set_error("sketch_reduce: bad arguments"); return MGS_EINVAL;
+  }
+  if (sketch_dim > 64) { set_error("sketch_dim must be <= 64 (__init__.py:249)"); return MGS_EINVAL; }
+  return launch_sketch_reduce(tau_image, H, W, n_stacks, sketch_dim, sketch_indices, sketch_dtau, (cudaStream_t)stream);
 }
 
 }  // extern "C"

@@ -1,0 +1,256 @@
+// Fused tracking / mapping loss (forward + backward in one sweep) and fused multi-tensor Adam.
+// Loss semantics: MonoGS utils/slam_utils.py:83-113 (tracking L1 rgb / rgbd), :188-205 + :58-75 +
+// utils/slam_frontend.py:596-598 (per-pixel residual -> Huber -> L2 norm), :224-253 (mapping L1).
+// Adam semantics: torch.optim.Adam(eps=1e-15, betas=(0.9,0.999)) as set up in
+// gaussian_splatting/scene/gaussian_model.py:285 and utils/slam_frontend.py:453.
+#include "launchers.h"
+
+namespace mgs {
+
+struct LossK {
+  int mode, npix, use_depth;
+  float thr, alpha, delta, scale, eps;
+  const float *image, *depth, *opacity, *gt, *gt_depth, *mask, *a, *b;
+};
+
+__device__ __forceinline__ float sgn(float x) { return (float)((x > 0.f) - (x < 0.f)); }
+
+// partial sums per block: [0] loss (L1 modes) or sum of squares (Huber), [1] dL/da, [2] dL/db, [3] depth term
+// pass 0: reductions only (needed first for the Huber norm); pass 1: gradients.  L1 modes do both in one launch.
+template <bool WRITE_GRADS, bool REDUCE>
+__global__ void __launch_bounds__(256)
+loss_kernel(const LossK k, const float* __restrict__ norm_in, double* __restrict__ partials,
+            float* __restrict__ dL_dimage, float* __restrict__ dL_ddepth) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  if (p < k.npix) {
+    const float a_raw = k.a ? k.a[0] : 1.f;
+    const float ea = k.a ? fabsf(a_raw) + k.eps : 1.f;
+    const float eb = k.b ? k.b[0] : 0.f;
+    const float sa = k.a ? sgn(a_raw) : 0.f;
+    const float g0 = k.gt[p], g1 = k.gt[k.npix + p], g2 = k.gt[2 * k.npix + p];
+    float m = (g0 + g1 + g2) > k.thr ? 1.f : 0.f;
+    if (k.mask) m *= k.mask[p];
+    const float op = k.opacity ? k.opacity[p] : 1.f;
+    const float w = (k.mode == MGS_LOSS_MAP_L1) ? 1.f : op;   // mapping loss has no opacity weight
+    const float gt3[3] = {g0, g1, g2};
+    float grad_scale = k.scale;
+    if (k.mode == MGS_LOSS_TRACK_HUBER) {
+      if (WRITE_GRADS) { const float nrm = norm_in[0]; grad_scale = nrm > 0.f ? k.scale / nrm : 0.f; }
+    } else {
+      grad_scale *= (k.use_depth ? k.alpha : 1.f) / (3.f * (float)k.npix);
+    }
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const float img = k.image[c * k.npix + p];
+      const float iab = ea * img + eb;
+      const float r = w * (iab * m - gt3[c] * m);
+      float dr;  // dLoss/dr up to grad_scale
+      if (k.mode == MGS_LOSS_TRACK_HUBER) {
+        const float ar = fabsf(r);
+        float h, dh;
+        if (ar < k.delta) { h = r; dh = 1.f; }
+        else { const float sq = sqrtf(2.f * k.delta * ar - k.delta * k.delta); h = sq * sgn(r); dh = k.delta / sq; }
+        if (REDUCE) acc[0] += h * h;
+        dr = h * dh;
+      } else {
+        if (REDUCE) acc[0] += fabsf(r);
+        dr = sgn(r);
+      }
+      if (WRITE_GRADS) {
+        const float gi = grad_scale * dr * w * m;   // d r / d iab = w*m
+        dL_dimage[c * k.npix + p] = gi * ea;
+        acc[1] += gi * img * sa;
+        acc[2] += gi;
+      }
+    }
+    if (k.use_depth && k.mode != MGS_LOSS_TRACK_HUBER) {
+      const float gd = k.gt_depth[p];
+      float dm = gd > 0.01f ? 1.f : 0.f;
+      if (k.mode == MGS_LOSS_TRACK_L1) dm *= (op > 0.95f) ? 1.f : 0.f;
+      const float d = k.depth[p];
+      const float rd = d * dm - gd * dm;
+      if (REDUCE) acc[3] += fabsf(rd);
+      if (WRITE_GRADS) dL_ddepth[p] = k.scale * (1.f - k.alpha) / (float)k.npix * sgn(rd) * dm;
+    } else if (WRITE_GRADS && dL_ddepth != nullptr) {
+      dL_ddepth[p] = 0.f;
+    }
+  }
+  // deterministic two-level reduction: warp shuffle -> shared -> one double4 per block
+  __shared__ float part[8][4];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int q = 0; q < 4; q++) {
+    float x = acc[q];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) part[warp][q] = x;
+  }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    double x = 0.0;
+#pragma unroll
+    for (int w8 = 0; w8 < 8; w8++) x += (double)part[w8][threadIdx.x];
+    partials[(size_t)blockIdx.x * 4 + threadIdx.x] = x;
+  }
+}
+
+// stage: 0 = Huber norm only (writes norm to out_loss), 1 = final (loss + dab)
+__global__ void __launch_bounds__(256)
+loss_finalize_kernel(const LossK k, const double* __restrict__ partials, const int nblocks, const int stage,
+                     float* __restrict__ out_loss, float* __restrict__ out_dab) {
+  __shared__ double sh[256][4];
+  double acc[4] = {0, 0, 0, 0};
+  for (int i = threadIdx.x; i < nblocks; i += 256)
+#pragma unroll
+    for (int q = 0; q < 4; q++) acc[q] += partials[(size_t)i * 4 + q];
+#pragma unroll
+  for (int q = 0; q < 4; q++) sh[threadIdx.x][q] = acc[q];
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (threadIdx.x < o)
+#pragma unroll
+      for (int q = 0; q < 4; q++) sh[threadIdx.x][q] += sh[threadIdx.x + o][q];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    if (k.mode == MGS_LOSS_TRACK_HUBER) {
+      if (stage == 0) out_loss[0] = (float)sqrt(sh[0][0]);   // un-scaled norm, consumed by the gradient pass
+      else { out_loss[0] = k.scale * out_loss[0]; if (out_dab) { out_dab[0] = (float)sh[0][1]; out_dab[1] = (float)sh[0][2]; } }
+    } else {
+      const double rgb = sh[0][0] / (3.0 * k.npix), dep = sh[0][3] / (double)k.npix;
+      const double l = k.use_depth ? k.alpha * rgb + (1.0 - k.alpha) * dep : rgb;
+      out_loss[0] = (float)(k.scale * l);
+      if (out_dab) { out_dab[0] = (float)sh[0][1]; out_dab[1] = (float)sh[0][2]; }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+constexpr int ADAM_MAX_GROUPS = 16;
+constexpr int ADAM_CHUNK = 2048;   // elements per block (256 threads x 2 float4)
+struct AdamPack {
+  float* p[ADAM_MAX_GROUPS]; const float* g[ADAM_MAX_GROUPS]; float* m[ADAM_MAX_GROUPS]; float* v[ADAM_MAX_GROUPS];
+  long long numel[ADAM_MAX_GROUPS]; float lr[ADAM_MAX_GROUPS]; int chunk_start[ADAM_MAX_GROUPS + 1];
+  int n;
+  float beta1, beta2, eps, bc1, bc2_sqrt;
+};
+
+__device__ __forceinline__ void adam_elem(float& p, const float g, float& m, float& v, const float step_size,
+                                          const AdamPack& a) {
+  m = m + (g - m) * (1.f - a.beta1);                 // exp_avg.lerp_(grad, 1 - beta1)
+  v = v * a.beta2 + (1.f - a.beta2) * g * g;         // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+  const float denom = sqrtf(v) / a.bc2_sqrt + a.eps;
+  p = p - step_size * (m / denom);                   // param.addcdiv_(exp_avg, denom, value=-step_size)
+}
+
+__global__ void __launch_bounds__(256) adam_kernel(const AdamPack a) {
+  int gi = 0;
+  while (gi + 1 < a.n && (int)blockIdx.x >= a.chunk_start[gi + 1]) gi++;
+  const long long base = (long long)(blockIdx.x - a.chunk_start[gi]) * ADAM_CHUNK;
+  const long long n = a.numel[gi];
+  float* __restrict__ p = a.p[gi]; const float* __restrict__ g = a.g[gi];
+  float* __restrict__ m = a.m[gi]; float* __restrict__ v = a.v[gi];
+  const float step_size = a.lr[gi] / a.bc1;
+  const bool vec = ((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0);
+#pragma unroll
+  for (int it = 0; it < ADAM_CHUNK / 1024; it++) {
+    const long long i = base + (long long)it * 1024 + threadIdx.x * 4;
+    if (i >= n) break;
+    if (vec && i + 4 <= n) {
+      float4 P4 = *reinterpret_cast<float4*>(p + i);
+      const float4 G4 = *reinterpret_cast<const float4*>(g + i);
+      float4 M4 = *reinterpret_cast<float4*>(m + i), V4 = *reinterpret_cast<float4*>(v + i);
+      adam_elem(P4.x, G4.x, M4.x, V4.x, step_size, a); adam_elem(P4.y, G4.y, M4.y, V4.y, step_size, a);
+      adam_elem(P4.z, G4.z, M4.z, V4.z, step_size, a); adam_elem(P4.w, G4.w, M4.w, V4.w, step_size, a);
+      *reinterpret_cast<float4*>(p + i) = P4; *reinterpret_cast<float4*>(m + i) = M4; *reinterpret_cast<float4*>(v + i) = V4;
+    } else {
+      for (long long j = i; j < min(i + 4, n); j++) {
+        float pj = p[j], mj = m[j], vj = v[j];
+        adam_elem(pj, g[j], mj, vj, step_size, a);
+        p[j] = pj; m[j] = mj; v[j] = vj;
+      }
+    }
+  }
+}
+
+}  // namespace mgs
+
+using namespace mgs;
+
+extern "C" {
+
+size_t mgs_loss_scratch_bytes(int32_t H, int32_t W) {
+  const size_t nblocks = ((size_t)H * W + 255) / 256;
+  return nblocks * 4 * sizeof(double) + 256;
+}
+
+int mgs_loss_fwd_bwd(const mgs_loss_args* args, float* out_loss, float* out_dab, float* dL_dimage, float* dL_ddepth,
+                     void* scratch, size_t scratch_bytes, void* stream) {
+  if (!args || !out_loss || !scratch) { set_error("loss: null argument"); return MGS_EINVAL; }
+  if (args->H <= 0 || args->W <= 0 || !args->image || !args->gt_image) { set_error("loss: bad image arguments"); return MGS_EINVAL; }
+  if (args->mode < 0 || args->mode > 2) { set_error("loss: unknown mode %d", args->mode); return MGS_EINVAL; }
+  if (args->mode != MGS_LOSS_MAP_L1 && !args->opacity) { set_error("loss: tracking modes need the opacity image"); return MGS_EINVAL; }
+  if (args->use_depth && (!args->depth || !args->gt_depth)) { set_error("loss: use_depth needs depth and gt_depth"); return MGS_EINVAL; }
+  if (args->use_depth && args->mode == MGS_LOSS_TRACK_HUBER) { set_error("loss: the per-pixel rgbd variant raises NotImplementedError in the reference (slam_utils.py:219)"); return MGS_EINVAL; }
+  if (scratch_bytes < mgs_loss_scratch_bytes(args->H, args->W)) { set_error("loss: scratch too small"); return MGS_ENOSPC; }
+  cudaStream_t s = (cudaStream_t)stream;
+  LossK k;
+  k.mode = args->mode; k.npix = args->H * args->W; k.use_depth = args->use_depth;
+  k.thr = args->rgb_boundary_threshold; k.alpha = args->alpha; k.delta = args->huber_delta; k.scale = args->loss_scale;
+  k.eps = 1e-8f;  // Camera.exposure_eps (utils/camera_utils.py:55)
+  k.image = args->image; k.depth = args->depth; k.opacity = args->opacity; k.gt = args->gt_image;
+  k.gt_depth = args->gt_depth; k.mask = args->grad_mask; k.a = args->exposure_a; k.b = args->exposure_b;
+  double* partials = reinterpret_cast<double*>(scratch);
+  const int nblocks = (k.npix + 255) / 256;
+  const bool grads = dL_dimage != nullptr;
+  if (grads && k.use_depth && !dL_ddepth) { set_error("loss: dL_ddepth required with use_depth"); return MGS_EINVAL; }
+  if (k.mode == MGS_LOSS_TRACK_HUBER) {
+    loss_kernel<false, true><<<nblocks, 256, 0, s>>>(k, nullptr, partials, nullptr, nullptr);
+    MGS_LAUNCH_CHECK();
+    loss_finalize_kernel<<<1, 256, 0, s>>>(k, partials, nblocks, 0, out_loss, nullptr);
+    MGS_LAUNCH_CHECK();
+    if (grads) {
+      loss_kernel<true, false><<<nblocks, 256, 0, s>>>(k, out_loss, partials, dL_dimage, dL_ddepth);
+      MGS_LAUNCH_CHECK();
+    } else MGS_CUDA_TRY(cudaMemsetAsync(partials, 0, (size_t)nblocks * 4 * sizeof(double), s));
+    loss_finalize_kernel<<<1, 256, 0, s>>>(k, partials, nblocks, 1, out_loss, out_dab);
+    MGS_LAUNCH_CHECK();
+  } else {
+    if (grads) loss_kernel<true, true><<<nblocks, 256, 0, s>>>(k, nullptr, partials, dL_dimage, dL_ddepth);
+    else loss_kernel<false, true><<<nblocks, 256, 0, s>>>(k, nullptr, partials, nullptr, nullptr);
+    MGS_LAUNCH_CHECK();
+    loss_finalize_kernel<<<1, 256, 0, s>>>(k, partials, nblocks, 1, out_loss, out_dab);
+    MGS_LAUNCH_CHECK();
+  }
+  return MGS_OK;
+}
+
+int mgs_adam_step(const mgs_adam_group* groups, int32_t n_groups, int32_t step, float beta1, float beta2, float eps,
+                  void* stream) {
+  if (!groups || n_groups <= 0 || step < 1) { set_error("adam: bad arguments"); return MGS_EINVAL; }
+  cudaStream_t s = (cudaStream_t)stream;
+  for (int g0 = 0; g0 < n_groups; g0 += ADAM_MAX_GROUPS) {
+    AdamPack a;
+    a.n = 0; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
+    a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
+    a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
+    int chunks = 0;
+    for (int gi = g0; gi < n_groups && gi < g0 + ADAM_MAX_GROUPS; gi++) {
+      const mgs_adam_group& G = groups[gi];
+      if (G.numel < 0 || (G.numel > 0 && (!G.param || !G.grad || !G.exp_avg || !G.exp_avg_sq))) { set_error("adam: group %d has null pointers", gi); return MGS_EINVAL; }
+      if (G.numel == 0) continue;
+      const int j = a.n++;
+      a.p[j] = G.param; a.g[j] = G.grad; a.m[j] = G.exp_avg; a.v[j] = G.exp_avg_sq; a.numel[j] = G.numel; a.lr[j] = G.lr;
+      a.chunk_start[j] = chunks;
+      chunks += (int)((G.numel + ADAM_CHUNK - 1) / ADAM_CHUNK);
+    }
+    a.chunk_start[a.n] = chunks;
+    if (chunks == 0) continue;
+    adam_kernel<<<chunks, 256, 0, s>>>(a);
+    MGS_LAUNCH_CHECK();
+  }
+  return MGS_OK;
+}
+
+}  // extern "C"

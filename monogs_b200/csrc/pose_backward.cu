@@ -1,0 +1,282 @@
+// Pose-only backward (tracking path) and the sketch-Jacobian reduction.
+//
+// The map from a Gaussian's screen-space gradients (dL/dmean2D, dL/dconic, dL/ddepth[, dL/dcolor]) to its
+// pose tangent dL/dtau is LINEAR (backward.cu:154-361, 433-567).  So instead of reducing screen-space
+// gradients over the 256 pixels of every tile for every Gaussian (the reference's dominant cost) and then
+// running the per-Gaussian chain, we
+//   1. build that linear map B_g (6 x NCOL floats) once per visible Gaussian (pose_jacobian_kernel),
+//   2. let every PIXEL apply B_g to its own contribution and accumulate its own 6-vector while it walks its
+//      tile list back to front (blend_backward_pose_kernel) — no cross-thread reduction, no atomics per
+//      Gaussian, no per-Gaussian gradient buffers,
+//   3. sum the per-pixel 6-vectors: over the image for grad_rho/grad_theta (__init__.py:339-342), or per
+//      sketch row for the sketched Jacobian (__init__.py:216-253, backward_sketch_jacobian.cu), where the
+//      SAME tau image serves every stack because only the pixel->row routing differs between stacks.
+#include "launchers.h"
+#include "gaussian_backward.cuh"
+#include "tma.cuh"
+
+namespace mgs {
+
+constexpr int POSE_BATCH = 128;
+
+// B_g layout: NCOL columns (mx, my, cxx, cxy, cyy, depth[, r, g, b]) of 6 floats each, padded to float4s.
+template <int NCOL> struct PoseJac { static constexpr int kFloats = (NCOL * 6 + 3) / 4 * 4; };
+
+template <int NCOL>
+__global__ void __launch_bounds__(256)
+pose_jacobian_kernel(const ViewConst v, const int P, const float* __restrict__ means3D, const float* __restrict__ shs,
+                     const float* __restrict__ scales, const float* __restrict__ rotations,
+                     const float* __restrict__ cov3D_precomp, const int32_t* __restrict__ radii,
+                     const float4* __restrict__ rgb4, float* __restrict__ jac) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= P || !(radii[idx] > 0)) return;
+  constexpr int NF = PoseJac<NCOL>::kFloats;
+  float B[NF];
+#pragma unroll
+  for (int k = 0; k < NF; k++) B[k] = 0.f;
+  const float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+  GaussCtx g;
+  if (cov3D_precomp != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) g.cov6[k] = cov3D_precomp[6 * (size_t)idx + k];
+  } else cov3d_from_scale_rot_b(scales, rotations, idx, v.scale_modifier, g.cov6);
+  gauss_ctx_init(g, v, p);
+  ProjCtx q;
+  proj_ctx_init(q, v, p);
+  float jx[6], jy[6];
+  mean2d_tau_jac(q, v.proj_raw, jx, jy);
+#pragma unroll
+  for (int k = 0; k < 6; k++) { B[0 * 6 + k] = jx[k]; B[1 * 6 + k] = jy[k]; }
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    ConicChainOut cc;
+    conic_chain(g, v, c == 0 ? 1.f : 0.f, c == 1 ? 1.f : 0.f, c == 2 ? 1.f : 0.f, cc);
+#pragma unroll
+    for (int k = 0; k < 6; k++) B[(2 + c) * 6 + k] = cc.tau[k];
+  }
+  B[5 * 6 + 2] = 1.f; B[5 * 6 + 3] = q.pC.y; B[5 * 6 + 4] = -q.pC.x;
+  if (NCOL == 9) {
+    const uint32_t cm = __float_as_uint(rgb4[idx].w);
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const float on = ((cm >> c) & 1u) ? 0.f : 1.f;
+      const float3 dcol = {c == 0 ? on : 0.f, c == 1 ? on : 0.f, c == 2 ? on : 0.f};
+      const float3 dm = sh_backward(v.D, v.M, p, v.campos, shs + (size_t)idx * v.M * 3, dcol, nullptr);
+      B[(6 + c) * 6 + 0] = -dm.x; B[(6 + c) * 6 + 1] = -dm.y; B[(6 + c) * 6 + 2] = -dm.z;
+    }
+  }
+  float4* out = reinterpret_cast<float4*>(jac + (size_t)idx * NF);
+#pragma unroll
+  for (int k = 0; k < NF / 4; k++) out[k] = make_float4(B[4 * k], B[4 * k + 1], B[4 * k + 2], B[4 * k + 3]);
+}
+
+template <int NCOL>
+__global__ void __launch_bounds__(256)
+blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* __restrict__ ranges,
+                           const SplatRec* __restrict__ recs, const float* __restrict__ jac,
+                           const float* __restrict__ bg, const float* __restrict__ final_T,
+                           const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix,
+                           const float* __restrict__ dL_dpix_depth, float* __restrict__ tau_image /* [6,H,W] or null */,
+                           float* __restrict__ tau_sum /* [6] or null */) {
+  constexpr int NF = PoseJac<NCOL>::kFloats;
+  __shared__ __align__(128) SplatRec stage[2][POSE_BATCH];
+  __shared__ __align__(16) float jstage[POSE_BATCH * NF];
+  __shared__ __align__(8) uint64_t full_bar[2];
+  __shared__ int s_max_contrib;
+  __shared__ float s_part[8][6];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tile = blockIdx.x;
+  const int tx = tile % gx, ty = tile / gx;
+  const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
+  const int py = ty * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = px < W && py < H;
+  const size_t pix = (size_t)py * W + px, plane = (size_t)W * H;
+  const float pxf = (float)px, pyf = (float)py;
+  const uint2 range = ranges[tile];
+
+  const float T_final = inside ? final_T[pix] : 0.f;
+  const int last_contributor = inside ? (int)n_contrib[pix] : 0;
+  float dpx0 = 0.f, dpx1 = 0.f, dpx2 = 0.f, dpd = 0.f;
+  if (inside) {
+    dpx0 = dL_dpix[pix]; dpx1 = dL_dpix[plane + pix]; dpx2 = dL_dpix[2 * plane + pix];
+    dpd = dL_dpix_depth[pix];
+  }
+  if (tid == 0) {
+    s_max_contrib = 0;
+    mbar_init(&full_bar[0], 1); mbar_init(&full_bar[1], 1);
+    mbar_init_fence();
+  }
+  __syncthreads();
+  {
+    int m = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0 && m > 0) atomicMax(&s_max_contrib, m);
+  }
+  __syncthreads();
+  const int n = min(s_max_contrib, (int)(range.y - range.x));
+  const int rounds = (n + POSE_BATCH - 1) / POSE_BATCH;
+  const SplatRec* src = recs + range.x;
+  auto issue = [&](int i) {
+    const int hi = n - i * POSE_BATCH, lo = max(0, hi - POSE_BATCH);
+    const uint32_t bytes = (uint32_t)(hi - lo) * sizeof(SplatRec);
+    mbar_expect_tx(&full_bar[i & 1], bytes);
+    bulk_g2s(&stage[i & 1][0], src + lo, bytes, &full_bar[i & 1]);
+  };
+  if (tid == 0 && rounds > 0) issue(0);
+
+  float T = T_final;
+  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ard = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f, last_alpha = 0.f;
+  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+  const float bg_dot_dpixel = bg[0] * dpx0 + bg[1] * dpx1 + bg[2] * dpx2;
+  float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+
+  for (int i = 0; i < rounds; i++) {
+    __syncthreads();  // all warps are done with jstage and with the stage the next copy overwrites
+    if (tid == 0 && i + 1 < rounds) issue(i + 1);
+    mbar_wait(&full_bar[i & 1], (i >> 1) & 1);
+    const int hi = n - i * POSE_BATCH, lo = max(0, hi - POSE_BATCH);
+    const int cnt = hi - lo;
+    const float4* rec4 = reinterpret_cast<const float4*>(&stage[i & 1][0]);
+    // gather the batch's Jacobians (L2-resident per-Gaussian array) into shared memory, float4 per thread
+    for (int e = tid; e < cnt * (NF / 4); e += 256) {
+      const int slot = e / (NF / 4), k = e - slot * (NF / 4);
+      const uint32_t id = __float_as_uint(rec4[3 * slot + 0].w);
+      reinterpret_cast<float4*>(jstage)[e] = __ldg(reinterpret_cast<const float4*>(jac + (size_t)id * NF) + k);
+    }
+    __syncthreads();
+    for (int j = cnt - 1; j >= 0; j--) {
+      const int contributor = lo + j;
+      const float4 g0 = rec4[3 * j + 0];
+      const float4 g1 = rec4[3 * j + 1];
+      const float dx = g0.x - pxf, dy = g0.y - pyf;
+      const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
+      const float G = expf(power);
+      const float alpha = min(0.99f, g1.w * G);
+      const bool skip = !inside || contributor >= last_contributor || power > 0.0f || alpha < 1.0f / 255.0f;
+      if (__ballot_sync(0xffffffffu, !skip) == 0u) continue;
+      if (!skip) {
+        const float4 g2 = rec4[3 * j + 2];
+        T = T / (1.f - alpha);
+        const float dchannel_dcolor = alpha * T;
+        float dL_dalpha = 0.0f;
+        ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = g2.x; dL_dalpha += (g2.x - ar0) * dpx0;
+        ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = g2.y; dL_dalpha += (g2.y - ar1) * dpx1;
+        ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = g2.z; dL_dalpha += (g2.z - ar2) * dpx2;
+        ard = last_alpha * ld + (1.f - last_alpha) * ard; ld = g0.z; dL_dalpha += (g0.z - ard) * dpd;
+        dL_dalpha *= T;
+        last_alpha = alpha;
+        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+        const float dL_dG = g1.w * dL_dalpha;
+        const float gdx = G * dx, gdy = G * dy;
+        float s[NCOL];
+        s[0] = dL_dG * (-gdx * g1.x - gdy * g1.y) * ddelx_dx;
+        s[1] = dL_dG * (-gdy * g1.z - gdx * g1.y) * ddely_dy;
+        s[2] = -0.5f * gdx * dx * dL_dG;
+        s[3] = -0.5f * gdx * dy * dL_dG;
+        s[4] = -0.5f * gdy * dy * dL_dG;
+        s[5] = dchannel_dcolor * dpd;
+        if (NCOL == 9) { s[6] = dchannel_dcolor * dpx0; s[7] = dchannel_dcolor * dpx1; s[8] = dchannel_dcolor * dpx2; }
+        const float4* J4 = reinterpret_cast<const float4*>(jstage + j * NF);
+        float Bf[NF];
+#pragma unroll
+        for (int k = 0; k < NF / 4; k++) { const float4 t4 = J4[k]; Bf[4 * k] = t4.x; Bf[4 * k + 1] = t4.y; Bf[4 * k + 2] = t4.z; Bf[4 * k + 3] = t4.w; }
+#pragma unroll
+        for (int c = 0; c < NCOL; c++)
+#pragma unroll
+          for (int k = 0; k < 6; k++) tau[k] = fmaf(s[c], Bf[c * 6 + k], tau[k]);
+      }
+    }
+  }
+
+  if (tau_image != nullptr && inside) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) tau_image[k * plane + pix] = tau[k];
+  }
+  if (tau_sum != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      float x = tau[k];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      if (lane == 0) s_part[warp][k] = x;
+    }
+    __syncthreads();
+    if (tid < 6) {
+      float x = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; w++) x += s_part[w][tid];
+      if (x != 0.f) atomicAdd(&tau_sum[tid], x);
+    }
+  }
+}
+
+// SJ[j, i, :] = sum over pixels with sketch_indices[j, pix] == i of tau_image[:, pix]
+__global__ void __launch_bounds__(256)
+sketch_reduce_kernel(const float* __restrict__ tau_image, const int npix, const int d,
+                     const int32_t* __restrict__ sketch_indices, float* __restrict__ sketch_dtau) {
+  extern __shared__ float acc[];  // [d][6]
+  const int stack = blockIdx.y;
+  for (int k = threadIdx.x; k < d * 6; k += blockDim.x) acc[k] = 0.f;
+  __syncthreads();
+  const int32_t* idx = sketch_indices + (size_t)stack * npix;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x) {
+    const int row = idx[p];
+    if (row < 0 || row >= d) continue;
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      const float x = tau_image[(size_t)k * npix + p];
+      if (x != 0.f) atomicAdd(&acc[row * 6 + k], x);
+    }
+  }
+  __syncthreads();
+  float* out = sketch_dtau + (size_t)stack * d * 6;
+  for (int k = threadIdx.x; k < d * 6; k += blockDim.x) {
+    const float x = acc[k];
+    if (x != 0.f) atomicAdd(&out[k], x);
+  }
+}
+
+size_t backward_pose_scratch_bytes(int P, int W, int H) {
+  (void)W; (void)H;
+  return ((size_t)(P > 0 ? P : 1) * PoseJac<9>::kFloats * sizeof(float) + 255) / 256 * 256;
+}
+
+int launch_backward_pose(const BackwardArgs& a, cudaStream_t s) {
+  const ViewConst& v = a.v;
+  const int P = a.P;
+  const size_t need = backward_pose_scratch_bytes(P, v.W, v.H);
+  if (a.scratch == nullptr || a.scratch_bytes < need) { set_error("pose backward scratch too small: %zu < %zu", a.scratch_bytes, need); return MGS_ENOSPC; }
+  float* jac = reinterpret_cast<float*>(a.scratch);
+  if (a.dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
+  const int tiles = v.gx * v.gy;
+  const bool with_color = (a.shs != nullptr && v.D > 0);
+  float* tau_image = a.sketch_dtau;  // reused field: per-pixel tau image [6,H,W] (may be null)
+#define MGS_POSE_LAUNCH(NC)                                                                                          \
+  pose_jacobian_kernel<NC><<<(P + 255) / 256, 256, 0, s>>>(v, P, a.means3D, a.shs, a.scales, a.rotations,            \
+                                                            a.cov3D_precomp, a.radii, ws_ptr<float4>(a.ws, a.L.rgb4), \
+                                                            jac);                                                     \
+  MGS_LAUNCH_CHECK();                                                                                                 \
+  blend_backward_pose_kernel<NC><<<tiles, 256, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges),              \
+                                                        ws_ptr<SplatRec>(a.ws, a.L.records), jac, v.bg,               \
+                                                        ws_ptr<float>(a.ws, a.L.final_T),                             \
+                                                        ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img,       \
+                                                        a.dL_ddepth_img, tau_image, a.dL_dtau_sum);                   \
+  MGS_LAUNCH_CHECK();
+  if (with_color) { MGS_POSE_LAUNCH(9) } else { MGS_POSE_LAUNCH(6) }
+#undef MGS_POSE_LAUNCH
+  return MGS_OK;
+}
+
+int launch_sketch_reduce(const float* tau_image, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,
+                         float* sketch_dtau, cudaStream_t s) {
+  MGS_CUDA_TRY(cudaMemsetAsync(sketch_dtau, 0, (size_t)n_stacks * d * 6 * sizeof(float), s));
+  const int npix = W * H;
+  dim3 grid(min((npix + 255) / 256, 148 * 2), n_stacks);
+  sketch_reduce_kernel<<<grid, 256, (size_t)d * 6 * sizeof(float), s>>>(tau_image, npix, d, sketch_indices, sketch_dtau);
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
+}
+
+}  // namespace mgs

@@ -9,6 +9,7 @@
 // Two block barriers per 256 Gaussians.
 #include "launchers.h"
 #include "gaussian_backward.cuh"
+#include "tma.cuh"
 
 namespace mgs {
 
@@ -21,29 +22,6 @@ struct __align__(16) G2DGrad {
 static_assert(sizeof(G2DGrad) == 48, "G2DGrad is 48 bytes");
 
 constexpr int BWD_BATCH = 256;
-
-__device__ __forceinline__ uint32_t smem_u32b(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init_b(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32b(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx_b(uint64_t* bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32b(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s_b(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-               ::"r"(smem_u32b(dst)), "l"(src), "r"(bytes), "r"(smem_u32b(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_b(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAITB_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONEB_%=;\n"
-      "bra WAITB_%=;\n"
-      "DONEB_%=:\n"
-      "}\n" ::"r"(smem_u32b(bar)), "r"(parity) : "memory");
-}
 
 // Sum 16 per-lane values across the warp; afterwards lane l (both lanes of each pair) holds the total of
 // value index l>>1.  8+4+2+1+1 = 16 shuffles instead of 16*5.
@@ -105,8 +83,8 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
   }
   if (tid == 0) {
     s_max_contrib = 0;
-    mbar_init_b(&full_bar[0], 1); mbar_init_b(&full_bar[1], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    mbar_init(&full_bar[0], 1); mbar_init(&full_bar[1], 1);
+    mbar_init_fence();
   }
   __syncthreads();
   {
@@ -125,8 +103,8 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
   auto issue = [&](int i) {  // batch i covers list positions [lo, hi), walked from hi-1 down to lo
     const int hi = n - i * BWD_BATCH, lo = max(0, hi - BWD_BATCH);
     const uint32_t bytes = (uint32_t)(hi - lo) * sizeof(SplatRec);
-    mbar_expect_tx_b(&full_bar[i & 1], bytes);
-    bulk_g2s_b(&stage[i & 1][0], src + lo, bytes, &full_bar[i & 1]);
+    mbar_expect_tx(&full_bar[i & 1], bytes);
+    bulk_g2s(&stage[i & 1][0], src + lo, bytes, &full_bar[i & 1]);
   };
   if (tid == 0 && rounds > 0) issue(0);
 
@@ -142,7 +120,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
     for (int k = 0; k < 3; k++) reinterpret_cast<float4*>(acc)[tid * 3 + k] = make_float4(0.f, 0.f, 0.f, 0.f);
     __syncthreads();
     if (tid == 0 && i + 1 < rounds) issue(i + 1);
-    mbar_wait_b(&full_bar[i & 1], (i >> 1) & 1);
+    mbar_wait(&full_bar[i & 1], (i >> 1) & 1);
     const int hi = n - i * BWD_BATCH, lo = max(0, hi - BWD_BATCH);
     const int cnt = hi - lo;
     const float4* rec4 = reinterpret_cast<const float4*>(&stage[i & 1][0]);

@@ -153,3 +153,167 @@ def raster_backward(rs, st, grad_mask, means3D, shs, colors_precomp, scales, rot
                                     g("opacity"), g("scales"), g("rotations"), g("cov3D"), g("tau"), g("tau_pg"),
                                     _stream()), "mgs_raster_backward")
     return out
+
+
+def raster_backward_pose(rs, st, means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
+                         grad_color, grad_depth, want_image=False):
+    """Pose-only backward: returns (tau_sum[6], tau_image[6,H,W] or None)."""
+    lib = L.lib()
+    dev, P = means3D.device, st.P
+    H, W = int(rs.image_height), int(rs.image_width)
+    means3D, shs, colors_precomp = _f32c(means3D), _f32c(shs), _f32c(colors_precomp)
+    scales, rotations, cov3D_precomp = _f32c(scales), _f32c(rotations), _f32c(cov3D_precomp)
+    grad_color, grad_depth = _f32c(grad_color), _f32c(grad_depth)
+    keep = []
+    view = make_view(rs, st.sh_coeffs, keep)
+    tau = torch.empty(6, device=dev, dtype=torch.float32)
+    tau_image = torch.empty(6, H, W, device=dev, dtype=torch.float32) if want_image else None
+    scratch = torch.empty(max(lib.mgs_raster_backward_pose_scratch_bytes(P, W, H), 256), device=dev, dtype=torch.uint8)
+    L.check(lib.mgs_raster_backward_pose(C.byref(view), P, L.ptr(means3D), L.ptr(shs), L.ptr(colors_precomp),
+                                         L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp), L.ptr(radii),
+                                         L.ptr(st.workspace), st.workspace.numel(), L.ptr(scratch), scratch.numel(),
+                                         L.ptr(grad_color), L.ptr(grad_depth), L.ptr(tau_image), L.ptr(tau),
+                                         _stream()), "mgs_raster_backward_pose")
+    return tau, tau_image
+
+
+def sketch_reduce(tau_image, sketch_indices, sketch_dim):
+    """sketch_indices i32[stack,H,W] -> f32[stack, sketch_dim, 6]."""
+    lib = L.lib()
+    if sketch_indices.dim() == 2:
+        sketch_indices = sketch_indices.unsqueeze(0)
+    idx = sketch_indices.to(torch.int32).contiguous()
+    n_stacks, H, W = idx.shape
+    out = torch.empty(n_stacks, sketch_dim, 6, device=tau_image.device, dtype=torch.float32)
+    L.check(lib.mgs_sketch_reduce(L.ptr(tau_image), H, W, n_stacks, sketch_dim, L.ptr(idx), L.ptr(out), _stream()),
+            "mgs_sketch_reduce")
+    return out
+
+
+def _opt(t):
+    return t if (t is not None and t.numel() > 0) else None
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    """Autograd node with the reference's argument order (__init__.py:61-84) and gradient tuple (:353-371)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
+                raster_settings, num_backward_gaussians, sketch_mode, sketch_dim, stack_dim, sketch_dtau,
+                sketch_indices):
+        color, radii, depth, opacity, n_touched, st = raster_forward(
+            raster_settings, means3D, opacities, _opt(sh), _opt(colors_precomp), _opt(scales), _opt(rotations),
+            _opt(cov3Ds_precomp))
+        ctx.raster_settings = raster_settings
+        ctx.state = st
+        ctx.sketch_mode, ctx.sketch_dim, ctx.stack_dim = sketch_mode, sketch_dim, stack_dim
+        ctx.repeat_iter = 0
+        ctx.num_rendered = st.num_rendered
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, sketch_dtau,
+                              sketch_indices)
+        ctx.mark_non_differentiable(radii, n_touched)
+        return color, radii, depth, opacity, n_touched
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_out_radii, grad_out_depth, grad_out_opacity, grad_n_touched):
+        # only grad_out_color and grad_out_depth are consumed (__init__.py:150,185-186; SURVEY Q7)
+        rs, st = ctx.raster_settings, ctx.state
+        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, sketch_dtau, sketch_indices = ctx.saved_tensors
+        H, W = int(rs.image_height), int(rs.image_width)
+        dev = means3D.device
+        if grad_out_color is None:
+            grad_out_color = torch.zeros(3, H, W, device=dev)
+        if grad_out_depth is None:
+            grad_out_depth = torch.zeros(1, H, W, device=dev)
+        need = ctx.needs_input_grad
+        g = [None] * 17
+        if ctx.sketch_mode != 0:
+            # sketched Jacobian rows for stack j = 0..stack_dim-1 of repeat `repeat_iter` (__init__.py:216-253)
+            assert ctx.sketch_dim <= 64
+            _, tau_image = raster_backward_pose(rs, st, means3D, _opt(sh), _opt(colors_precomp), _opt(scales),
+                                                _opt(rotations), _opt(cov3Ds_precomp), radii, grad_out_color,
+                                                grad_out_depth, want_image=True)
+            idx = sketch_indices[ctx.repeat_iter][: ctx.stack_dim]
+            g[15] = sketch_reduce(tau_image, idx, ctx.sketch_dim).to(sketch_dtau.dtype).view(sketch_dtau.shape)
+            ctx.repeat_iter += 1
+            return tuple(g)
+        mask = 0
+        if need[0]: mask |= L.GRAD_MEANS3D
+        if need[1]: mask |= L.GRAD_MEANS2D
+        if need[2] or need[3]: mask |= L.GRAD_COLOR
+        if need[4]: mask |= L.GRAD_OPACITY
+        if need[5] or need[6] or need[7]: mask |= L.GRAD_COV
+        want_tau = need[8] or need[9]
+        if mask == 0 and want_tau:
+            tau, _ = raster_backward_pose(rs, st, means3D, _opt(sh), _opt(colors_precomp), _opt(scales),
+                                          _opt(rotations), _opt(cov3Ds_precomp), radii, grad_out_color,
+                                          grad_out_depth)
+        elif mask != 0 or want_tau:
+            if want_tau: mask |= L.GRAD_TAU
+            out = raster_backward(rs, st, mask, means3D, _opt(sh), _opt(colors_precomp), _opt(scales),
+                                  _opt(rotations), _opt(cov3Ds_precomp), radii, grad_out_color, grad_out_depth)
+            tau = out.get("tau")
+            if need[0]: g[0] = out["means3D"]
+            if need[1]: g[1] = out["means2D"]
+            if need[2]: g[2] = out["color"]
+            if need[3]: g[3] = out["color"]
+            if need[4]: g[4] = out["opacity"]
+            if need[5]: g[5] = out["scales"]
+            if need[6]: g[6] = out["rotations"]
+            if need[7]: g[7] = out["cov3D"]
+        if want_tau:
+            if need[8]: g[8] = tau[3:].view(1, -1)   # grad_theta
+            if need[9]: g[9] = tau[:3].view(1, -1)   # grad_rho
+        ctx.repeat_iter += 1
+        return tuple(g)
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
+                        raster_settings, num_backward_gaussians=-1, sketch_mode=0, sketch_dim=0, stack_dim=0,
+                        sketch_dtau=None, sketch_indices=None):
+    dev = means3D.device
+    if sketch_dtau is None: sketch_dtau = torch.empty(0, device=dev)
+    if sketch_indices is None: sketch_indices = torch.empty(0, device=dev, dtype=torch.int32)
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                                     theta, rho, raster_settings, num_backward_gaussians, sketch_mode, sketch_dim,
+                                     stack_dim, sketch_dtau, sketch_indices)
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """bool[P] near-plane test (reference __init__.py:412-421)."""
+        with torch.no_grad():
+            rs = self.raster_settings
+            pos = _f32c(positions)
+            P = pos.size(0)
+            out = torch.zeros(P, device=pos.device, dtype=torch.uint8)
+            vm, pm = _f32c(rs.viewmatrix), _f32c(rs.projmatrix)
+            L.check(L.lib().mgs_mark_visible(P, L.ptr(pos), L.ptr(vm), L.ptr(pm), L.ptr(out), _stream()),
+                    "mgs_mark_visible")
+        return out.bool()
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None, theta=None, rho=None, num_backward_gaussians=None, sketch_mode=0, sketch_dim=0,
+                stack_dim=0, sketch_dtau=None, sketch_indices=None):
+        raster_settings = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        empty = lambda: torch.Tensor([])
+        shs = empty() if shs is None else shs
+        colors_precomp = empty() if colors_precomp is None else colors_precomp
+        scales = empty() if scales is None else scales
+        rotations = empty() if rotations is None else rotations
+        cov3D_precomp = empty() if cov3D_precomp is None else cov3D_precomp
+        theta = empty() if theta is None else theta
+        rho = empty() if rho is None else rho
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, cov3D_precomp,
+                                   theta, rho, raster_settings, num_backward_gaussians=num_backward_gaussians,
+                                   sketch_mode=sketch_mode, sketch_dim=sketch_dim, stack_dim=stack_dim,
+                                   sketch_dtau=sketch_dtau, sketch_indices=sketch_indices)

@@ -1,0 +1,85 @@
+"""Fused loss, fused Adam and on-device pose update against their torch restatements
+(MonoGS utils/slam_utils.py, torch.optim.Adam, utils/pose_utils.py)."""
+import pytest
+import torch
+
+from tests import util as U
+
+pytestmark = pytest.mark.gpu
+
+
+def _images(H=97, W=131, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    image = torch.rand(3, H, W, generator=g)
+    gt = torch.rand(3, H, W, generator=g)
+    gt[:, :5, :] = 0.0                               # below rgb_boundary_threshold -> masked out
+    depth = torch.rand(1, H, W, generator=g) * 3
+    gt_depth = torch.rand(1, H, W, generator=g) * 3
+    gt_depth[:, :, :7] = 0.0
+    opacity = torch.rand(1, H, W, generator=g)
+    opacity[:, 40:, :] = opacity[:, 40:, :] * 0.05 + 0.95
+    grad_mask = (torch.rand(1, H, W, generator=g) > 0.4).float()
+    return image, gt, depth, gt_depth, opacity, grad_mask
+
+
+@pytest.mark.parametrize("mode,use_depth,use_mask", [(0, False, True), (0, True, True), (1, False, False),
+                                                     (2, False, False), (2, True, False)])
+def test_fused_loss_matches_torch(mode, use_depth, use_mask):
+    from monogs_b200 import ops
+    from oracle import golden as G
+    image, gt, depth, gt_depth, opacity, grad_mask = _images()
+    a0, b0 = torch.tensor([-0.7]), torch.tensor([0.05])
+    # torch restatement on CPU in float64
+    im, dp, a, b = [t.double().requires_grad_(True) for t in (image, depth, a0, b0)]
+    ref = G.loss_ref(mode, im, dp, opacity.double(), gt.double(), a, b, grad_mask=grad_mask.double() if use_mask else None,
+                     gt_depth=gt_depth.double() if use_depth else None)
+    ref.backward()
+    imc, dpc, ac, bc = [t.cuda().requires_grad_(True) for t in (image, depth, a0, b0)]
+    if mode == 0:
+        out = ops.tracking_loss(imc, dpc, opacity.cuda(), gt.cuda(), ac, bc, grad_mask=grad_mask.cuda() if use_mask else None,
+                                gt_depth=gt_depth.cuda() if use_depth else None)
+    elif mode == 1:
+        out = ops.tracking_loss_huber(imc, opacity.cuda(), gt.cuda(), ac, bc)
+    else:
+        out = ops.mapping_loss(imc, dpc, gt.cuda(), ac, bc, gt_depth=gt_depth.cuda() if use_depth else None)
+    (out * 1.7).backward()
+    assert abs(out.item() - ref.item()) <= 1e-5 * abs(ref.item())
+    assert U.rel_err(imc.grad, 1.7 * im.grad) <= 1e-5
+    if use_depth:
+        assert U.rel_err(dpc.grad, 1.7 * dp.grad) <= 1e-5
+    assert U.rel_err(ac.grad, 1.7 * a.grad) <= 1e-4 and U.rel_err(bc.grad, 1.7 * b.grad) <= 1e-4
+
+
+def test_fused_adam_matches_torch():
+    from monogs_b200 import ops
+    g = torch.Generator().manual_seed(0)
+    shapes = [(5003, 3), (5003, 1, 3), (5003, 15, 3), (5003, 1), (5003, 3), (5003, 4), (3,), (1,)]
+    lrs = [1.6e-4, 2.5e-3, 1.25e-4, 0.05, 1e-3, 1e-3, 3e-3, 2e-2]
+    ps_ref = [torch.randn(*s, generator=g).cuda().requires_grad_(True) for s in shapes]
+    ps_mine = [p.detach().clone().requires_grad_(True) for p in ps_ref]
+    opt_ref = torch.optim.Adam([{"params": [p], "lr": lr} for p, lr in zip(ps_ref, lrs)], lr=0.0, eps=1e-15)
+    opt_mine = ops.FusedAdam([{"params": [p], "lr": lr} for p, lr in zip(ps_mine, lrs)], lr=0.0, eps=1e-15)
+    for it in range(5):
+        for pr, pm in zip(ps_ref, ps_mine):
+            gr = torch.randn(pr.shape, generator=g).cuda() * (10.0 ** (it - 3))
+            pr.grad, pm.grad = gr.clone(), gr.clone()
+        opt_ref.step(); opt_mine.step()
+    for pr, pm in zip(ps_ref, ps_mine):
+        assert U.rel_err(pm, pr) <= 1e-6
+
+
+def test_pose_update_matches_se3_exp():
+    from monogs_b200 import ops, scene as S
+    T0 = S.se3_exp(torch.tensor([0.3, -0.2, 0.5, 0.2, 0.1, -0.3])).float()
+    for tau in ([0.01, -0.005, 0.008, 0.004, -0.003, 0.002], [1e-7, 0, 0, 0, 1e-7, 0], [0.2, 0.1, -0.3, 0.5, -0.4, 0.3]):
+        tau = torch.tensor(tau)
+        T = T0.clone().cuda()
+        rho, theta = tau[:3].clone().cuda(), tau[3:].clone().cuda()
+        proj = S.make_camera(64, 48, 60.0, 60.0, 32.0, 24.0).projmatrix_raw.cuda()
+        conv, view, full = ops.pose_update(T, rho, theta, proj_raw=proj, want_matrices=True)
+        ref = (S.se3_exp(tau) @ T0.double()).float()
+        assert U.rel_err(T, ref) <= 1e-6
+        assert rho.abs().sum() == 0 and theta.abs().sum() == 0
+        assert int(conv.item()) == int(float((tau ** 2).sum()) < 1e-8)
+        assert U.rel_err(view, ref.t()) <= 1e-6
+        assert U.rel_err(full, ref.t() @ proj.cpu()) <= 1e-5

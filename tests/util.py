@@ -1,0 +1,48 @@
+"""Shared helpers for the parity tests: small seeded scenes, running the product through its Python surface
+(which calls the C-ABI), the GPU oracle (oracle/_ref) and the CPU oracle (oracle/golden.py)."""
+import torch
+
+from monogs_b200 import scene as S
+
+# (name, P, W, H, fx, fy, cx, cy, sh_degree) — small cases the CPU oracle finishes in seconds
+SMALL = {
+    "tiny": (400, 64, 48, 60.0, 61.0, 31.3, 23.6, 0),
+    "ragged": (1500, 150, 100, 120.0, 118.0, 74.2, 50.3, 0),     # W,H not multiples of 16
+    "sh3": (1200, 128, 96, 110.0, 110.0, 63.5, 47.5, 3),
+    "dense": (3000, 96, 64, 80.0, 80.0, 47.5, 31.5, 1),
+}
+
+
+def small_case(name, seed=0, T_w2c=None):
+    P, W, H, fx, fy, cx, cy, deg = SMALL[name]
+    sc = S.make_scene(P, W, H, fx, fy, cx, cy, deg, seed)
+    if T_w2c is None:
+        # a non-identity pose so the rotation part of the pose Jacobian is exercised
+        T_w2c = S.se3_exp(torch.tensor([0.05, -0.03, 0.04, 0.02, -0.015, 0.01])).float()
+    cam = S.make_camera(W, H, fx, fy, cx, cy, T_w2c)
+    return sc, cam
+
+
+def to_dev(nt, dev="cuda"):
+    return type(nt)(*[x.to(dev) if isinstance(x, torch.Tensor) else x for x in nt])
+
+
+def settings(cam, bg, sh_degree):
+    from monogs_b200.rasterizer import GaussianRasterizationSettings
+    return GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, bg, 1.0, cam.viewmatrix,
+                                         cam.projmatrix, cam.projmatrix_raw, sh_degree, cam.campos, False, False)
+
+
+def golden_args(sc, colors_precomp=None, cov3D_precomp=None):
+    a = dict(means3D=sc.means3D, opacities=sc.opacities, sh_degree=sc.sh_degree, scale_modifier=1.0)
+    if colors_precomp is None: a["shs"] = sc.shs
+    else: a["colors_precomp"] = colors_precomp
+    if cov3D_precomp is None: a["scales"], a["rotations"] = sc.scales, sc.rotations
+    else: a["cov3D_precomp"] = cov3D_precomp
+    return a
+
+
+def rel_err(a, b):
+    """max |a-b| / max |b| — the 'relative' of BASELINE.json's 1e-4 / 1e-3 gates."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
