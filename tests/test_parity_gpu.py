@@ -128,7 +128,10 @@ def test_cpu_oracle_vs_reference_and_product(name):
     if mism == 0:
         keys_ref, list_ref = ref_gpu.binning(fw)
         assert torch.equal(res["point_list"].cuda().int(), list_ref)
-        assert torch.equal(res["keys"].cuda(), keys_ref)
+        # tile half exact; depth half within 2 ulp (the CPU oracle has no FMA contraction)
+        kc = res["keys"].cuda()
+        assert torch.equal(kc >> 32, keys_ref >> 32)
+        assert int(((kc & 0xFFFFFFFF) - (keys_ref & 0xFFFFFFFF)).abs().max()) <= 2
     tol_i, tol_g = (IMG_TOL, GRAD_TOL) if mism == 0 else (5e-2, 5e-2)
     for k in ("color", "depth", "opacity"):
         assert U.rel_err(res[k], fw[k]) <= tol_i, k
