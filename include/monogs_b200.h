@@ -53,6 +53,12 @@ typedef struct mgs_view {
 const char* mgs_last_error_string(void);
 int mgs_version(void);
 
+/* Optional per-kernel timing with CUDA events on the launching stream (off by default; do not enable under
+ * CUDA-graph capture).  mgs_profile_enable(1) clears and starts collecting, mgs_profile_report synchronises the
+ * device and writes one line per kernel, "<name> <launches> <total_ms>\n", returning the number of lines. */
+int mgs_profile_enable(int32_t on);
+int mgs_profile_report(char* buf, size_t buf_bytes);
+
 /* ---- rasterizer forward: replaces _C.rasterize_gaussians (ext.cpp:46, rasterize_points.cu:35-127,
  *      cuda_rasterizer/rasterizer_impl.cu:198-344).  The three growable torch arenas of the reference
  *      become one caller-owned workspace that forward fills and backward reads. ---- */
@@ -163,6 +169,10 @@ typedef struct mgs_adam_group {
 } mgs_adam_group;
 int mgs_adam_step(const mgs_adam_group* groups /* host array */, int32_t n_groups, int32_t step /* t>=1 */,
                   float beta1, float beta2, float eps, void* stream);
+/* Same update with the step number kept on the device: uses t = *step_counter + 1 and then increments the
+ * counter, so an optimisation loop can be captured once in a CUDA graph and replayed for every iteration. */
+int mgs_adam_step_device(const mgs_adam_group* groups, int32_t n_groups, int32_t* step_counter /* device i32[1] */,
+                         float beta1, float beta2, float eps, void* stream);
 
 /* ---- simple-knn: replaces simple_knn._C.distCUDA2 (submodules/simple-knn/spatial.cu:15-26,
  *      simple_knn.cu:46-222): mean squared distance to the three nearest other points. ---- */

@@ -50,6 +50,8 @@ _VP = C.POINTER(MgsView)
 SIGNATURES = {
     "mgs_last_error_string": (C.c_char_p, []),
     "mgs_version": (C.c_int, []),
+    "mgs_profile_enable": (C.c_int, [_I32]),
+    "mgs_profile_report": (C.c_int, [C.c_char_p, _SZ]),
     "mgs_raster_workspace_bytes": (_SZ, [_I32, _I32, _I32, _I64]),
     "mgs_raster_preprocess": (C.c_int, [_VP, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P, _P]),
     "mgs_raster_render": (C.c_int, [_VP, _I32, _P, _P, _P, _SZ, _I64, _P, _P, _P, _P, _P]),
@@ -65,6 +67,7 @@ SIGNATURES = {
     "mgs_loss_fwd_bwd": (C.c_int, [C.POINTER(MgsLossArgs), _P, _P, _P, _P, _P, _SZ, _P]),
     "mgs_loss_scratch_bytes": (_SZ, [_I32, _I32]),
     "mgs_adam_step": (C.c_int, [C.POINTER(MgsAdamGroup), _I32, _I32, _F, _F, _F, _P]),
+    "mgs_adam_step_device": (C.c_int, [C.POINTER(MgsAdamGroup), _I32, _P, _F, _F, _F, _P]),
     "mgs_knn_workspace_bytes": (_SZ, [_I32]),
     "mgs_knn_dist2": (C.c_int, [_I32, _P, _P, _P, _SZ, _P]),
     "mgs_pose_update": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _F, _P]),

@@ -6,6 +6,8 @@
 using namespace mgs;
 
 namespace mgs {
+void prof_enable(bool on);
+int prof_report(char* buf, size_t n);
 int launch_backward_full(const BackwardArgs& a, cudaStream_t s);
 int launch_backward_pose(const BackwardArgs& a, cudaStream_t s);
 size_t backward_pose_scratch_bytes(int P, int W, int H);
@@ -40,6 +42,8 @@ extern "C" {
 
 const char* mgs_last_error_string(void) { return mgs::get_error(); }
 int mgs_version(void) { return 100; }
+int mgs_profile_enable(int32_t on) { prof_enable(on != 0); return MGS_OK; }
+int mgs_profile_report(char* buf, size_t buf_bytes) { if (!buf) { set_error("null buffer"); return MGS_EINVAL; } return prof_report(buf, buf_bytes); }
 
 size_t mgs_raster_workspace_bytes(int32_t P, int32_t W, int32_t H, int64_t R_cap) {
   WsLayout L;

@@ -109,10 +109,9 @@ blend_forward_kernel(const int W, const int H, const int gx,
 int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
                          float* out_opacity, int32_t* n_touched, cudaStream_t s) {
   const int tiles = v.gx * v.gy;
-  blend_forward_kernel<<<tiles, 256, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges),
-                                             ws_ptr<SplatRec>(ws, L.records), v.bg,
-                                             ws_ptr<float>(ws, L.final_T), ws_ptr<uint32_t>(ws, L.n_contrib),
-                                             out_color, out_depth, out_opacity, n_touched);
+  MGS_PROF("blend_forward", s, blend_forward_kernel<<<tiles, 256, 0, s>>>(
+      v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
+      ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched));
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

@@ -25,6 +25,12 @@ void set_error(const char* fmt, ...);
   } while (0)
 #define MGS_LAUNCH_CHECK() MGS_CUDA_TRY(cudaGetLastError())
 
+// ---- optional per-kernel CUDA-event timing (mgs_profile_enable / mgs_profile_report); off by default and
+//      never used under graph capture.  bench.py uses it for the live roofline numbers. ----
+void prof_begin(const char* name, cudaStream_t s);
+void prof_end(cudaStream_t s);
+#define MGS_PROF(name, s, ...) do { mgs::prof_begin(name, s); __VA_ARGS__; mgs::prof_end(s); } while (0)
+
 // ---- per-instance record: what a tile's blend loop consumes, contiguous per tile after the sort ----
 // 48 B, 16-B aligned so a tile's list [start,end) is one legal cp.async.bulk source.
 struct __align__(16) SplatRec {

@@ -268,8 +268,8 @@ int mgs_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* works
 int mgs_pose_update(float* T_w2c, float* rho, float* theta, const float* proj_raw, float* viewmatrix_out,
                     float* projmatrix_out, int32_t* converged_out, float converged_threshold, void* stream) {
   if (!T_w2c || !rho || !theta) { set_error("pose_update: null argument"); return MGS_EINVAL; }
-  pose_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(T_w2c, rho, theta, proj_raw, viewmatrix_out, projmatrix_out,
-                                                         converged_out, converged_threshold);
+  MGS_PROF("pose_update", (cudaStream_t)stream, pose_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(
+      T_w2c, rho, theta, proj_raw, viewmatrix_out, projmatrix_out, converged_out, converged_threshold));
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

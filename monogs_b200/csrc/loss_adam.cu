@@ -134,6 +134,7 @@ struct AdamPack {
   long long numel[ADAM_MAX_GROUPS]; float lr[ADAM_MAX_GROUPS]; int chunk_start[ADAM_MAX_GROUPS + 1];
   int n;
   float beta1, beta2, eps, bc1, bc2_sqrt;
+  const int* step_dev;   // when non-null the step number is *step_dev + 1 and bc1/bc2_sqrt are derived on device
 };
 
 __device__ __forceinline__ void adam_elem(float& p, const float g, float& m, float& v, const float step_size,
@@ -144,7 +145,19 @@ __device__ __forceinline__ void adam_elem(float& p, const float g, float& m, flo
   p = p - step_size * (m / denom);                   // param.addcdiv_(exp_avg, denom, value=-step_size)
 }
 
-__global__ void __launch_bounds__(256) adam_kernel(const AdamPack a) {
+__global__ void adam_step_inc_kernel(int* step_dev) { step_dev[0] += 1; }
+
+__global__ void __launch_bounds__(256) adam_kernel(AdamPack a) {
+  if (a.step_dev != nullptr) {   // uniform branch: device-side step counter (CUDA-graph friendly)
+    __shared__ float s_bc[2];
+    if (threadIdx.x == 0) {
+      const double t = (double)(a.step_dev[0] + 1);
+      s_bc[0] = (float)(1.0 - pow((double)a.beta1, t));
+      s_bc[1] = (float)sqrt(1.0 - pow((double)a.beta2, t));
+    }
+    __syncthreads();
+    a.bc1 = s_bc[0]; a.bc2_sqrt = s_bc[1];
+  }
   int gi = 0;
   while (gi + 1 < a.n && (int)blockIdx.x >= a.chunk_start[gi + 1]) gi++;
   const long long base = (long long)(blockIdx.x - a.chunk_start[gi]) * ADAM_CHUNK;
@@ -205,6 +218,7 @@ int mgs_loss_fwd_bwd(const mgs_loss_args* args, float* out_loss, float* out_dab,
   const int nblocks = (k.npix + 255) / 256;
   const bool grads = dL_dimage != nullptr;
   if (grads && k.use_depth && !dL_ddepth) { set_error("loss: dL_ddepth required with use_depth"); return MGS_EINVAL; }
+  prof_begin("loss", s);
   if (k.mode == MGS_LOSS_TRACK_HUBER) {
     loss_kernel<false, true><<<nblocks, 256, 0, s>>>(k, nullptr, partials, nullptr, nullptr);
     MGS_LAUNCH_CHECK();
@@ -223,16 +237,32 @@ int mgs_loss_fwd_bwd(const mgs_loss_args* args, float* out_loss, float* out_dab,
     loss_finalize_kernel<<<1, 256, 0, s>>>(k, partials, nblocks, 1, out_loss, out_dab);
     MGS_LAUNCH_CHECK();
   }
+  prof_end(s);
   return MGS_OK;
 }
 
+static int adam_impl(const mgs_adam_group* groups, int32_t n_groups, int32_t step, int32_t* step_dev, float beta1,
+                     float beta2, float eps, void* stream);
+
 int mgs_adam_step(const mgs_adam_group* groups, int32_t n_groups, int32_t step, float beta1, float beta2, float eps,
                   void* stream) {
-  if (!groups || n_groups <= 0 || step < 1) { set_error("adam: bad arguments"); return MGS_EINVAL; }
+  if (step < 1) { set_error("adam: step must be >= 1"); return MGS_EINVAL; }
+  return adam_impl(groups, n_groups, step, nullptr, beta1, beta2, eps, stream);
+}
+
+int mgs_adam_step_device(const mgs_adam_group* groups, int32_t n_groups, int32_t* step_counter, float beta1,
+                         float beta2, float eps, void* stream) {
+  if (!step_counter) { set_error("adam: step_counter is null"); return MGS_EINVAL; }
+  return adam_impl(groups, n_groups, 1, step_counter, beta1, beta2, eps, stream);
+}
+
+static int adam_impl(const mgs_adam_group* groups, int32_t n_groups, int32_t step, int32_t* step_dev, float beta1,
+                     float beta2, float eps, void* stream) {
+  if (!groups || n_groups <= 0) { set_error("adam: bad arguments"); return MGS_EINVAL; }
   cudaStream_t s = (cudaStream_t)stream;
   for (int g0 = 0; g0 < n_groups; g0 += ADAM_MAX_GROUPS) {
     AdamPack a;
-    a.n = 0; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
+    a.n = 0; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.step_dev = step_dev;
     a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
     a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
     int chunks = 0;
@@ -247,9 +277,10 @@ int mgs_adam_step(const mgs_adam_group* groups, int32_t n_groups, int32_t step, 
     }
     a.chunk_start[a.n] = chunks;
     if (chunks == 0) continue;
-    adam_kernel<<<chunks, 256, 0, s>>>(a);
+    MGS_PROF("adam", s, adam_kernel<<<chunks, 256, 0, s>>>(a));
     MGS_LAUNCH_CHECK();
   }
+  if (step_dev) { adam_step_inc_kernel<<<1, 1, 0, s>>>(step_dev); MGS_LAUNCH_CHECK(); }
   return MGS_OK;
 }
 

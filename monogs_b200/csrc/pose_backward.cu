@@ -254,15 +254,19 @@ int launch_backward_pose(const BackwardArgs& a, cudaStream_t s) {
   const bool with_color = (a.shs != nullptr && v.D > 0);
   float* tau_image = a.sketch_dtau;  // reused field: per-pixel tau image [6,H,W] (may be null)
 #define MGS_POSE_LAUNCH(NC)                                                                                          \
+  prof_begin("pose_jacobian", s);                                                                                   \
   pose_jacobian_kernel<NC><<<(P + 255) / 256, 256, 0, s>>>(v, P, a.means3D, a.shs, a.scales, a.rotations,            \
                                                             a.cov3D_precomp, a.radii, ws_ptr<float4>(a.ws, a.L.rgb4), \
                                                             jac);                                                     \
+  prof_end(s);                                                                                                        \
   MGS_LAUNCH_CHECK();                                                                                                 \
+  prof_begin("blend_backward_pose", s);                                                                             \
   blend_backward_pose_kernel<NC><<<tiles, 256, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges),              \
                                                         ws_ptr<SplatRec>(a.ws, a.L.records), jac, v.bg,               \
                                                         ws_ptr<float>(a.ws, a.L.final_T),                             \
                                                         ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img,       \
                                                         a.dL_ddepth_img, tau_image, a.dL_dtau_sum);                   \
+  prof_end(s);                                                                                                        \
   MGS_LAUNCH_CHECK();
   if (with_color) { MGS_POSE_LAUNCH(9) } else { MGS_POSE_LAUNCH(6) }
 #undef MGS_POSE_LAUNCH

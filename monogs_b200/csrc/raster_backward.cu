@@ -306,15 +306,19 @@ int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   MGS_CUDA_TRY(cudaMemsetAsync(g2d, 0, (size_t)P * sizeof(G2DGrad), s));
   if (a.dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
   const int tiles = v.gx * v.gy;
+  prof_begin("blend_backward_full", s);
   blend_backward_full_kernel<<<tiles, 256, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges),
                                                    ws_ptr<SplatRec>(a.ws, a.L.records), v.bg,
                                                    ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib),
                                                    a.dL_dcolor_img, a.dL_ddepth_img, g2d);
+  prof_end(s);
   MGS_LAUNCH_CHECK();
+  prof_begin("preprocess_backward", s);
   preprocess_backward_kernel<<<(P + 255) / 256, 256, 0, s>>>(
       v, P, a.grad_mask, a.means3D, a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp, a.radii,
       ws_ptr<float4>(a.ws, a.L.rgb4), g2d, a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dcolors_or_sh, a.dL_dopacity,
       a.dL_dscales, a.dL_drotations, a.dL_dcov3D, a.dL_dtau_sum, a.dL_dtau_pg);
+  prof_end(s);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

@@ -6,6 +6,9 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cstdarg>
 #include <cstdio>
+#include <map>
+#include <string>
+#include <vector>
 
 namespace mgs {
 
@@ -14,6 +17,44 @@ void set_error(const char* fmt, ...) {
   va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
 }
 const char* get_error() { return g_err; }
+
+// ---- kernel timer ----
+struct ProfRec { const char* name; cudaEvent_t e0, e1; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof;
+static ProfRec g_cur;
+void prof_begin(const char* name, cudaStream_t s) {
+  if (!g_prof_on) return;
+  g_cur.name = name;
+  cudaEventCreate(&g_cur.e0); cudaEventCreate(&g_cur.e1);
+  cudaEventRecord(g_cur.e0, s);
+}
+void prof_end(cudaStream_t s) {
+  if (!g_prof_on) return;
+  cudaEventRecord(g_cur.e1, s);
+  g_prof.push_back(g_cur);
+}
+void prof_enable(bool on) {
+  for (auto& r : g_prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  g_prof.clear();
+  g_prof_on = on;
+}
+int prof_report(char* buf, size_t n) {
+  cudaDeviceSynchronize();
+  std::map<std::string, std::pair<int, double>> agg;
+  for (auto& r : g_prof) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) { auto& a = agg[r.name]; a.first++; a.second += ms; }
+  }
+  size_t off = 0;
+  for (auto& kv : agg) {
+    int w = snprintf(buf + off, off < n ? n - off : 0, "%s %d %.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+    if (w < 0 || off + (size_t)w >= n) break;
+    off += (size_t)w;
+  }
+  if (n) buf[off < n ? off : n - 1] = 0;
+  return (int)agg.size();
+}
 
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
@@ -269,14 +310,16 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s) {
   if (P == 0) return MGS_OK;
-  preprocess_kernel<<<(P + 255) / 256, 256, 0, s>>>(
+  MGS_PROF("preprocess", s, preprocess_kernel<<<(P + 255) / 256, 256, 0, s>>>(
       v, P, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
       ws_ptr<float>(ws, L.depths), ws_ptr<float2>(ws, L.means2D), ws_ptr<float4>(ws, L.conic_opacity),
-      ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched));
+      ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched)));
   MGS_LAUNCH_CHECK();
   size_t tmp = L.scan_tmp_bytes;
+  prof_begin("cub_scan", s);
   MGS_CUDA_TRY(cub::DeviceScan::InclusiveSum(ws_ptr<void>(ws, L.scan_tmp), tmp, ws_ptr<uint32_t>(ws, L.tiles_touched),
                                              ws_ptr<uint32_t>(ws, L.point_offsets), P, s));
+  prof_end(s);
   return MGS_OK;
 }
 
@@ -291,19 +334,21 @@ int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const
   const uint32_t bit = tile_id_bits(tiles);
   const uint64_t sentinel = ((uint64_t)((1u << bit) - 1u) << 32) | 0xFFFFFFFFull;
   const int64_t n_thr = P > R_cap ? P : R_cap;
-  emit_keys_kernel<<<(unsigned)((n_thr + 255) / 256), 256, 0, s>>>(
+  MGS_PROF("emit_keys", s, emit_keys_kernel<<<(unsigned)((n_thr + 255) / 256), 256, 0, s>>>(
       P, (uint32_t)R_cap, v.gx, v.gy, sentinel, ws_ptr<float2>(ws, L.means2D), ws_ptr<float>(ws, L.depths),
       ws_ptr<uint32_t>(ws, L.point_offsets), radii, hdr, ws_ptr<uint64_t>(ws, L.keys_in),
-      ws_ptr<uint32_t>(ws, L.vals_in));
+      ws_ptr<uint32_t>(ws, L.vals_in)));
   MGS_LAUNCH_CHECK();
   size_t tmp = L.sort_tmp_bytes;
+  prof_begin("cub_sort", s);
   MGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(ws_ptr<void>(ws, L.sort_tmp), tmp, ws_ptr<uint64_t>(ws, L.keys_in),
                                                ws_ptr<uint64_t>(ws, L.keys_out), ws_ptr<uint32_t>(ws, L.vals_in),
                                                ws_ptr<uint32_t>(ws, L.vals_out), (int)R_cap, 0, (int)(32 + bit), s));
-  ranges_records_kernel<<<(unsigned)((R_cap + 255) / 256), 256, 0, s>>>(
+  prof_end(s);
+  MGS_PROF("ranges_records", s, ranges_records_kernel<<<(unsigned)((R_cap + 255) / 256), 256, 0, s>>>(
       (uint32_t)R_cap, hdr, ws_ptr<uint64_t>(ws, L.keys_out), ws_ptr<uint32_t>(ws, L.vals_out),
       ws_ptr<float2>(ws, L.means2D), ws_ptr<float>(ws, L.depths), ws_ptr<float4>(ws, L.conic_opacity),
-      ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records));
+      ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records)));
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

@@ -1,0 +1,161 @@
+"""Device-resident pose tracking loop on top of the C-ABI (the reference's FrontEnd.tracking inner loop,
+utils/slam_frontend.py:455-630, first-order phase).
+
+One iteration = render -> fused tracking loss (fwd+bwd) -> pose-only backward -> Adam on
+(cam_trans_delta lr 1e-3, cam_rot_delta lr 3e-3, exposure_a 2e-2, exposure_b 2e-2; configs/mono/tum/base_config.yaml
+`lr:` block) -> T <- Exp(tau) T.  Every stage is a call into libmonogs_b200.so on the caller's stream with
+device-side counts, so the iteration has no host synchronisation and is captured once into a CUDA graph and
+replayed (the reference blocks on cudaMemcpy of num_rendered every forward, rasterizer_impl.cu:284, and pays a
+Python + autograd round trip per stage).  torch provides memory, streams and the graph object only.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+from .rasterizer import make_view, GaussianRasterizationSettings, _stream
+
+KERNELS_PER_ITER = 14   # own kernels launched per iteration (CUB scan/sort launches not counted)
+
+
+class PoseTracker:
+    def __init__(self, means3D, opacities, shs, scales, rotations, sh_degree, cam, bg, T_w2c, mode=L.LOSS_TRACK_HUBER,
+                 use_depth=False, lr=(1e-3, 3e-3, 2e-2, 2e-2), capacity_headroom=1.3, use_graph=True):
+        lib = self.lib = L.lib()
+        dev = self.dev = means3D.device
+        f = dict(device=dev, dtype=torch.float32)
+        self.P, self.H, self.W = means3D.size(0), cam.H, cam.W
+        self.means3D, self.opacities, self.shs = means3D.contiguous(), opacities.contiguous(), shs.contiguous()
+        self.scales, self.rotations = scales.contiguous(), rotations.contiguous()
+        self.M = shs.size(1)
+        # pose + matrices live in fixed device buffers that the view struct points at
+        self.T = T_w2c.to(**f).contiguous().clone()
+        self.proj_raw = cam.projmatrix_raw.to(**f).contiguous()
+        self.viewmatrix = self.T.t().contiguous()
+        self.projmatrix = (self.viewmatrix @ self.proj_raw).contiguous()
+        self.bg = bg.to(**f).contiguous()
+        rs = GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, self.bg, 1.0, self.viewmatrix,
+                                           self.projmatrix, self.proj_raw, sh_degree, self.viewmatrix, False, False)
+        self._keep = []
+        self.view = make_view(rs, self.M, self._keep)
+        assert self.view.viewmatrix == self.viewmatrix.data_ptr() and self.view.campos == self.viewmatrix.data_ptr()
+        # optimiser state: params = [rho(3), theta(3), a(1), b(1)], grads = [tau(6), dab(2)]
+        self.params = torch.zeros(8, **f)
+        self.tau = torch.zeros(6, **f)
+        self.dab = torch.zeros(2, **f)
+        self.exp_avg, self.exp_avg_sq = torch.zeros(8, **f), torch.zeros(8, **f)
+        self.lr = lr
+        self.step_dev = torch.zeros(1, device=dev, dtype=torch.int32)   # Adam step number, kept on the device
+        self.mode, self.use_depth = mode, use_depth
+        # outputs / intermediates
+        self.color, self.depth = torch.empty(3, self.H, self.W, **f), torch.empty(1, self.H, self.W, **f)
+        self.opacity = torch.empty(1, self.H, self.W, **f)
+        self.radii = torch.zeros(self.P, device=dev, dtype=torch.int32)
+        self.n_touched = torch.zeros(self.P, device=dev, dtype=torch.int32)
+        self.g_color, self.g_depth = torch.zeros(3, self.H, self.W, **f), torch.zeros(1, self.H, self.W, **f)
+        self.loss = torch.zeros(1, **f)
+        self.converged = torch.zeros(1, device=dev, dtype=torch.int32)
+        self.gt_image = torch.zeros(3, self.H, self.W, **f)
+        self.gt_depth = torch.zeros(1, self.H, self.W, **f) if use_depth else None
+        self.grad_mask = None
+        self.loss_scratch = torch.empty(lib.mgs_loss_scratch_bytes(self.H, self.W), device=dev, dtype=torch.uint8)
+        self.bwd_scratch = torch.empty(max(lib.mgs_raster_backward_pose_scratch_bytes(self.P, self.W, self.H), 256),
+                                       device=dev, dtype=torch.uint8)
+        self.headroom = capacity_headroom
+        self.R_cap, self.ws = 0, None
+        self.use_graph, self.graph = use_graph, None
+        self._size_workspace()
+
+    # ------------------------------------------------------------------------------------------------
+    def _size_workspace(self):
+        """One synchronous preprocess to learn num_rendered, then capacity = headroom x that."""
+        lib = self.lib
+        base = lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, 0)
+        tmp = torch.empty(base, device=self.dev, dtype=torch.uint8)
+        n_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        L.check(lib.mgs_raster_preprocess(C.byref(self.view), self.P, L.ptr(self.means3D), L.ptr(self.opacities),
+                                          L.ptr(self.shs), None, L.ptr(self.scales), L.ptr(self.rotations), None,
+                                          L.ptr(self.radii), L.ptr(tmp), tmp.numel(), C.c_void_p(n_host.data_ptr()),
+                                          _stream()), "mgs_raster_preprocess")
+        torch.cuda.current_stream().synchronize()
+        R = int(n_host.item())
+        self.R_cap = max(int(R * self.headroom) + 4096, 4096)
+        self.ws = torch.empty(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev,
+                              dtype=torch.uint8)
+        self.graph = None
+
+    def _loss_args(self):
+        a = L.MgsLossArgs()
+        a.mode, a.H, a.W, a.use_depth = self.mode, self.H, self.W, int(self.use_depth)
+        a.rgb_boundary_threshold, a.alpha, a.huber_delta, a.loss_scale = 0.01, 0.95, 0.01, 1.0
+        a.image, a.depth, a.opacity = self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr()
+        a.gt_image = self.gt_image.data_ptr()
+        a.gt_depth = self.gt_depth.data_ptr() if self.gt_depth is not None else None
+        a.grad_mask = self.grad_mask.data_ptr() if self.grad_mask is not None else None
+        a.exposure_a, a.exposure_b = self.params[6:7].data_ptr(), self.params[7:8].data_ptr()
+        return a
+
+    def _enqueue(self):
+        """The whole iteration as C-ABI calls on the current stream; no host sync anywhere."""
+        lib, s, v = self.lib, _stream(), C.byref(self.view)
+        L.check(lib.mgs_raster_preprocess(v, self.P, L.ptr(self.means3D), L.ptr(self.opacities), L.ptr(self.shs), None,
+                                          L.ptr(self.scales), L.ptr(self.rotations), None, L.ptr(self.radii),
+                                          L.ptr(self.ws), self.ws.numel(), None, s), "mgs_raster_preprocess")
+        L.check(lib.mgs_raster_render(v, self.P, None, L.ptr(self.radii), L.ptr(self.ws), self.ws.numel(), self.R_cap,
+                                      L.ptr(self.color), L.ptr(self.depth), L.ptr(self.opacity), L.ptr(self.n_touched),
+                                      s), "mgs_raster_render")
+        la = self._loss_args()
+        L.check(lib.mgs_loss_fwd_bwd(C.byref(la), L.ptr(self.loss), L.ptr(self.dab), L.ptr(self.g_color),
+                                     L.ptr(self.g_depth), L.ptr(self.loss_scratch), self.loss_scratch.numel(), s),
+                "mgs_loss_fwd_bwd")
+        L.check(lib.mgs_raster_backward_pose(v, self.P, L.ptr(self.means3D), L.ptr(self.shs), None, L.ptr(self.scales),
+                                             L.ptr(self.rotations), None, L.ptr(self.radii), L.ptr(self.ws),
+                                             self.ws.numel(), L.ptr(self.bwd_scratch), self.bwd_scratch.numel(),
+                                             L.ptr(self.g_color), L.ptr(self.g_depth), None, L.ptr(self.tau), s),
+                "mgs_raster_backward_pose")
+        groups = (L.MgsAdamGroup * 4)()
+        spans = ((0, 3, self.tau, 0), (3, 6, self.tau, 3), (6, 7, self.dab, 0), (7, 8, self.dab, 1))
+        for i, (lo, hi, gsrc, goff) in enumerate(spans):
+            groups[i].param = self.params[lo:hi].data_ptr()
+            groups[i].grad = gsrc[goff:goff + (hi - lo)].data_ptr()
+            groups[i].exp_avg, groups[i].exp_avg_sq = self.exp_avg[lo:hi].data_ptr(), self.exp_avg_sq[lo:hi].data_ptr()
+            groups[i].numel, groups[i].lr = hi - lo, self.lr[i]
+        L.check(lib.mgs_adam_step_device(groups, 4, L.ptr(self.step_dev), 0.9, 0.999, 1e-15, s), "mgs_adam_step_device")
+        L.check(lib.mgs_pose_update(L.ptr(self.T), L.ptr(self.params[0:3]), L.ptr(self.params[3:6]), L.ptr(self.proj_raw),
+                                    L.ptr(self.viewmatrix), L.ptr(self.projmatrix), L.ptr(self.converged), 1e-4, s),
+                "mgs_pose_update")
+
+    # ------------------------------------------------------------------------------------------------
+    def set_frame(self, gt_image, gt_depth=None, grad_mask=None, non_blocking=True):
+        """New target frame (host pinned or device tensors); resets the per-frame optimiser state like the
+        reference, which builds a fresh Adam per frame (slam_frontend.py:364-392,453)."""
+        self.gt_image.copy_(gt_image, non_blocking=non_blocking)
+        if self.gt_depth is not None and gt_depth is not None:
+            self.gt_depth.copy_(gt_depth, non_blocking=non_blocking)
+        if grad_mask is not None:
+            if self.grad_mask is None:
+                self.grad_mask = torch.zeros(1, self.H, self.W, device=self.dev)
+                self.graph = None
+            self.grad_mask.copy_(grad_mask, non_blocking=non_blocking)
+        self.exp_avg.zero_(); self.exp_avg_sq.zero_(); self.params[:6].zero_(); self.step_dev.zero_()
+
+    def step(self):
+        """One tracking iteration: the first call captures the C-ABI call sequence into a CUDA graph (the Adam step
+        number lives on the device, so one graph serves every iteration); later calls replay it."""
+        if not self.use_graph:
+            self._enqueue()
+            return
+        if self.graph is None:
+            torch.cuda.synchronize()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self._enqueue()
+        self.graph.replay()
+
+    def check_capacity(self):
+        """Synchronous check of the device-side overflow flag; regrows the workspace if the splat count outgrew it."""
+        n, ov = C.c_int32(0), C.c_int32(0)
+        L.check(self.lib.mgs_raster_query(L.ptr(self.ws), C.byref(n), C.byref(ov), _stream()), "mgs_raster_query")
+        if ov.value:
+            self._size_workspace()
+        return n.value, bool(ov.value)
