@@ -30,6 +30,7 @@ blend_forward_kernel(const int W, const int H, const int gx,
   const int py = ty * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
+  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 4);
 
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
@@ -66,30 +67,38 @@ blend_forward_kernel(const int W, const int H, const int gx,
     }
     mbar_wait(&full_bar[i & 1], (i >> 1) & 1);
     const float4* rec4 = reinterpret_cast<const float4*>(&stage[i & 1][0]);
+    const float* recf = reinterpret_cast<const float*>(&stage[i & 1][0]);
     const int cnt = min(FWD_BATCH, n - i * FWD_BATCH);
     const uint32_t base = (uint32_t)i * FWD_BATCH;
-    for (int j = 0; j < cnt; j++) {
+    for (int c0 = 0; c0 < cnt; c0 += 32) {
+      // lane-parallel exact cull: which of these 32 splats can reach this warp's 8x4 patch at all?
+      const int jj = c0 + lane;
+      unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
       if (__ballot_sync(0xffffffffu, !done) == 0u) break;
-      const float4 g0 = rec4[3 * j + 0];  // x, y, depth, id
-      const float4 g1 = rec4[3 * j + 1];  // conic xyz, opacity
-      const float dx = g0.x - pxf, dy = g0.y - pyf;
-      const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
-      bool valid = !done && !(power > 0.0f);
-      const float alpha = min(0.99f, g1.w * expf(power));
-      valid = valid && !(alpha < 1.0f / 255.0f);
-      const float test_T = T * (1 - alpha);
-      if (valid && test_T < 0.0001f) { done = true; valid = false; }
-      const unsigned touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
-      if (valid) {
-        const float4 g2 = rec4[3 * j + 2];
-        C0 += g2.x * alpha * T;
-        C1 += g2.y * alpha * T;
-        C2 += g2.z * alpha * T;
-        D += g0.z * alpha * T;
-        T = test_T;
-        last_contributor = base + j + 1;
+      while (hits) {
+        const int j = c0 + __ffs(hits) - 1;
+        hits &= hits - 1;
+        const float4 g0 = rec4[3 * j + 0];  // x, y, depth, id
+        const float4 g1 = rec4[3 * j + 1];  // conic xyz, opacity
+        const float dx = g0.x - pxf, dy = g0.y - pyf;
+        const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
+        bool valid = !done && !(power > 0.0f);
+        const float alpha = min(0.99f, g1.w * expf(power));
+        valid = valid && !(alpha < 1.0f / 255.0f);
+        const float test_T = T * (1 - alpha);
+        if (valid && test_T < 0.0001f) { done = true; valid = false; }
+        const unsigned touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
+        if (valid) {
+          const float4 g2 = rec4[3 * j + 2];
+          C0 += g2.x * alpha * T;
+          C1 += g2.y * alpha * T;
+          C2 += g2.z * alpha * T;
+          D += g0.z * alpha * T;
+          T = test_T;
+          last_contributor = base + j + 1;
+        }
+        if (touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
       }
-      if (touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
     }
   }
 

@@ -2,6 +2,7 @@
 // Reference paths are relative to /root/reference/submodules/diff-gaussian-rasterization/cuda_rasterizer.
 #pragma once
 #include <cuda_runtime.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stddef.h>
 #include "../../include/monogs_b200.h"
@@ -36,7 +37,7 @@ void prof_end(cudaStream_t s);
 struct __align__(16) SplatRec {
   float x, y, depth; uint32_t id;       // pixel-space mean, view depth (forward.cu:254), Gaussian index
   float cx, cy, cz, opacity;            // conic (inverse 2D covariance) + opacity (forward.cu:257)
-  float r, g, b, pad;                   // colour after SH evaluation / precomputed
+  float r, g, b; uint32_t extent;       // colour; half2 (hx, hy): half-extents of the alpha >= 1/255 ellipse
 };
 static_assert(sizeof(SplatRec) == 48, "SplatRec must stay 48 bytes");
 
@@ -127,6 +128,35 @@ __device__ __forceinline__ void tile_rect(float2 p, int max_radius, int gx, int 
   rmin.y = min(gy, max(0, (int)((p.y - max_radius) / TILE_Y)));
   rmax.x = min(gx, max(0, (int)((p.x + max_radius + TILE_X - 1) / TILE_X)));
   rmax.y = min(gy, max(0, (int)((p.y + max_radius + TILE_Y - 1) / TILE_Y)));
+}
+
+// Half-extents (in pixels, rounded UP to fp16) of the axis-aligned box around the region where this splat can
+// pass the blend's `alpha >= 1/255` test (forward.cu:352-355): alpha = op*exp(power) >= 1/255  <=>
+// d^T conic d <= 2 ln(255 op), an ellipse whose box is sqrt(2 ln(255 op) * cov_xx/yy), cov = conic^-1.
+// A warp patch that misses the box holds only pixels the reference would skip, so culling it is exact; the
+// 0.2 % + 0.01 px margin dwarfs fp32 rounding of power/exp.  Non-PD conics get an infinite box (never culled),
+// op <= 1/255 gets a negative one (always culled: alpha <= op < 1/255 everywhere).
+__device__ __forceinline__ uint32_t splat_extent(float cx, float cy, float cz, float op) {
+  float hx, hy;
+  const float det = cx * cz - cy * cy;
+  if (!(op * 255.f > 1.f)) { hx = hy = -1.f; }
+  else if (!(det > 0.f) || !(cx > 0.f) || !(cz > 0.f)) { hx = hy = __int_as_float(0x7f800000); }
+  else {
+    const float two_tau = 2.f * logf(255.f * op);
+    hx = sqrtf(two_tau * cz / det) * 1.002f + 0.01f;
+    hy = sqrtf(two_tau * cx / det) * 1.002f + 0.01f;
+    if (!(hx == hx)) hx = __int_as_float(0x7f800000);
+    if (!(hy == hy)) hy = __int_as_float(0x7f800000);
+  }
+  const __half2 h = __halves2half2(__float2half_ru(hx), __float2half_ru(hy));
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+// lane-parallel cull test of record `rec` (12 floats) against the pixel box [x0,x1] x [y0,y1]
+__device__ __forceinline__ bool splat_hits(const float* rec, float x0, float x1, float y0, float y1) {
+  const float x = rec[0], y = rec[1];
+  const uint32_t e = __float_as_uint(rec[11]);
+  const float2 h = __half22float2(*reinterpret_cast<const __half2*>(&e));
+  return (x + h.x >= x0) && (x - h.x <= x1) && (y + h.y >= y0) && (y - h.y <= y1);
 }
 
 // SH basis constants (auxiliary.h:21-39)

@@ -93,6 +93,7 @@ blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* 
   const bool inside = px < W && py < H;
   const size_t pix = (size_t)py * W + px, plane = (size_t)W * H;
   const float pxf = (float)px, pyf = (float)py;
+  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 4);
   const uint2 range = ranges[tile];
 
   const float T_final = inside ? final_T[pix] : 0.f;
@@ -146,7 +147,14 @@ blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* 
       reinterpret_cast<float4*>(jstage)[e] = __ldg(reinterpret_cast<const float4*>(jac + (size_t)id * NF) + k);
     }
     __syncthreads();
-    for (int j = cnt - 1; j >= 0; j--) {
+    const float* recf = reinterpret_cast<const float*>(&stage[i & 1][0]);
+    for (int c0 = ((cnt - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
+     // lane-parallel exact cull of 32 splats against this warp's 8x4 patch (see splat_extent)
+     const int jj = c0 + lane;
+     unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+     while (hits) {
+      const int j = c0 + 31 - __clz(hits);
+      hits &= ~(1u << (j - c0));
       const int contributor = lo + j;
       const float4 g0 = rec4[3 * j + 0];
       const float4 g1 = rec4[3 * j + 1];
@@ -187,6 +195,7 @@ blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* 
 #pragma unroll
           for (int k = 0; k < 6; k++) tau[k] = fmaf(s[c], Bf[c * 6 + k], tau[k]);
       }
+     }
     }
   }
 

@@ -72,6 +72,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
   const bool inside = px < W && py < H;
   const size_t pix = (size_t)py * W + px, plane = (size_t)W * H;
   const float pxf = (float)px, pyf = (float)py;
+  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 4);
   const uint2 range = ranges[tile];
 
   const float T_final = inside ? final_T[pix] : 0.f;
@@ -124,7 +125,14 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
     const int hi = n - i * BWD_BATCH, lo = max(0, hi - BWD_BATCH);
     const int cnt = hi - lo;
     const float4* rec4 = reinterpret_cast<const float4*>(&stage[i & 1][0]);
-    for (int j = cnt - 1; j >= 0; j--) {
+    const float* recf = reinterpret_cast<const float*>(&stage[i & 1][0]);
+    for (int c0 = ((cnt - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
+     // lane-parallel exact cull of 32 splats against this warp's 8x4 patch (see splat_extent)
+     const int jj = c0 + lane;
+     unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+     while (hits) {
+      const int j = c0 + 31 - __clz(hits);
+      hits &= ~(1u << (j - c0));
       const int contributor = lo + j;  // list position of this Gaussian
       const float4 g0 = rec4[3 * j + 0];
       const float4 g1 = rec4[3 * j + 1];
@@ -166,6 +174,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
       }
       const float tot = warp_reduce16_transpose(v, lane);
       if (!(lane & 1) && lane < 24) atomicAdd(&acc[j * 12 + (lane >> 1)], tot);
+     }
     }
     __syncthreads();
     if (tid < cnt) {

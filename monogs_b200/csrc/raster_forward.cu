@@ -302,7 +302,7 @@ ranges_records_kernel(const uint32_t R_cap, const WsHeader* __restrict__ hdr,
   float4* out = reinterpret_cast<float4*>(recs + i);
   out[0] = make_float4(xy.x, xy.y, depths[id], __uint_as_float(id));
   out[1] = co;
-  out[2] = make_float4(c.x, c.y, c.z, 0.f);
+  out[2] = make_float4(c.x, c.y, c.z, __uint_as_float(splat_extent(co.x, co.y, co.z, co.w)));
 }
 
 
