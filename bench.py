@@ -141,21 +141,18 @@ def kernel_profile(cfg, dev, steps):
 
 
 def algorithmic_bytes(P, P_vis, R, R_cap, W, H, M=1):
-    """Per-launch algorithmic bytes of every kernel on the tracking path."""
+    """Per-launch algorithmic bytes of every kernel of the fused tracking iteration."""
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
-    n_pass = 6
     return {
-        "preprocess": 12 * P + 4 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8 + 16 + 16) + 4 * P,
-        "cub_scan": 8 * P,
-        "emit_keys": P * 4 + P_vis * 16 + R_cap * 12,
-        "cub_sort": R_cap * (8 + 24 * n_pass),
-        "ranges_records": R * (12 + 44 + 48) + 8 * tiles,
-        "blend_forward": R * 48 + 28 * W * H + 8 * tiles,
-        "loss": 2 * (12 + 12 + 4) * W * H + 16 * W * H,
-        "pose_jacobian": P * 4 + P_vis * (12 + 28 + 16 + 144),
-        "blend_backward_pose": R * (48 + 144) + 24 * W * H + 8 * tiles,
-        "adam": 8 * 28,
-        "pose_update": 64 * 4,
+        "preprocess": 12 * P + 4 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8 + 16 + 16) + 12 * P + P_vis * 144,
+        "cub_sort_depth": P * (8 + 16 * 4),
+        "cub_scan": 12 * P,
+        "emit_keys": P * 4 + P_vis * 16 + R_cap * 8,
+        "cub_sort": R_cap * (8 + 16 * 2),
+        "ranges_records": R * (8 + 44 + 48) + 8 * tiles,
+        "blend_forward": R * 48 + (28 + 12 + 12) * W * H + 40 * tiles,
+        "blend_backward_pose": R * (48 + 144) + 20 * W * H + 8 * tiles,
+        "track_update": 32 * tiles,
     }
 
 

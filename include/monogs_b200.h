@@ -187,6 +187,35 @@ int mgs_knn_dist2(int32_t P, const float* points /* f32[P,3] */, float* mean_dis
 int mgs_pose_update(float* T_w2c, float* rho, float* theta, const float* proj_raw, float* viewmatrix_out,
                     float* projmatrix_out, int32_t* converged_out, float converged_threshold, void* stream);
 
+/* ---- one whole tracking iteration, fused (the first-order inner loop of FrontEnd.tracking,
+ *      utils/slam_frontend.py:455-630): render -> tracking loss (fused into the forward blend) -> pose-only backward
+ *      -> Adam on (rho lr[0], theta lr[1], exposure_a lr[2], exposure_b lr[3]) -> T <- Exp(rho,theta) T.
+ *      No host synchronisation; CUDA-graph capturable.  view.viewmatrix / view.projmatrix (and view.campos when it
+ *      aliases the view matrix, as in MonoGS) are device buffers that the call UPDATES IN PLACE with the new pose.
+ *      params = f32[8] (rho, theta, a, b); exp_avg / exp_avg_sq = f32[8]; step_counter = device i32[1]. ---- */
+typedef struct mgs_track_args {
+  mgs_view view;
+  int32_t P;
+  const float *means3D, *opacities, *shs, *scales, *rotations;
+  int32_t loss_mode;   /* MGS_LOSS_TRACK_L1 or MGS_LOSS_TRACK_HUBER */
+  int32_t use_depth;   /* rgbd variant of TRACK_L1 */
+  float rgb_boundary_threshold, alpha, huber_delta;
+  const float *gt_image, *gt_depth, *grad_mask;
+  float* T_w2c;        /* f32[4,4] row-major, in/out */
+  float *params, *exp_avg, *exp_avg_sq;
+  int32_t* step_counter;
+  float lr[4];
+  float beta1, beta2, adam_eps, converged_threshold;
+  float *out_color, *out_depth, *out_opacity;
+  int32_t *radii, *n_touched;
+  float *loss /* f32[1] */, *tau /* f32[6] */, *dab /* f32[2] */;
+  int32_t* converged;  /* i32[1], optional */
+  void* workspace; size_t workspace_bytes; int64_t R_cap;
+  void* scratch; size_t scratch_bytes;
+} mgs_track_args;
+size_t mgs_track_scratch_bytes(int32_t P, int32_t W, int32_t H);
+int mgs_track_iteration(const mgs_track_args* args, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

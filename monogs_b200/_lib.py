@@ -43,6 +43,25 @@ class MgsAdamGroup(C.Structure):
     ]
 
 
+class MgsTrackArgs(C.Structure):
+    _fields_ = [
+        ("view", MgsView), ("P", C.c_int32),
+        ("means3D", C.c_void_p), ("opacities", C.c_void_p), ("shs", C.c_void_p), ("scales", C.c_void_p),
+        ("rotations", C.c_void_p),
+        ("loss_mode", C.c_int32), ("use_depth", C.c_int32),
+        ("rgb_boundary_threshold", C.c_float), ("alpha", C.c_float), ("huber_delta", C.c_float),
+        ("gt_image", C.c_void_p), ("gt_depth", C.c_void_p), ("grad_mask", C.c_void_p),
+        ("T_w2c", C.c_void_p), ("params", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+        ("step_counter", C.c_void_p), ("lr", C.c_float * 4),
+        ("beta1", C.c_float), ("beta2", C.c_float), ("adam_eps", C.c_float), ("converged_threshold", C.c_float),
+        ("out_color", C.c_void_p), ("out_depth", C.c_void_p), ("out_opacity", C.c_void_p),
+        ("radii", C.c_void_p), ("n_touched", C.c_void_p),
+        ("loss", C.c_void_p), ("tau", C.c_void_p), ("dab", C.c_void_p), ("converged", C.c_void_p),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("R_cap", C.c_int64),
+        ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+    ]
+
+
 _P, _I32, _I64, _U32, _F, _SZ = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_float, C.c_size_t
 _VP = C.POINTER(MgsView)
 
@@ -70,6 +89,8 @@ SIGNATURES = {
     "mgs_adam_step_device": (C.c_int, [C.POINTER(MgsAdamGroup), _I32, _P, _F, _F, _F, _P]),
     "mgs_knn_workspace_bytes": (_SZ, [_I32]),
     "mgs_knn_dist2": (C.c_int, [_I32, _P, _P, _P, _SZ, _P]),
+    "mgs_track_scratch_bytes": (_SZ, [_I32, _I32, _I32]),
+    "mgs_track_iteration": (C.c_int, [C.POINTER(MgsTrackArgs), _P]),
     "mgs_pose_update": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _F, _P]),
 }
 

@@ -190,7 +190,7 @@ int mgs_raster_backward_pose(const mgs_view* view, int32_t P, const float* means
     if (tau_image) MGS_CUDA_TRY(cudaMemsetAsync(tau_image, 0, 6 * npix * sizeof(float), s));
     return MGS_OK;
   }
-  if (!means3D || !radii || !workspace || !dL_dout_color || !dL_dout_depth) { set_error("null required input"); return MGS_EINVAL; }
+  if (!means3D || !radii || !workspace || !dL_dout_color) { set_error("null required input"); return MGS_EINVAL; }   // dL_dout_depth may be null (= zeros)
   if ((rc = check_options(view, shs, colors_precomp, scales, rotations, cov3D_precomp))) return rc;
   BackwardArgs a;
   memset(&a, 0, sizeof(a));

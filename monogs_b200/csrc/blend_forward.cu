@@ -7,19 +7,23 @@
 // ballot and per CTA with __syncthreads_count, like the reference's block vote.
 #include "launchers.h"
 #include "tma.cuh"
+#include "loss_pixel.cuh"
 
 namespace mgs {
 
 constexpr int FWD_BATCH = 256;
 constexpr int FWD_STAGES = 2;
 
+template <bool FUSED_LOSS>
 __global__ void __launch_bounds__(256)
 blend_forward_kernel(const int W, const int H, const int gx,
                      const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
                      const float* __restrict__ bg,
                      float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                      float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
-                     int32_t* __restrict__ n_touched) {
+                     int32_t* __restrict__ n_touched,
+                     const LossK lk, const float loss_grad_scale, float* __restrict__ g_img, float* __restrict__ g_depth,
+                     double* __restrict__ loss_partials) {
   __shared__ __align__(128) SplatRec stage[FWD_STAGES][FWD_BATCH];
   __shared__ __align__(8) uint64_t full_bar[FWD_STAGES];
 
@@ -113,14 +117,38 @@ blend_forward_kernel(const int W, const int H, const int gx,
     out_depth[pix] = D;
     out_opacity[pix] = 1 - T;
   }
+  if (FUSED_LOSS) {
+    // loss + its (un-normalised) gradient straight from the registers that hold the blended pixel
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    if (inside) {
+      const size_t pix = (size_t)py * W + px;
+      const size_t plane = (size_t)W * H;
+      const float img[3] = {C0 + T * bg[0], C1 + T * bg[1], C2 + T * bg[2]};
+      float gi[3], gd;
+      loss_pixel<true, true>(lk, (int)pix, img, D, 1 - T, loss_grad_scale, acc, gi, gd);
+      g_img[pix] = gi[0]; g_img[plane + pix] = gi[1]; g_img[2 * plane + pix] = gi[2];
+      if (g_depth != nullptr) g_depth[pix] = gd;
+    }
+    loss_block_reduce(acc, loss_partials + (size_t)tile * 4);
+  }
 }
 
 int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
-                         float* out_opacity, int32_t* n_touched, cudaStream_t s) {
+                         float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl) {
   const int tiles = v.gx * v.gy;
-  MGS_PROF("blend_forward", s, blend_forward_kernel<<<tiles, 256, 0, s>>>(
-      v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
-      ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched));
+  prof_begin("blend_forward", s);
+  if (fl == nullptr) {
+    LossK none{};
+    blend_forward_kernel<false><<<tiles, 256, 0, s>>>(
+        v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
+        ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, none, 0.f, nullptr, nullptr, nullptr);
+  } else {
+    blend_forward_kernel<true><<<tiles, 256, 0, s>>>(
+        v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
+        ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, *fl->k, fl->grad_scale, fl->g_img,
+        fl->g_depth, fl->partials);
+  }
+  prof_end(s);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

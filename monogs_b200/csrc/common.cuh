@@ -54,8 +54,9 @@ static_assert(sizeof(WsHeader) == 256, "header is one 256-B slot");
 struct WsLayout {
   size_t header, depths, means2D, conic_opacity, rgb4, tiles_touched, point_offsets;
   size_t final_T, n_contrib, ranges, records;
-  size_t keys_in, keys_out, vals_in, vals_out, scan_tmp, sort_tmp;
-  size_t scan_tmp_bytes, sort_tmp_bytes;
+  size_t dkey_in, dkey_out, perm_in, perm;                    // depth sort of the Gaussians (u32 each, per P)
+  size_t keys_in, keys_out, vals_in, vals_out, scan_tmp, sort_tmp, dsort_tmp;   // tile keys are u32 now
+  size_t scan_tmp_bytes, sort_tmp_bytes, dsort_tmp_bytes;
   size_t total;
 };
 // needs a CUDA device only for the two CUB size queries

@@ -4,16 +4,9 @@
 // Adam semantics: torch.optim.Adam(eps=1e-15, betas=(0.9,0.999)) as set up in
 // gaussian_splatting/scene/gaussian_model.py:285 and utils/slam_frontend.py:453.
 #include "launchers.h"
+#include "loss_pixel.cuh"
 
 namespace mgs {
-
-struct LossK {
-  int mode, npix, use_depth;
-  float thr, alpha, delta, scale, eps;
-  const float *image, *depth, *opacity, *gt, *gt_depth, *mask, *a, *b;
-};
-
-__device__ __forceinline__ float sgn(float x) { return (float)((x > 0.f) - (x < 0.f)); }
 
 // partial sums per block: [0] loss (L1 modes) or sum of squares (Huber), [1] dL/da, [2] dL/db, [3] depth term
 // pass 0: reductions only (needed first for the Huber norm); pass 1: gradients.  L1 modes do both in one launch.
@@ -24,75 +17,23 @@ loss_kernel(const LossK k, const float* __restrict__ norm_in, double* __restrict
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
   if (p < k.npix) {
-    const float a_raw = k.a ? k.a[0] : 1.f;
-    const float ea = k.a ? fabsf(a_raw) + k.eps : 1.f;
-    const float eb = k.b ? k.b[0] : 0.f;
-    const float sa = k.a ? sgn(a_raw) : 0.f;
-    const float g0 = k.gt[p], g1 = k.gt[k.npix + p], g2 = k.gt[2 * k.npix + p];
-    float m = (g0 + g1 + g2) > k.thr ? 1.f : 0.f;
-    if (k.mask) m *= k.mask[p];
-    const float op = k.opacity ? k.opacity[p] : 1.f;
-    const float w = (k.mode == MGS_LOSS_MAP_L1) ? 1.f : op;   // mapping loss has no opacity weight
-    const float gt3[3] = {g0, g1, g2};
     float grad_scale = k.scale;
     if (k.mode == MGS_LOSS_TRACK_HUBER) {
       if (WRITE_GRADS) { const float nrm = norm_in[0]; grad_scale = nrm > 0.f ? k.scale / nrm : 0.f; }
     } else {
       grad_scale *= (k.use_depth ? k.alpha : 1.f) / (3.f * (float)k.npix);
     }
-#pragma unroll
-    for (int c = 0; c < 3; c++) {
-      const float img = k.image[c * k.npix + p];
-      const float iab = ea * img + eb;
-      const float r = w * (iab * m - gt3[c] * m);
-      float dr;  // dLoss/dr up to grad_scale
-      if (k.mode == MGS_LOSS_TRACK_HUBER) {
-        const float ar = fabsf(r);
-        float h, dh;
-        if (ar < k.delta) { h = r; dh = 1.f; }
-        else { const float sq = sqrtf(2.f * k.delta * ar - k.delta * k.delta); h = sq * sgn(r); dh = k.delta / sq; }
-        if (REDUCE) acc[0] += h * h;
-        dr = h * dh;
-      } else {
-        if (REDUCE) acc[0] += fabsf(r);
-        dr = sgn(r);
-      }
-      if (WRITE_GRADS) {
-        const float gi = grad_scale * dr * w * m;   // d r / d iab = w*m
-        dL_dimage[c * k.npix + p] = gi * ea;
-        acc[1] += gi * img * sa;
-        acc[2] += gi;
-      }
-    }
-    if (k.use_depth && k.mode != MGS_LOSS_TRACK_HUBER) {
-      const float gd = k.gt_depth[p];
-      float dm = gd > 0.01f ? 1.f : 0.f;
-      if (k.mode == MGS_LOSS_TRACK_L1) dm *= (op > 0.95f) ? 1.f : 0.f;
-      const float d = k.depth[p];
-      const float rd = d * dm - gd * dm;
-      if (REDUCE) acc[3] += fabsf(rd);
-      if (WRITE_GRADS) dL_ddepth[p] = k.scale * (1.f - k.alpha) / (float)k.npix * sgn(rd) * dm;
-    } else if (WRITE_GRADS && dL_ddepth != nullptr) {
-      dL_ddepth[p] = 0.f;
+    const float img[3] = {k.image[p], k.image[k.npix + p], k.image[2 * k.npix + p]};
+    const float op = k.opacity ? k.opacity[p] : 1.f;
+    const float d = (k.use_depth && k.depth) ? k.depth[p] : 0.f;
+    float g_img[3], g_d;
+    loss_pixel<WRITE_GRADS, REDUCE>(k, p, img, d, op, grad_scale, acc, g_img, g_d);
+    if (WRITE_GRADS) {
+      dL_dimage[p] = g_img[0]; dL_dimage[k.npix + p] = g_img[1]; dL_dimage[2 * k.npix + p] = g_img[2];
+      if (dL_ddepth != nullptr) dL_ddepth[p] = g_d;
     }
   }
-  // deterministic two-level reduction: warp shuffle -> shared -> one double4 per block
-  __shared__ float part[8][4];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-#pragma unroll
-  for (int q = 0; q < 4; q++) {
-    float x = acc[q];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-    if (lane == 0) part[warp][q] = x;
-  }
-  __syncthreads();
-  if (threadIdx.x < 4) {
-    double x = 0.0;
-#pragma unroll
-    for (int w8 = 0; w8 < 8; w8++) x += (double)part[w8][threadIdx.x];
-    partials[(size_t)blockIdx.x * 4 + threadIdx.x] = x;
-  }
+  loss_block_reduce(acc, partials + (size_t)blockIdx.x * 4);
 }
 
 // stage: 0 = Huber norm only (writes norm to out_loss), 1 = final (loss + dab)
@@ -208,12 +149,7 @@ int mgs_loss_fwd_bwd(const mgs_loss_args* args, float* out_loss, float* out_dab,
   if (args->use_depth && args->mode == MGS_LOSS_TRACK_HUBER) { set_error("loss: the per-pixel rgbd variant raises NotImplementedError in the reference (slam_utils.py:219)"); return MGS_EINVAL; }
   if (scratch_bytes < mgs_loss_scratch_bytes(args->H, args->W)) { set_error("loss: scratch too small"); return MGS_ENOSPC; }
   cudaStream_t s = (cudaStream_t)stream;
-  LossK k;
-  k.mode = args->mode; k.npix = args->H * args->W; k.use_depth = args->use_depth;
-  k.thr = args->rgb_boundary_threshold; k.alpha = args->alpha; k.delta = args->huber_delta; k.scale = args->loss_scale;
-  k.eps = 1e-8f;  // Camera.exposure_eps (utils/camera_utils.py:55)
-  k.image = args->image; k.depth = args->depth; k.opacity = args->opacity; k.gt = args->gt_image;
-  k.gt_depth = args->gt_depth; k.mask = args->grad_mask; k.a = args->exposure_a; k.b = args->exposure_b;
+  const LossK k = make_loss_k(args);
   double* partials = reinterpret_cast<double*>(scratch);
   const int nblocks = (k.npix + 255) / 256;
   const bool grads = dL_dimage != nullptr;

@@ -12,15 +12,12 @@
 //      sketch row for the sketched Jacobian (__init__.py:216-253, backward_sketch_jacobian.cu), where the
 //      SAME tau image serves every stack because only the pixel->row routing differs between stacks.
 #include "launchers.h"
-#include "gaussian_backward.cuh"
+#include "pose_jac.cuh"
 #include "tma.cuh"
 
 namespace mgs {
 
 constexpr int POSE_BATCH = 128;
-
-// B_g layout: NCOL columns (mx, my, cxx, cxy, cyy, depth[, r, g, b]) of 6 floats each, padded to float4s.
-template <int NCOL> struct PoseJac { static constexpr int kFloats = (NCOL * 6 + 3) / 4 * 4; };
 
 template <int NCOL>
 __global__ void __launch_bounds__(256)
@@ -30,47 +27,12 @@ pose_jacobian_kernel(const ViewConst v, const int P, const float* __restrict__ m
                      const float4* __restrict__ rgb4, float* __restrict__ jac) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P || !(radii[idx] > 0)) return;
-  constexpr int NF = PoseJac<NCOL>::kFloats;
-  float B[NF];
-#pragma unroll
-  for (int k = 0; k < NF; k++) B[k] = 0.f;
   const float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
-  GaussCtx g;
-  if (cov3D_precomp != nullptr) {
-#pragma unroll
-    for (int k = 0; k < 6; k++) g.cov6[k] = cov3D_precomp[6 * (size_t)idx + k];
-  } else cov3d_from_scale_rot_b(scales, rotations, idx, v.scale_modifier, g.cov6);
-  gauss_ctx_init(g, v, p);
-  ProjCtx q;
-  proj_ctx_init(q, v, p);
-  float jx[6], jy[6];
-  mean2d_tau_jac(q, v.proj_raw, jx, jy);
-#pragma unroll
-  for (int k = 0; k < 6; k++) { B[0 * 6 + k] = jx[k]; B[1 * 6 + k] = jy[k]; }
-#pragma unroll
-  for (int c = 0; c < 3; c++) {
-    ConicChainOut cc;
-    conic_chain(g, v, c == 0 ? 1.f : 0.f, c == 1 ? 1.f : 0.f, c == 2 ? 1.f : 0.f, cc);
-#pragma unroll
-    for (int k = 0; k < 6; k++) B[(2 + c) * 6 + k] = cc.tau[k];
-  }
-  B[5 * 6 + 2] = 1.f; B[5 * 6 + 3] = q.pC.y; B[5 * 6 + 4] = -q.pC.x;
-  if (NCOL == 9) {
-    const uint32_t cm = __float_as_uint(rgb4[idx].w);
-#pragma unroll
-    for (int c = 0; c < 3; c++) {
-      const float on = ((cm >> c) & 1u) ? 0.f : 1.f;
-      const float3 dcol = {c == 0 ? on : 0.f, c == 1 ? on : 0.f, c == 2 ? on : 0.f};
-      const float3 dm = sh_backward(v.D, v.M, p, v.campos, shs + (size_t)idx * v.M * 3, dcol, nullptr);
-      B[(6 + c) * 6 + 0] = -dm.x; B[(6 + c) * 6 + 1] = -dm.y; B[(6 + c) * 6 + 2] = -dm.z;
-    }
-  }
-  float4* out = reinterpret_cast<float4*>(jac + (size_t)idx * NF);
-#pragma unroll
-  for (int k = 0; k < NF / 4; k++) out[k] = make_float4(B[4 * k], B[4 * k + 1], B[4 * k + 2], B[4 * k + 3]);
+  const uint32_t cm = (NCOL == 9) ? __float_as_uint(rgb4[idx].w) : 0u;
+  build_pose_jac<NCOL>(v, idx, p, shs, scales, rotations, cov3D_precomp, cm, jac);
 }
 
-template <int NCOL>
+template <int NCOL, bool HAS_DEPTH>
 __global__ void __launch_bounds__(256)
 blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* __restrict__ ranges,
                            const SplatRec* __restrict__ recs, const float* __restrict__ jac,
@@ -101,7 +63,7 @@ blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* 
   float dpx0 = 0.f, dpx1 = 0.f, dpx2 = 0.f, dpd = 0.f;
   if (inside) {
     dpx0 = dL_dpix[pix]; dpx1 = dL_dpix[plane + pix]; dpx2 = dL_dpix[2 * plane + pix];
-    dpd = dL_dpix_depth[pix];
+    if (HAS_DEPTH) dpd = dL_dpix_depth[pix];
   }
   if (tid == 0) {
     s_max_contrib = 0;
@@ -166,16 +128,17 @@ blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* 
       if (__ballot_sync(0xffffffffu, !skip) == 0u) continue;
       if (!skip) {
         const float4 g2 = rec4[3 * j + 2];
-        T = T / (1.f - alpha);
+        const float inv_1ma = __fdividef(1.f, 1.f - alpha);   // 1-alpha in [0.01,1]: MUFU.RCP, 1 ulp vs the IEEE divide
+        T = T * inv_1ma;
         const float dchannel_dcolor = alpha * T;
         float dL_dalpha = 0.0f;
         ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = g2.x; dL_dalpha += (g2.x - ar0) * dpx0;
         ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = g2.y; dL_dalpha += (g2.y - ar1) * dpx1;
         ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = g2.z; dL_dalpha += (g2.z - ar2) * dpx2;
-        ard = last_alpha * ld + (1.f - last_alpha) * ard; ld = g0.z; dL_dalpha += (g0.z - ard) * dpd;
+        if (HAS_DEPTH) { ard = last_alpha * ld + (1.f - last_alpha) * ard; ld = g0.z; dL_dalpha += (g0.z - ard) * dpd; }
         dL_dalpha *= T;
         last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+        dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
         const float dL_dG = g1.w * dL_dalpha;
         const float gdx = G * dx, gdy = G * dy;
         float s[NCOL];
@@ -184,16 +147,18 @@ blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* 
         s[2] = -0.5f * gdx * dx * dL_dG;
         s[3] = -0.5f * gdx * dy * dL_dG;
         s[4] = -0.5f * gdy * dy * dL_dG;
-        s[5] = dchannel_dcolor * dpd;
+        s[5] = HAS_DEPTH ? dchannel_dcolor * dpd : 0.f;
         if (NCOL == 9) { s[6] = dchannel_dcolor * dpx0; s[7] = dchannel_dcolor * dpx1; s[8] = dchannel_dcolor * dpx2; }
         const float4* J4 = reinterpret_cast<const float4*>(jstage + j * NF);
         float Bf[NF];
 #pragma unroll
         for (int k = 0; k < NF / 4; k++) { const float4 t4 = J4[k]; Bf[4 * k] = t4.x; Bf[4 * k + 1] = t4.y; Bf[4 * k + 2] = t4.z; Bf[4 * k + 3] = t4.w; }
 #pragma unroll
-        for (int c = 0; c < NCOL; c++)
+        for (int c = 0; c < NCOL; c++) {
+          if (!HAS_DEPTH && c == 5) continue;   // no depth gradient (mono tracking): skip the depth column
 #pragma unroll
           for (int k = 0; k < 6; k++) tau[k] = fmaf(s[c], Bf[c * 6 + k], tau[k]);
+        }
       }
      }
     }
@@ -252,6 +217,28 @@ size_t backward_pose_scratch_bytes(int P, int W, int H) {
   return ((size_t)(P > 0 ? P : 1) * PoseJac<9>::kFloats * sizeof(float) + 255) / 256 * 256;
 }
 
+template <int NC, bool HD>
+static int launch_blend_pose_t(const BackwardArgs& a, const float* jac, float* tau_image, cudaStream_t s) {
+  const ViewConst& v = a.v;
+  prof_begin("blend_backward_pose", s);
+  blend_backward_pose_kernel<NC, HD><<<v.gx * v.gy, 256, 0, s>>>(
+      v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges), ws_ptr<SplatRec>(a.ws, a.L.records), jac, v.bg,
+      ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img, a.dL_ddepth_img,
+      tau_image, a.dL_dtau_sum);
+  prof_end(s);
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
+}
+
+// blend pass only: `jac` already holds the per-Gaussian maps (built by pose_jacobian_kernel or by the fused
+// tracking preprocess); a null dL_ddepth_img means "no depth gradient" and drops the depth column entirely
+int launch_blend_backward_pose(const BackwardArgs& a, const float* jac, bool with_color, cudaStream_t s) {
+  float* tau_image = a.sketch_dtau;  // reused field: per-pixel tau image [6,H,W] (may be null)
+  const bool hd = a.dL_ddepth_img != nullptr;
+  if (with_color) return hd ? launch_blend_pose_t<9, true>(a, jac, tau_image, s) : launch_blend_pose_t<9, false>(a, jac, tau_image, s);
+  return hd ? launch_blend_pose_t<6, true>(a, jac, tau_image, s) : launch_blend_pose_t<6, false>(a, jac, tau_image, s);
+}
+
 int launch_backward_pose(const BackwardArgs& a, cudaStream_t s) {
   const ViewConst& v = a.v;
   const int P = a.P;
@@ -259,27 +246,17 @@ int launch_backward_pose(const BackwardArgs& a, cudaStream_t s) {
   if (a.scratch == nullptr || a.scratch_bytes < need) { set_error("pose backward scratch too small: %zu < %zu", a.scratch_bytes, need); return MGS_ENOSPC; }
   float* jac = reinterpret_cast<float*>(a.scratch);
   if (a.dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
-  const int tiles = v.gx * v.gy;
   const bool with_color = (a.shs != nullptr && v.D > 0);
-  float* tau_image = a.sketch_dtau;  // reused field: per-pixel tau image [6,H,W] (may be null)
-#define MGS_POSE_LAUNCH(NC)                                                                                          \
-  prof_begin("pose_jacobian", s);                                                                                   \
-  pose_jacobian_kernel<NC><<<(P + 255) / 256, 256, 0, s>>>(v, P, a.means3D, a.shs, a.scales, a.rotations,            \
-                                                            a.cov3D_precomp, a.radii, ws_ptr<float4>(a.ws, a.L.rgb4), \
-                                                            jac);                                                     \
-  prof_end(s);                                                                                                        \
-  MGS_LAUNCH_CHECK();                                                                                                 \
-  prof_begin("blend_backward_pose", s);                                                                             \
-  blend_backward_pose_kernel<NC><<<tiles, 256, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges),              \
-                                                        ws_ptr<SplatRec>(a.ws, a.L.records), jac, v.bg,               \
-                                                        ws_ptr<float>(a.ws, a.L.final_T),                             \
-                                                        ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img,       \
-                                                        a.dL_ddepth_img, tau_image, a.dL_dtau_sum);                   \
-  prof_end(s);                                                                                                        \
+  prof_begin("pose_jacobian", s);
+  if (with_color)
+    pose_jacobian_kernel<9><<<(P + 255) / 256, 256, 0, s>>>(v, P, a.means3D, a.shs, a.scales, a.rotations, a.cov3D_precomp,
+                                                            a.radii, ws_ptr<float4>(a.ws, a.L.rgb4), jac);
+  else
+    pose_jacobian_kernel<6><<<(P + 255) / 256, 256, 0, s>>>(v, P, a.means3D, a.shs, a.scales, a.rotations, a.cov3D_precomp,
+                                                            a.radii, ws_ptr<float4>(a.ws, a.L.rgb4), jac);
+  prof_end(s);
   MGS_LAUNCH_CHECK();
-  if (with_color) { MGS_POSE_LAUNCH(9) } else { MGS_POSE_LAUNCH(6) }
-#undef MGS_POSE_LAUNCH
-  return MGS_OK;
+  return launch_blend_backward_pose(a, jac, with_color, s);
 }
 
 int launch_sketch_reduce(const float* tau_image, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,

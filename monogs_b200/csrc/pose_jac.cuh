@@ -1,0 +1,53 @@
+// Builder of the per-Gaussian linear map screen-space gradients -> pose tangent (see pose_backward.cu).
+#pragma once
+#include "gaussian_backward.cuh"
+
+namespace mgs {
+
+// B_g layout: NCOL columns (mx, my, cxx, cxy, cyy, depth[, r, g, b]) of 6 floats each, padded to float4s.
+template <int NCOL> struct PoseJac { static constexpr int kFloats = (NCOL * 6 + 3) / 4 * 4; };
+
+template <int NCOL>
+__device__ __forceinline__ void build_pose_jac(const ViewConst& v, const int idx, const float3& p,
+                                               const float* __restrict__ shs, const float* __restrict__ scales,
+                                               const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
+                                               const uint32_t clamp_mask, float* __restrict__ jac) {
+  constexpr int NF = PoseJac<NCOL>::kFloats;
+  float B[NF];
+#pragma unroll
+  for (int k = 0; k < NF; k++) B[k] = 0.f;
+  GaussCtx g;
+  if (cov3D_precomp != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) g.cov6[k] = cov3D_precomp[6 * (size_t)idx + k];
+  } else cov3d_from_scale_rot_b(scales, rotations, idx, v.scale_modifier, g.cov6);
+  gauss_ctx_init(g, v, p);
+  ProjCtx q;
+  proj_ctx_init(q, v, p);
+  float jx[6], jy[6];
+  mean2d_tau_jac(q, v.proj_raw, jx, jy);
+#pragma unroll
+  for (int k = 0; k < 6; k++) { B[0 * 6 + k] = jx[k]; B[1 * 6 + k] = jy[k]; }
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    ConicChainOut cc;
+    conic_chain(g, v, c == 0 ? 1.f : 0.f, c == 1 ? 1.f : 0.f, c == 2 ? 1.f : 0.f, cc);
+#pragma unroll
+    for (int k = 0; k < 6; k++) B[(2 + c) * 6 + k] = cc.tau[k];
+  }
+  B[5 * 6 + 2] = 1.f; B[5 * 6 + 3] = q.pC.y; B[5 * 6 + 4] = -q.pC.x;
+  if (NCOL == 9) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const float on = ((clamp_mask >> c) & 1u) ? 0.f : 1.f;
+      const float3 dcol = {c == 0 ? on : 0.f, c == 1 ? on : 0.f, c == 2 ? on : 0.f};
+      const float3 dm = sh_backward(v.D, v.M, p, v.campos, shs + (size_t)idx * v.M * 3, dcol, nullptr);
+      B[(6 + c) * 6 + 0] = -dm.x; B[(6 + c) * 6 + 1] = -dm.y; B[(6 + c) * 6 + 2] = -dm.z;
+    }
+  }
+  float4* out = reinterpret_cast<float4*>(jac + (size_t)idx * NF);
+#pragma unroll
+  for (int k = 0; k < NF / 4; k++) out[k] = make_float4(B[4 * k], B[4 * k + 1], B[4 * k + 2], B[4 * k + 3]);
+}
+
+}  // namespace mgs

@@ -147,7 +147,8 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
       for (int k = 0; k < 16; k++) v[k] = 0.f;
       if (!skip) {
         const float4 g2 = rec4[3 * j + 2];
-        T = T / (1.f - alpha);
+        const float inv_1ma = __fdividef(1.f, 1.f - alpha);   // 1-alpha in [0.01,1]: MUFU.RCP, 1 ulp vs the IEEE divide
+        T = T * inv_1ma;
         const float dchannel_dcolor = alpha * T;
         float dL_dalpha = 0.0f;
         ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = g2.x; dL_dalpha += (g2.x - ar0) * dpx0;
@@ -156,7 +157,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
         ard = last_alpha * ld + (1.f - last_alpha) * ard; ld = g0.z; dL_dalpha += (g0.z - ard) * dpd;
         dL_dalpha *= T;
         last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+        dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
         const float dL_dG = g1.w * dL_dalpha;   // clamp at 0.99 deliberately ignored (Q6)
         const float gdx = G * dx, gdy = G * dy;
         const float dG_ddelx = -gdx * g1.x - gdy * g1.y;

@@ -2,8 +2,10 @@
 // packed records, alpha blend.  Replaces CudaRasterizer::Rasterizer::forward (rasterizer_impl.cu:198-344),
 // FORWARD::preprocess / FORWARD::render (forward.cu:157-258, 263-392).
 #include "launchers.h"
+#include "pose_jac.cuh"
 #include <cub/device/device_scan.cuh>
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
 #include <cstdarg>
 #include <cstdio>
 #include <map>
@@ -58,13 +60,31 @@ int prof_report(char* buf, size_t n) {
 
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
+// tiles_touched read through the depth-order permutation (input iterator of the scan)
+struct PermLoad {
+  const uint32_t* tiles_touched;
+  __host__ __device__ __forceinline__ uint32_t operator()(const uint32_t& g) const { return tiles_touched[g]; }
+};
+using PermIter = cub::TransformInputIterator<uint32_t, PermLoad, const uint32_t*>;
+
 int ws_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, WsLayout* L) {
   if (P < 0 || W <= 0 || H <= 0 || R_cap < 0) { set_error("ws_layout: bad sizes"); return MGS_EINVAL; }
   const size_t Pp = (size_t)(P > 0 ? P : 1), Rp = (size_t)(R_cap > 0 ? R_cap : 1);
   const size_t npix = (size_t)W * H;
   const size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
+  size_t scan_b = 0, sort_b = 0, dsort_b = 0;
+  cudaError_t e = cub::DeviceScan::InclusiveSum(nullptr, scan_b, PermIter(nullptr, PermLoad{nullptr}), (uint32_t*)nullptr, (int)Pp);
+  if (e == cudaSuccess)
+    e = cub::DeviceRadixSort::SortPairs(nullptr, sort_b, (uint32_t*)nullptr, (uint32_t*)nullptr,
+                                        (uint32_t*)nullptr, (uint32_t*)nullptr, (int)Rp);
+  if (e == cudaSuccess)
+    e = cub::DeviceRadixSort::SortPairs(nullptr, dsort_b, (uint32_t*)nullptr, (uint32_t*)nullptr,
+                                        (uint32_t*)nullptr, (uint32_t*)nullptr, (int)Pp);
+  if (e != cudaSuccess) { set_error("CUB size query failed: %s", cudaGetErrorString(e)); return MGS_ECUDA; }
+  L->scan_tmp_bytes = scan_b; L->sort_tmp_bytes = sort_b; L->dsort_tmp_bytes = dsort_b;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes); return o; };
+  // ---- R_cap-independent part (stage 1 and backward use only this) ----
   L->header = take(sizeof(WsHeader));
   L->depths = take(Pp * 4);
   L->means2D = take(Pp * 8);
@@ -72,22 +92,21 @@ int ws_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, WsLayout* L) {
   L->rgb4 = take(Pp * 16);
   L->tiles_touched = take(Pp * 4);
   L->point_offsets = take(Pp * 4);
+  L->dkey_in = take(Pp * 4);
+  L->dkey_out = take(Pp * 4);
+  L->perm_in = take(Pp * 4);
+  L->perm = take(Pp * 4);
+  L->scan_tmp = take(scan_b);
+  L->dsort_tmp = take(dsort_b);
   L->final_T = take(npix * 4);
   L->n_contrib = take(npix * 4);
   L->ranges = take(tiles * 8);
+  // ---- per-instance part ----
   L->records = take(Rp * sizeof(SplatRec));
-  L->keys_in = take(Rp * 8);
-  L->keys_out = take(Rp * 8);
+  L->keys_in = take(Rp * 4);
+  L->keys_out = take(Rp * 4);
   L->vals_in = take(Rp * 4);
   L->vals_out = take(Rp * 4);
-  size_t scan_b = 0, sort_b = 0;
-  cudaError_t e = cub::DeviceScan::InclusiveSum(nullptr, scan_b, (uint32_t*)nullptr, (uint32_t*)nullptr, (int)Pp);
-  if (e == cudaSuccess)
-    e = cub::DeviceRadixSort::SortPairs(nullptr, sort_b, (uint64_t*)nullptr, (uint64_t*)nullptr,
-                                        (uint32_t*)nullptr, (uint32_t*)nullptr, (int)Rp);
-  if (e != cudaSuccess) { set_error("CUB size query failed: %s", cudaGetErrorString(e)); return MGS_ECUDA; }
-  L->scan_tmp_bytes = scan_b; L->sort_tmp_bytes = sort_b;
-  L->scan_tmp = take(scan_b);
   L->sort_tmp = take(sort_b);
   L->total = off;
   return MGS_OK;
@@ -178,6 +197,7 @@ __device__ __forceinline__ float3 sh_to_rgb(int idx, int deg, int M, const float
   return make_float3(c[0], c[1], c[2]);
 }
 
+template <int JAC_NCOL>   // 0: plain; 6 / 9: also build the pose Jacobian of visible Gaussians (tracking path)
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const ViewConst v, const int P,
                   const float* __restrict__ means3D, const float* __restrict__ opacities,
@@ -186,11 +206,12 @@ preprocess_kernel(const ViewConst v, const int P,
                   const float* __restrict__ cov3D_precomp,
                   int32_t* __restrict__ radii, float* __restrict__ depths, float2* __restrict__ means2D,
                   float4* __restrict__ conic_opacity, float4* __restrict__ rgb4,
-                  uint32_t* __restrict__ tiles_touched) {
+                  uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ dkey, uint32_t* __restrict__ iota,
+                  float* __restrict__ jac) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= P) return;
   int my_radius_i = 0;
-  uint32_t touched = 0;
+  uint32_t touched = 0, depth_key = 0xFFFFFFFFu;   // culled Gaussians sort to the end and emit nothing
   do {
     const float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
     // near cull only (auxiliary.h:139-164)
@@ -220,19 +241,23 @@ preprocess_kernel(const ViewConst v, const int P,
     tile_rect(pix, (int)my_radius, v.gx, v.gy, rmin, rmax);
     const uint32_t area = (rmax.x - rmin.x) * (rmax.y - rmin.y);
     if (area == 0) break;
+    uint32_t cm = 0;
     if (colors_precomp == nullptr) {
-      uint32_t cm;
       const float3 c = sh_to_rgb(idx, v.D, v.M, p, v.campos, shs, cm);
       rgb4[idx] = make_float4(c.x, c.y, c.z, __uint_as_float(cm));
     }
+    if (JAC_NCOL > 0) build_pose_jac<(JAC_NCOL > 0 ? JAC_NCOL : 6)>(v, idx, p, shs, scales, rotations, cov3D_precomp, cm, jac);
     depths[idx] = pview.z;
     means2D[idx] = pix;
     conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
     my_radius_i = (int)my_radius;
     touched = area;
+    depth_key = __float_as_uint(pview.z);   // > 0.2, so the bit pattern orders like the float (rasterizer_impl.cu:99-101)
   } while (0);
   radii[idx] = my_radius_i;
   tiles_touched[idx] = touched;
+  dkey[idx] = depth_key;
+  iota[idx] = (uint32_t)idx;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -245,28 +270,28 @@ __global__ void bin_header_kernel(const uint32_t* __restrict__ point_offsets, in
   hdr->r_used = n > R_cap ? R_cap : n;
 }
 
-// K3: emit (tile|depth) keys + Gaussian ids (rasterizer_impl.cu:70-111); slots [r_used, R_cap) get a
-// sentinel key whose tile id is never a real tile so the sort length can stay a host constant.
+// K3: emit tile keys + Gaussian ids (rasterizer_impl.cu:70-111).  The reference sorts 64-bit (tile|depth) keys in
+// one go; here the Gaussians were first stably sorted by depth bits (P items, 32-bit keys), instances are emitted in
+// that order, and only the tile bits remain to be sorted (stable LSD radix => identical final permutation, ties keep
+// ascending Gaussian index, at a third of the sort passes on 8-byte instead of 12-byte pairs).  Slots
+// [r_used, R_cap) get a sentinel tile id that is never a real tile so the sort length stays a host constant.
 __global__ void __launch_bounds__(256)
-emit_keys_kernel(const int P, const uint32_t R_cap, const int gx, const int gy, const uint64_t sentinel,
-                 const float2* __restrict__ means2D, const float* __restrict__ depths,
+emit_keys_kernel(const int P, const uint32_t R_cap, const int gx, const int gy, const uint32_t sentinel,
+                 const uint32_t* __restrict__ perm, const float2* __restrict__ means2D,
                  const uint32_t* __restrict__ offsets, const int32_t* __restrict__ radii,
                  const WsHeader* __restrict__ hdr,
-                 uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+                 uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < (uint32_t)P) {
-    const int rad = radii[i];
+    const uint32_t g = perm[i];
+    const int rad = radii[g];
     if (rad > 0) {
       uint32_t off = (i == 0) ? 0u : offsets[i - 1];
       uint2 rmin, rmax;
-      tile_rect(means2D[i], rad, gx, gy, rmin, rmax);
-      const uint32_t dbits = __float_as_uint(depths[i]);
+      tile_rect(means2D[g], rad, gx, gy, rmin, rmax);
       for (uint32_t y = rmin.y; y < rmax.y; y++)
         for (uint32_t x = rmin.x; x < rmax.x; x++) {
-          if (off < R_cap) {
-            keys[off] = ((uint64_t)(y * gx + x) << 32) | dbits;
-            vals[off] = i;
-          }
+          if (off < R_cap) { keys[off] = y * gx + x; vals[off] = g; }
           off++;
         }
     }
@@ -278,7 +303,7 @@ emit_keys_kernel(const int P, const uint32_t R_cap, const int gx, const int gy, 
 // sorted list, the 48-B records the blend kernels stream.
 __global__ void __launch_bounds__(256)
 ranges_records_kernel(const uint32_t R_cap, const WsHeader* __restrict__ hdr,
-                      const uint64_t* __restrict__ keys, const uint32_t* __restrict__ ids,
+                      const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ids,
                       const float2* __restrict__ means2D, const float* __restrict__ depths,
                       const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
                       const float* __restrict__ colors_precomp,
@@ -286,10 +311,10 @@ ranges_records_kernel(const uint32_t R_cap, const WsHeader* __restrict__ hdr,
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   const uint32_t L = hdr->r_used;
   if (i >= L) return;
-  const uint32_t tile = (uint32_t)(keys[i] >> 32);
+  const uint32_t tile = keys[i];
   if (i == 0) ranges[tile].x = 0;
   else {
-    const uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
+    const uint32_t prev = keys[i - 1];
     if (tile != prev) { ranges[prev].y = i; ranges[tile].x = i; }
   }
   if (i == L - 1) ranges[tile].y = L;
@@ -308,16 +333,32 @@ ranges_records_kernel(const uint32_t R_cap, const WsHeader* __restrict__ hdr,
 
 int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
                       const float* colors_precomp, const float* scales, const float* rotations,
-                      const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s) {
+                      const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
+                      float* jac, int jac_ncol) {
   if (P == 0) return MGS_OK;
-  MGS_PROF("preprocess", s, preprocess_kernel<<<(P + 255) / 256, 256, 0, s>>>(
-      v, P, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
-      ws_ptr<float>(ws, L.depths), ws_ptr<float2>(ws, L.means2D), ws_ptr<float4>(ws, L.conic_opacity),
-      ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched)));
+#define MGS_PRE_ARGS v, P, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,           \
+      ws_ptr<float>(ws, L.depths), ws_ptr<float2>(ws, L.means2D), ws_ptr<float4>(ws, L.conic_opacity),               \
+      ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched), ws_ptr<uint32_t>(ws, L.dkey_in),            \
+      ws_ptr<uint32_t>(ws, L.perm_in), jac
+  prof_begin("preprocess", s);
+  if (jac == nullptr) preprocess_kernel<0><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+  else if (jac_ncol == 9) preprocess_kernel<9><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+  else preprocess_kernel<6><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+  prof_end(s);
+#undef MGS_PRE_ARGS
   MGS_LAUNCH_CHECK();
+  // stable sort of the Gaussians by depth bits -> perm (depth order, ties by index)
+  size_t dtmp = L.dsort_tmp_bytes;
+  prof_begin("cub_sort_depth", s);
+  MGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(ws_ptr<void>(ws, L.dsort_tmp), dtmp, ws_ptr<uint32_t>(ws, L.dkey_in),
+                                               ws_ptr<uint32_t>(ws, L.dkey_out), ws_ptr<uint32_t>(ws, L.perm_in),
+                                               ws_ptr<uint32_t>(ws, L.perm), P, 0, 32, s));
+  prof_end(s);
+  // inclusive scan of tiles_touched in depth order
   size_t tmp = L.scan_tmp_bytes;
   prof_begin("cub_scan", s);
-  MGS_CUDA_TRY(cub::DeviceScan::InclusiveSum(ws_ptr<void>(ws, L.scan_tmp), tmp, ws_ptr<uint32_t>(ws, L.tiles_touched),
+  MGS_CUDA_TRY(cub::DeviceScan::InclusiveSum(ws_ptr<void>(ws, L.scan_tmp), tmp,
+                                             PermIter(ws_ptr<uint32_t>(ws, L.perm), PermLoad{ws_ptr<uint32_t>(ws, L.tiles_touched)}),
                                              ws_ptr<uint32_t>(ws, L.point_offsets), P, s));
   prof_end(s);
   return MGS_OK;
@@ -332,21 +373,21 @@ int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const
   MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(ws, L.ranges), 0, (size_t)tiles * sizeof(uint2), s));
   if (R_cap == 0 || P == 0) return MGS_OK;
   const uint32_t bit = tile_id_bits(tiles);
-  const uint64_t sentinel = ((uint64_t)((1u << bit) - 1u) << 32) | 0xFFFFFFFFull;
+  const uint32_t sentinel = (1u << bit) - 1u;
   const int64_t n_thr = P > R_cap ? P : R_cap;
   MGS_PROF("emit_keys", s, emit_keys_kernel<<<(unsigned)((n_thr + 255) / 256), 256, 0, s>>>(
-      P, (uint32_t)R_cap, v.gx, v.gy, sentinel, ws_ptr<float2>(ws, L.means2D), ws_ptr<float>(ws, L.depths),
-      ws_ptr<uint32_t>(ws, L.point_offsets), radii, hdr, ws_ptr<uint64_t>(ws, L.keys_in),
+      P, (uint32_t)R_cap, v.gx, v.gy, sentinel, ws_ptr<uint32_t>(ws, L.perm), ws_ptr<float2>(ws, L.means2D),
+      ws_ptr<uint32_t>(ws, L.point_offsets), radii, hdr, ws_ptr<uint32_t>(ws, L.keys_in),
       ws_ptr<uint32_t>(ws, L.vals_in)));
   MGS_LAUNCH_CHECK();
   size_t tmp = L.sort_tmp_bytes;
   prof_begin("cub_sort", s);
-  MGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(ws_ptr<void>(ws, L.sort_tmp), tmp, ws_ptr<uint64_t>(ws, L.keys_in),
-                                               ws_ptr<uint64_t>(ws, L.keys_out), ws_ptr<uint32_t>(ws, L.vals_in),
-                                               ws_ptr<uint32_t>(ws, L.vals_out), (int)R_cap, 0, (int)(32 + bit), s));
+  MGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(ws_ptr<void>(ws, L.sort_tmp), tmp, ws_ptr<uint32_t>(ws, L.keys_in),
+                                               ws_ptr<uint32_t>(ws, L.keys_out), ws_ptr<uint32_t>(ws, L.vals_in),
+                                               ws_ptr<uint32_t>(ws, L.vals_out), (int)R_cap, 0, (int)bit, s));
   prof_end(s);
   MGS_PROF("ranges_records", s, ranges_records_kernel<<<(unsigned)((R_cap + 255) / 256), 256, 0, s>>>(
-      (uint32_t)R_cap, hdr, ws_ptr<uint64_t>(ws, L.keys_out), ws_ptr<uint32_t>(ws, L.vals_out),
+      (uint32_t)R_cap, hdr, ws_ptr<uint32_t>(ws, L.keys_out), ws_ptr<uint32_t>(ws, L.vals_out),
       ws_ptr<float2>(ws, L.means2D), ws_ptr<float>(ws, L.depths), ws_ptr<float4>(ws, L.conic_opacity),
       ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records)));
   MGS_LAUNCH_CHECK();

@@ -15,12 +15,14 @@ import torch
 from . import _lib as L
 from .rasterizer import make_view, GaussianRasterizationSettings, _stream
 
-KERNELS_PER_ITER = 14   # own kernels launched per iteration (CUB scan/sort launches not counted)
+KERNELS_PER_ITER = 8    # own kernels per fused iteration: preprocess(+jac), header, emit_keys, ranges_records,
+                        # blend_forward(+loss), blend_backward_pose, track_update (+1 spare: CUB launches not counted)
+KERNELS_PER_ITER_COMPOSED = 14
 
 
 class PoseTracker:
     def __init__(self, means3D, opacities, shs, scales, rotations, sh_degree, cam, bg, T_w2c, mode=L.LOSS_TRACK_HUBER,
-                 use_depth=False, lr=(1e-3, 3e-3, 2e-2, 2e-2), capacity_headroom=1.3, use_graph=True):
+                 use_depth=False, lr=(1e-3, 3e-3, 2e-2, 2e-2), capacity_headroom=1.3, use_graph=True, fused=True):
         lib = self.lib = L.lib()
         dev = self.dev = means3D.device
         f = dict(device=dev, dtype=torch.float32)
@@ -61,6 +63,8 @@ class PoseTracker:
         self.loss_scratch = torch.empty(lib.mgs_loss_scratch_bytes(self.H, self.W), device=dev, dtype=torch.uint8)
         self.bwd_scratch = torch.empty(max(lib.mgs_raster_backward_pose_scratch_bytes(self.P, self.W, self.H), 256),
                                        device=dev, dtype=torch.uint8)
+        self.fused = fused
+        self.track_scratch = torch.empty(lib.mgs_track_scratch_bytes(self.P, self.W, self.H), device=dev, dtype=torch.uint8)
         self.headroom = capacity_headroom
         self.R_cap, self.ws = 0, None
         self.use_graph, self.graph = use_graph, None
@@ -95,8 +99,36 @@ class PoseTracker:
         a.exposure_a, a.exposure_b = self.params[6:7].data_ptr(), self.params[7:8].data_ptr()
         return a
 
+    def _track_args(self):
+        t = L.MgsTrackArgs()
+        t.view = self.view
+        t.P = self.P
+        t.means3D, t.opacities, t.shs = self.means3D.data_ptr(), self.opacities.data_ptr(), self.shs.data_ptr()
+        t.scales, t.rotations = self.scales.data_ptr(), self.rotations.data_ptr()
+        t.loss_mode, t.use_depth = self.mode, int(self.use_depth)
+        t.rgb_boundary_threshold, t.alpha, t.huber_delta = 0.01, 0.95, 0.01
+        t.gt_image = self.gt_image.data_ptr()
+        t.gt_depth = self.gt_depth.data_ptr() if self.gt_depth is not None else None
+        t.grad_mask = self.grad_mask.data_ptr() if self.grad_mask is not None else None
+        t.T_w2c, t.params = self.T.data_ptr(), self.params.data_ptr()
+        t.exp_avg, t.exp_avg_sq, t.step_counter = self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.step_dev.data_ptr()
+        for i in range(4):
+            t.lr[i] = self.lr[i]
+        t.beta1, t.beta2, t.adam_eps, t.converged_threshold = 0.9, 0.999, 1e-15, 1e-4
+        t.out_color, t.out_depth, t.out_opacity = self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr()
+        t.radii, t.n_touched = self.radii.data_ptr(), self.n_touched.data_ptr()
+        t.loss, t.tau, t.dab, t.converged = self.loss.data_ptr(), self.tau.data_ptr(), self.dab.data_ptr(), self.converged.data_ptr()
+        t.workspace, t.workspace_bytes, t.R_cap = self.ws.data_ptr(), self.ws.numel(), self.R_cap
+        t.scratch, t.scratch_bytes = self.track_scratch.data_ptr(), self.track_scratch.numel()
+        return t
+
     def _enqueue(self):
-        """The whole iteration as C-ABI calls on the current stream; no host sync anywhere."""
+        """The whole iteration on the current stream, no host sync anywhere: one fused C-ABI call
+        (mgs_track_iteration) or, with fused=False, the same iteration composed from the individual entry points."""
+        if self.fused:
+            t = self._track_args()
+            L.check(self.lib.mgs_track_iteration(C.byref(t), _stream()), "mgs_track_iteration")
+            return
         lib, s, v = self.lib, _stream(), C.byref(self.view)
         L.check(lib.mgs_raster_preprocess(v, self.P, L.ptr(self.means3D), L.ptr(self.opacities), L.ptr(self.shs), None,
                                           L.ptr(self.scales), L.ptr(self.rotations), None, L.ptr(self.radii),

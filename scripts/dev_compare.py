@@ -41,8 +41,9 @@ names = ["header","depths","means2D","conic_opacity","rgb4","tiles_touched","poi
 o = dict(zip(names, list(off)))
 ws = st.workspace
 R = st.num_rendered
-keys_mine = ws[o["keys_out"]:o["keys_out"] + 8 * R].view(torch.int64)
 list_mine = ws[o["vals_out"]:o["vals_out"] + 4 * R].view(torch.int32)
+Pn = sc.means3D.size(0)
+keys_mine = (ws[o["keys_out"]:o["keys_out"] + 4 * R].view(torch.int32).long() << 32) | (ws[o["depths"]:o["depths"] + 4 * Pn].view(torch.int32)[list_mine.long()].long() & 0xFFFFFFFF)
 tiles = ((cam.W + 15) // 16) * ((cam.H + 15) // 16)
 ranges_mine = ws[o["ranges"]:o["ranges"] + 8 * tiles].view(torch.int32).view(tiles, 2)
 print("keys equal", bool((keys_mine == keys_ref).all()), "list equal", bool((list_mine == list_ref).all()),

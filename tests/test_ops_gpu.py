@@ -83,3 +83,33 @@ def test_pose_update_matches_se3_exp():
         assert int(conv.item()) == int(float((tau ** 2).sum()) < 1e-8)
         assert U.rel_err(view, ref.t()) <= 1e-6
         assert U.rel_err(full, ref.t() @ proj.cpu()) <= 1e-5
+
+
+@pytest.mark.parametrize("mode,use_depth", [(1, False), (0, False), (0, True)])
+def test_fused_track_iteration_matches_composed_entry_points(mode, use_depth):
+    """mgs_track_iteration (loss fused into the forward blend, Jacobian into preprocess, one update kernel) follows
+    the same trajectory as the iteration composed from the individual C-ABI calls, and tracking reduces the loss."""
+    from monogs_b200 import scene as S, rasterizer as RZ
+    from monogs_b200.tracking import PoseTracker
+    sc, cam = U.small_case("dense", T_w2c=torch.eye(4))
+    scd = U.to_dev(sc)
+    bg = torch.tensor([0.05, 0.1, 0.15]).cuda()
+    T_gt = S.se3_exp(torch.tensor(S.GT_TAU)).float()
+    cam_gt = U.to_dev(S.make_camera(cam.W, cam.H, cam.fx, cam.fy, cam.cx, cam.cy, T_gt))
+    gt, _, gt_depth, _, _, _ = RZ.raster_forward(U.settings(cam_gt, bg, sc.sh_degree), scd.means3D, scd.opacities, scd.shs,
+                                                 None, scd.scales, scd.rotations, None)
+    runs = []
+    for fused, graph in ((True, True), (False, False)):
+        tr = PoseTracker(scd.means3D, scd.opacities, scd.shs, scd.scales, scd.rotations, sc.sh_degree, cam, bg, torch.eye(4),
+                         mode=mode, use_depth=use_depth, use_graph=graph, fused=fused)
+        tr.set_frame(gt, gt_depth=gt_depth if use_depth else None)
+        losses = []
+        for _ in range(12):
+            tr.step()
+            losses.append(float(tr.loss))
+        runs.append((losses, tr.T.clone(), tr.tau.clone(), tr.params.clone(), tr.color.clone()))
+    (l0, T0, tau0, p0, c0), (l1, T1, tau1, p1, c1) = runs
+    assert all(abs(a - b) <= 1e-4 * abs(b) + 1e-7 for a, b in zip(l0, l1)), (l0, l1)
+    assert U.rel_err(T0, T1) <= 1e-4 and U.rel_err(p0, p1) <= 1e-3 and U.rel_err(c0, c1) <= 1e-4
+    assert U.rel_err(tau0, tau1) <= 2e-3
+    assert l0[-1] < l0[0]

@@ -44,8 +44,11 @@ def _ws_views(st, P, cam):
     o = dict(zip(names, list(off)))
     ws, R = st.workspace, st.num_rendered
     tiles = ((cam.W + 15) // 16) * ((cam.H + 15) // 16)
-    return dict(keys=ws[o["keys_out"]:o["keys_out"] + 8 * R].view(torch.int64),
-                plist=ws[o["vals_out"]:o["vals_out"] + 4 * R].view(torch.int32),
+    plist = ws[o["vals_out"]:o["vals_out"] + 4 * R].view(torch.int32)
+    tile_keys = ws[o["keys_out"]:o["keys_out"] + 4 * R].view(torch.int32).long()
+    depth_bits = ws[o["depths"]:o["depths"] + 4 * P].view(torch.int32)[plist.long()].long() & 0xFFFFFFFF
+    # the library sorts depth and tile bits in two stable passes; the reference's 64-bit key is their concatenation
+    return dict(keys=(tile_keys << 32) | depth_bits, plist=plist,
                 ranges=ws[o["ranges"]:o["ranges"] + 8 * tiles].view(torch.int32).view(tiles, 2),
                 n_contrib=ws[o["n_contrib"]:o["n_contrib"] + 4 * cam.W * cam.H].view(torch.int32).view(cam.H, cam.W),
                 final_T=ws[o["final_T"]:o["final_T"] + 4 * cam.W * cam.H].view(torch.float32).view(cam.H, cam.W))
