@@ -199,6 +199,8 @@ typedef struct mgs_track_args {
   const float *means3D, *opacities, *shs, *scales, *rotations;
   int32_t loss_mode;   /* MGS_LOSS_TRACK_L1 or MGS_LOSS_TRACK_HUBER */
   int32_t use_depth;   /* rgbd variant of TRACK_L1 */
+  int32_t fast_math;   /* 1: blend exponent via ex2.approx (rel. err ~4e-7) and n_touched NOT produced (left untouched);
+                          0: expf as in the reference, n_touched written */
   float rgb_boundary_threshold, alpha, huber_delta;
   const float *gt_image, *gt_depth, *grad_mask;
   float* T_w2c;        /* f32[4,4] row-major, in/out */

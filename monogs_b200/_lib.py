@@ -48,7 +48,7 @@ class MgsTrackArgs(C.Structure):
         ("view", MgsView), ("P", C.c_int32),
         ("means3D", C.c_void_p), ("opacities", C.c_void_p), ("shs", C.c_void_p), ("scales", C.c_void_p),
         ("rotations", C.c_void_p),
-        ("loss_mode", C.c_int32), ("use_depth", C.c_int32),
+        ("loss_mode", C.c_int32), ("use_depth", C.c_int32), ("fast_math", C.c_int32),
         ("rgb_boundary_threshold", C.c_float), ("alpha", C.c_float), ("huber_delta", C.c_float),
         ("gt_image", C.c_void_p), ("gt_depth", C.c_void_p), ("grad_mask", C.c_void_p),
         ("T_w2c", C.c_void_p), ("params", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),

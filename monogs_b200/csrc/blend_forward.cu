@@ -14,7 +14,7 @@ namespace mgs {
 constexpr int FWD_BATCH = 256;
 constexpr int FWD_STAGES = 2;
 
-template <bool FUSED_LOSS>
+template <bool FUSED_LOSS, bool FAST>   // FAST: approximate exp2 and no n_touched (tracking does not use it)
 __global__ void __launch_bounds__(256)
 blend_forward_kernel(const int W, const int H, const int gx,
                      const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
@@ -87,11 +87,12 @@ blend_forward_kernel(const int W, const int H, const int gx,
         const float dx = g0.x - pxf, dy = g0.y - pyf;
         const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
         bool valid = !done && !(power > 0.0f);
-        const float alpha = min(0.99f, g1.w * expf(power));
+        const float alpha = min(0.99f, g1.w * blend_exp<FAST>(power));
         valid = valid && !(alpha < 1.0f / 255.0f);
         const float test_T = T * (1 - alpha);
         if (valid && test_T < 0.0001f) { done = true; valid = false; }
-        const unsigned touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
+        unsigned touch = 0u;
+        if (!FAST) touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
         if (valid) {
           const float4 g2 = rec4[3 * j + 2];
           C0 += g2.x * alpha * T;
@@ -101,7 +102,7 @@ blend_forward_kernel(const int W, const int H, const int gx,
           T = test_T;
           last_contributor = base + j + 1;
         }
-        if (touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
+        if (!FAST && touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
       }
     }
   }
@@ -139,14 +140,16 @@ int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float*
   prof_begin("blend_forward", s);
   if (fl == nullptr) {
     LossK none{};
-    blend_forward_kernel<false><<<tiles, 256, 0, s>>>(
+    blend_forward_kernel<false, false><<<tiles, 256, 0, s>>>(
         v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
         ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, none, 0.f, nullptr, nullptr, nullptr);
   } else {
-    blend_forward_kernel<true><<<tiles, 256, 0, s>>>(
-        v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
-        ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, *fl->k, fl->grad_scale, fl->g_img,
-        fl->g_depth, fl->partials);
+#define MGS_FWD_ARGS v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg,                  \
+        ws_ptr<float>(ws, L.final_T), ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, \
+        *fl->k, fl->grad_scale, fl->g_img, fl->g_depth, fl->partials
+    if (fl->fast) blend_forward_kernel<true, true><<<tiles, 256, 0, s>>>(MGS_FWD_ARGS);
+    else blend_forward_kernel<true, false><<<tiles, 256, 0, s>>>(MGS_FWD_ARGS);
+#undef MGS_FWD_ARGS
   }
   prof_end(s);
   MGS_LAUNCH_CHECK();

@@ -160,6 +160,18 @@ __device__ __forceinline__ bool splat_hits(const float* rec, float x0, float x1,
   return (x + h.x >= x0) && (x - h.x <= x1) && (y + h.y >= y0) && (y - h.y <= y1);
 }
 
+// exp() of the blend exponent.  FAST = false: expf, bit-identical to the reference's images.  FAST = true (fused
+// tracking iteration only): one FMUL + MUFU.EX2 (ex2.approx.ftz), relative error ~4e-7 — far inside the 1e-4 image
+// tolerance; forward and backward of one iteration always use the same variant, so T is recovered consistently.
+template <bool FAST> __device__ __forceinline__ float blend_exp(float power) {
+  if (FAST) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(power * 1.4426950408889634f));
+    return r;
+  }
+  return expf(power);
+}
+
 // SH basis constants (auxiliary.h:21-39)
 __device__ constexpr float kSH0 = 0.28209479177387814f;
 __device__ constexpr float kSH1 = 0.4886025119029199f;

@@ -14,7 +14,7 @@ int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const
                    const WsLayout& L, int64_t R_cap, cudaStream_t s);
 struct LossK;
 // optional fused loss epilogue of the forward blend (tracking path): per-pixel loss + un-normalised gradient images
-struct FusedLoss { const LossK* k; float grad_scale; float* g_img; float* g_depth; double* partials; };
+struct FusedLoss { const LossK* k; float grad_scale; float* g_img; float* g_depth; double* partials; bool fast; };
 int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
                          float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl = nullptr);
 
@@ -30,7 +30,7 @@ struct BackwardArgs {
   int sketch_dim; const int32_t* sketch_indices; float* sketch_dtau;
 };
 int launch_backward(const BackwardArgs& a, cudaStream_t s);
-int launch_blend_backward_pose(const BackwardArgs& a, const float* jac, bool with_color, cudaStream_t s);
+int launch_blend_backward_pose(const BackwardArgs& a, const float* jac, bool with_color, cudaStream_t s, bool fast = false);
 size_t backward_scratch_bytes(int P, int sketch_dim);
 
 }  // namespace mgs

@@ -32,7 +32,7 @@ pose_jacobian_kernel(const ViewConst v, const int P, const float* __restrict__ m
   build_pose_jac<NCOL>(v, idx, p, shs, scales, rotations, cov3D_precomp, cm, jac);
 }
 
-template <int NCOL, bool HAS_DEPTH>
+template <int NCOL, bool HAS_DEPTH, bool FAST>
 __global__ void __launch_bounds__(256)
 blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* __restrict__ ranges,
                            const SplatRec* __restrict__ recs, const float* __restrict__ jac,
@@ -122,7 +122,7 @@ blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* 
       const float4 g1 = rec4[3 * j + 1];
       const float dx = g0.x - pxf, dy = g0.y - pyf;
       const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
-      const float G = expf(power);
+      const float G = blend_exp<FAST>(power);
       const float alpha = min(0.99f, g1.w * G);
       const bool skip = !inside || contributor >= last_contributor || power > 0.0f || alpha < 1.0f / 255.0f;
       if (__ballot_sync(0xffffffffu, !skip) == 0u) continue;
@@ -217,11 +217,11 @@ size_t backward_pose_scratch_bytes(int P, int W, int H) {
   return ((size_t)(P > 0 ? P : 1) * PoseJac<9>::kFloats * sizeof(float) + 255) / 256 * 256;
 }
 
-template <int NC, bool HD>
+template <int NC, bool HD, bool FAST>
 static int launch_blend_pose_t(const BackwardArgs& a, const float* jac, float* tau_image, cudaStream_t s) {
   const ViewConst& v = a.v;
   prof_begin("blend_backward_pose", s);
-  blend_backward_pose_kernel<NC, HD><<<v.gx * v.gy, 256, 0, s>>>(
+  blend_backward_pose_kernel<NC, HD, FAST><<<v.gx * v.gy, 256, 0, s>>>(
       v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges), ws_ptr<SplatRec>(a.ws, a.L.records), jac, v.bg,
       ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img, a.dL_ddepth_img,
       tau_image, a.dL_dtau_sum);
@@ -231,12 +231,17 @@ static int launch_blend_pose_t(const BackwardArgs& a, const float* jac, float* t
 }
 
 // blend pass only: `jac` already holds the per-Gaussian maps (built by pose_jacobian_kernel or by the fused
-// tracking preprocess); a null dL_ddepth_img means "no depth gradient" and drops the depth column entirely
-int launch_blend_backward_pose(const BackwardArgs& a, const float* jac, bool with_color, cudaStream_t s) {
+// tracking preprocess); a null dL_ddepth_img means "no depth gradient" and drops the depth column entirely;
+// `fast` must match the exp variant the forward pass of this iteration used
+int launch_blend_backward_pose(const BackwardArgs& a, const float* jac, bool with_color, cudaStream_t s, bool fast) {
   float* tau_image = a.sketch_dtau;  // reused field: per-pixel tau image [6,H,W] (may be null)
   const bool hd = a.dL_ddepth_img != nullptr;
-  if (with_color) return hd ? launch_blend_pose_t<9, true>(a, jac, tau_image, s) : launch_blend_pose_t<9, false>(a, jac, tau_image, s);
-  return hd ? launch_blend_pose_t<6, true>(a, jac, tau_image, s) : launch_blend_pose_t<6, false>(a, jac, tau_image, s);
+  if (fast) {
+    if (with_color) return hd ? launch_blend_pose_t<9, true, true>(a, jac, tau_image, s) : launch_blend_pose_t<9, false, true>(a, jac, tau_image, s);
+    return hd ? launch_blend_pose_t<6, true, true>(a, jac, tau_image, s) : launch_blend_pose_t<6, false, true>(a, jac, tau_image, s);
+  }
+  if (with_color) return hd ? launch_blend_pose_t<9, true, false>(a, jac, tau_image, s) : launch_blend_pose_t<9, false, false>(a, jac, tau_image, s);
+  return hd ? launch_blend_pose_t<6, true, false>(a, jac, tau_image, s) : launch_blend_pose_t<6, false, false>(a, jac, tau_image, s);
 }
 
 int launch_backward_pose(const BackwardArgs& a, cudaStream_t s) {

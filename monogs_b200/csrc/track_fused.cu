@@ -126,7 +126,7 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
                               ws, L, s, jac, with_color ? 9 : 6)))
     return rc;
-  MGS_CUDA_TRY(cudaMemsetAsync(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
+  if (!t->fast_math) MGS_CUDA_TRY(cudaMemsetAsync(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
   MGS_CUDA_TRY(cudaMemsetAsync(tau_raw, 0, 6 * sizeof(float), s));
   if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s))) return rc;
 
@@ -138,14 +138,14 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   FusedLoss fl;
   fl.k = &lk;
   fl.grad_scale = (t->loss_mode == MGS_LOSS_TRACK_HUBER) ? 1.f : (use_depth ? t->alpha : 1.f) / (3.f * (float)npix);
-  fl.g_img = g_img; fl.g_depth = use_depth ? g_depth : nullptr; fl.partials = partials;
+  fl.g_img = g_img; fl.g_depth = use_depth ? g_depth : nullptr; fl.partials = partials; fl.fast = t->fast_math != 0;
   if ((rc = launch_blend_forward(v, ws, L, t->out_color, t->out_depth, t->out_opacity, t->n_touched, s, &fl))) return rc;
 
   BackwardArgs a;
   memset(&a, 0, sizeof(a));
   a.v = v; a.P = P; a.grad_mask = MGS_GRAD_TAU; a.ws = ws; a.L = L;
   a.dL_dcolor_img = g_img; a.dL_ddepth_img = use_depth ? g_depth : nullptr; a.dL_dtau_sum = tau_raw;
-  if ((rc = launch_blend_backward_pose(a, jac, with_color, s))) return rc;
+  if ((rc = launch_blend_backward_pose(a, jac, with_color, s, t->fast_math != 0))) return rc;
 
   TrackUpdateK k;
   k.mode = t->loss_mode; k.use_depth = use_depth; k.npix = (int)npix; k.tiles = tiles; k.alpha = t->alpha; k.scale = 1.f;

@@ -22,7 +22,7 @@ KERNELS_PER_ITER_COMPOSED = 14
 
 class PoseTracker:
     def __init__(self, means3D, opacities, shs, scales, rotations, sh_degree, cam, bg, T_w2c, mode=L.LOSS_TRACK_HUBER,
-                 use_depth=False, lr=(1e-3, 3e-3, 2e-2, 2e-2), capacity_headroom=1.3, use_graph=True, fused=True):
+                 use_depth=False, lr=(1e-3, 3e-3, 2e-2, 2e-2), capacity_headroom=1.3, use_graph=True, fused=True, fast_math=True):
         lib = self.lib = L.lib()
         dev = self.dev = means3D.device
         f = dict(device=dev, dtype=torch.float32)
@@ -63,7 +63,7 @@ class PoseTracker:
         self.loss_scratch = torch.empty(lib.mgs_loss_scratch_bytes(self.H, self.W), device=dev, dtype=torch.uint8)
         self.bwd_scratch = torch.empty(max(lib.mgs_raster_backward_pose_scratch_bytes(self.P, self.W, self.H), 256),
                                        device=dev, dtype=torch.uint8)
-        self.fused = fused
+        self.fused, self.fast_math = fused, fast_math
         self.track_scratch = torch.empty(lib.mgs_track_scratch_bytes(self.P, self.W, self.H), device=dev, dtype=torch.uint8)
         self.headroom = capacity_headroom
         self.R_cap, self.ws = 0, None
@@ -105,7 +105,7 @@ class PoseTracker:
         t.P = self.P
         t.means3D, t.opacities, t.shs = self.means3D.data_ptr(), self.opacities.data_ptr(), self.shs.data_ptr()
         t.scales, t.rotations = self.scales.data_ptr(), self.rotations.data_ptr()
-        t.loss_mode, t.use_depth = self.mode, int(self.use_depth)
+        t.loss_mode, t.use_depth, t.fast_math = self.mode, int(self.use_depth), int(self.fast_math)
         t.rgb_boundary_threshold, t.alpha, t.huber_delta = 0.01, 0.95, 0.01
         t.gt_image = self.gt_image.data_ptr()
         t.gt_depth = self.gt_depth.data_ptr() if self.gt_depth is not None else None
