@@ -144,12 +144,11 @@ def algorithmic_bytes(P, P_vis, R, R_cap, W, H, M=1):
     """Per-launch algorithmic bytes of every kernel of the fused tracking iteration."""
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     return {
-        "preprocess": 12 * P + 4 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8 + 16 + 16) + 12 * P + P_vis * 144,
-        "cub_sort_depth": P * (8 + 16 * 4),
-        "cub_scan": 12 * P,
-        "emit_keys": P * 4 + P_vis * 16 + R_cap * 8,
-        "cub_sort": R_cap * (8 + 16 * 2),
-        "ranges_records": R * (8 + 44 + 48) + 8 * tiles,
+        "preprocess": 12 * P + 8 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8 + 16 + 16) + P_vis * 144,
+        "tile_scan": 16 * tiles,
+        "emit": 4 * P + P_vis * 12 + 8 * R,
+        "tile_sort_records": R * (8 + 44 + 48) + 8 * tiles,
+        "tile_sort_records_large": 8 * tiles,
         "blend_forward": R * 48 + (28 + 12 + 12) * W * H + 40 * tiles,
         "blend_backward_pose": R * (48 + 144) + 20 * W * H + 8 * tiles,
         "track_update": 32 * tiles,

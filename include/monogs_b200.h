@@ -67,7 +67,7 @@ int mgs_profile_report(char* buf, size_t buf_bytes);
 size_t mgs_raster_workspace_bytes(int32_t P, int32_t W, int32_t H, int64_t R_cap);
 
 /* Stage 1 (forward.cu:157-258 + the InclusiveSum at rasterizer_impl.cu:280): per-Gaussian projection,
- * conic, radius, tile rect, SH->RGB and the inclusive scan of tiles touched.  Writes radii[P] and leaves
+ * conic, radius, tile rect, SH->RGB, the per-tile instance counts and their scan (= num_rendered).  Writes radii[P] and leaves
  * num_rendered in the workspace; if num_rendered_out is non-null it also receives the value through an
  * async copy on `stream` (device or pinned host pointer).  Optional inputs are null exactly where the
  * reference receives empty tensors (__init__.py:433-447). */
@@ -78,10 +78,11 @@ int mgs_raster_preprocess(const mgs_view* view, int32_t P,
                           int32_t* radii, void* workspace, size_t workspace_bytes,
                           int32_t* num_rendered_out, void* stream);
 
-/* Stage 2 (rasterizer_impl.cu:286-341): key generation, 64-bit (tile|depth) stable sort, tile ranges,
- * packed per-instance records and the alpha blend.  R_cap is the capacity the workspace was sized for;
- * if the device-side num_rendered exceeds it the overflow flag in the workspace is set and only the first
- * R_cap instances (in Gaussian order) are rendered.  Never synchronises.  out_* and n_touched are fully
+/* Stage 2 (rasterizer_impl.cu:286-341): binning — the reference's 64-bit (tile|depth) stable sort, done as a counting
+ * sort on the tile half (tile ranges fall out of the scan) plus a per-tile sort of (depth bits, Gaussian id), which
+ * yields the identical order — packed per-instance records and the alpha blend.  R_cap is the capacity the workspace
+ * was sized for; if the device-side num_rendered exceeds it the overflow flag in the workspace is set, instances
+ * beyond slot R_cap are dropped and the images are incomplete (re-run with a larger capacity).  Never synchronises.  out_* and n_touched are fully
  * written (n_touched is zeroed first), so the caller need not pre-fill them. */
 int mgs_raster_render(const mgs_view* view, int32_t P, const float* colors_precomp, const int32_t* radii,
                       void* workspace, size_t workspace_bytes, int64_t R_cap,

@@ -75,9 +75,8 @@ int mgs_raster_preprocess(const mgs_view* view, int32_t P, const float* means3D,
   if ((rc = launch_preprocess(v, P, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
                               workspace, L, s)))
     return rc;
-  const uint32_t* last = ws_ptr<uint32_t>(workspace, L.point_offsets) + (P - 1);
-  MGS_CUDA_TRY(cudaMemcpyAsync(&hdr->num_rendered, last, sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
-  if (num_rendered_out) MGS_CUDA_TRY(cudaMemcpyAsync(num_rendered_out, last, sizeof(uint32_t), cudaMemcpyDefault, s));
+  if ((rc = launch_tile_scan(v, workspace, L, 0xFFFFFFFFLL, s))) return rc;   // header.num_rendered = sum of the tile counts
+  if (num_rendered_out) MGS_CUDA_TRY(cudaMemcpyAsync(num_rendered_out, &hdr->num_rendered, sizeof(uint32_t), cudaMemcpyDefault, s));
   return MGS_OK;
 }
 
@@ -122,9 +121,8 @@ int mgs_debug_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, size_t* out
   WsLayout L;
   int rc = ws_layout(P, W, H, R_cap, &L);
   if (rc) return rc;
-  const size_t v[17] = {L.header, L.depths, L.means2D, L.conic_opacity, L.rgb4, L.tiles_touched, L.point_offsets,
-                        L.final_T, L.n_contrib, L.ranges, L.records, L.keys_in, L.keys_out, L.vals_in, L.vals_out,
-                        L.scan_tmp, L.sort_tmp};
+  const size_t v[17] = {L.header, L.depths, L.means2D, L.conic_opacity, L.rgb4, L.tiles_touched, L.tile_ctr,
+                        L.final_T, L.n_contrib, L.ranges, L.records, L.tile_ctr, L.list, L.total, 0, 0, 0};
   for (int i = 0; i < 17; i++) out[i] = v[i];
   return MGS_OK;
 }

@@ -12,6 +12,9 @@ namespace mgs {
 constexpr int TILE_X = 16;   // config.h:16-17 — the tile size is part of the parity contract (keys, ranges)
 constexpr int TILE_Y = 16;
 constexpr int TILE_PIX = TILE_X * TILE_Y;
+// per-tile atomic counters sit one per 128-B line: L2 serialises atomics per line, so densely packed counters
+// (38 lines for 1200 tiles) cap the whole chip at a few atomics per clock
+constexpr int TILE_CTR_STRIDE = 32;
 
 // ---- error plumbing -------------------------------------------------------------------------
 void set_error(const char* fmt, ...);
@@ -52,14 +55,13 @@ static_assert(sizeof(WsHeader) == 256, "header is one 256-B slot");
 // Host-side view of the workspace.  Everything backward needs lives at offsets that do not depend on
 // R_cap (header, per-Gaussian state, image state, then the records), so backward never needs R_cap.
 struct WsLayout {
-  size_t header, depths, means2D, conic_opacity, rgb4, tiles_touched, point_offsets;
+  size_t header, depths, means2D, conic_opacity, rgb4, tiles_touched;
+  size_t tile_ctr;                                // u32[tiles][TILE_CTR_STRIDE]: [0] instances per tile, [1] scatter cursor
   size_t final_T, n_contrib, ranges, records;
-  size_t dkey_in, dkey_out, perm_in, perm;                    // depth sort of the Gaussians (u32 each, per P)
-  size_t keys_in, keys_out, vals_in, vals_out, scan_tmp, sort_tmp, dsort_tmp;   // tile keys are u32 now
-  size_t scan_tmp_bytes, sort_tmp_bytes, dsort_tmp_bytes;
+  size_t list;                                    // u64[R_cap]: (depth bits << 32 | Gaussian id), grouped by tile
   size_t total;
 };
-// needs a CUDA device only for the two CUB size queries
+// pure host arithmetic (no CUDA call)
 int ws_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, WsLayout* out);
 
 template <typename T> __host__ __device__ inline T* ws_ptr(void* base, size_t off) {

@@ -10,6 +10,7 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
                       float* jac = nullptr, int jac_ncol = 0);
+int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s);
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
                    const WsLayout& L, int64_t R_cap, cudaStream_t s);
 struct LossK;

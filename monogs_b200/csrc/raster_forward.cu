@@ -3,9 +3,8 @@
 // FORWARD::preprocess / FORWARD::render (forward.cu:157-258, 263-392).
 #include "launchers.h"
 #include "pose_jac.cuh"
-#include <cub/device/device_scan.cuh>
-#include <cub/device/device_radix_sort.cuh>
-#include <cub/iterator/transform_input_iterator.cuh>
+#include <cub/block/block_scan.cuh>
+#include <cub/block/block_merge_sort.cuh>
 #include <cstdarg>
 #include <cstdio>
 #include <map>
@@ -60,28 +59,11 @@ int prof_report(char* buf, size_t n) {
 
 static inline size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
-// tiles_touched read through the depth-order permutation (input iterator of the scan)
-struct PermLoad {
-  const uint32_t* tiles_touched;
-  __host__ __device__ __forceinline__ uint32_t operator()(const uint32_t& g) const { return tiles_touched[g]; }
-};
-using PermIter = cub::TransformInputIterator<uint32_t, PermLoad, const uint32_t*>;
-
 int ws_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, WsLayout* L) {
   if (P < 0 || W <= 0 || H <= 0 || R_cap < 0) { set_error("ws_layout: bad sizes"); return MGS_EINVAL; }
   const size_t Pp = (size_t)(P > 0 ? P : 1), Rp = (size_t)(R_cap > 0 ? R_cap : 1);
   const size_t npix = (size_t)W * H;
   const size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
-  size_t scan_b = 0, sort_b = 0, dsort_b = 0;
-  cudaError_t e = cub::DeviceScan::InclusiveSum(nullptr, scan_b, PermIter(nullptr, PermLoad{nullptr}), (uint32_t*)nullptr, (int)Pp);
-  if (e == cudaSuccess)
-    e = cub::DeviceRadixSort::SortPairs(nullptr, sort_b, (uint32_t*)nullptr, (uint32_t*)nullptr,
-                                        (uint32_t*)nullptr, (uint32_t*)nullptr, (int)Rp);
-  if (e == cudaSuccess)
-    e = cub::DeviceRadixSort::SortPairs(nullptr, dsort_b, (uint32_t*)nullptr, (uint32_t*)nullptr,
-                                        (uint32_t*)nullptr, (uint32_t*)nullptr, (int)Pp);
-  if (e != cudaSuccess) { set_error("CUB size query failed: %s", cudaGetErrorString(e)); return MGS_ECUDA; }
-  L->scan_tmp_bytes = scan_b; L->sort_tmp_bytes = sort_b; L->dsort_tmp_bytes = dsort_b;
   size_t off = 0;
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes); return o; };
   // ---- R_cap-independent part (stage 1 and backward use only this) ----
@@ -91,23 +73,13 @@ int ws_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, WsLayout* L) {
   L->conic_opacity = take(Pp * 16);
   L->rgb4 = take(Pp * 16);
   L->tiles_touched = take(Pp * 4);
-  L->point_offsets = take(Pp * 4);
-  L->dkey_in = take(Pp * 4);
-  L->dkey_out = take(Pp * 4);
-  L->perm_in = take(Pp * 4);
-  L->perm = take(Pp * 4);
-  L->scan_tmp = take(scan_b);
-  L->dsort_tmp = take(dsort_b);
+  L->tile_ctr = take(tiles * TILE_CTR_STRIDE * 4);
   L->final_T = take(npix * 4);
   L->n_contrib = take(npix * 4);
   L->ranges = take(tiles * 8);
   // ---- per-instance part ----
   L->records = take(Rp * sizeof(SplatRec));
-  L->keys_in = take(Rp * 4);
-  L->keys_out = take(Rp * 4);
-  L->vals_in = take(Rp * 4);
-  L->vals_out = take(Rp * 4);
-  L->sort_tmp = take(sort_b);
+  L->list = take(Rp * 8);
   L->total = off;
   return MGS_OK;
 }
@@ -197,6 +169,50 @@ __device__ __forceinline__ float3 sh_to_rgb(int idx, int deg, int M, const float
   return make_float3(c[0], c[1], c[2]);
 }
 
+// Visit every tile of a splat's rect, four tiles per callback so that the callback can keep four atomics in flight
+// (a chain of dependent atomics is latency-bound: ~0.5 us each).  Rects of up to 32 tiles are walked by the owning
+// lane; larger ones are broadcast (with the owner's 64-bit payload) and walked by the whole warp, lane-strided, so one
+// screen-filling splat does not serialise a warp.  Must be reached by all 32 lanes.
+// fn(const uint32_t (&tile)[4], int count, payload of the owning Gaussian).
+template <typename F>
+__device__ __forceinline__ void for_each_tile(const uint2 rmin, const uint2 rmax, const int gx,
+                                              const unsigned long long payload, F&& fn) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t w = rmax.x - rmin.x, area = w * (rmax.y - rmin.y);
+  const bool big = area > 32u;
+  if (area != 0u && !big) {
+    uint32_t x = rmin.x, y = rmin.y;
+    for (uint32_t t = 0; t < area; t += 4u) {
+      uint32_t tl[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        tl[u] = y * gx + x;
+        if (++x == rmax.x) { x = rmin.x; y++; }
+      }
+      fn(tl, (int)min(4u, area - t), payload);
+    }
+  }
+  unsigned m = __ballot_sync(0xffffffffu, big);
+  while (m) {
+    const int src = __ffs(m) - 1;
+    m &= m - 1;
+    const uint32_t x0 = __shfl_sync(0xffffffffu, rmin.x, src), y0 = __shfl_sync(0xffffffffu, rmin.y, src);
+    const uint32_t ww = __shfl_sync(0xffffffffu, w, src), aa = __shfl_sync(0xffffffffu, area, src);
+    const unsigned long long pl = __shfl_sync(0xffffffffu, payload, src);
+    for (uint32_t t0 = 0; t0 < aa; t0 += 128u) {
+      uint32_t tl[4];
+      int cnt = 0;
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const uint32_t t = t0 + 32u * u + lane;
+        tl[u] = (y0 + t / ww) * gx + x0 + t % ww;
+        cnt += t < aa ? 1 : 0;           // valid slots are a prefix: t grows with u
+      }
+      fn(tl, cnt, pl);
+    }
+  }
+}
+
 template <int JAC_NCOL>   // 0: plain; 6 / 9: also build the pose Jacobian of visible Gaussians (tracking path)
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const ViewConst v, const int P,
@@ -206,13 +222,13 @@ preprocess_kernel(const ViewConst v, const int P,
                   const float* __restrict__ cov3D_precomp,
                   int32_t* __restrict__ radii, float* __restrict__ depths, float2* __restrict__ means2D,
                   float4* __restrict__ conic_opacity, float4* __restrict__ rgb4,
-                  uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ dkey, uint32_t* __restrict__ iota,
+                  uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ tile_ctr,
                   float* __restrict__ jac) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= P) return;
   int my_radius_i = 0;
-  uint32_t touched = 0, depth_key = 0xFFFFFFFFu;   // culled Gaussians sort to the end and emit nothing
-  do {
+  uint32_t touched = 0;
+  uint2 rmin = {0u, 0u}, rmax = {0u, 0u};
+  if (idx < P) do {
     const float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
     // near cull only (auxiliary.h:139-164)
     const float4 ph = xform4x4(p, v.proj);
@@ -237,9 +253,9 @@ preprocess_kernel(const ViewConst v, const int P,
     const float lambda2 = mid - sqrtf(max(0.1f, mid * mid - det));
     const float my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
     const float2 pix = {ndc_to_pix(pproj.x, v.W), ndc_to_pix(pproj.y, v.H)};
-    uint2 rmin, rmax;
-    tile_rect(pix, (int)my_radius, v.gx, v.gy, rmin, rmax);
-    const uint32_t area = (rmax.x - rmin.x) * (rmax.y - rmin.y);
+    uint2 r0, r1;
+    tile_rect(pix, (int)my_radius, v.gx, v.gy, r0, r1);
+    const uint32_t area = (r1.x - r0.x) * (r1.y - r0.y);
     if (area == 0) break;
     uint32_t cm = 0;
     if (colors_precomp == nullptr) {
@@ -252,94 +268,189 @@ preprocess_kernel(const ViewConst v, const int P,
     conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
     my_radius_i = (int)my_radius;
     touched = area;
-    depth_key = __float_as_uint(pview.z);   // > 0.2, so the bit pattern orders like the float (rasterizer_impl.cu:99-101)
+    rmin = r0; rmax = r1;
   } while (0);
-  radii[idx] = my_radius_i;
-  tiles_touched[idx] = touched;
-  dkey[idx] = depth_key;
-  iota[idx] = (uint32_t)idx;
+  if (idx < P) {
+    radii[idx] = my_radius_i;
+    tiles_touched[idx] = touched;
+  }
+  // instances per tile (the histogram of the counting sort that replaces the reference's global key sort)
+  for_each_tile(rmin, rmax, v.gx, 0ull, [&](const uint32_t (&tile)[4], int cnt, unsigned long long) {
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (u < cnt) atomicAdd(&tile_ctr[tile[u] * TILE_CTR_STRIDE], 1u);
+  });
 }
 
 // ------------------------------------------------------------------------------------------------
-// Binning.  bin_header: device-side instance count (no host sync, rasterizer_impl.cu:284 removed).
+// Binning.  The reference sorts R 64-bit (tile | depth) keys globally (rasterizer_impl.cu:70-111, 306-311).  Tile ids
+// are a small dense range, so the tile half is a COUNTING sort: per-tile counts (above) -> exclusive scan (tile
+// ranges, rasterizer_impl.cu:116-138, fall out of it directly) -> scatter of (depth bits << 32 | Gaussian id) into the
+// tile's segment -> per-tile sort of that 64-bit word in shared memory.  The reference's radix sort is stable and its
+// instances are emitted in Gaussian-index order, so ties on (tile, depth) are ordered by index there too: the result
+// is the same permutation, bit for bit.
 // ------------------------------------------------------------------------------------------------
-__global__ void bin_header_kernel(const uint32_t* __restrict__ point_offsets, int P, uint32_t R_cap, WsHeader* hdr) {
-  const uint32_t n = P > 0 ? point_offsets[P - 1] : 0u;
-  hdr->num_rendered = n;
-  hdr->overflow = n > R_cap ? 1u : 0u;
-  hdr->r_used = n > R_cap ? R_cap : n;
+constexpr int SCAN_THREADS = 1024;
+__global__ void __launch_bounds__(SCAN_THREADS)
+tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_t R_cap,
+                 uint2* __restrict__ ranges, WsHeader* __restrict__ hdr) {
+  using Scan = cub::BlockScan<uint32_t, SCAN_THREADS>;
+  __shared__ typename Scan::TempStorage tmp;
+  uint32_t carry = 0;
+  for (int base = 0; base < tiles; base += SCAN_THREADS) {
+    const int t = base + threadIdx.x;
+    const uint32_t c = t < tiles ? tile_ctr[(size_t)t * TILE_CTR_STRIDE] : 0u;
+    uint32_t excl, total;
+    Scan(tmp).ExclusiveSum(c, excl, total);
+    if (t < tiles) {
+      const uint32_t start = carry + excl;
+      ranges[t] = (c == 0u) ? make_uint2(0u, 0u)                                  // untouched tiles keep {0,0}
+                            : make_uint2(min(start, R_cap), min(start + c, R_cap));
+      tile_ctr[(size_t)t * TILE_CTR_STRIDE + 1] = start;
+    }
+    carry += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    hdr->num_rendered = carry;
+    hdr->overflow = carry > R_cap ? 1u : 0u;
+    hdr->r_used = carry > R_cap ? R_cap : carry;
+  }
 }
 
-// K3: emit tile keys + Gaussian ids (rasterizer_impl.cu:70-111).  The reference sorts 64-bit (tile|depth) keys in
-// one go; here the Gaussians were first stably sorted by depth bits (P items, 32-bit keys), instances are emitted in
-// that order, and only the tile bits remain to be sorted (stable LSD radix => identical final permutation, ties keep
-// ascending Gaussian index, at a third of the sort passes on 8-byte instead of 12-byte pairs).  Slots
-// [r_used, R_cap) get a sentinel tile id that is never a real tile so the sort length stays a host constant.
+// scatter: one (depth bits << 32 | id) word per (Gaussian, tile) into the tile's segment, slot taken atomically
 __global__ void __launch_bounds__(256)
-emit_keys_kernel(const int P, const uint32_t R_cap, const int gx, const int gy, const uint32_t sentinel,
-                 const uint32_t* __restrict__ perm, const float2* __restrict__ means2D,
-                 const uint32_t* __restrict__ offsets, const int32_t* __restrict__ radii,
-                 const WsHeader* __restrict__ hdr,
-                 uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < (uint32_t)P) {
-    const uint32_t g = perm[i];
-    const int rad = radii[g];
+emit_kernel(const int P, const uint32_t R_cap, const int gx, const int gy,
+            const float2* __restrict__ means2D, const float* __restrict__ depths, const int32_t* __restrict__ radii,
+            uint32_t* __restrict__ tile_ctr, unsigned long long* __restrict__ list) {
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  uint2 rmin = {0u, 0u}, rmax = {0u, 0u};
+  unsigned long long word = 0ull;
+  if (idx < P) {
+    const int rad = radii[idx];
     if (rad > 0) {
-      uint32_t off = (i == 0) ? 0u : offsets[i - 1];
-      uint2 rmin, rmax;
-      tile_rect(means2D[g], rad, gx, gy, rmin, rmax);
-      for (uint32_t y = rmin.y; y < rmax.y; y++)
-        for (uint32_t x = rmin.x; x < rmax.x; x++) {
-          if (off < R_cap) { keys[off] = y * gx + x; vals[off] = g; }
-          off++;
-        }
+      tile_rect(means2D[idx], rad, gx, gy, rmin, rmax);
+      // view depth > 0.2, so its bit pattern orders like the float (rasterizer_impl.cu:99-101)
+      word = ((unsigned long long)__float_as_uint(depths[idx]) << 32) | (uint32_t)idx;
     }
   }
-  if (i < R_cap && i >= hdr->r_used) { keys[i] = sentinel; vals[i] = 0xFFFFFFFFu; }
+  for_each_tile(rmin, rmax, gx, word, [&](const uint32_t (&tile)[4], int cnt, unsigned long long w) {
+    uint32_t slot[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (u < cnt) slot[u] = atomicAdd(&tile_ctr[tile[u] * TILE_CTR_STRIDE + 1], 1u);
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+      if (u < cnt && slot[u] < R_cap) list[slot[u]] = w;
+  });
 }
 
-// K5 + record packing: tile [start,end) ranges (rasterizer_impl.cu:116-138) and, in the same pass over the
-// sorted list, the 48-B records the blend kernels stream.
-__global__ void __launch_bounds__(256)
-ranges_records_kernel(const uint32_t R_cap, const WsHeader* __restrict__ hdr,
-                      const uint32_t* __restrict__ keys, const uint32_t* __restrict__ ids,
-                      const float2* __restrict__ means2D, const float* __restrict__ depths,
-                      const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
-                      const float* __restrict__ colors_precomp,
-                      uint2* __restrict__ ranges, SplatRec* __restrict__ recs) {
-  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-  const uint32_t L = hdr->r_used;
-  if (i >= L) return;
-  const uint32_t tile = keys[i];
-  if (i == 0) ranges[tile].x = 0;
-  else {
-    const uint32_t prev = keys[i - 1];
-    if (tile != prev) { ranges[prev].y = i; ranges[tile].x = i; }
-  }
-  if (i == L - 1) ranges[tile].y = L;
-  const uint32_t id = ids[i];
+// Per-tile sort of the 64-bit words + record packing.  Lists of up to SORT_CAP words are merge-sorted from registers
+// (cub::BlockMergeSort, 2/4/8/16 words per thread by list length; every word is unique, slots >= n are padded with
+// ~0 which no real word equals).  Longer lists are sorted in place in global memory (L2) with a bitonic network in
+// its "mirror" form: every compare-exchange puts the smaller word at the lower index, so slots >= n act as +inf
+// without being stored and n need not be a power of two.
+constexpr int SORT_CAP = 4096;
+struct U64Less { __device__ __forceinline__ bool operator()(unsigned long long a, unsigned long long b) const { return a < b; } };
+
+__device__ __forceinline__ void write_record(const unsigned long long w, SplatRec* __restrict__ dst,
+                                             const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
+                                             const float4* __restrict__ rgb4, const float* __restrict__ colors_precomp) {
+  const uint32_t id = (uint32_t)w;
   const float2 xy = means2D[id];
   const float4 co = conic_opacity[id];
   float4 c;
   if (colors_precomp != nullptr) c = make_float4(colors_precomp[3 * id], colors_precomp[3 * id + 1], colors_precomp[3 * id + 2], 0.f);
   else c = rgb4[id];
-  float4* out = reinterpret_cast<float4*>(recs + i);
-  out[0] = make_float4(xy.x, xy.y, depths[id], __uint_as_float(id));
+  float4* out = reinterpret_cast<float4*>(dst);
+  out[0] = make_float4(xy.x, xy.y, __uint_as_float((uint32_t)(w >> 32)), __uint_as_float(id));
   out[1] = co;
   out[2] = make_float4(c.x, c.y, c.z, __uint_as_float(splat_extent(co.x, co.y, co.z, co.w)));
 }
 
+template <int IPT, typename Temp>
+__device__ __noinline__ void sort_tile_regs(Temp& temp, const unsigned long long* __restrict__ seg, const int n,
+                                            SplatRec* __restrict__ dst, const float2* __restrict__ means2D,
+                                            const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
+                                            const float* __restrict__ colors_precomp) {
+  using Sort = cub::BlockMergeSort<unsigned long long, 256, IPT>;
+  unsigned long long k[IPT];
+#pragma unroll
+  for (int i = 0; i < IPT; i++) {
+    const int e = threadIdx.x * IPT + i;
+    k[i] = e < n ? seg[e] : ~0ull;
+  }
+  Sort(reinterpret_cast<typename Sort::TempStorage&>(temp)).Sort(k, U64Less());
+#pragma unroll
+  for (int i = 0; i < IPT; i++) {
+    const int e = threadIdx.x * IPT + i;
+    if (e < n) write_record(k[i], dst + e, means2D, conic_opacity, rgb4, colors_precomp);
+  }
+}
+
+// Two launches cover the tiles: LARGE = false takes lists of up to 1024 words (few registers, 8 KB of shared memory,
+// full occupancy — the common case), LARGE = true the rest; a CTA whose tile belongs to the other launch exits at once.
+template <bool LARGE>
+__global__ void __launch_bounds__(256)
+tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ list,
+                         const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
+                         const float4* __restrict__ rgb4, const float* __restrict__ colors_precomp,
+                         SplatRec* __restrict__ recs) {
+  using Temp = typename cub::BlockMergeSort<unsigned long long, 256, LARGE ? 16 : 4>::TempStorage;
+  __shared__ Temp temp;
+  const uint2 range = ranges[blockIdx.x];
+  const int n = (int)(range.y - range.x);
+  if (n == 0 || (n > 1024) != LARGE) return;
+  unsigned long long* seg = list + range.x;
+  SplatRec* dst = recs + range.x;
+  if (!LARGE) {
+    if (n <= 512) sort_tile_regs<2>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+    else sort_tile_regs<4>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+    return;
+  }
+  if (n <= SORT_CAP) {
+    if (n <= 2048) sort_tile_regs<8>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+    else sort_tile_regs<16>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+    return;
+  }
+  int N = 1;
+  while (N < n) N <<= 1;
+  for (int k = 2; k <= N; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      const bool mirror = (j == (k >> 1));
+      for (int q = threadIdx.x; q < (N >> 1); q += blockDim.x) {
+        const int lo = q & (j - 1), blk = (q - lo) << 1;   // block of 2j slots, offset lo inside its lower half
+        const int i = blk + lo;
+        const int p = mirror ? blk + 2 * j - 1 - lo : i + j;
+        if (p < n) {
+          const unsigned long long a = __ldcg(seg + i), b = __ldcg(seg + p);
+          if (a > b) { __stcg(seg + i, b); __stcg(seg + p, a); }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  for (int e = threadIdx.x; e < n; e += blockDim.x)
+    write_record(__ldcg(seg + e), dst + e, means2D, conic_opacity, rgb4, colors_precomp);
+}
+
+int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s) {
+  MGS_PROF("tile_scan", s, tile_scan_kernel<<<1, SCAN_THREADS, 0, s>>>(
+      ws_ptr<uint32_t>(ws, L.tile_ctr), v.gx * v.gy, (uint32_t)R_cap, ws_ptr<uint2>(ws, L.ranges),
+      ws_ptr<WsHeader>(ws, L.header)));
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
+}
 
 int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
                       float* jac, int jac_ncol) {
   if (P == 0) return MGS_OK;
+  MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(ws, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
 #define MGS_PRE_ARGS v, P, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,           \
       ws_ptr<float>(ws, L.depths), ws_ptr<float2>(ws, L.means2D), ws_ptr<float4>(ws, L.conic_opacity),               \
-      ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched), ws_ptr<uint32_t>(ws, L.dkey_in),            \
-      ws_ptr<uint32_t>(ws, L.perm_in), jac
+      ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched), ws_ptr<uint32_t>(ws, L.tile_ctr), jac
   prof_begin("preprocess", s);
   if (jac == nullptr) preprocess_kernel<0><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
   else if (jac_ncol == 9) preprocess_kernel<9><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
@@ -347,50 +458,26 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
   prof_end(s);
 #undef MGS_PRE_ARGS
   MGS_LAUNCH_CHECK();
-  // stable sort of the Gaussians by depth bits -> perm (depth order, ties by index)
-  size_t dtmp = L.dsort_tmp_bytes;
-  prof_begin("cub_sort_depth", s);
-  MGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(ws_ptr<void>(ws, L.dsort_tmp), dtmp, ws_ptr<uint32_t>(ws, L.dkey_in),
-                                               ws_ptr<uint32_t>(ws, L.dkey_out), ws_ptr<uint32_t>(ws, L.perm_in),
-                                               ws_ptr<uint32_t>(ws, L.perm), P, 0, 32, s));
-  prof_end(s);
-  // inclusive scan of tiles_touched in depth order
-  size_t tmp = L.scan_tmp_bytes;
-  prof_begin("cub_scan", s);
-  MGS_CUDA_TRY(cub::DeviceScan::InclusiveSum(ws_ptr<void>(ws, L.scan_tmp), tmp,
-                                             PermIter(ws_ptr<uint32_t>(ws, L.perm), PermLoad{ws_ptr<uint32_t>(ws, L.tiles_touched)}),
-                                             ws_ptr<uint32_t>(ws, L.point_offsets), P, s));
-  prof_end(s);
   return MGS_OK;
 }
 
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
                    const WsLayout& L, int64_t R_cap, cudaStream_t s) {
-  WsHeader* hdr = ws_ptr<WsHeader>(ws, L.header);
-  const uint32_t tiles = (uint32_t)v.gx * v.gy;
-  bin_header_kernel<<<1, 1, 0, s>>>(ws_ptr<uint32_t>(ws, L.point_offsets), P, (uint32_t)R_cap, hdr);
-  MGS_LAUNCH_CHECK();
-  MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(ws, L.ranges), 0, (size_t)tiles * sizeof(uint2), s));
+  const int tiles = v.gx * v.gy;
+  int rc = launch_tile_scan(v, ws, L, R_cap, s);   // ranges (clipped to R_cap), scatter cursors, header
+  if (rc) return rc;
   if (R_cap == 0 || P == 0) return MGS_OK;
-  const uint32_t bit = tile_id_bits(tiles);
-  const uint32_t sentinel = (1u << bit) - 1u;
-  const int64_t n_thr = P > R_cap ? P : R_cap;
-  MGS_PROF("emit_keys", s, emit_keys_kernel<<<(unsigned)((n_thr + 255) / 256), 256, 0, s>>>(
-      P, (uint32_t)R_cap, v.gx, v.gy, sentinel, ws_ptr<uint32_t>(ws, L.perm), ws_ptr<float2>(ws, L.means2D),
-      ws_ptr<uint32_t>(ws, L.point_offsets), radii, hdr, ws_ptr<uint32_t>(ws, L.keys_in),
-      ws_ptr<uint32_t>(ws, L.vals_in)));
+  MGS_PROF("emit", s, emit_kernel<<<(P + 255) / 256, 256, 0, s>>>(
+      P, (uint32_t)R_cap, v.gx, v.gy, ws_ptr<float2>(ws, L.means2D), ws_ptr<float>(ws, L.depths), radii,
+      ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<unsigned long long>(ws, L.list)));
   MGS_LAUNCH_CHECK();
-  size_t tmp = L.sort_tmp_bytes;
-  prof_begin("cub_sort", s);
-  MGS_CUDA_TRY(cub::DeviceRadixSort::SortPairs(ws_ptr<void>(ws, L.sort_tmp), tmp, ws_ptr<uint32_t>(ws, L.keys_in),
-                                               ws_ptr<uint32_t>(ws, L.keys_out), ws_ptr<uint32_t>(ws, L.vals_in),
-                                               ws_ptr<uint32_t>(ws, L.vals_out), (int)R_cap, 0, (int)bit, s));
-  prof_end(s);
-  MGS_PROF("ranges_records", s, ranges_records_kernel<<<(unsigned)((R_cap + 255) / 256), 256, 0, s>>>(
-      (uint32_t)R_cap, hdr, ws_ptr<uint32_t>(ws, L.keys_out), ws_ptr<uint32_t>(ws, L.vals_out),
-      ws_ptr<float2>(ws, L.means2D), ws_ptr<float>(ws, L.depths), ws_ptr<float4>(ws, L.conic_opacity),
-      ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records)));
+#define MGS_SORT_ARGS ws_ptr<uint2>(ws, L.ranges), ws_ptr<unsigned long long>(ws, L.list), ws_ptr<float2>(ws, L.means2D), \
+      ws_ptr<float4>(ws, L.conic_opacity), ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<SplatRec>(ws, L.records)
+  MGS_PROF("tile_sort_records", s, tile_sort_records_kernel<false><<<tiles, 256, 0, s>>>(MGS_SORT_ARGS));
   MGS_LAUNCH_CHECK();
+  MGS_PROF("tile_sort_records_large", s, tile_sort_records_kernel<true><<<tiles, 256, 0, s>>>(MGS_SORT_ARGS));
+  MGS_LAUNCH_CHECK();
+#undef MGS_SORT_ARGS
   return MGS_OK;
 }
 

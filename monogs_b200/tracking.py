@@ -15,8 +15,8 @@ import torch
 from . import _lib as L
 from .rasterizer import make_view, GaussianRasterizationSettings, _stream
 
-KERNELS_PER_ITER = 8    # own kernels per fused iteration: preprocess(+jac), header, emit_keys, ranges_records,
-                        # blend_forward(+loss), blend_backward_pose, track_update (+1 spare: CUB launches not counted)
+KERNELS_PER_ITER = 8    # own kernels per fused iteration: preprocess(+jac, +tile counts), tile_scan, emit,
+                        # tile_sort_records x2 (short / long lists), blend_forward(+loss), blend_backward_pose, track_update
 KERNELS_PER_ITER_COMPOSED = 14
 
 

@@ -39,15 +39,19 @@ def _ws_views(st, P, cam):
     lib.mgs_debug_layout.restype = C.c_int
     lib.mgs_debug_layout.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.POINTER(C.c_size_t)]
     assert lib.mgs_debug_layout(P, cam.W, cam.H, st.num_rendered, off) == 0
-    names = ["header", "depths", "means2D", "conic_opacity", "rgb4", "tiles_touched", "point_offsets", "final_T",
-             "n_contrib", "ranges", "records", "keys_in", "keys_out", "vals_in", "vals_out", "scan_tmp", "sort_tmp"]
+    names = ["header", "depths", "means2D", "conic_opacity", "rgb4", "tiles_touched", "tile_count", "final_T",
+             "n_contrib", "ranges", "records", "tile_cursor", "list", "total"]
     o = dict(zip(names, list(off)))
     ws, R = st.workspace, st.num_rendered
     tiles = ((cam.W + 15) // 16) * ((cam.H + 15) // 16)
-    plist = ws[o["vals_out"]:o["vals_out"] + 4 * R].view(torch.int32)
-    tile_keys = ws[o["keys_out"]:o["keys_out"] + 4 * R].view(torch.int32).long()
-    depth_bits = ws[o["depths"]:o["depths"] + 4 * P].view(torch.int32)[plist.long()].long() & 0xFFFFFFFF
-    # the library sorts depth and tile bits in two stable passes; the reference's 64-bit key is their concatenation
+    # what the blend kernels consume: the packed 48-B records (x y depth id | conic opacity | rgb extent), tile by tile
+    recs = ws[o["records"]:o["records"] + 48 * R].view(torch.int32).view(R, 12)
+    plist = recs[:, 3].contiguous()
+    depth_bits = recs[:, 2].long() & 0xFFFFFFFF
+    rng = ws[o["ranges"]:o["ranges"] + 8 * tiles].view(torch.int32).view(tiles, 2).long()
+    tile_keys = torch.repeat_interleave(torch.arange(tiles, device=ws.device), rng[:, 1] - rng[:, 0])
+    assert tile_keys.numel() == R
+    # the library counting-sorts the tile half and sorts (depth, id) per tile; the reference's 64-bit key is the pair
     return dict(keys=(tile_keys << 32) | depth_bits, plist=plist,
                 ranges=ws[o["ranges"]:o["ranges"] + 8 * tiles].view(torch.int32).view(tiles, 2),
                 n_contrib=ws[o["n_contrib"]:o["n_contrib"] + 4 * cam.W * cam.H].view(torch.int32).view(cam.H, cam.W),
@@ -108,7 +112,7 @@ def _setup(name, seed=0):
     return sc, cam, bg, gc, gd
 
 
-@pytest.mark.parametrize("name", ["tiny", "ragged", "sh3", "dense"])
+@pytest.mark.parametrize("name", ["tiny", "ragged", "sh3", "dense", "packed8", "packed16", "crowded"])
 def test_product_vs_reference_small(name):
     sc, cam, bg, gc, gd = _setup(name)
     scd, camd = U.to_dev(sc), U.to_dev(cam)
