@@ -149,6 +149,7 @@ def algorithmic_bytes(P, P_vis, R, R_cap, W, H, M=1):
         "emit": 4 * P + P_vis * 12 + 8 * R,
         "tile_sort_records": R * (8 + 44 + 48) + 8 * tiles,
         "tile_sort_records_large": 8 * tiles,
+        "blend_track": R * (48 + 144) + (20 + 12) * W * H + 40 * tiles,
         "blend_forward": R * 48 + (28 + 12 + 12) * W * H + 40 * tiles,
         "blend_backward_pose": R * (48 + 144) + 20 * W * H + 8 * tiles,
         "track_update": 32 * tiles,

@@ -1,0 +1,253 @@
+// Single-pass tracking blend: forward alpha blend, tracking loss and the pose tangent of that loss in ONE walk over
+// each tile's list (replaces renderCUDA forward.cu:263-392 + the loss of utils/slam_utils.py + renderCUDA backward
+// backward.cu:800-1027 + the per-Gaussian chain, for the tracking case where only grad_rho / grad_theta are consumed).
+//
+// The reference's backward walks the list back to front because dC/dalpha_i needs the colour composited BEHIND splat i.
+// With r_i = 1/(1-alpha_i), T_i the transmittance in front of i and Cpre_i the colour accumulated before i,
+//     dL/dalpha_i = sum_ch g_ch * r_i * (T_i c_i,ch + Cpre_i,ch)  -  r_i * sum_ch g_ch * out_ch        (g = dL/d out)
+// (same value as backward.cu:927-975 including the background term; out_ch = final pixel colour).  Everything that
+// depends on the still unknown g and out factors out of the sum over splats, so a pixel accumulates, front to back,
+//     E      = sum_i  vp_i                         vp_i = r_i * opacity_i * B_i^T geom_i   (6-vector, B_i = pose_jac.cuh)
+//     A_ch   = sum_i (T_i c_i,ch + Cpre_i,ch) vp_i
+// and, once its colour and the loss gradient g are known in the epilogue, contracts
+//     tau_pixel = sum_ch g_ch * (A_ch - out_ch * E)        (+ the same for depth, + g_d * sum_i alpha_i T_i dz_i/dtau).
+// The local Jacobians are exactly the reference's (clamp ignored, Q6; FoV quirk inside B_i, Q8), only the order of
+// the sum differs.  One pass instead of two: no second exp per pair, no g / final_T / n_contrib round trip.
+#include "launchers.h"
+#include "tma.cuh"
+#include "loss_pixel.cuh"
+#include "pose_jac.cuh"
+
+namespace mgs {
+
+constexpr int TRK_BATCH = 128;
+constexpr int TRK_NF = PoseJac<6>::kFloats;   // 36
+
+constexpr int TRK_STAGES = 3;
+constexpr size_t TRK_SMEM = (size_t)TRK_STAGES * TRK_BATCH * sizeof(SplatRec) + 2 * (size_t)TRK_BATCH * TRK_NF * sizeof(float);
+
+__device__ __forceinline__ void cp_async16(void* dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// Pipeline per tile: records of batch i+2 in flight by bulk copy (TMA), pose Jacobians of batch i+1 gathered by cp.async
+// (their ids come from the records of i+1, already landed), batch i being blended: one CTA barrier (the early-out
+// vote) per batch and no load latency on the blend path.
+template <bool HAS_DEPTH, bool FAST>   // FAST: ex2.approx exponent, n_touched not produced
+__global__ void __launch_bounds__(256, 3)
+blend_track_kernel(const int W, const int H, const int gx, const uint2* __restrict__ ranges,
+                   const SplatRec* __restrict__ recs, const float* __restrict__ jac, const float* __restrict__ bg,
+                   float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
+                   int32_t* __restrict__ n_touched, const LossK lk, const float loss_grad_scale,
+                   double* __restrict__ loss_partials, float* __restrict__ tau_sum) {
+  extern __shared__ __align__(128) unsigned char trk_smem[];
+  SplatRec (*stage)[TRK_BATCH] = reinterpret_cast<SplatRec (*)[TRK_BATCH]>(trk_smem);
+  float (*jstage)[TRK_BATCH * TRK_NF] =
+      reinterpret_cast<float (*)[TRK_BATCH * TRK_NF]>(trk_smem + (size_t)TRK_STAGES * TRK_BATCH * sizeof(SplatRec));
+  __shared__ __align__(8) uint64_t full_bar[TRK_STAGES];
+  __shared__ float s_part[8][6];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tile = blockIdx.x;
+  const int tx = tile % gx, ty = tile / gx;
+  const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
+  const int py = ty * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+  const bool inside = px < W && py < H;
+  const float pxf = (float)px, pyf = (float)py;
+  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 4);
+  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+
+  const uint2 range = ranges[tile];
+  const int n = (int)(range.y - range.x);
+  const int rounds = (n + TRK_BATCH - 1) / TRK_BATCH;
+  const SplatRec* src = recs + range.x;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < TRK_STAGES; s++) mbar_init(&full_bar[s], 1);
+    mbar_init_fence();
+  }
+  __syncthreads();
+  auto issue = [&](int i) {   // records of batch i -> stage[i % 3]
+    const uint32_t bytes = (uint32_t)min(n - i * TRK_BATCH, TRK_BATCH) * sizeof(SplatRec);
+    mbar_expect_tx(&full_bar[i % TRK_STAGES], bytes);
+    bulk_g2s(&stage[i % TRK_STAGES][0], src + (size_t)i * TRK_BATCH, bytes, &full_bar[i % TRK_STAGES]);
+  };
+  auto wait_records = [&](int i) { mbar_wait(&full_bar[i % TRK_STAGES], (i / TRK_STAGES) & 1); };
+  auto gather = [&](int i) {  // pose Jacobians of batch i (L2-resident per-Gaussian array) -> jstage[i & 1], 16 B per cp.async
+    const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
+    const float4* rec4 = reinterpret_cast<const float4*>(&stage[i % TRK_STAGES][0]);
+    float4* dst = reinterpret_cast<float4*>(&jstage[i & 1][0]);
+    for (int e = tid; e < cnt * (TRK_NF / 4); e += 256) {
+      const int slot = e / (TRK_NF / 4), k = e - slot * (TRK_NF / 4);
+      const uint32_t id = __float_as_uint(rec4[3 * slot + 0].w);
+      cp_async16(dst + e, reinterpret_cast<const float4*>(jac + (size_t)id * TRK_NF) + k);
+    }
+    cp_async_commit();
+  };
+  if (tid == 0 && rounds > 0) { issue(0); if (rounds > 1) issue(1); }
+  if (rounds > 0) { wait_records(0); gather(0); }
+
+  bool done = !inside;
+  float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
+  float E[6], A0[6], A1[6], A2[6], Ad[6], F0 = 0.f, F1 = 0.f, F2 = 0.f;
+#pragma unroll
+  for (int k = 0; k < 6; k++) { E[k] = 0.f; A0[k] = 0.f; A1[k] = 0.f; A2[k] = 0.f; Ad[k] = 0.f; }
+
+  for (int i = 0; i < rounds; i++) {
+    cp_async_wait_all();   // this thread's share of the Jacobians of batch i has landed
+    // CTA vote; publishes the Jacobians of batch i and guarantees every warp left the buffers reused below
+    if (__syncthreads_count(done) == TILE_PIX) {
+      if (tid == 0 && i + 1 < rounds) wait_records(i + 1);   // never exit with a bulk copy in flight
+      break;
+    }
+    if (tid == 0 && i + 2 < rounds) issue(i + 2);
+    if (i + 1 < rounds) { wait_records(i + 1); gather(i + 1); }
+    const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
+    const float4* rec4 = reinterpret_cast<const float4*>(&stage[i % TRK_STAGES][0]);
+    const float* recf = reinterpret_cast<const float*>(&stage[i % TRK_STAGES][0]);
+    const float* jst = &jstage[i & 1][0];
+    for (int c0 = 0; c0 < cnt; c0 += 32) {
+      // lane-parallel exact cull of 32 splats against this warp's 8x4 patch (see splat_extent)
+      const int jj = c0 + lane;
+      unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+      if (__ballot_sync(0xffffffffu, !done) == 0u) break;
+      while (hits) {
+        const int j = c0 + __ffs(hits) - 1;
+        hits &= hits - 1;
+        const float4 g0 = rec4[3 * j + 0];  // x, y, depth, id
+        const float4 g1 = rec4[3 * j + 1];  // conic xyz, opacity
+        const float dx = g0.x - pxf, dy = g0.y - pyf;
+        const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
+        bool valid = !done && !(power > 0.0f);
+        const float G = blend_exp<FAST>(power);
+        const float alpha = min(0.99f, g1.w * G);
+        valid = valid && !(alpha < 1.0f / 255.0f);
+        const float test_T = T * (1 - alpha);
+        if (valid && test_T < 0.0001f) { done = true; valid = false; }
+        if (!FAST) {
+          const unsigned touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
+          if (touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
+        }
+        if (__ballot_sync(0xffffffffu, valid) == 0u) continue;
+        if (valid) {
+          const float4 g2 = rec4[3 * j + 2];
+          // vp = r * opacity * B^T geom  (geom: d alpha / d (mean2D, conic) up to the opacity factor, backward.cu:986-1010)
+          const float f = g1.w * __fdividef(1.f, 1.f - alpha);   // 1-alpha in [0.01,1]
+          const float gdx = G * dx, gdy = G * dy;
+          float q[5];
+          q[0] = f * (-gdx * g1.x - gdy * g1.y) * ddelx_dx;
+          q[1] = f * (-gdy * g1.z - gdx * g1.y) * ddely_dy;
+          q[2] = -0.5f * gdx * dx * f;
+          q[3] = -0.5f * gdx * dy * f;
+          q[4] = -0.5f * gdy * dy * f;
+          const float4* J4 = reinterpret_cast<const float4*>(jst + j * TRK_NF);
+          float Bf[TRK_NF];
+#pragma unroll
+          for (int k = 0; k < TRK_NF / 4; k++) { const float4 t4 = J4[k]; Bf[4 * k] = t4.x; Bf[4 * k + 1] = t4.y; Bf[4 * k + 2] = t4.z; Bf[4 * k + 3] = t4.w; }
+          float vp[6];
+#pragma unroll
+          for (int k = 0; k < 6; k++) vp[k] = q[0] * Bf[k];
+#pragma unroll
+          for (int c = 1; c < 5; c++)
+#pragma unroll
+            for (int k = 0; k < 6; k++) vp[k] = fmaf(q[c], Bf[c * 6 + k], vp[k]);
+          const float w0 = fmaf(T, g2.x, C0), w1 = fmaf(T, g2.y, C1), w2 = fmaf(T, g2.z, C2);
+#pragma unroll
+          for (int k = 0; k < 6; k++) {
+            E[k] += vp[k];
+            A0[k] = fmaf(w0, vp[k], A0[k]);
+            A1[k] = fmaf(w1, vp[k], A1[k]);
+            A2[k] = fmaf(w2, vp[k], A2[k]);
+          }
+          const float aT = alpha * T;
+          if (HAS_DEPTH) {
+            const float wd = fmaf(T, g0.z, D);
+#pragma unroll
+            for (int k = 0; k < 6; k++) Ad[k] = fmaf(wd, vp[k], Ad[k]);
+            // depth column of B: dz/dtau = (0, 0, 1, y_C, -x_C, 0)
+            F0 += aT; F1 = fmaf(aT, Bf[5 * 6 + 3], F1); F2 = fmaf(aT, Bf[5 * 6 + 4], F2);
+          }
+          C0 = fmaf(g2.x, aT, C0);
+          C1 = fmaf(g2.y, aT, C1);
+          C2 = fmaf(g2.z, aT, C2);
+          D = fmaf(g0.z, aT, D);
+          T = test_T;
+        }
+      }
+    }
+  }
+
+  // epilogue: outputs, loss and its gradient from the registers that hold the blended pixel, tangent contraction
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (inside) {
+    const size_t pix = (size_t)py * W + px;
+    const size_t plane = (size_t)W * H;
+    const float img[3] = {C0 + T * bg[0], C1 + T * bg[1], C2 + T * bg[2]};
+    out_color[pix] = img[0];
+    out_color[plane + pix] = img[1];
+    out_color[2 * plane + pix] = img[2];
+    out_depth[pix] = D;
+    out_opacity[pix] = 1 - T;
+    float gi[3], gd;
+    loss_pixel<true, true>(lk, (int)pix, img, D, 1 - T, loss_grad_scale, acc, gi, gd);
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      float t = gi[0] * (A0[k] - img[0] * E[k]);
+      t = fmaf(gi[1], A1[k] - img[1] * E[k], t);
+      t = fmaf(gi[2], A2[k] - img[2] * E[k], t);
+      if (HAS_DEPTH) t = fmaf(gd, Ad[k] - D * E[k], t);
+      tau[k] = t;
+    }
+    if (HAS_DEPTH) { tau[2] = fmaf(gd, F0, tau[2]); tau[3] = fmaf(gd, F1, tau[3]); tau[4] = fmaf(gd, F2, tau[4]); }
+  }
+  loss_block_reduce(acc, loss_partials + (size_t)tile * 4);
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    float x = tau[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) s_part[warp][k] = x;
+  }
+  __syncthreads();
+  if (tid < 6) {
+    float x = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; w++) x += s_part[w][tid];
+    if (x != 0.f) atomicAdd(&tau_sum[tid], x);
+  }
+}
+
+// tau_sum must be zeroed by the caller; jac holds the 6-column per-Gaussian maps (PoseJac<6>)
+int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
+                       float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
+                       float* tau_sum, cudaStream_t s) {
+  const int tiles = v.gx * v.gy;
+  static bool attr_set = false;
+  if (!attr_set) {
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    attr_set = true;
+  }
+#define MGS_TRK_ARGS v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color,   \
+      out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum
+  prof_begin("blend_track", s);
+  if (has_depth) {
+    if (fl.fast) blend_track_kernel<true, true><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+    else blend_track_kernel<true, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+  } else {
+    if (fl.fast) blend_track_kernel<false, true><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+    else blend_track_kernel<false, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+  }
+  prof_end(s);
+#undef MGS_TRK_ARGS
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
+}
+
+}  // namespace mgs

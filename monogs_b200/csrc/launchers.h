@@ -19,6 +19,11 @@ struct FusedLoss { const LossK* k; float grad_scale; float* g_img; float* g_dept
 int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
                          float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl = nullptr);
 
+// single-pass tracking blend (blend_track.cu): forward + loss + pose tangent; SH degree 0 / 6-column Jacobians only
+int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
+                       float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
+                       float* tau_sum, cudaStream_t s);
+
 struct BackwardArgs {
   ViewConst v; int P; uint32_t grad_mask;
   const float *means3D, *shs, *colors_precomp, *scales, *rotations, *cov3D_precomp;

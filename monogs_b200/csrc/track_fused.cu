@@ -3,9 +3,10 @@
 //
 //   preprocess (+ pose Jacobian of visible Gaussians, same thread)           1 kernel
 //   depth sort, scan, header, emit keys, tile sort, ranges + records         3 kernels + CUB
-//   forward blend with the loss fused into its epilogue                      1 kernel
+//   SH degree 0: single-pass blend = forward + loss + pose tangent (blend_track.cu)   1 kernel
+//   SH degree > 0: forward blend with the loss fused into its epilogue        1 kernel
 //       (per-pixel residual, Huber / L1 term, un-normalised dL/dimage, per-tile partial sums)
-//   pose-only backward blend (per-pixel tau accumulation)                    1 kernel
+//     + pose-only backward blend (per-pixel tau accumulation)                 1 kernel
 //   update: loss + norm from the partials, tau/dab scaling, Adam (device step counter), T <- Exp(tau) T,
 //           view / projection matrices                                        1 kernel
 //
@@ -139,13 +140,19 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   fl.k = &lk;
   fl.grad_scale = (t->loss_mode == MGS_LOSS_TRACK_HUBER) ? 1.f : (use_depth ? t->alpha : 1.f) / (3.f * (float)npix);
   fl.g_img = g_img; fl.g_depth = use_depth ? g_depth : nullptr; fl.partials = partials; fl.fast = t->fast_math != 0;
-  if ((rc = launch_blend_forward(v, ws, L, t->out_color, t->out_depth, t->out_opacity, t->n_touched, s, &fl))) return rc;
-
-  BackwardArgs a;
-  memset(&a, 0, sizeof(a));
-  a.v = v; a.P = P; a.grad_mask = MGS_GRAD_TAU; a.ws = ws; a.L = L;
-  a.dL_dcolor_img = g_img; a.dL_ddepth_img = use_depth ? g_depth : nullptr; a.dL_dtau_sum = tau_raw;
-  if ((rc = launch_blend_backward_pose(a, jac, with_color, s, t->fast_math != 0))) return rc;
+  if (!with_color) {
+    // SH degree 0: colours do not depend on the pose -> forward, loss and pose tangent in one pass over the tile lists
+    if ((rc = launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
+                                 tau_raw, s)))
+      return rc;
+  } else {
+    if ((rc = launch_blend_forward(v, ws, L, t->out_color, t->out_depth, t->out_opacity, t->n_touched, s, &fl))) return rc;
+    BackwardArgs a;
+    memset(&a, 0, sizeof(a));
+    a.v = v; a.P = P; a.grad_mask = MGS_GRAD_TAU; a.ws = ws; a.L = L;
+    a.dL_dcolor_img = g_img; a.dL_ddepth_img = use_depth ? g_depth : nullptr; a.dL_dtau_sum = tau_raw;
+    if ((rc = launch_blend_backward_pose(a, jac, with_color, s, t->fast_math != 0))) return rc;
+  }
 
   TrackUpdateK k;
   k.mode = t->loss_mode; k.use_depth = use_depth; k.npix = (int)npix; k.tiles = tiles; k.alpha = t->alpha; k.scale = 1.f;

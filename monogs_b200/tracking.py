@@ -15,8 +15,8 @@ import torch
 from . import _lib as L
 from .rasterizer import make_view, GaussianRasterizationSettings, _stream
 
-KERNELS_PER_ITER = 8    # own kernels per fused iteration: preprocess(+jac, +tile counts), tile_scan, emit,
-                        # tile_sort_records x2 (short / long lists), blend_forward(+loss), blend_backward_pose, track_update
+KERNELS_PER_ITER = 7    # own kernels per fused iteration (SH degree 0): preprocess(+jac, +tile counts), tile_scan, emit,
+                        # tile_sort_records x2 (short / long lists), blend_track (forward+loss+pose tangent), track_update
 KERNELS_PER_ITER_COMPOSED = 14
 
 
