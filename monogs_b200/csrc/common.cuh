@@ -154,12 +154,31 @@ __device__ __forceinline__ uint32_t splat_extent(float cx, float cy, float cz, f
   const __half2 h = __halves2half2(__float2half_ru(hx), __float2half_ru(hy));
   return *reinterpret_cast<const uint32_t*>(&h);
 }
-// lane-parallel cull test of record `rec` (12 floats) against the pixel box [x0,x1] x [y0,y1]
+// lane-parallel cull test of record `rec` (12 floats) against the pixel box [x0,x1] x [y0,y1]: the half-extent box
+// first, then exactly — the minimum of f(d) = d^T conic d over the box against 2 ln(255 op) (alpha >= 1/255 <=>
+// f <= 2 ln(255 op), forward.cu:352-355).  f is a positive-definite quadratic centred on the splat, so when the centre
+// lies outside the box the minimum sits on the edge(s) facing it: at most two 1-D clamped minimisations.  The box
+// holds every pixel centre of the patch, so a patch culled here holds only pixels the reference would skip.
 __device__ __forceinline__ bool splat_hits(const float* rec, float x0, float x1, float y0, float y1) {
   const float x = rec[0], y = rec[1];
   const uint32_t e = __float_as_uint(rec[11]);
   const float2 h = __half22float2(*reinterpret_cast<const __half2*>(&e));
-  return (x + h.x >= x0) && (x - h.x <= x1) && (y + h.y >= y0) && (y - h.y <= y1);
+  if (!((x + h.x >= x0) && (x - h.x <= x1) && (y + h.y >= y0) && (y - h.y <= y1))) return false;
+  const float dxe = fminf(fmaxf(x, x0), x1) - x, dye = fminf(fmaxf(y, y0), y1) - y;   // centre -> nearest box point
+  if (dxe == 0.f && dye == 0.f) return true;
+  const float a = rec[4], b = rec[5], c = rec[6], op = rec[7];
+  if (!(a > 0.f) || !(c > 0.f) || !(a * c - b * b > 0.f)) return true;   // not positive definite: never culled
+  float fmin = __int_as_float(0x7f800000);
+  if (dxe != 0.f) {
+    const float t = fminf(fmaxf(y - __fdividef(b * dxe, c), y0), y1) - y;
+    fmin = a * dxe * dxe + 2.f * b * dxe * t + c * t * t;
+  }
+  if (dye != 0.f) {
+    const float s = fminf(fmaxf(x - __fdividef(b * dye, a), x0), x1) - x;
+    fmin = fminf(fmin, a * s * s + 2.f * b * s * dye + c * dye * dye);
+  }
+  const float thr = 2.f * __logf(255.f * op);   // op > 1/255 here (the half-extent box of op <= 1/255 is empty)
+  return !(fmin > thr * 1.001f + 1e-3f);         // NaN -> not culled
 }
 
 // exp() of the blend exponent.  FAST = false: expf, bit-identical to the reference's images.  FAST = true (fused
