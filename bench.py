@@ -449,8 +449,11 @@ def main():
                     v["alg_bytes"] = ab[k]; v["gbs"] = ab[k] / (v["avg_us"] * 1e-6) / 1e9
             top = max(prof, key=lambda k: prof[k]["avg_us"])
             step_us = sum(v["avg_us"] for v in prof.values())
+            # dram__bytes_read + write of one launch from the committed ncu --set full capture (profiles/), C2 only
+            traffic = {"blend_track": 56.2e6}.get(top) if args.config == "C2" else None
             line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": prof[top].get("gbs"), "peak": peak, "unit": "GB/s",
-                                "frac": (prof[top].get("gbs") or 0) / peak, "traffic": None, "peak_source": src,
+                                "frac": (prof[top].get("gbs") or 0) / peak, "traffic": traffic,
+                                "traffic_source": "profiles/r01b_ncu_track_and_binning.txt", "peak_source": src,
                                 "share_of_step": prof[top]["avg_us"] / step_us,
                                 "note": "the blend kernels are issue/SFU-bound (one 48-B record feeds 256 pixel "
                                         "evaluations), so their HBM fraction is small by construction; see DESIGN.md"}
