@@ -266,22 +266,22 @@ def ref_cuda_leg(cfg, dev, steps, warmup, flush):
                     "reference wrapper allocations + eager Huber/L2 loss + torch Adam + torch pose update"}
 
 
-def mapping_leg(dev, rank, world, iters=10, warmup=3, P=200_000, window=8):
+def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engine=True):
     """Config C4: 8-keyframe mapping window, views round-robin over ranks, one allreduce of the gradient arena,
-    fused Adam on every rank.  Returns iterations/s (max over ranks)."""
+    fused Adam on every rank.  engine=True: monogs_b200.mapping.MapEngine (mgs_map_*: raw parameters, activations once
+    per iteration, no host sync); engine=False: the same iteration through the drop-in autograd surface (MappingStep).
+    Returns iterations/s (max over ranks)."""
     import torch.distributed as dist
     from monogs_b200 import scene as S, ops
-    from monogs_b200.mapping import MappingStep
+    from monogs_b200.mapping import MappingStep, MapEngine, MapView
     from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
     sc, cam = S.make_config("C2", P=P)
     bg = torch.zeros(3, device=dev)
     inv_sig = lambda x: torch.log(x / (1 - x))
-    params = {"xyz": sc.means3D.to(dev).requires_grad_(True), "f_dc": sc.shs.to(dev).requires_grad_(True),
-              "opacity": inv_sig(sc.opacities.clamp(1e-4, 1 - 1e-4)).to(dev).requires_grad_(True),
-              "scaling": torch.log(sc.scales).to(dev).requires_grad_(True),
-              "rotation": sc.rotations.to(dev).requires_grad_(True)}
+    raw = {"xyz": sc.means3D.to(dev), "f_dc": sc.shs.to(dev).contiguous(),
+           "opacity": inv_sig(sc.opacities.clamp(1e-4, 1 - 1e-4)).to(dev), "scaling": torch.log(sc.scales).to(dev),
+           "rotation": sc.rotations.to(dev)}
     lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "opacity": 0.05, "scaling": 1e-3, "rotation": 1e-3}
-    opt = ops.FusedAdam([{"params": [p], "lr": lrs[k]} for k, p in params.items()], lr=0.0, eps=1e-15)
     views = []
     for i in range(window):
         tau = torch.tensor(S.GT_TAU) * (i - window / 2) * 0.5
@@ -290,39 +290,53 @@ def mapping_leg(dev, rank, world, iters=10, warmup=3, P=200_000, window=8):
         rs = GaussianRasterizationSettings(c.H, c.W, c.tanfovx, c.tanfovy, bg, 1.0, c.viewmatrix, c.projmatrix,
                                            c.projmatrix_raw, 0, c.campos, False, False)
         with torch.no_grad():
-            gt = GaussianRasterizer(rs)(means3D=params["xyz"], means2D=torch.zeros_like(params["xyz"]), shs=params["f_dc"],
-                                        opacities=torch.sigmoid(params["opacity"]), scales=torch.exp(params["scaling"]),
-                                        rotations=torch.nn.functional.normalize(params["rotation"]))[0]
+            gt = GaussianRasterizer(rs)(means3D=raw["xyz"], means2D=torch.zeros_like(raw["xyz"]), shs=raw["f_dc"],
+                                        opacities=torch.sigmoid(raw["opacity"]), scales=torch.exp(raw["scaling"]),
+                                        rotations=torch.nn.functional.normalize(raw["rotation"]))[0]
         views.append((rs, (gt * 0.9 + 0.05).contiguous()))
+    if engine:
+        eng = MapEngine({k: v.clone() for k, v in raw.items()}, lrs, sh_degree=0, W=cam.W, H=cam.H, capacity_headroom=1.5)
+        mviews = [MapView(rs, gt) for rs, gt in views]
+        run = lambda: eng.step(mviews)
+        nbytes = eng.arena.nbytes()
+    else:
+        params = {k: v.clone().requires_grad_(True) for k, v in raw.items()}
+        opt = ops.FusedAdam([{"params": [p], "lr": lrs[k]} for k, p in params.items()], lr=0.0, eps=1e-15)
 
-    def view_loss(p, view):      # gaussian_renderer/__init__.py:79-168 activations + get_loss_mapping_rgb
-        rs, gt = view
-        image, _, depth, _, _ = GaussianRasterizer(rs)(
-            means3D=p["xyz"], means2D=torch.zeros_like(p["xyz"]), shs=p["f_dc"], opacities=torch.sigmoid(p["opacity"]),
-            scales=torch.exp(p["scaling"]), rotations=torch.nn.functional.normalize(p["rotation"]))
-        return ops.mapping_loss(image, None, gt)
+        def view_loss(p, view):      # gaussian_renderer/__init__.py:79-168 activations + get_loss_mapping_rgb
+            rs, gt = view
+            image, _, depth, _, _ = GaussianRasterizer(rs)(
+                means3D=p["xyz"], means2D=torch.zeros_like(p["xyz"]), shs=p["f_dc"], opacities=torch.sigmoid(p["opacity"]),
+                scales=torch.exp(p["scaling"]), rotations=torch.nn.functional.normalize(p["rotation"]))
+            return ops.mapping_loss(image, None, gt)
 
-    def reg(p):                  # slam_backend.py:244-246
-        s = torch.exp(p["scaling"])
-        return 10 * (s - s.mean(dim=1, keepdim=True)).abs().mean()
-    ms = MappingStep(params, opt, view_loss, reg)
+        def reg(p):                  # slam_backend.py:244-246
+            s = torch.exp(p["scaling"])
+            return 10 * (s - s.mean(dim=1, keepdim=True)).abs().mean()
+        ms = MappingStep(params, opt, view_loss, reg)
+        run = lambda: ms.step(views)
+        nbytes = ms.arena.nbytes()
     for _ in range(warmup):
-        ms.step(views)
+        run()
     torch.cuda.synchronize()
     if world > 1: dist.barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):
-        ms.step(views)
+        run()
     e1.record()
     torch.cuda.synchronize()
     if world > 1: dist.barrier()
     t = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1: dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return {"iters_per_s": 1e3 * iters / float(t), "n_gpus": world, "window": window, "gaussians": P,
-            "views_per_rank": len(range(rank, window, world)), "allreduce_bytes": ms.arena.nbytes() if world > 1 else 0,
-            "scaling": "strong", "what": "8-keyframe window: per-view render+mapping loss+full backward, one "
-            "sum-allreduce of the gradient arena, fused Adam on every rank"}
+    out = {"iters_per_s": 1e3 * iters / float(t), "n_gpus": world, "window": window, "gaussians": P,
+           "views_per_rank": len(range(rank, window, world)), "allreduce_bytes": nbytes if world > 1 else 0,
+           "scaling": "strong", "api": "MapEngine (mgs_map_*)" if engine else "drop-in autograd surface (MappingStep)",
+           "what": "8-keyframe window: per-view render+mapping loss+full backward, isotropic regulariser, one "
+                   "sum-allreduce of the gradient arena, fused Adam on every rank"}
+    if engine:
+        out["overflow"] = eng.check_capacity()[1]
+    return out
 
 
 def e2e_dropin_leg(cfg, dev, steps, warmup, gt_host):
@@ -472,6 +486,11 @@ def main():
             line["mapping"] = mapping_leg(dev, rank, world)
         except Exception as ex:
             line["mapping"] = {"error": repr(ex)[:300]}
+        if world == 1:
+            try:
+                line["mapping_dropin"] = mapping_leg(dev, rank, world, iters=10, warmup=3, engine=False)
+            except Exception as ex:
+                line["mapping_dropin"] = {"error": repr(ex)[:300]}
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

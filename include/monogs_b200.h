@@ -219,6 +219,62 @@ typedef struct mgs_track_args {
 size_t mgs_track_scratch_bytes(int32_t P, int32_t W, int32_t H);
 int mgs_track_iteration(const mgs_track_args* args, void* stream);
 
+/* ---- keyframe-window mapping iteration on the RAW Gaussian parameters (SURVEY.md §8 rows f1 + e).
+ *      Replaces, per iteration of BackEnd.map (utils/slam_backend.py:157-333): the per-render parameter activations and
+ *      their autograd chain (gaussian_splatting/scene/gaussian_model.py:77-97, gaussian_renderer/__init__.py:79-114:
+ *      sigmoid(_opacity), exp(_scaling), normalize(_rotation), cat(f_dc, f_rest)), render + get_loss_mapping
+ *      (utils/slam_utils.py:224-253) + backward for every view, the isotropic regulariser (:244-246) and the
+ *      densification statistics (:292-299, gaussian_model.py:693-697).  The activations run ONCE per iteration
+ *      (mgs_map_begin), every view accumulates activated-space gradients in place (mgs_map_view, no host
+ *      synchronisation), and mgs_map_end applies the activation chain rule once and writes the raw-parameter gradients
+ *      — the arena NCCL all-reduces and the fused Adam consumes. ---- */
+typedef struct mgs_gaussians {
+  int32_t P;
+  int32_t sh_coeffs;        /* M: coefficients per channel stored (1 + rest) */
+  int32_t sh_degree;        /* active degree */
+  int32_t isotropic;        /* 1: scaling_raw is [P,1] and is repeated to three axes (gaussian_renderer/__init__.py:92-95) */
+  const float* xyz;          /* f32[P,3] */
+  const float* f_dc;         /* f32[P,1,3] */
+  const float* f_rest;       /* f32[P,M-1,3], null when M == 1 */
+  const float* opacity_raw;  /* f32[P,1], pre-sigmoid */
+  const float* scaling_raw;  /* f32[P,3] (or [P,1]), pre-exp */
+  const float* rotation_raw; /* f32[P,4], un-normalised (w,x,y,z) */
+} mgs_gaussians;
+
+typedef struct mgs_map_args {
+  mgs_gaussians g;
+  /* raw-parameter gradients, same shapes as the parameters.  grad_xyz and grad_f_dc are accumulated in place by the
+   * views (zeroed by mgs_map_begin); the others are written by mgs_map_end. */
+  float *grad_xyz, *grad_f_dc, *grad_f_rest, *grad_opacity, *grad_scaling, *grad_rotation;
+  /* densification statistics updated in place by every view with update_stats != 0; each may be null */
+  float *xyz_gradient_accum, *denom, *max_radii2D;   /* f32[P] each */
+  float* loss_total;        /* device f32[1]: sum of the view losses (+ regulariser), zeroed by mgs_map_begin */
+  void* scratch; size_t scratch_bytes;   /* mgs_map_scratch_bytes(P, M, W_max, H_max) */
+} mgs_map_args;
+
+typedef struct mgs_map_view {
+  mgs_view view;
+  const float* gt_image;    /* f32[3,H,W] */
+  const float* gt_depth;    /* f32[1,H,W], null = monocular (get_loss_mapping_rgb) */
+  const float* exposure_a;  /* device f32[1] or null (initialization: image_ab = image) */
+  const float* exposure_b;
+  float rgb_boundary_threshold, alpha;
+  int32_t update_stats;
+  float *out_color, *out_depth, *out_opacity;   /* f32[3,H,W], f32[1,H,W], f32[1,H,W] */
+  int32_t *radii, *n_touched;                   /* i32[P] of THIS view (visibility filter, occ_aware_visibility) */
+  float* tau;               /* f32[6]: pose tangent (rho, theta) of this view's loss, optional */
+  float* dab;               /* f32[2]: dL/d(exposure_a, exposure_b), optional */
+  float* loss;              /* f32[1]: this view's loss, optional */
+  void* workspace; size_t workspace_bytes; int64_t R_cap;
+} mgs_map_view;
+
+size_t mgs_map_scratch_bytes(int32_t P, int32_t sh_coeffs, int32_t W_max, int32_t H_max);
+int mgs_map_begin(const mgs_map_args* args, void* stream);
+int mgs_map_view_fwd_bwd(const mgs_map_args* args, const mgs_map_view* view, void* stream);
+/* add_regulariser: 1 on exactly one rank of a data-parallel group so the all-reduced sum counts the isotropic term
+ * weight * mean|s - mean(s)| once (weight = 10 in the reference). */
+int mgs_map_end(const mgs_map_args* args, int32_t add_regulariser, float regulariser_weight, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -62,6 +62,36 @@ class MgsTrackArgs(C.Structure):
     ]
 
 
+class MgsGaussians(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("sh_coeffs", C.c_int32), ("sh_degree", C.c_int32), ("isotropic", C.c_int32),
+        ("xyz", C.c_void_p), ("f_dc", C.c_void_p), ("f_rest", C.c_void_p), ("opacity_raw", C.c_void_p),
+        ("scaling_raw", C.c_void_p), ("rotation_raw", C.c_void_p),
+    ]
+
+
+class MgsMapArgs(C.Structure):
+    _fields_ = [
+        ("g", MgsGaussians),
+        ("grad_xyz", C.c_void_p), ("grad_f_dc", C.c_void_p), ("grad_f_rest", C.c_void_p), ("grad_opacity", C.c_void_p),
+        ("grad_scaling", C.c_void_p), ("grad_rotation", C.c_void_p),
+        ("xyz_gradient_accum", C.c_void_p), ("denom", C.c_void_p), ("max_radii2D", C.c_void_p),
+        ("loss_total", C.c_void_p), ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+    ]
+
+
+class MgsMapView(C.Structure):
+    _fields_ = [
+        ("view", MgsView),
+        ("gt_image", C.c_void_p), ("gt_depth", C.c_void_p), ("exposure_a", C.c_void_p), ("exposure_b", C.c_void_p),
+        ("rgb_boundary_threshold", C.c_float), ("alpha", C.c_float), ("update_stats", C.c_int32),
+        ("out_color", C.c_void_p), ("out_depth", C.c_void_p), ("out_opacity", C.c_void_p),
+        ("radii", C.c_void_p), ("n_touched", C.c_void_p),
+        ("tau", C.c_void_p), ("dab", C.c_void_p), ("loss", C.c_void_p),
+        ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("R_cap", C.c_int64),
+    ]
+
+
 _P, _I32, _I64, _U32, _F, _SZ = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_float, C.c_size_t
 _VP = C.POINTER(MgsView)
 
@@ -92,6 +122,10 @@ SIGNATURES = {
     "mgs_track_scratch_bytes": (_SZ, [_I32, _I32, _I32]),
     "mgs_track_iteration": (C.c_int, [C.POINTER(MgsTrackArgs), _P]),
     "mgs_pose_update": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _F, _P]),
+    "mgs_map_scratch_bytes": (_SZ, [_I32, _I32, _I32, _I32]),
+    "mgs_map_begin": (C.c_int, [C.POINTER(MgsMapArgs), _P]),
+    "mgs_map_view_fwd_bwd": (C.c_int, [C.POINTER(MgsMapArgs), C.POINTER(MgsMapView), _P]),
+    "mgs_map_end": (C.c_int, [C.POINTER(MgsMapArgs), _I32, _F, _P]),
 }
 
 _lib = None

@@ -162,18 +162,18 @@ blend_track_kernel(const int W, const int H, const int gx, const uint2* __restri
             A1[k] = fmaf(w1, vp[k], A1[k]);
             A2[k] = fmaf(w2, vp[k], A2[k]);
           }
-          const float aT = alpha * T;
           if (HAS_DEPTH) {
+            const float aT = alpha * T;
             const float wd = fmaf(T, g0.z, D);
 #pragma unroll
             for (int k = 0; k < 6; k++) Ad[k] = fmaf(wd, vp[k], Ad[k]);
             // depth column of B: dz/dtau = (0, 0, 1, y_C, -x_C, 0)
             F0 += aT; F1 = fmaf(aT, Bf[5 * 6 + 3], F1); F2 = fmaf(aT, Bf[5 * 6 + 4], F2);
           }
-          C0 = fmaf(g2.x, aT, C0);
-          C1 = fmaf(g2.y, aT, C1);
-          C2 = fmaf(g2.z, aT, C2);
-          D = fmaf(g0.z, aT, D);
+          C0 += g2.x * alpha * T;   // same expression as forward.cu:364-367 / blend_forward.cu: identical image bits
+          C1 += g2.y * alpha * T;
+          C2 += g2.z * alpha * T;
+          D += g0.z * alpha * T;
           T = test_T;
         }
       }

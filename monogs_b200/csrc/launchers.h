@@ -32,10 +32,15 @@ struct BackwardArgs {
   const float *dL_dcolor_img, *dL_ddepth_img;
   float *dL_dmeans3D, *dL_dmeans2D, *dL_dcolors_or_sh, *dL_dopacity, *dL_dscales, *dL_drotations, *dL_dcov3D;
   float *dL_dtau_sum, *dL_dtau_pg;
+  // mapping window (map_fused.cu): accumulate == 1 adds into the gradient outputs (visible Gaussians only) instead of
+  // overwriting them; optional densification statistics updated in the same pass (gaussian_model.py:693-697,
+  // slam_backend.py:292-299): grad_accum[g] += |dL/dmean2D.xy|, denom[g] += 1, max_radii2D[g] = max(., radii[g])
+  int accumulate; float *stat_grad_accum, *stat_denom, *stat_max_radii;
   // sketch mode (sketch_dim > 0): per-pixel row routing, output sketch_dtau[d,6]
   int sketch_dim; const int32_t* sketch_indices; float* sketch_dtau;
 };
 int launch_backward(const BackwardArgs& a, cudaStream_t s);
+int launch_backward_full(const BackwardArgs& a, cudaStream_t s);
 int launch_blend_backward_pose(const BackwardArgs& a, const float* jac, bool with_color, cudaStream_t s, bool fast = false);
 size_t backward_scratch_bytes(int P, int sketch_dim);
 

@@ -225,11 +225,14 @@ preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
                            float* __restrict__ dL_dmeans3D, float* __restrict__ dL_dmeans2D,
                            float* __restrict__ dL_dcolors_or_sh, float* __restrict__ dL_dopacity,
                            float* __restrict__ dL_dscales, float* __restrict__ dL_drotations,
-                           float* __restrict__ dL_dcov3D, float* __restrict__ tau_sum, float* __restrict__ tau_pg) {
+                           float* __restrict__ dL_dcov3D, float* __restrict__ tau_sum, float* __restrict__ tau_pg,
+                           const int accumulate, float* __restrict__ stat_grad_accum, float* __restrict__ stat_denom,
+                           float* __restrict__ stat_max_radii) {
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (idx < P) {
-    const bool vis = radii[idx] > 0;
+    const int rad = radii[idx];
+    const bool vis = rad > 0;
     float3 dmean = {0.f, 0.f, 0.f}, dscale = {0.f, 0.f, 0.f};
     float4 drot = {0.f, 0.f, 0.f, 0.f};
     float dcov6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -270,14 +273,33 @@ preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
       if (shs != nullptr) {
         const uint32_t cm = __float_as_uint(rgb4[idx].w);
         const float3 dcol = {(cm & 1u) ? 0.f : gg.r, (cm & 2u) ? 0.f : gg.g, (cm & 4u) ? 0.f : gg.b};
-        const float3 dms = sh_backward(v.D, Msh, p, v.campos, shs + (size_t)idx * Msh * 3, dcol, dsh);
+        const float3 dms = sh_backward(v.D, Msh, p, v.campos, shs + (size_t)idx * Msh * 3, dcol, dsh, accumulate != 0);
         dmean.x += dms.x; dmean.y += dms.y; dmean.z += dms.z;
         tau[0] += -dms.x; tau[1] += -dms.y; tau[2] += -dms.z;
       }
       if (scales != nullptr && (mask & MGS_GRAD_COV)) cov3d_backward(scales, rotations, idx, v.scale_modifier, dcov6, dscale, drot);
-    } else if (dsh != nullptr) {
+    } else if (dsh != nullptr && !accumulate) {
       for (int k = 0; k < 3 * Msh; k++) dsh[k] = 0.f;
     }
+    if (accumulate) {
+      if (vis) {   // sum over the views of a mapping window; Gaussians outside this view contribute nothing
+        if (mask & MGS_GRAD_MEANS3D) { dL_dmeans3D[3 * idx] += dmean.x; dL_dmeans3D[3 * idx + 1] += dmean.y; dL_dmeans3D[3 * idx + 2] += dmean.z; }
+        if (mask & MGS_GRAD_MEANS2D) { dL_dmeans2D[3 * idx] += gg.mx; dL_dmeans2D[3 * idx + 1] += gg.my; }
+        if (mask & MGS_GRAD_OPACITY) dL_dopacity[idx] += gg.op;
+        if ((mask & MGS_GRAD_COLOR) && shs == nullptr) {
+          dL_dcolors_or_sh[3 * idx] += gg.r; dL_dcolors_or_sh[3 * idx + 1] += gg.g; dL_dcolors_or_sh[3 * idx + 2] += gg.b;
+        }
+        if ((mask & MGS_GRAD_COV) && scales != nullptr) {
+          dL_dscales[3 * idx] += dscale.x; dL_dscales[3 * idx + 1] += dscale.y; dL_dscales[3 * idx + 2] += dscale.z;
+          float4 d = reinterpret_cast<float4*>(dL_drotations)[idx];
+          d.x += drot.x; d.y += drot.y; d.z += drot.z; d.w += drot.w;
+          reinterpret_cast<float4*>(dL_drotations)[idx] = d;
+        }
+        if (stat_grad_accum != nullptr) stat_grad_accum[idx] += sqrtf(gg.mx * gg.mx + gg.my * gg.my);
+        if (stat_denom != nullptr) stat_denom[idx] += 1.f;
+        if (stat_max_radii != nullptr) stat_max_radii[idx] = fmaxf(stat_max_radii[idx], (float)rad);
+      }
+    } else {
     if (mask & MGS_GRAD_MEANS3D) { dL_dmeans3D[3 * idx] = dmean.x; dL_dmeans3D[3 * idx + 1] = dmean.y; dL_dmeans3D[3 * idx + 2] = dmean.z; }
     if (mask & MGS_GRAD_MEANS2D) { dL_dmeans2D[3 * idx] = gg.mx; dL_dmeans2D[3 * idx + 1] = gg.my; dL_dmeans2D[3 * idx + 2] = 0.f; }
     if (mask & MGS_GRAD_OPACITY) dL_dopacity[idx] = gg.op;
@@ -293,6 +315,7 @@ preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
 #pragma unroll
         for (int k = 0; k < 6; k++) dL_dcov3D[6 * (size_t)idx + k] = dcov6[k];
       }
+    }
     }
     if (tau_pg != nullptr) {
 #pragma unroll
@@ -327,7 +350,8 @@ int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   preprocess_backward_kernel<<<(P + 255) / 256, 256, 0, s>>>(
       v, P, a.grad_mask, a.means3D, a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp, a.radii,
       ws_ptr<float4>(a.ws, a.L.rgb4), g2d, a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dcolors_or_sh, a.dL_dopacity,
-      a.dL_dscales, a.dL_drotations, a.dL_dcov3D, a.dL_dtau_sum, a.dL_dtau_pg);
+      a.dL_dscales, a.dL_drotations, a.dL_dcov3D, a.dL_dtau_sum, a.dL_dtau_pg, a.accumulate, a.stat_grad_accum,
+      a.stat_denom, a.stat_max_radii);
   prof_end(s);
   MGS_LAUNCH_CHECK();
   return MGS_OK;

@@ -10,7 +10,8 @@ every rank applies the identical update, so no parameter broadcast is needed.
 All Gaussian gradients live in ONE contiguous fp32 arena (`grad_arena`): each parameter's .grad is a view into
 it, autograd accumulates in place, and the collective is a single all_reduce over 4*(11+3M)*P bytes.
 """
-from typing import Callable, Dict, List, Sequence
+import ctypes as C
+from typing import Callable, Dict, List, NamedTuple, Optional, Sequence
 
 import torch
 import torch.distributed as dist
@@ -86,3 +87,187 @@ class MappingStep:
             dist.all_reduce(total, op=dist.ReduceOp.SUM, group=self.group)
         self.opt.step()                # identical update on every rank (replicated params + Adam state)
         return total
+
+
+class MapView(NamedTuple):
+    """One keyframe as the mapping engine consumes it (the fields BackEnd.map reads from a Camera,
+    utils/camera_utils.py:94-108, plus its target images)."""
+    settings: object                      # GaussianRasterizationSettings (matrices on the device)
+    gt_image: torch.Tensor                # f32[3,H,W]
+    gt_depth: Optional[torch.Tensor] = None     # f32[1,H,W]; None = monocular loss
+    exposure_a: Optional[torch.Tensor] = None   # f32[1] device tensors; None = initialization (image_ab = image)
+    exposure_b: Optional[torch.Tensor] = None
+    update_stats: bool = True
+
+
+class MapViewResult(NamedTuple):
+    radii: torch.Tensor        # i32[P]  (visibility_filter = radii > 0)
+    n_touched: torch.Tensor    # i32[P]  (occ_aware_visibility = n_touched > 0)
+    tau: torch.Tensor          # f32[6]  pose tangent (rho, theta) of this view's loss
+    dab: torch.Tensor          # f32[2]  dL/d(exposure_a, exposure_b)
+    loss: torch.Tensor         # f32[1]
+
+
+class MapEngine:
+    """Device-resident mapping iteration over the C-ABI (mgs_map_begin / mgs_map_view_fwd_bwd / mgs_map_end).
+
+    Holds the RAW Gaussian parameters (gaussian_model.py:77-97: _xyz, _features_dc, _features_rest, _opacity, _scaling,
+    _rotation), one contiguous gradient arena that aliases their .grad, the densification statistics and a fused Adam.
+    `step(views)` = one iteration of BackEnd.map (slam_backend.py:157-333) up to and including optimizer.step():
+    activations once, every view of this rank's round-robin share rendered + back-propagated in place, the isotropic
+    regulariser on rank 0, one sum-allreduce of the arena (NCCL over NVLink/NVSwitch; gloo in the CPU tests can not run
+    this class — it needs the CUDA library), fused Adam on every rank.  Nothing in the iteration synchronises the host.
+    """
+
+    NAMES = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
+
+    def __init__(self, params: Dict[str, torch.Tensor], lrs: Dict[str, float], sh_degree: int = 0, W: int = 640, H: int = 480,
+                 capacity_headroom: float = 2.0, group=None, regulariser_weight: float = 10.0,
+                 rgb_boundary_threshold: float = 0.01, alpha: float = 0.95):
+        from . import _lib as L
+        from .ops import FusedAdam
+        self.L, self.lib = L, L.lib()
+        self.params = {k: params[k] for k in self.NAMES if k in params and params[k] is not None and params[k].numel() > 0}
+        self.dev = self.params["xyz"].device
+        self.P = self.params["xyz"].size(0)
+        self.M = 1 + (self.params["f_rest"].size(1) if "f_rest" in self.params else 0)
+        self.sh_degree = sh_degree
+        self.isotropic = self.params["scaling"].size(-1) == 1
+        for p in self.params.values():
+            assert p.is_contiguous() and p.dtype == torch.float32 and p.device == self.dev
+        self.arena = GradArena(list(self.params.values()))
+        self.grads = dict(zip(self.params.keys(), self.arena.views))
+        self.opt = FusedAdam([{"params": [p], "lr": lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15)
+        f = dict(device=self.dev, dtype=torch.float32)
+        self.xyz_gradient_accum, self.denom = torch.zeros(self.P, **f), torch.zeros(self.P, **f)
+        self.max_radii2D = torch.zeros(self.P, **f)
+        self.loss_total = torch.zeros(1, **f)
+        self.W, self.H = W, H
+        self.scratch = torch.empty(self.lib.mgs_map_scratch_bytes(self.P, self.M, W, H), device=self.dev, dtype=torch.uint8)
+        self.color, self.depth, self.opacity = torch.empty(3, H, W, **f), torch.empty(1, H, W, **f), torch.empty(1, H, W, **f)
+        self.headroom = capacity_headroom
+        self.R_cap, self.ws = 0, None
+        self.reg_weight, self.thr, self.alpha = regulariser_weight, rgb_boundary_threshold, alpha
+        self.group = group
+        self.distributed = dist.is_available() and dist.is_initialized()
+        self.world = dist.get_world_size(group) if self.distributed else 1
+        self.rank = dist.get_rank(group) if self.distributed else 0
+        self._keep = []
+        self._slots = {}
+
+    # ------------------------------------------------------------------------------------------------
+    def _args(self):
+        L = self.L
+        a = L.MgsMapArgs()
+        g, p = a.g, self.params
+        g.P, g.sh_coeffs, g.sh_degree, g.isotropic = self.P, self.M, self.sh_degree, int(self.isotropic)
+        g.xyz, g.f_dc = p["xyz"].data_ptr(), p["f_dc"].data_ptr()
+        g.f_rest = p["f_rest"].data_ptr() if "f_rest" in p else None
+        g.opacity_raw, g.scaling_raw, g.rotation_raw = p["opacity"].data_ptr(), p["scaling"].data_ptr(), p["rotation"].data_ptr()
+        gr = self.grads
+        a.grad_xyz, a.grad_f_dc = gr["xyz"].data_ptr(), gr["f_dc"].data_ptr()
+        a.grad_f_rest = gr["f_rest"].data_ptr() if "f_rest" in gr else None
+        a.grad_opacity, a.grad_scaling, a.grad_rotation = gr["opacity"].data_ptr(), gr["scaling"].data_ptr(), gr["rotation"].data_ptr()
+        a.xyz_gradient_accum, a.denom, a.max_radii2D = self.xyz_gradient_accum.data_ptr(), self.denom.data_ptr(), self.max_radii2D.data_ptr()
+        a.loss_total, a.scratch, a.scratch_bytes = self.loss_total.data_ptr(), self.scratch.data_ptr(), self.scratch.numel()
+        return a
+
+    def _ensure_capacity(self, view: MapView):
+        """First use: one synchronous preprocess to learn num_rendered; capacity = headroom x that (shared by all views,
+        which are processed one after the other on the stream)."""
+        if self.ws is not None:
+            return
+        from .rasterizer import make_view, _stream
+        L, lib = self.L, self.lib
+        with torch.no_grad():
+            op = torch.sigmoid(self.params["opacity"]).contiguous()
+            sc = torch.exp(self.params["scaling"]).contiguous()
+            if self.isotropic: sc = sc.repeat(1, 3).contiguous()
+            rot = torch.nn.functional.normalize(self.params["rotation"]).contiguous()
+            shs = (torch.cat((self.params["f_dc"], self.params["f_rest"]), dim=1).contiguous() if "f_rest" in self.params
+                   else self.params["f_dc"])
+        keep = []
+        v = make_view(view.settings._replace(sh_degree=self.sh_degree), self.M, keep)
+        base = lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, 0)
+        tmp = torch.empty(base, device=self.dev, dtype=torch.uint8)
+        radii = torch.zeros(self.P, device=self.dev, dtype=torch.int32)
+        n_host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        L.check(lib.mgs_raster_preprocess(C.byref(v), self.P, L.ptr(self.params["xyz"]), L.ptr(op), L.ptr(shs), None, L.ptr(sc),
+                                          L.ptr(rot), None, L.ptr(radii), L.ptr(tmp), tmp.numel(),
+                                          C.c_void_p(n_host.data_ptr()), _stream()), "mgs_raster_preprocess")
+        torch.cuda.current_stream().synchronize()
+        self.R_cap = max(int(int(n_host.item()) * self.headroom) + 4096, 4096)
+        self.ws = torch.empty(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev, dtype=torch.uint8)
+
+    def _slot(self, i):
+        """Per-view output buffers (kept across iterations: the same window is mapped many times)."""
+        s = self._slots.get(i)
+        if s is None:
+            s = self._slots[i] = MapViewResult(torch.zeros(self.P, device=self.dev, dtype=torch.int32),
+                                               torch.zeros(self.P, device=self.dev, dtype=torch.int32),
+                                               torch.zeros(6, device=self.dev), torch.zeros(2, device=self.dev),
+                                               torch.zeros(1, device=self.dev))
+        return s
+
+    def render_backward_view(self, args, view: MapView, slot: MapViewResult):
+        from .rasterizer import make_view, _stream
+        L = self.L
+        mv = L.MgsMapView()
+        keep = []
+        mv.view = make_view(view.settings._replace(sh_degree=self.sh_degree), self.M, keep)
+        self._keep.append(keep)
+        mv.gt_image = view.gt_image.data_ptr()
+        mv.gt_depth = view.gt_depth.data_ptr() if view.gt_depth is not None else None
+        mv.exposure_a = view.exposure_a.data_ptr() if view.exposure_a is not None else None
+        mv.exposure_b = view.exposure_b.data_ptr() if view.exposure_b is not None else None
+        mv.rgb_boundary_threshold, mv.alpha, mv.update_stats = self.thr, self.alpha, int(view.update_stats)
+        mv.out_color, mv.out_depth, mv.out_opacity = self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr()
+        mv.radii, mv.n_touched = slot.radii.data_ptr(), slot.n_touched.data_ptr()
+        mv.tau, mv.dab, mv.loss = slot.tau.data_ptr(), slot.dab.data_ptr(), slot.loss.data_ptr()
+        mv.workspace, mv.workspace_bytes, mv.R_cap = self.ws.data_ptr(), self.ws.numel(), self.R_cap
+        L.check(self.lib.mgs_map_view_fwd_bwd(C.byref(args), C.byref(mv), _stream()), "mgs_map_view_fwd_bwd")
+
+    def backward_only(self, views: Sequence[MapView]) -> Dict[int, MapViewResult]:
+        """Everything of an iteration up to the raw-parameter gradients of THIS rank's views (no exchange, no Adam)."""
+        from .rasterizer import _stream
+        L = self.L
+        for p, v in zip(self.arena.params, self.arena.views):
+            p.grad = v
+        self._keep = []
+        args = self._args()
+        self._ensure_capacity(views[0])
+        L.check(self.lib.mgs_map_begin(C.byref(args), _stream()), "mgs_map_begin")
+        out = {}
+        for i in shard_views(len(views), self.world, self.rank):
+            slot = self._slot(i)
+            self.render_backward_view(args, views[i], slot)
+            out[i] = slot
+        L.check(self.lib.mgs_map_end(C.byref(args), int(self.rank == 0), self.reg_weight, _stream()), "mgs_map_end")
+        return out
+
+    def step(self, views: Sequence[MapView]):
+        """One data-parallel mapping iteration.  Returns (total loss f32[1] on the device, {view index: MapViewResult})."""
+        out = self.backward_only(views)
+        if self.distributed and self.world > 1:
+            dist.all_reduce(self.arena.flat, op=dist.ReduceOp.SUM, group=self.group)   # the single exchange of the path
+            dist.all_reduce(self.loss_total, op=dist.ReduceOp.SUM, group=self.group)
+        self.opt.step()
+        return self.loss_total, out
+
+    def sync_stats(self):
+        """Side channels needed only before densify / prune: sum of the locally accumulated
+        statistics, max of the radii."""
+        if self.distributed and self.world > 1:
+            dist.all_reduce(self.xyz_gradient_accum, op=dist.ReduceOp.SUM, group=self.group)
+            dist.all_reduce(self.denom, op=dist.ReduceOp.SUM, group=self.group)
+            dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=self.group)
+
+    def check_capacity(self):
+        """Synchronous check of the device-side overflow flag of the last rendered view; regrows on overflow."""
+        from .rasterizer import _stream
+        n, ov = C.c_int32(0), C.c_int32(0)
+        self.L.check(self.lib.mgs_raster_query(self.L.ptr(self.ws), C.byref(n), C.byref(ov), _stream()), "mgs_raster_query")
+        if ov.value:
+            self.headroom *= 1.5
+            self.ws = None
+        return n.value, bool(ov.value)

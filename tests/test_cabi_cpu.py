@@ -53,7 +53,8 @@ def test_ctypes_table_matches_header():
 def test_struct_layouts_match_header_field_order():
     L = _lib()
     src = open(HEADER).read()
-    for cname, cls in (("mgs_view", L.MgsView), ("mgs_loss_args", L.MgsLossArgs), ("mgs_adam_group", L.MgsAdamGroup)):
+    for cname, cls in (("mgs_view", L.MgsView), ("mgs_loss_args", L.MgsLossArgs), ("mgs_adam_group", L.MgsAdamGroup),
+                       ("mgs_gaussians", L.MgsGaussians), ("mgs_map_args", L.MgsMapArgs), ("mgs_map_view", L.MgsMapView)):
         body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (cname, cname), src, flags=re.S).group(1)
         body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
         names = []

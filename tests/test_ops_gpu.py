@@ -115,3 +115,33 @@ def test_fused_track_iteration_matches_composed_entry_points(mode, use_depth):
     assert U.rel_err(T0, T1) <= 1e-4 and U.rel_err(p0, p1) <= 1e-3 and U.rel_err(c0, c1) <= 1e-3
     assert U.rel_err(tau0, tau1) <= 2e-3
     assert l0[-1] < l0[0]
+
+
+@pytest.mark.parametrize("mode,use_depth", [(1, False), (0, False), (0, True)])
+def test_single_pass_blend_matches_two_pass_first_step(mode, use_depth):
+    """The single-pass tracking blend (blend_track.cu: forward-order accumulators, tangent contracted in the epilogue)
+    against the two-pass path built from the parity-tested entry points (forward, fused loss, pose-only backward), one
+    step from the same state, exact exponent in both: images identical, loss and pose tangent to 1e-4."""
+    from monogs_b200 import scene as S, rasterizer as RZ
+    from monogs_b200.tracking import PoseTracker
+    sc, cam = U.small_case("dense", T_w2c=torch.eye(4))
+    sc = sc._replace(shs=sc.shs[:, :1].contiguous(), sh_degree=0)     # SH degree 0: the single-pass kernel's domain
+    scd = U.to_dev(sc)
+    bg = torch.tensor([0.05, 0.1, 0.15]).cuda()
+    T_gt = S.se3_exp(torch.tensor(S.GT_TAU)).float()
+    cam_gt = U.to_dev(S.make_camera(cam.W, cam.H, cam.fx, cam.fy, cam.cx, cam.cy, T_gt))
+    gt, _, gt_depth, _, _, _ = RZ.raster_forward(U.settings(cam_gt, bg, 0), scd.means3D, scd.opacities, scd.shs, None,
+                                                 scd.scales, scd.rotations, None)
+    out = []
+    for fused in (True, False):
+        tr = PoseTracker(scd.means3D, scd.opacities, scd.shs, scd.scales, scd.rotations, 0, cam, bg, torch.eye(4),
+                         mode=mode, use_depth=use_depth, use_graph=False, fused=fused, fast_math=False)
+        tr.set_frame(gt, gt_depth=gt_depth if use_depth else None)
+        tr.step()
+        torch.cuda.synchronize()
+        out.append((tr.loss.clone(), tr.tau.clone(), tr.dab.clone(), tr.color.clone(), tr.depth.clone(), tr.n_touched.clone()))
+    (l0, t0, d0, c0, z0, n0), (l1, t1, d1, c1, z1, n1) = out
+    assert torch.equal(c0, c1) and torch.equal(z0, z1) and torch.equal(n0, n1)
+    assert U.rel_err(l0, l1) <= 1e-5
+    assert U.rel_err(t0, t1) <= 1e-4, (t0, t1)
+    assert U.rel_err(d0, d1) <= 1e-4
