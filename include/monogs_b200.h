@@ -275,6 +275,42 @@ int mgs_map_view_fwd_bwd(const mgs_map_args* args, const mgs_map_view* view, voi
  * weight * mean|s - mean(s)| once (weight = 10 in the reference). */
 int mgs_map_end(const mgs_map_args* args, int32_t add_regulariser, float regulariser_weight, void* stream);
 
+/* ---- densify / clone / split / prune of the parameter arena together with its Adam moments.
+ *      Replaces GaussianModel.densify_and_prune / densify_and_clone / densify_and_split / prune_points and the optimizer
+ *      surgery of cat_tensors_to_optimizer / _prune_optimizer (gaussian_splatting/scene/gaussian_model.py:470-691).
+ *      mgs_densify_plan decides per source Gaussian and scans; the host reads the four totals (the new size is needed
+ *      to allocate), then mgs_densify_apply writes the final arena
+ *          [kept originals | clones | children rep 0 | .. | children rep n_split-1]        (each in source order)
+ *      which is the order the reference's cat / boolean-mask sequence produces.  New points get zero Adam moments. ---- */
+typedef struct mgs_densify_cfg {
+  int32_t mode;            /* 0: densify_and_prune(max_grad, min_opacity, extent, max_screen_size); 1: prune_points(mask) */
+  int32_t n_split;         /* N of densify_and_split (2) */
+  float grad_threshold;    /* max_grad */
+  float min_opacity;
+  float extent;
+  float percent_dense;     /* 0.01 */
+  float max_screen_size;   /* 0 = None: the world-size prune (max scale > 0.1 extent) is applied only when non-zero */
+} mgs_densify_cfg;
+
+typedef struct mgs_gaussian_state {   /* arrays in the order xyz, f_dc, f_rest, opacity, scaling, rotation */
+  float* param[6];
+  float* exp_avg[6];       /* Adam moments; entries may be null (no optimizer state yet) */
+  float* exp_avg_sq[6];
+  int32_t* unique_kfIDs;   /* i32[P], optional */
+  int32_t* n_obs;          /* i32[P], optional */
+} mgs_gaussian_state;
+
+size_t mgs_densify_scratch_bytes(int32_t P);
+/* totals_out (device or pinned host i32[4], written by an async copy on `stream`):
+ * [0] kept originals, [1] clones, [2] children PER REPETITION, [3] split-selected Gaussians (rows of noise per repetition).
+ * New size = totals[0] + totals[1] + n_split * totals[2].  xyz_gradient_accum may be null (no gradient statistics). */
+int mgs_densify_plan(const mgs_gaussians* g, const float* xyz_gradient_accum, const float* denom, const uint8_t* prune_mask,
+                     const mgs_densify_cfg* cfg, void* scratch, size_t scratch_bytes, int32_t* totals_out, void* stream);
+/* noise: f32[n_split * totals[3], 3] standard-normal draws, row r * totals[3] + k for repetition r of the k-th selected
+ * Gaussian (the layout of `samples` at gaussian_model.py:612-614); may be null when totals[3] == 0 or mode == 1. */
+int mgs_densify_apply(const mgs_gaussians* g, const mgs_gaussian_state* src, const mgs_gaussian_state* dst,
+                      const mgs_densify_cfg* cfg, const float* noise, const void* scratch, size_t scratch_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

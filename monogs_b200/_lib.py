@@ -92,6 +92,20 @@ class MgsMapView(C.Structure):
     ]
 
 
+class MgsDensifyCfg(C.Structure):
+    _fields_ = [
+        ("mode", C.c_int32), ("n_split", C.c_int32), ("grad_threshold", C.c_float), ("min_opacity", C.c_float),
+        ("extent", C.c_float), ("percent_dense", C.c_float), ("max_screen_size", C.c_float),
+    ]
+
+
+class MgsGaussianState(C.Structure):
+    _fields_ = [
+        ("param", C.c_void_p * 6), ("exp_avg", C.c_void_p * 6), ("exp_avg_sq", C.c_void_p * 6),
+        ("unique_kfIDs", C.c_void_p), ("n_obs", C.c_void_p),
+    ]
+
+
 _P, _I32, _I64, _U32, _F, _SZ = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_float, C.c_size_t
 _VP = C.POINTER(MgsView)
 
@@ -122,6 +136,10 @@ SIGNATURES = {
     "mgs_track_scratch_bytes": (_SZ, [_I32, _I32, _I32]),
     "mgs_track_iteration": (C.c_int, [C.POINTER(MgsTrackArgs), _P]),
     "mgs_pose_update": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _F, _P]),
+    "mgs_densify_scratch_bytes": (_SZ, [_I32]),
+    "mgs_densify_plan": (C.c_int, [C.POINTER(MgsGaussians), _P, _P, _P, C.POINTER(MgsDensifyCfg), _P, _SZ, _P, _P]),
+    "mgs_densify_apply": (C.c_int, [C.POINTER(MgsGaussians), C.POINTER(MgsGaussianState), C.POINTER(MgsGaussianState),
+                                    C.POINTER(MgsDensifyCfg), _P, _P, _SZ, _P]),
     "mgs_map_scratch_bytes": (_SZ, [_I32, _I32, _I32, _I32]),
     "mgs_map_begin": (C.c_int, [C.POINTER(MgsMapArgs), _P]),
     "mgs_map_view_fwd_bwd": (C.c_int, [C.POINTER(MgsMapArgs), C.POINTER(MgsMapView), _P]),

@@ -27,7 +27,9 @@ class GradArena:
 
     def __init__(self, params: Sequence[torch.Tensor]):
         self.params = list(params)
-        n = sum(p.numel() for p in self.params)
+        # every view starts on a 16-byte boundary: the kernels read / write [P,4] rows as float4
+        pad4 = lambda n: (n + 3) // 4 * 4
+        n = sum(pad4(p.numel()) for p in self.params)
         dev = self.params[0].device if self.params else "cpu"
         self.flat = torch.zeros(n, device=dev, dtype=torch.float32)
         self.views = []
@@ -35,7 +37,7 @@ class GradArena:
         for p in self.params:
             v = self.flat[off:off + p.numel()].view(p.shape)
             self.views.append(v)
-            off += p.numel()
+            off += pad4(p.numel())
 
     def attach(self):
         """Zero the arena and (re)install the aliases; call before the backward passes of an iteration."""
@@ -137,6 +139,7 @@ class MapEngine:
             assert p.is_contiguous() and p.dtype == torch.float32 and p.device == self.dev
         self.arena = GradArena(list(self.params.values()))
         self.grads = dict(zip(self.params.keys(), self.arena.views))
+        self.lrs = dict(lrs)
         self.opt = FusedAdam([{"params": [p], "lr": lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15)
         f = dict(device=self.dev, dtype=torch.float32)
         self.xyz_gradient_accum, self.denom = torch.zeros(self.P, **f), torch.zeros(self.P, **f)
@@ -271,3 +274,52 @@ class MapEngine:
             self.headroom *= 1.5
             self.ws = None
         return n.value, bool(ov.value)
+
+    # ------------------------------------------------------------------------------------------------
+    def _adam_moments(self):
+        m, v = {}, {}
+        for k, p in self.params.items():
+            st = self.opt.state.get(p)
+            m[k] = st["exp_avg"] if st is not None else torch.zeros_like(p)
+            v[k] = st["exp_avg_sq"] if st is not None else torch.zeros_like(p)
+        return m, v
+
+    def _adopt(self, out):
+        """Install the arrays a densify / prune produced: parameters, Adam moments (step counts carried over, like the
+        reference's replace-in-place of optimizer.state), a fresh gradient arena, zeroed statistics
+        (densification_postfix, gaussian_model.py:592-594), re-sized scratch; the instance capacity is re-estimated."""
+        from .ops import FusedAdam
+        steps = {k: (self.opt.state[p]["step"] if p in self.opt.state else 0) for k, p in self.params.items()}
+        self.params = {k: out["params"][k] for k in self.params}
+        self.P = self.params["xyz"].size(0)
+        self.arena = GradArena(list(self.params.values()))
+        self.grads = dict(zip(self.params.keys(), self.arena.views))
+        self.opt = FusedAdam([{"params": [p], "lr": self.lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15)
+        for k, p in self.params.items():
+            if steps[k] > 0:
+                self.opt.state[p] = dict(step=steps[k], exp_avg=out["exp_avg"][k], exp_avg_sq=out["exp_avg_sq"][k])
+        f = dict(device=self.dev, dtype=torch.float32)
+        self.xyz_gradient_accum, self.denom = torch.zeros(self.P, **f), torch.zeros(self.P, **f)
+        self.max_radii2D = torch.zeros(self.P, **f)
+        self.scratch = torch.empty(self.lib.mgs_map_scratch_bytes(self.P, self.M, self.W, self.H), device=self.dev, dtype=torch.uint8)
+        self.ws, self._slots = None, {}
+
+    def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, percent_dense=0.01, unique_kfIDs=None,
+                          n_obs=None, noise=None, generator=None):
+        """GaussianModel.densify_and_prune on the engine's arena (gaussian_model.py:676-691).  Call sync_stats() first
+        in a data-parallel group, and draw from identically seeded generators on every rank."""
+        from . import densify as DZ
+        m, v = self._adam_moments()
+        out = DZ.densify_and_prune(self.params, m, v, self.xyz_gradient_accum, self.denom, max_grad, min_opacity, extent,
+                                   max_screen_size, percent_dense=percent_dense, unique_kfIDs=unique_kfIDs, n_obs=n_obs,
+                                   noise=noise, generator=generator)
+        self._adopt(out)
+        return out
+
+    def prune_points(self, mask, unique_kfIDs=None, n_obs=None):
+        """GaussianModel.prune_points(mask) on the engine's arena (gaussian_model.py:512-527)."""
+        from . import densify as DZ
+        m, v = self._adam_moments()
+        out = DZ.prune_points(self.params, m, v, mask, unique_kfIDs=unique_kfIDs, n_obs=n_obs)
+        self._adopt(out)
+        return out

@@ -132,3 +132,34 @@ def test_map_engine_step_reduces_loss():
         total, _ = eng.step(views)
         losses.append(float(total))
     assert losses[-1] < losses[0]
+
+
+def test_map_engine_densify_between_steps():
+    """Statistics gathered by the views drive densify_and_prune on the arena; moments of surviving Gaussians are carried
+    over, new ones start at zero, and mapping continues on the resized arena."""
+    from monogs_b200.mapping import MapEngine
+    sc, cam = U.small_case("dense")
+    p = {k: v.detach().clone() for k, v in _raw_params(sc).items()}
+    views = _views(sc, cam, 3, False, False)
+    lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "f_rest": 2.5e-3 / 20, "opacity": 0.05, "scaling": 1e-3, "rotation": 1e-3}
+    eng = MapEngine(p, lrs, sh_degree=sc.sh_degree, W=cam.W, H=cam.H)
+    for _ in range(3):
+        eng.step(views)
+    P0 = eng.P
+    assert float(eng.denom.max()) == 6.0      # two of the three views update the statistics, three iterations
+    m_before = eng.opt.state[eng.params["xyz"]]["exp_avg"].clone()
+    grads = eng.xyz_gradient_accum / eng.denom
+    thr = float(grads[~grads.isnan()].median())
+    out = eng.densify_and_prune(thr, 0.05, 6.0, 20.0, generator=torch.Generator(device="cuda").manual_seed(1))
+    c = out["counts"]
+    assert eng.P == c["kept"] + c["cloned"] + c["children"] and eng.P != P0 and c["cloned"] + c["children"] > 0
+    st = eng.opt.state[eng.params["xyz"]]
+    assert st["step"] == 3 and float(st["exp_avg"][c["kept"]:].abs().max()) == 0.0
+    assert float(st["exp_avg"][: c["kept"]].abs().sum()) > 0 and st["exp_avg"].size(0) == eng.P
+    assert float(eng.denom.sum()) == 0.0 and eng.max_radii2D.numel() == eng.P
+    l0 = float(eng.step(views)[0])
+    for _ in range(5):
+        l1 = float(eng.step(views)[0])
+    assert l1 < l0
+    assert not eng.check_capacity()[1]
+    del m_before
