@@ -311,6 +311,31 @@ int mgs_densify_plan(const mgs_gaussians* g, const float* xyz_gradient_accum, co
 int mgs_densify_apply(const mgs_gaussians* g, const mgs_gaussian_state* src, const mgs_gaussian_state* dst,
                       const mgs_densify_cfg* cfg, const float* noise, const void* scratch, size_t scratch_bytes, void* stream);
 
+/* ---- per-frame image preprocessing and covisibility bookkeeping ---- */
+/* Exact lower median (torch.median) of n floats by radix select on the float bits; NaNs are skipped; device result. */
+size_t mgs_median_scratch_bytes(void);
+int mgs_median(const float* x, int64_t n, float* out /* device f32[1] */, void* scratch, size_t scratch_bytes, void* stream);
+/* get_median_depth (utils/slam_utils.py:286-297): median of depth over depth > 0 [and opacity > 0.95] [and mask != 0];
+ * opacity / mask / n_valid_out may be null.  NaN when nothing is valid. */
+int mgs_median_depth(const float* depth, const float* opacity, const float* mask, int64_t n, float* out, int32_t* n_valid_out,
+                     void* scratch, size_t scratch_bytes, void* stream);
+/* sqrt(gv^2 + gh^2) of the Scharr gradients of mean_c(image), zero where the 3x3 neighbourhood of |gray| > eps is not
+ * full (image_gradient + image_gradient_mask, utils/slam_utils.py:7-41; Camera.compute_grad_mask, camera_utils.py:110-118). */
+int mgs_frame_grad_intensity(const float* image /* f32[C,H,W] */, int32_t C, int32_t H, int32_t W, float eps,
+                             float* intensity /* f32[H,W] */, void* stream);
+/* Camera.compute_grad_mask (utils/camera_utils.py:110-142): grad_mask = intensity > median * edge_threshold (global median;
+ * patch_median != 0: per 32x32 patch as for Replica), rgb_pixel_mask = (sum_c image > thr) * grad_mask,
+ * rgb_pixel_mask_mapping = (sum_c image > thr).  Masks are f32[1,H,W] of 0/1; the last two may be null.
+ * scratch: mgs_median_scratch_bytes() + 256 bytes. */
+int mgs_frame_masks(const float* image /* f32[3,H,W] */, int32_t H, int32_t W, float edge_threshold, float rgb_boundary_threshold,
+                    int32_t patch_median, float* intensity_scratch /* f32[H,W] */, float* grad_mask, float* rgb_pixel_mask,
+                    float* rgb_pixel_mask_mapping, void* scratch, size_t scratch_bytes, void* stream);
+/* bits[w] bit b = n_touched[32 w + b] > 0 (occ_aware_visibility, utils/slam_backend.py:251-255); u32[(P+31)/32]. */
+int mgs_visibility_pack(int32_t P, const int32_t* n_touched, uint32_t* bits, void* stream);
+/* out i32[K+1,3]: row k < K = (|cur & kf_k|, |cur | kf_k|, |kf_k|), row K = (|cur|, 0, 0): the counts behind is_keyframe /
+ * add_to_window / the mapping overlap check (utils/slam_frontend.py:1713-1741, 1918-1932).  kf_bits is u32[K, words]. */
+int mgs_covisibility(int32_t P, const uint32_t* cur_bits, int32_t K, const uint32_t* kf_bits, int32_t* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -136,6 +136,13 @@ SIGNATURES = {
     "mgs_track_scratch_bytes": (_SZ, [_I32, _I32, _I32]),
     "mgs_track_iteration": (C.c_int, [C.POINTER(MgsTrackArgs), _P]),
     "mgs_pose_update": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _F, _P]),
+    "mgs_median_scratch_bytes": (_SZ, []),
+    "mgs_median": (C.c_int, [_P, _I64, _P, _P, _SZ, _P]),
+    "mgs_median_depth": (C.c_int, [_P, _P, _P, _I64, _P, _P, _P, _SZ, _P]),
+    "mgs_frame_grad_intensity": (C.c_int, [_P, _I32, _I32, _I32, _F, _P, _P]),
+    "mgs_frame_masks": (C.c_int, [_P, _I32, _I32, _F, _F, _I32, _P, _P, _P, _P, _P, _SZ, _P]),
+    "mgs_visibility_pack": (C.c_int, [_I32, _P, _P, _P]),
+    "mgs_covisibility": (C.c_int, [_I32, _P, _I32, _P, _P, _P]),
     "mgs_densify_scratch_bytes": (_SZ, [_I32]),
     "mgs_densify_plan": (C.c_int, [C.POINTER(MgsGaussians), _P, _P, _P, C.POINTER(MgsDensifyCfg), _P, _SZ, _P, _P]),
     "mgs_densify_apply": (C.c_int, [C.POINTER(MgsGaussians), C.POINTER(MgsGaussianState), C.POINTER(MgsGaussianState),
