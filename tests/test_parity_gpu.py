@@ -259,9 +259,9 @@ def test_mark_visible_and_knn():
     assert U.rel_err(distCUDA2(pts.cuda()), G.knn_dist2(pts)) <= 1e-6
 
 
-@pytest.mark.parametrize("cfg", ["C1", "C2"])
+@pytest.mark.parametrize("cfg", ["C1", "C2", "C3", "C5"])
 def test_full_size_configs_vs_reference(cfg):
-    """BASELINE.json configs 1 and 2 at full size against the reference build."""
+    """BASELINE.json configs 1, 2, 3 and 5 (2M Gaussians, 1920x1080, SH degree 3) at full size against the reference build."""
     from monogs_b200 import scene as S
     sc, cam = S.make_config(cfg)
     gc, gd = S.output_grads(cam.W, cam.H)
