@@ -61,21 +61,27 @@ map_activate_kernel(const mgs_gaussians g, const MapScratch m, float* __restrict
   const float4 q = reinterpret_cast<const float4*>(g.rotation_raw)[idx];
   const float nrm = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);   // F.normalize eps
   reinterpret_cast<float4*>(m.act_rot)[idx] = make_float4(q.x / nrm, q.y / nrm, q.z / nrm, q.w / nrm);
-  const int M = g.sh_coeffs;
-  if (M > 1) {   // get_features = cat(f_dc, f_rest) (gaussian_model.py:89-93)
-    float* dst = m.act_shs + (size_t)idx * M * 3;
-    float* dz = m.d_shs + (size_t)idx * M * 3;
-    dst[0] = g.f_dc[3 * idx]; dst[1] = g.f_dc[3 * idx + 1]; dst[2] = g.f_dc[3 * idx + 2];
-    const float* rest = g.f_rest + (size_t)idx * (M - 1) * 3;
-    for (int k = 0; k < 3 * (M - 1); k++) dst[3 + k] = rest[k];
-    for (int k = 0; k < 3 * M; k++) dz[k] = 0.f;
-  } else {
+  if (g.sh_coeffs == 1) {   // M > 1: sh_cat_kernel + a memset of the SH gradient accumulator
     grad_f_dc[3 * idx] = 0.f; grad_f_dc[3 * idx + 1] = 0.f; grad_f_dc[3 * idx + 2] = 0.f;
   }
   grad_xyz[3 * idx] = 0.f; grad_xyz[3 * idx + 1] = 0.f; grad_xyz[3 * idx + 2] = 0.f;
   m.d_opacity[idx] = 0.f;
   m.d_scales[3 * idx] = 0.f; m.d_scales[3 * idx + 1] = 0.f; m.d_scales[3 * idx + 2] = 0.f;
   reinterpret_cast<float4*>(m.d_rot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+// get_features = cat(f_dc, f_rest) (gaussian_model.py:89-93) and its inverse for the gradient, one thread per float so
+// that both sides of the copy are coalesced (a per-Gaussian loop strides 12*M bytes between neighbouring threads)
+template <bool SPLIT>
+__global__ void __launch_bounds__(256)
+sh_cat_kernel(const size_t n /* P*M*3 */, const int M, float* __restrict__ cat, float* __restrict__ f_dc, float* __restrict__ f_rest) {
+  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= n) return;
+  const size_t row = e / (size_t)(3 * M);
+  const int k = (int)(e - row * (size_t)(3 * M));
+  float* part = k < 3 ? f_dc + row * 3 + k : f_rest + row * (size_t)(3 * (M - 1)) + (k - 3);
+  if (SPLIT) *part = cat[e];
+  else cat[e] = *part;
 }
 
 // per-view loss from the per-tile partial sums of the forward epilogue (get_loss_mapping_rgb / _rgbd)
@@ -137,13 +143,6 @@ map_end_kernel(const mgs_gaussians g, const MapScratch m, float* __restrict__ gr
     const float yd = y.x * d.x + y.y * d.y + y.z * d.z + y.w * d.w;
     reinterpret_cast<float4*>(grad_rotation)[idx] =
         make_float4((d.x - y.x * yd) / nrm, (d.y - y.y * yd) / nrm, (d.z - y.z * yd) / nrm, (d.w - y.w * yd) / nrm);
-    const int M = g.sh_coeffs;
-    if (M > 1) {   // split the SH gradient back into its two parameters
-      const float* src = m.d_shs + (size_t)idx * M * 3;
-      grad_f_dc[3 * idx] = src[0]; grad_f_dc[3 * idx + 1] = src[1]; grad_f_dc[3 * idx + 2] = src[2];
-      float* rest = grad_f_rest + (size_t)idx * (M - 1) * 3;
-      for (int k = 0; k < 3 * (M - 1); k++) rest[k] = src[3 + k];
-    }
   }
   if (reg_weight != 0.f) {   // uniform branch
     __shared__ float part[8];
@@ -196,6 +195,14 @@ int mgs_map_begin(const mgs_map_args* a, void* stream) {
   if (P == 0) { MGS_CUDA_TRY(cudaMemsetAsync(a->loss_total, 0, sizeof(float), s)); return MGS_OK; }
   MGS_PROF("map_activate", s, map_activate_kernel<<<(P + 255) / 256, 256, 0, s>>>(a->g, m, a->grad_xyz, a->grad_f_dc, a->loss_total));
   MGS_LAUNCH_CHECK();
+  const int M = a->g.sh_coeffs;
+  if (M > 1) {
+    const size_t n = (size_t)P * M * 3;
+    MGS_PROF("sh_cat", s, sh_cat_kernel<false><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(
+        n, M, m.act_shs, const_cast<float*>(a->g.f_dc), const_cast<float*>(a->g.f_rest)));
+    MGS_LAUNCH_CHECK();
+    MGS_CUDA_TRY(cudaMemsetAsync(m.d_shs, 0, n * sizeof(float), s));
+  }
   return MGS_OK;
 }
 
@@ -272,6 +279,12 @@ int mgs_map_end(const mgs_map_args* a, int32_t add_regulariser, float regularise
                                                                        a->grad_scaling, a->grad_rotation,
                                                                        add_regulariser ? regulariser_weight : 0.f, a->loss_total));
   MGS_LAUNCH_CHECK();
+  const int M = a->g.sh_coeffs;
+  if (M > 1) {   // split the SH gradient back into its two parameters
+    const size_t n = (size_t)P * M * 3;
+    MGS_PROF("sh_split", s, sh_cat_kernel<true><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, M, m.d_shs, a->grad_f_dc, a->grad_f_rest));
+    MGS_LAUNCH_CHECK();
+  }
   return MGS_OK;
 }
 
