@@ -48,7 +48,8 @@ struct WsHeader {
   uint32_t num_rendered;   // last element of the inclusive scan (rasterizer_impl.cu:284)
   uint32_t overflow;       // 1 when num_rendered > R_cap
   uint32_t r_used;         // min(num_rendered, R_cap): instances actually binned
-  uint32_t pad[61];
+  uint32_t n_large;        // tiles whose list exceeds 1024 words; their ids are tile_ctr[i * TILE_CTR_STRIDE + 2], i < n_large
+  uint32_t pad[60];
 };
 static_assert(sizeof(WsHeader) == 256, "header is one 256-B slot");
 

@@ -290,23 +290,37 @@ preprocess_kernel(const ViewConst v, const int P,
 // instances are emitted in Gaussian-index order, so ties on (tile, depth) are ordered by index there too: the result
 // is the same permutation, bit for bit.
 // ------------------------------------------------------------------------------------------------
-constexpr int SCAN_THREADS = 1024;
+constexpr int SCAN_THREADS = 1024, SCAN_IPT = 4, LARGE_LIST = 1024;
 __global__ void __launch_bounds__(SCAN_THREADS)
 tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_t R_cap,
                  uint2* __restrict__ ranges, WsHeader* __restrict__ hdr) {
   using Scan = cub::BlockScan<uint32_t, SCAN_THREADS>;
   __shared__ typename Scan::TempStorage tmp;
+  __shared__ uint32_t n_large;
+  if (threadIdx.x == 0) n_large = 0u;
+  __syncthreads();
   uint32_t carry = 0;
-  for (int base = 0; base < tiles; base += SCAN_THREADS) {
-    const int t = base + threadIdx.x;
-    const uint32_t c = t < tiles ? tile_ctr[(size_t)t * TILE_CTR_STRIDE] : 0u;
+  for (int base = 0; base < tiles; base += SCAN_THREADS * SCAN_IPT) {
+    const int t0 = base + threadIdx.x * SCAN_IPT;
+    uint32_t c[SCAN_IPT], sum = 0u;
+#pragma unroll
+    for (int i = 0; i < SCAN_IPT; i++) c[i] = t0 + i < tiles ? tile_ctr[(size_t)(t0 + i) * TILE_CTR_STRIDE] : 0u;
+#pragma unroll
+    for (int i = 0; i < SCAN_IPT; i++) sum += c[i];
     uint32_t excl, total;
-    Scan(tmp).ExclusiveSum(c, excl, total);
-    if (t < tiles) {
-      const uint32_t start = carry + excl;
-      ranges[t] = (c == 0u) ? make_uint2(0u, 0u)                                  // untouched tiles keep {0,0}
-                            : make_uint2(min(start, R_cap), min(start + c, R_cap));
-      tile_ctr[(size_t)t * TILE_CTR_STRIDE + 1] = start;
+    Scan(tmp).ExclusiveSum(sum, excl, total);
+    uint32_t start = carry + excl;
+#pragma unroll
+    for (int i = 0; i < SCAN_IPT; i++) {
+      const int t = t0 + i;
+      if (t < tiles) {
+        const uint32_t lo = min(start, R_cap), hi = min(start + c[i], R_cap);
+        ranges[t] = (c[i] == 0u) ? make_uint2(0u, 0u) : make_uint2(lo, hi);            // untouched tiles keep {0,0}
+        tile_ctr[(size_t)t * TILE_CTR_STRIDE + 1] = start;
+        if (hi - lo > (uint32_t)LARGE_LIST)
+          tile_ctr[(size_t)atomicAdd(&n_large, 1u) * TILE_CTR_STRIDE + 2] = (uint32_t)t;
+        start += c[i];
+      }
     }
     carry += total;
     __syncthreads();
@@ -315,6 +329,7 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
     hdr->num_rendered = carry;
     hdr->overflow = carry > R_cap ? 1u : 0u;
     hdr->r_used = carry > R_cap ? R_cap : carry;
+    hdr->n_large = n_large;
   }
 }
 
@@ -388,50 +403,61 @@ __device__ __noinline__ void sort_tile_regs(Temp& temp, const unsigned long long
   }
 }
 
-// Two launches cover the tiles: LARGE = false takes lists of up to 1024 words (few registers, 8 KB of shared memory,
-// full occupancy — the common case), LARGE = true the rest; a CTA whose tile belongs to the other launch exits at once.
+// Two launches cover the tiles.  LARGE = false: one CTA per tile, lists of up to 1024 words (few registers, 8 KB of
+// shared memory, full occupancy — the common case).  LARGE = true: a fixed grid walks the list of large tiles the scan
+// kernel compacted (tile_ctr[i * TILE_CTR_STRIDE + 2], i < header.n_large); with no large tile it costs an empty wave
+// of a few hundred CTAs instead of one CTA per tile.
 template <bool LARGE>
 __global__ void __launch_bounds__(256)
 tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ list,
                          const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                          const float4* __restrict__ rgb4, const float* __restrict__ colors_precomp,
-                         SplatRec* __restrict__ recs) {
+                         SplatRec* __restrict__ recs, const uint32_t* __restrict__ tile_ctr,
+                         const WsHeader* __restrict__ hdr) {
   using Temp = typename cub::BlockMergeSort<unsigned long long, 256, LARGE ? 16 : 4>::TempStorage;
   __shared__ Temp temp;
-  const uint2 range = ranges[blockIdx.x];
-  const int n = (int)(range.y - range.x);
-  if (n == 0 || (n > 1024) != LARGE) return;
-  unsigned long long* seg = list + range.x;
-  SplatRec* dst = recs + range.x;
   if (!LARGE) {
+    const uint2 range = ranges[blockIdx.x];
+    const int n = (int)(range.y - range.x);
+    if (n == 0 || n > LARGE_LIST) return;
+    unsigned long long* seg = list + range.x;
+    SplatRec* dst = recs + range.x;
     if (n <= 512) sort_tile_regs<2>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
     else sort_tile_regs<4>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
     return;
   }
-  if (n <= SORT_CAP) {
-    if (n <= 2048) sort_tile_regs<8>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
-    else sort_tile_regs<16>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
-    return;
-  }
-  int N = 1;
-  while (N < n) N <<= 1;
-  for (int k = 2; k <= N; k <<= 1) {
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      const bool mirror = (j == (k >> 1));
-      for (int q = threadIdx.x; q < (N >> 1); q += blockDim.x) {
-        const int lo = q & (j - 1), blk = (q - lo) << 1;   // block of 2j slots, offset lo inside its lower half
-        const int i = blk + lo;
-        const int p = mirror ? blk + 2 * j - 1 - lo : i + j;
-        if (p < n) {
-          const unsigned long long a = __ldcg(seg + i), b = __ldcg(seg + p);
-          if (a > b) { __stcg(seg + i, b); __stcg(seg + p, a); }
-        }
-      }
-      __syncthreads();
+  const uint32_t n_large = hdr->n_large;
+  for (uint32_t li = blockIdx.x; li < n_large; li += gridDim.x) {
+    const uint2 range = ranges[tile_ctr[(size_t)li * TILE_CTR_STRIDE + 2]];
+    const int n = (int)(range.y - range.x);
+    unsigned long long* seg = list + range.x;
+    SplatRec* dst = recs + range.x;
+    if (n <= SORT_CAP) {
+      if (n <= 2048) sort_tile_regs<8>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+      else sort_tile_regs<16>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+      __syncthreads();          // temp is reused by the next tile
+      continue;
     }
+    int N = 1;
+    while (N < n) N <<= 1;
+    for (int k = 2; k <= N; k <<= 1) {
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        const bool mirror = (j == (k >> 1));
+        for (int q = threadIdx.x; q < (N >> 1); q += blockDim.x) {
+          const int lo = q & (j - 1), blk = (q - lo) << 1;   // block of 2j slots, offset lo inside its lower half
+          const int i = blk + lo;
+          const int p = mirror ? blk + 2 * j - 1 - lo : i + j;
+          if (p < n) {
+            const unsigned long long a = __ldcg(seg + i), b = __ldcg(seg + p);
+            if (a > b) { __stcg(seg + i, b); __stcg(seg + p, a); }
+          }
+        }
+        __syncthreads();
+      }
+    }
+    for (int e = threadIdx.x; e < n; e += blockDim.x)
+      write_record(__ldcg(seg + e), dst + e, means2D, conic_opacity, rgb4, colors_precomp);
   }
-  for (int e = threadIdx.x; e < n; e += blockDim.x)
-    write_record(__ldcg(seg + e), dst + e, means2D, conic_opacity, rgb4, colors_precomp);
 }
 
 int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s) {
@@ -472,10 +498,12 @@ int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const
       ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<unsigned long long>(ws, L.list)));
   MGS_LAUNCH_CHECK();
 #define MGS_SORT_ARGS ws_ptr<uint2>(ws, L.ranges), ws_ptr<unsigned long long>(ws, L.list), ws_ptr<float2>(ws, L.means2D), \
-      ws_ptr<float4>(ws, L.conic_opacity), ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<SplatRec>(ws, L.records)
+      ws_ptr<float4>(ws, L.conic_opacity), ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<SplatRec>(ws, L.records),     \
+      ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<WsHeader>(ws, L.header)
   MGS_PROF("tile_sort_records", s, tile_sort_records_kernel<false><<<tiles, 256, 0, s>>>(MGS_SORT_ARGS));
   MGS_LAUNCH_CHECK();
-  MGS_PROF("tile_sort_records_large", s, tile_sort_records_kernel<true><<<tiles, 256, 0, s>>>(MGS_SORT_ARGS));
+  MGS_PROF("tile_sort_records_large", s,
+           tile_sort_records_kernel<true><<<tiles < 592 ? tiles : 592, 256, 0, s>>>(MGS_SORT_ARGS));
   MGS_LAUNCH_CHECK();
 #undef MGS_SORT_ARGS
   return MGS_OK;

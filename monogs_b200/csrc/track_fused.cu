@@ -31,51 +31,94 @@ struct TrackUpdateK {
   float *T, *view_out, *proj_out; const float* proj_raw; int* converged; float thr;
 };
 
+// One CTA.  Everything the serial tail needs is staged in shared memory by separate threads while the per-tile partials
+// are being reduced (a single thread chasing ~60 dependent global loads and stores costs an L2 round trip each), the
+// double-precision bias corrections are computed by another warp meanwhile, and the results go out in parallel.
 __global__ void __launch_bounds__(256) track_update_kernel(const TrackUpdateK k) {
-  __shared__ double sh[256][4];
+  __shared__ double red[8][4];
+  __shared__ float s_in[64];     // [0,6) tau_raw  [8,16) exp_avg  [16,24) exp_avg_sq  [24,32) params  [32,48) T  [48,64) proj_raw
+  __shared__ float s_out[72];    // [0,6) tau [6,8) dab [8,16) exp_avg [16,24) exp_avg_sq [24,32) params [32,48) T [48,64) view [64] loss
+  __shared__ float s_proj[16];
+  __shared__ float s_bc[2];
+  __shared__ int s_conv;
+  const int tid = threadIdx.x;
+  if (tid < 6) s_in[tid] = k.tau_raw[tid];
+  else if (tid >= 8 && tid < 16) s_in[tid] = k.exp_avg[tid - 8];
+  else if (tid >= 16 && tid < 24) s_in[tid] = k.exp_avg_sq[tid - 16];
+  else if (tid >= 24 && tid < 32) s_in[tid] = k.params[tid - 24];
+  else if (tid >= 32 && tid < 48) s_in[tid] = k.T[tid - 32];
+  else if (tid >= 48 && tid < 64) s_in[tid] = k.proj_raw ? k.proj_raw[tid - 48] : 0.f;
+  else if (tid == 64) {
+    const double t = (double)(k.step[0] + 1);
+    k.step[0] += 1;
+    s_bc[0] = (float)(1.0 - pow((double)k.beta1, t));
+    s_bc[1] = (float)sqrt(1.0 - pow((double)k.beta2, t));
+  }
   double acc[4] = {0, 0, 0, 0};
-  for (int i = threadIdx.x; i < k.tiles; i += 256)
+  const double2* p2 = reinterpret_cast<const double2*>(k.partials);
+#pragma unroll 4
+  for (int i = tid; i < k.tiles; i += 256) {
+    const double2 a = p2[2 * i], b = p2[2 * i + 1];
+    acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y;
+  }
 #pragma unroll
-    for (int q = 0; q < 4; q++) acc[q] += k.partials[(size_t)i * 4 + q];
+  for (int q = 0; q < 4; q++) {
 #pragma unroll
-  for (int q = 0; q < 4; q++) sh[threadIdx.x][q] = acc[q];
+    for (int o = 16; o > 0; o >>= 1) acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], o);
+    if ((tid & 31) == 0) red[tid >> 5][q] = acc[q];
+  }
   __syncthreads();
-  for (int o = 128; o > 0; o >>= 1) {
-    if (threadIdx.x < o)
+  if (tid == 0) {
+    double tot[4];
 #pragma unroll
-      for (int q = 0; q < 4; q++) sh[threadIdx.x][q] += sh[threadIdx.x + o][q];
-    __syncthreads();
-  }
-  if (threadIdx.x != 0) return;
-  float gscale = 1.f;
-  if (k.mode == MGS_LOSS_TRACK_HUBER) {
-    const float nrm = (float)sqrt(sh[0][0]);
-    k.loss[0] = k.scale * nrm;
-    gscale = nrm > 0.f ? k.scale / nrm : 0.f;
-  } else {
-    const double rgb = sh[0][0] / (3.0 * k.npix), dep = sh[0][3] / (double)k.npix;
-    k.loss[0] = (float)(k.scale * (k.use_depth ? k.alpha * rgb + (1.0 - k.alpha) * dep : rgb));
-  }
-  float g[8];
+    for (int q = 0; q < 4; q++) {
+      double t = 0;
 #pragma unroll
-  for (int i = 0; i < 6; i++) { g[i] = k.tau_raw[i] * gscale; k.tau[i] = g[i]; }
-  g[6] = (float)sh[0][1] * gscale; g[7] = (float)sh[0][2] * gscale;
-  k.dab[0] = g[6]; k.dab[1] = g[7];
-  // Adam (torch.optim.Adam, eps outside the bias-corrected sqrt) on [rho(3), theta(3), a, b]
-  const double t = (double)(k.step[0] + 1);
-  k.step[0] += 1;
-  const float bc1 = (float)(1.0 - pow((double)k.beta1, t)), bc2s = (float)sqrt(1.0 - pow((double)k.beta2, t));
+      for (int w = 0; w < 8; w++) t += red[w][q];
+      tot[q] = t;
+    }
+    float gscale = 1.f;
+    if (k.mode == MGS_LOSS_TRACK_HUBER) {
+      const float nrm = (float)sqrt(tot[0]);
+      s_out[64] = k.scale * nrm;
+      gscale = nrm > 0.f ? k.scale / nrm : 0.f;
+    } else {
+      const double rgb = tot[0] / (3.0 * k.npix), dep = tot[3] / (double)k.npix;
+      s_out[64] = (float)(k.scale * (k.use_depth ? k.alpha * rgb + (1.0 - k.alpha) * dep : rgb));
+    }
+    float g[8];
 #pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const float lr = k.lr[i < 3 ? 0 : (i < 6 ? 1 : i - 4)];
-    float m = k.exp_avg[i], v = k.exp_avg_sq[i];
-    m = m + (g[i] - m) * (1.f - k.beta1);
-    v = v * k.beta2 + (1.f - k.beta2) * g[i] * g[i];
-    const float denom = sqrtf(v) / bc2s + k.eps;
-    k.params[i] = k.params[i] - (lr / bc1) * (m / denom);
-    k.exp_avg[i] = m; k.exp_avg_sq[i] = v;
+    for (int i = 0; i < 6; i++) { g[i] = s_in[i] * gscale; s_out[i] = g[i]; }
+    g[6] = (float)tot[1] * gscale; g[7] = (float)tot[2] * gscale;
+    s_out[6] = g[6]; s_out[7] = g[7];
+    // Adam (torch.optim.Adam, eps outside the bias-corrected sqrt) on [rho(3), theta(3), a, b]
+    const float bc1 = s_bc[0], bc2s = s_bc[1];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const float lr = k.lr[i < 3 ? 0 : (i < 6 ? 1 : i - 4)];
+      float m = s_in[8 + i], v = s_in[16 + i];
+      m = m + (g[i] - m) * (1.f - k.beta1);
+      v = v * k.beta2 + (1.f - k.beta2) * g[i] * g[i];
+      const float denom = sqrtf(v) / bc2s + k.eps;
+      s_out[24 + i] = s_in[24 + i] - (lr / bc1) * (m / denom);
+      s_out[8 + i] = m; s_out[16 + i] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < 16; i++) s_out[32 + i] = s_in[32 + i];
+    pose_update_dev(s_out + 32, s_out + 24, s_out + 27, k.proj_raw ? s_in + 48 : nullptr, k.view_out ? s_out + 48 : nullptr,
+                    k.proj_out ? s_proj : nullptr, k.converged ? &s_conv : nullptr, k.thr);
   }
-  pose_update_dev(k.T, k.params, k.params + 3, k.proj_raw, k.view_out, k.proj_out, k.converged, k.thr);
+  __syncthreads();
+  if (tid < 6) k.tau[tid] = s_out[tid];
+  else if (tid < 8) k.dab[tid - 6] = s_out[tid];
+  else if (tid < 16) k.exp_avg[tid - 8] = s_out[tid];
+  else if (tid < 24) k.exp_avg_sq[tid - 16] = s_out[tid];
+  else if (tid < 32) k.params[tid - 24] = s_out[tid];
+  else if (tid < 48) k.T[tid - 32] = s_out[tid];
+  else if (tid < 64) { if (k.view_out) k.view_out[tid - 48] = s_out[tid]; }
+  else if (tid < 80) { if (k.view_out && k.proj_out && k.proj_raw) k.proj_out[tid - 64] = s_proj[tid - 64]; }
+  else if (tid == 80) k.loss[0] = s_out[64];
+  else if (tid == 81) { if (k.converged) k.converged[0] = s_conv; }
 }
 
 }  // namespace mgs

@@ -184,6 +184,38 @@ class PoseTracker:
                 self._enqueue()
         self.graph.replay()
 
+    def bind_host(self, gt_host, loss_host, tau_host):
+        """Host-resident frame in, loss + pose tangent out, one graph launch per iteration (step_host()).
+        gt_host [3,H,W], loss_host [1] and tau_host [6] are pinned host tensors.  The captured graph is
+            gt_image <- staging;  { the iteration's kernels  ||  staging <- gt_host on a second stream };
+            loss_host <- loss, tau_host <- tau
+        so every iteration moves one frame host -> device and its results device -> host, with the upload of the
+        NEXT iteration's frame hidden behind the current iteration's kernels: the contents of gt_host at replay k
+        are what iteration k+1 tracks against (the frame stays the same for the ~100 iterations of a tracking loop,
+        slam_frontend.py:455); bind_host() itself uploads the first frame."""
+        assert gt_host.is_pinned() and loss_host.is_pinned() and tau_host.is_pinned()
+        self._stage = torch.empty_like(self.gt_image)
+        self._stage.copy_(gt_host, non_blocking=True)
+        torch.cuda.synchronize()
+        side = torch.cuda.Stream()
+        self.host_graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.host_graph):
+            main = torch.cuda.current_stream()
+            self.gt_image.copy_(self._stage, non_blocking=True)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                self._stage.copy_(gt_host, non_blocking=True)
+            self._enqueue()
+            loss_host.copy_(self.loss, non_blocking=True)
+            tau_host.copy_(self.tau, non_blocking=True)
+            main.wait_stream(side)
+
+    def step_host(self, sync=True):
+        """One iteration of the host-bound pipeline set up by bind_host()."""
+        self.host_graph.replay()
+        if sync:
+            torch.cuda.current_stream().synchronize()
+
     def check_capacity(self):
         """Synchronous check of the device-side overflow flag; regrows the workspace if the splat count outgrew it."""
         n, ov = C.c_int32(0), C.c_int32(0)

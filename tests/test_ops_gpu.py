@@ -145,3 +145,42 @@ def test_single_pass_blend_matches_two_pass_first_step(mode, use_depth):
     assert U.rel_err(l0, l1) <= 1e-5
     assert U.rel_err(t0, t1) <= 1e-4, (t0, t1)
     assert U.rel_err(d0, d1) <= 1e-4
+
+
+def test_host_bound_tracking_pipeline_matches_device_steps():
+    """PoseTracker.bind_host / step_host (frame from pinned host memory, loss + tangent back to pinned host memory, one
+    graph launch per iteration with the next frame's upload beside the kernels) follows the device-resident step()
+    sequence exactly: same kernels on the same frame."""
+    from monogs_b200 import scene as S, rasterizer as RZ
+    from monogs_b200.tracking import PoseTracker
+    sc, cam = U.small_case("dense", T_w2c=torch.eye(4))
+    sc = sc._replace(shs=sc.shs[:, :1].contiguous(), sh_degree=0)
+    scd = U.to_dev(sc)
+    bg = torch.tensor([0.05, 0.1, 0.15]).cuda()
+    T_gt = S.se3_exp(torch.tensor(S.GT_TAU)).float()
+    cam_gt = U.to_dev(S.make_camera(cam.W, cam.H, cam.fx, cam.fy, cam.cx, cam.cy, T_gt))
+    gt, _, _, _, _, _ = RZ.raster_forward(U.settings(cam_gt, bg, 0), scd.means3D, scd.opacities, scd.shs, None, scd.scales,
+                                          scd.rotations, None)
+    mk = lambda: PoseTracker(scd.means3D, scd.opacities, scd.shs, scd.scales, scd.rotations, 0, cam, bg, torch.eye(4))
+    a = mk()
+    a.set_frame(gt)
+    dev_losses, dev_taus = [], []
+    for _ in range(6):
+        a.step()
+        dev_losses.append(float(a.loss)); dev_taus.append(a.tau.cpu().clone())
+    b = mk()
+    gt_host = gt.cpu().pin_memory()
+    loss_host, tau_host = torch.zeros(1).pin_memory(), torch.zeros(6).pin_memory()
+    b.bind_host(gt_host, loss_host, tau_host)
+    b.set_frame(b._stage)
+    for i in range(6):
+        b.step_host()
+        assert abs(float(loss_host) - dev_losses[i]) <= 1e-5 * abs(dev_losses[i]) + 1e-8, i
+        assert U.rel_err(tau_host, dev_taus[i]) <= 1e-3, i
+    assert U.rel_err(b.T, a.T) <= 1e-5
+    # a new frame written into the host buffer is what the iteration AFTER the next replay sees
+    gt_host.mul_(0.5)
+    b.step_host()
+    assert torch.equal(b._stage.cpu(), gt_host) and not torch.equal(b.gt_image.cpu(), gt_host)
+    b.step_host()
+    assert torch.equal(b.gt_image.cpu(), gt_host)
