@@ -92,9 +92,13 @@ blend_track_kernel(const int W, const int H, const int gx, const uint2* __restri
 
   bool done = !inside;
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
-  float E[6], A0[6], A1[6], A2[6], Ad[6], F0 = 0.f, F1 = 0.f, F2 = 0.f;
+  // The 6-vector accumulators live as three f32x2 register pairs each: the 54 multiply-adds per hit that build vp and
+  // fold it into E / A_ch issue as 27 packed FMUL2 / FFMA2 / FADD2 (sm_100 packed fp32; same IEEE operation per half,
+  // so the sums keep their bits).
+  float2 E2[3], A02[3], A12[3], A22[3], Ad2[3];
+  float F0 = 0.f, F1 = 0.f, F2 = 0.f;
 #pragma unroll
-  for (int k = 0; k < 6; k++) { E[k] = 0.f; A0[k] = 0.f; A1[k] = 0.f; A2[k] = 0.f; Ad[k] = 0.f; }
+  for (int k = 0; k < 3; k++) { E2[k] = A02[k] = A12[k] = A22[k] = Ad2[k] = make_float2(0.f, 0.f); }
 
   for (int i = 0; i < rounds; i++) {
     cp_async_wait_all();   // this thread's share of the Jacobians of batch i has landed
@@ -144,31 +148,41 @@ blend_track_kernel(const int W, const int H, const int gx, const uint2* __restri
           q[3] = -0.5f * gdx * dy * f;
           q[4] = -0.5f * gdy * dy * f;
           const float4* J4 = reinterpret_cast<const float4*>(jst + j * TRK_NF);
-          float Bf[TRK_NF];
+          float2 B2[TRK_NF / 2];   // row c of B = pairs 3c .. 3c+2
 #pragma unroll
-          for (int k = 0; k < TRK_NF / 4; k++) { const float4 t4 = J4[k]; Bf[4 * k] = t4.x; Bf[4 * k + 1] = t4.y; Bf[4 * k + 2] = t4.z; Bf[4 * k + 3] = t4.w; }
-          float vp[6];
+          for (int k = 0; k < TRK_NF / 4; k++) {
+            const float4 t4 = J4[k];
+            B2[2 * k] = make_float2(t4.x, t4.y); B2[2 * k + 1] = make_float2(t4.z, t4.w);
+          }
+          float2 vp2[3];
+          {
+            const float2 qq = make_float2(q[0], q[0]);
 #pragma unroll
-          for (int k = 0; k < 6; k++) vp[k] = q[0] * Bf[k];
+            for (int m = 0; m < 3; m++) vp2[m] = __fmul2_rn(qq, B2[m]);
+          }
 #pragma unroll
-          for (int c = 1; c < 5; c++)
+          for (int c = 1; c < 5; c++) {
+            const float2 qq = make_float2(q[c], q[c]);
 #pragma unroll
-            for (int k = 0; k < 6; k++) vp[k] = fmaf(q[c], Bf[c * 6 + k], vp[k]);
+            for (int m = 0; m < 3; m++) vp2[m] = __ffma2_rn(qq, B2[c * 3 + m], vp2[m]);
+          }
           const float w0 = fmaf(T, g2.x, C0), w1 = fmaf(T, g2.y, C1), w2 = fmaf(T, g2.z, C2);
+          const float2 w02 = make_float2(w0, w0), w12 = make_float2(w1, w1), w22 = make_float2(w2, w2);
 #pragma unroll
-          for (int k = 0; k < 6; k++) {
-            E[k] += vp[k];
-            A0[k] = fmaf(w0, vp[k], A0[k]);
-            A1[k] = fmaf(w1, vp[k], A1[k]);
-            A2[k] = fmaf(w2, vp[k], A2[k]);
+          for (int m = 0; m < 3; m++) {
+            E2[m] = __fadd2_rn(E2[m], vp2[m]);
+            A02[m] = __ffma2_rn(w02, vp2[m], A02[m]);
+            A12[m] = __ffma2_rn(w12, vp2[m], A12[m]);
+            A22[m] = __ffma2_rn(w22, vp2[m], A22[m]);
           }
           if (HAS_DEPTH) {
             const float aT = alpha * T;
             const float wd = fmaf(T, g0.z, D);
+            const float2 wd2 = make_float2(wd, wd);
 #pragma unroll
-            for (int k = 0; k < 6; k++) Ad[k] = fmaf(wd, vp[k], Ad[k]);
+            for (int m = 0; m < 3; m++) Ad2[m] = __ffma2_rn(wd2, vp2[m], Ad2[m]);
             // depth column of B: dz/dtau = (0, 0, 1, y_C, -x_C, 0)
-            F0 += aT; F1 = fmaf(aT, Bf[5 * 6 + 3], F1); F2 = fmaf(aT, Bf[5 * 6 + 4], F2);
+            F0 += aT; F1 = fmaf(aT, B2[16].y, F1); F2 = fmaf(aT, B2[17].x, F2);
           }
           C0 += g2.x * alpha * T;   // same expression as forward.cu:364-367 / blend_forward.cu: identical image bits
           C1 += g2.y * alpha * T;
@@ -194,6 +208,13 @@ blend_track_kernel(const int W, const int H, const int gx, const uint2* __restri
     out_opacity[pix] = 1 - T;
     float gi[3], gd;
     loss_pixel<true, true>(lk, (int)pix, img, D, 1 - T, loss_grad_scale, acc, gi, gd);
+    float E[6], A0[6], A1[6], A2[6], Ad[6];
+#pragma unroll
+    for (int m = 0; m < 3; m++) {
+      E[2 * m] = E2[m].x; E[2 * m + 1] = E2[m].y; A0[2 * m] = A02[m].x; A0[2 * m + 1] = A02[m].y;
+      A1[2 * m] = A12[m].x; A1[2 * m + 1] = A12[m].y; A2[2 * m] = A22[m].x; A2[2 * m + 1] = A22[m].y;
+      Ad[2 * m] = Ad2[m].x; Ad[2 * m + 1] = Ad2[m].y;
+    }
 #pragma unroll
     for (int k = 0; k < 6; k++) {
       float t = gi[0] * (A0[k] - img[0] * E[k]);
