@@ -23,33 +23,45 @@ static_assert(sizeof(G2DGrad) == 48, "G2DGrad is 48 bytes");
 
 constexpr int BWD_BATCH = 256;
 
-// Sum 16 per-lane values across the warp; afterwards lane l (both lanes of each pair) holds the total of
-// value index l>>1.  8+4+2+1+1 = 16 shuffles instead of 16*5.
-__device__ __forceinline__ float warp_reduce16_transpose(float (&v)[16], int lane) {
-#pragma unroll
-  for (int i = 0; i < 8; i++) {
+// Sum 10 per-lane values across the warp with a transposing butterfly: every exchange step halves the number of live
+// values per lane (5+3+2+1+1 = 12 shuffles instead of 10*5).  Afterwards the lane whose reduce10_slot() is k holds the
+// warp total of v[k]; other lanes hold duplicates.
+__device__ __forceinline__ float warp_reduce10_transpose(const float (&v)[10], const int lane) {
+  float b[5], c[3], d[2];
+  {
     const bool hi = lane & 16;
-    const float keep = hi ? v[i + 8] : v[i], send = hi ? v[i] : v[i + 8];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-  }
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    const bool hi = lane & 8;
-    const float keep = hi ? v[i + 4] : v[i], send = hi ? v[i] : v[i + 4];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-  }
-#pragma unroll
-  for (int i = 0; i < 2; i++) {
-    const bool hi = lane & 4;
-    const float keep = hi ? v[i + 2] : v[i], send = hi ? v[i] : v[i + 2];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    for (int i = 0; i < 5; i++) {
+      const float keep = hi ? v[i + 5] : v[i], send = hi ? v[i] : v[i + 5];
+      b[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
   }
   {
-    const bool hi = lane & 2;
-    const float keep = hi ? v[1] : v[0], send = hi ? v[0] : v[1];
-    v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+    const bool hi = lane & 8;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const float keep = hi ? b[i + 3] : b[i], send = hi ? b[i] : b[i + 3];
+      c[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
+    c[2] = b[2] + __shfl_xor_sync(0xffffffffu, b[2], 8);
   }
-  return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+  {
+    const bool hi = lane & 4;
+    const float keep = hi ? c[1] : c[0], send = hi ? c[0] : c[1];
+    d[0] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+    d[1] = c[2] + __shfl_xor_sync(0xffffffffu, c[2], 4);
+  }
+  const bool hi = lane & 2;
+  const float keep = hi ? d[1] : d[0], send = hi ? d[0] : d[1];
+  const float e = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+  return e + __shfl_xor_sync(0xffffffffu, e, 1);
+}
+// index of the value whose total this lane owns after warp_reduce10_transpose, or -1
+__device__ __forceinline__ int reduce10_slot(const int lane) {
+  if (lane & 1) return -1;
+  const int half = 5 * (lane >> 4);
+  if (lane & 2) return (lane & 12) ? -1 : 2 + half;
+  return ((lane & 4) ? 1 : 0) + ((lane & 8) ? 3 : 0) + half;
 }
 
 __global__ void __launch_bounds__(256)
@@ -114,6 +126,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
   float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f, last_alpha = 0.f;
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
   const float bg_dot_dpixel = bg[0] * dpx0 + bg[1] * dpx1 + bg[2] * dpx2;
+  const int slot = reduce10_slot(lane);
 
   for (int i = 0; i < rounds; i++) {
     // zero this thread's accumulator slot; the barrier also retires all reads of the other stage
@@ -142,14 +155,14 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
       const float alpha = min(0.99f, g1.w * G);
       const bool skip = !inside || contributor >= last_contributor || power > 0.0f || alpha < 1.0f / 255.0f;
       if (__ballot_sync(0xffffffffu, !skip) == 0u) continue;
-      float v[16];
-#pragma unroll
-      for (int k = 0; k < 16; k++) v[k] = 0.f;
+      // per-lane moments of u = G * dL/dalpha about the Gaussian centre and the colour / depth weights; everything that
+      // is constant per Gaussian (opacity, conic, the 0.5 W / 0.5 H factors) is applied once, after the sums, by the flush
+      float u = 0.f, w = 0.f;
       if (!skip) {
         const float4 g2 = rec4[3 * j + 2];
         const float inv_1ma = __fdividef(1.f, 1.f - alpha);   // 1-alpha in [0.01,1]: MUFU.RCP, 1 ulp vs the IEEE divide
         T = T * inv_1ma;
-        const float dchannel_dcolor = alpha * T;
+        w = alpha * T;
         float dL_dalpha = 0.0f;
         ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = g2.x; dL_dalpha += (g2.x - ar0) * dpx0;
         ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = g2.y; dL_dalpha += (g2.y - ar1) * dpx1;
@@ -158,31 +171,28 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
         dL_dalpha *= T;
         last_alpha = alpha;
         dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
-        const float dL_dG = g1.w * dL_dalpha;   // clamp at 0.99 deliberately ignored (Q6)
-        const float gdx = G * dx, gdy = G * dy;
-        const float dG_ddelx = -gdx * g1.x - gdy * g1.y;
-        const float dG_ddely = -gdy * g1.z - gdx * g1.y;
-        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-        v[1] = dL_dG * dG_ddely * ddely_dy;
-        v[2] = -0.5f * gdx * dx * dL_dG;
-        v[3] = -0.5f * gdx * dy * dL_dG;
-        v[4] = -0.5f * gdy * dy * dL_dG;
-        v[5] = G * dL_dalpha;
-        v[6] = dchannel_dcolor * dpd;
-        v[8] = dchannel_dcolor * dpx0;
-        v[9] = dchannel_dcolor * dpx1;
-        v[10] = dchannel_dcolor * dpx2;
+        u = G * dL_dalpha;
       }
-      const float tot = warp_reduce16_transpose(v, lane);
-      if (!(lane & 1) && lane < 24) atomicAdd(&acc[j * 12 + (lane >> 1)], tot);
+      const float ux = u * dx, uy = u * dy;
+      const float v[10] = {u, ux, uy, ux * dx, ux * dy, uy * dy, w * dpd, w * dpx0, w * dpx1, w * dpx2};
+      const float tot = warp_reduce10_transpose(v, lane);
+      if (slot >= 0) atomicAdd(&acc[j * 12 + slot], tot);
      }
     }
     __syncthreads();
     if (tid < cnt) {
-      const float4 a0 = reinterpret_cast<const float4*>(acc)[tid * 3 + 0];
-      const float4 a1 = reinterpret_cast<const float4*>(acc)[tid * 3 + 1];
-      const float4 a2 = reinterpret_cast<const float4*>(acc)[tid * 3 + 2];
+      const float4 m0 = reinterpret_cast<const float4*>(acc)[tid * 3 + 0];   // sum u, u dx, u dy, u dx dx
+      const float4 m1 = reinterpret_cast<const float4*>(acc)[tid * 3 + 1];   // u dx dy, u dy dy, depth, colour r
+      const float4 m2 = reinterpret_cast<const float4*>(acc)[tid * 3 + 2];   // colour g, b
+      const float4 co = rec4[3 * tid + 1];                                    // conic xyz, opacity
       const uint32_t id = __float_as_uint(rec4[3 * tid + 0].w);
+      // dL/dG = opacity * dL/dalpha (clamp at 0.99 deliberately ignored, Q6); dG/d(delta) and dG/d(conic) as in
+      // backward.cu:986-1010 with the per-Gaussian factors taken out of the pixel sums
+      const float hop = -0.5f * co.w;
+      const float4 a0 = make_float4(-co.w * (co.x * m0.y + co.y * m0.z) * ddelx_dx,
+                                    -co.w * (co.z * m0.z + co.y * m0.y) * ddely_dy, hop * m0.w, hop * m1.x);
+      const float4 a1 = make_float4(hop * m1.y, m0.x, m1.z, 0.f);
+      const float4 a2 = make_float4(m1.w, m2.x, m2.y, 0.f);
       float4* dst = reinterpret_cast<float4*>(g2d + id);
       if (a0.x != 0.f || a0.y != 0.f || a0.z != 0.f || a0.w != 0.f) atomicAdd(dst + 0, a0);
       if (a1.x != 0.f || a1.y != 0.f || a1.z != 0.f) atomicAdd(dst + 1, a1);
