@@ -1,21 +1,24 @@
 // Per-tile alpha blend, forward (replaces renderCUDA, forward.cu:263-392).
 //
-// One CTA per 16x16 tile, 256 threads, each warp owns an 8x4 pixel patch so that a small splat touches
-// few warps.  The tile's packed 48-B records are contiguous after the sort, so batches of 256 records
-// (12 KB) are streamed global->shared with cp.async.bulk (TMA 1-D, UBLKCP) into a two-stage ring tracked
-// by mbarriers; one elected thread issues the copies.  Early termination is decided per warp with a
-// ballot and per CTA with __syncthreads_count, like the reference's block vote.
+// One CTA per 16x16 tile, 128 threads; each warp owns an 8x8 pixel patch and each thread two pixels of one column
+// (rows y and y+4), evaluated together with packed fp32 (blend_pair.cuh).  The tile's packed 48-B records are
+// contiguous after the sort, so batches of 128 records (6 KB) are streamed global->shared with cp.async.bulk
+// (TMA 1-D, UBLKCP) into a two-stage ring tracked by mbarriers; one elected thread issues the copies.  A warp walks
+// only the records that can reach its patch (lane-parallel exact cull, splat_hits).  Early termination is decided
+// per warp with a ballot and per CTA with __syncthreads_count, like the reference's block vote.
 #include "launchers.h"
 #include "tma.cuh"
 #include "loss_pixel.cuh"
+#include "blend_pair.cuh"
 
 namespace mgs {
 
-constexpr int FWD_BATCH = 256;
+constexpr int FWD_BATCH = 128;
 constexpr int FWD_STAGES = 2;
+constexpr int FWD_THREADS = 128;
 
 template <bool FUSED_LOSS, bool FAST>   // FAST: approximate exp2 and no n_touched (tracking does not use it)
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(FWD_THREADS)
 blend_forward_kernel(const int W, const int H, const int gx,
                      const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
                      const float* __restrict__ bg,
@@ -31,10 +34,10 @@ blend_forward_kernel(const int W, const int H, const int gx,
   const int tile = blockIdx.x;
   const int tx = tile % gx, ty = tile / gx;
   const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
-  const int py = ty * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
-  const bool inside = px < W && py < H;
-  const float pxf = (float)px, pyf = (float)py;
-  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 4);
+  const int py0 = ty * TILE_Y + (warp >> 1) * 8 + (lane >> 3), py1 = py0 + 4;
+  const bool in0 = px < W && py0 < H, in1 = px < W && py1 < H;
+  const float2 npx = make_float2(-(float)px, -(float)px), npy = make_float2(-(float)py0, -(float)py1);
+  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 8);
 
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
@@ -53,13 +56,13 @@ blend_forward_kernel(const int W, const int H, const int gx,
     bulk_g2s(&stage[0][0], src, bytes, &full_bar[0]);
   }
 
-  bool done = !inside;
-  float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
-  uint32_t last_contributor = 0;
+  bool done0 = !in0, done1 = !in1;
+  float2 T = make_float2(1.f, 1.f), C0 = make_float2(0.f, 0.f), C1 = C0, C2 = C0, D = C0;
+  uint32_t last0 = 0, last1 = 0;
 
   for (int i = 0; i < rounds; i++) {
     // CTA vote; also guarantees every warp left the stage that the next copy overwrites
-    if (__syncthreads_count(done) == TILE_PIX) {
+    if (__syncthreads_count(done0 && done1) == FWD_THREADS) {
       if (tid == 0) mbar_wait(&full_bar[i & 1], (i >> 1) & 1);  // never exit with a bulk copy in flight
       break;
     }
@@ -75,63 +78,67 @@ blend_forward_kernel(const int W, const int H, const int gx,
     const int cnt = min(FWD_BATCH, n - i * FWD_BATCH);
     const uint32_t base = (uint32_t)i * FWD_BATCH;
     for (int c0 = 0; c0 < cnt; c0 += 32) {
-      // lane-parallel exact cull: which of these 32 splats can reach this warp's 8x4 patch at all?
+      // lane-parallel exact cull: which of these 32 splats can reach this warp's 8x8 patch at all?
       const int jj = c0 + lane;
-      unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
-      if (__ballot_sync(0xffffffffu, !done) == 0u) break;
+      unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 7.f));
+      if (__ballot_sync(0xffffffffu, !(done0 && done1)) == 0u) break;
       while (hits) {
         const int j = c0 + __ffs(hits) - 1;
         hits &= hits - 1;
         const float4 g0 = rec4[3 * j + 0];  // x, y, depth, id
         const float4 g1 = rec4[3 * j + 1];  // conic xyz, opacity
-        const float dx = g0.x - pxf, dy = g0.y - pyf;
-        const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
-        bool valid = !done && !(power > 0.0f);
-        const float alpha = min(0.99f, g1.w * blend_exp<FAST>(power));
-        valid = valid && !(alpha < 1.0f / 255.0f);
-        const float test_T = T * (1 - alpha);
-        if (valid && test_T < 0.0001f) { done = true; valid = false; }
-        unsigned touch = 0u;
-        if (!FAST) touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
-        if (valid) {
-          const float4 g2 = rec4[3 * j + 2];
-          C0 += g2.x * alpha * T;
-          C1 += g2.y * alpha * T;
-          C2 += g2.z * alpha * T;
-          D += g0.z * alpha * T;
-          T = test_T;
-          last_contributor = base + j + 1;
+        float2 dx, dy, power, G, alpha;
+        pair_alpha<FAST>(g0, g1, npx, npy, dx, dy, power, G, alpha);
+        bool v0 = !done0 && !(power.x > 0.0f) && !(alpha.x < 1.0f / 255.0f);
+        bool v1 = !done1 && !(power.y > 0.0f) && !(alpha.y < 1.0f / 255.0f);
+        const float2 test_T = __fmul2_rn(T, one_minus2(alpha));
+        if (v0 && test_T.x < 0.0001f) { done0 = true; v0 = false; }
+        if (v1 && test_T.y < 0.0001f) { done1 = true; v1 = false; }
+        if (!FAST) {
+          const unsigned t0 = __ballot_sync(0xffffffffu, v0 && test_T.x > 0.5f);
+          const unsigned t1 = __ballot_sync(0xffffffffu, v1 && test_T.y > 0.5f);
+          if ((t0 | t1) != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(t0) + __popc(t1));
         }
-        if (!FAST && touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
+        if (v0 || v1) {
+          const float4 g2 = rec4[3 * j + 2];
+          // colour += c * alpha * T as (c * alpha) * T + colour (forward.cu:364-367); a masked pixel adds c * 0
+          const float2 am = make_float2(v0 ? alpha.x : 0.f, v1 ? alpha.y : 0.f);
+          C0 = __ffma2_rn(T, __fmul2_rn(bcast2(g2.x), am), C0);
+          C1 = __ffma2_rn(T, __fmul2_rn(bcast2(g2.y), am), C1);
+          C2 = __ffma2_rn(T, __fmul2_rn(bcast2(g2.z), am), C2);
+          D = __ffma2_rn(T, __fmul2_rn(bcast2(g0.z), am), D);
+          if (v0) { T.x = test_T.x; last0 = base + j + 1; }
+          if (v1) { T.y = test_T.y; last1 = base + j + 1; }
+        }
       }
     }
   }
 
-  if (inside) {
-    const size_t pix = (size_t)py * W + px;
-    const size_t plane = (size_t)W * H;
-    final_T[pix] = T;
-    n_contrib[pix] = last_contributor;
-    out_color[pix] = C0 + T * bg[0];
-    out_color[plane + pix] = C1 + T * bg[1];
-    out_color[2 * plane + pix] = C2 + T * bg[2];
-    out_depth[pix] = D;
-    out_opacity[pix] = 1 - T;
-  }
-  if (FUSED_LOSS) {
-    // loss + its (un-normalised) gradient straight from the registers that hold the blended pixel
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    if (inside) {
-      const size_t pix = (size_t)py * W + px;
-      const size_t plane = (size_t)W * H;
-      const float img[3] = {C0 + T * bg[0], C1 + T * bg[1], C2 + T * bg[2]};
+  const size_t plane = (size_t)W * H;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    const bool inside = k ? in1 : in0;
+    if (!inside) continue;
+    const size_t pix = (size_t)(k ? py1 : py0) * W + px;
+    const float Tk = k ? T.y : T.x, Dk = k ? D.y : D.x;
+    const float img[3] = {(k ? C0.y : C0.x) + Tk * bg[0], (k ? C1.y : C1.x) + Tk * bg[1], (k ? C2.y : C2.x) + Tk * bg[2]};
+    final_T[pix] = Tk;
+    n_contrib[pix] = k ? last1 : last0;
+    out_color[pix] = img[0];
+    out_color[plane + pix] = img[1];
+    out_color[2 * plane + pix] = img[2];
+    out_depth[pix] = Dk;
+    out_opacity[pix] = 1 - Tk;
+    if (FUSED_LOSS) {
+      // loss + its (un-normalised) gradient straight from the registers that hold the blended pixel
       float gi[3], gd;
-      loss_pixel<true, true>(lk, (int)pix, img, D, 1 - T, loss_grad_scale, acc, gi, gd);
+      loss_pixel<true, true>(lk, (int)pix, img, Dk, 1 - Tk, loss_grad_scale, acc, gi, gd);
       g_img[pix] = gi[0]; g_img[plane + pix] = gi[1]; g_img[2 * plane + pix] = gi[2];
       if (g_depth != nullptr) g_depth[pix] = gd;
     }
-    loss_block_reduce(acc, loss_partials + (size_t)tile * 4);
   }
+  if (FUSED_LOSS) loss_block_reduce(acc, loss_partials + (size_t)tile * 4);
 }
 
 int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
@@ -140,15 +147,15 @@ int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float*
   prof_begin("blend_forward", s);
   if (fl == nullptr) {
     LossK none{};
-    blend_forward_kernel<false, false><<<tiles, 256, 0, s>>>(
+    blend_forward_kernel<false, false><<<tiles, FWD_THREADS, 0, s>>>(
         v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
         ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, none, 0.f, nullptr, nullptr, nullptr);
   } else {
 #define MGS_FWD_ARGS v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg,                  \
         ws_ptr<float>(ws, L.final_T), ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, \
         *fl->k, fl->grad_scale, fl->g_img, fl->g_depth, fl->partials
-    if (fl->fast) blend_forward_kernel<true, true><<<tiles, 256, 0, s>>>(MGS_FWD_ARGS);
-    else blend_forward_kernel<true, false><<<tiles, 256, 0, s>>>(MGS_FWD_ARGS);
+    if (fl->fast) blend_forward_kernel<true, true><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
+    else blend_forward_kernel<true, false><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
 #undef MGS_FWD_ARGS
   }
   prof_end(s);

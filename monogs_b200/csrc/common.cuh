@@ -57,7 +57,8 @@ static_assert(sizeof(WsHeader) == 256, "header is one 256-B slot");
 // R_cap (header, per-Gaussian state, image state, then the records), so backward never needs R_cap.
 struct WsLayout {
   size_t header, depths, means2D, conic_opacity, rgb4, tiles_touched;
-  size_t tile_ctr;                                // u32[tiles][TILE_CTR_STRIDE]: [0] instances per tile, [1] scatter cursor
+  size_t tile_ctr;                                // u32[tiles][TILE_CTR_STRIDE]: [0] instances per tile, [1] scatter cursor,
+                                                  // [2] compact list of large tiles
   size_t final_T, n_contrib, ranges, records;
   size_t list;                                    // u64[R_cap]: (depth bits << 32 | Gaussian id), grouped by tile
   size_t total;

@@ -10,6 +10,7 @@
 #include "launchers.h"
 #include "gaussian_backward.cuh"
 #include "tma.cuh"
+#include "blend_pair.cuh"
 
 namespace mgs {
 
@@ -21,7 +22,8 @@ struct __align__(16) G2DGrad {
 };
 static_assert(sizeof(G2DGrad) == 48, "G2DGrad is 48 bytes");
 
-constexpr int BWD_BATCH = 256;
+constexpr int BWD_BATCH = 128;     // records per batch = threads per CTA (one flush thread per record)
+constexpr int BWD_THREADS = 128;
 
 // Sum 10 per-lane values across the warp with a transposing butterfly: every exchange step halves the number of live
 // values per lane (5+3+2+1+1 = 12 shuffles instead of 10*5).  Afterwards the lane whose reduce10_slot() is k holds the
@@ -64,7 +66,13 @@ __device__ __forceinline__ int reduce10_slot(const int lane) {
   return ((lane & 4) ? 1 : 0) + ((lane & 8) ? 3 : 0) + half;
 }
 
-__global__ void __launch_bounds__(256)
+// Two pixels per thread (same column, rows y and y+4 of the warp's 8x8 patch) with packed fp32, see blend_pair.cuh.
+// A pixel that skips a splat (outside, behind its last contributor, power > 0 or alpha < 1/255) takes part with
+// alpha = 0, which leaves its recurrences untouched exactly:  T / (1 - 0) = T,  and the pending fold
+// accum = last_alpha * last_colour + (1 - last_alpha) * accum  is simply applied one splat early and followed by a
+// fold with last_alpha = 0.  So the per-pixel updates run unconditionally for both halves, and the "last colour" is
+// the colour of the previous record the warp processed: warp-uniform, not per-pixel state.
+__global__ void __launch_bounds__(BWD_THREADS)
 blend_backward_full_kernel(const int W, const int H, const int gx,
                            const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
                            const float* __restrict__ bg, const float* __restrict__ final_T,
@@ -80,20 +88,18 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
   const int tile = blockIdx.x;
   const int tx = tile % gx, ty = tile / gx;
   const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
-  const int py = ty * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
-  const bool inside = px < W && py < H;
-  const size_t pix = (size_t)py * W + px, plane = (size_t)W * H;
-  const float pxf = (float)px, pyf = (float)py;
-  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 4);
+  const int py0 = ty * TILE_Y + (warp >> 1) * 8 + (lane >> 3), py1 = py0 + 4;
+  const bool in0 = px < W && py0 < H, in1 = px < W && py1 < H;
+  const size_t pix0 = (size_t)py0 * W + px, pix1 = (size_t)py1 * W + px, plane = (size_t)W * H;
+  const float2 npx = make_float2(-(float)px, -(float)px), npy = make_float2(-(float)py0, -(float)py1);
+  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 8);
   const uint2 range = ranges[tile];
 
-  const float T_final = inside ? final_T[pix] : 0.f;
-  const int last_contributor = inside ? (int)n_contrib[pix] : 0;
-  float dpx0 = 0.f, dpx1 = 0.f, dpx2 = 0.f, dpd = 0.f;
-  if (inside) {
-    dpx0 = dL_dpix[pix]; dpx1 = dL_dpix[plane + pix]; dpx2 = dL_dpix[2 * plane + pix];
-    dpd = dL_dpix_depth[pix];
-  }
+  const float2 T_final = make_float2(in0 ? final_T[pix0] : 0.f, in1 ? final_T[pix1] : 0.f);
+  const int last0 = in0 ? (int)n_contrib[pix0] : 0, last1 = in1 ? (int)n_contrib[pix1] : 0;
+  float2 dp0 = make_float2(0.f, 0.f), dp1 = dp0, dp2 = dp0, dpd = dp0;
+  if (in0) { dp0.x = dL_dpix[pix0]; dp1.x = dL_dpix[plane + pix0]; dp2.x = dL_dpix[2 * plane + pix0]; dpd.x = dL_dpix_depth[pix0]; }
+  if (in1) { dp0.y = dL_dpix[pix1]; dp1.y = dL_dpix[plane + pix1]; dp2.y = dL_dpix[2 * plane + pix1]; dpd.y = dL_dpix_depth[pix1]; }
   if (tid == 0) {
     s_max_contrib = 0;
     mbar_init(&full_bar[0], 1); mbar_init(&full_bar[1], 1);
@@ -101,7 +107,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
   }
   __syncthreads();
   {
-    int m = last_contributor;
+    int m = max(last0, last1);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
     if (lane == 0 && m > 0) atomicMax(&s_max_contrib, m);
@@ -121,11 +127,14 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
   };
   if (tid == 0 && rounds > 0) issue(0);
 
-  float T = T_final;
-  float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, ard = 0.f;       // accum_rec colour / depth
-  float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f, last_alpha = 0.f;
+  float2 T = T_final;
+  const float2 zero2 = make_float2(0.f, 0.f);
+  float2 ar0 = zero2, ar1 = zero2, ar2 = zero2, ard = zero2, last_alpha = zero2;   // accum_rec colour / depth
+  float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, ld = 0.f;                                    // last processed record (warp-uniform)
   const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
-  const float bg_dot_dpixel = bg[0] * dpx0 + bg[1] * dpx1 + bg[2] * dpx2;
+  const float b0 = bg[0], b1 = bg[1], b2 = bg[2];
+  const float2 bg_dot_dpixel = make_float2(b0 * dp0.x + b1 * dp1.x + b2 * dp2.x, b0 * dp0.y + b1 * dp1.y + b2 * dp2.y);
+  const float2 neg_T_final = neg2(T_final);
   const int slot = reduce10_slot(lane);
 
   for (int i = 0; i < rounds; i++) {
@@ -140,41 +149,49 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
     const float4* rec4 = reinterpret_cast<const float4*>(&stage[i & 1][0]);
     const float* recf = reinterpret_cast<const float*>(&stage[i & 1][0]);
     for (int c0 = ((cnt - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
-     // lane-parallel exact cull of 32 splats against this warp's 8x4 patch (see splat_extent)
+     // lane-parallel exact cull of 32 splats against this warp's 8x8 patch (see splat_extent)
      const int jj = c0 + lane;
-     unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+     unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 7.f));
      while (hits) {
       const int j = c0 + 31 - __clz(hits);
       hits &= ~(1u << (j - c0));
       const int contributor = lo + j;  // list position of this Gaussian
       const float4 g0 = rec4[3 * j + 0];
       const float4 g1 = rec4[3 * j + 1];
-      const float dx = g0.x - pxf, dy = g0.y - pyf;
-      const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
-      const float G = expf(power);
-      const float alpha = min(0.99f, g1.w * G);
-      const bool skip = !inside || contributor >= last_contributor || power > 0.0f || alpha < 1.0f / 255.0f;
-      if (__ballot_sync(0xffffffffu, !skip) == 0u) continue;
+      float2 dx, dy, power, G, alpha;
+      pair_alpha<false>(g0, g1, npx, npy, dx, dy, power, G, alpha);
+      const bool skip0 = !in0 || contributor >= last0 || power.x > 0.0f || alpha.x < 1.0f / 255.0f;
+      const bool skip1 = !in1 || contributor >= last1 || power.y > 0.0f || alpha.y < 1.0f / 255.0f;
+      if (__ballot_sync(0xffffffffu, !(skip0 && skip1)) == 0u) continue;
+      const float4 g2 = rec4[3 * j + 2];
+      const float2 ae = make_float2(skip0 ? 0.f : alpha.x, skip1 ? 0.f : alpha.y);
+      const float2 oma = one_minus2(ae);
+      // 1-alpha in [0.01,1]: MUFU.RCP, 1 ulp vs the IEEE divide; exactly 1 for a skipped pixel
+      const float2 inv_1ma = make_float2(__fdividef(1.f, oma.x), __fdividef(1.f, oma.y));
+      T = __fmul2_rn(T, inv_1ma);
+      const float2 w = __fmul2_rn(ae, T);                        // dchannel_dcolor
+      const float2 oml = one_minus2(last_alpha);
+      ar0 = __ffma2_rn(last_alpha, bcast2(lc0), __fmul2_rn(oml, ar0));
+      ar1 = __ffma2_rn(last_alpha, bcast2(lc1), __fmul2_rn(oml, ar1));
+      ar2 = __ffma2_rn(last_alpha, bcast2(lc2), __fmul2_rn(oml, ar2));
+      ard = __ffma2_rn(last_alpha, bcast2(ld), __fmul2_rn(oml, ard));
+      float2 dL_dalpha = __fmul2_rn(__fadd2_rn(bcast2(g2.x), neg2(ar0)), dp0);
+      dL_dalpha = __ffma2_rn(__fadd2_rn(bcast2(g2.y), neg2(ar1)), dp1, dL_dalpha);
+      dL_dalpha = __ffma2_rn(__fadd2_rn(bcast2(g2.z), neg2(ar2)), dp2, dL_dalpha);
+      dL_dalpha = __ffma2_rn(__fadd2_rn(bcast2(g0.z), neg2(ard)), dpd, dL_dalpha);
+      lc0 = g2.x; lc1 = g2.y; lc2 = g2.z; ld = g0.z;
+      last_alpha = ae;
+      dL_dalpha = __fmul2_rn(dL_dalpha, T);
+      dL_dalpha = __ffma2_rn(__fmul2_rn(neg_T_final, inv_1ma), bg_dot_dpixel, dL_dalpha);
       // per-lane moments of u = G * dL/dalpha about the Gaussian centre and the colour / depth weights; everything that
       // is constant per Gaussian (opacity, conic, the 0.5 W / 0.5 H factors) is applied once, after the sums, by the flush
-      float u = 0.f, w = 0.f;
-      if (!skip) {
-        const float4 g2 = rec4[3 * j + 2];
-        const float inv_1ma = __fdividef(1.f, 1.f - alpha);   // 1-alpha in [0.01,1]: MUFU.RCP, 1 ulp vs the IEEE divide
-        T = T * inv_1ma;
-        w = alpha * T;
-        float dL_dalpha = 0.0f;
-        ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = g2.x; dL_dalpha += (g2.x - ar0) * dpx0;
-        ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = g2.y; dL_dalpha += (g2.y - ar1) * dpx1;
-        ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = g2.z; dL_dalpha += (g2.z - ar2) * dpx2;
-        ard = last_alpha * ld + (1.f - last_alpha) * ard; ld = g0.z; dL_dalpha += (g0.z - ard) * dpd;
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
-        u = G * dL_dalpha;
-      }
-      const float ux = u * dx, uy = u * dy;
-      const float v[10] = {u, ux, uy, ux * dx, ux * dy, uy * dy, w * dpd, w * dpx0, w * dpx1, w * dpx2};
+      float2 u = __fmul2_rn(G, dL_dalpha);
+      u.x = skip0 ? 0.f : u.x; u.y = skip1 ? 0.f : u.y;
+      const float2 ux = __fmul2_rn(u, dx), uy = __fmul2_rn(u, dy);
+      const float2 uxx = __fmul2_rn(ux, dx), uxy = __fmul2_rn(ux, dy), uyy = __fmul2_rn(uy, dy);
+      const float2 wd = __fmul2_rn(w, dpd), w0 = __fmul2_rn(w, dp0), w1 = __fmul2_rn(w, dp1), w2 = __fmul2_rn(w, dp2);
+      const float v[10] = {u.x + u.y, ux.x + ux.y, uy.x + uy.y, uxx.x + uxx.y, uxy.x + uxy.y, uyy.x + uyy.y,
+                           wd.x + wd.y, w0.x + w0.y, w1.x + w1.y, w2.x + w2.y};
       const float tot = warp_reduce10_transpose(v, lane);
       if (slot >= 0) atomicAdd(&acc[j * 12 + slot], tot);
      }
@@ -350,7 +367,7 @@ int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   if (a.dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
   const int tiles = v.gx * v.gy;
   prof_begin("blend_backward_full", s);
-  blend_backward_full_kernel<<<tiles, 256, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges),
+  blend_backward_full_kernel<<<tiles, BWD_THREADS, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges),
                                                    ws_ptr<SplatRec>(a.ws, a.L.records), v.bg,
                                                    ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib),
                                                    a.dL_dcolor_img, a.dL_ddepth_img, g2d);
