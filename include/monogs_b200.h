@@ -260,6 +260,7 @@ typedef struct mgs_map_view {
   const float* exposure_b;
   float rgb_boundary_threshold, alpha;
   int32_t update_stats;
+  int32_t fast_math;        /* 1: ex2.approx exponent in this view's forward and backward blend (rel. error ~4e-7) */
   float *out_color, *out_depth, *out_opacity;   /* f32[3,H,W], f32[1,H,W], f32[1,H,W] */
   int32_t *radii, *n_touched;                   /* i32[P] of THIS view (visibility filter, occ_aware_visibility) */
   float* tau;               /* f32[6]: pose tangent (rho, theta) of this view's loss, optional */

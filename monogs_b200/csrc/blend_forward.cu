@@ -17,7 +17,7 @@ constexpr int FWD_BATCH = 128;
 constexpr int FWD_STAGES = 2;
 constexpr int FWD_THREADS = 128;
 
-template <bool FUSED_LOSS, bool FAST>   // FAST: approximate exp2 and no n_touched (tracking does not use it)
+template <bool FUSED_LOSS, bool FAST, bool TOUCH>   // FAST: ex2.approx exponent; TOUCH: n_touched produced
 __global__ void __launch_bounds__(FWD_THREADS)
 blend_forward_kernel(const int W, const int H, const int gx,
                      const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
@@ -94,7 +94,7 @@ blend_forward_kernel(const int W, const int H, const int gx,
         const float2 test_T = __fmul2_rn(T, one_minus2(alpha));
         if (v0 && test_T.x < 0.0001f) { done0 = true; v0 = false; }
         if (v1 && test_T.y < 0.0001f) { done1 = true; v1 = false; }
-        if (!FAST) {
+        if (TOUCH) {
           const unsigned t0 = __ballot_sync(0xffffffffu, v0 && test_T.x > 0.5f);
           const unsigned t1 = __ballot_sync(0xffffffffu, v1 && test_T.y > 0.5f);
           if ((t0 | t1) != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(t0) + __popc(t1));
@@ -147,15 +147,16 @@ int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float*
   prof_begin("blend_forward", s);
   if (fl == nullptr) {
     LossK none{};
-    blend_forward_kernel<false, false><<<tiles, FWD_THREADS, 0, s>>>(
+    blend_forward_kernel<false, false, true><<<tiles, FWD_THREADS, 0, s>>>(
         v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
         ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, none, 0.f, nullptr, nullptr, nullptr);
   } else {
 #define MGS_FWD_ARGS v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg,                  \
         ws_ptr<float>(ws, L.final_T), ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, \
         *fl->k, fl->grad_scale, fl->g_img, fl->g_depth, fl->partials
-    if (fl->fast) blend_forward_kernel<true, true><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
-    else blend_forward_kernel<true, false><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
+    if (fl->fast && n_touched == nullptr) blend_forward_kernel<true, true, false><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
+    else if (fl->fast) blend_forward_kernel<true, true, true><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
+    else blend_forward_kernel<true, false, true><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
 #undef MGS_FWD_ARGS
   }
   prof_end(s);

@@ -36,6 +36,7 @@ struct BackwardArgs {
   // overwriting them; optional densification statistics updated in the same pass (gaussian_model.py:693-697,
   // slam_backend.py:292-299): grad_accum[g] += |dL/dmean2D.xy|, denom[g] += 1, max_radii2D[g] = max(., radii[g])
   int accumulate; float *stat_grad_accum, *stat_denom, *stat_max_radii;
+  bool fast = false;   // blend_backward_full only: exponent variant of the forward that produced ws (blend_exp<FAST>)
   // sketch mode (sketch_dim > 0): per-pixel row routing, output sketch_dtau[d,6]
   int sketch_dim; const int32_t* sketch_indices; float* sketch_dtau;
 };

@@ -248,7 +248,7 @@ int mgs_map_view_fwd_bwd(const mgs_map_args* a, const mgs_map_view* mv, void* st
   lk.mask = nullptr; lk.a = mv->exposure_a; lk.b = mv->exposure_b;
   FusedLoss fl;
   fl.k = &lk; fl.grad_scale = (use_depth ? mv->alpha : 1.f) / (3.f * (float)npix);
-  fl.g_img = m.g_img; fl.g_depth = m.g_depth; fl.partials = m.partials; fl.fast = false;
+  fl.g_img = m.g_img; fl.g_depth = m.g_depth; fl.partials = m.partials; fl.fast = mv->fast_math != 0;
   if ((rc = launch_blend_forward(v, ws, L, mv->out_color, mv->out_depth, mv->out_opacity, mv->n_touched, s, &fl))) return rc;
   MGS_PROF("map_loss_finalize", s, map_loss_finalize_kernel<<<1, 256, 0, s>>>(m.partials, tiles, (int)npix, use_depth, mv->alpha,
                                                                              mv->loss, a->loss_total, mv->dab));
@@ -265,6 +265,7 @@ int mgs_map_view_fwd_bwd(const mgs_map_args* a, const mgs_map_view* mv, void* st
   b.dL_dscales = m.d_scales; b.dL_drotations = m.d_rot; b.dL_dtau_sum = mv->tau;
   b.accumulate = 1;
   if (mv->update_stats) { b.stat_grad_accum = a->xyz_gradient_accum; b.stat_denom = a->denom; b.stat_max_radii = a->max_radii2D; }
+  b.fast = mv->fast_math != 0;
   return launch_backward_full(b, s);
 }
 

@@ -72,6 +72,7 @@ __device__ __forceinline__ int reduce10_slot(const int lane) {
 // accum = last_alpha * last_colour + (1 - last_alpha) * accum  is simply applied one splat early and followed by a
 // fold with last_alpha = 0.  So the per-pixel updates run unconditionally for both halves, and the "last colour" is
 // the colour of the previous record the warp processed: warp-uniform, not per-pixel state.
+template <bool FAST>   // FAST: the ex2.approx exponent of a FAST forward (T is recovered with the same alpha)
 __global__ void __launch_bounds__(BWD_THREADS)
 blend_backward_full_kernel(const int W, const int H, const int gx,
                            const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
@@ -159,7 +160,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
       const float4 g0 = rec4[3 * j + 0];
       const float4 g1 = rec4[3 * j + 1];
       float2 dx, dy, power, G, alpha;
-      pair_alpha<false>(g0, g1, npx, npy, dx, dy, power, G, alpha);
+      pair_alpha<FAST>(g0, g1, npx, npy, dx, dy, power, G, alpha);
       const bool skip0 = !in0 || contributor >= last0 || power.x > 0.0f || alpha.x < 1.0f / 255.0f;
       const bool skip1 = !in1 || contributor >= last1 || power.y > 0.0f || alpha.y < 1.0f / 255.0f;
       if (__ballot_sync(0xffffffffu, !(skip0 && skip1)) == 0u) continue;
@@ -367,10 +368,11 @@ int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   if (a.dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
   const int tiles = v.gx * v.gy;
   prof_begin("blend_backward_full", s);
-  blend_backward_full_kernel<<<tiles, BWD_THREADS, 0, s>>>(v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges),
-                                                   ws_ptr<SplatRec>(a.ws, a.L.records), v.bg,
-                                                   ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib),
-                                                   a.dL_dcolor_img, a.dL_ddepth_img, g2d);
+#define MGS_BWD_ARGS v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges), ws_ptr<SplatRec>(a.ws, a.L.records), v.bg,          \
+      ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img, a.dL_ddepth_img, g2d
+  if (a.fast) blend_backward_full_kernel<true><<<tiles, BWD_THREADS, 0, s>>>(MGS_BWD_ARGS);
+  else blend_backward_full_kernel<false><<<tiles, BWD_THREADS, 0, s>>>(MGS_BWD_ARGS);
+#undef MGS_BWD_ARGS
   prof_end(s);
   MGS_LAUNCH_CHECK();
   prof_begin("preprocess_backward", s);

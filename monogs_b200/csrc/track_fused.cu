@@ -189,7 +189,7 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
                                  tau_raw, s)))
       return rc;
   } else {
-    if ((rc = launch_blend_forward(v, ws, L, t->out_color, t->out_depth, t->out_opacity, t->n_touched, s, &fl))) return rc;
+    if ((rc = launch_blend_forward(v, ws, L, t->out_color, t->out_depth, t->out_opacity, t->fast_math ? nullptr : t->n_touched, s, &fl))) return rc;
     BackwardArgs a;
     memset(&a, 0, sizeof(a));
     a.v = v; a.P = P; a.grad_mask = MGS_GRAD_TAU; a.ws = ws; a.L = L;

@@ -125,9 +125,10 @@ class MapEngine:
 
     def __init__(self, params: Dict[str, torch.Tensor], lrs: Dict[str, float], sh_degree: int = 0, W: int = 640, H: int = 480,
                  capacity_headroom: float = 2.0, group=None, regulariser_weight: float = 10.0,
-                 rgb_boundary_threshold: float = 0.01, alpha: float = 0.95):
+                 rgb_boundary_threshold: float = 0.01, alpha: float = 0.95, fast_math: bool = True):
         from . import _lib as L
         from .ops import FusedAdam
+        self.fast_math = fast_math   # ex2.approx exponent in the blend kernels (relative error ~4e-7), like PoseTracker
         self.L, self.lib = L, L.lib()
         self.params = {k: params[k] for k in self.NAMES if k in params and params[k] is not None and params[k].numel() > 0}
         self.dev = self.params["xyz"].device
@@ -224,6 +225,7 @@ class MapEngine:
         mv.exposure_a = view.exposure_a.data_ptr() if view.exposure_a is not None else None
         mv.exposure_b = view.exposure_b.data_ptr() if view.exposure_b is not None else None
         mv.rgb_boundary_threshold, mv.alpha, mv.update_stats = self.thr, self.alpha, int(view.update_stats)
+        mv.fast_math = int(self.fast_math)
         mv.out_color, mv.out_depth, mv.out_opacity = self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr()
         mv.radii, mv.n_touched = slot.radii.data_ptr(), slot.n_touched.data_ptr()
         mv.tau, mv.dab, mv.loss = slot.tau.data_ptr(), slot.dab.data_ptr(), slot.loss.data_ptr()

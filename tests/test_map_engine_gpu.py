@@ -76,10 +76,14 @@ def _reference_iteration(p, views, sh_degree, alpha=0.95, thr=0.01):
     return total.detach(), per_view
 
 
-@pytest.mark.parametrize("name,with_depth,with_exposure,isotropic",
-                         [("tiny", False, False, False), ("dense", True, True, False), ("ragged", True, True, True),
-                          ("sh3", False, True, False)])
-def test_map_engine_matches_autograd_path(name, with_depth, with_exposure, isotropic):
+@pytest.mark.parametrize("name,with_depth,with_exposure,isotropic,fast",
+                         [("tiny", False, False, False, False), ("dense", True, True, False, False),
+                          ("ragged", True, True, True, False), ("sh3", False, True, False, False),
+                          ("dense", True, True, False, True), ("sh3", False, True, False, True)])
+def test_map_engine_matches_autograd_path(name, with_depth, with_exposure, isotropic, fast):
+    """fast = False: the exact exponent, integer outputs equal to the autograd path's.  fast = True (the MapEngine
+    default): ex2.approx in forward and backward blend; a borderline `T > 0.5` decision may move, so n_touched is
+    compared as a count of differing entries."""
     from monogs_b200.mapping import MapEngine
     sc, cam = U.small_case(name)
     p_ref = _raw_params(sc, isotropic)
@@ -88,7 +92,7 @@ def test_map_engine_matches_autograd_path(name, with_depth, with_exposure, isotr
 
     p = {k: v.detach().clone() for k, v in p_ref.items()}
     lrs = {k: 0.0 for k in p}
-    eng = MapEngine(p, lrs, sh_degree=sc.sh_degree, W=cam.W, H=cam.H)
+    eng = MapEngine(p, lrs, sh_degree=sc.sh_degree, W=cam.W, H=cam.H, fast_math=fast)
     res = eng.backward_only(views)
     torch.cuda.synchronize()
     n, ov = eng.check_capacity()
@@ -104,7 +108,9 @@ def test_map_engine_matches_autograd_path(name, with_depth, with_exposure, isotr
     acc, den, mr = torch.zeros(P, device="cuda"), torch.zeros(P, device="cuda"), torch.zeros(P, device="cuda")
     for i, v in enumerate(views):
         r = res[i]
-        assert torch.equal(r.radii, pv[i]["radii"]) and torch.equal(r.n_touched, pv[i]["n_touched"])
+        assert torch.equal(r.radii, pv[i]["radii"])
+        if fast: assert int((r.n_touched != pv[i]["n_touched"]).sum()) <= max(2, P // 500)
+        else: assert torch.equal(r.n_touched, pv[i]["n_touched"])
         assert U.rel_err(r.loss, pv[i]["loss"].view(1)) <= 1e-5
         tau_ref = torch.cat((pv[i]["rho"].grad, pv[i]["theta"].grad))
         assert U.rel_err(r.tau, tau_ref) <= TOL
