@@ -37,7 +37,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // vote) per batch and no load latency on the blend path.
 template <bool HAS_DEPTH, bool FAST>   // FAST: ex2.approx exponent, n_touched not produced
 __global__ void __launch_bounds__(256, 3)
-blend_track_kernel(const int W, const int H, const int gx, const uint2* __restrict__ ranges,
+blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __restrict__ tile_order, const uint2* __restrict__ ranges,
                    const SplatRec* __restrict__ recs, const float* __restrict__ jac, const float* __restrict__ bg,
                    float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
                    int32_t* __restrict__ n_touched, const LossK lk, const float loss_grad_scale,
@@ -50,7 +50,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint2* __restri
   __shared__ float s_part[8][6];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tile = blockIdx.x;
+  const int tile = (int)tile_order[(size_t)blockIdx.x * TILE_CTR_STRIDE + 3];   // heavy tiles first (tile_scan_kernel)
   const int tx = tile % gx, ty = tile / gx;
   const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
   const int py = ty * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
@@ -255,7 +255,7 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
     MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
     attr_set = true;
   }
-#define MGS_TRK_ARGS v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color,   \
+#define MGS_TRK_ARGS v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color,   \
       out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum
   prof_begin("blend_track", s);
   if (has_depth) {

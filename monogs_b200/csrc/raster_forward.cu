@@ -296,8 +296,8 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
                  uint2* __restrict__ ranges, WsHeader* __restrict__ hdr) {
   using Scan = cub::BlockScan<uint32_t, SCAN_THREADS>;
   __shared__ typename Scan::TempStorage tmp;
-  __shared__ uint32_t n_large;
-  if (threadIdx.x == 0) n_large = 0u;
+  __shared__ uint32_t n_large, max_count;
+  if (threadIdx.x == 0) { n_large = 0u; max_count = 0u; }
   __syncthreads();
   uint32_t carry = 0;
   for (int base = 0; base < tiles; base += SCAN_THREADS * SCAN_IPT) {
@@ -307,6 +307,11 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
     for (int i = 0; i < SCAN_IPT; i++) c[i] = t0 + i < tiles ? tile_ctr[(size_t)(t0 + i) * TILE_CTR_STRIDE] : 0u;
 #pragma unroll
     for (int i = 0; i < SCAN_IPT; i++) sum += c[i];
+    {
+      uint32_t m = max(max(c[0], c[1]), max(c[2], c[3]));
+      m = __reduce_max_sync(0xffffffffu, m);
+      if ((threadIdx.x & 31) == 0 && m > 0u) atomicMax(&max_count, m);
+    }
     uint32_t excl, total;
     Scan(tmp).ExclusiveSum(sum, excl, total);
     uint32_t start = carry + excl;
@@ -330,6 +335,36 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
     hdr->overflow = carry > R_cap ? 1u : 0u;
     hdr->r_used = carry > R_cap ? R_cap : carry;
     hdr->n_large = n_large;
+  }
+  // Heavy-first launch order for per-tile kernels that run in several waves (blend_track_kernel: 3 CTAs per SM): a
+  // counting sort of the tiles into 64 buckets of list length, longest lists first, written to
+  // tile_ctr[i * TILE_CTR_STRIDE + 3].  CTAs are dispatched in blockIdx order, so the long tiles start at once and the
+  // short ones fill the tail of the grid instead of the other way round.
+  __shared__ uint32_t bucket[64];
+  if (threadIdx.x < 64) bucket[threadIdx.x] = 0u;
+  __syncthreads();
+  const uint32_t scale = max_count > 0u ? max_count : 1u;
+  for (int t = threadIdx.x; t < tiles; t += SCAN_THREADS) {
+    const uint32_t c = tile_ctr[(size_t)t * TILE_CTR_STRIDE];
+    atomicAdd(&bucket[63u - (uint32_t)(((unsigned long long)c * 63ull) / scale)], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {   // exclusive scan of the 64 bucket sizes
+    const uint32_t a = bucket[2 * threadIdx.x], b = bucket[2 * threadIdx.x + 1];
+    uint32_t incl = a + b;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)threadIdx.x >= o) incl += up;
+    }
+    bucket[2 * threadIdx.x] = incl - a - b;
+    bucket[2 * threadIdx.x + 1] = incl - b;
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < tiles; t += SCAN_THREADS) {
+    const uint32_t c = tile_ctr[(size_t)t * TILE_CTR_STRIDE];
+    const uint32_t pos = atomicAdd(&bucket[63u - (uint32_t)(((unsigned long long)c * 63ull) / scale)], 1u);
+    tile_ctr[(size_t)pos * TILE_CTR_STRIDE + 3] = (uint32_t)t;
   }
 }
 
