@@ -261,6 +261,9 @@ typedef struct mgs_map_view {
   float rgb_boundary_threshold, alpha;
   int32_t update_stats;
   int32_t fast_math;        /* 1: ex2.approx exponent in this view's forward and backward blend (rel. error ~4e-7) */
+  int32_t slot;             /* 0 or 1: which copy of the per-view loss-gradient images in args->scratch this view uses, so
+                             * that the forward of one view may run beside the backward of another (different streams,
+                             * different workspaces, different slots) */
   float *out_color, *out_depth, *out_opacity;   /* f32[3,H,W], f32[1,H,W], f32[1,H,W] */
   int32_t *radii, *n_touched;                   /* i32[P] of THIS view (visibility filter, occ_aware_visibility) */
   float* tau;               /* f32[6]: pose tangent (rho, theta) of this view's loss, optional */
@@ -272,6 +275,12 @@ typedef struct mgs_map_view {
 size_t mgs_map_scratch_bytes(int32_t P, int32_t sh_coeffs, int32_t W_max, int32_t H_max);
 int mgs_map_begin(const mgs_map_args* args, void* stream);
 int mgs_map_view_fwd_bwd(const mgs_map_args* args, const mgs_map_view* view, void* stream);
+/* The two halves of mgs_map_view_fwd_bwd.  forward: preprocess, binning, blend + mapping loss (writes the view's
+ * workspace, radii, n_touched, loss, dab and slot `view->slot` of the loss-gradient images).  backward: backward blend +
+ * per-Gaussian backward accumulating into args' gradients and statistics, tau.  All backward calls of an iteration
+ * must be ordered among themselves (one stream); a forward may overlap the backward of another view. */
+int mgs_map_view_forward(const mgs_map_args* args, const mgs_map_view* view, void* stream);
+int mgs_map_view_backward(const mgs_map_args* args, const mgs_map_view* view, void* stream);
 /* add_regulariser: 1 on exactly one rank of a data-parallel group so the all-reduced sum counts the isotropic term
  * weight * mean|s - mean(s)| once (weight = 10 in the reference). */
 int mgs_map_end(const mgs_map_args* args, int32_t add_regulariser, float regulariser_weight, void* stream);

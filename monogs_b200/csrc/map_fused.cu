@@ -21,7 +21,7 @@ struct MapScratch {
   float *act_opacity, *act_scales, *act_rot, *act_shs;   // activated parameters (act_shs aliases f_dc when M == 1)
   float *d_opacity, *d_scales, *d_rot, *d_shs;           // activated-space gradient accumulators (d_shs: M > 1 only)
   void* bwd; size_t bwd_bytes;                           // per-Gaussian screen-space accumulator of the backward blend
-  float *g_img, *g_depth; double* partials;
+  float *g_img[2], *g_depth[2]; double* partials[2];    // two slots: forward of view k+1 may overlap backward of view k
   size_t total;
 };
 
@@ -40,8 +40,10 @@ static MapScratch carve_map_scratch(void* base, int P, int M, int W, int H) {
   m.d_shs = (float*)take(M > 1 ? Pp * M * 12 : 0);
   m.bwd_bytes = backward_scratch_bytes(P, 0);
   m.bwd = take(m.bwd_bytes);
-  m.g_img = (float*)take(3 * npix * 4); m.g_depth = (float*)take(npix * 4);
-  m.partials = (double*)take(tiles * 4 * 8);
+  for (int k = 0; k < 2; k++) {
+    m.g_img[k] = (float*)take(3 * npix * 4); m.g_depth[k] = (float*)take(npix * 4);
+    m.partials[k] = (double*)take(tiles * 4 * 8);
+  }
   m.total = off;
   return m;
 }
@@ -206,7 +208,10 @@ int mgs_map_begin(const mgs_map_args* a, void* stream) {
   return MGS_OK;
 }
 
-int mgs_map_view_fwd_bwd(const mgs_map_args* a, const mgs_map_view* mv, void* stream) {
+// shared validation + derived state of the two halves of a view
+struct MapViewCtx { ViewConst v; WsLayout L; MapScratch m; const float* shs; int P, M, tiles, use_depth, slot; size_t npix; };
+
+static int map_view_ctx(const mgs_map_args* a, const mgs_map_view* mv, MapViewCtx* c) {
   int rc = check_map_args(a);
   if (rc) return rc;
   if (!mv) { set_error("map: view is null"); return MGS_EINVAL; }
@@ -218,55 +223,79 @@ int mgs_map_view_fwd_bwd(const mgs_map_args* a, const mgs_map_view* mv, void* st
   }
   if ((mv->exposure_a == nullptr) != (mv->exposure_b == nullptr)) { set_error("map: give both exposure parameters or neither"); return MGS_EINVAL; }
   if (mv->R_cap <= 0 || mv->R_cap > 0x7fffffffLL) { set_error("map: bad R_cap"); return MGS_EINVAL; }
+  if (mv->slot < 0 || mv->slot > 1) { set_error("map: slot must be 0 or 1"); return MGS_EINVAL; }
+  const mgs_gaussians& g = a->g;
+  c->P = g.P; c->M = g.sh_coeffs; c->slot = mv->slot;
+  const int W = view->image_width, H = view->image_height;
+  if (c->P == 0) return MGS_OK;
+  c->m = carve_map_scratch(a->scratch, c->P, c->M, W, H);
+  if (a->scratch_bytes < c->m.total) { set_error("map: scratch too small for this view: %zu < %zu", a->scratch_bytes, c->m.total); return MGS_ENOSPC; }
+  if ((rc = ws_layout(c->P, W, H, mv->R_cap, &c->L))) return rc;
+  if (mv->workspace_bytes < c->L.total) { set_error("map: workspace too small: %zu < %zu", mv->workspace_bytes, c->L.total); return MGS_ENOSPC; }
+  mgs_view vv = *view;
+  vv.sh_degree = g.sh_degree; vv.sh_coeffs = c->M;
+  if (g.sh_degree > 0 && !vv.campos) { set_error("map: campos required for sh_degree > 0"); return MGS_EINVAL; }
+  c->v = make_view_const(&vv);
+  c->npix = (size_t)W * H;
+  c->tiles = c->v.gx * c->v.gy;
+  c->use_depth = mv->gt_depth != nullptr;
+  c->shs = c->M > 1 ? c->m.act_shs : g.f_dc;
+  return MGS_OK;
+}
+
+int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* stream) {
+  MapViewCtx c;
+  int rc = map_view_ctx(a, mv, &c);
+  if (rc) return rc;
+  if (c.P == 0) return MGS_OK;
   cudaStream_t s = (cudaStream_t)stream;
   const mgs_gaussians& g = a->g;
-  const int P = g.P, M = g.sh_coeffs, W = view->image_width, H = view->image_height;
-  if (P == 0) return MGS_OK;
-  const MapScratch m = carve_map_scratch(a->scratch, P, M, W, H);
-  if (a->scratch_bytes < m.total) { set_error("map: scratch too small for this view: %zu < %zu", a->scratch_bytes, m.total); return MGS_ENOSPC; }
-  WsLayout L;
-  if ((rc = ws_layout(P, W, H, mv->R_cap, &L))) return rc;
-  if (mv->workspace_bytes < L.total) { set_error("map: workspace too small: %zu < %zu", mv->workspace_bytes, L.total); return MGS_ENOSPC; }
-  mgs_view vv = *view;
-  vv.sh_degree = g.sh_degree; vv.sh_coeffs = M;
-  if (g.sh_degree > 0 && !vv.campos) { set_error("map: campos required for sh_degree > 0"); return MGS_EINVAL; }
-  const ViewConst v = make_view_const(&vv);
-  const size_t npix = (size_t)W * H;
-  const int tiles = v.gx * v.gy;
-  const int use_depth = mv->gt_depth != nullptr;
-  const float* shs = M > 1 ? m.act_shs : g.f_dc;
+  const MapScratch& m = c.m;
   void* ws = mv->workspace;
-
-  if ((rc = launch_preprocess(v, P, g.xyz, m.act_opacity, shs, nullptr, m.act_scales, m.act_rot, nullptr, mv->radii, ws, L, s))) return rc;
-  MGS_CUDA_TRY(cudaMemsetAsync(mv->n_touched, 0, (size_t)P * sizeof(int32_t), s));
-  if ((rc = launch_binning(v, P, nullptr, mv->radii, ws, L, mv->R_cap, s))) return rc;
+  if ((rc = launch_preprocess(c.v, c.P, g.xyz, m.act_opacity, c.shs, nullptr, m.act_scales, m.act_rot, nullptr, mv->radii, ws, c.L, s))) return rc;
+  MGS_CUDA_TRY(cudaMemsetAsync(mv->n_touched, 0, (size_t)c.P * sizeof(int32_t), s));
+  if ((rc = launch_binning(c.v, c.P, nullptr, mv->radii, ws, c.L, mv->R_cap, s))) return rc;
 
   LossK lk;
-  lk.mode = MGS_LOSS_MAP_L1; lk.npix = (int)npix; lk.use_depth = use_depth;
+  lk.mode = MGS_LOSS_MAP_L1; lk.npix = (int)c.npix; lk.use_depth = c.use_depth;
   lk.thr = mv->rgb_boundary_threshold; lk.alpha = mv->alpha; lk.delta = 0.f; lk.scale = 1.f; lk.eps = 1e-8f;
   lk.image = nullptr; lk.depth = nullptr; lk.opacity = nullptr; lk.gt = mv->gt_image; lk.gt_depth = mv->gt_depth;
   lk.mask = nullptr; lk.a = mv->exposure_a; lk.b = mv->exposure_b;
   FusedLoss fl;
-  fl.k = &lk; fl.grad_scale = (use_depth ? mv->alpha : 1.f) / (3.f * (float)npix);
-  fl.g_img = m.g_img; fl.g_depth = m.g_depth; fl.partials = m.partials; fl.fast = mv->fast_math != 0;
-  if ((rc = launch_blend_forward(v, ws, L, mv->out_color, mv->out_depth, mv->out_opacity, mv->n_touched, s, &fl))) return rc;
-  MGS_PROF("map_loss_finalize", s, map_loss_finalize_kernel<<<1, 256, 0, s>>>(m.partials, tiles, (int)npix, use_depth, mv->alpha,
+  fl.k = &lk; fl.grad_scale = (c.use_depth ? mv->alpha : 1.f) / (3.f * (float)c.npix);
+  fl.g_img = m.g_img[c.slot]; fl.g_depth = m.g_depth[c.slot]; fl.partials = m.partials[c.slot]; fl.fast = mv->fast_math != 0;
+  if ((rc = launch_blend_forward(c.v, ws, c.L, mv->out_color, mv->out_depth, mv->out_opacity, mv->n_touched, s, &fl))) return rc;
+  MGS_PROF("map_loss_finalize", s, map_loss_finalize_kernel<<<1, 256, 0, s>>>(m.partials[c.slot], c.tiles, (int)c.npix, c.use_depth, mv->alpha,
                                                                              mv->loss, a->loss_total, mv->dab));
   MGS_LAUNCH_CHECK();
+  return MGS_OK;
+}
 
+int mgs_map_view_backward(const mgs_map_args* a, const mgs_map_view* mv, void* stream) {
+  MapViewCtx c;
+  int rc = map_view_ctx(a, mv, &c);
+  if (rc) return rc;
+  if (c.P == 0) return MGS_OK;
+  const mgs_gaussians& g = a->g;
+  const MapScratch& m = c.m;
   BackwardArgs b;
   memset(&b, 0, sizeof(b));
-  b.v = v; b.P = P;
+  b.v = c.v; b.P = c.P;
   b.grad_mask = MGS_GRAD_MEANS3D | MGS_GRAD_COLOR | MGS_GRAD_OPACITY | MGS_GRAD_COV | (mv->tau ? MGS_GRAD_TAU : 0u);
-  b.means3D = g.xyz; b.shs = shs; b.scales = m.act_scales; b.rotations = m.act_rot; b.radii = mv->radii;
-  b.ws = ws; b.L = L; b.scratch = m.bwd; b.scratch_bytes = m.bwd_bytes;
-  b.dL_dcolor_img = m.g_img; b.dL_ddepth_img = m.g_depth;
-  b.dL_dmeans3D = a->grad_xyz; b.dL_dcolors_or_sh = M > 1 ? m.d_shs : a->grad_f_dc; b.dL_dopacity = m.d_opacity;
+  b.means3D = g.xyz; b.shs = c.shs; b.scales = m.act_scales; b.rotations = m.act_rot; b.radii = mv->radii;
+  b.ws = mv->workspace; b.L = c.L; b.scratch = m.bwd; b.scratch_bytes = m.bwd_bytes;
+  b.dL_dcolor_img = m.g_img[c.slot]; b.dL_ddepth_img = m.g_depth[c.slot];
+  b.dL_dmeans3D = a->grad_xyz; b.dL_dcolors_or_sh = c.M > 1 ? m.d_shs : a->grad_f_dc; b.dL_dopacity = m.d_opacity;
   b.dL_dscales = m.d_scales; b.dL_drotations = m.d_rot; b.dL_dtau_sum = mv->tau;
   b.accumulate = 1;
   if (mv->update_stats) { b.stat_grad_accum = a->xyz_gradient_accum; b.stat_denom = a->denom; b.stat_max_radii = a->max_radii2D; }
   b.fast = mv->fast_math != 0;
-  return launch_backward_full(b, s);
+  return launch_backward_full(b, (cudaStream_t)stream);
+}
+
+int mgs_map_view_fwd_bwd(const mgs_map_args* a, const mgs_map_view* mv, void* stream) {
+  const int rc = mgs_map_view_forward(a, mv, stream);
+  return rc ? rc : mgs_map_view_backward(a, mv, stream);
 }
 
 int mgs_map_end(const mgs_map_args* a, int32_t add_regulariser, float regulariser_weight, void* stream) {

@@ -125,10 +125,14 @@ class MapEngine:
 
     def __init__(self, params: Dict[str, torch.Tensor], lrs: Dict[str, float], sh_degree: int = 0, W: int = 640, H: int = 480,
                  capacity_headroom: float = 2.0, group=None, regulariser_weight: float = 10.0,
-                 rgb_boundary_threshold: float = 0.01, alpha: float = 0.95, fast_math: bool = True):
+                 rgb_boundary_threshold: float = 0.01, alpha: float = 0.95, fast_math: bool = True, overlap: bool = True):
         from . import _lib as L
         from .ops import FusedAdam
         self.fast_math = fast_math   # ex2.approx exponent in the blend kernels (relative error ~4e-7), like PoseTracker
+        # overlap: the forward half of view k+1 (preprocess, binning, blend + loss) runs on the caller's stream beside the
+        # backward half of view k on a second stream; two workspaces and two loss-gradient slots alternate
+        self.overlap = overlap
+        self._bwd_stream = None
         self.L, self.lib = L, L.lib()
         self.params = {k: params[k] for k in self.NAMES if k in params and params[k] is not None and params[k].numel() > 0}
         self.dev = self.params["xyz"].device
@@ -150,7 +154,7 @@ class MapEngine:
         self.scratch = torch.empty(self.lib.mgs_map_scratch_bytes(self.P, self.M, W, H), device=self.dev, dtype=torch.uint8)
         self.color, self.depth, self.opacity = torch.empty(3, H, W, **f), torch.empty(1, H, W, **f), torch.empty(1, H, W, **f)
         self.headroom = capacity_headroom
-        self.R_cap, self.ws = 0, None
+        self.R_cap, self.ws, self.ws2 = 0, None, None
         self.reg_weight, self.thr, self.alpha = regulariser_weight, rgb_boundary_threshold, alpha
         self.group = group
         self.distributed = dist.is_available() and dist.is_initialized()
@@ -202,6 +206,7 @@ class MapEngine:
         torch.cuda.current_stream().synchronize()
         self.R_cap = max(int(int(n_host.item()) * self.headroom) + 4096, 4096)
         self.ws = torch.empty(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev, dtype=torch.uint8)
+        self.ws2 = torch.zeros_like(self.ws) if self.overlap else None   # zeroed: its header may be queried before first use
 
     def _slot(self, i):
         """Per-view output buffers (kept across iterations: the same window is mapped many times)."""
@@ -213,8 +218,8 @@ class MapEngine:
                                                torch.zeros(1, device=self.dev))
         return s
 
-    def render_backward_view(self, args, view: MapView, slot: MapViewResult):
-        from .rasterizer import make_view, _stream
+    def _view_desc(self, view: MapView, slot: MapViewResult, k: int = 0):
+        from .rasterizer import make_view
         L = self.L
         mv = L.MgsMapView()
         keep = []
@@ -225,12 +230,44 @@ class MapEngine:
         mv.exposure_a = view.exposure_a.data_ptr() if view.exposure_a is not None else None
         mv.exposure_b = view.exposure_b.data_ptr() if view.exposure_b is not None else None
         mv.rgb_boundary_threshold, mv.alpha, mv.update_stats = self.thr, self.alpha, int(view.update_stats)
-        mv.fast_math = int(self.fast_math)
+        mv.fast_math, mv.slot = int(self.fast_math), k & 1
         mv.out_color, mv.out_depth, mv.out_opacity = self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr()
         mv.radii, mv.n_touched = slot.radii.data_ptr(), slot.n_touched.data_ptr()
         mv.tau, mv.dab, mv.loss = slot.tau.data_ptr(), slot.dab.data_ptr(), slot.loss.data_ptr()
-        mv.workspace, mv.workspace_bytes, mv.R_cap = self.ws.data_ptr(), self.ws.numel(), self.R_cap
-        L.check(self.lib.mgs_map_view_fwd_bwd(C.byref(args), C.byref(mv), _stream()), "mgs_map_view_fwd_bwd")
+        ws = self.ws2 if (k & 1) and self.ws2 is not None else self.ws
+        mv.workspace, mv.workspace_bytes, mv.R_cap = ws.data_ptr(), ws.numel(), self.R_cap
+        return mv
+
+    def render_backward_view(self, args, view: MapView, slot: MapViewResult):
+        """One view, forward and backward back to back on the current stream."""
+        from .rasterizer import _stream
+        mv = self._view_desc(view, slot, 0)
+        self.L.check(self.lib.mgs_map_view_fwd_bwd(C.byref(args), C.byref(mv), _stream()), "mgs_map_view_fwd_bwd")
+
+    def _views_overlapped(self, args, todo):
+        """forward(k) on the current stream, backward(k) on the second stream after it; forward(k+2) waits for
+        backward(k) because it reuses that view's workspace and loss-gradient slot.  Backward calls are ordered among
+        themselves (they accumulate into the same gradients)."""
+        L, lib = self.L, self.lib
+        main = torch.cuda.current_stream()
+        if self._bwd_stream is None:
+            self._bwd_stream = torch.cuda.Stream(device=self.dev)
+        side = self._bwd_stream
+        bwd_done = []
+        for k, (view, slot) in enumerate(todo):
+            mv = self._view_desc(view, slot, k)
+            if k >= 2:
+                main.wait_event(bwd_done[k - 2])
+            L.check(lib.mgs_map_view_forward(C.byref(args), C.byref(mv), C.c_void_p(main.cuda_stream)), "mgs_map_view_forward")
+            ev = torch.cuda.Event()
+            ev.record(main)
+            side.wait_event(ev)
+            L.check(lib.mgs_map_view_backward(C.byref(args), C.byref(mv), C.c_void_p(side.cuda_stream)), "mgs_map_view_backward")
+            ev = torch.cuda.Event()
+            ev.record(side)
+            bwd_done.append(ev)
+        if bwd_done:
+            main.wait_event(bwd_done[-1])
 
     def backward_only(self, views: Sequence[MapView]) -> Dict[int, MapViewResult]:
         """Everything of an iteration up to the raw-parameter gradients of THIS rank's views (no exchange, no Adam)."""
@@ -243,10 +280,14 @@ class MapEngine:
         self._ensure_capacity(views[0])
         L.check(self.lib.mgs_map_begin(C.byref(args), _stream()), "mgs_map_begin")
         out = {}
-        for i in shard_views(len(views), self.world, self.rank):
-            slot = self._slot(i)
-            self.render_backward_view(args, views[i], slot)
-            out[i] = slot
+        mine = list(shard_views(len(views), self.world, self.rank))
+        for i in mine:
+            out[i] = self._slot(i)
+        if self.overlap and len(mine) > 1:
+            self._views_overlapped(args, [(views[i], out[i]) for i in mine])
+        else:
+            for i in mine:
+                self.render_backward_view(args, views[i], out[i])
         L.check(self.lib.mgs_map_end(C.byref(args), int(self.rank == 0), self.reg_weight, _stream()), "mgs_map_end")
         return out
 
@@ -268,14 +309,18 @@ class MapEngine:
             dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=self.group)
 
     def check_capacity(self):
-        """Synchronous check of the device-side overflow flag of the last rendered view; regrows on overflow."""
+        """Synchronous check of the device-side overflow flag of the last rendered view(s); regrows on overflow."""
         from .rasterizer import _stream
-        n, ov = C.c_int32(0), C.c_int32(0)
-        self.L.check(self.lib.mgs_raster_query(self.L.ptr(self.ws), C.byref(n), C.byref(ov), _stream()), "mgs_raster_query")
-        if ov.value:
+        n_max, over = 0, False
+        for ws in (self.ws, self.ws2):
+            if ws is None: continue
+            n, ov = C.c_int32(0), C.c_int32(0)
+            self.L.check(self.lib.mgs_raster_query(self.L.ptr(ws), C.byref(n), C.byref(ov), _stream()), "mgs_raster_query")
+            n_max, over = max(n_max, n.value), over or bool(ov.value)
+        if over:
             self.headroom *= 1.5
-            self.ws = None
-        return n.value, bool(ov.value)
+            self.ws = self.ws2 = None
+        return n_max, over
 
     # ------------------------------------------------------------------------------------------------
     def _adam_moments(self):
