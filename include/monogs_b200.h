@@ -261,7 +261,7 @@ typedef struct mgs_map_view {
   float rgb_boundary_threshold, alpha;
   int32_t update_stats;
   int32_t fast_math;        /* 1: ex2.approx exponent in this view's forward and backward blend (rel. error ~4e-7) */
-  int32_t slot;             /* 0 or 1: which copy of the per-view loss-gradient images in args->scratch this view uses, so
+  int32_t slot;             /* 0..3: which copy of the per-view loss-gradient images in args->scratch this view uses, so
                              * that the forward of one view may run beside the backward of another (different streams,
                              * different workspaces, different slots) */
   float *out_color, *out_depth, *out_opacity;   /* f32[3,H,W], f32[1,H,W], f32[1,H,W] */
@@ -278,7 +278,8 @@ int mgs_map_view_fwd_bwd(const mgs_map_args* args, const mgs_map_view* view, voi
 /* The two halves of mgs_map_view_fwd_bwd.  forward: preprocess, binning, blend + mapping loss (writes the view's
  * workspace, radii, n_touched, loss, dab and slot `view->slot` of the loss-gradient images).  backward: backward blend +
  * per-Gaussian backward accumulating into args' gradients and statistics, tau.  All backward calls of an iteration
- * must be ordered among themselves (one stream); a forward may overlap the backward of another view. */
+ * must be ordered among themselves (one stream); a forward may overlap the backward or the forward of another view
+ * (different streams, workspaces, slots and output images). */
 int mgs_map_view_forward(const mgs_map_args* args, const mgs_map_view* view, void* stream);
 int mgs_map_view_backward(const mgs_map_args* args, const mgs_map_view* view, void* stream);
 /* add_regulariser: 1 on exactly one rank of a data-parallel group so the all-reduced sum counts the isotropic term

@@ -17,11 +17,13 @@
 
 namespace mgs {
 
+constexpr int MAP_SLOTS = 4;
+
 struct MapScratch {
   float *act_opacity, *act_scales, *act_rot, *act_shs;   // activated parameters (act_shs aliases f_dc when M == 1)
   float *d_opacity, *d_scales, *d_rot, *d_shs;           // activated-space gradient accumulators (d_shs: M > 1 only)
   void* bwd; size_t bwd_bytes;                           // per-Gaussian screen-space accumulator of the backward blend
-  float *g_img[2], *g_depth[2]; double* partials[2];    // two slots: forward of view k+1 may overlap backward of view k
+  float *g_img[MAP_SLOTS], *g_depth[MAP_SLOTS]; double* partials[MAP_SLOTS];   // forwards of later views may overlap the backward of an earlier one
   size_t total;
 };
 
@@ -40,7 +42,7 @@ static MapScratch carve_map_scratch(void* base, int P, int M, int W, int H) {
   m.d_shs = (float*)take(M > 1 ? Pp * M * 12 : 0);
   m.bwd_bytes = backward_scratch_bytes(P, 0);
   m.bwd = take(m.bwd_bytes);
-  for (int k = 0; k < 2; k++) {
+  for (int k = 0; k < MAP_SLOTS; k++) {
     m.g_img[k] = (float*)take(3 * npix * 4); m.g_depth[k] = (float*)take(npix * 4);
     m.partials[k] = (double*)take(tiles * 4 * 8);
   }
@@ -109,7 +111,7 @@ map_loss_finalize_kernel(const double* __restrict__ partials, const int tiles, c
     const double rgb = sh[0][0] / (3.0 * npix), dep = sh[0][3] / (double)npix;
     const float l = (float)(use_depth ? alpha * rgb + (1.0 - alpha) * dep : rgb);
     if (loss_view) loss_view[0] = l;
-    loss_total[0] += l;   // views are stream-ordered: no race
+    atomicAdd(loss_total, l);   // forwards of different views may run on different streams
     if (dab) { dab[0] = (float)sh[0][1]; dab[1] = (float)sh[0][2]; }
   }
 }
@@ -223,7 +225,7 @@ static int map_view_ctx(const mgs_map_args* a, const mgs_map_view* mv, MapViewCt
   }
   if ((mv->exposure_a == nullptr) != (mv->exposure_b == nullptr)) { set_error("map: give both exposure parameters or neither"); return MGS_EINVAL; }
   if (mv->R_cap <= 0 || mv->R_cap > 0x7fffffffLL) { set_error("map: bad R_cap"); return MGS_EINVAL; }
-  if (mv->slot < 0 || mv->slot > 1) { set_error("map: slot must be 0 or 1"); return MGS_EINVAL; }
+  if (mv->slot < 0 || mv->slot >= MAP_SLOTS) { set_error("map: slot must be in [0, %d)", MAP_SLOTS); return MGS_EINVAL; }
   const mgs_gaussians& g = a->g;
   c->P = g.P; c->M = g.sh_coeffs; c->slot = mv->slot;
   const int W = view->image_width, H = view->image_height;

@@ -132,7 +132,8 @@ class MapEngine:
         # overlap: the forward half of view k+1 (preprocess, binning, blend + loss) runs on the caller's stream beside the
         # backward half of view k on a second stream; two workspaces and two loss-gradient slots alternate
         self.overlap = overlap
-        self._bwd_stream = None
+        self._bwd_stream = self._fwd2_stream = None
+        self.n_pipe = 3             # workspaces / slots in flight: two forwards + one backward
         self.L, self.lib = L, L.lib()
         self.params = {k: params[k] for k in self.NAMES if k in params and params[k] is not None and params[k].numel() > 0}
         self.dev = self.params["xyz"].device
@@ -153,8 +154,9 @@ class MapEngine:
         self.W, self.H = W, H
         self.scratch = torch.empty(self.lib.mgs_map_scratch_bytes(self.P, self.M, W, H), device=self.dev, dtype=torch.uint8)
         self.color, self.depth, self.opacity = torch.empty(3, H, W, **f), torch.empty(1, H, W, **f), torch.empty(1, H, W, **f)
+        self._out_extra = []
         self.headroom = capacity_headroom
-        self.R_cap, self.ws, self.ws2 = 0, None, None
+        self.R_cap, self.ws, self.ws_extra = 0, None, []
         self.reg_weight, self.thr, self.alpha = regulariser_weight, rgb_boundary_threshold, alpha
         self.group = group
         self.distributed = dist.is_available() and dist.is_initialized()
@@ -206,7 +208,7 @@ class MapEngine:
         torch.cuda.current_stream().synchronize()
         self.R_cap = max(int(int(n_host.item()) * self.headroom) + 4096, 4096)
         self.ws = torch.empty(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev, dtype=torch.uint8)
-        self.ws2 = torch.zeros_like(self.ws) if self.overlap else None   # zeroed: its header may be queried before first use
+        self.ws_extra, self._out_extra = [], []
 
     def _slot(self, i):
         """Per-view output buffers (kept across iterations: the same window is mapped many times)."""
@@ -230,11 +232,16 @@ class MapEngine:
         mv.exposure_a = view.exposure_a.data_ptr() if view.exposure_a is not None else None
         mv.exposure_b = view.exposure_b.data_ptr() if view.exposure_b is not None else None
         mv.rgb_boundary_threshold, mv.alpha, mv.update_stats = self.thr, self.alpha, int(view.update_stats)
-        mv.fast_math, mv.slot = int(self.fast_math), k & 1
-        mv.out_color, mv.out_depth, mv.out_opacity = self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr()
+        r = k % self.n_pipe if self.overlap else 0      # resource set of this view: workspace, slot, output images
+        while r > len(self.ws_extra):                   # allocated on first use: a one-view iteration needs only self.ws
+            self.ws_extra.append(torch.zeros_like(self.ws))
+            self._out_extra.append((torch.empty_like(self.color), torch.empty_like(self.depth), torch.empty_like(self.opacity)))
+        ws = self.ws if r == 0 else self.ws_extra[r - 1]
+        color, depth, opacity = (self.color, self.depth, self.opacity) if r == 0 else self._out_extra[r - 1]
+        mv.fast_math, mv.slot = int(self.fast_math), r
+        mv.out_color, mv.out_depth, mv.out_opacity = color.data_ptr(), depth.data_ptr(), opacity.data_ptr()
         mv.radii, mv.n_touched = slot.radii.data_ptr(), slot.n_touched.data_ptr()
         mv.tau, mv.dab, mv.loss = slot.tau.data_ptr(), slot.dab.data_ptr(), slot.loss.data_ptr()
-        ws = self.ws2 if (k & 1) and self.ws2 is not None else self.ws
         mv.workspace, mv.workspace_bytes, mv.R_cap = ws.data_ptr(), ws.numel(), self.R_cap
         return mv
 
@@ -245,22 +252,26 @@ class MapEngine:
         self.L.check(self.lib.mgs_map_view_fwd_bwd(C.byref(args), C.byref(mv), _stream()), "mgs_map_view_fwd_bwd")
 
     def _views_overlapped(self, args, todo):
-        """forward(k) on the current stream, backward(k) on the second stream after it; forward(k+2) waits for
-        backward(k) because it reuses that view's workspace and loss-gradient slot.  Backward calls are ordered among
-        themselves (they accumulate into the same gradients)."""
+        """forward(k) alternates between the caller's stream and a second forward stream, backward(k) follows it on the
+        backward stream; forward(k + n_pipe) waits for backward(k) because it reuses that view's workspace, loss-gradient
+        slot and output images.  Backward calls are ordered among themselves (they accumulate into the same gradients)."""
         L, lib = self.L, self.lib
         main = torch.cuda.current_stream()
         if self._bwd_stream is None:
-            self._bwd_stream = torch.cuda.Stream(device=self.dev)
-        side = self._bwd_stream
+            self._bwd_stream, self._fwd2_stream = torch.cuda.Stream(device=self.dev), torch.cuda.Stream(device=self.dev)
+        side, fwd = self._bwd_stream, (main, self._fwd2_stream)
+        begin = torch.cuda.Event()
+        begin.record(main)                       # mgs_map_begin (activations, zeroed accumulators) is on the caller's stream
+        fwd[1].wait_event(begin)
         bwd_done = []
         for k, (view, slot) in enumerate(todo):
             mv = self._view_desc(view, slot, k)
-            if k >= 2:
-                main.wait_event(bwd_done[k - 2])
-            L.check(lib.mgs_map_view_forward(C.byref(args), C.byref(mv), C.c_void_p(main.cuda_stream)), "mgs_map_view_forward")
+            f = fwd[k & 1]
+            if k >= self.n_pipe:
+                f.wait_event(bwd_done[k - self.n_pipe])
+            L.check(lib.mgs_map_view_forward(C.byref(args), C.byref(mv), C.c_void_p(f.cuda_stream)), "mgs_map_view_forward")
             ev = torch.cuda.Event()
-            ev.record(main)
+            ev.record(f)
             side.wait_event(ev)
             L.check(lib.mgs_map_view_backward(C.byref(args), C.byref(mv), C.c_void_p(side.cuda_stream)), "mgs_map_view_backward")
             ev = torch.cuda.Event()
@@ -312,14 +323,14 @@ class MapEngine:
         """Synchronous check of the device-side overflow flag of the last rendered view(s); regrows on overflow."""
         from .rasterizer import _stream
         n_max, over = 0, False
-        for ws in (self.ws, self.ws2):
+        for ws in [self.ws] + list(self.ws_extra):
             if ws is None: continue
             n, ov = C.c_int32(0), C.c_int32(0)
             self.L.check(self.lib.mgs_raster_query(self.L.ptr(ws), C.byref(n), C.byref(ov), _stream()), "mgs_raster_query")
             n_max, over = max(n_max, n.value), over or bool(ov.value)
         if over:
             self.headroom *= 1.5
-            self.ws = self.ws2 = None
+            self.ws, self.ws_extra = None, []
         return n_max, over
 
     # ------------------------------------------------------------------------------------------------
