@@ -264,6 +264,8 @@ typedef struct mgs_map_view {
   int32_t slot;             /* 0..3: which copy of the per-view loss-gradient images in args->scratch this view uses, so
                              * that the forward of one view may run beside the backward of another (different streams,
                              * different workspaces, different slots) */
+  int32_t concurrent_backward; /* 1: this view's backward accumulates gradients and statistics with atomics, so that
+                             * backward calls of different views (different slots) may run on different streams */
   float *out_color, *out_depth, *out_opacity;   /* f32[3,H,W], f32[1,H,W], f32[1,H,W] */
   int32_t *radii, *n_touched;                   /* i32[P] of THIS view (visibility filter, occ_aware_visibility) */
   float* tau;               /* f32[6]: pose tangent (rho, theta) of this view's loss, optional */
@@ -278,7 +280,7 @@ int mgs_map_view_fwd_bwd(const mgs_map_args* args, const mgs_map_view* view, voi
 /* The two halves of mgs_map_view_fwd_bwd.  forward: preprocess, binning, blend + mapping loss (writes the view's
  * workspace, radii, n_touched, loss, dab and slot `view->slot` of the loss-gradient images).  backward: backward blend +
  * per-Gaussian backward accumulating into args' gradients and statistics, tau.  All backward calls of an iteration
- * must be ordered among themselves (one stream); a forward may overlap the backward or the forward of another view
+  * must be ordered among themselves (one stream) unless every view sets concurrent_backward; a forward may overlap the backward or the forward of another view
  * (different streams, workspaces, slots and output images). */
 int mgs_map_view_forward(const mgs_map_args* args, const mgs_map_view* view, void* stream);
 int mgs_map_view_backward(const mgs_map_args* args, const mgs_map_view* view, void* stream);

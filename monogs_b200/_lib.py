@@ -84,7 +84,7 @@ class MgsMapView(C.Structure):
     _fields_ = [
         ("view", MgsView),
         ("gt_image", C.c_void_p), ("gt_depth", C.c_void_p), ("exposure_a", C.c_void_p), ("exposure_b", C.c_void_p),
-        ("rgb_boundary_threshold", C.c_float), ("alpha", C.c_float), ("update_stats", C.c_int32), ("fast_math", C.c_int32), ("slot", C.c_int32),
+        ("rgb_boundary_threshold", C.c_float), ("alpha", C.c_float), ("update_stats", C.c_int32), ("fast_math", C.c_int32), ("slot", C.c_int32), ("concurrent_backward", C.c_int32),
         ("out_color", C.c_void_p), ("out_depth", C.c_void_p), ("out_opacity", C.c_void_p),
         ("radii", C.c_void_p), ("n_touched", C.c_void_p),
         ("tau", C.c_void_p), ("dab", C.c_void_p), ("loss", C.c_void_p),

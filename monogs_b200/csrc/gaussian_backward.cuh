@@ -174,7 +174,7 @@ __device__ __forceinline__ void mean2d_tau_jac(const ProjCtx& q, const float* __
 // the caller) and returns dL/dmean through the view direction.  dcol must already carry the clamp mask.
 __device__ __forceinline__ float3 sh_backward(int deg, int M, const float3& pos, const float* __restrict__ campos,
                                               const float* __restrict__ sh, const float3 dcol,
-                                              float* __restrict__ dsh /* may be null */, const bool accumulate = false) {
+                                              float* __restrict__ dsh /* may be null */, const int accumulate = 0 /* 1: +=, 2: atomicAdd */) {
   const float3 dir_orig = {pos.x - campos[0], pos.y - campos[1], pos.z - campos[2]};
   const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
   const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;
@@ -213,7 +213,9 @@ __device__ __forceinline__ float3 sh_backward(int deg, int M, const float3& pos,
     }
   }
   const int n = (deg + 1) * (deg + 1);
-  if (dsh != nullptr && accumulate) {   // mapping window: gradients of several views summed in place
+  if (dsh != nullptr && accumulate == 2) {   // views of a mapping window running concurrently
+    for (int k = 0; k < n; k++) { atomicAdd(dsh + 3 * k, w[k] * dcol.x); atomicAdd(dsh + 3 * k + 1, w[k] * dcol.y); atomicAdd(dsh + 3 * k + 2, w[k] * dcol.z); }
+  } else if (dsh != nullptr && accumulate) {   // mapping window: gradients of several views summed in place
     for (int k = 0; k < n; k++) { dsh[3 * k] += w[k] * dcol.x; dsh[3 * k + 1] += w[k] * dcol.y; dsh[3 * k + 2] += w[k] * dcol.z; }
   } else if (dsh != nullptr) {
     for (int k = 0; k < n; k++) { dsh[3 * k] = w[k] * dcol.x; dsh[3 * k + 1] = w[k] * dcol.y; dsh[3 * k + 2] = w[k] * dcol.z; }

@@ -22,7 +22,7 @@ constexpr int MAP_SLOTS = 4;
 struct MapScratch {
   float *act_opacity, *act_scales, *act_rot, *act_shs;   // activated parameters (act_shs aliases f_dc when M == 1)
   float *d_opacity, *d_scales, *d_rot, *d_shs;           // activated-space gradient accumulators (d_shs: M > 1 only)
-  void* bwd; size_t bwd_bytes;                           // per-Gaussian screen-space accumulator of the backward blend
+  void* bwd[MAP_SLOTS]; size_t bwd_bytes;                // per-Gaussian screen-space accumulator of the backward blend, per slot
   float *g_img[MAP_SLOTS], *g_depth[MAP_SLOTS]; double* partials[MAP_SLOTS];   // forwards of later views may overlap the backward of an earlier one
   size_t total;
 };
@@ -41,7 +41,7 @@ static MapScratch carve_map_scratch(void* base, int P, int M, int W, int H) {
   m.d_opacity = (float*)take(Pp * 4); m.d_scales = (float*)take(Pp * 12); m.d_rot = (float*)take(Pp * 16);
   m.d_shs = (float*)take(M > 1 ? Pp * M * 12 : 0);
   m.bwd_bytes = backward_scratch_bytes(P, 0);
-  m.bwd = take(m.bwd_bytes);
+  for (int k = 0; k < MAP_SLOTS; k++) m.bwd[k] = take(m.bwd_bytes);
   for (int k = 0; k < MAP_SLOTS; k++) {
     m.g_img[k] = (float*)take(3 * npix * 4); m.g_depth[k] = (float*)take(npix * 4);
     m.partials[k] = (double*)take(tiles * 4 * 8);
@@ -285,11 +285,11 @@ int mgs_map_view_backward(const mgs_map_args* a, const mgs_map_view* mv, void* s
   b.v = c.v; b.P = c.P;
   b.grad_mask = MGS_GRAD_MEANS3D | MGS_GRAD_COLOR | MGS_GRAD_OPACITY | MGS_GRAD_COV | (mv->tau ? MGS_GRAD_TAU : 0u);
   b.means3D = g.xyz; b.shs = c.shs; b.scales = m.act_scales; b.rotations = m.act_rot; b.radii = mv->radii;
-  b.ws = mv->workspace; b.L = c.L; b.scratch = m.bwd; b.scratch_bytes = m.bwd_bytes;
+  b.ws = mv->workspace; b.L = c.L; b.scratch = m.bwd[c.slot]; b.scratch_bytes = m.bwd_bytes;
   b.dL_dcolor_img = m.g_img[c.slot]; b.dL_ddepth_img = m.g_depth[c.slot];
   b.dL_dmeans3D = a->grad_xyz; b.dL_dcolors_or_sh = c.M > 1 ? m.d_shs : a->grad_f_dc; b.dL_dopacity = m.d_opacity;
   b.dL_dscales = m.d_scales; b.dL_drotations = m.d_rot; b.dL_dtau_sum = mv->tau;
-  b.accumulate = 1;
+  b.accumulate = mv->concurrent_backward ? 2 : 1;
   if (mv->update_stats) { b.stat_grad_accum = a->xyz_gradient_accum; b.stat_denom = a->denom; b.stat_max_radii = a->max_radii2D; }
   b.fast = mv->fast_math != 0;
   return launch_backward_full(b, (cudaStream_t)stream);

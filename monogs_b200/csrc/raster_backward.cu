@@ -301,7 +301,7 @@ preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
       if (shs != nullptr) {
         const uint32_t cm = __float_as_uint(rgb4[idx].w);
         const float3 dcol = {(cm & 1u) ? 0.f : gg.r, (cm & 2u) ? 0.f : gg.g, (cm & 4u) ? 0.f : gg.b};
-        const float3 dms = sh_backward(v.D, Msh, p, v.campos, shs + (size_t)idx * Msh * 3, dcol, dsh, accumulate != 0);
+        const float3 dms = sh_backward(v.D, Msh, p, v.campos, shs + (size_t)idx * Msh * 3, dcol, dsh, accumulate);
         dmean.x += dms.x; dmean.y += dms.y; dmean.z += dms.z;
         tau[0] += -dms.x; tau[1] += -dms.y; tau[2] += -dms.z;
       }
@@ -311,21 +311,30 @@ preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
     }
     if (accumulate) {
       if (vis) {   // sum over the views of a mapping window; Gaussians outside this view contribute nothing
-        if (mask & MGS_GRAD_MEANS3D) { dL_dmeans3D[3 * idx] += dmean.x; dL_dmeans3D[3 * idx + 1] += dmean.y; dL_dmeans3D[3 * idx + 2] += dmean.z; }
-        if (mask & MGS_GRAD_MEANS2D) { dL_dmeans2D[3 * idx] += gg.mx; dL_dmeans2D[3 * idx + 1] += gg.my; }
-        if (mask & MGS_GRAD_OPACITY) dL_dopacity[idx] += gg.op;
+        // accumulate == 2: backward passes of different views may run concurrently -> atomics
+        const bool at = accumulate == 2;
+        auto add = [at](float* q, const float x) { if (at) atomicAdd(q, x); else *q += x; };
+        if (mask & MGS_GRAD_MEANS3D) { add(dL_dmeans3D + 3 * idx, dmean.x); add(dL_dmeans3D + 3 * idx + 1, dmean.y); add(dL_dmeans3D + 3 * idx + 2, dmean.z); }
+        if (mask & MGS_GRAD_MEANS2D) { add(dL_dmeans2D + 3 * idx, gg.mx); add(dL_dmeans2D + 3 * idx + 1, gg.my); }
+        if (mask & MGS_GRAD_OPACITY) add(dL_dopacity + idx, gg.op);
         if ((mask & MGS_GRAD_COLOR) && shs == nullptr) {
-          dL_dcolors_or_sh[3 * idx] += gg.r; dL_dcolors_or_sh[3 * idx + 1] += gg.g; dL_dcolors_or_sh[3 * idx + 2] += gg.b;
+          add(dL_dcolors_or_sh + 3 * idx, gg.r); add(dL_dcolors_or_sh + 3 * idx + 1, gg.g); add(dL_dcolors_or_sh + 3 * idx + 2, gg.b);
         }
         if ((mask & MGS_GRAD_COV) && scales != nullptr) {
-          dL_dscales[3 * idx] += dscale.x; dL_dscales[3 * idx + 1] += dscale.y; dL_dscales[3 * idx + 2] += dscale.z;
-          float4 d = reinterpret_cast<float4*>(dL_drotations)[idx];
-          d.x += drot.x; d.y += drot.y; d.z += drot.z; d.w += drot.w;
-          reinterpret_cast<float4*>(dL_drotations)[idx] = d;
+          add(dL_dscales + 3 * idx, dscale.x); add(dL_dscales + 3 * idx + 1, dscale.y); add(dL_dscales + 3 * idx + 2, dscale.z);
+          if (at) atomicAdd(reinterpret_cast<float4*>(dL_drotations) + idx, drot);
+          else {
+            float4 d = reinterpret_cast<float4*>(dL_drotations)[idx];
+            d.x += drot.x; d.y += drot.y; d.z += drot.z; d.w += drot.w;
+            reinterpret_cast<float4*>(dL_drotations)[idx] = d;
+          }
         }
-        if (stat_grad_accum != nullptr) stat_grad_accum[idx] += sqrtf(gg.mx * gg.mx + gg.my * gg.my);
-        if (stat_denom != nullptr) stat_denom[idx] += 1.f;
-        if (stat_max_radii != nullptr) stat_max_radii[idx] = fmaxf(stat_max_radii[idx], (float)rad);
+        if (stat_grad_accum != nullptr) add(stat_grad_accum + idx, sqrtf(gg.mx * gg.mx + gg.my * gg.my));
+        if (stat_denom != nullptr) add(stat_denom + idx, 1.f);
+        if (stat_max_radii != nullptr) {   // radii >= 0: the float order is the order of the bit patterns
+          if (at) atomicMax(reinterpret_cast<int*>(stat_max_radii) + idx, __float_as_int((float)rad));
+          else stat_max_radii[idx] = fmaxf(stat_max_radii[idx], (float)rad);
+        }
       }
     } else {
     if (mask & MGS_GRAD_MEANS3D) { dL_dmeans3D[3 * idx] = dmean.x; dL_dmeans3D[3 * idx + 1] = dmean.y; dL_dmeans3D[3 * idx + 2] = dmean.z; }

@@ -132,8 +132,8 @@ class MapEngine:
         # overlap: the forward half of view k+1 (preprocess, binning, blend + loss) runs on the caller's stream beside the
         # backward half of view k on a second stream; two workspaces and two loss-gradient slots alternate
         self.overlap = overlap
-        self._bwd_stream = self._fwd2_stream = None
-        self.n_pipe = 3             # workspaces / slots in flight: two forwards + one backward
+        self._bwd_streams = self._fwd2_stream = None
+        self.n_pipe = 4             # workspaces / slots in flight: two forwards + two backwards
         self.L, self.lib = L, L.lib()
         self.params = {k: params[k] for k in self.NAMES if k in params and params[k] is not None and params[k].numel() > 0}
         self.dev = self.params["xyz"].device
@@ -164,6 +164,7 @@ class MapEngine:
         self.rank = dist.get_rank(group) if self.distributed else 0
         self._keep = []
         self._slots = {}
+        self._concurrent = False
 
     # ------------------------------------------------------------------------------------------------
     def _args(self):
@@ -238,7 +239,7 @@ class MapEngine:
             self._out_extra.append((torch.empty_like(self.color), torch.empty_like(self.depth), torch.empty_like(self.opacity)))
         ws = self.ws if r == 0 else self.ws_extra[r - 1]
         color, depth, opacity = (self.color, self.depth, self.opacity) if r == 0 else self._out_extra[r - 1]
-        mv.fast_math, mv.slot = int(self.fast_math), r
+        mv.fast_math, mv.slot, mv.concurrent_backward = int(self.fast_math), r, int(self.overlap and self._concurrent)
         mv.out_color, mv.out_depth, mv.out_opacity = color.data_ptr(), depth.data_ptr(), opacity.data_ptr()
         mv.radii, mv.n_touched = slot.radii.data_ptr(), slot.n_touched.data_ptr()
         mv.tau, mv.dab, mv.loss = slot.tau.data_ptr(), slot.dab.data_ptr(), slot.loss.data_ptr()
@@ -252,33 +253,37 @@ class MapEngine:
         self.L.check(self.lib.mgs_map_view_fwd_bwd(C.byref(args), C.byref(mv), _stream()), "mgs_map_view_fwd_bwd")
 
     def _views_overlapped(self, args, todo):
-        """forward(k) alternates between the caller's stream and a second forward stream, backward(k) follows it on the
-        backward stream; forward(k + n_pipe) waits for backward(k) because it reuses that view's workspace, loss-gradient
-        slot and output images.  Backward calls are ordered among themselves (they accumulate into the same gradients)."""
+        """Views in flight on four streams: forward(k) alternates between the caller's stream and a second forward
+        stream, backward(k) follows it on one of two backward streams (their gradient / statistics accumulation is
+        atomic, mgs_map_view.concurrent_backward); forward(k + n_pipe) waits for backward(k) because it reuses that
+        view's workspace, scratch slot and output images."""
         L, lib = self.L, self.lib
         main = torch.cuda.current_stream()
-        if self._bwd_stream is None:
-            self._bwd_stream, self._fwd2_stream = torch.cuda.Stream(device=self.dev), torch.cuda.Stream(device=self.dev)
-        side, fwd = self._bwd_stream, (main, self._fwd2_stream)
+        if self._bwd_streams is None:
+            self._bwd_streams = (torch.cuda.Stream(device=self.dev), torch.cuda.Stream(device=self.dev))
+            self._fwd2_stream = torch.cuda.Stream(device=self.dev)
+        fwd = (main, self._fwd2_stream)
         begin = torch.cuda.Event()
         begin.record(main)                       # mgs_map_begin (activations, zeroed accumulators) is on the caller's stream
         fwd[1].wait_event(begin)
+        self._concurrent = True
         bwd_done = []
         for k, (view, slot) in enumerate(todo):
             mv = self._view_desc(view, slot, k)
-            f = fwd[k & 1]
+            f, b = fwd[k & 1], self._bwd_streams[k & 1]
             if k >= self.n_pipe:
                 f.wait_event(bwd_done[k - self.n_pipe])
             L.check(lib.mgs_map_view_forward(C.byref(args), C.byref(mv), C.c_void_p(f.cuda_stream)), "mgs_map_view_forward")
             ev = torch.cuda.Event()
             ev.record(f)
-            side.wait_event(ev)
-            L.check(lib.mgs_map_view_backward(C.byref(args), C.byref(mv), C.c_void_p(side.cuda_stream)), "mgs_map_view_backward")
+            b.wait_event(ev)
+            L.check(lib.mgs_map_view_backward(C.byref(args), C.byref(mv), C.c_void_p(b.cuda_stream)), "mgs_map_view_backward")
             ev = torch.cuda.Event()
-            ev.record(side)
+            ev.record(b)
             bwd_done.append(ev)
-        if bwd_done:
-            main.wait_event(bwd_done[-1])
+        self._concurrent = False
+        for ev in bwd_done[-2:]:
+            main.wait_event(ev)
 
     def backward_only(self, views: Sequence[MapView]) -> Dict[int, MapViewResult]:
         """Everything of an iteration up to the raw-parameter gradients of THIS rank's views (no exchange, no Adam)."""
