@@ -172,9 +172,10 @@ __device__ __forceinline__ void mean2d_tau_jac(const ProjCtx& q, const float* __
 
 // SH backward (backward.cu:25-149).  Writes dL/dsh for the active coefficients (inactive ones are zeroed by
 // the caller) and returns dL/dmean through the view direction.  dcol must already carry the clamp mask.
+// sh and dsh may be the same row (shared-memory staging, sh_stage.cuh): every coefficient is read before dsh is written.
 __device__ __forceinline__ float3 sh_backward(int deg, int M, const float3& pos, const float* __restrict__ campos,
-                                              const float* __restrict__ sh, const float3 dcol,
-                                              float* __restrict__ dsh /* may be null */, const int accumulate = 0 /* 1: +=, 2: atomicAdd */) {
+                                              const float* sh, const float3 dcol,
+                                              float* dsh /* may be null */, const int accumulate = 0 /* 1: +=, 2: atomicAdd */) {
   const float3 dir_orig = {pos.x - campos[0], pos.y - campos[1], pos.z - campos[2]};
   const float len = sqrtf(dir_orig.x * dir_orig.x + dir_orig.y * dir_orig.y + dir_orig.z * dir_orig.z);
   const float x = dir_orig.x / len, y = dir_orig.y / len, z = dir_orig.z / len;

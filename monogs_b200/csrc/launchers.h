@@ -9,7 +9,7 @@ const char* get_error();
 int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
-                      float* jac = nullptr, int jac_ncol = 0);
+                      float* jac = nullptr, int jac_ncol = 0, const float* sh_rest = nullptr);
 int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s);
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
                    const WsLayout& L, int64_t R_cap, cudaStream_t s);
@@ -36,6 +36,9 @@ struct BackwardArgs {
   // overwriting them; optional densification statistics updated in the same pass (gaussian_model.py:693-697,
   // slam_backend.py:292-299): grad_accum[g] += |dL/dmean2D.xy|, denom[g] += 1, max_radii2D[g] = max(., radii[g])
   int accumulate; float *stat_grad_accum, *stat_denom, *stat_max_radii;
+  // split SH layout (mapping engine): shs = f_dc [P,1,3], sh_rest = f_rest [P,M-1,3]; gradients go to dL_dcolors_or_sh
+  // ([P,1,3]) and dL_dsh_rest ([P,M-1,3]).  Null = one array [P,M,3].
+  const float* sh_rest = nullptr; float* dL_dsh_rest = nullptr;
   bool fast = false;   // blend_backward_full only: exponent variant of the forward that produced ws (blend_exp<FAST>)
   // sketch mode (sketch_dim > 0): per-pixel row routing, output sketch_dtau[d,6]
   int sketch_dim; const int32_t* sketch_indices; float* sketch_dtau;

@@ -11,6 +11,7 @@
 #include "gaussian_backward.cuh"
 #include "tma.cuh"
 #include "blend_pair.cuh"
+#include "sh_stage.cuh"
 
 namespace mgs {
 
@@ -243,9 +244,12 @@ __device__ __forceinline__ void block_add6(float (&t)[6], float* __restrict__ ou
 }
 
 // K9 + K10 fused: one thread per Gaussian, screen-space gradients -> all parameter gradients + pose tangent.
+// STAGE: SH rows in, SH gradient rows out through shared memory with coalesced 16-byte accesses (sh_stage.cuh).
+template <bool STAGE>
 __global__ void __launch_bounds__(256)
 preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
                            const float* __restrict__ means3D, const float* __restrict__ shs,
+                           const float* __restrict__ sh_rest, float* __restrict__ dL_dsh_rest,
                            const float* __restrict__ colors_precomp, const float* __restrict__ scales,
                            const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
                            const int32_t* __restrict__ radii, const float4* __restrict__ rgb4,
@@ -256,18 +260,36 @@ preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
                            float* __restrict__ dL_dcov3D, float* __restrict__ tau_sum, float* __restrict__ tau_pg,
                            const int accumulate, float* __restrict__ stat_grad_accum, float* __restrict__ stat_denom,
                            float* __restrict__ stat_max_radii) {
+  extern __shared__ __align__(16) float sh_tile[];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int RS = sh_row_stride(v.M);
+  float* tile = sh_tile + (threadIdx.x >> 5) * 32 * RS;
+  const int first = blockIdx.x * blockDim.x + (threadIdx.x & ~31);
+  const int n_rows = min(32, P - first);
+  const bool want_dsh = shs != nullptr && (mask & MGS_GRAD_COLOR);
+  bool vis = false;
+  if (idx < P) vis = radii[idx] > 0;
+  const unsigned vis_mask = __ballot_sync(0xffffffffu, vis);
+  if (STAGE && vis_mask != 0u) {   // warp-uniform
+    if (sh_rest == nullptr) sh_stage_load(tile, RS, shs + (size_t)first * 3 * v.M, 3 * v.M, 0, n_rows, lane);
+    else {
+      sh_stage_load(tile, RS, shs + (size_t)first * 3, 3, 0, n_rows, lane);
+      sh_stage_load(tile, RS, sh_rest + (size_t)first * 3 * (v.M - 1), 3 * (v.M - 1), 3, n_rows, lane);
+    }
+    __syncwarp();
+  }
   float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   if (idx < P) {
     const int rad = radii[idx];
-    const bool vis = rad > 0;
     float3 dmean = {0.f, 0.f, 0.f}, dscale = {0.f, 0.f, 0.f};
     float4 drot = {0.f, 0.f, 0.f, 0.f};
     float dcov6[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     G2DGrad gg;
     gg.mx = gg.my = gg.cx = gg.cy = gg.cw = gg.op = gg.dd = gg.r = gg.g = gg.b = 0.f;
     const int Msh = v.M;
-    float* dsh = (shs != nullptr && (mask & MGS_GRAD_COLOR)) ? dL_dcolors_or_sh + (size_t)idx * Msh * 3 : nullptr;
+    float* dsh = !want_dsh ? nullptr : (STAGE ? tile + lane * RS : dL_dcolors_or_sh + (size_t)idx * Msh * 3);
+    const float* sh_row = STAGE ? tile + lane * RS : (shs != nullptr ? shs + (size_t)idx * Msh * 3 : nullptr);
     if (vis) {
       const float4* src = reinterpret_cast<const float4*>(g2d + idx);
       const float4 a0 = src[0], a1 = src[1], a2 = src[2];
@@ -301,12 +323,12 @@ preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
       if (shs != nullptr) {
         const uint32_t cm = __float_as_uint(rgb4[idx].w);
         const float3 dcol = {(cm & 1u) ? 0.f : gg.r, (cm & 2u) ? 0.f : gg.g, (cm & 4u) ? 0.f : gg.b};
-        const float3 dms = sh_backward(v.D, Msh, p, v.campos, shs + (size_t)idx * Msh * 3, dcol, dsh, accumulate);
+        const float3 dms = sh_backward(v.D, Msh, p, v.campos, sh_row, dcol, dsh, STAGE ? 0 : accumulate);
         dmean.x += dms.x; dmean.y += dms.y; dmean.z += dms.z;
         tau[0] += -dms.x; tau[1] += -dms.y; tau[2] += -dms.z;
       }
       if (scales != nullptr && (mask & MGS_GRAD_COV)) cov3d_backward(scales, rotations, idx, v.scale_modifier, dcov6, dscale, drot);
-    } else if (dsh != nullptr && !accumulate) {
+    } else if (dsh != nullptr && (STAGE || !accumulate)) {   // staged rows of invisible Gaussians must read as zero
       for (int k = 0; k < 3 * Msh; k++) dsh[k] = 0.f;
     }
     if (accumulate) {
@@ -359,6 +381,15 @@ preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
       for (int k = 0; k < 6; k++) tau_pg[6 * (size_t)idx + k] = tau[k];
     }
   }
+  if (STAGE && want_dsh && n_rows > 0 && (accumulate == 0 || vis_mask != 0u)) {
+    __syncwarp();
+    if (sh_rest == nullptr)
+      sh_stage_store(tile, RS, dL_dcolors_or_sh + (size_t)first * 3 * v.M, 3 * v.M, 0, n_rows, lane, accumulate, vis_mask);
+    else {
+      sh_stage_store(tile, RS, dL_dcolors_or_sh + (size_t)first * 3, 3, 0, n_rows, lane, accumulate, vis_mask);
+      sh_stage_store(tile, RS, dL_dsh_rest + (size_t)first * 3 * (v.M - 1), 3 * (v.M - 1), 3, n_rows, lane, accumulate, vis_mask);
+    }
+  }
   if (tau_sum != nullptr) block_add6(tau, tau_sum);
 }
 
@@ -385,11 +416,19 @@ int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   prof_end(s);
   MGS_LAUNCH_CHECK();
   prof_begin("preprocess_backward", s);
-  preprocess_backward_kernel<<<(P + 255) / 256, 256, 0, s>>>(
-      v, P, a.grad_mask, a.means3D, a.shs, a.colors_precomp, a.scales, a.rotations, a.cov3D_precomp, a.radii,
-      ws_ptr<float4>(a.ws, a.L.rgb4), g2d, a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dcolors_or_sh, a.dL_dopacity,
-      a.dL_dscales, a.dL_drotations, a.dL_dcov3D, a.dL_dtau_sum, a.dL_dtau_pg, a.accumulate, a.stat_grad_accum,
-      a.stat_denom, a.stat_max_radii);
+#define MGS_PB_ARGS v, P, a.grad_mask, a.means3D, a.shs, a.sh_rest, a.dL_dsh_rest, a.colors_precomp, a.scales, a.rotations,        \
+      a.cov3D_precomp, a.radii, ws_ptr<float4>(a.ws, a.L.rgb4), g2d, a.dL_dmeans3D, a.dL_dmeans2D, a.dL_dcolors_or_sh,      \
+      a.dL_dopacity, a.dL_dscales, a.dL_drotations, a.dL_dcov3D, a.dL_dtau_sum, a.dL_dtau_pg, a.accumulate,                \
+      a.stat_grad_accum, a.stat_denom, a.stat_max_radii
+  const bool stage = a.shs != nullptr && v.M > 1;
+  if (a.sh_rest != nullptr && (!stage || ((a.grad_mask & MGS_GRAD_COLOR) && a.dL_dsh_rest == nullptr))) {
+    set_error("backward: split SH layout needs sh_coeffs > 1 and dL_dsh_rest"); return MGS_EINVAL;
+  }
+  if (stage) {
+    const int T = 128;
+    preprocess_backward_kernel<true><<<(P + T - 1) / T, T, (size_t)T * sh_row_stride(v.M) * sizeof(float), s>>>(MGS_PB_ARGS);
+  } else preprocess_backward_kernel<false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PB_ARGS);
+#undef MGS_PB_ARGS
   prof_end(s);
   MGS_LAUNCH_CHECK();
   return MGS_OK;

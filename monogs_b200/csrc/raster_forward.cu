@@ -3,6 +3,7 @@
 // FORWARD::preprocess / FORWARD::render (forward.cu:157-258, 263-392).
 #include "launchers.h"
 #include "pose_jac.cuh"
+#include "sh_stage.cuh"
 #include <cub/block/block_scan.cuh>
 #include <cub/block/block_merge_sort.cuh>
 #include <cstdarg>
@@ -126,9 +127,8 @@ __device__ __forceinline__ Cov2DOut cov2d_project(const float3& mean, const View
 }
 
 // SH -> RGB (forward.cu:22-73).  Returns the clamped colour and a 3-bit mask of channels clamped at 0.
-__device__ __forceinline__ float3 sh_to_rgb(int idx, int deg, int M, const float3& pos, const float* __restrict__ campos,
-                                            const float* __restrict__ shs, uint32_t& clamp_mask) {
-  const float* sh = shs + (size_t)idx * M * 3;
+__device__ __forceinline__ float3 sh_to_rgb(int deg, const float3& pos, const float* __restrict__ campos,
+                                            const float* __restrict__ sh /* this Gaussian's row [M,3] */, uint32_t& clamp_mask) {
   float w[16];
   w[0] = kSH0;
   if (deg > 0) {
@@ -213,23 +213,34 @@ __device__ __forceinline__ void for_each_tile(const uint2 rmin, const uint2 rmax
   }
 }
 
-template <int JAC_NCOL>   // 0: plain; 6 / 9: also build the pose Jacobian of visible Gaussians (tracking path)
+// JAC_NCOL 0: plain; 6 / 9: also build the pose Jacobian of visible Gaussians (tracking path).
+// STAGE: SH rows of the warp's 32 Gaussians go through shared memory with coalesced 16-byte loads (sh_stage.cuh);
+// sh_rest != nullptr selects the split layout (shs = f_dc [P,1,3], sh_rest = f_rest [P,M-1,3]).
+template <int JAC_NCOL, bool STAGE>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const ViewConst v, const int P,
                   const float* __restrict__ means3D, const float* __restrict__ opacities,
-                  const float* __restrict__ shs, const float* __restrict__ colors_precomp,
+                  const float* __restrict__ shs, const float* __restrict__ sh_rest, const float* __restrict__ colors_precomp,
                   const float* __restrict__ scales, const float* __restrict__ rotations,
                   const float* __restrict__ cov3D_precomp,
                   int32_t* __restrict__ radii, float* __restrict__ depths, float2* __restrict__ means2D,
                   float4* __restrict__ conic_opacity, float4* __restrict__ rgb4,
                   uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ tile_ctr,
                   float* __restrict__ jac) {
+  extern __shared__ __align__(16) float sh_tile[];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   int my_radius_i = 0;
   uint32_t touched = 0;
   uint2 rmin = {0u, 0u}, rmax = {0u, 0u};
+  // phase 1: geometry and culling
+  bool alive = false;
+  float3 p = {0.f, 0.f, 0.f}, conic = {0.f, 0.f, 0.f};
+  float2 pix = {0.f, 0.f};
+  float view_z = 0.f, my_radius = 0.f;
+  uint2 r0 = {0u, 0u}, r1 = {0u, 0u};
+  uint32_t area = 0;
   if (idx < P) do {
-    const float3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    p = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
     // near cull only (auxiliary.h:139-164)
     const float4 ph = xform4x4(p, v.proj);
     const float pw = 1.0f / (ph.w + 0.0000001f);
@@ -247,29 +258,50 @@ preprocess_kernel(const ViewConst v, const int P,
     const float det = (cv.a * cv.c - cv.b * cv.b);
     if (det == 0.0f) break;
     const float det_inv = 1.f / det;
-    const float3 conic = {cv.c * det_inv, -cv.b * det_inv, cv.a * det_inv};
+    conic = make_float3(cv.c * det_inv, -cv.b * det_inv, cv.a * det_inv);
     const float mid = 0.5f * (cv.a + cv.c);
     const float lambda1 = mid + sqrtf(max(0.1f, mid * mid - det));
     const float lambda2 = mid - sqrtf(max(0.1f, mid * mid - det));
-    const float my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
-    const float2 pix = {ndc_to_pix(pproj.x, v.W), ndc_to_pix(pproj.y, v.H)};
-    uint2 r0, r1;
+    my_radius = ceilf(3.f * sqrtf(max(lambda1, lambda2)));
+    pix = make_float2(ndc_to_pix(pproj.x, v.W), ndc_to_pix(pproj.y, v.H));
     tile_rect(pix, (int)my_radius, v.gx, v.gy, r0, r1);
-    const uint32_t area = (r1.x - r0.x) * (r1.y - r0.y);
+    area = (r1.x - r0.x) * (r1.y - r0.y);
     if (area == 0) break;
+    view_z = pview.z;
+    alive = true;
+  } while (0);
+  // phase 2: colour, pose Jacobian, per-Gaussian outputs
+  const float* sh_row = nullptr;
+  if (STAGE) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int RS = sh_row_stride(v.M);
+    float* tile = sh_tile + warp * 32 * RS;
+    const int first = blockIdx.x * blockDim.x + warp * 32;
+    const int n_rows = min(32, P - first);
+    if (__ballot_sync(0xffffffffu, alive) != 0u) {   // warp-uniform
+      if (sh_rest == nullptr) sh_stage_load(tile, RS, shs + (size_t)first * 3 * v.M, 3 * v.M, 0, n_rows, lane);
+      else {
+        sh_stage_load(tile, RS, shs + (size_t)first * 3, 3, 0, n_rows, lane);
+        sh_stage_load(tile, RS, sh_rest + (size_t)first * 3 * (v.M - 1), 3 * (v.M - 1), 3, n_rows, lane);
+      }
+      __syncwarp();
+    }
+    sh_row = tile + lane * RS;
+  } else if (shs != nullptr) sh_row = shs + (size_t)idx * v.M * 3;
+  if (alive) {
     uint32_t cm = 0;
     if (colors_precomp == nullptr) {
-      const float3 c = sh_to_rgb(idx, v.D, v.M, p, v.campos, shs, cm);
+      const float3 c = sh_to_rgb(v.D, p, v.campos, sh_row, cm);
       rgb4[idx] = make_float4(c.x, c.y, c.z, __uint_as_float(cm));
     }
     if (JAC_NCOL > 0) build_pose_jac<(JAC_NCOL > 0 ? JAC_NCOL : 6)>(v, idx, p, shs, scales, rotations, cov3D_precomp, cm, jac);
-    depths[idx] = pview.z;
+    depths[idx] = view_z;
     means2D[idx] = pix;
     conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
     my_radius_i = (int)my_radius;
     touched = area;
     rmin = r0; rmax = r1;
-  } while (0);
+  }
   if (idx < P) {
     radii[idx] = my_radius_i;
     tiles_touched[idx] = touched;
@@ -506,16 +538,27 @@ int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_
 int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
-                      float* jac, int jac_ncol) {
+                      float* jac, int jac_ncol, const float* sh_rest) {
   if (P == 0) return MGS_OK;
   MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(ws, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
-#define MGS_PRE_ARGS v, P, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,           \
+#define MGS_PRE_ARGS v, P, means3D, opacities, shs, sh_rest, colors_precomp, scales, rotations, cov3D_precomp, radii,  \
       ws_ptr<float>(ws, L.depths), ws_ptr<float2>(ws, L.means2D), ws_ptr<float4>(ws, L.conic_opacity),               \
       ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched), ws_ptr<uint32_t>(ws, L.tile_ctr), jac
+  // SH rows of more than one coefficient are staged through shared memory (128 threads: 4 tiles of [32][3M | 1] floats)
+  const bool stage = shs != nullptr && colors_precomp == nullptr && v.M > 1;
+  if (sh_rest != nullptr && !stage) { set_error("preprocess: split SH layout needs sh_coeffs > 1 and no colors_precomp"); return MGS_EINVAL; }
   prof_begin("preprocess", s);
-  if (jac == nullptr) preprocess_kernel<0><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-  else if (jac_ncol == 9) preprocess_kernel<9><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-  else preprocess_kernel<6><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+  if (stage) {
+    const int T = 128;
+    const size_t smem = (size_t)T * sh_row_stride(v.M) * sizeof(float);
+    if (jac == nullptr) preprocess_kernel<0, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+    else if (jac_ncol == 9) preprocess_kernel<9, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+    else preprocess_kernel<6, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+  } else {
+    if (jac == nullptr) preprocess_kernel<0, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+    else if (jac_ncol == 9) preprocess_kernel<9, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+    else preprocess_kernel<6, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+  }
   prof_end(s);
 #undef MGS_PRE_ARGS
   MGS_LAUNCH_CHECK();
