@@ -243,7 +243,7 @@ typedef struct mgs_gaussians {
 
 typedef struct mgs_map_args {
   mgs_gaussians g;
-  /* raw-parameter gradients, same shapes as the parameters.  grad_xyz and grad_f_dc are accumulated in place by the
+  /* raw-parameter gradients, same shapes as the parameters.  grad_xyz, grad_f_dc and grad_f_rest are accumulated in place by the
    * views (zeroed by mgs_map_begin); the others are written by mgs_map_end. */
   float *grad_xyz, *grad_f_dc, *grad_f_rest, *grad_opacity, *grad_scaling, *grad_rotation;
   /* densification statistics updated in place by every view with update_stats != 0; each may be null */

@@ -20,8 +20,9 @@ namespace mgs {
 constexpr int MAP_SLOTS = 4;
 
 struct MapScratch {
-  float *act_opacity, *act_scales, *act_rot, *act_shs;   // activated parameters (act_shs aliases f_dc when M == 1)
-  float *d_opacity, *d_scales, *d_rot, *d_shs;           // activated-space gradient accumulators (d_shs: M > 1 only)
+  float *act_opacity, *act_scales, *act_rot;             // activated parameters (SH features have no activation and are
+                                                         // read in place from f_dc / f_rest: split layout of sh_stage.cuh)
+  float *d_opacity, *d_scales, *d_rot;                   // activated-space gradient accumulators
   void* bwd[MAP_SLOTS]; size_t bwd_bytes;                // per-Gaussian screen-space accumulator of the backward blend, per slot
   float *g_img[MAP_SLOTS], *g_depth[MAP_SLOTS]; double* partials[MAP_SLOTS];   // forwards of later views may overlap the backward of an earlier one
   size_t total;
@@ -37,9 +38,7 @@ static MapScratch carve_map_scratch(void* base, int P, int M, int W, int H) {
   size_t off = 0;
   auto take = [&](size_t bytes) { char* q = p ? p + off : nullptr; off += up256(bytes); return q; };
   m.act_opacity = (float*)take(Pp * 4); m.act_scales = (float*)take(Pp * 12); m.act_rot = (float*)take(Pp * 16);
-  m.act_shs = (float*)take(M > 1 ? Pp * M * 12 : 0);
   m.d_opacity = (float*)take(Pp * 4); m.d_scales = (float*)take(Pp * 12); m.d_rot = (float*)take(Pp * 16);
-  m.d_shs = (float*)take(M > 1 ? Pp * M * 12 : 0);
   m.bwd_bytes = backward_scratch_bytes(P, 0);
   for (int k = 0; k < MAP_SLOTS; k++) m.bwd[k] = take(m.bwd_bytes);
   for (int k = 0; k < MAP_SLOTS; k++) {
@@ -65,7 +64,7 @@ map_activate_kernel(const mgs_gaussians g, const MapScratch m, float* __restrict
   const float4 q = reinterpret_cast<const float4*>(g.rotation_raw)[idx];
   const float nrm = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);   // F.normalize eps
   reinterpret_cast<float4*>(m.act_rot)[idx] = make_float4(q.x / nrm, q.y / nrm, q.z / nrm, q.w / nrm);
-  if (g.sh_coeffs == 1) {   // M > 1: sh_cat_kernel + a memset of the SH gradient accumulator
+  if (g.sh_coeffs == 1) {   // M > 1: grad_f_dc / grad_f_rest are zeroed by memsets in mgs_map_begin
     grad_f_dc[3 * idx] = 0.f; grad_f_dc[3 * idx + 1] = 0.f; grad_f_dc[3 * idx + 2] = 0.f;
   }
   grad_xyz[3 * idx] = 0.f; grad_xyz[3 * idx + 1] = 0.f; grad_xyz[3 * idx + 2] = 0.f;
@@ -74,19 +73,6 @@ map_activate_kernel(const mgs_gaussians g, const MapScratch m, float* __restrict
   reinterpret_cast<float4*>(m.d_rot)[idx] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
-// get_features = cat(f_dc, f_rest) (gaussian_model.py:89-93) and its inverse for the gradient, one thread per float so
-// that both sides of the copy are coalesced (a per-Gaussian loop strides 12*M bytes between neighbouring threads)
-template <bool SPLIT>
-__global__ void __launch_bounds__(256)
-sh_cat_kernel(const size_t n /* P*M*3 */, const int M, float* __restrict__ cat, float* __restrict__ f_dc, float* __restrict__ f_rest) {
-  const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= n) return;
-  const size_t row = e / (size_t)(3 * M);
-  const int k = (int)(e - row * (size_t)(3 * M));
-  float* part = k < 3 ? f_dc + row * 3 + k : f_rest + row * (size_t)(3 * (M - 1)) + (k - 3);
-  if (SPLIT) *part = cat[e];
-  else cat[e] = *part;
-}
 
 // per-view loss from the per-tile partial sums of the forward epilogue (get_loss_mapping_rgb / _rgbd)
 __global__ void __launch_bounds__(256)
@@ -200,12 +186,9 @@ int mgs_map_begin(const mgs_map_args* a, void* stream) {
   MGS_PROF("map_activate", s, map_activate_kernel<<<(P + 255) / 256, 256, 0, s>>>(a->g, m, a->grad_xyz, a->grad_f_dc, a->loss_total));
   MGS_LAUNCH_CHECK();
   const int M = a->g.sh_coeffs;
-  if (M > 1) {
-    const size_t n = (size_t)P * M * 3;
-    MGS_PROF("sh_cat", s, sh_cat_kernel<false><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(
-        n, M, m.act_shs, const_cast<float*>(a->g.f_dc), const_cast<float*>(a->g.f_rest)));
-    MGS_LAUNCH_CHECK();
-    MGS_CUDA_TRY(cudaMemsetAsync(m.d_shs, 0, n * sizeof(float), s));
+  if (M > 1) {   // SH gradients accumulate straight into the raw-parameter gradients (features have no activation)
+    MGS_CUDA_TRY(cudaMemsetAsync(a->grad_f_dc, 0, (size_t)P * 3 * sizeof(float), s));
+    MGS_CUDA_TRY(cudaMemsetAsync(a->grad_f_rest, 0, (size_t)P * (M - 1) * 3 * sizeof(float), s));
   }
   return MGS_OK;
 }
@@ -241,7 +224,7 @@ static int map_view_ctx(const mgs_map_args* a, const mgs_map_view* mv, MapViewCt
   c->npix = (size_t)W * H;
   c->tiles = c->v.gx * c->v.gy;
   c->use_depth = mv->gt_depth != nullptr;
-  c->shs = c->M > 1 ? c->m.act_shs : g.f_dc;
+  c->shs = g.f_dc;   // M > 1: split layout, f_rest passed beside it
   return MGS_OK;
 }
 
@@ -254,7 +237,8 @@ int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* st
   const mgs_gaussians& g = a->g;
   const MapScratch& m = c.m;
   void* ws = mv->workspace;
-  if ((rc = launch_preprocess(c.v, c.P, g.xyz, m.act_opacity, c.shs, nullptr, m.act_scales, m.act_rot, nullptr, mv->radii, ws, c.L, s))) return rc;
+  if ((rc = launch_preprocess(c.v, c.P, g.xyz, m.act_opacity, c.shs, nullptr, m.act_scales, m.act_rot, nullptr, mv->radii, ws, c.L, s,
+                              nullptr, 0, c.M > 1 ? g.f_rest : nullptr))) return rc;
   MGS_CUDA_TRY(cudaMemsetAsync(mv->n_touched, 0, (size_t)c.P * sizeof(int32_t), s));
   if ((rc = launch_binning(c.v, c.P, nullptr, mv->radii, ws, c.L, mv->R_cap, s))) return rc;
 
@@ -287,7 +271,8 @@ int mgs_map_view_backward(const mgs_map_args* a, const mgs_map_view* mv, void* s
   b.means3D = g.xyz; b.shs = c.shs; b.scales = m.act_scales; b.rotations = m.act_rot; b.radii = mv->radii;
   b.ws = mv->workspace; b.L = c.L; b.scratch = m.bwd[c.slot]; b.scratch_bytes = m.bwd_bytes;
   b.dL_dcolor_img = m.g_img[c.slot]; b.dL_ddepth_img = m.g_depth[c.slot];
-  b.dL_dmeans3D = a->grad_xyz; b.dL_dcolors_or_sh = c.M > 1 ? m.d_shs : a->grad_f_dc; b.dL_dopacity = m.d_opacity;
+  b.dL_dmeans3D = a->grad_xyz; b.dL_dcolors_or_sh = a->grad_f_dc; b.dL_dopacity = m.d_opacity;
+  if (c.M > 1) { b.sh_rest = g.f_rest; b.dL_dsh_rest = a->grad_f_rest; }
   b.dL_dscales = m.d_scales; b.dL_drotations = m.d_rot; b.dL_dtau_sum = mv->tau;
   b.accumulate = mv->concurrent_backward ? 2 : 1;
   if (mv->update_stats) { b.stat_grad_accum = a->xyz_gradient_accum; b.stat_denom = a->denom; b.stat_max_radii = a->max_radii2D; }
@@ -311,12 +296,6 @@ int mgs_map_end(const mgs_map_args* a, int32_t add_regulariser, float regularise
                                                                        a->grad_scaling, a->grad_rotation,
                                                                        add_regulariser ? regulariser_weight : 0.f, a->loss_total));
   MGS_LAUNCH_CHECK();
-  const int M = a->g.sh_coeffs;
-  if (M > 1) {   // split the SH gradient back into its two parameters
-    const size_t n = (size_t)P * M * 3;
-    MGS_PROF("sh_split", s, sh_cat_kernel<true><<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, M, m.d_shs, a->grad_f_dc, a->grad_f_rest));
-    MGS_LAUNCH_CHECK();
-  }
   return MGS_OK;
 }
 

@@ -24,19 +24,19 @@ struct FastDiv {
   __device__ __forceinline__ uint32_t div(uint32_t e) const { return __umulhi(e, magic); }
 };
 
-// Fast path of both directions: 32 full rows, row length a multiple of 4 (a 16-byte chunk never crosses a row) and a
-// 16-byte aligned block.  Batches of up to 6 chunks per lane keep 6 x 512 B per warp in flight: the per-Gaussian kernels
-// run at ~25 % occupancy, so memory-level parallelism has to come from each warp.
+// Fast path of both directions: 32 full rows and a 16-byte aligned block (32 * row_len floats is always a whole number
+// of 16-byte chunks; a chunk may span two rows).  Batches of up to 6 chunks per lane keep 6 x 512 B per warp in flight:
+// the per-Gaussian kernels run at ~25 % occupancy, so memory-level parallelism has to come from each warp.
 constexpr int SH_BATCH = 6;
 
-__device__ __forceinline__ bool sh_fast_path(const void* p, const int row_len, const int n_rows) {
-  return n_rows == 32 && (row_len & 3) == 0 && (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
+__device__ __forceinline__ bool sh_fast_path(const void* p, const int n_rows) {
+  return n_rows == 32 && (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
 }
 
 __device__ __forceinline__ void sh_stage_load_fast(float* __restrict__ tile, const int RS, const float* __restrict__ src,
                                                    const int row_len, const int dst_off, const int lane) {
   const int chunks = 8 * row_len;            // 32 rows * row_len / 4
-  const FastDiv fd((uint32_t)(row_len >> 2));
+  const FastDiv fd((uint32_t)row_len);
   const float4* src4 = reinterpret_cast<const float4*>(src);
   for (int c0 = lane; c0 < chunks; c0 += 32 * SH_BATCH) {
     float4 t[SH_BATCH];
@@ -49,9 +49,12 @@ __device__ __forceinline__ void sh_stage_load_fast(float* __restrict__ tile, con
     for (int u = 0; u < SH_BATCH; u++) {
       const int c = c0 + 32 * u;
       if (c < chunks) {
-        const int r = (int)fd.div((uint32_t)c), k = (c - r * (row_len >> 2)) << 2;
-        float* q = tile + r * RS + dst_off + k;
-        q[0] = t[u].x; q[1] = t[u].y; q[2] = t[u].z; q[3] = t[u].w;
+        const int r = (int)fd.div((uint32_t)(4 * c)), k = 4 * c - r * row_len;
+        float* q = tile + r * RS + dst_off + k;          // element i of the chunk: row r (+1 past the row end)
+        const int wrap = RS - row_len;                   // jump from the end of row r to the start of row r+1
+        const float val[4] = {t[u].x, t[u].y, t[u].z, t[u].w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) q[i + (k + i >= row_len ? wrap : 0)] = val[i];
       }
     }
   }
@@ -61,20 +64,24 @@ __device__ __forceinline__ void sh_stage_store_fast(const float* __restrict__ ti
                                                     const int row_len, const int src_off, const int lane, const int mode,
                                                     const unsigned row_mask) {
   const int chunks = 8 * row_len;
-  const FastDiv fd((uint32_t)(row_len >> 2));
+  const FastDiv fd((uint32_t)row_len);
   float4* dst4 = reinterpret_cast<float4*>(dst);
+  const int wrap = RS - row_len;
   for (int c0 = lane; c0 < chunks; c0 += 32 * SH_BATCH) {
     float4 t[SH_BATCH];
     bool on[SH_BATCH];
     const float* q[SH_BATCH];
+    int kk[SH_BATCH];
 #pragma unroll
     for (int u = 0; u < SH_BATCH; u++) {
       const int c = c0 + 32 * u;
       on[u] = false;
       if (c < chunks) {
-        const int r = (int)fd.div((uint32_t)c), k = (c - r * (row_len >> 2)) << 2;
-        on[u] = mode == 0 || ((row_mask >> r) & 1u) != 0u;
+        const int r = (int)fd.div((uint32_t)(4 * c)), k = 4 * c - r * row_len;
+        const int r_last = k + 3 >= row_len ? min(r + 1, 31) : r;
+        on[u] = mode == 0 || (((row_mask >> r) | (row_mask >> r_last)) & 1u) != 0u;
         q[u] = tile + r * RS + src_off + k;
+        kk[u] = k;
         if (on[u] && mode == 1) t[u] = dst4[c];          // all read-modify-write loads of the batch first
       }
     }
@@ -82,7 +89,10 @@ __device__ __forceinline__ void sh_stage_store_fast(const float* __restrict__ ti
     for (int u = 0; u < SH_BATCH; u++) {
       const int c = c0 + 32 * u;
       if (!on[u]) continue;
-      const float4 v4 = make_float4(q[u][0], q[u][1], q[u][2], q[u][3]);
+      float val[4];
+#pragma unroll
+      for (int i = 0; i < 4; i++) val[i] = q[u][i + (kk[u] + i >= row_len ? wrap : 0)];
+      const float4 v4 = make_float4(val[0], val[1], val[2], val[3]);
       if (mode == 0) dst4[c] = v4;
       else if (mode == 1) dst4[c] = make_float4(t[u].x + v4.x, t[u].y + v4.y, t[u].z + v4.z, t[u].w + v4.w);
       else atomicAdd(dst4 + c, v4);
@@ -93,7 +103,7 @@ __device__ __forceinline__ void sh_stage_store_fast(const float* __restrict__ ti
 // global block [n_rows][row_len] (contiguous) -> tile rows at column dst_off
 __device__ __forceinline__ void sh_stage_load(float* __restrict__ tile, const int RS, const float* __restrict__ src,
                                               const int row_len, const int dst_off, const int n_rows, const int lane) {
-  if (sh_fast_path(src, row_len, n_rows)) { sh_stage_load_fast(tile, RS, src, row_len, dst_off, lane); return; }
+  if (sh_fast_path(src, n_rows)) { sh_stage_load_fast(tile, RS, src, row_len, dst_off, lane); return; }
   const int total = n_rows * row_len;
   const FastDiv fd((uint32_t)row_len);
   if ((reinterpret_cast<uintptr_t>(src) & 15u) == 0) {
@@ -126,7 +136,7 @@ __device__ __forceinline__ void sh_stage_load(float* __restrict__ tile, const in
 __device__ __forceinline__ void sh_stage_store(const float* __restrict__ tile, const int RS, float* __restrict__ dst,
                                                const int row_len, const int src_off, const int n_rows, const int lane,
                                                const int mode, const unsigned row_mask) {
-  if (sh_fast_path(dst, row_len, n_rows)) { sh_stage_store_fast(tile, RS, dst, row_len, src_off, lane, mode, row_mask); return; }
+  if (sh_fast_path(dst, n_rows)) { sh_stage_store_fast(tile, RS, dst, row_len, src_off, lane, mode, row_mask); return; }
   const int total = n_rows * row_len;
   const FastDiv fd((uint32_t)row_len);
   const bool vec = (reinterpret_cast<uintptr_t>(dst) & 15u) == 0;
