@@ -79,7 +79,8 @@ def _reference_iteration(p, views, sh_degree, alpha=0.95, thr=0.01):
 @pytest.mark.parametrize("name,with_depth,with_exposure,isotropic,fast",
                          [("tiny", False, False, False, False), ("dense", True, True, False, False),
                           ("ragged", True, True, True, False), ("sh3", False, True, False, False),
-                          ("dense", True, True, False, True), ("sh3", False, True, False, True)])
+                          ("dense", True, True, False, True), ("sh3", False, True, False, True),
+                          ("sh2", False, False, False, False), ("sh3_full", True, True, False, True)])
 def test_map_engine_matches_autograd_path(name, with_depth, with_exposure, isotropic, fast):
     """fast = False: the exact exponent, integer outputs equal to the autograd path's.  fast = True (the MapEngine
     default): ex2.approx in forward and backward blend; a borderline `T > 0.5` decision may move, so n_touched is

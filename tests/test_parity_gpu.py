@@ -112,7 +112,7 @@ def _setup(name, seed=0):
     return sc, cam, bg, gc, gd
 
 
-@pytest.mark.parametrize("name", ["tiny", "ragged", "sh3", "dense", "packed8", "packed16", "crowded"])
+@pytest.mark.parametrize("name", ["tiny", "ragged", "sh3", "sh2", "sh3_full", "dense", "packed8", "packed16", "crowded"])
 def test_product_vs_reference_small(name):
     sc, cam, bg, gc, gd = _setup(name)
     scd, camd = U.to_dev(sc), U.to_dev(cam)

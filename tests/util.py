@@ -10,6 +10,8 @@ SMALL = {
     "ragged": (1500, 150, 100, 120.0, 118.0, 74.2, 50.3, 0),     # W,H not multiples of 16
     "sh3": (1200, 128, 96, 110.0, 110.0, 63.5, 47.5, 3),
     "dense": (3000, 96, 64, 80.0, 80.0, 47.5, 31.5, 1),
+    "sh2": (2048, 96, 64, 80.0, 80.0, 47.5, 31.5, 2),            # 9 coefficients: 27-float rows, 16-byte chunks span rows
+    "sh3_full": (4096, 128, 96, 110.0, 110.0, 63.5, 47.5, 3),    # P a multiple of 32: every warp on the staging fast path
     "packed8": (12000, 48, 32, 60.0, 60.0, 23.5, 15.5, 0),       # ~1.5k instances per tile: 8 words per thread in the tile sort
     "packed16": (24000, 48, 32, 60.0, 60.0, 23.5, 15.5, 0),      # ~3k per tile: 16 words per thread
     "crowded": (60000, 48, 32, 60.0, 60.0, 23.5, 15.5, 0),      # 6 tiles with > 4096 instances each: the in-L2 tile sort
