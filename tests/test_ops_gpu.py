@@ -117,8 +117,8 @@ def test_fused_track_iteration_matches_composed_entry_points(mode, use_depth):
     assert l0[-1] < l0[0]
 
 
-@pytest.mark.parametrize("mode,use_depth", [(1, False), (0, False), (0, True)])
-def test_single_pass_blend_matches_two_pass_first_step(mode, use_depth):
+@pytest.mark.parametrize("mode,use_depth,masked", [(1, False, False), (0, False, False), (0, True, False), (1, False, True), (0, True, True)])
+def test_single_pass_blend_matches_two_pass_first_step(mode, use_depth, masked):
     """The single-pass tracking blend (blend_track.cu: forward-order accumulators, tangent contracted in the epilogue)
     against the two-pass path built from the parity-tested entry points (forward, fused loss, pose-only backward), one
     step from the same state, exact exponent in both: images identical, loss and pose tangent to 1e-4."""
@@ -136,7 +136,12 @@ def test_single_pass_blend_matches_two_pass_first_step(mode, use_depth):
     for fused in (True, False):
         tr = PoseTracker(scd.means3D, scd.opacities, scd.shs, scd.scales, scd.rotations, 0, cam, bg, torch.eye(4),
                          mode=mode, use_depth=use_depth, use_graph=False, fused=fused, fast_math=False)
-        tr.set_frame(gt, gt_depth=gt_depth if use_depth else None)
+        # masked: a gradient mask over about half of the frame (Camera.compute_grad_mask) and a band of invalid depth; the
+        # single-pass kernel skips the tangent accumulation of zero-weight pixels, which must not change anything
+        gm = (torch.rand(1, cam.H, cam.W, generator=torch.Generator().manual_seed(5)) > 0.5).float().cuda() if masked else None
+        gd = gt_depth.clone() if use_depth else None
+        if masked and use_depth: gd[:, : cam.H // 4] = 0.0
+        tr.set_frame(gt, gt_depth=gd, grad_mask=gm)
         tr.step()
         torch.cuda.synchronize()
         out.append((tr.loss.clone(), tr.tau.clone(), tr.dab.clone(), tr.color.clone(), tr.depth.clone(), tr.n_touched.clone()))
