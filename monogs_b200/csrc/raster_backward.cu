@@ -246,7 +246,7 @@ __device__ __forceinline__ void block_add6(float (&t)[6], float* __restrict__ ou
 // K9 + K10 fused: one thread per Gaussian, screen-space gradients -> all parameter gradients + pose tangent.
 // STAGE: SH rows in, SH gradient rows out through shared memory with coalesced 16-byte accesses (sh_stage.cuh).
 template <bool STAGE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)   // 80 registers: the kernel is latency-bound, occupancy pays (C5: 474 -> 376 us)
 preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
                            const float* __restrict__ means3D, const float* __restrict__ shs,
                            const float* __restrict__ sh_rest, float* __restrict__ dL_dsh_rest,
