@@ -261,9 +261,42 @@ def ref_cuda_leg(cfg, dev, steps, warmup, flush):
     rt = ref_tracking.RefTracker(scd, camd, bg, torch.eye(4), S.make_camera)
     rt.set_frame(gt)
     ms_t = timed_steps(rt.step, steps, warmup, flush, none)
-    return {"raster_fwd_bwd_iters_per_s": 1e3 * steps / ms_r, "tracking_iters_per_s": 1e3 * steps / ms_t,
-            "what": "unmodified reference CUDA sources built for sm_100a (oracle/Makefile); tracking iteration = "
-                    "reference wrapper allocations + eager Huber/L2 loss + torch Adam + torch pose update"}
+    out = {"raster_fwd_bwd_iters_per_s": 1e3 * steps / ms_r, "tracking_iters_per_s": 1e3 * steps / ms_t,
+           "what": "unmodified reference CUDA sources built for sm_100a (oracle/Makefile); tracking iteration = "
+                   "reference wrapper allocations + eager Huber/L2 loss + torch Adam + torch pose update; mapping "
+                   "iteration = config C4 (8-view window) with per-view activations, eager L1 loss, one autograd "
+                   "backward, torch Adam"}
+    try:
+        out["mapping_iters_per_s"] = ref_mapping_leg(dev, flush)
+    except Exception as ex:  # noqa: BLE001 - context only
+        out["mapping_error"] = repr(ex)[:200]
+    return out
+
+
+def ref_mapping_leg(dev, flush, P=200_000, window=8, iters=6, warmup=2):
+    """Config C4 through oracle/ref_mapping.py (the reference CUDA rasterizer inside the reference-style iteration)."""
+    from oracle import ref_gpu, ref_mapping
+    from monogs_b200 import scene as S
+    sc, cam = S.make_config("C2", P=P)
+    bg = torch.zeros(3, device=dev)
+    inv_sig = lambda x: torch.log(x / (1 - x))
+    raw = {"xyz": sc.means3D.to(dev), "f_dc": sc.shs.to(dev).contiguous(),
+           "opacity": inv_sig(sc.opacities.clamp(1e-4, 1 - 1e-4)).to(dev), "scaling": torch.log(sc.scales).to(dev),
+           "rotation": sc.rotations.to(dev)}
+    lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "opacity": 0.05, "scaling": 1e-3, "rotation": 1e-3}
+    cams, gts = [], []
+    for i in range(window):
+        tau = torch.tensor(S.GT_TAU) * (i - window / 2) * 0.5
+        c = S.make_camera(cam.W, cam.H, cam.fx, cam.fy, cam.cx, cam.cy, S.se3_exp(tau).float())
+        c = S.Camera(*[x.to(dev) if isinstance(x, torch.Tensor) else x for x in c])
+        with torch.no_grad():
+            fw = ref_gpu.forward(c, bg, raw["xyz"], torch.sigmoid(raw["opacity"]), shs=raw["f_dc"], scales=torch.exp(raw["scaling"]),
+                                 rotations=torch.nn.functional.normalize(raw["rotation"]), sh_degree=0)
+        cams.append(c)
+        gts.append((fw["color"] * 0.9 + 0.05).contiguous())
+    rm = ref_mapping.RefMapper(raw, lrs, cams, gts, bg)
+    ms = timed_steps(rm.step, iters, warmup, flush, lambda: None)
+    return 1e3 * iters / ms
 
 
 def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engine=True):
