@@ -10,9 +10,9 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
                       float* jac = nullptr, int jac_ncol = 0, const float* sh_rest = nullptr);
-int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s);
+int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false);
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
-                   const WsLayout& L, int64_t R_cap, cudaStream_t s);
+                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false);
 struct LossK;
 // optional fused loss epilogue of the forward blend (tracking path): per-pixel loss + un-normalised gradient images
 struct FusedLoss { const LossK* k; float grad_scale; float* g_img; float* g_depth; double* partials; bool fast; };

@@ -325,7 +325,7 @@ preprocess_kernel(const ViewConst v, const int P,
 constexpr int SCAN_THREADS = 1024, SCAN_IPT = 4, LARGE_LIST = 1024;
 __global__ void __launch_bounds__(SCAN_THREADS)
 tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_t R_cap,
-                 uint2* __restrict__ ranges, WsHeader* __restrict__ hdr) {
+                 uint2* __restrict__ ranges, WsHeader* __restrict__ hdr, const int heavy_first) {
   using Scan = cub::BlockScan<uint32_t, SCAN_THREADS>;
   __shared__ typename Scan::TempStorage tmp;
   __shared__ uint32_t n_large, max_count;
@@ -372,6 +372,7 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
   // counting sort of the tiles into 64 buckets of list length, longest lists first, written to
   // tile_ctr[i * TILE_CTR_STRIDE + 3].  CTAs are dispatched in blockIdx order, so the long tiles start at once and the
   // short ones fill the tail of the grid instead of the other way round.
+  if (!heavy_first) return;   // only the single-pass tracking blend reads the order (neutral at C3, +1 % at C1 / C2)
   __shared__ uint32_t bucket[64];
   if (threadIdx.x < 64) bucket[threadIdx.x] = 0u;
   __syncthreads();
@@ -527,10 +528,10 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
   }
 }
 
-int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s) {
+int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first) {
   MGS_PROF("tile_scan", s, tile_scan_kernel<<<1, SCAN_THREADS, 0, s>>>(
       ws_ptr<uint32_t>(ws, L.tile_ctr), v.gx * v.gy, (uint32_t)R_cap, ws_ptr<uint2>(ws, L.ranges),
-      ws_ptr<WsHeader>(ws, L.header)));
+      ws_ptr<WsHeader>(ws, L.header), heavy_first ? 1 : 0));
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }
@@ -566,9 +567,9 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
 }
 
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
-                   const WsLayout& L, int64_t R_cap, cudaStream_t s) {
+                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first) {
   const int tiles = v.gx * v.gy;
-  int rc = launch_tile_scan(v, ws, L, R_cap, s);   // ranges (clipped to R_cap), scatter cursors, header
+  int rc = launch_tile_scan(v, ws, L, R_cap, s, heavy_first);   // ranges (clipped to R_cap), scatter cursors, header
   if (rc) return rc;
   if (R_cap == 0 || P == 0) return MGS_OK;
   MGS_PROF("emit", s, emit_kernel<<<(P + 255) / 256, 256, 0, s>>>(

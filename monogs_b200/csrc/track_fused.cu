@@ -172,7 +172,7 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
     return rc;
   if (!t->fast_math) MGS_CUDA_TRY(cudaMemsetAsync(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
   MGS_CUDA_TRY(cudaMemsetAsync(tau_raw, 0, 6 * sizeof(float), s));
-  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s))) return rc;
+  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, /*heavy_first=*/!with_color))) return rc;
 
   LossK lk;
   lk.mode = t->loss_mode; lk.npix = (int)npix; lk.use_depth = use_depth;
