@@ -170,3 +170,34 @@ def test_map_engine_densify_between_steps():
     assert l1 < l0
     assert not eng.check_capacity()[1]
     del m_before
+
+
+@pytest.mark.parametrize("name", ["dense", "sh3"])
+def test_map_engine_pipeline_matches_single_stream(name):
+    """Seven views through the four-stream pipeline (resource sets reused from the fifth view on, atomic gradient and
+    statistics accumulation, two forwards in flight) against the one-stream schedule: same gradients up to the order of
+    the float additions, same integer outputs and statistics."""
+    from monogs_b200.mapping import MapEngine
+    sc, cam = U.small_case(name)
+    p0 = {k: v.detach().clone() for k, v in _raw_params(sc).items()}
+    views = _views(sc, cam, 7, True, False)
+    lrs = {k: 0.0 for k in p0}
+    res = {}
+    for overlap in (False, True):
+        eng = MapEngine({k: v.clone() for k, v in p0.items()}, lrs, sh_degree=sc.sh_degree, W=cam.W, H=cam.H, fast_math=False,
+                        overlap=overlap)
+        for _ in range(2):      # the second iteration reuses every resource set
+            out = eng.backward_only(views)
+        torch.cuda.synchronize()
+        assert not eng.check_capacity()[1]
+        res[overlap] = (eng, out)
+    (e0, o0), (e1, o1) = res[False], res[True]
+    assert U.rel_err(e1.loss_total, e0.loss_total) <= 1e-6
+    for k in p0:
+        if k == "rotation" and float(e0.grads[k].abs().max()) == 0.0: continue
+        assert U.rel_err(e1.grads[k], e0.grads[k]) <= 1e-5, k
+    for i in o0:
+        assert torch.equal(o1[i].radii, o0[i].radii) and torch.equal(o1[i].n_touched, o0[i].n_touched)
+        assert U.rel_err(o1[i].loss, o0[i].loss) <= 1e-6 and U.rel_err(o1[i].tau, o0[i].tau) <= 1e-5
+    assert U.rel_err(e1.xyz_gradient_accum, e0.xyz_gradient_accum) <= 1e-5
+    assert torch.equal(e1.denom, e0.denom) and torch.equal(e1.max_radii2D, e0.max_radii2D)
