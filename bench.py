@@ -506,7 +506,7 @@ def main():
             traffic = {"blend_track": 57.8e6}.get(top) if args.config == "C2" else None
             line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": prof[top].get("gbs"), "peak": peak, "unit": "GB/s",
                                 "frac": (prof[top].get("gbs") or 0) / peak, "traffic": traffic,
-                                "traffic_source": "profiles/r01c_ncu_full_blend_kernels.txt", "peak_source": src,
+                                "traffic_source": "profiles/r01d_ncu_full_blend_kernels.txt", "peak_source": src,
                                 "issue_slot_utilisation": {"blend_track": 0.683}.get(top),
                                 "share_of_step": prof[top]["avg_us"] / step_us,
                                 "note": "the blend kernels are issue/SFU-bound (one 48-B record feeds 256 pixel "
