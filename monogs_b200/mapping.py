@@ -234,9 +234,7 @@ class MapEngine:
         mv.exposure_b = view.exposure_b.data_ptr() if view.exposure_b is not None else None
         mv.rgb_boundary_threshold, mv.alpha, mv.update_stats = self.thr, self.alpha, int(view.update_stats)
         r = k % self.n_pipe if self.overlap else 0      # resource set of this view: workspace, slot, output images
-        while r > len(self.ws_extra):                   # allocated on first use: a one-view iteration needs only self.ws
-            self.ws_extra.append(torch.zeros_like(self.ws))
-            self._out_extra.append((torch.empty_like(self.color), torch.empty_like(self.depth), torch.empty_like(self.opacity)))
+        self._ensure_sets(r + 1)
         ws = self.ws if r == 0 else self.ws_extra[r - 1]
         color, depth, opacity = (self.color, self.depth, self.opacity) if r == 0 else self._out_extra[r - 1]
         mv.fast_math, mv.slot, mv.concurrent_backward = int(self.fast_math), r, int(self.overlap and self._concurrent)
@@ -245,6 +243,14 @@ class MapEngine:
         mv.tau, mv.dab, mv.loss = slot.tau.data_ptr(), slot.dab.data_ptr(), slot.loss.data_ptr()
         mv.workspace, mv.workspace_bytes, mv.R_cap = ws.data_ptr(), ws.numel(), self.R_cap
         return mv
+
+    def _ensure_sets(self, n):
+        """Resource sets 1 .. n-1 (set 0 is self.ws / self.color ...), allocated on first use: a one-view iteration needs
+        only set 0.  The zero fill runs on the CALLER's stream, so it must be enqueued before the event the other streams
+        wait for (_views_overlapped allocates before it records `begin`)."""
+        while n - 1 > len(self.ws_extra):
+            self.ws_extra.append(torch.zeros_like(self.ws))
+            self._out_extra.append((torch.empty_like(self.color), torch.empty_like(self.depth), torch.empty_like(self.opacity)))
 
     def render_backward_view(self, args, view: MapView, slot: MapViewResult):
         """One view, forward and backward back to back on the current stream."""
@@ -263,6 +269,7 @@ class MapEngine:
             self._bwd_streams = (torch.cuda.Stream(device=self.dev), torch.cuda.Stream(device=self.dev))
             self._fwd2_stream = torch.cuda.Stream(device=self.dev)
         fwd = (main, self._fwd2_stream)
+        self._ensure_sets(min(len(todo), self.n_pipe))   # their zero fill is on `main`, ahead of the `begin` event
         begin = torch.cuda.Event()
         begin.record(main)                       # mgs_map_begin (activations, zeroed accumulators) is on the caller's stream
         fwd[1].wait_event(begin)

@@ -292,3 +292,20 @@ def test_full_size_properties_c3():
     t2, _ = RZ.raster_backward_pose(rs, pr["st"], scd.means3D, scd.shs, None, scd.scales, scd.rotations, None, pr["radii"],
                                     2.0 * gc.cuda(), 2.0 * gd.cuda())
     assert U.rel_err(t2, 2.0 * pr["tau_pose"]) <= 1e-4
+
+
+@pytest.mark.parametrize("name", ["sh2", "sh3_full"])
+def test_sh_staging_with_unaligned_rows(name):
+    """The shared-memory SH staging (sh_stage.cuh) moves 16-byte chunks when a warp's block of rows is 16-byte aligned
+    and falls back to element-wise moves otherwise: a coefficient array that starts one float into its storage must
+    give bit-identical colours and the same SH gradients (up to the order of the float atomics of the backward blend)."""
+    sc, cam, bg, gc, gd = _setup(name)
+    scd, camd = U.to_dev(sc), U.to_dev(cam)
+    ref = _product(scd, camd, bg.cuda(), gc.cuda(), gd.cuda())
+    flat = torch.empty(scd.shs.numel() + 1, device="cuda")
+    flat[1:] = scd.shs.reshape(-1)
+    shifted = flat[1:].view_as(scd.shs)
+    assert shifted.is_contiguous() and shifted.data_ptr() % 16 == 4
+    got = _product(scd._replace(shs=shifted), camd, bg.cuda(), gc.cuda(), gd.cuda())
+    assert torch.equal(got["color"], ref["color"])
+    assert U.rel_err(got["g"]["color"], ref["g"]["color"]) <= 1e-5 and U.rel_err(got["g"]["means3D"], ref["g"]["means3D"]) <= 1e-5
