@@ -139,7 +139,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
         if (valid) {
           const float4 g2 = rec4[3 * j + 2];
           // vp = r * opacity * B^T geom  (geom: d alpha / d (mean2D, conic) up to the opacity factor, backward.cu:986-1010)
-          const float f = g1.w * __fdividef(1.f, 1.f - alpha);   // 1-alpha in [0.01,1]
+          const float f = g1.w * rcp_unit(1.f - alpha);   // 1-alpha in [0.01,1]
           const float gdx = G * dx, gdy = G * dy;
           float q[5];
           q[0] = f * (-gdx * g1.x - gdy * g1.y) * ddelx_dx;

@@ -183,6 +183,15 @@ __device__ __forceinline__ bool splat_hits(const float* rec, float x0, float x1,
   return !(fmin > thr * 1.001f + 1e-3f);         // NaN -> not culled
 }
 
+// 1 / x for x in [0.01, 1] (x = 1 - alpha, alpha <= 0.99): the bare MUFU.RCP.  __fdividef(1, x) wraps the same
+// instruction in a range fix-up for |x| > 2^126 (compare, select, conditional rescale: 4 more issue slots per call)
+// that can never trigger here; the value is the same.
+__device__ __forceinline__ float rcp_unit(const float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 // exp() of the blend exponent.  FAST = false: expf, bit-identical to the reference's images.  FAST = true (fused
 // tracking iteration only): one FMUL + MUFU.EX2 (ex2.approx.ftz), relative error ~4e-7 — far inside the 1e-4 image
 // tolerance; forward and backward of one iteration always use the same variant, so T is recovered consistently.

@@ -128,7 +128,7 @@ blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* 
       if (__ballot_sync(0xffffffffu, !skip) == 0u) continue;
       if (!skip) {
         const float4 g2 = rec4[3 * j + 2];
-        const float inv_1ma = __fdividef(1.f, 1.f - alpha);   // 1-alpha in [0.01,1]: MUFU.RCP, 1 ulp vs the IEEE divide
+        const float inv_1ma = rcp_unit(1.f - alpha);   // 1-alpha in [0.01,1]: MUFU.RCP, 1 ulp vs the IEEE divide
         T = T * inv_1ma;
         const float dchannel_dcolor = alpha * T;
         float dL_dalpha = 0.0f;

@@ -169,7 +169,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
       const float2 ae = make_float2(skip0 ? 0.f : alpha.x, skip1 ? 0.f : alpha.y);
       const float2 oma = one_minus2(ae);
       // 1-alpha in [0.01,1]: MUFU.RCP, 1 ulp vs the IEEE divide; exactly 1 for a skipped pixel
-      const float2 inv_1ma = make_float2(__fdividef(1.f, oma.x), __fdividef(1.f, oma.y));
+      const float2 inv_1ma = make_float2(rcp_unit(oma.x), rcp_unit(oma.y));
       T = __fmul2_rn(T, inv_1ma);
       const float2 w = __fmul2_rn(ae, T);                        // dchannel_dcolor
       const float2 oml = one_minus2(last_alpha);
