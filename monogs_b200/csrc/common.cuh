@@ -135,6 +135,23 @@ __device__ __forceinline__ void tile_rect(float2 p, int max_radius, int gx, int 
   rmax.y = min(gy, max(0, (int)((p.y + max_radius + TILE_Y - 1) / TILE_Y)));
 }
 
+// 1 / x for a normal positive x far from the ends of the exponent range (1 - alpha in [0.01, 1]; a positive-definite
+// conic entry): the bare MUFU.RCP.  __fdividef(1, x) wraps the same
+// instruction in a range fix-up for |x| > 2^126 (compare, select, conditional rescale: 4 more issue slots per call)
+// that can never trigger here; the value is the same.
+__device__ __forceinline__ float rcp_unit(const float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
+// log2 of a normal positive x (255 * opacity > 1): the bare MUFU.LG2, without __logf's denormal rescue
+__device__ __forceinline__ float lg2_normal(const float x) {
+  float r;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+
 // Half-extents (in pixels, rounded UP to fp16) of the axis-aligned box around the region where this splat can
 // pass the blend's `alpha >= 1/255` test (forward.cu:352-355): alpha = op*exp(power) >= 1/255  <=>
 // d^T conic d <= 2 ln(255 op), an ellipse whose box is sqrt(2 ln(255 op) * cov_xx/yy), cov = conic^-1.
@@ -172,24 +189,15 @@ __device__ __forceinline__ bool splat_hits(const float* rec, float x0, float x1,
   if (!(a > 0.f) || !(c > 0.f) || !(a * c - b * b > 0.f)) return true;   // not positive definite: never culled
   float fmin = __int_as_float(0x7f800000);
   if (dxe != 0.f) {
-    const float t = fminf(fmaxf(y - __fdividef(b * dxe, c), y0), y1) - y;
+    const float t = fminf(fmaxf(y - b * dxe * rcp_unit(c), y0), y1) - y;
     fmin = a * dxe * dxe + 2.f * b * dxe * t + c * t * t;
   }
   if (dye != 0.f) {
-    const float s = fminf(fmaxf(x - __fdividef(b * dye, a), x0), x1) - x;
+    const float s = fminf(fmaxf(x - b * dye * rcp_unit(a), x0), x1) - x;
     fmin = fminf(fmin, a * s * s + 2.f * b * s * dye + c * dye * dye);
   }
-  const float thr = 2.f * __logf(255.f * op);   // op > 1/255 here (the half-extent box of op <= 1/255 is empty)
+  const float thr = 1.3862943611198906f * lg2_normal(255.f * op);   // 2 ln(255 op); op > 1/255 here (the half-extent box of op <= 1/255 is empty)
   return !(fmin > thr * 1.001f + 1e-3f);         // NaN -> not culled
-}
-
-// 1 / x for x in [0.01, 1] (x = 1 - alpha, alpha <= 0.99): the bare MUFU.RCP.  __fdividef(1, x) wraps the same
-// instruction in a range fix-up for |x| > 2^126 (compare, select, conditional rescale: 4 more issue slots per call)
-// that can never trigger here; the value is the same.
-__device__ __forceinline__ float rcp_unit(const float x) {
-  float r;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-  return r;
 }
 
 // exp() of the blend exponent.  FAST = false: expf, bit-identical to the reference's images.  FAST = true (fused
