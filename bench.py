@@ -453,28 +453,45 @@ def main():
     n_rendered, overflow = tr.check_capacity()
     # ---- e2e: host frame in, loss + tangent out, every step, through the C-ABI tracker ----
     gt_host = gt.cpu().pin_memory()
-    loss_host = torch.zeros(1).pin_memory(); tau_host = torch.zeros(6).pin_memory()
 
     # PoseTracker.bind_host: one graph launch per iteration = [frame <- staging] -> {kernels || next frame's H2D into the
-    # staging buffer on a second stream} -> loss + tangent D2H.  Every step still moves its own 3.7 MB frame host -> device
-    # and its loss + tangent device -> host inside the timed region.
+    # staging buffer on a second stream} -> loss + tangent D2H.  Every step moves its own 3.7 MB frame host -> device and
+    # its loss + tangent device -> host inside the timed region.  e2e: step_host_lagged() (iteration k is launched before
+    # the host waits for the results of k-1, two result slots); e2e_sync: a full synchronize after every launch.
+    loss_host = torch.zeros(2).pin_memory(); tau_host = torch.zeros(2, 6).pin_memory()
     tr.bind_host(gt_host, loss_host, tau_host)
+    sink = [0.0]
 
-    def e2e_step():
+    def arm():
         if step_count[0] % 100 == 0:
             tr.set_frame(tr._stage)                      # new frame: fresh Adam state (slam_frontend.py:453)
         step_count[0] += 1
+
+    def e2e_lagged():
+        arm()
+        slot = tr.step_host_lagged()
+        if slot is not None: sink[0] += float(loss_host[slot]) + float(tau_host[slot, 0])   # the host reads the result
+
+    def e2e_sync_step():
+        arm()
         tr.step_host()
-    for _ in range(args.warmup): e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps): e2e_step()
-    torch.cuda.synchronize(); barrier()
-    te = torch.tensor([time.perf_counter() - t0], device=dev)
-    if world > 1: dist.all_reduce(te, op=dist.ReduceOp.MAX)
-    e2e = {"value": world * args.steps / float(te), "unit": "iters/s", "h2d_bytes_per_step": gt_host.numel() * 4,
-           "d2h_bytes_per_step": 28, "api": "monogs_b200.tracking.PoseTracker.bind_host/step_host over the C-ABI: one CUDA-graph "
-           "launch + one stream synchronize per iteration; the next frame's H2D copy runs beside the kernels"}
+        sink[0] += float(loss_host[0]) + float(tau_host[0, 0])
+
+    def run_e2e(fn):
+        for _ in range(args.warmup): fn()
+        torch.cuda.synchronize(); barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps): fn()
+        torch.cuda.synchronize(); barrier()
+        te = torch.tensor([time.perf_counter() - t0], device=dev)
+        if world > 1: dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        return world * args.steps / float(te)
+    e2e_sync = run_e2e(e2e_sync_step)
+    e2e = {"value": run_e2e(e2e_lagged), "unit": "iters/s", "h2d_bytes_per_step": gt_host.numel() * 4,
+           "d2h_bytes_per_step": 28, "value_sync_every_step": e2e_sync,
+           "api": "monogs_b200.tracking.PoseTracker.bind_host/step_host_lagged over the C-ABI: one CUDA-graph launch per "
+                  "iteration, the next frame's H2D copy beside the kernels, the host waits for iteration k-1 after launching k "
+                  "(value_sync_every_step: step_host(), a stream synchronize after every launch)"}
     line = {"metric": METRIC, "value": value, "unit": "iters/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",

@@ -186,35 +186,57 @@ class PoseTracker:
 
     def bind_host(self, gt_host, loss_host, tau_host):
         """Host-resident frame in, loss + pose tangent out, one graph launch per iteration (step_host()).
-        gt_host [3,H,W], loss_host [1] and tau_host [6] are pinned host tensors.  The captured graph is
+        gt_host [3,H,W], loss_host [S] and tau_host [S,6] (or [6] when S = 1) are pinned host tensors.  The captured graph is
             gt_image <- staging;  { the iteration's kernels  ||  staging <- gt_host on a second stream };
-            loss_host <- loss, tau_host <- tau
+            loss_host[s] <- loss, tau_host[s] <- tau
         so every iteration moves one frame host -> device and its results device -> host, with the upload of the
         NEXT iteration's frame hidden behind the current iteration's kernels: the contents of gt_host at replay k
         are what iteration k+1 tracks against (the frame stays the same for the ~100 iterations of a tracking loop,
-        slam_frontend.py:455); bind_host() itself uploads the first frame."""
+        slam_frontend.py:455); bind_host() itself uploads the first frame.
+        S = 2 result slots enable step_host_lagged(): iteration k is launched before the host waits for iteration
+        k-1, so the GPU never idles while the host turns around (one graph per slot, used alternately)."""
         assert gt_host.is_pinned() and loss_host.is_pinned() and tau_host.is_pinned()
+        S = loss_host.numel()
+        tau_slots = tau_host.view(S, 6)
         self._stage = torch.empty_like(self.gt_image)
         self._stage.copy_(gt_host, non_blocking=True)
         torch.cuda.synchronize()
         side = torch.cuda.Stream()
-        self.host_graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.host_graph):
-            main = torch.cuda.current_stream()
-            self.gt_image.copy_(self._stage, non_blocking=True)
-            side.wait_stream(main)
-            with torch.cuda.stream(side):
-                self._stage.copy_(gt_host, non_blocking=True)
-            self._enqueue()
-            loss_host.copy_(self.loss, non_blocking=True)
-            tau_host.copy_(self.tau, non_blocking=True)
-            main.wait_stream(side)
+        self.host_graphs, self._host_ev, self._host_k = [], [torch.cuda.Event() for _ in range(S)], 0
+        for slot in range(S):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                main = torch.cuda.current_stream()
+                self.gt_image.copy_(self._stage, non_blocking=True)
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    self._stage.copy_(gt_host, non_blocking=True)
+                self._enqueue()
+                loss_host[slot:slot + 1].copy_(self.loss, non_blocking=True)
+                tau_slots[slot].copy_(self.tau, non_blocking=True)
+                main.wait_stream(side)
+            self.host_graphs.append(g)
+        self.host_graph = self.host_graphs[0]
 
     def step_host(self, sync=True):
-        """One iteration of the host-bound pipeline set up by bind_host()."""
+        """One iteration of the host-bound pipeline set up by bind_host(); results in slot 0."""
         self.host_graph.replay()
         if sync:
             torch.cuda.current_stream().synchronize()
+
+    def step_host_lagged(self):
+        """Launch iteration k, then wait for iteration k-1 only.  Returns the result slot (0 / 1) that now holds
+        iteration k-1's loss and tangent, or None for the first call.  Needs two result slots (bind_host)."""
+        S = len(self.host_graphs)
+        assert S >= 2, "bind_host() with loss_host[2], tau_host[2, 6]"
+        k = self._host_k
+        self.host_graphs[k % S].replay()
+        self._host_ev[k % S].record()
+        self._host_k = k + 1
+        if k == 0:
+            return None
+        self._host_ev[(k - 1) % S].synchronize()
+        return (k - 1) % S
 
     def check_capacity(self):
         """Synchronous check of the device-side overflow flag; regrows the workspace if the splat count outgrew it."""

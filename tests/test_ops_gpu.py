@@ -189,3 +189,35 @@ def test_host_bound_tracking_pipeline_matches_device_steps():
     assert torch.equal(b._stage.cpu(), gt_host) and not torch.equal(b.gt_image.cpu(), gt_host)
     b.step_host()
     assert torch.equal(b.gt_image.cpu(), gt_host)
+
+
+def test_lagged_host_pipeline_returns_previous_iteration():
+    """step_host_lagged(): iteration k is launched before the host waits for k-1; the slot it returns holds exactly the
+    results step() produces for iteration k-1."""
+    from monogs_b200 import scene as S, rasterizer as RZ
+    from monogs_b200.tracking import PoseTracker
+    sc, cam = U.small_case("dense", T_w2c=torch.eye(4))
+    sc = sc._replace(shs=sc.shs[:, :1].contiguous(), sh_degree=0)
+    scd = U.to_dev(sc)
+    bg = torch.tensor([0.05, 0.1, 0.15]).cuda()
+    cam_gt = U.to_dev(S.make_camera(cam.W, cam.H, cam.fx, cam.fy, cam.cx, cam.cy, S.se3_exp(torch.tensor(S.GT_TAU)).float()))
+    gt = RZ.raster_forward(U.settings(cam_gt, bg, 0), scd.means3D, scd.opacities, scd.shs, None, scd.scales, scd.rotations, None)[0]
+    mk = lambda: PoseTracker(scd.means3D, scd.opacities, scd.shs, scd.scales, scd.rotations, 0, cam, bg, torch.eye(4))
+    a = mk()
+    a.set_frame(gt)
+    ref = []
+    for _ in range(7):
+        a.step()
+        ref.append((float(a.loss), a.tau.cpu().clone()))
+    b = mk()
+    loss_host, tau_host = torch.zeros(2).pin_memory(), torch.zeros(2, 6).pin_memory()
+    b.bind_host(gt.cpu().pin_memory(), loss_host, tau_host)
+    b.set_frame(b._stage)
+    got = []
+    for k in range(8):
+        slot = b.step_host_lagged()
+        assert (slot is None) == (k == 0)
+        if slot is not None:
+            got.append((float(loss_host[slot]), tau_host[slot].clone()))
+    for (l0, t0), (l1, t1) in zip(ref, got):
+        assert abs(l0 - l1) <= 1e-5 * abs(l0) + 1e-8 and U.rel_err(t1, t0) <= 1e-3
