@@ -25,13 +25,15 @@ def shard_views(n_views: int, world: int, rank: int) -> List[int]:
 class GradArena:
     """Flat gradient buffer with per-parameter views; p.grad aliases the arena."""
 
-    def __init__(self, params: Sequence[torch.Tensor]):
+    def __init__(self, params: Sequence[torch.Tensor], extra: int = 0):
         self.params = list(params)
         # every view starts on a 16-byte boundary: the kernels read / write [P,4] rows as float4
         pad4 = lambda n: (n + 3) // 4 * 4
         n = sum(pad4(p.numel()) for p in self.params)
         dev = self.params[0].device if self.params else "cpu"
-        self.flat = torch.zeros(n, device=dev, dtype=torch.float32)
+        # `extra` trailing floats ride along in the same all-reduce (the summed loss of a mapping iteration)
+        self.flat = torch.zeros(n + pad4(extra), device=dev, dtype=torch.float32)
+        self.extra = self.flat[n:n + extra]
         self.views = []
         off = 0
         for p in self.params:
@@ -143,14 +145,14 @@ class MapEngine:
         self.isotropic = self.params["scaling"].size(-1) == 1
         for p in self.params.values():
             assert p.is_contiguous() and p.dtype == torch.float32 and p.device == self.dev
-        self.arena = GradArena(list(self.params.values()))
+        self.arena = GradArena(list(self.params.values()), extra=1)   # + the iteration's loss: one all-reduce for both
         self.grads = dict(zip(self.params.keys(), self.arena.views))
         self.lrs = dict(lrs)
         self.opt = FusedAdam([{"params": [p], "lr": lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15)
         f = dict(device=self.dev, dtype=torch.float32)
         self.xyz_gradient_accum, self.denom = torch.zeros(self.P, **f), torch.zeros(self.P, **f)
         self.max_radii2D = torch.zeros(self.P, **f)
-        self.loss_total = torch.zeros(1, **f)
+        self.loss_total = self.arena.extra
         self.W, self.H = W, H
         self.scratch = torch.empty(self.lib.mgs_map_scratch_bytes(self.P, self.M, W, H), device=self.dev, dtype=torch.uint8)
         self.color, self.depth, self.opacity = torch.empty(3, H, W, **f), torch.empty(1, H, W, **f), torch.empty(1, H, W, **f)
@@ -319,7 +321,7 @@ class MapEngine:
         out = self.backward_only(views)
         if self.distributed and self.world > 1:
             dist.all_reduce(self.arena.flat, op=dist.ReduceOp.SUM, group=self.group)   # the single exchange of the path
-            dist.all_reduce(self.loss_total, op=dist.ReduceOp.SUM, group=self.group)
+                                                                                     # (gradients + loss_total, its last element)
         self.opt.step()
         return self.loss_total, out
 
@@ -362,7 +364,8 @@ class MapEngine:
         steps = {k: (self.opt.state[p]["step"] if p in self.opt.state else 0) for k, p in self.params.items()}
         self.params = {k: out["params"][k] for k in self.params}
         self.P = self.params["xyz"].size(0)
-        self.arena = GradArena(list(self.params.values()))
+        self.arena = GradArena(list(self.params.values()), extra=1)
+        self.loss_total = self.arena.extra
         self.grads = dict(zip(self.params.keys(), self.arena.views))
         self.opt = FusedAdam([{"params": [p], "lr": self.lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15)
         for k, p in self.params.items():
