@@ -159,11 +159,13 @@ def algorithmic_bytes(P, P_vis, R, R_cap, W, H, M=1):
 _CPU_STATE = {}
 
 
-def cpu_oracle_rate(cfg, tile_stride=1, gauss_stride=1):
+def cpu_oracle_rate(cfg, tile_stride=1, gauss_stride=1, stage_scale=None):
     """CPU oracle (oracle/golden.py) on the host cores, rasterizer forward+backward of the config.  A bounded sample:
     the alpha blend (fwd+bwd) runs on every `tile_stride`-th tile with its real tile lists, the per-Gaussian stages
-    (preprocess, per-Gaussian backward) on every `gauss_stride`-th Gaussian; each stage time is scaled by the inverse
-    of the fraction of work it covered.  Scene and tile lists are built once, untimed."""
+    (preprocess, per-Gaussian backward) on every `gauss_stride`-th Gaussian.  Each stage time is scaled to the whole
+    workload by `stage_scale` (four factors: full-pass time / sample time of that stage, measured by the caller) —
+    the oracle's vectorised stages have fixed costs, so the inverse work fraction (the default when stage_scale is
+    None) over-estimates the full pass for small samples.  Scene and tile lists are built once, untimed."""
     from monogs_b200 import scene as S
     from oracle import golden as G
     torch.set_num_threads(os.cpu_count())
@@ -197,9 +199,12 @@ def cpu_oracle_rate(cfg, tile_stride=1, gauss_stride=1):
     G.gaussian_backward(pre_s, g2d_s, sc.means3D[sel], cam, shs=sc.shs[sel], scales=sc.scales[sel], rotations=sc.rotations[sel],
                         sh_degree=sc.sh_degree)
     t4 = time.perf_counter()
-    full = (t1 - t0) / gfrac + (t2 - t1) / tfrac + (t3 - t2) / tfrac + (t4 - t3) / gfrac
+    stages = [t1 - t0, t2 - t1, t3 - t2, t4 - t3]
+    if stage_scale is None:
+        stage_scale = [1.0 / gfrac, 1.0 / tfrac, 1.0 / tfrac, 1.0 / gfrac]
+    full = sum(t * k for t, k in zip(stages, stage_scale))
     return 1.0 / full, {"measured_s": t4 - t0, "tile_fraction": tfrac, "gaussian_fraction": gfrac, "tile_stride": tile_stride,
-                        "gauss_stride": gauss_stride}
+                        "gauss_stride": gauss_stride, "stages": stages}
 
 
 def _sample_text(info):
@@ -212,18 +217,29 @@ def run_reference(args, rank):
     """--impl reference: the reference's CPU implementation of the path = the CPU oracle, rank 0 only."""
     if rank != 0:
         return
-    # a full pass costs ~8 s on 16 cores: size the per-step sample so that K+W steps end within ~2.5 minutes
+    # Size the per-step sample so that K+W steps end within ~3 minutes.  The oracle's stages have fixed costs, so a
+    # sample is NOT scaled by its work fraction: two untimed full passes (the second one warm) give each stage's
+    # full-pass time, the chosen sample is timed the same way, and every step's stage times are scaled by
+    # full / sample of that stage.  With stride 1 the factors are 1 and a step is the whole pass.
     n = args.warmup + args.steps
-    stride = 1
-    while stride < 64 and n * 8.0 / stride > 150.0:
+    cpu_oracle_rate(args.config)
+    _, full = cpu_oracle_rate(args.config)
+    t_full = sum(full["stages"])
+    stride, scale, cal = 1, None, full
+    while stride < 64 and n * sum(cal["stages"]) > 180.0:
         stride *= 2
+        cpu_oracle_rate(args.config, tile_stride=stride, gauss_stride=stride)
+        _, cal = cpu_oracle_rate(args.config, tile_stride=stride, gauss_stride=stride)
+    if stride > 1:
+        scale = [f / max(c, 1e-9) for f, c in zip(full["stages"], cal["stages"])]
     vals = []
     for i in range(n):
-        v, info = cpu_oracle_rate(args.config, tile_stride=stride, gauss_stride=stride)
+        v, info = cpu_oracle_rate(args.config, tile_stride=stride, gauss_stride=stride, stage_scale=scale)
         if i >= args.warmup:
             vals.append(v)
     v = len(vals) / sum(1.0 / x for x in vals)
-    sample = _sample_text(info)
+    sample = _sample_text(info) + (f"; stage times scaled by full-pass / sample time measured once before the steps "
+                                   f"(full pass {t_full:.2f} s)" if stride > 1 else "")
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "iters/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
