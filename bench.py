@@ -315,9 +315,10 @@ def ref_mapping_leg(dev, flush, P=200_000, window=8, iters=6, warmup=2):
     return 1e3 * iters / ms
 
 
-def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engine=True):
+def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engine=True, exchange="nccl"):
     """Config C4: 8-keyframe mapping window, views round-robin over ranks, one allreduce of the gradient arena,
-    fused Adam on every rank.  engine=True: monogs_b200.mapping.MapEngine (mgs_map_*: raw parameters, activations once
+    fused Adam on every rank (exchange="peer": reduce-scatter + Adam + parameter all-gather as ONE kernel over NVLink peer
+    mappings, mgs_peer_reduce_adam).  engine=True: monogs_b200.mapping.MapEngine (mgs_map_*: raw parameters, activations once
     per iteration, no host sync); engine=False: the same iteration through the drop-in autograd surface (MappingStep).
     Returns iterations/s (max over ranks)."""
     import torch.distributed as dist
@@ -344,7 +345,8 @@ def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engin
                                         rotations=torch.nn.functional.normalize(raw["rotation"]))[0]
         views.append((rs, (gt * 0.9 + 0.05).contiguous()))
     if engine:
-        eng = MapEngine({k: v.clone() for k, v in raw.items()}, lrs, sh_degree=0, W=cam.W, H=cam.H, capacity_headroom=1.5)
+        eng = MapEngine({k: v.clone() for k, v in raw.items()}, lrs, sh_degree=0, W=cam.W, H=cam.H, capacity_headroom=1.5,
+                        exchange=exchange)
         mviews = [MapView(rs, gt) for rs, gt in views]
         run = lambda: eng.step(mviews)
         nbytes = eng.arena.nbytes()
@@ -385,6 +387,12 @@ def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engin
                    "sum-allreduce of the gradient arena, fused Adam on every rank"}
     if engine:
         out["overflow"] = eng.check_capacity()[1]
+        out["exchange"] = ("mgs_peer_reduce_adam: gradient reduce-scatter + Adam + parameter all-gather in one kernel over "
+                           "NVLink peer mappings" if exchange == "peer" else "NCCL all_reduce of the gradient arena, then fused Adam")
+        if exchange == "peer":
+            out["peer_timeout_epoch"] = eng.block.error_epoch(None)
+            out["allreduce_bytes"] = 0
+            out["peer_bytes_in_out_per_rank"] = 2 * nbytes * (world - 1) // world
     return out
 
 
@@ -559,6 +567,11 @@ def main():
             line["mapping"] = mapping_leg(dev, rank, world)
         except Exception as ex:
             line["mapping"] = {"error": repr(ex)[:300]}
+        if world > 1:
+            try:
+                line["mapping_peer"] = mapping_leg(dev, rank, world, exchange="peer")
+            except Exception as ex:
+                line["mapping_peer"] = {"error": repr(ex)[:300]}
         if world == 1:
             try:
                 line["mapping_dropin"] = mapping_leg(dev, rank, world, iters=10, warmup=3, engine=False)

@@ -288,6 +288,45 @@ int mgs_map_view_backward(const mgs_map_args* args, const mgs_map_view* view, vo
  * weight * mean|s - mean(s)| once (weight = 10 in the reference). */
 int mgs_map_end(const mgs_map_args* args, int32_t add_regulariser, float regulariser_weight, void* stream);
 
+/* ---- peer-memory exchange of the data-parallel mapping step.  The reference has no multi-GPU path
+ *      (BackEnd.map, utils/slam_backend.py:157-333, renders the whole window on one GPU and calls
+ *      torch.optim.Adam.step, gaussian_model.py:285); in the sharded window every rank holds gradients of its own views
+ *      and the step that follows is "sum over ranks, then Adam".  mgs_peer_reduce_adam does both in one kernel over
+ *      NVLink peer mappings: rank r owns slice r of the flat arena, reads that slice of EVERY rank's gradient arena
+ *      (summed in rank order), applies Adam to it (moments of a slice live on its owner only) and stores the new
+ *      parameters into EVERY rank's parameter arena; the trailing loss element is summed into every rank's loss_out.
+ *      A second one-warp kernel holds the stream until all ranks have finished, so the caller's next launch may reuse
+ *      the gradient arena and read the parameters.  No host synchronisation, no NCCL call.
+ *      Blocks come from mgs_peer_alloc (cudaMalloc, zero filled) and are mapped into the other ranks' address space
+ *      with mgs_peer_export / mgs_peer_open (CUDA IPC; the 64-byte handles travel by any host channel). ---- */
+#define MGS_PEER_MAX 8
+#define MGS_PEER_MAX_SEGMENTS 16
+#define MGS_PEER_HANDLE_BYTES 64
+int mgs_peer_alloc(size_t bytes, void** out_ptr);
+int mgs_peer_free(void* ptr);
+int mgs_peer_export(const void* ptr, uint8_t* handle /* host u8[MGS_PEER_HANDLE_BYTES] */);
+int mgs_peer_open(const uint8_t* handle, void** out_ptr);
+int mgs_peer_close(void* ptr);
+size_t mgs_peer_flags_bytes(void);   /* size of one rank's flag block (zero filled before first use) */
+typedef struct mgs_peer_exchange {
+  int32_t world, rank;                      /* 1..MGS_PEER_MAX ranks; entries [0, world) of the tables are used */
+  float* param_arena[MGS_PEER_MAX];         /* f32[numel] of every rank, as mapped in THIS process; [rank] is local */
+  const float* grad_arena[MGS_PEER_MAX];    /* f32[numel], same layout */
+  float* loss_out[MGS_PEER_MAX];            /* f32[4] per rank: receives the summed loss segment */
+  uint32_t* flags[MGS_PEER_MAX];            /* mgs_peer_flags_bytes() per rank */
+  float* exp_avg; float* exp_avg_sq;        /* local f32[numel]; only this rank's slice is read and written */
+  int64_t numel;                            /* arena length in floats, multiple of 4 */
+  int32_t n_segments;                       /* consecutive segments covering [0, numel): one per parameter tensor */
+  int64_t segment_end[MGS_PEER_MAX_SEGMENTS];   /* exclusive ends in floats, multiples of 4 */
+  float segment_lr[MGS_PEER_MAX_SEGMENTS];      /* learning rate of the segment; < 0: sum only (the loss element) */
+} mgs_peer_exchange;
+/* step: Adam step number t >= 1 (identical on all ranks); epoch: strictly increasing per call on the same blocks,
+ * identical on all ranks, first call 1.  Slice r = float4 units [r*ceil(numel/4/world), ...). */
+int mgs_peer_reduce_adam(const mgs_peer_exchange* x, int32_t step, uint32_t epoch, float beta1, float beta2, float eps,
+                         void* stream);
+/* Synchronises `stream` and returns the epoch at which a wait of this rank timed out (0 = none). */
+int mgs_peer_error(const uint32_t* flags, uint32_t* out_epoch, void* stream);
+
 /* ---- densify / clone / split / prune of the parameter arena together with its Adam moments.
  *      Replaces GaussianModel.densify_and_prune / densify_and_clone / densify_and_split / prune_points and the optimizer
  *      surgery of cat_tensors_to_optimizer / _prune_optimizer (gaussian_splatting/scene/gaussian_model.py:470-691).

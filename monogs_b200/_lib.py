@@ -106,6 +106,19 @@ class MgsGaussianState(C.Structure):
     ]
 
 
+PEER_MAX, PEER_MAX_SEGMENTS, PEER_HANDLE_BYTES = 8, 16, 64
+
+
+class MgsPeerExchange(C.Structure):
+    _fields_ = [
+        ("world", C.c_int32), ("rank", C.c_int32),
+        ("param_arena", C.c_void_p * PEER_MAX), ("grad_arena", C.c_void_p * PEER_MAX), ("loss_out", C.c_void_p * PEER_MAX),
+        ("flags", C.c_void_p * PEER_MAX),
+        ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p), ("numel", C.c_int64), ("n_segments", C.c_int32),
+        ("segment_end", C.c_int64 * PEER_MAX_SEGMENTS), ("segment_lr", C.c_float * PEER_MAX_SEGMENTS),
+    ]
+
+
 _P, _I32, _I64, _U32, _F, _SZ = C.c_void_p, C.c_int32, C.c_int64, C.c_uint32, C.c_float, C.c_size_t
 _VP = C.POINTER(MgsView)
 
@@ -153,6 +166,14 @@ SIGNATURES = {
     "mgs_map_view_forward": (C.c_int, [C.POINTER(MgsMapArgs), C.POINTER(MgsMapView), _P]),
     "mgs_map_view_backward": (C.c_int, [C.POINTER(MgsMapArgs), C.POINTER(MgsMapView), _P]),
     "mgs_map_end": (C.c_int, [C.POINTER(MgsMapArgs), _I32, _F, _P]),
+    "mgs_peer_alloc": (C.c_int, [_SZ, C.POINTER(C.c_void_p)]),
+    "mgs_peer_free": (C.c_int, [_P]),
+    "mgs_peer_export": (C.c_int, [_P, C.c_char_p]),
+    "mgs_peer_open": (C.c_int, [C.c_char_p, C.POINTER(C.c_void_p)]),
+    "mgs_peer_close": (C.c_int, [_P]),
+    "mgs_peer_flags_bytes": (_SZ, []),
+    "mgs_peer_reduce_adam": (C.c_int, [C.POINTER(MgsPeerExchange), _I32, _U32, _F, _F, _F, _P]),
+    "mgs_peer_error": (C.c_int, [_P, C.POINTER(_U32), _P]),
 }
 
 _lib = None

@@ -3,7 +3,7 @@
 set -e
 cd "$(dirname "$0")"
 mkdir -p ../lib
-SRCS="raster_forward.cu blend_forward.cu blend_track.cu raster_backward.cu pose_backward.cu loss_adam.cu knn_pose.cu track_fused.cu map_fused.cu densify.cu frame_ops.cu api.cu"
+SRCS="raster_forward.cu blend_forward.cu blend_track.cu raster_backward.cu pose_backward.cu loss_adam.cu knn_pose.cu track_fused.cu map_fused.cu densify.cu frame_ops.cu peer_exchange.cu api.cu"
 OBJS=""
 pids=()
 for f in $SRCS; do

@@ -5,6 +5,7 @@
 // gaussian_splatting/scene/gaussian_model.py:285 and utils/slam_frontend.py:453.
 #include "launchers.h"
 #include "loss_pixel.cuh"
+#include "adam_elem.cuh"
 
 namespace mgs {
 
@@ -77,17 +78,6 @@ struct AdamPack {
   float beta1, beta2, eps, bc1, bc2_sqrt;
   const int* step_dev;   // when non-null the step number is *step_dev + 1 and bc1/bc2_sqrt are derived on device
 };
-
-// coefficients are passed by value: writing into the __grid_constant__-like parameter struct would make the compiler
-// spill the whole 700-byte AdamPack to local memory in every thread (measured: 9x DRAM write amplification)
-struct AdamCoef { float beta1, beta2, eps, bc2_sqrt; };
-__device__ __forceinline__ void adam_elem(float& p, const float g, float& m, float& v, const float step_size,
-                                          const AdamCoef a) {
-  m = m + (g - m) * (1.f - a.beta1);                 // exp_avg.lerp_(grad, 1 - beta1)
-  v = v * a.beta2 + (1.f - a.beta2) * g * g;         // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
-  const float denom = sqrtf(v) / a.bc2_sqrt + a.eps;
-  p = p - step_size * (m / denom);                   // param.addcdiv_(exp_avg, denom, value=-step_size)
-}
 
 __global__ void adam_step_inc_kernel(int* step_dev) { step_dev[0] += 1; }
 

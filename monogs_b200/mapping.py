@@ -25,21 +25,38 @@ def shard_views(n_views: int, world: int, rank: int) -> List[int]:
 class GradArena:
     """Flat gradient buffer with per-parameter views; p.grad aliases the arena."""
 
-    def __init__(self, params: Sequence[torch.Tensor], extra: int = 0):
+    def __init__(self, params: Sequence[torch.Tensor], extra: int = 0, flat: Optional[torch.Tensor] = None):
+        """flat: an existing zero-filled f32 buffer of exactly the arena's length to use instead of a new allocation
+        (the peer-visible gradient arena of monogs_b200.peer.PeerBlock)."""
         self.params = list(params)
         # every view starts on a 16-byte boundary: the kernels read / write [P,4] rows as float4
         pad4 = lambda n: (n + 3) // 4 * 4
         n = sum(pad4(p.numel()) for p in self.params)
         dev = self.params[0].device if self.params else "cpu"
         # `extra` trailing floats ride along in the same all-reduce (the summed loss of a mapping iteration)
-        self.flat = torch.zeros(n + pad4(extra), device=dev, dtype=torch.float32)
+        self.numel = n + pad4(extra)
+        if flat is None:
+            flat = torch.zeros(self.numel, device=dev, dtype=torch.float32)
+        assert flat.numel() == self.numel and flat.dtype == torch.float32 and flat.is_contiguous()
+        self.flat = flat
         self.extra = self.flat[n:n + extra]
-        self.views = []
-        off = 0
+        self.views = self.views_over(self.flat)
+        # exclusive end of every parameter's (padded) segment, then the trailing extra segment
+        self.segment_ends, off = [], 0
         for p in self.params:
-            v = self.flat[off:off + p.numel()].view(p.shape)
-            self.views.append(v)
             off += pad4(p.numel())
+            self.segment_ends.append(off)
+        if extra:
+            self.segment_ends.append(self.numel)
+
+    def views_over(self, flat: torch.Tensor):
+        """Per-parameter views with this arena's layout over another flat buffer of the same length."""
+        pad4 = lambda n: (n + 3) // 4 * 4
+        views, off = [], 0
+        for p in self.params:
+            views.append(flat[off:off + p.numel()].view(p.shape))
+            off += pad4(p.numel())
+        return views
 
     def attach(self):
         """Zero the arena and (re)install the aliases; call before the backward passes of an iteration."""
@@ -121,13 +138,19 @@ class MapEngine:
     activations once, every view of this rank's round-robin share rendered + back-propagated in place, the isotropic
     regulariser on rank 0, one sum-allreduce of the arena (NCCL over NVLink/NVSwitch; gloo in the CPU tests can not run
     this class — it needs the CUDA library), fused Adam on every rank.  Nothing in the iteration synchronises the host.
+
+    exchange="peer": the all-reduce + Adam pair becomes ONE kernel over NVLink peer mappings (mgs_peer_reduce_adam,
+    monogs_b200.peer): parameters and gradients live in a peer-visible block, every rank reduces and updates its
+    1/world slice of the arena and stores the new parameters into every rank's block; Adam moments are sharded (each
+    rank holds the live moments of its own slice; sync_stats() gathers them before a densify).
     """
 
     NAMES = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
 
     def __init__(self, params: Dict[str, torch.Tensor], lrs: Dict[str, float], sh_degree: int = 0, W: int = 640, H: int = 480,
                  capacity_headroom: float = 2.0, group=None, regulariser_weight: float = 10.0,
-                 rgb_boundary_threshold: float = 0.01, alpha: float = 0.95, fast_math: bool = True, overlap: bool = True):
+                 rgb_boundary_threshold: float = 0.01, alpha: float = 0.95, fast_math: bool = True, overlap: bool = True,
+                 exchange: str = "nccl"):
         from . import _lib as L
         from .ops import FusedAdam
         self.fast_math = fast_math   # ex2.approx exponent in the blend kernels (relative error ~4e-7), like PoseTracker
@@ -167,8 +190,45 @@ class MapEngine:
         self._keep = []
         self._slots = {}
         self._concurrent = False
+        assert exchange in ("nccl", "peer")
+        self.exchange, self.block = exchange, None
+        if exchange == "peer":
+            self._install_peer(steps=0)
 
     # ------------------------------------------------------------------------------------------------
+    def _install_peer(self, steps: int, moments=None):
+        """Move parameters and gradients into a peer-visible block (collective when world > 1): self.params become views
+        of the block's parameter arena, the gradient arena IS the block's, the Adam moments are two local flat buffers
+        with the same layout whose views are installed as the optimizer state."""
+        from .peer import PeerBlock
+        from .ops import FusedAdam
+        old = self.block
+        block = PeerBlock(self.arena.numel, self.dev)
+        if self.distributed and self.world > 1:
+            block.connect(self.group)
+        arena = GradArena(list(self.params.values()), extra=1, flat=block.grads)
+        with torch.no_grad():
+            pviews = arena.views_over(block.params)
+            for v, p in zip(pviews, self.params.values()):
+                v.copy_(p)
+        self.params = dict(zip(self.params.keys(), pviews))
+        arena.params = list(self.params.values())
+        self.arena, self.block = arena, block
+        self.grads = dict(zip(self.params.keys(), arena.views))
+        self.loss_total = arena.extra            # where mgs_map_end adds this rank's share
+        self._m_flat, self._v_flat = torch.zeros_like(block.params), torch.zeros_like(block.params)
+        mv, vv = arena.views_over(self._m_flat), arena.views_over(self._v_flat)
+        self.opt = FusedAdam([{"params": [p], "lr": self.lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15)
+        for i, (k, p) in enumerate(self.params.items()):
+            if moments is not None:
+                mv[i].copy_(moments[0][k]); vv[i].copy_(moments[1][k])
+            self.opt.state[p] = dict(step=steps, exp_avg=mv[i], exp_avg_sq=vv[i])
+        self._peer_step, self._epoch = steps, 0
+        self._peer_x = block.exchange(self._m_flat, self._v_flat, arena.segment_ends,
+                                      [self.lrs[k] for k in self.params] + [-1.0])
+        if old is not None:
+            old.close()
+
     def _args(self):
         L = self.L
         a = L.MgsMapArgs()
@@ -319,6 +379,16 @@ class MapEngine:
     def step(self, views: Sequence[MapView]):
         """One data-parallel mapping iteration.  Returns (total loss f32[1] on the device, {view index: MapViewResult})."""
         out = self.backward_only(views)
+        if self.exchange == "peer":
+            # gradient reduce-scatter + Adam on this rank's slice + parameter all-gather, one kernel over peer memory
+            from .rasterizer import _stream
+            self._peer_step += 1
+            self._epoch += 1
+            for st in self.opt.state.values():
+                st["step"] = self._peer_step
+            self.L.check(self.lib.mgs_peer_reduce_adam(C.byref(self._peer_x), self._peer_step, self._epoch, 0.9, 0.999, 1e-15,
+                                                       _stream()), "mgs_peer_reduce_adam")
+            return self.block.loss_out[:1], out
         if self.distributed and self.world > 1:
             dist.all_reduce(self.arena.flat, op=dist.ReduceOp.SUM, group=self.group)   # the single exchange of the path
                                                                                      # (gradients + loss_total, its last element)
@@ -332,6 +402,12 @@ class MapEngine:
             dist.all_reduce(self.xyz_gradient_accum, op=dist.ReduceOp.SUM, group=self.group)
             dist.all_reduce(self.denom, op=dist.ReduceOp.SUM, group=self.group)
             dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=self.group)
+            if self.exchange == "peer":      # sharded Adam moments: every rank fetches the live slices of the others
+                for r in range(self.world):
+                    b, e = self.block.slice_of(r)
+                    src = dist.get_global_rank(self.group, r) if self.group is not None else r
+                    dist.broadcast(self._m_flat[b:e], src=src, group=self.group)
+                    dist.broadcast(self._v_flat[b:e], src=src, group=self.group)
 
     def check_capacity(self):
         """Synchronous check of the device-side overflow flag of the last rendered view(s); regrows on overflow."""
@@ -376,6 +452,9 @@ class MapEngine:
         self.max_radii2D = torch.zeros(self.P, **f)
         self.scratch = torch.empty(self.lib.mgs_map_scratch_bytes(self.P, self.M, self.W, self.H), device=self.dev, dtype=torch.uint8)
         self.ws, self._slots = None, {}
+        if self.exchange == "peer":
+            assert len(set(steps.values())) == 1, "the engine's parameters step together"
+            self._install_peer(steps=next(iter(steps.values())), moments=(out["exp_avg"], out["exp_avg_sq"]))
 
     def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, percent_dense=0.01, unique_kfIDs=None,
                           n_obs=None, noise=None, generator=None):

@@ -1,0 +1,154 @@
+"""Cross-GPU check and timing of mgs_peer_reduce_adam (run under torchrun, one rank per GPU of one node):
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 \
+        scripts/check_peer_exchange.py [--out gpurun_out/peer_exchange.json]
+
+1. parity: seeded per-rank gradient arenas; the peer exchange against the rank-ordered sum of the all-gathered arenas
+   followed by the multi-tensor Adam — bit-exact parameters on every rank, bit-exact moments on the slice owners.
+2. timing (CUDA events, max over ranks): the exchange alone, peer kernel vs NCCL all_reduce + Adam, at the arena sizes
+   of configs C4 (200k Gaussians, SH 0) and C5 (2M Gaussians, SH 3).
+3. the C4 mapping iteration through MapEngine with either exchange (bench.mapping_leg).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+BETAS, EPS = (0.9, 0.999), 1e-15
+
+
+def layout(P, M, dev):
+    from monogs_b200.mapping import GradArena
+    shapes = {"xyz": (P, 3), "f_dc": (P, 1, 3), "opacity": (P, 1), "scaling": (P, 3), "rotation": (P, 4)}
+    lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "opacity": 0.05, "scaling": 1e-3, "rotation": 1e-3}
+    if M > 1:
+        shapes["f_rest"], lrs["f_rest"] = (P, M - 1, 3), 2.5e-3 / 20
+    protos = [torch.empty(s, device=dev) for s in shapes.values()]
+    return GradArena(protos, extra=1), list(lrs.values()) + [-1.0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default=None)
+    ap.add_argument("--no-mapping", action="store_true")
+    args = ap.parse_args()
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    from monogs_b200 import _lib as L, ops
+    from monogs_b200.peer import PeerBlock
+    lib = L.lib()
+    stream = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    report = {"world": world}
+
+    # ---- 1. parity ----
+    lay, lrs = layout(10_007, 1, dev)
+    n = lay.numel
+    blk = PeerBlock(n, dev).connect()
+    g = torch.Generator().manual_seed(17)
+    p0 = torch.randn(n, generator=g).to(dev)
+    blk.params.copy_(p0)
+    m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    x = blk.exchange(m, v, lay.segment_ends, lrs)
+    ref_p, ref_g = p0.clone(), torch.zeros(n, device=dev)
+    rv, rg = lay.views_over(ref_p), lay.views_over(ref_g)
+    for a, b in zip(rv, rg):
+        a.grad = b
+    opt = ops.FusedAdam([{"params": [a], "lr": lr} for a, lr in zip(rv, lrs[:-1])], lr=0.0, betas=BETAS, eps=EPS)
+    ok = True
+    for step in range(1, 5):
+        gr = torch.Generator().manual_seed(100 * step + rank)
+        mine = torch.randn(n, generator=gr).to(dev) * 10.0 ** (-(step % 4))
+        blk.grads.copy_(mine)
+        allg = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allg, mine)
+        s = allg[0].clone()
+        for t in allg[1:]:
+            s += t
+        ref_g.copy_(s)
+        opt.step()
+        torch.cuda.synchronize()
+        dist.barrier()
+        L.check(lib.mgs_peer_reduce_adam(C.byref(x), step, step, BETAS[0], BETAS[1], EPS, stream()), "mgs_peer_reduce_adam")
+        torch.cuda.synchronize()
+        for a, b in zip(rv, lay.views_over(blk.params)):
+            ok &= bool(torch.equal(a, b))
+        ok &= bool(torch.equal(blk.loss_out[:1], s[n - 4:n - 3]))
+        lo, hi = blk.slice_of(rank)
+        for k, (a, mv, vv) in enumerate(zip(rv, lay.views_over(m), lay.views_over(v))):
+            beg = lay.segment_ends[k - 1] if k else 0
+            i0, i1 = max(lo, beg) - beg, min(hi, beg + a.numel()) - beg
+            if i1 > i0:
+                ok &= bool(torch.equal(mv.reshape(-1)[i0:i1], opt.state[a]["exp_avg"].reshape(-1)[i0:i1]))
+                ok &= bool(torch.equal(vv.reshape(-1)[i0:i1], opt.state[a]["exp_avg_sq"].reshape(-1)[i0:i1]))
+    ok &= blk.error_epoch(stream()) == 0
+    t = torch.tensor([int(ok)], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    report["parity_bit_exact"] = bool(int(t))
+    blk.close()
+
+    # ---- 2. exchange timing ----
+    def timed(fn, iters=20, warm=5):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize(); dist.barrier()
+        tt = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt) * 1e3   # us
+
+    report["exchange_us"] = {}
+    for name, P, M in (("C4", 200_000, 1), ("C5", 2_000_000, 16)):
+        lay, lrs = layout(P, M, dev)
+        n = lay.numel
+        blk = PeerBlock(n, dev).connect()
+        blk.params.normal_(); blk.grads.normal_()
+        m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+        x = blk.exchange(m, v, lay.segment_ends, lrs)
+        state = {"e": 0}
+
+        def peer():
+            state["e"] += 1
+            L.check(lib.mgs_peer_reduce_adam(C.byref(x), state["e"], state["e"], BETAS[0], BETAS[1], EPS, stream()), "peer")
+        pp, gg = torch.randn(n, device=dev), torch.randn(n, device=dev)
+        pv, gv = lay.views_over(pp), lay.views_over(gg)
+        for a, b in zip(pv, gv):
+            a.grad = b
+        opt2 = ops.FusedAdam([{"params": [a], "lr": lr} for a, lr in zip(pv, lrs[:-1])], lr=0.0, betas=BETAS, eps=EPS)
+
+        def nccl():
+            dist.all_reduce(gg)
+            opt2.step()
+        t_peer, t_nccl = timed(peer), timed(nccl)
+        report["exchange_us"][name] = {"arena_bytes": 4 * n, "peer_reduce_adam": t_peer, "nccl_allreduce_plus_adam": t_nccl,
+                                       "peer_timeout_epoch": blk.error_epoch(stream())}
+        blk.close()
+        del pp, gg, m, v, opt2
+
+    # ---- 3. mapping iteration ----
+    if not args.no_mapping:
+        import bench
+        report["mapping_C4"] = {ex: bench.mapping_leg(dev, rank, world, exchange=ex)["iters_per_s"] for ex in ("nccl", "peer")}
+    if rank == 0:
+        print(json.dumps(report))
+        if args.out:
+            with open(args.out, "w") as f:
+                json.dump(report, f, indent=1)
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
