@@ -315,7 +315,7 @@ def ref_mapping_leg(dev, flush, P=200_000, window=8, iters=6, warmup=2):
     return 1e3 * iters / ms
 
 
-def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engine=True, exchange="nccl"):
+def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engine=True, exchange="nccl", cfg="C2"):
     """Config C4: 8-keyframe mapping window, views round-robin over ranks, one allreduce of the gradient arena,
     fused Adam on every rank (exchange="peer": reduce-scatter + Adam + parameter all-gather as ONE kernel over NVLink peer
     mappings, mgs_peer_reduce_adam).  engine=True: monogs_b200.mapping.MapEngine (mgs_map_*: raw parameters, activations once
@@ -325,27 +325,32 @@ def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engin
     from monogs_b200 import scene as S, ops
     from monogs_b200.mapping import MappingStep, MapEngine, MapView
     from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
-    sc, cam = S.make_config("C2", P=P)
+    sc, cam = S.make_config(cfg, P=P)
+    deg = sc.sh_degree
     bg = torch.zeros(3, device=dev)
     inv_sig = lambda x: torch.log(x / (1 - x))
-    raw = {"xyz": sc.means3D.to(dev), "f_dc": sc.shs.to(dev).contiguous(),
+    raw = {"xyz": sc.means3D.to(dev), "f_dc": sc.shs[:, :1].to(dev).contiguous(),
            "opacity": inv_sig(sc.opacities.clamp(1e-4, 1 - 1e-4)).to(dev), "scaling": torch.log(sc.scales).to(dev),
            "rotation": sc.rotations.to(dev)}
     lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "opacity": 0.05, "scaling": 1e-3, "rotation": 1e-3}
+    if sc.shs.size(1) > 1:      # config C5: SH degree 3 (gaussian_model.py:281: the rest coefficients train at lr / 20)
+        raw["f_rest"], lrs["f_rest"] = sc.shs[:, 1:].to(dev).contiguous(), 2.5e-3 / 20
+    shs_all = sc.shs.to(dev).contiguous()
     views = []
     for i in range(window):
         tau = torch.tensor(S.GT_TAU) * (i - window / 2) * 0.5
         c = S.make_camera(cam.W, cam.H, cam.fx, cam.fy, cam.cx, cam.cy, S.se3_exp(tau).float())
         c = S.Camera(*[x.to(dev) if isinstance(x, torch.Tensor) else x for x in c])
         rs = GaussianRasterizationSettings(c.H, c.W, c.tanfovx, c.tanfovy, bg, 1.0, c.viewmatrix, c.projmatrix,
-                                           c.projmatrix_raw, 0, c.campos, False, False)
+                                           c.projmatrix_raw, deg, c.campos, False, False)
         with torch.no_grad():
-            gt = GaussianRasterizer(rs)(means3D=raw["xyz"], means2D=torch.zeros_like(raw["xyz"]), shs=raw["f_dc"],
+            gt = GaussianRasterizer(rs)(means3D=raw["xyz"], means2D=torch.zeros_like(raw["xyz"]), shs=shs_all,
                                         opacities=torch.sigmoid(raw["opacity"]), scales=torch.exp(raw["scaling"]),
                                         rotations=torch.nn.functional.normalize(raw["rotation"]))[0]
         views.append((rs, (gt * 0.9 + 0.05).contiguous()))
     if engine:
-        eng = MapEngine({k: v.clone() for k, v in raw.items()}, lrs, sh_degree=0, W=cam.W, H=cam.H, capacity_headroom=1.5,
+        del shs_all
+        eng = MapEngine({k: v.clone() for k, v in raw.items()}, lrs, sh_degree=deg, W=cam.W, H=cam.H, capacity_headroom=1.5,
                         exchange=exchange)
         mviews = [MapView(rs, gt) for rs, gt in views]
         run = lambda: eng.step(mviews)
@@ -380,7 +385,7 @@ def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engin
     if world > 1: dist.barrier()
     t = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1: dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    out = {"iters_per_s": 1e3 * iters / float(t), "n_gpus": world, "window": window, "gaussians": P,
+    out = {"iters_per_s": 1e3 * iters / float(t), "n_gpus": world, "window": window, "gaussians": sc.means3D.size(0), "config": cfg,
            "views_per_rank": len(range(rank, window, world)), "allreduce_bytes": nbytes if world > 1 else 0,
            "scaling": "strong", "api": "MapEngine (mgs_map_*)" if engine else "drop-in autograd surface (MappingStep)",
            "what": "8-keyframe window: per-view render+mapping loss+full backward, isotropic regulariser, one "

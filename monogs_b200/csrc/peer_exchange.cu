@@ -21,11 +21,13 @@
 // hanging the GPU.
 #include "launchers.h"
 #include "adam_elem.cuh"
+#include "tma.cuh"
+#include <cstdlib>
+#include <cstring>
 #include "../../include/monogs_b200.h"
 
 namespace mgs {
 
-constexpr int PEER_CHUNK4 = 512;   // float4 per CTA (256 threads x 2)
 constexpr int FLAG_PHASE1 = MGS_PEER_MAX, FLAG_DONE = 2 * MGS_PEER_MAX, FLAG_ERROR = 2 * MGS_PEER_MAX + 1;
 
 struct PeerPack {
@@ -61,54 +63,113 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, 
   }
 }
 
+// shared -> global bulk store (TMA, async proxy), tracked by the issuing thread's bulk-group
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Persistent CTAs walk the rank's slice in chunks of PEER_CHUNK4 float4.  Per chunk one elected thread pulls that chunk
+// of EVERY rank's gradient arena into a shared-memory stage with 1-D bulk copies (TMA reads over NVLink need no
+// registers and stay in flight PEER_STAGES-1 chunks ahead: the ~2 us peer latency is covered by tens of KB per CTA),
+// the CTA sums the stage in rank order, applies Adam to its own parameters / moments (plain coalesced float4 traffic
+// on local HBM), stages the new parameters in shared memory and the elected thread pushes them to every rank's
+// parameter arena with bulk stores.
+template <int PEER_CHUNK4, int PEER_STAGES>   // float4 per chunk and rank; gradient stages in flight per CTA
 __global__ void __launch_bounds__(256) peer_reduce_adam_kernel(const __grid_constant__ PeerPack a) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint64_t full_bar[PEER_STAGES];
+  const int tid = threadIdx.x;
+  const uint32_t stage_bytes = (uint32_t)a.world * PEER_CHUNK4 * 16;
+  float4* out_buf = reinterpret_cast<float4*>(smem_raw + (size_t)PEER_STAGES * stage_bytes);   // 3 x PEER_CHUNK4 float4
   uint32_t* my_flags = a.flags[a.rank];
-  if (blockIdx.x == 0 && threadIdx.x < a.world) {   // phase 0: this rank's gradients are final (stream order)
-    __threadfence_system();
-    st_release_sys(a.flags[threadIdx.x] + a.rank, a.epoch);
+  if (tid == 0) {
+    for (int st = 0; st < PEER_STAGES; st++) mbar_init(&full_bar[st], 1);
+    mbar_init_fence();
   }
-  if (threadIdx.x < a.world) wait_flag(my_flags + threadIdx.x, a.epoch, my_flags + FLAG_ERROR);
+  if (blockIdx.x == 0 && tid < a.world) {   // phase 0: this rank's gradients are final (stream order)
+    __threadfence_system();
+    st_release_sys(a.flags[tid] + a.rank, a.epoch);
+  }
+  if (tid < a.world) wait_flag(my_flags + tid, a.epoch, my_flags + FLAG_ERROR);
   __syncthreads();
+
+  const long long n4 = a.q_end - a.q_begin;
+  const long long n_chunks = (n4 + PEER_CHUNK4 - 1) / PEER_CHUNK4;
+  // chunk k of this CTA is global chunk blockIdx.x + k * gridDim.x
+  const long long my_chunks = n_chunks > (long long)blockIdx.x ? (n_chunks - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  auto chunk_q0 = [&](long long k) { return a.q_begin + ((long long)blockIdx.x + k * gridDim.x) * PEER_CHUNK4; };
+  auto chunk_len = [&](long long q0) { const long long r = a.q_end - q0; return (int)(r < PEER_CHUNK4 ? r : PEER_CHUNK4); };
+  auto issue = [&](long long k) {   // elected thread: stage k % PEER_STAGES <- chunk k of every rank's gradient arena
+    const int st = (int)(k % PEER_STAGES);
+    const long long q0 = chunk_q0(k);
+    const uint32_t bytes = (uint32_t)chunk_len(q0) * 16;
+    mbar_expect_tx(&full_bar[st], bytes * a.world);
+    for (int r = 0; r < a.world; r++)
+      bulk_g2s(smem_raw + (size_t)st * stage_bytes + (size_t)r * PEER_CHUNK4 * 16, a.grad[r] + q0 * 4, bytes, &full_bar[st]);
+  };
+  if (tid == 0)
+    for (long long k = 0; k < PEER_STAGES - 1 && k < my_chunks; k++) issue(k);
 
   const AdamCoef co{a.beta1, a.beta2, a.eps, a.bc2_sqrt};
   float* __restrict__ p_own = a.param[a.rank];
+  for (long long k = 0; k < my_chunks; k++) {
+    const int st = (int)(k % PEER_STAGES);
+    if (tid == 0 && k + PEER_STAGES - 1 < my_chunks) issue(k + PEER_STAGES - 1);   // its stage was drained in iteration k-1
+    const long long q0 = chunk_q0(k);
+    const int len = chunk_len(q0);
+    float4 P4[PEER_CHUNK4 / 256], M4[PEER_CHUNK4 / 256], V4[PEER_CHUNK4 / 256];
 #pragma unroll
-  for (int it = 0; it < PEER_CHUNK4 / 256; it++) {
-    const long long q = a.q_begin + (long long)blockIdx.x * PEER_CHUNK4 + it * 256 + threadIdx.x;
-    if (q >= a.q_end) break;
-    const long long i = q * 4;
-    float4 G[MGS_PEER_MAX];
-#pragma unroll
-    for (int r = 0; r < MGS_PEER_MAX; r++)   // all loads in flight first; L1 bypassed (peer lines must not be reused)
-      if (r < a.world) G[r] = __ldcg(reinterpret_cast<const float4*>(a.grad[r] + i));
-    float4 S = G[0];
-#pragma unroll
-    for (int r = 1; r < MGS_PEER_MAX; r++)   // fixed rank order: the sum does not depend on the owner
-      if (r < a.world) { S.x += G[r].x; S.y += G[r].y; S.z += G[r].z; S.w += G[r].w; }
-    int sg = 0;
-    while (sg + 1 < a.n_seg && q >= a.seg_end4[sg]) sg++;
-    const float lr = a.seg_lr[sg];
-    if (lr < 0.f) {                          // the loss element: every rank gets the sum
-#pragma unroll
-      for (int r = 0; r < MGS_PEER_MAX; r++)
-        if (r < a.world) *reinterpret_cast<float4*>(a.loss_out[r]) = S;
-      continue;
+    for (int it = 0; it < PEER_CHUNK4 / 256; it++) {   // local HBM traffic goes out before the wait on the stage
+      const int j = it * 256 + tid;
+      if (j < len) {
+        const long long i = (q0 + j) * 4;
+        P4[it] = *reinterpret_cast<const float4*>(p_own + i);
+        M4[it] = *reinterpret_cast<const float4*>(a.m + i); V4[it] = *reinterpret_cast<const float4*>(a.v + i);
+      }
     }
-    const float step_size = lr / a.bc1;
-    float4 P4 = *reinterpret_cast<const float4*>(p_own + i);
-    float4 M4 = *reinterpret_cast<const float4*>(a.m + i), V4 = *reinterpret_cast<const float4*>(a.v + i);
-    adam_elem(P4.x, S.x, M4.x, V4.x, step_size, co); adam_elem(P4.y, S.y, M4.y, V4.y, step_size, co);
-    adam_elem(P4.z, S.z, M4.z, V4.z, step_size, co); adam_elem(P4.w, S.w, M4.w, V4.w, step_size, co);
-    *reinterpret_cast<float4*>(a.m + i) = M4; *reinterpret_cast<float4*>(a.v + i) = V4;
+    mbar_wait(&full_bar[st], (uint32_t)((k / PEER_STAGES) & 1));
+    const float4* stage = reinterpret_cast<const float4*>(smem_raw + (size_t)st * stage_bytes);
+    float4* out = out_buf + (size_t)(k % 3) * PEER_CHUNK4;
 #pragma unroll
-    for (int r = 0; r < MGS_PEER_MAX; r++)   // parameter all-gather: the owner stores its slice into every arena
-      if (r < a.world) *reinterpret_cast<float4*>(a.param[r] + i) = P4;
+    for (int it = 0; it < PEER_CHUNK4 / 256; it++) {
+      const int j = it * 256 + tid;
+      if (j >= len) break;
+      const long long q = q0 + j, i = q * 4;
+      float4 S = stage[j];
+      for (int r = 1; r < a.world; r++) {    // fixed rank order: the sum does not depend on the owner
+        const float4 G = stage[(size_t)r * PEER_CHUNK4 + j];
+        S.x += G.x; S.y += G.y; S.z += G.z; S.w += G.w;
+      }
+      int sg = 0;
+      while (sg + 1 < a.n_seg && q >= a.seg_end4[sg]) sg++;
+      const float lr = a.seg_lr[sg];
+      if (lr < 0.f) {                        // the loss element: every rank gets the sum; its parameter slot is unused
+        for (int r = 0; r < a.world; r++) *reinterpret_cast<float4*>(a.loss_out[r]) = S;
+      } else {
+        const float step_size = lr / a.bc1;
+        adam_elem(P4[it].x, S.x, M4[it].x, V4[it].x, step_size, co); adam_elem(P4[it].y, S.y, M4[it].y, V4[it].y, step_size, co);
+        adam_elem(P4[it].z, S.z, M4[it].z, V4[it].z, step_size, co); adam_elem(P4[it].w, S.w, M4[it].w, V4[it].w, step_size, co);
+        *reinterpret_cast<float4*>(a.m + i) = M4[it]; *reinterpret_cast<float4*>(a.v + i) = V4[it];
+      }
+      out[j] = P4[it];
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the staged parameters become visible to the bulk stores
+    __syncthreads();   // stage st is drained, out[k % 3] is complete; also orders thread 0's wait of iteration k-1
+    if (tid == 0) {
+      for (int r = 0; r < a.world; r++) bulk_s2g(a.param[r] + q0 * 4, out, (uint32_t)len * 16);   // parameter all-gather
+      bulk_commit();
+      bulk_wait_read<1>();   // the stores of iteration k-1 have read their buffer: out[(k+2) % 3] is free for k+2
+    }
   }
 
   // phase 1: the last CTA of this rank tells every rank that the slice is stored and the gradients are released
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) {
+  if (tid == 0) {
+    bulk_wait<0>();                                  // this CTA's parameter stores are complete
+    asm volatile("fence.proxy.async;" ::: "memory");
+    __threadfence_system();
     const unsigned int done = atomicAdd(my_flags + FLAG_DONE, 1u);
     if (done == gridDim.x - 1) {
       my_flags[FLAG_DONE] = 0;
@@ -126,6 +187,34 @@ __global__ void peer_wait_kernel(uint32_t* my_flags, int world, uint32_t epoch) 
 }  // namespace mgs
 
 using namespace mgs;
+
+// tuning knob (MGS_PEER_VARIANT, read once): chunk size x stage count of the kernel; 0 = the measured best
+static int peer_variant() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("MGS_PEER_VARIANT"); v = e ? atoi(e) : 0; }
+  return v;
+}
+
+template <int PEER_CHUNK4, int PEER_STAGES>
+static int launch_peer(const PeerPack& a, cudaStream_t s) {
+  const size_t smem = (size_t)PEER_STAGES * a.world * PEER_CHUNK4 * 16 + 3 * PEER_CHUNK4 * 16;
+  static int resident[MGS_PEER_MAX + 1] = {0};   // persistent grid: resident CTAs of the device for this world size
+  if (resident[a.world] == 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    MGS_CUDA_TRY(cudaGetDevice(&dev));
+    MGS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(peer_reduce_adam_kernel<PEER_CHUNK4, PEER_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+    MGS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, peer_reduce_adam_kernel<PEER_CHUNK4, PEER_STAGES>, 256, smem));
+    if (per_sm < 1) { set_error("peer_reduce_adam: %zu bytes of shared memory do not fit", smem); return MGS_ENOSPC; }
+    resident[a.world] = sms * per_sm;
+  }
+  long long ctas = (a.q_end - a.q_begin + PEER_CHUNK4 - 1) / PEER_CHUNK4;
+  if (ctas > resident[a.world]) ctas = resident[a.world];
+  if (ctas < 1) ctas = 1;   // an empty slice still takes part in both phases
+  MGS_PROF("peer_reduce_adam", s, peer_reduce_adam_kernel<PEER_CHUNK4, PEER_STAGES><<<(unsigned)ctas, 256, smem, s>>>(a));
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
+}
 
 extern "C" {
 
@@ -201,10 +290,16 @@ int mgs_peer_reduce_adam(const mgs_peer_exchange* x, int32_t step, uint32_t epoc
   a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
   a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
   cudaStream_t s = (cudaStream_t)stream;
-  long long ctas = (a.q_end - a.q_begin + PEER_CHUNK4 - 1) / PEER_CHUNK4;
-  if (ctas < 1) ctas = 1;   // an empty slice still takes part in both phases
-  MGS_PROF("peer_reduce_adam", s, peer_reduce_adam_kernel<<<(unsigned)ctas, 256, 0, s>>>(a));
-  MGS_LAUNCH_CHECK();
+  int rc = MGS_OK;
+  switch (peer_variant()) {
+    case 1: rc = launch_peer<1024, 3>(a, s); break;
+    case 2: rc = launch_peer<512, 4>(a, s); break;
+    case 3: rc = launch_peer<1024, 2>(a, s); break;
+    case 4: rc = launch_peer<256, 4>(a, s); break;
+    case 5: rc = launch_peer<256, 6>(a, s); break;
+    default: rc = launch_peer<512, 3>(a, s); break;
+  }
+  if (rc) return rc;
   MGS_PROF("peer_wait", s, peer_wait_kernel<<<1, 32, 0, s>>>(a.flags[a.rank], a.world, epoch));
   MGS_LAUNCH_CHECK();
   return MGS_OK;

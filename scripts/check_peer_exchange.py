@@ -38,6 +38,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--out", default=None)
     ap.add_argument("--no-mapping", action="store_true")
+    ap.add_argument("--c5", action="store_true", help="also the C5 stress mapping iteration (2M Gaussians, 1920x1080, SH 3), "
+                                                      "one view per rank, with either exchange")
+    ap.add_argument("--timing-only", action="store_true", help="skip the parity pass (kernel-variant sweeps)")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -47,9 +50,28 @@ def main():
     from monogs_b200.peer import PeerBlock
     lib = L.lib()
     stream = lambda: C.c_void_p(torch.cuda.current_stream().cuda_stream)
-    report = {"world": world}
+    report = {"world": world, "variant": os.environ.get("MGS_PEER_VARIANT", "0")}
 
-    # ---- 1. parity ----
+    if not args.timing_only:
+        parity(report, rank, world, dev, lib, L, ops, PeerBlock, stream)
+    timing(report, rank, world, dev, lib, L, ops, PeerBlock, stream)
+    if not args.no_mapping:
+        import bench
+        report["mapping_C4"] = {ex: bench.mapping_leg(dev, rank, world, exchange=ex)["iters_per_s"] for ex in ("nccl", "peer")}
+    if args.c5:
+        import bench
+        report["mapping_C5_one_view_per_rank"] = {
+            ex: bench.mapping_leg(dev, rank, world, iters=6, warmup=2, P=None, window=world, exchange=ex, cfg="C5")["iters_per_s"]
+            for ex in ("nccl", "peer")}
+    if rank == 0:
+        print(json.dumps(report))
+        if args.out:
+            with open(args.out, "w") as f:
+                json.dump(report, f, indent=1)
+    dist.destroy_process_group()
+
+
+def parity(report, rank, world, dev, lib, L, ops, PeerBlock, stream):
     lay, lrs = layout(10_007, 1, dev)
     n = lay.numel
     blk = PeerBlock(n, dev).connect()
@@ -95,7 +117,8 @@ def main():
     report["parity_bit_exact"] = bool(int(t))
     blk.close()
 
-    # ---- 2. exchange timing ----
+
+def timing(report, rank, world, dev, lib, L, ops, PeerBlock, stream):
     def timed(fn, iters=20, warm=5):
         for _ in range(warm):
             fn()
@@ -110,6 +133,20 @@ def main():
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         return float(tt) * 1e3   # us
 
+    # NVLink reference: a plain peer copy of 256 MB (rank 0 pulls from the next device), the denominator of the
+    # exchange's link bandwidth
+    if rank == 0 and torch.cuda.device_count() > 1:
+        src = torch.empty(64 << 20, device=torch.device("cuda", 1), dtype=torch.float32)
+        dst = torch.empty(64 << 20, device=dev, dtype=torch.float32)
+        for _ in range(3): dst.copy_(src)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10): dst.copy_(src)
+        e1.record(); torch.cuda.synchronize()
+        report["p2p_copy_gbs"] = 10 * src.numel() * 4 / (e0.elapsed_time(e1) * 1e-3) / 1e9
+        del src, dst
+    dist.barrier()
     report["exchange_us"] = {}
     for name, P, M in (("C4", 200_000, 1), ("C5", 2_000_000, 16)):
         lay, lrs = layout(P, M, dev)
@@ -134,20 +171,13 @@ def main():
             opt2.step()
         t_peer, t_nccl = timed(peer), timed(nccl)
         report["exchange_us"][name] = {"arena_bytes": 4 * n, "peer_reduce_adam": t_peer, "nccl_allreduce_plus_adam": t_nccl,
-                                       "peer_timeout_epoch": blk.error_epoch(stream())}
+                                       "peer_timeout_epoch": blk.error_epoch(stream()),
+                                       # every direction of a rank's links carries the gradient slices it pulls in (read responses) or serves, plus
+                                       # the parameter slices it pushes / receives: 2 x (world-1)/world x arena bytes each way
+                                       "peer_link_gbs_per_direction": 2 * 4 * n * (world - 1) / world / (t_peer * 1e-6) / 1e9}
         blk.close()
         del pp, gg, m, v, opt2
 
-    # ---- 3. mapping iteration ----
-    if not args.no_mapping:
-        import bench
-        report["mapping_C4"] = {ex: bench.mapping_leg(dev, rank, world, exchange=ex)["iters_per_s"] for ex in ("nccl", "peer")}
-    if rank == 0:
-        print(json.dumps(report))
-        if args.out:
-            with open(args.out, "w") as f:
-                json.dump(report, f, indent=1)
-    dist.destroy_process_group()
 
 
 if __name__ == "__main__":
