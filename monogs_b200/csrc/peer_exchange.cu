@@ -44,6 +44,9 @@ struct PeerPack {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
@@ -165,17 +168,22 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_kernel(const __grid_cons
     }
   }
 
-  // phase 1: the last CTA of this rank tells every rank that the slice is stored and the gradients are released
+  // phase 1: the last CTA of this rank tells every rank that the slice is stored and the gradients are released.
+  // One lane per destination: every lane fences once and stores its flag, so the eight signals leave together instead
+  // of eight release stores each waiting for the acknowledgement of the one before.
+  __shared__ int s_last;
   if (tid == 0) {
     bulk_wait<0>();                                  // this CTA's parameter stores are complete
     asm volatile("fence.proxy.async;" ::: "memory");
     __threadfence_system();
     const unsigned int done = atomicAdd(my_flags + FLAG_DONE, 1u);
-    if (done == gridDim.x - 1) {
-      my_flags[FLAG_DONE] = 0;
-      __threadfence_system();
-      for (int r = 0; r < a.world; r++) st_release_sys(a.flags[r] + FLAG_PHASE1 + a.rank, a.epoch);
-    }
+    s_last = (done == gridDim.x - 1);
+    if (s_last) my_flags[FLAG_DONE] = 0;
+  }
+  __syncthreads();
+  if (s_last && tid < a.world) {
+    __threadfence_system();
+    st_relaxed_sys(a.flags[tid] + FLAG_PHASE1 + a.rank, a.epoch);
   }
 }
 
