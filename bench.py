@@ -315,7 +315,7 @@ def ref_mapping_leg(dev, flush, P=200_000, window=8, iters=6, warmup=2):
     return 1e3 * iters / ms
 
 
-def mapping_leg(dev, rank, world, iters=20, warmup=5, P=200_000, window=8, engine=True, exchange="nccl", cfg="C2"):
+def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engine=True, exchange="nccl", cfg="C2"):
     """Config C4: 8-keyframe mapping window, views round-robin over ranks, one allreduce of the gradient arena,
     fused Adam on every rank (exchange="peer": reduce-scatter + Adam + parameter all-gather as ONE kernel over NVLink peer
     mappings, mgs_peer_reduce_adam).  engine=True: monogs_b200.mapping.MapEngine (mgs_map_*: raw parameters, activations once

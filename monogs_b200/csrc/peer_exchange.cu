@@ -92,10 +92,9 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_kernel(const __grid_cons
     for (int st = 0; st < PEER_STAGES; st++) mbar_init(&full_bar[st], 1);
     mbar_init_fence();
   }
-  if (blockIdx.x == 0 && tid < a.world) {   // phase 0: this rank's gradients are final (stream order)
-    __threadfence_system();
-    st_release_sys(a.flags[tid] + a.rank, a.epoch);
-  }
+  if (blockIdx.x == 0 && tid < a.world)     // phase 0: this rank's gradients are final (stream order); the release
+    st_release_sys(a.flags[tid] + a.rank, a.epoch);   // store carries the system-scope fence
+
   if (tid < a.world) wait_flag(my_flags + tid, a.epoch, my_flags + FLAG_ERROR);
   __syncthreads();
 
