@@ -394,7 +394,10 @@ def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engin
         out["overflow"] = eng.check_capacity()[1]
         out["exchange"] = ("mgs_peer_reduce_adam: gradient reduce-scatter + Adam + parameter all-gather in one kernel over "
                            "NVLink peer mappings" if exchange == "peer" else "NCCL all_reduce of the gradient arena, then fused Adam")
-        if exchange == "peer":
+        if exchange == "nvls":
+            out["exchange"] = ("mgs_peer_reduce_adam over the NVSwitch multicast mapping: multimem.ld_reduce of the gradient "
+                               "slices (summed in the switch) + Adam + multimem.st of the parameters, one kernel")
+        if exchange != "nccl":
             out["peer_timeout_epoch"] = eng.block.error_epoch(None)
             out["allreduce_bytes"] = 0
             out["peer_bytes_in_out_per_rank"] = 2 * nbytes * (world - 1) // world
@@ -577,6 +580,10 @@ def main():
                 line["mapping_peer"] = mapping_leg(dev, rank, world, exchange="peer")
             except Exception as ex:
                 line["mapping_peer"] = {"error": repr(ex)[:300]}
+            try:
+                line["mapping_nvls"] = mapping_leg(dev, rank, world, exchange="nvls")
+            except Exception as ex:
+                line["mapping_nvls"] = {"error": repr(ex)[:300]}
         if world == 1:
             try:
                 line["mapping_dropin"] = mapping_leg(dev, rank, world, iters=10, warmup=3, engine=False)

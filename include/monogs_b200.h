@@ -319,6 +319,12 @@ typedef struct mgs_peer_exchange {
   int32_t n_segments;                       /* consecutive segments covering [0, numel): one per parameter tensor */
   int64_t segment_end[MGS_PEER_MAX_SEGMENTS];   /* exclusive ends in floats, multiples of 4 */
   float segment_lr[MGS_PEER_MAX_SEGMENTS];      /* learning rate of the segment; < 0: sum only (the loss element) */
+  /* Optional NVSwitch multicast (NVLS) mappings of the same memory — one address that reaches the arena of EVERY rank
+   * (cuMulticast* objects; torch.distributed._symmetric_memory provides them).  All three or none.  When given, the
+   * gradients are read with multimem.ld_reduce (summed inside the switch, association order unspecified) and the
+   * parameters / loss are written with multimem.st; the unicast tables above are still used for the flags, the own
+   * parameters and nothing else. */
+  const float* grad_multicast; float* param_multicast; float* loss_multicast;
 } mgs_peer_exchange;
 /* step: Adam step number t >= 1 (identical on all ranks); epoch: strictly increasing per call on the same blocks,
  * identical on all ranks, first call 1.  Slice r = float4 units [r*ceil(numel/4/world), ...). */

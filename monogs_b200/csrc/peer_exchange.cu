@@ -33,6 +33,7 @@ constexpr int FLAG_PHASE1 = MGS_PEER_MAX, FLAG_DONE = 2 * MGS_PEER_MAX, FLAG_ERR
 struct PeerPack {
   float* param[MGS_PEER_MAX]; const float* grad[MGS_PEER_MAX]; float* loss_out[MGS_PEER_MAX]; uint32_t* flags[MGS_PEER_MAX];
   float *m, *v;
+  const float* grad_mc; float* param_mc; float* loss_mc;   // NVSwitch multicast mappings of the same arenas (null: unicast path)
   long long q_begin, q_end;                       // this rank's slice of the arena, in float4 units
   long long seg_end4[MGS_PEER_MAX_SEGMENTS];      // segment ends, float4 units
   float seg_lr[MGS_PEER_MAX_SEGMENTS];            // < 0: sum only (the loss element)
@@ -186,6 +187,76 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_kernel(const __grid_cons
   }
 }
 
+// ---- NVSwitch multicast variant (NVLS) -------------------------------------------------------------------------------
+// The gradient arenas are read through the multicast mapping with multimem.ld_reduce: the switch fetches the addressed
+// 16 bytes from EVERY rank and returns their fp32 sum, so the owner receives its slice once instead of once per peer;
+// multimem.st through the multicast mapping of the parameter arenas hands one copy to the switch, which writes all
+// ranks.  Link volume per rank and direction drops from 2(N-1)/N x arena to ~1 x arena (serve (N-1)/N of the own
+// gradients + push 1/N of the parameters one way, receive 1/N reduced + (N-1)/N of the parameters the other way).
+// The sum's association order is the switch's; every rank still ends with identical parameters because only the owner
+// of a slice computes it.  Register path: PEER_MC_UNROLL independent reductions per thread in flight.
+__device__ __forceinline__ float4 multimem_ld_reduce_add(const float* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(mc) : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st(float* mc, const float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+template <int PEER_MC_UNROLL>
+__global__ void __launch_bounds__(256) peer_reduce_adam_mc_kernel(const __grid_constant__ PeerPack a) {
+  const int tid = threadIdx.x;
+  uint32_t* my_flags = a.flags[a.rank];
+  if (blockIdx.x == 0 && tid < a.world) st_release_sys(a.flags[tid] + a.rank, a.epoch);   // phase 0, as in the unicast kernel
+  if (tid < a.world) wait_flag(my_flags + tid, a.epoch, my_flags + FLAG_ERROR);
+  __syncthreads();
+  const AdamCoef co{a.beta1, a.beta2, a.eps, a.bc2_sqrt};
+  float* p_own = a.param[a.rank];
+  constexpr int U = PEER_MC_UNROLL;
+  for (long long base = a.q_begin + (long long)blockIdx.x * 256 * U; base < a.q_end; base += (long long)gridDim.x * 256 * U) {
+    float4 S[U], P4[U], M4[U], V4[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const long long q = base + u * 256 + tid;
+      if (q < a.q_end) {
+        S[u] = multimem_ld_reduce_add(a.grad_mc + q * 4);
+        P4[u] = *reinterpret_cast<const float4*>(p_own + q * 4);
+        M4[u] = *reinterpret_cast<const float4*>(a.m + q * 4); V4[u] = *reinterpret_cast<const float4*>(a.v + q * 4);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const long long q = base + u * 256 + tid;
+      if (q >= a.q_end) break;
+      int sg = 0;
+      while (sg + 1 < a.n_seg && q >= a.seg_end4[sg]) sg++;
+      const float lr = a.seg_lr[sg];
+      if (lr < 0.f) { multimem_st(a.loss_mc, S[u]); continue; }   // the loss element: every rank gets the sum
+      const float step_size = lr / a.bc1;
+      adam_elem(P4[u].x, S[u].x, M4[u].x, V4[u].x, step_size, co); adam_elem(P4[u].y, S[u].y, M4[u].y, V4[u].y, step_size, co);
+      adam_elem(P4[u].z, S[u].z, M4[u].z, V4[u].z, step_size, co); adam_elem(P4[u].w, S[u].w, M4[u].w, V4[u].w, step_size, co);
+      *reinterpret_cast<float4*>(a.m + q * 4) = M4[u]; *reinterpret_cast<float4*>(a.v + q * 4) = V4[u];
+      multimem_st(a.param_mc + q * 4, P4[u]);   // parameter all-gather: one store, the switch writes every rank
+    }
+  }
+  // phase 1
+  __shared__ int s_last;
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned int done = atomicAdd(my_flags + FLAG_DONE, 1u);
+    s_last = (done == gridDim.x - 1);
+    if (s_last) my_flags[FLAG_DONE] = 0;
+  }
+  __syncthreads();
+  if (s_last && tid < a.world) {
+    __threadfence_system();
+    st_relaxed_sys(a.flags[tid] + FLAG_PHASE1 + a.rank, a.epoch);
+  }
+}
+
 __global__ void peer_wait_kernel(uint32_t* my_flags, int world, uint32_t epoch) {
   if ((int)threadIdx.x < world) wait_flag(my_flags + FLAG_PHASE1 + threadIdx.x, epoch, my_flags + FLAG_ERROR);
   __threadfence_system();
@@ -200,6 +271,30 @@ static int peer_variant() {
   static int v = -1;
   if (v < 0) { const char* e = getenv("MGS_PEER_VARIANT"); v = e ? atoi(e) : 0; }
   return v;
+}
+
+static int peer_mc_unroll() {   // tuning knob (MGS_PEER_MC_UNROLL, read once): reductions in flight per thread
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("MGS_PEER_MC_UNROLL"); v = e ? atoi(e) : 4; }
+  return v;
+}
+
+template <int U>
+static int launch_peer_mc(const PeerPack& a, cudaStream_t s) {
+  static int resident_mc = 0;
+  if (resident_mc == 0) {
+    int dev = 0, sms = 0, per_sm = 0;
+    MGS_CUDA_TRY(cudaGetDevice(&dev));
+    MGS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    MGS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, peer_reduce_adam_mc_kernel<U>, 256, 0));
+    resident_mc = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  long long ctas = (a.q_end - a.q_begin + 256 * U - 1) / (256 * U);
+  if (ctas > resident_mc) ctas = resident_mc;
+  if (ctas < 1) ctas = 1;
+  MGS_PROF("peer_reduce_adam_mc", s, peer_reduce_adam_mc_kernel<U><<<(unsigned)ctas, 256, 0, s>>>(a));
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
 }
 
 template <int PEER_CHUNK4, int PEER_STAGES>
@@ -290,6 +385,11 @@ int mgs_peer_reduce_adam(const mgs_peer_exchange* x, int32_t step, uint32_t epoc
   if (prev != x->numel) { set_error("peer_reduce_adam: the segments must cover the arena"); return MGS_EINVAL; }
   a.n_seg = x->n_segments; a.world = x->world; a.rank = x->rank; a.epoch = epoch;
   a.m = x->exp_avg; a.v = x->exp_avg_sq;
+  a.grad_mc = x->grad_multicast; a.param_mc = x->param_multicast; a.loss_mc = x->loss_multicast;
+  const bool mc = a.grad_mc || a.param_mc || a.loss_mc;
+  if (mc && (!a.grad_mc || !a.param_mc || !a.loss_mc || (((uintptr_t)a.grad_mc | (uintptr_t)a.param_mc | (uintptr_t)a.loss_mc) & 15))) {
+    set_error("peer_reduce_adam: the multicast mappings come as three 16-byte aligned pointers or not at all"); return MGS_EINVAL;
+  }
   const long long n4 = x->numel / 4, per = (n4 + x->world - 1) / x->world;
   a.q_begin = per * x->rank < n4 ? per * x->rank : n4;
   a.q_end = a.q_begin + per < n4 ? a.q_begin + per : n4;
@@ -298,6 +398,13 @@ int mgs_peer_reduce_adam(const mgs_peer_exchange* x, int32_t step, uint32_t epoc
   a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
   cudaStream_t s = (cudaStream_t)stream;
   int rc = MGS_OK;
+  if (mc) {
+    switch (peer_mc_unroll()) {
+      case 2: rc = launch_peer_mc<2>(a, s); break;
+      case 8: rc = launch_peer_mc<8>(a, s); break;
+      default: rc = launch_peer_mc<4>(a, s); break;
+    }
+  } else
   switch (peer_variant()) {
     case 1: rc = launch_peer<1024, 3>(a, s); break;
     case 2: rc = launch_peer<512, 4>(a, s); break;

@@ -143,6 +143,8 @@ class MapEngine:
     monogs_b200.peer): parameters and gradients live in a peer-visible block, every rank reduces and updates its
     1/world slice of the arena and stores the new parameters into every rank's block; Adam moments are sharded (each
     rank holds the live moments of its own slice; sync_stats() gathers them before a densify).
+    exchange="nvls": the same kernel over an NVSwitch multicast mapping of the blocks (torch symmetric memory): the
+    gradient sum happens inside the switch (multimem.ld_reduce) and one multimem.st writes the parameters of all ranks.
     """
 
     NAMES = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
@@ -190,9 +192,9 @@ class MapEngine:
         self._keep = []
         self._slots = {}
         self._concurrent = False
-        assert exchange in ("nccl", "peer")
+        assert exchange in ("nccl", "peer", "nvls")
         self.exchange, self.block = exchange, None
-        if exchange == "peer":
+        if exchange != "nccl":
             self._install_peer(steps=0)
 
     # ------------------------------------------------------------------------------------------------
@@ -203,7 +205,8 @@ class MapEngine:
         from .peer import PeerBlock
         from .ops import FusedAdam
         old = self.block
-        block = PeerBlock(self.arena.numel, self.dev)
+        assert self.exchange == "peer" or (self.distributed and self.world > 1), "exchange=\"nvls\" needs a process group"
+        block = PeerBlock(self.arena.numel, self.dev, backend="symm" if self.exchange == "nvls" else "ipc")
         if self.distributed and self.world > 1:
             block.connect(self.group)
         arena = GradArena(list(self.params.values()), extra=1, flat=block.grads)
@@ -379,7 +382,7 @@ class MapEngine:
     def step(self, views: Sequence[MapView]):
         """One data-parallel mapping iteration.  Returns (total loss f32[1] on the device, {view index: MapViewResult})."""
         out = self.backward_only(views)
-        if self.exchange == "peer":
+        if self.exchange != "nccl":
             # gradient reduce-scatter + Adam on this rank's slice + parameter all-gather, one kernel over peer memory
             from .rasterizer import _stream
             self._peer_step += 1
@@ -402,7 +405,7 @@ class MapEngine:
             dist.all_reduce(self.xyz_gradient_accum, op=dist.ReduceOp.SUM, group=self.group)
             dist.all_reduce(self.denom, op=dist.ReduceOp.SUM, group=self.group)
             dist.all_reduce(self.max_radii2D, op=dist.ReduceOp.MAX, group=self.group)
-            if self.exchange == "peer":      # sharded Adam moments: every rank fetches the live slices of the others
+            if self.exchange != "nccl":      # sharded Adam moments: every rank fetches the live slices of the others
                 for r in range(self.world):
                     b, e = self.block.slice_of(r)
                     src = dist.get_global_rank(self.group, r) if self.group is not None else r
@@ -452,7 +455,7 @@ class MapEngine:
         self.max_radii2D = torch.zeros(self.P, **f)
         self.scratch = torch.empty(self.lib.mgs_map_scratch_bytes(self.P, self.M, self.W, self.H), device=self.dev, dtype=torch.uint8)
         self.ws, self._slots = None, {}
-        if self.exchange == "peer":
+        if self.exchange != "nccl":
             assert len(set(steps.values())) == 1, "the engine's parameters step together"
             self._install_peer(steps=next(iter(steps.values())), moments=(out["exp_avg"], out["exp_avg_sq"]))
 

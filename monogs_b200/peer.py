@@ -25,21 +25,38 @@ class _Raw:
 
 
 class PeerBlock:
-    def __init__(self, numel: int, dev: torch.device):
+    """backend="ipc": cudaMalloc + CUDA IPC (unicast peer mappings; the TMA kernel).  backend="symm": the block is a
+    torch.distributed._symmetric_memory allocation (CUDA VMM), whose rendezvous returns the peer mappings AND an NVSwitch
+    multicast mapping of the same memory: mgs_peer_reduce_adam then reduces inside the switch (multimem.ld_reduce) and
+    broadcasts the parameters with multimem.st."""
+
+    def __init__(self, numel: int, dev: torch.device, backend: str = "ipc"):
         assert numel > 0 and numel % 4 == 0, "arena length must be a positive multiple of 4 floats"
+        assert backend in ("ipc", "symm")
         self.lib = L.lib()
-        self.numel, self.dev = numel, dev
+        self.numel, self.dev, self.backend = numel, dev, backend
         self.flag_bytes = int(self.lib.mgs_peer_flags_bytes())
         self.nbytes = 2 * numel * 4 + 16 + self.flag_bytes
-        p = C.c_void_p()
-        with torch.cuda.device(dev):
-            L.check(self.lib.mgs_peer_alloc(self.nbytes, C.byref(p)), "mgs_peer_alloc")
-        self.ptr = p.value
         self._opened: List[int] = []
-        self.params = torch.as_tensor(_Raw(self.ptr, numel, "<f4", self), device=dev)
-        self.grads = torch.as_tensor(_Raw(self.ptr + 4 * numel, numel, "<f4", self), device=dev)
-        self.loss_out = torch.as_tensor(_Raw(self.ptr + 8 * numel, 4, "<f4", self), device=dev)
-        self.flags = torch.as_tensor(_Raw(self.ptr + 8 * numel + 16, self.flag_bytes // 4, "<i4", self), device=dev)
+        self.mc_base = 0
+        if backend == "symm":
+            import torch.distributed._symmetric_memory as symm_mem
+            self._symm = symm_mem.empty(self.nbytes // 4, dtype=torch.float32, device=dev)
+            self._symm.zero_()
+            torch.cuda.synchronize(dev)
+            self.ptr = self._symm.data_ptr()
+            self.params, self.grads = self._symm[:numel], self._symm[numel:2 * numel]
+            self.loss_out = self._symm[2 * numel:2 * numel + 4]
+            self.flags = self._symm[2 * numel + 4:].view(torch.int32)
+        else:
+            p = C.c_void_p()
+            with torch.cuda.device(dev):
+                L.check(self.lib.mgs_peer_alloc(self.nbytes, C.byref(p)), "mgs_peer_alloc")
+            self.ptr = p.value
+            self.params = torch.as_tensor(_Raw(self.ptr, numel, "<f4", self), device=dev)
+            self.grads = torch.as_tensor(_Raw(self.ptr + 4 * numel, numel, "<f4", self), device=dev)
+            self.loss_out = torch.as_tensor(_Raw(self.ptr + 8 * numel, 4, "<f4", self), device=dev)
+            self.flags = torch.as_tensor(_Raw(self.ptr + 8 * numel + 16, self.flag_bytes // 4, "<i4", self), device=dev)
         self.world, self.rank = 1, 0
         self.bases = [self.ptr]
 
@@ -53,6 +70,17 @@ class PeerBlock:
         """Exchange the handles over `group` and map every other rank's block (collective)."""
         world, rank = dist.get_world_size(group), dist.get_rank(group)
         assert world <= L.PEER_MAX, f"at most {L.PEER_MAX} ranks share peer blocks (one NVLink domain)"
+        if self.backend == "symm":
+            import torch.distributed._symmetric_memory as symm_mem
+            h = symm_mem.rendezvous(self._symm, group=(group if group is not None else dist.group.WORLD).group_name)
+            if not h.multicast_ptr:
+                raise RuntimeError("symmetric memory gave no multicast mapping (no NVSwitch multicast on this box): use "
+                                   "exchange=\"peer\"")
+            self._handle = h
+            self.world, self.rank, self.bases, self.mc_base = world, rank, [int(p) for p in h.buffer_ptrs], int(h.multicast_ptr)
+            assert self.bases[rank] == self.ptr
+            dist.barrier(group)
+            return self
         handles: List[Optional[bytes]] = [None] * world
         dist.all_gather_object(handles, (self.handle(), self.numel), group=group)
         bases = []
@@ -89,6 +117,9 @@ class PeerBlock:
         assert exp_avg.numel() == self.numel and exp_avg_sq.numel() == self.numel
         x.exp_avg, x.exp_avg_sq = exp_avg.data_ptr(), exp_avg_sq.data_ptr()
         assert len(segment_ends) == len(segment_lrs) <= L.PEER_MAX_SEGMENTS
+        if self.mc_base:
+            x.param_multicast, x.grad_multicast = self.mc_base, self.mc_base + 4 * self.numel
+            x.loss_multicast = self.mc_base + 8 * self.numel
         x.n_segments = len(segment_ends)
         for i, (e, lr) in enumerate(zip(segment_ends, segment_lrs)):
             x.segment_end[i], x.segment_lr[i] = int(e), float(lr)
@@ -107,6 +138,9 @@ class PeerBlock:
         return e.value
 
     def close(self):
+        if self.backend == "symm":
+            self.ptr = None       # the symmetric allocation is released with its tensors
+            return
         if getattr(self, "ptr", None):
             with torch.cuda.device(self.dev):
                 for p in self._opened:

@@ -40,6 +40,7 @@ def main():
     ap.add_argument("--no-mapping", action="store_true")
     ap.add_argument("--c5", action="store_true", help="also the C5 stress mapping iteration (2M Gaussians, 1920x1080, SH 3), "
                                                       "one view per rank, with either exchange")
+    ap.add_argument("--no-nvls", action="store_true", help="skip the NVSwitch multicast variant")
     ap.add_argument("--timing-only", action="store_true", help="skip the parity pass (kernel-variant sweeps)")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
@@ -54,15 +55,22 @@ def main():
 
     if not args.timing_only:
         parity(report, rank, world, dev, lib, L, ops, PeerBlock, stream)
-    timing(report, rank, world, dev, lib, L, ops, PeerBlock, stream)
+        if not args.no_nvls:
+            try:
+                parity(report, rank, world, dev, lib, L, ops, PeerBlock, stream, backend="symm")
+            except Exception as ex:  # no multicast on this box: say so and go on with the unicast kernel
+                report["nvls_unavailable"] = repr(ex)[:300]
+                args.no_nvls = True
+    timing(report, rank, world, dev, lib, L, ops, PeerBlock, stream, nvls=not args.no_nvls)
+    exchanges = ("nccl", "peer") if args.no_nvls else ("nccl", "peer", "nvls")
     if not args.no_mapping:
         import bench
-        report["mapping_C4"] = {ex: bench.mapping_leg(dev, rank, world, exchange=ex)["iters_per_s"] for ex in ("nccl", "peer")}
+        report["mapping_C4"] = {ex: bench.mapping_leg(dev, rank, world, exchange=ex)["iters_per_s"] for ex in exchanges}
     if args.c5:
         import bench
         report["mapping_C5_one_view_per_rank"] = {
             ex: bench.mapping_leg(dev, rank, world, iters=6, warmup=2, P=None, window=world, exchange=ex, cfg="C5")["iters_per_s"]
-            for ex in ("nccl", "peer")}
+            for ex in exchanges}
     if rank == 0:
         print(json.dumps(report))
         if args.out:
@@ -71,10 +79,13 @@ def main():
     dist.destroy_process_group()
 
 
-def parity(report, rank, world, dev, lib, L, ops, PeerBlock, stream):
+def parity(report, rank, world, dev, lib, L, ops, PeerBlock, stream, backend="ipc"):
+    """backend="ipc": unicast TMA kernel, bit-exact.  backend="symm": the multicast kernel; the switch's summation order is
+    its own, so parameters are compared by max |difference| / max |value| per tensor and must agree BETWEEN ranks bit for bit."""
     lay, lrs = layout(10_007, 1, dev)
     n = lay.numel
-    blk = PeerBlock(n, dev).connect()
+    blk = PeerBlock(n, dev, backend=backend).connect()
+    worst = 0.0
     g = torch.Generator().manual_seed(17)
     p0 = torch.randn(n, generator=g).to(dev)
     blk.params.copy_(p0)
@@ -101,6 +112,17 @@ def parity(report, rank, world, dev, lib, L, ops, PeerBlock, stream):
         dist.barrier()
         L.check(lib.mgs_peer_reduce_adam(C.byref(x), step, step, BETAS[0], BETAS[1], EPS, stream()), "mgs_peer_reduce_adam")
         torch.cuda.synchronize()
+        if backend == "symm":
+            for a, b in zip(rv, lay.views_over(blk.params)):
+                worst = max(worst, float((a - b).abs().max() / a.abs().max()))
+            worst = max(worst, float((blk.loss_out[0] - s[n - 4]).abs() / s[n - 4].abs().clamp_min(1e-30)))
+            # every rank must hold the same bits: compare the arena with rank 0's
+            flat = torch.cat([t_.reshape(-1) for t_ in lay.views_over(blk.params)])
+            ref0 = flat.clone()
+            dist.broadcast(ref0, src=0)
+            ok &= bool(torch.equal(flat, ref0))
+            ref_p.copy_(blk.params)      # follow the switch's sums so that the steps stay comparable one at a time
+            continue
         for a, b in zip(rv, lay.views_over(blk.params)):
             ok &= bool(torch.equal(a, b))
         ok &= bool(torch.equal(blk.loss_out[:1], s[n - 4:n - 3]))
@@ -114,11 +136,17 @@ def parity(report, rank, world, dev, lib, L, ops, PeerBlock, stream):
     ok &= blk.error_epoch(stream()) == 0
     t = torch.tensor([int(ok)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
-    report["parity_bit_exact"] = bool(int(t))
+    if backend == "symm":
+        w = torch.tensor([worst], device=dev)
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)
+        report["nvls_ranks_bit_identical"] = bool(int(t))
+        report["nvls_max_rel_diff_vs_rank_ordered_sum"] = float(w)
+    else:
+        report["parity_bit_exact"] = bool(int(t))
     blk.close()
 
 
-def timing(report, rank, world, dev, lib, L, ops, PeerBlock, stream):
+def timing(report, rank, world, dev, lib, L, ops, PeerBlock, stream, nvls=True):
     def timed(fn, iters=20, warm=5):
         for _ in range(warm):
             fn()
@@ -170,7 +198,20 @@ def timing(report, rank, world, dev, lib, L, ops, PeerBlock, stream):
             dist.all_reduce(gg)
             opt2.step()
         t_peer, t_nccl = timed(peer), timed(nccl)
-        report["exchange_us"][name] = {"arena_bytes": 4 * n, "peer_reduce_adam": t_peer, "nccl_allreduce_plus_adam": t_nccl,
+        t_nvls = None
+        if nvls:
+            blk2 = PeerBlock(n, dev, backend="symm").connect()
+            blk2.params.normal_(); blk2.grads.normal_()
+            x2 = blk2.exchange(m, v, lay.segment_ends, lrs)
+            st2 = {"e": 0}
+
+            def nvls_fn():
+                st2["e"] += 1
+                L.check(lib.mgs_peer_reduce_adam(C.byref(x2), st2["e"], st2["e"], BETAS[0], BETAS[1], EPS, stream()), "nvls")
+            t_nvls = timed(nvls_fn)
+            assert blk2.error_epoch(stream()) == 0
+            del blk2, x2
+        report["exchange_us"][name] = {"arena_bytes": 4 * n, "peer_reduce_adam": t_peer, "nccl_allreduce_plus_adam": t_nccl, "nvls_reduce_adam": t_nvls,
                                        "peer_timeout_epoch": blk.error_epoch(stream()),
                                        # every direction of a rank's links carries the gradient slices it pulls in (read responses) or serves, plus
                                        # the parameter slices it pushes / receives: 2 x (world-1)/world x arena bytes each way

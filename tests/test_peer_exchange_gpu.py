@@ -4,6 +4,10 @@ torch.optim.Adam in test_ops_gpu.py).  On one GPU the "ranks" are blocks of one 
 (PeerBlock.local_group): flags, slices and the rank-ordered sum are the same code as across GPUs; the cross-GPU run is
 scripts/check_peer_exchange.py under torchrun.  Bar: bit-exact (same element arithmetic, sum in rank order)."""
 import ctypes as C
+import json
+import os
+import subprocess
+import sys
 
 import pytest
 import torch
@@ -153,3 +157,21 @@ def test_map_engine_peer_exchange_matches_allreduce_path():
     for _ in range(5):
         l1 = float(peer.step(views)[0])
     assert l1 < l0 and peer.block.error_epoch(None) == 0
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs of one NVLink domain")
+def test_peer_exchange_across_two_gpus(tmp_path):
+    """The same exchange between two processes on two GPUs (CUDA IPC mappings, NVLink): scripts/check_peer_exchange.py
+    under torchrun.  Unicast kernel: bit-exact against the rank-ordered sum + multi-tensor Adam.  Multicast (NVLS) kernel,
+    where the box offers it: identical bits on both ranks, within 1e-5 of the rank-ordered result."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = tmp_path / "report.json"
+    subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                    "127.0.0.1", "--master-port", "29533", os.path.join(root, "scripts", "check_peer_exchange.py"),
+                    "--no-mapping", "--out", str(out)], check=True, timeout=600, cwd=root)
+    r = json.load(open(out))
+    assert r["parity_bit_exact"]
+    for v in r["exchange_us"].values():
+        assert v["peer_timeout_epoch"] == 0
+    if "nvls_unavailable" not in r:
+        assert r["nvls_ranks_bit_identical"] and r["nvls_max_rel_diff_vs_rank_ordered_sum"] <= 1e-5
