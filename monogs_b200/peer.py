@@ -59,6 +59,7 @@ class PeerBlock:
             self.flags = torch.as_tensor(_Raw(self.ptr + 8 * numel + 16, self.flag_bytes // 4, "<i4", self), device=dev)
         self.world, self.rank = 1, 0
         self.bases = [self.ptr]
+        self._group, self._connected = None, False
 
     # ------------------------------------------------------------------------------------------------
     def handle(self) -> bytes:
@@ -69,6 +70,7 @@ class PeerBlock:
     def connect(self, group=None):
         """Exchange the handles over `group` and map every other rank's block (collective)."""
         world, rank = dist.get_world_size(group), dist.get_rank(group)
+        self._group, self._connected = group, True
         assert world <= L.PEER_MAX, f"at most {L.PEER_MAX} ranks share peer blocks (one NVLink domain)"
         if self.backend == "symm":
             import torch.distributed._symmetric_memory as symm_mem
@@ -138,6 +140,8 @@ class PeerBlock:
         return e.value
 
     def close(self):
+        """Unmap the other ranks' blocks, then free this one.  Collective for a connected block: an exporter must not free
+        its allocation while another process still has it mapped, so the ranks meet between the two steps."""
         if self.backend == "symm":
             self.ptr = None       # the symmetric allocation is released with its tensors
             return
@@ -147,5 +151,7 @@ class PeerBlock:
                     self.lib.mgs_peer_close(C.c_void_p(p))
                 self._opened = []
                 torch.cuda.synchronize(self.dev)
+                if self._connected:
+                    dist.barrier(self._group)
                 self.lib.mgs_peer_free(C.c_void_p(self.ptr))
             self.ptr = None
