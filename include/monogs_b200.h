@@ -325,6 +325,8 @@ typedef struct mgs_peer_exchange {
    * parameters / loss are written with multimem.st; the unicast tables above are still used for the flags, the own
    * parameters and nothing else. */
   const float* grad_multicast; float* param_multicast; float* loss_multicast;
+  uint32_t timeout_ms;   /* how long a rank waits on the device for its peers before it gives up, records the epoch in
+                          * its error word (mgs_peer_error) and goes on with whatever it has; 0 = 60 000 */
 } mgs_peer_exchange;
 /* step: Adam step number t >= 1 (identical on all ranks); epoch: strictly increasing per call on the same blocks,
  * identical on all ranks, first call 1.  Slice r = float4 units [r*ceil(numel/4/world), ...). */

@@ -117,6 +117,7 @@ class MgsPeerExchange(C.Structure):
         ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p), ("numel", C.c_int64), ("n_segments", C.c_int32),
         ("segment_end", C.c_int64 * PEER_MAX_SEGMENTS), ("segment_lr", C.c_float * PEER_MAX_SEGMENTS),
         ("grad_multicast", C.c_void_p), ("param_multicast", C.c_void_p), ("loss_multicast", C.c_void_p),
+        ("timeout_ms", C.c_uint32),
     ]
 
 

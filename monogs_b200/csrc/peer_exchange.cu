@@ -17,8 +17,8 @@
 // Phase 1 ("my slice is stored everywhere and I no longer read your gradients") is signalled by the last CTA to
 // finish; peer_wait_kernel, next on the stream, holds the rank's following work (mgs_map_begin zeroes the gradient
 // arena and reads the parameters) until every rank's phase-1 flag has arrived.  Flags carry the caller's epoch
-// (strictly increasing), so they are never reset.  A wait that exceeds ~4 s sets the block's error word instead of
-// hanging the GPU.
+// (strictly increasing), so they are never reset.  A wait that exceeds the caller's timeout (60 s by default) sets the
+// block's error word instead of hanging the GPU for good.
 #include "launchers.h"
 #include "adam_elem.cuh"
 #include "tma.cuh"
@@ -39,6 +39,7 @@ struct PeerPack {
   float seg_lr[MGS_PEER_MAX_SEGMENTS];            // < 0: sum only (the loss element)
   int n_seg, world, rank;
   uint32_t epoch;
+  unsigned long long timeout_ns;
   float beta1, beta2, eps, bc1, bc2_sqrt;
 };
 
@@ -58,12 +59,13 @@ __device__ __forceinline__ unsigned long long global_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-// spin until *flag has reached `epoch` (wrap-safe); gives up after ~4 s and records it in the local error word
-__device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, uint32_t* error_word) {
+// spin until *flag has reached `epoch` (wrap-safe); gives up after timeout_ns and records it in the local error word
+__device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, uint32_t* error_word,
+                                          unsigned long long timeout_ns) {
   const unsigned long long t0 = global_ns();
   while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
     __nanosleep(64);
-    if (global_ns() - t0 > 4000000000ull) { atomicExch(error_word, epoch); break; }
+    if (global_ns() - t0 > timeout_ns) { atomicExch(error_word, epoch); break; }
   }
 }
 
@@ -96,7 +98,7 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_kernel(const __grid_cons
   if (blockIdx.x == 0 && tid < a.world)     // phase 0: this rank's gradients are final (stream order); the release
     st_release_sys(a.flags[tid] + a.rank, a.epoch);   // store carries the system-scope fence
 
-  if (tid < a.world) wait_flag(my_flags + tid, a.epoch, my_flags + FLAG_ERROR);
+  if (tid < a.world) wait_flag(my_flags + tid, a.epoch, my_flags + FLAG_ERROR, a.timeout_ns);
   __syncthreads();
 
   const long long n4 = a.q_end - a.q_begin;
@@ -210,7 +212,7 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_mc_kernel(const __grid_c
   const int tid = threadIdx.x;
   uint32_t* my_flags = a.flags[a.rank];
   if (blockIdx.x == 0 && tid < a.world) st_release_sys(a.flags[tid] + a.rank, a.epoch);   // phase 0, as in the unicast kernel
-  if (tid < a.world) wait_flag(my_flags + tid, a.epoch, my_flags + FLAG_ERROR);
+  if (tid < a.world) wait_flag(my_flags + tid, a.epoch, my_flags + FLAG_ERROR, a.timeout_ns);
   __syncthreads();
   const AdamCoef co{a.beta1, a.beta2, a.eps, a.bc2_sqrt};
   float* p_own = a.param[a.rank];
@@ -257,8 +259,8 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_mc_kernel(const __grid_c
   }
 }
 
-__global__ void peer_wait_kernel(uint32_t* my_flags, int world, uint32_t epoch) {
-  if ((int)threadIdx.x < world) wait_flag(my_flags + FLAG_PHASE1 + threadIdx.x, epoch, my_flags + FLAG_ERROR);
+__global__ void peer_wait_kernel(uint32_t* my_flags, int world, uint32_t epoch, unsigned long long timeout_ns) {
+  if ((int)threadIdx.x < world) wait_flag(my_flags + FLAG_PHASE1 + threadIdx.x, epoch, my_flags + FLAG_ERROR, timeout_ns);
   __threadfence_system();
 }
 
@@ -281,10 +283,12 @@ static int peer_mc_unroll() {   // tuning knob (MGS_PEER_MC_UNROLL, read once): 
 
 template <int U>
 static int launch_peer_mc(const PeerPack& a, cudaStream_t s) {
-  static int resident_mc = 0;
+  static int resident_by_dev[64] = {0};   // per device: the attribute and the occupancy belong to the current device
+  int dev = 0;
+  MGS_CUDA_TRY(cudaGetDevice(&dev));
+  int& resident_mc = resident_by_dev[dev & 63];
   if (resident_mc == 0) {
-    int dev = 0, sms = 0, per_sm = 0;
-    MGS_CUDA_TRY(cudaGetDevice(&dev));
+    int sms = 0, per_sm = 0;
     MGS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     MGS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, peer_reduce_adam_mc_kernel<U>, 256, 0));
     resident_mc = sms * (per_sm > 0 ? per_sm : 1);
@@ -300,10 +304,12 @@ static int launch_peer_mc(const PeerPack& a, cudaStream_t s) {
 template <int PEER_CHUNK4, int PEER_STAGES>
 static int launch_peer(const PeerPack& a, cudaStream_t s) {
   const size_t smem = (size_t)PEER_STAGES * a.world * PEER_CHUNK4 * 16 + 3 * PEER_CHUNK4 * 16;
-  static int resident[MGS_PEER_MAX + 1] = {0};   // persistent grid: resident CTAs of the device for this world size
+  static int resident_by_dev[64][MGS_PEER_MAX + 1] = {{0}};   // persistent grid: resident CTAs per device and world size
+  int dev = 0;
+  MGS_CUDA_TRY(cudaGetDevice(&dev));
+  int* resident = resident_by_dev[dev & 63];
   if (resident[a.world] == 0) {
-    int dev = 0, sms = 0, per_sm = 0;
-    MGS_CUDA_TRY(cudaGetDevice(&dev));
+    int sms = 0, per_sm = 0;
     MGS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     MGS_CUDA_TRY(cudaFuncSetAttribute(peer_reduce_adam_kernel<PEER_CHUNK4, PEER_STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
     MGS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, peer_reduce_adam_kernel<PEER_CHUNK4, PEER_STAGES>, 256, smem));
@@ -384,6 +390,7 @@ int mgs_peer_reduce_adam(const mgs_peer_exchange* x, int32_t step, uint32_t epoc
   }
   if (prev != x->numel) { set_error("peer_reduce_adam: the segments must cover the arena"); return MGS_EINVAL; }
   a.n_seg = x->n_segments; a.world = x->world; a.rank = x->rank; a.epoch = epoch;
+  a.timeout_ns = (unsigned long long)(x->timeout_ms ? x->timeout_ms : 60000u) * 1000000ull;
   a.m = x->exp_avg; a.v = x->exp_avg_sq;
   a.grad_mc = x->grad_multicast; a.param_mc = x->param_multicast; a.loss_mc = x->loss_multicast;
   const bool mc = a.grad_mc || a.param_mc || a.loss_mc;
@@ -414,7 +421,7 @@ int mgs_peer_reduce_adam(const mgs_peer_exchange* x, int32_t step, uint32_t epoc
     default: rc = launch_peer<512, 3>(a, s); break;
   }
   if (rc) return rc;
-  MGS_PROF("peer_wait", s, peer_wait_kernel<<<1, 32, 0, s>>>(a.flags[a.rank], a.world, epoch));
+  MGS_PROF("peer_wait", s, peer_wait_kernel<<<1, 32, 0, s>>>(a.flags[a.rank], a.world, epoch, a.timeout_ns));
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

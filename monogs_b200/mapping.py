@@ -424,6 +424,11 @@ class MapEngine:
         if over:
             self.headroom *= 1.5
             self.ws, self.ws_extra = None, []
+        if self.block is not None:
+            epoch = self.block.error_epoch(_stream())
+            if epoch:
+                raise RuntimeError(f"peer exchange {epoch}: a rank of the group never arrived (device-side wait timed out); "
+                                   "parameters on this rank are stale from that iteration on")
         return n_max, over
 
     # ------------------------------------------------------------------------------------------------

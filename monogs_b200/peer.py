@@ -110,8 +110,9 @@ class PeerBlock:
 
     # ------------------------------------------------------------------------------------------------
     def exchange(self, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor, segment_ends: Sequence[int],
-                 segment_lrs: Sequence[float]) -> "L.MgsPeerExchange":
+                 segment_lrs: Sequence[float], timeout_ms: int = 0) -> "L.MgsPeerExchange":
         x = L.MgsPeerExchange()
+        x.timeout_ms = timeout_ms
         x.world, x.rank, x.numel = self.world, self.rank, self.numel
         for r, b in enumerate(self.bases):
             x.param_arena[r], x.grad_arena[r] = b, b + 4 * self.numel

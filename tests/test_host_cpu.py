@@ -76,3 +76,36 @@ def test_missing_library_fails_loudly(monkeypatch):
     monkeypatch.setattr(L, "LIB_PATH", "/nonexistent/libmonogs_b200.so")
     with pytest.raises(RuntimeError, match="no CPU or eager fallback"):
         L.lib()
+
+
+def test_grad_arena_layout_and_peer_slices():
+    """Host logic of the fused exchange (no device): every parameter view starts on a 16-byte boundary, the segment table
+    covers the arena with the loss slot last, views over a sibling buffer share the layout, and the per-rank float4 slices
+    (the arithmetic mgs_peer_reduce_adam repeats on the device) tile the arena without gaps or overlap for 1..8 ranks."""
+    import torch
+    from monogs_b200.mapping import GradArena
+    from monogs_b200.peer import PeerBlock
+    P = 1001
+    shapes = [(P, 3), (P, 1, 3), (P, 15, 3), (P, 1), (P, 3), (P, 4)]
+    params = [torch.zeros(s) for s in shapes]
+    arena = GradArena(params, extra=1)
+    pad4 = lambda n: (n + 3) // 4 * 4
+    assert arena.numel == sum(pad4(p.numel()) for p in params) + 4 and arena.numel % 4 == 0
+    assert arena.segment_ends[-1] == arena.numel and len(arena.segment_ends) == len(params) + 1
+    assert all(e % 4 == 0 for e in arena.segment_ends) and arena.segment_ends == sorted(set(arena.segment_ends))
+    for v, p in zip(arena.views, params):
+        assert v.shape == p.shape and (v.data_ptr() - arena.flat.data_ptr()) % 16 == 0
+    other = torch.arange(arena.numel, dtype=torch.float32)
+    for v, w, e, p in zip(arena.views, arena.views_over(other), arena.segment_ends, params):
+        assert w.shape == v.shape and float(w.reshape(-1)[0]) == e - pad4(p.numel())
+    assert arena.extra.data_ptr() - arena.flat.data_ptr() == 4 * (arena.numel - 4)
+    external = torch.zeros(arena.numel)
+    assert GradArena(params, extra=1, flat=external).flat.data_ptr() == external.data_ptr()
+    for world in range(1, 9):
+        for numel in (arena.numel, 56, 4, 8 * 4 * 1000 + 4):
+            blk = PeerBlock.__new__(PeerBlock)      # slice arithmetic only: no allocation
+            blk.numel, blk.world = numel, world
+            cuts = [blk.slice_of(r) for r in range(world)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == numel
+            for (b0, e0), (b1, e1) in zip(cuts, cuts[1:]):
+                assert e0 == b1 and b0 <= e0 and b0 % 4 == 0
