@@ -552,11 +552,11 @@ def main():
             top = max(prof, key=lambda k: prof[k]["avg_us"])
             step_us = sum(v["avg_us"] for v in prof.values())
             # dram__bytes_read + write of one launch from the committed ncu --set full capture (profiles/), C2 only
-            traffic = {"blend_track": 56.4e6}.get(top) if args.config == "C2" else None
+            traffic = {"blend_track": 56.9e6}.get(top) if args.config == "C2" else None
             line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": prof[top].get("gbs"), "peak": peak, "unit": "GB/s",
                                 "frac": (prof[top].get("gbs") or 0) / peak, "traffic": traffic,
-                                "traffic_source": "profiles/r01d_ncu_full_blend_kernels.txt", "peak_source": src,
-                                "issue_slot_utilisation": {"blend_track": 0.683}.get(top),
+                                "traffic_source": "profiles/r01e_ncu_full_blend_kernels.txt", "peak_source": src,
+                                "issue_slot_utilisation": {"blend_track": 0.677}.get(top),
                                 "share_of_step": prof[top]["avg_us"] / step_us,
                                 "note": "the blend kernels are issue/SFU-bound (one 48-B record feeds 256 pixel "
                                         "evaluations), so their HBM fraction is small by construction; see DESIGN.md"}
