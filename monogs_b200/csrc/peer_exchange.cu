@@ -37,6 +37,7 @@ struct PeerPack {
   long long q_begin, q_end;                       // this rank's slice of the arena, in float4 units
   long long seg_end4[MGS_PEER_MAX_SEGMENTS];      // segment ends, float4 units
   float seg_lr[MGS_PEER_MAX_SEGMENTS];            // < 0: sum only (the loss element)
+  float seg_step[MGS_PEER_MAX_SEGMENTS];          // lr / bias correction 1, the step size of the segment
   int n_seg, world, rank;
   uint32_t epoch;
   unsigned long long timeout_ns;
@@ -98,8 +99,11 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_kernel(const __grid_cons
   if (blockIdx.x == 0 && tid < a.world)     // phase 0: this rank's gradients are final (stream order); the release
     st_release_sys(a.flags[tid] + a.rank, a.epoch);   // store carries the system-scope fence
 
-  if (tid < a.world) wait_flag(my_flags + tid, a.epoch, my_flags + FLAG_ERROR, a.timeout_ns);
-  __syncthreads();
+  __syncthreads();                          // the mbarriers are initialised for everybody
+  // only the elected thread has to see the other ranks' phase-0 flags: it issues every load of a peer's gradients; the
+  // rest of the CTA goes on to its local loads and meets it at the stage's mbarrier
+  if (tid == 0)
+    for (int r = 0; r < a.world; r++) wait_flag(my_flags + r, a.epoch, my_flags + FLAG_ERROR, a.timeout_ns);
 
   const long long n4 = a.q_end - a.q_begin;
   const long long n_chunks = (n4 + PEER_CHUNK4 - 1) / PEER_CHUNK4;
@@ -154,7 +158,7 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_kernel(const __grid_cons
       if (lr < 0.f) {                        // the loss element: every rank gets the sum; its parameter slot is unused
         for (int r = 0; r < a.world; r++) *reinterpret_cast<float4*>(a.loss_out[r]) = S;
       } else {
-        const float step_size = lr / a.bc1;
+        const float step_size = a.seg_step[sg];
         adam_elem(P4[it].x, S.x, M4[it].x, V4[it].x, step_size, co); adam_elem(P4[it].y, S.y, M4[it].y, V4[it].y, step_size, co);
         adam_elem(P4[it].z, S.z, M4[it].z, V4[it].z, step_size, co); adam_elem(P4[it].w, S.w, M4[it].w, V4[it].w, step_size, co);
         *reinterpret_cast<float4*>(a.m + i) = M4[it]; *reinterpret_cast<float4*>(a.v + i) = V4[it];
@@ -403,6 +407,7 @@ int mgs_peer_reduce_adam(const mgs_peer_exchange* x, int32_t step, uint32_t epoc
   a.beta1 = beta1; a.beta2 = beta2; a.eps = eps;
   a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
   a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
+  for (int sgi = 0; sgi < a.n_seg; sgi++) a.seg_step[sgi] = a.seg_lr[sgi] / a.bc1;   // the same fp32 division adam_kernel does
   cudaStream_t s = (cudaStream_t)stream;
   int rc = MGS_OK;
   if (mc) {
