@@ -145,6 +145,7 @@ class MapEngine:
     rank holds the live moments of its own slice; sync_stats() gathers them before a densify).
     exchange="nvls": the same kernel over an NVSwitch multicast mapping of the blocks (torch symmetric memory): the
     gradient sum happens inside the switch (multimem.ld_reduce) and one multimem.st writes the parameters of all ranks.
+    exchange="auto": "peer" for 2..7 ranks of one node, "nvls" for 8 (falling back to "peer" without multicast), else "nccl".
     """
 
     NAMES = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
@@ -192,9 +193,23 @@ class MapEngine:
         self._keep = []
         self._slots = {}
         self._concurrent = False
-        assert exchange in ("nccl", "peer", "nvls")
+        assert exchange in ("nccl", "peer", "nvls", "auto")
+        if exchange == "auto":
+            # the measured choice: the unicast kernel up to 4 ranks, the multicast kernel at 8, NCCL whenever
+            # the group is not one NVLink domain of at most 8 CUDA ranks of this node
+            import os
+            one_node = int(os.environ.get("LOCAL_WORLD_SIZE", self.world)) == self.world
+            fused = (self.distributed and 1 < self.world <= 8 and one_node and self.dev.type == "cuda"
+                     and dist.get_backend(group) == "nccl")
+            exchange = ("nvls" if self.world >= 8 else "peer") if fused else "nccl"
         self.exchange, self.block = exchange, None
-        if exchange != "nccl":
+        if exchange == "nvls":
+            try:
+                self._install_peer(steps=0)
+            except RuntimeError:      # no multicast mapping on this box (the same on every rank): the unicast kernel
+                self.exchange = "peer"
+                self._install_peer(steps=0)
+        elif exchange != "nccl":
             self._install_peer(steps=0)
 
     # ------------------------------------------------------------------------------------------------
