@@ -52,6 +52,9 @@ typedef struct mgs_view {
 
 const char* mgs_last_error_string(void);
 int mgs_version(void);
+/* cudaStreamSynchronize(stream): the one host wait of the drop-in forward (the reference reads num_rendered back at
+ * cuda_rasterizer/rasterizer_impl.cu:284) without a round trip through the caller's stream object. */
+int mgs_stream_synchronize(void* stream);
 
 /* Optional per-kernel timing with CUDA events on the launching stream (off by default; do not enable under
  * CUDA-graph capture).  mgs_profile_enable(1) clears and starts collecting, mgs_profile_report synchronises the

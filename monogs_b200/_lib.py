@@ -128,6 +128,7 @@ _VP = C.POINTER(MgsView)
 SIGNATURES = {
     "mgs_last_error_string": (C.c_char_p, []),
     "mgs_version": (C.c_int, []),
+    "mgs_stream_synchronize": (C.c_int, [_P]),
     "mgs_profile_enable": (C.c_int, [_I32]),
     "mgs_profile_report": (C.c_int, [C.c_char_p, _SZ]),
     "mgs_raster_workspace_bytes": (_SZ, [_I32, _I32, _I32, _I64]),

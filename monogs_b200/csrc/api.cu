@@ -42,6 +42,11 @@ extern "C" {
 
 const char* mgs_last_error_string(void) { return mgs::get_error(); }
 int mgs_version(void) { return 100; }
+
+int mgs_stream_synchronize(void* stream) {
+  MGS_CUDA_TRY(cudaStreamSynchronize((cudaStream_t)stream));
+  return MGS_OK;
+}
 int mgs_profile_enable(int32_t on) { prof_enable(on != 0); return MGS_OK; }
 int mgs_profile_report(char* buf, size_t buf_bytes) { if (!buf) { set_error("null buffer"); return MGS_EINVAL; } return prof_report(buf, buf_bytes); }
 
