@@ -13,6 +13,7 @@ def timed(self, views):
     host.append(time.perf_counter() - t0)
     return r
 MP.MapEngine.step = timed
-r = bench.mapping_leg(dev, 0, 1, iters=40, warmup=5)
+window = int(sys.argv[1]) if len(sys.argv) > 1 else 8   # 1 = what a rank of an 8-GPU group enqueues per iteration
+r = bench.mapping_leg(dev, 0, 1, iters=40, warmup=5, window=window)
 h = sorted(host[5:])
 print("device it/s", r["iters_per_s"], "-> ms/iter", 1e3 / r["iters_per_s"], " host enqueue ms/iter median", 1e3 * h[len(h) // 2])
