@@ -88,3 +88,34 @@ def test_product_does_not_import_the_oracle():
                 if f.endswith((".py", ".cu", ".cuh", ".h")):
                     txt = open(os.path.join(dp, f)).read()
                     assert "oracle" not in txt.replace("the oracle", "").lower() or f == "scene.py", os.path.join(dp, f)
+
+
+def test_struct_layouts_match_header(tmp_path):
+    """Every struct of the header, compiled as plain C by gcc, has the size and the field offsets of its ctypes mirror in
+    monogs_b200/_lib.py (a field added on one side only would shift everything behind it without any error at run time)."""
+    import subprocess
+    L = _lib()
+    pairs = {"mgs_view": L.MgsView, "mgs_loss_args": L.MgsLossArgs, "mgs_adam_group": L.MgsAdamGroup,
+             "mgs_track_args": L.MgsTrackArgs, "mgs_gaussians": L.MgsGaussians, "mgs_map_args": L.MgsMapArgs,
+             "mgs_map_view": L.MgsMapView, "mgs_peer_exchange": L.MgsPeerExchange, "mgs_densify_cfg": L.MgsDensifyCfg,
+             "mgs_gaussian_state": L.MgsGaussianState}
+    declared = set(re.findall(r"^}\s*(mgs_\w+);", open(HEADER).read(), flags=re.M))
+    assert declared == set(pairs), declared ^ set(pairs)
+    lines = ['#include <stdio.h>', '#include <stddef.h>', f'#include "{HEADER}"', 'int main(void) {']
+    for cname, cls in pairs.items():
+        lines.append(f'  printf("{cname} size %zu\\n", sizeof({cname}));')
+        for fname, _ in cls._fields_:
+            lines.append(f'  printf("{cname} {fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ['  return 0;', '}']
+    src, exe = tmp_path / "layout.c", tmp_path / "layout"
+    src.write_text("\n".join(lines))
+    subprocess.run(["gcc", "-std=c11", "-o", str(exe), str(src)], check=True)     # a missing field fails to compile
+    got = {}
+    for ln in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines():
+        c, f, v = ln.split()
+        got[(c, f)] = int(v)
+    for cname, cls in pairs.items():
+        assert got[(cname, "size")] == C.sizeof(cls), cname
+        for fname, _ in cls._fields_:
+            assert got[(cname, fname)] == getattr(cls, fname).offset, (cname, fname)
+        # and no field of the header is missing from the mirror: the sizes agree and the last fields line up
