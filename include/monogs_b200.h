@@ -95,6 +95,31 @@ int mgs_raster_render(const mgs_view* view, int32_t P, const float* colors_preco
 /* Reads (num_rendered, overflow) back from a workspace; synchronises `stream`. */
 int mgs_raster_query(const void* workspace, int32_t* num_rendered, int32_t* overflow, void* stream);
 
+/* The whole forward of _C.rasterize_gaussians (rasterize_points.cu:35-127) in ONE call that never waits for the device:
+ * stage 1 + stage 2 with the caller's GUESS of the capacity (the previous call's num_rendered plus headroom).  Where the
+ * reference blocks on cudaMemcpy(num_rendered) in the middle of its forward (rasterizer_impl.cu:284), this call copies
+ * status_out = i32[6] {num_rendered, overflow, r_used, n_large, overflow_sticky, max_rendered} (pinned host or device
+ * memory) right after the scan and records ready_event (a cudaEvent_t, optional) behind that copy, BEFORE the emit / sort /
+ * blend kernels are queued: the caller returns to its own work, waits for the event when it needs num_rendered (long fired
+ * by then) and, in the rare case overflow != 0, grows the workspace (the per-Gaussian state sits at offsets that do not
+ * depend on R_cap, so a copy of the first mgs_raster_workspace_bytes(P, W, H, 0) bytes carries it over) and calls
+ * mgs_raster_render again.  Outputs and n_touched are fully written. */
+int mgs_raster_forward(const mgs_view* view, int32_t P,
+                       const float* means3D, const float* opacities,
+                       const float* shs, const float* colors_precomp,
+                       const float* scales, const float* rotations, const float* cov3D_precomp,
+                       int32_t* radii, void* workspace, size_t workspace_bytes, int64_t R_cap,
+                       float* out_color, float* out_depth, float* out_opacity, int32_t* n_touched,
+                       int32_t* status_out, void* ready_event, void* stream);
+
+/* Asynchronous copy of the first six header words of a workspace (see status_out above) to pinned host or device
+ * memory.  The two sticky words are only ever raised by the kernels: a loop that renders many views into one workspace
+ * (mgs_track_iteration, mgs_map_view_*) polls them once in a while — no host wait inside the loop — and still learns
+ * about ANY render that did not fit.  mgs_raster_status_reset clears the header (also required once before the first
+ * use of a workspace whose sticky words are going to be read: the library never clears them itself). */
+int mgs_raster_status_async(const void* workspace, int32_t* status_out /* i32[6] */, void* stream);
+int mgs_raster_status_reset(void* workspace, void* stream);
+
 /* ---- rasterizer backward: replaces _C.rasterize_gaussians_backward (ext.cpp:47,
  *      rasterize_points.cu:150-254, rasterizer_impl.cu:348-470, backward.cu).  Gradient outputs whose
  *      request bit is clear may be null.  All requested outputs are fully overwritten (no pre-zeroing

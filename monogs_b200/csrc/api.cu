@@ -121,6 +121,56 @@ int mgs_raster_query(const void* workspace, int32_t* num_rendered, int32_t* over
   return MGS_OK;
 }
 
+int mgs_raster_status_async(const void* workspace, int32_t* status_out, void* stream) {
+  if (!workspace || !status_out) { set_error("raster_status: null argument"); return MGS_EINVAL; }
+  MGS_CUDA_TRY(cudaMemcpyAsync(status_out, workspace, 6 * sizeof(uint32_t), cudaMemcpyDefault, (cudaStream_t)stream));
+  return MGS_OK;
+}
+
+int mgs_raster_status_reset(void* workspace, void* stream) {
+  if (!workspace) { set_error("raster_status_reset: workspace is null"); return MGS_EINVAL; }
+  MGS_CUDA_TRY(cudaMemsetAsync(workspace, 0, sizeof(WsHeader), (cudaStream_t)stream));
+  return MGS_OK;
+}
+
+int mgs_raster_forward(const mgs_view* view, int32_t P, const float* means3D, const float* opacities,
+                       const float* shs, const float* colors_precomp, const float* scales, const float* rotations,
+                       const float* cov3D_precomp, int32_t* radii, void* workspace, size_t workspace_bytes, int64_t R_cap,
+                       float* out_color, float* out_depth, float* out_opacity, int32_t* n_touched,
+                       int32_t* status_out, void* ready_event, void* stream) {
+  int rc = check_view(view, false);
+  if (rc) return rc;
+  if (P < 0 || R_cap < 0 || R_cap > 0x7fffffffLL) { set_error("bad P or R_cap"); return MGS_EINVAL; }
+  if (!workspace || !out_color || !out_depth || !out_opacity) { set_error("null output/workspace"); return MGS_EINVAL; }
+  cudaStream_t s = (cudaStream_t)stream;
+  const int W = view->image_width, H = view->image_height;
+  WsLayout L;
+  if ((rc = ws_layout(P, W, H, R_cap, &L))) return rc;
+  if (workspace_bytes < L.total) { set_error("workspace too small: %zu < %zu", workspace_bytes, L.total); return MGS_ENOSPC; }
+  if (P == 0) {  // rasterize_points.cu:90 — zero-filled outputs, no kernels
+    MGS_CUDA_TRY(cudaMemsetAsync(workspace, 0, sizeof(WsHeader), s));
+    MGS_CUDA_TRY(cudaMemsetAsync(out_color, 0, (size_t)3 * W * H * 4, s));
+    MGS_CUDA_TRY(cudaMemsetAsync(out_depth, 0, (size_t)W * H * 4, s));
+    MGS_CUDA_TRY(cudaMemsetAsync(out_opacity, 0, (size_t)W * H * 4, s));
+    if (status_out) MGS_CUDA_TRY(cudaMemcpyAsync(status_out, workspace, 6 * sizeof(uint32_t), cudaMemcpyDefault, s));
+    if (ready_event) MGS_CUDA_TRY(cudaEventRecord((cudaEvent_t)ready_event, s));
+    return MGS_OK;
+  }
+  if (!means3D || !opacities || !radii || !n_touched) { set_error("means3D/opacities/radii/n_touched must be non-null"); return MGS_EINVAL; }
+  if ((rc = check_options(view, shs, colors_precomp, scales, rotations, cov3D_precomp))) return rc;
+  const ViewConst v = make_view_const(view);
+  if ((rc = launch_preprocess(v, P, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
+                              workspace, L, s)))
+    return rc;
+  MGS_CUDA_TRY(cudaMemsetAsync(n_touched, 0, (size_t)P * sizeof(int32_t), s));
+  if ((rc = launch_tile_scan(v, workspace, L, R_cap, s))) return rc;
+  // the verdict of the scan goes out before the heavy kernels are queued behind it
+  if (status_out) MGS_CUDA_TRY(cudaMemcpyAsync(status_out, workspace, 6 * sizeof(uint32_t), cudaMemcpyDefault, s));
+  if (ready_event) MGS_CUDA_TRY(cudaEventRecord((cudaEvent_t)ready_event, s));
+  if ((rc = launch_binning(v, P, colors_precomp, radii, workspace, L, R_cap, s, false, /*scan_done=*/true))) return rc;
+  return launch_blend_forward(v, workspace, L, out_color, out_depth, out_opacity, n_touched, s);
+}
+
 // test hook: byte offsets of the workspace regions, in WsLayout order (tests read keys/ranges through it)
 int mgs_debug_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, size_t* out /* >= 17 */) {
   WsLayout L;

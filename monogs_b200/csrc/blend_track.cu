@@ -247,13 +247,17 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s) {
   const int tiles = v.gx * v.gy;
-  static bool attr_set = false;
-  if (!attr_set) {
+  // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute
+  static bool attr_set[64] = {};
+  int dev = 0;
+  MGS_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { set_error("blend_track: device ordinal %d out of range", dev); return MGS_EINVAL; }
+  if (!attr_set[dev]) {
     MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
     MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
     MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
     MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
-    attr_set = true;
+    attr_set[dev] = true;
   }
 #define MGS_TRK_ARGS v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color,   \
       out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum

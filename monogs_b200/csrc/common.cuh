@@ -49,7 +49,12 @@ struct WsHeader {
   uint32_t overflow;       // 1 when num_rendered > R_cap
   uint32_t r_used;         // min(num_rendered, R_cap): instances actually binned
   uint32_t n_large;        // tiles whose list exceeds 1024 words; their ids are tile_ctr[i * TILE_CTR_STRIDE + 2], i < n_large
-  uint32_t pad[60];
+  // sticky words: only ever raised by the kernels, cleared by mgs_raster_status_reset.  A loop that reuses one
+  // workspace for many renders (PoseTracker, MapEngine: several views per workspace and iteration) reads them once in a
+  // while instead of after every render, and still learns about ANY render that did not fit.
+  uint32_t overflow_sticky;   // 1 once any binning into this workspace saw num_rendered > R_cap
+  uint32_t max_rendered;      // largest num_rendered any binning into this workspace saw
+  uint32_t pad[58];
 };
 static_assert(sizeof(WsHeader) == 256, "header is one 256-B slot");
 

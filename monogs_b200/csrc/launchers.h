@@ -12,7 +12,7 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
                       float* jac = nullptr, int jac_ncol = 0, const float* sh_rest = nullptr);
 int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false);
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
-                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false);
+                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false, bool scan_done = false);
 struct LossK;
 // optional fused loss epilogue of the forward blend (tracking path): per-pixel loss + un-normalised gradient images
 struct FusedLoss { const LossK* k; float grad_scale; float* g_img; float* g_depth; double* partials; bool fast; };

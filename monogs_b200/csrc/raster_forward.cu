@@ -367,6 +367,8 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
     hdr->overflow = carry > R_cap ? 1u : 0u;
     hdr->r_used = carry > R_cap ? R_cap : carry;
     hdr->n_large = n_large;
+    if (carry > R_cap) hdr->overflow_sticky = 1u;
+    if (carry > hdr->max_rendered) hdr->max_rendered = carry;
   }
   // Heavy-first launch order for per-tile kernels that run in several waves (blend_track_kernel: 3 CTAs per SM): a
   // counting sort of the tiles into 64 buckets of list length, longest lists first, written to
@@ -567,10 +569,12 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
 }
 
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
-                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first) {
+                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first, bool scan_done) {
   const int tiles = v.gx * v.gy;
-  int rc = launch_tile_scan(v, ws, L, R_cap, s, heavy_first);   // ranges (clipped to R_cap), scatter cursors, header
-  if (rc) return rc;
+  if (!scan_done) {
+    int rc = launch_tile_scan(v, ws, L, R_cap, s, heavy_first);   // ranges (clipped to R_cap), scatter cursors, header
+    if (rc) return rc;
+  }
   if (R_cap == 0 || P == 0) return MGS_OK;
   MGS_PROF("emit", s, emit_kernel<<<(P + 255) / 256, 256, 0, s>>>(
       P, (uint32_t)R_cap, v.gx, v.gy, ws_ptr<float2>(ws, L.means2D), ws_ptr<float>(ws, L.depths), radii,

@@ -185,6 +185,10 @@ class MapEngine:
         self._out_extra = []
         self.headroom = capacity_headroom
         self.R_cap, self.ws, self.ws_extra = 0, None, []
+        self._seen_max, self.overflow_polls, self.poll_every, self._since_poll = 0, 0, 16, 0
+        self._status = torch.zeros(8, 8, dtype=torch.int32).pin_memory() if self.dev.type == "cuda" else None
+        self._status_ev = torch.cuda.Event() if self.dev.type == "cuda" else None
+        self._status_pending, self._status_n, self._graph = False, 0, None
         self.reg_weight, self.thr, self.alpha = regulariser_weight, rgb_boundary_threshold, alpha
         self.group = group
         self.distributed = dist.is_available() and dist.is_initialized()
@@ -263,9 +267,11 @@ class MapEngine:
         a.loss_total, a.scratch, a.scratch_bytes = self.loss_total.data_ptr(), self.scratch.data_ptr(), self.scratch.numel()
         return a
 
-    def _ensure_capacity(self, view: MapView):
-        """First use: one synchronous preprocess to learn num_rendered; capacity = headroom x that (shared by all views,
-        which are processed one after the other on the stream)."""
+    def _ensure_capacity(self, views: Sequence[MapView]):
+        """First use (and after every regrow): one synchronous preprocess of EVERY view this rank renders to learn their
+        num_rendered; capacity = headroom x the largest (all workspaces share one size).  Afterwards the sticky header
+        words of the workspaces (overflow_sticky, max_rendered: raised by the scan kernel for ANY view rendered into that
+        workspace, never cleared by it) are polled without a host wait, see poll_capacity()."""
         if self.ws is not None:
             return
         from .rasterizer import make_view, _stream
@@ -277,19 +283,53 @@ class MapEngine:
             rot = torch.nn.functional.normalize(self.params["rotation"]).contiguous()
             shs = (torch.cat((self.params["f_dc"], self.params["f_rest"]), dim=1).contiguous() if "f_rest" in self.params
                    else self.params["f_dc"])
-        keep = []
-        v = make_view(view.settings._replace(sh_degree=self.sh_degree), self.M, keep)
         base = lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, 0)
         tmp = torch.empty(base, device=self.dev, dtype=torch.uint8)
         radii = torch.zeros(self.P, device=self.dev, dtype=torch.int32)
-        n_host = torch.zeros(1, dtype=torch.int32).pin_memory()
-        L.check(lib.mgs_raster_preprocess(C.byref(v), self.P, L.ptr(self.params["xyz"]), L.ptr(op), L.ptr(shs), None, L.ptr(sc),
-                                          L.ptr(rot), None, L.ptr(radii), L.ptr(tmp), tmp.numel(),
-                                          C.c_void_p(n_host.data_ptr()), _stream()), "mgs_raster_preprocess")
-        torch.cuda.current_stream().synchronize()
-        self.R_cap = max(int(int(n_host.item()) * self.headroom) + 4096, 4096)
-        self.ws = torch.empty(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev, dtype=torch.uint8)
+        n_host = torch.zeros(max(len(views), 1), dtype=torch.int32).pin_memory()
+        for k, view in enumerate(views):
+            keep = []
+            v = make_view(view.settings._replace(sh_degree=self.sh_degree), self.M, keep)
+            L.check(lib.mgs_raster_preprocess(C.byref(v), self.P, L.ptr(self.params["xyz"]), L.ptr(op), L.ptr(shs), None, L.ptr(sc),
+                                              L.ptr(rot), None, L.ptr(radii), L.ptr(tmp), tmp.numel(),
+                                              C.c_void_p(n_host[k:].data_ptr()), _stream(self.dev)), "mgs_raster_preprocess")
+        torch.cuda.current_stream(self.dev).synchronize()
+        seen = max(int(n_host.max()), self._seen_max)
+        self.R_cap = max(int(seen * self.headroom) + 4096, 4096)
+        # zero-filled: the sticky header words are read by poll_capacity()
+        self.ws = torch.zeros(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev, dtype=torch.uint8)
         self.ws_extra, self._out_extra = [], []
+        self._status_pending = False
+        self._graph = None
+
+    def poll_capacity(self):
+        """Overflow watch without a host wait (called by step() every `poll_every` iterations): enqueue a 24-byte copy of
+        every workspace header to pinned memory, and look at the copies enqueued at the previous poll (event.query(), never
+        a synchronize).  Any view of any iteration in between that exceeded R_cap has raised overflow_sticky in its
+        workspace: the engine counts it (`overflow_polls`), drops the workspaces and re-estimates the capacity from the
+        largest num_rendered seen, before the next iteration.  A count within 10 % of the capacity regrows proactively.
+        Returns True when the workspaces were dropped."""
+        from .rasterizer import _stream
+        dropped = False
+        if self._status_pending and self._status_ev.query():
+            self._status_pending = False
+            n = self._status_n
+            over = bool(self._status[:n, 4].any())
+            self._seen_max = max(self._seen_max, int(self._status[:n, 5].max()))
+            if over:
+                self.overflow_polls += 1
+            if over or self._seen_max * 1.1 > self.R_cap:
+                self.ws, self.ws_extra = None, []
+                dropped = True
+        if not self._status_pending and self.ws is not None:
+            wss = [self.ws] + list(self.ws_extra)
+            with torch.cuda.device(self.dev):
+                for k, ws in enumerate(wss):
+                    self.L.check(self.lib.mgs_raster_status_async(self.L.ptr(ws), C.c_void_p(self._status[k:].data_ptr()),
+                                                                  _stream(self.dev)), "mgs_raster_status_async")
+                self._status_ev.record(torch.cuda.current_stream(self.dev))
+            self._status_n, self._status_pending = len(wss), True
+        return dropped
 
     def _slot(self, i):
         """Per-view output buffers (kept across iterations: the same window is mapped many times)."""
@@ -380,10 +420,14 @@ class MapEngine:
             p.grad = v
         self._keep = []
         args = self._args()
-        self._ensure_capacity(views[0])
+        mine = list(shard_views(len(views), self.world, self.rank))
+        self._since_poll += 1
+        if self._since_poll >= self.poll_every:
+            self._since_poll = 0
+            self.poll_capacity()
+        self._ensure_capacity([views[i] for i in mine])
         L.check(self.lib.mgs_map_begin(C.byref(args), _stream()), "mgs_map_begin")
         out = {}
-        mine = list(shard_views(len(views), self.world, self.rank))
         for i in mine:
             out[i] = self._slot(i)
         if self.overlap and len(mine) > 1:
@@ -431,13 +475,17 @@ class MapEngine:
         """Synchronous check of the device-side overflow flag of the last rendered view(s); regrows on overflow."""
         from .rasterizer import _stream
         n_max, over = 0, False
-        for ws in [self.ws] + list(self.ws_extra):
-            if ws is None: continue
-            n, ov = C.c_int32(0), C.c_int32(0)
-            self.L.check(self.lib.mgs_raster_query(self.L.ptr(ws), C.byref(n), C.byref(ov), _stream()), "mgs_raster_query")
-            n_max, over = max(n_max, n.value), over or bool(ov.value)
+        wss = [ws for ws in [self.ws] + list(self.ws_extra) if ws is not None]
+        if wss:
+            st = torch.zeros(len(wss), 8, dtype=torch.int32).pin_memory()
+            for k, ws in enumerate(wss):
+                self.L.check(self.lib.mgs_raster_status_async(self.L.ptr(ws), C.c_void_p(st[k:].data_ptr()), _stream()),
+                             "mgs_raster_status_async")
+            torch.cuda.current_stream(self.dev).synchronize()
+            # sticky words: ANY view rendered into these workspaces since they were allocated, not only the last one
+            n_max, over = int(st[:, 5].max()), bool(st[:, 4].any())
+            self._seen_max = max(self._seen_max, n_max)
         if over:
-            self.headroom *= 1.5
             self.ws, self.ws_extra = None, []
         if self.block is not None:
             epoch = self.block.error_epoch(_stream())
@@ -474,7 +522,7 @@ class MapEngine:
         self.xyz_gradient_accum, self.denom = torch.zeros(self.P, **f), torch.zeros(self.P, **f)
         self.max_radii2D = torch.zeros(self.P, **f)
         self.scratch = torch.empty(self.lib.mgs_map_scratch_bytes(self.P, self.M, self.W, self.H), device=self.dev, dtype=torch.uint8)
-        self.ws, self._slots = None, {}
+        self.ws, self._slots, self._seen_max = None, {}, 0
         if self.exchange != "nccl":
             assert len(set(steps.values())) == 1, "the engine's parameters step together"
             self._install_peer(steps=next(iter(steps.values())), moments=(out["exp_avg"], out["exp_avg_sq"]))

@@ -141,18 +141,43 @@ class PeerBlock:
         return e.value
 
     def close(self):
-        """Unmap the other ranks' blocks, then free this one.  Collective for a connected block: an exporter must not free
-        its allocation while another process still has it mapped, so the ranks meet between the two steps."""
+        """Drain this device, unmap the other ranks' blocks, then free this one.  Collective for a connected block: an
+        exporter must not free its allocation while another process still has it mapped, so the ranks meet between the two
+        steps.  The synchronize comes FIRST: a peer_reduce_adam / peer_wait kernel still queued on this rank reads and
+        writes the peers' mappings."""
         if self.backend == "symm":
+            if getattr(self, "ptr", None):
+                torch.cuda.synchronize(self.dev)
             self.ptr = None       # the symmetric allocation is released with its tensors
             return
         if getattr(self, "ptr", None):
             with torch.cuda.device(self.dev):
+                torch.cuda.synchronize(self.dev)
                 for p in self._opened:
                     self.lib.mgs_peer_close(C.c_void_p(p))
                 self._opened = []
-                torch.cuda.synchronize(self.dev)
                 if self._connected:
                     dist.barrier(self._group)
                 self.lib.mgs_peer_free(C.c_void_p(self.ptr))
             self.ptr = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+        return False
+
+    def __del__(self):
+        # Last resort for a block that was never closed: release the local allocation and mappings WITHOUT the collective
+        # barrier (a finalizer can not rendezvous).  A connected block should be closed explicitly, on every rank.
+        try:
+            if getattr(self, "backend", None) == "ipc" and getattr(self, "ptr", None):
+                with torch.cuda.device(self.dev):
+                    torch.cuda.synchronize(self.dev)
+                    for p in self._opened:
+                        self.lib.mgs_peer_close(C.c_void_p(p))
+                    self.lib.mgs_peer_free(C.c_void_p(self.ptr))
+                self.ptr = None
+        except Exception:   # interpreter shutdown: the driver reclaims everything
+            pass

@@ -7,6 +7,7 @@ same 17-tuple of gradients, `grad_rho` / `grad_theta` shaped [1,3].  torch is us
 the current stream only; all arithmetic happens in libmonogs_b200.so.
 """
 import ctypes as C
+import threading
 from typing import NamedTuple
 
 import torch
@@ -43,13 +44,36 @@ _raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
 _raw_device = getattr(torch._C, "_cuda_getDevice", None)
 
 
-def _stream():
-    """Handle of torch's current stream on the current device.  torch.cuda.current_stream() builds a Stream object and
-    resolves the device through several Python layers (~20 us per call, six calls per drop-in tracking step); the raw
-    accessors return the same handle in about a microsecond."""
+def _stream(dev=None):
+    """Handle of torch's current stream on `dev` (a torch.device / index; default: the current device).  Callers pass the
+    device of the tensors they hand to the library, so the launch goes to a stream of THAT device even when it is not the
+    current one (several GPUs in one process).  torch.cuda.current_stream() builds a Stream object and resolves the device
+    through several Python layers (~20 us per call, six calls per drop-in tracking step); the raw accessors return the
+    same handle in about a microsecond."""
+    if isinstance(dev, torch.device):
+        dev = dev.index
     if _raw_stream is not None and _raw_device is not None:
-        return C.c_void_p(_raw_stream(_raw_device()))
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        return C.c_void_p(_raw_stream(_raw_device() if dev is None else dev))
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+class _on:
+    """`with _on(dev):` — make `dev` the current CUDA device for the library calls inside (the kernels are launched on the
+    device that is current, so it must be the one that owns the pointers); a no-op when it already is."""
+    __slots__ = ("dev", "prev")
+
+    def __init__(self, dev):
+        self.dev = dev.index if isinstance(dev, torch.device) else dev
+
+    def __enter__(self):
+        self.prev = None
+        if self.dev is not None and _raw_device is not None and _raw_device() != self.dev:
+            self.prev = _raw_device()
+            torch.cuda.set_device(self.dev)
+
+    def __exit__(self, *exc):
+        if self.prev is not None:
+            torch.cuda.set_device(self.prev)
 
 
 def make_view(rs: GaussianRasterizationSettings, sh_coeffs: int, keep: list) -> L.MgsView:
@@ -76,9 +100,64 @@ class RasterState:
     __slots__ = ("workspace", "num_rendered", "P", "sh_coeffs")
 
 
+class _DevCache(threading.local):
+    """Per thread and device: a pinned status slot + the event that guards it, and the last num_rendered seen for a
+    (P, W, H) problem — the capacity guess of the next forward of that size."""
+
+    def __init__(self):
+        self.by_dev = {}
+
+    def get(self, dev):
+        c = self.by_dev.get(dev.index)
+        if c is None:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(dev))    # materialises the cudaEvent_t the library records into
+            c = self.by_dev[dev.index] = dict(status=torch.zeros(8, dtype=torch.int32).pin_memory(), event=ev, guess={})
+        return c
+
+
+_cache = _DevCache()
+CAPACITY_HEADROOM = 1.25     # workspace capacity of a speculative forward = previous num_rendered of that size x this
+
+
+def _debug_guard(rs, s, what, args_fn, dump):
+    """debug=True (auxiliary.h:166-173 CHECK_CUDA, __init__.py:109-116,202-209): wait for the launches of `what` and
+    raise on any CUDA error; on failure the inputs are written to `dump` before the exception propagates."""
+    class _G:
+        def __enter__(self_g):
+            self_g.snapshot = _cpu_deep_copy(args_fn()) if rs.debug else None   # copied before they can be corrupted
+            return self_g
+
+        def __exit__(self_g, et, ev, tb):
+            if not rs.debug:
+                return False
+            if et is None:
+                try:
+                    L.check(L.lib().mgs_stream_synchronize(s), what + " (debug synchronize)")
+                    return False
+                except RuntimeError:
+                    torch.save(self_g.snapshot, dump)
+                    print(f"\nAn error occured in {what}. Please forward {dump} for debugging.")
+                    raise
+            torch.save(self_g.snapshot, dump)
+            print(f"\nAn error occured in {what}. Please forward {dump} for debugging.")
+            return False
+    return _G()
+
+
+def _cpu_deep_copy(args):
+    return tuple(a.detach().cpu().clone() if isinstance(a, torch.Tensor) else a for a in args)
+
+
 def raster_forward(rs, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp):
-    """Two-stage forward with the reference's single host read of num_rendered in between
-    (rasterizer_impl.cu:284).  Returns (color, radii, depth, opacity, n_touched, state)."""
+    """Forward of the drop-in surface.  Returns (color, radii, depth, opacity, n_touched, state).
+
+    The reference blocks the host in the middle of every forward to read num_rendered (rasterizer_impl.cu:284) before it
+    can size the binning buffers.  Here the first forward of a (P, W, H) problem does the same (two stages, one read);
+    every later one launches the whole pipeline at once into a workspace sized from the previous call's count
+    (x CAPACITY_HEADROOM) and only then waits for the count, which the device sent out right after the scan — so the
+    device is never idle while the host turns around, num_rendered is exact on return, and in the rare case the guess
+    was too small the binning + blend are simply repeated at the right size before returning."""
     lib = L.lib()
     dev = means3D.device
     if means3D.dim() != 2 or means3D.size(1) != 3:
@@ -90,35 +169,55 @@ def raster_forward(rs, means3D, opacities, shs, colors_precomp, scales, rotation
     M = shs.size(1) if shs is not None else 0
     keep = []
     view = make_view(rs, M, keep)
-    color = torch.empty(3, H, W, device=dev, dtype=torch.float32)
-    depth = torch.empty(1, H, W, device=dev, dtype=torch.float32)
-    opacity = torch.empty(1, H, W, device=dev, dtype=torch.float32)
-    radii = torch.zeros(P, device=dev, dtype=torch.int32)
-    n_touched = torch.zeros(P, device=dev, dtype=torch.int32)
+    f = dict(device=dev, dtype=torch.float32)
+    color, depth, opacity = torch.empty(3, H, W, **f), torch.empty(1, H, W, **f), torch.empty(1, H, W, **f)
+    # both fully written by the library (radii by the preprocess, n_touched zeroed before the blend)
+    radii = torch.empty(P, device=dev, dtype=torch.int32)
+    n_touched = torch.empty(P, device=dev, dtype=torch.int32)
     st = RasterState()
     st.P, st.sh_coeffs = P, M
     if P == 0:  # rasterize_points.cu:90 — legal, zero-filled outputs
         color.zero_(); depth.zero_(); opacity.zero_()
         st.workspace, st.num_rendered = torch.empty(0, device=dev, dtype=torch.uint8), 0
         return color, radii, depth, opacity, n_touched, st
-    s = _stream()
-    base = lib.mgs_raster_workspace_bytes(P, W, H, 0)
-    ws = torch.empty(base, device=dev, dtype=torch.uint8)
-    n_host = torch.empty(1, dtype=torch.int32).pin_memory()
-    L.check(lib.mgs_raster_preprocess(C.byref(view), P, L.ptr(means3D), L.ptr(opacities), L.ptr(shs),
-                                      L.ptr(colors_precomp), L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp),
-                                      L.ptr(radii), L.ptr(ws), ws.numel(), C.c_void_p(n_host.data_ptr()), s),
-            "mgs_raster_preprocess")
-    L.check(lib.mgs_stream_synchronize(s), "mgs_stream_synchronize")
-    R = int(n_host.item())
-    need = lib.mgs_raster_workspace_bytes(P, W, H, R)
-    if need > ws.numel():
-        big = torch.empty(need, device=dev, dtype=torch.uint8)
-        big[:base].copy_(ws)  # per-Gaussian state sits at R-independent offsets
-        ws = big
-    L.check(lib.mgs_raster_render(C.byref(view), P, L.ptr(colors_precomp), L.ptr(radii), L.ptr(ws), ws.numel(), R,
-                                  L.ptr(color), L.ptr(depth), L.ptr(opacity), L.ptr(n_touched), s),
-            "mgs_raster_render")
+    with _on(dev):
+        s = _stream(dev)
+        cache = _cache.get(dev)
+        status, key = cache["status"], (P, W, H)
+        guess = cache["guess"].get(key)
+        snap = lambda: (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3D_precomp,
+                        rs.viewmatrix, rs.projmatrix, rs.projmatrix_raw, rs.tanfovx, rs.tanfovy, H, W, shs, rs.sh_degree,
+                        rs.campos, rs.prefiltered, rs.debug)
+        with _debug_guard(rs, s, "forward", snap, "snapshot_fw.dump"):
+            base = lib.mgs_raster_workspace_bytes(P, W, H, 0)
+            if guess is None:
+                ws = torch.empty(base, device=dev, dtype=torch.uint8)
+                L.check(lib.mgs_raster_preprocess(C.byref(view), P, L.ptr(means3D), L.ptr(opacities), L.ptr(shs),
+                                                  L.ptr(colors_precomp), L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp),
+                                                  L.ptr(radii), L.ptr(ws), ws.numel(), C.c_void_p(status.data_ptr()), s),
+                        "mgs_raster_preprocess")
+                L.check(lib.mgs_stream_synchronize(s), "mgs_stream_synchronize")
+                R, rerun = int(status[0]), True
+            else:
+                R_cap = int(guess * CAPACITY_HEADROOM) + 4096
+                ws = torch.empty(lib.mgs_raster_workspace_bytes(P, W, H, R_cap), device=dev, dtype=torch.uint8)
+                L.check(lib.mgs_raster_forward(C.byref(view), P, L.ptr(means3D), L.ptr(opacities), L.ptr(shs),
+                                               L.ptr(colors_precomp), L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp),
+                                               L.ptr(radii), L.ptr(ws), ws.numel(), R_cap, L.ptr(color), L.ptr(depth),
+                                               L.ptr(opacity), L.ptr(n_touched), C.c_void_p(status.data_ptr()),
+                                               C.c_void_p(cache["event"].cuda_event), s), "mgs_raster_forward")
+                cache["event"].synchronize()      # the status left the device before emit / sort / blend were queued
+                R, rerun = int(status[0]), bool(status[1])
+            if rerun:
+                need = lib.mgs_raster_workspace_bytes(P, W, H, R)
+                if need > ws.numel():
+                    big = torch.empty(need, device=dev, dtype=torch.uint8)
+                    big[:base].copy_(ws[:base])  # per-Gaussian state sits at R-independent offsets
+                    ws = big
+                L.check(lib.mgs_raster_render(C.byref(view), P, L.ptr(colors_precomp), L.ptr(radii), L.ptr(ws), ws.numel(), R,
+                                              L.ptr(color), L.ptr(depth), L.ptr(opacity), L.ptr(n_touched), s),
+                        "mgs_raster_render")
+            cache["guess"][key] = R
     st.workspace, st.num_rendered = ws, R
     return color, radii, depth, opacity, n_touched, st
 
@@ -155,12 +254,18 @@ def raster_backward(rs, st, grad_mask, means3D, shs, colors_precomp, scales, rot
         return out
     scratch = torch.empty(lib.mgs_raster_backward_scratch_bytes(P), device=dev, dtype=torch.uint8)
     g = lambda k: L.ptr(out[k]) if k in out else None
-    L.check(lib.mgs_raster_backward(C.byref(view), P, grad_mask, L.ptr(means3D), L.ptr(shs), L.ptr(colors_precomp),
-                                    L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp), L.ptr(radii),
-                                    L.ptr(st.workspace), st.workspace.numel(), L.ptr(scratch), scratch.numel(),
-                                    L.ptr(grad_color), L.ptr(grad_depth), g("means3D"), g("means2D"), g("color"),
-                                    g("opacity"), g("scales"), g("rotations"), g("cov3D"), g("tau"), g("tau_pg"),
-                                    _stream()), "mgs_raster_backward")
+    with _on(dev):
+        s = _stream(dev)
+        snap = lambda: (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3D_precomp,
+                        rs.viewmatrix, rs.projmatrix, rs.projmatrix_raw, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, shs,
+                        rs.sh_degree, rs.campos, st.workspace, st.num_rendered, rs.debug)
+        with _debug_guard(rs, s, "backward", snap, "snapshot_bw.dump"):
+            L.check(lib.mgs_raster_backward(C.byref(view), P, grad_mask, L.ptr(means3D), L.ptr(shs), L.ptr(colors_precomp),
+                                            L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp), L.ptr(radii),
+                                            L.ptr(st.workspace), st.workspace.numel(), L.ptr(scratch), scratch.numel(),
+                                            L.ptr(grad_color), L.ptr(grad_depth), g("means3D"), g("means2D"), g("color"),
+                                            g("opacity"), g("scales"), g("rotations"), g("cov3D"), g("tau"), g("tau_pg"),
+                                            s), "mgs_raster_backward")
     return out
 
 
@@ -178,11 +283,17 @@ def raster_backward_pose(rs, st, means3D, shs, colors_precomp, scales, rotations
     tau = torch.empty(6, device=dev, dtype=torch.float32)
     tau_image = torch.empty(6, H, W, device=dev, dtype=torch.float32) if want_image else None
     scratch = torch.empty(max(lib.mgs_raster_backward_pose_scratch_bytes(P, W, H), 256), device=dev, dtype=torch.uint8)
-    L.check(lib.mgs_raster_backward_pose(C.byref(view), P, L.ptr(means3D), L.ptr(shs), L.ptr(colors_precomp),
-                                         L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp), L.ptr(radii),
-                                         L.ptr(st.workspace), st.workspace.numel(), L.ptr(scratch), scratch.numel(),
-                                         L.ptr(grad_color), L.ptr(grad_depth), L.ptr(tau_image), L.ptr(tau),
-                                         _stream()), "mgs_raster_backward_pose")
+    with _on(dev):
+        s = _stream(dev)
+        snap = lambda: (rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3D_precomp,
+                        rs.viewmatrix, rs.projmatrix, rs.projmatrix_raw, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, shs,
+                        rs.sh_degree, rs.campos, st.workspace, st.num_rendered, rs.debug)
+        with _debug_guard(rs, s, "backward", snap, "snapshot_bw.dump"):
+            L.check(lib.mgs_raster_backward_pose(C.byref(view), P, L.ptr(means3D), L.ptr(shs), L.ptr(colors_precomp),
+                                                 L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp), L.ptr(radii),
+                                                 L.ptr(st.workspace), st.workspace.numel(), L.ptr(scratch), scratch.numel(),
+                                                 L.ptr(grad_color), L.ptr(grad_depth), L.ptr(tau_image), L.ptr(tau),
+                                                 s), "mgs_raster_backward_pose")
     return tau, tau_image
 
 
@@ -194,8 +305,9 @@ def sketch_reduce(tau_image, sketch_indices, sketch_dim):
     idx = sketch_indices.to(torch.int32).contiguous()
     n_stacks, H, W = idx.shape
     out = torch.empty(n_stacks, sketch_dim, 6, device=tau_image.device, dtype=torch.float32)
-    L.check(lib.mgs_sketch_reduce(L.ptr(tau_image), H, W, n_stacks, sketch_dim, L.ptr(idx), L.ptr(out), _stream()),
-            "mgs_sketch_reduce")
+    with _on(tau_image.device):
+        L.check(lib.mgs_sketch_reduce(L.ptr(tau_image), H, W, n_stacks, sketch_dim, L.ptr(idx), L.ptr(out),
+                                      _stream(tau_image.device)), "mgs_sketch_reduce")
     return out
 
 
@@ -301,8 +413,9 @@ class GaussianRasterizer(nn.Module):
             P = pos.size(0)
             out = torch.zeros(P, device=pos.device, dtype=torch.uint8)
             vm, pm = _f32c(rs.viewmatrix), _f32c(rs.projmatrix)
-            L.check(L.lib().mgs_mark_visible(P, L.ptr(pos), L.ptr(vm), L.ptr(pm), L.ptr(out), _stream()),
-                    "mgs_mark_visible")
+            with _on(pos.device):
+                L.check(L.lib().mgs_mark_visible(P, L.ptr(pos), L.ptr(vm), L.ptr(pm), L.ptr(out), _stream(pos.device)),
+                        "mgs_mark_visible")
         return out.bool()
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,

@@ -22,7 +22,10 @@ KERNELS_PER_ITER_COMPOSED = 14
 
 class PoseTracker:
     def __init__(self, means3D, opacities, shs, scales, rotations, sh_degree, cam, bg, T_w2c, mode=L.LOSS_TRACK_HUBER,
-                 use_depth=False, lr=(1e-3, 3e-3, 2e-2, 2e-2), capacity_headroom=1.3, use_graph=True, fused=True, fast_math=True):
+                 use_depth=False, lr=(1e-3, 3e-3, 2e-2, 2e-2), capacity_headroom=1.3, use_graph=True, fused=True, fast_math=True,
+                 adam_eps=1e-8):
+        """adam_eps: the reference builds the pose / exposure optimiser as torch.optim.Adam(opt_params) with torch's default
+        eps = 1e-8 (utils/slam_frontend.py:453); only the Gaussian optimiser uses 1e-15 (gaussian_model.py:285)."""
         lib = self.lib = L.lib()
         dev = self.dev = means3D.device
         f = dict(device=dev, dtype=torch.float32)
@@ -46,7 +49,7 @@ class PoseTracker:
         self.tau = torch.zeros(6, **f)
         self.dab = torch.zeros(2, **f)
         self.exp_avg, self.exp_avg_sq = torch.zeros(8, **f), torch.zeros(8, **f)
-        self.lr = lr
+        self.lr, self.adam_eps = lr, float(adam_eps)
         self.step_dev = torch.zeros(1, device=dev, dtype=torch.int32)   # Adam step number, kept on the device
         self.mode, self.use_depth = mode, use_depth
         # outputs / intermediates
@@ -68,6 +71,12 @@ class PoseTracker:
         self.headroom = capacity_headroom
         self.R_cap, self.ws = 0, None
         self.use_graph, self.graph = use_graph, None
+        self._seen_max = 0
+        self._status = torch.zeros(8, dtype=torch.int32).pin_memory()
+        self._status_ev = torch.cuda.Event()
+        self._status_pending = False
+        self._host_bind = None
+        self.overflow_frames = 0     # frames during which at least one iteration dropped instances (see poll_capacity)
         self._size_workspace()
 
     # ------------------------------------------------------------------------------------------------
@@ -80,13 +89,17 @@ class PoseTracker:
         L.check(lib.mgs_raster_preprocess(C.byref(self.view), self.P, L.ptr(self.means3D), L.ptr(self.opacities),
                                           L.ptr(self.shs), None, L.ptr(self.scales), L.ptr(self.rotations), None,
                                           L.ptr(self.radii), L.ptr(tmp), tmp.numel(), C.c_void_p(n_host.data_ptr()),
-                                          _stream()), "mgs_raster_preprocess")
-        torch.cuda.current_stream().synchronize()
+                                          _stream(self.dev)), "mgs_raster_preprocess")
+        torch.cuda.current_stream(self.dev).synchronize()
         R = int(n_host.item())
-        self.R_cap = max(int(R * self.headroom) + 4096, 4096)
-        self.ws = torch.empty(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev,
+        self.R_cap = max(int(max(R, self._seen_max) * self.headroom) + 4096, 4096)
+        # zero-filled: the sticky header words (overflow_sticky, max_rendered) are read by poll_capacity()
+        self.ws = torch.zeros(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev,
                               dtype=torch.uint8)
         self.graph = None
+        self._status_pending = False
+        if getattr(self, "_host_bind", None) is not None:
+            self.bind_host(*self._host_bind)     # the captured host graphs point into the old workspace
 
     def _loss_args(self):
         a = L.MgsLossArgs()
@@ -114,7 +127,7 @@ class PoseTracker:
         t.exp_avg, t.exp_avg_sq, t.step_counter = self.exp_avg.data_ptr(), self.exp_avg_sq.data_ptr(), self.step_dev.data_ptr()
         for i in range(4):
             t.lr[i] = self.lr[i]
-        t.beta1, t.beta2, t.adam_eps, t.converged_threshold = 0.9, 0.999, 1e-15, 1e-4
+        t.beta1, t.beta2, t.adam_eps, t.converged_threshold = 0.9, 0.999, self.adam_eps, 1e-4
         t.out_color, t.out_depth, t.out_opacity = self.color.data_ptr(), self.depth.data_ptr(), self.opacity.data_ptr()
         t.radii, t.n_touched = self.radii.data_ptr(), self.n_touched.data_ptr()
         t.loss, t.tau, t.dab, t.converged = self.loss.data_ptr(), self.tau.data_ptr(), self.dab.data_ptr(), self.converged.data_ptr()
@@ -127,9 +140,9 @@ class PoseTracker:
         (mgs_track_iteration) or, with fused=False, the same iteration composed from the individual entry points."""
         if self.fused:
             t = self._track_args()
-            L.check(self.lib.mgs_track_iteration(C.byref(t), _stream()), "mgs_track_iteration")
+            L.check(self.lib.mgs_track_iteration(C.byref(t), _stream(self.dev)), "mgs_track_iteration")
             return
-        lib, s, v = self.lib, _stream(), C.byref(self.view)
+        lib, s, v = self.lib, _stream(self.dev), C.byref(self.view)
         L.check(lib.mgs_raster_preprocess(v, self.P, L.ptr(self.means3D), L.ptr(self.opacities), L.ptr(self.shs), None,
                                           L.ptr(self.scales), L.ptr(self.rotations), None, L.ptr(self.radii),
                                           L.ptr(self.ws), self.ws.numel(), None, s), "mgs_raster_preprocess")
@@ -152,15 +165,43 @@ class PoseTracker:
             groups[i].grad = gsrc[goff:goff + (hi - lo)].data_ptr()
             groups[i].exp_avg, groups[i].exp_avg_sq = self.exp_avg[lo:hi].data_ptr(), self.exp_avg_sq[lo:hi].data_ptr()
             groups[i].numel, groups[i].lr = hi - lo, self.lr[i]
-        L.check(lib.mgs_adam_step_device(groups, 4, L.ptr(self.step_dev), 0.9, 0.999, 1e-15, s), "mgs_adam_step_device")
+        L.check(lib.mgs_adam_step_device(groups, 4, L.ptr(self.step_dev), 0.9, 0.999, self.adam_eps, s), "mgs_adam_step_device")
         L.check(lib.mgs_pose_update(L.ptr(self.T), L.ptr(self.params[0:3]), L.ptr(self.params[3:6]), L.ptr(self.proj_raw),
                                     L.ptr(self.viewmatrix), L.ptr(self.projmatrix), L.ptr(self.converged), 1e-4, s),
                 "mgs_pose_update")
 
     # ------------------------------------------------------------------------------------------------
-    def set_frame(self, gt_image, gt_depth=None, grad_mask=None, non_blocking=True):
+    def poll_capacity(self):
+        """Overflow watch without a host wait.  The scan kernel raises two sticky words in the workspace header
+        (overflow_sticky, max_rendered) whenever an iteration's tile instances exceed R_cap; once per frame the tracker
+        enqueues a 24-byte copy of the header to pinned memory and looks at the copy it enqueued one frame earlier (long
+        complete: event.query(), never synchronize).  An overflow regrows the workspace (and re-captures the graph) before
+        the next frame and is counted in `overflow_frames`; a count that merely approaches the capacity regrows it
+        proactively.  Returns True when the workspace was regrown."""
+        regrown = False
+        if self._status_pending and self._status_ev.query():
+            self._status_pending = False
+            over, seen = bool(self._status[4]), int(self._status[5])
+            self._seen_max = max(self._seen_max, seen)
+            if over:
+                self.overflow_frames += 1
+            if over or seen * 1.1 > self.R_cap:
+                self._size_workspace()
+                regrown = True
+        if not self._status_pending:
+            with torch.cuda.device(self.dev):
+                L.check(self.lib.mgs_raster_status_async(L.ptr(self.ws), C.c_void_p(self._status.data_ptr()), _stream(self.dev)),
+                        "mgs_raster_status_async")
+                self._status_ev.record(torch.cuda.current_stream(self.dev))
+            self._status_pending = True
+        return regrown
+
+    def set_frame(self, gt_image, gt_depth=None, grad_mask=None, non_blocking=True, exposure=(0.0, 0.0)):
         """New target frame (host pinned or device tensors); resets the per-frame optimiser state like the
-        reference, which builds a fresh Adam per frame (slam_frontend.py:364-392,453)."""
+        reference, which builds a fresh Adam per frame (slam_frontend.py:364-392,453) and a fresh Camera whose exposure
+        starts at a = b = 0 (utils/camera_utils.py:56-61); only the pose is carried over.  exposure=None keeps the
+        previous frame's (a, b)."""
+        self.poll_capacity()
         self.gt_image.copy_(gt_image, non_blocking=non_blocking)
         if self.gt_depth is not None and gt_depth is not None:
             self.gt_depth.copy_(gt_depth, non_blocking=non_blocking)
@@ -170,6 +211,8 @@ class PoseTracker:
                 self.graph = None
             self.grad_mask.copy_(grad_mask, non_blocking=non_blocking)
         self.exp_avg.zero_(); self.exp_avg_sq.zero_(); self.params[:6].zero_(); self.step_dev.zero_()
+        if exposure is not None:
+            self.params[6].fill_(float(exposure[0])); self.params[7].fill_(float(exposure[1]))
 
     def step(self):
         """One tracking iteration: the first call captures the C-ABI call sequence into a CUDA graph (the Adam step
@@ -196,17 +239,18 @@ class PoseTracker:
         S = 2 result slots enable step_host_lagged(): iteration k is launched before the host waits for iteration
         k-1, so the GPU never idles while the host turns around (one graph per slot, used alternately)."""
         assert gt_host.is_pinned() and loss_host.is_pinned() and tau_host.is_pinned()
+        self._host_bind = (gt_host, loss_host, tau_host)
         S = loss_host.numel()
         tau_slots = tau_host.view(S, 6)
         self._stage = torch.empty_like(self.gt_image)
         self._stage.copy_(gt_host, non_blocking=True)
         torch.cuda.synchronize()
-        side = torch.cuda.Stream()
+        side = torch.cuda.Stream(device=self.dev)
         self.host_graphs, self._host_ev, self._host_k = [], [torch.cuda.Event() for _ in range(S)], 0
         for slot in range(S):
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                main = torch.cuda.current_stream()
+                main = torch.cuda.current_stream(self.dev)
                 self.gt_image.copy_(self._stage, non_blocking=True)
                 side.wait_stream(main)
                 with torch.cuda.stream(side):
@@ -222,7 +266,7 @@ class PoseTracker:
         """One iteration of the host-bound pipeline set up by bind_host(); results in slot 0."""
         self.host_graph.replay()
         if sync:
-            torch.cuda.current_stream().synchronize()
+            torch.cuda.current_stream(self.dev).synchronize()
 
     def step_host_lagged(self):
         """Launch iteration k, then wait for iteration k-1 only.  Returns the result slot (0 / 1) that now holds
@@ -241,7 +285,8 @@ class PoseTracker:
     def check_capacity(self):
         """Synchronous check of the device-side overflow flag; regrows the workspace if the splat count outgrew it."""
         n, ov = C.c_int32(0), C.c_int32(0)
-        L.check(self.lib.mgs_raster_query(L.ptr(self.ws), C.byref(n), C.byref(ov), _stream()), "mgs_raster_query")
+        L.check(self.lib.mgs_raster_query(L.ptr(self.ws), C.byref(n), C.byref(ov), _stream(self.dev)), "mgs_raster_query")
+        self._seen_max = max(self._seen_max, n.value)
         if ov.value:
             self._size_workspace()
         return n.value, bool(ov.value)

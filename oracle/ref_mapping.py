@@ -41,18 +41,32 @@ class RefMapper:
         self.opt = torch.optim.Adam([{"params": [p], "lr": lrs[k]} for k, p in self.p.items()], lr=0.0, eps=1e-15)
         self.cams, self.gts, self.bg, self.deg, self.thr = cams, gts, bg, sh_degree, thr
 
+    def loss_and_grads(self):
+        """One iteration up to the raw-parameter gradients (no optimizer step): (total loss, {name: grad}, per-view
+        forward dicts of ref_gpu.forward with radii / n_touched)."""
+        total = self._forward_backward()
+        grads = {k: v.grad.detach().clone() for k, v in self.p.items()}
+        self.opt.zero_grad(set_to_none=True)
+        return total.detach(), grads, self.fws
+
     def step(self):
+        total = self._forward_backward()
+        self.opt.step()
+        self.opt.zero_grad(set_to_none=True)
+        return total.detach()
+
+    def _forward_backward(self):
         p = self.p
+        self.fws = []
         total = 0.0
         for slot, (cam, gt) in enumerate(zip(self.cams, self.gts)):
             image, depth, opacity = _RefRasterizeFull.apply(p["xyz"], p["f_dc"], torch.sigmoid(p["opacity"]),
                                                             torch.exp(p["scaling"]),
                                                             torch.nn.functional.normalize(p["rotation"]), cam, self.bg, self.deg, slot)
+            self.fws.append(image.grad_fn.fw if image.grad_fn is not None else None)
             mask = (gt.sum(dim=0) > self.thr).view(1, *gt.shape[1:])
             total = total + torch.abs(image * mask - gt * mask).mean()
         s = torch.exp(p["scaling"])
         total = total + 10 * torch.abs(s - s.mean(dim=1).view(-1, 1)).mean()
         total.backward()
-        self.opt.step()
-        self.opt.zero_grad(set_to_none=True)
-        return total.detach()
+        return total

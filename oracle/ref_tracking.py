@@ -63,8 +63,16 @@ def _so3_exp(theta):
 
 
 class RefTracker:
-    def __init__(self, sc, cam, bg, T_w2c, make_camera):
+    """mode "huber": the fork's first-order objective, ||Huber(opacity * (image_ab*m - gt*m))||_2 with m = the rgb
+    boundary mask (slam_utils.py:188-205, slam_frontend.py:506,596-598).  mode "l1": get_loss_tracking (slam_utils.py:83-113)
+    — mean(opacity * |image_ab*m - gt*m|) with m = boundary mask x grad_mask, and with a gt_depth the rgbd mix
+    alpha * l1_rgb + (1 - alpha) * mean|depth*dm - gt_depth*dm|, dm = (gt_depth > 0.01) * (opacity > 0.95).
+    After step(): .image / .depth / .opacity / .loss of the iteration, .grads = (tau[6] = rho|theta, dab[2])."""
+
+    def __init__(self, sc, cam, bg, T_w2c, make_camera, mode="huber", alpha=0.95):
         self.sc, self.bg, self.make_camera = sc, bg, make_camera
+        self.mode, self.alpha = mode, alpha
+        self.gt_depth = self.grad_mask = None
         self.cam0 = cam
         self.T = T_w2c.clone().to(bg.device)
         self.rot = torch.zeros(3, device=bg.device, requires_grad=True)
@@ -76,9 +84,10 @@ class RefTracker:
         self.gt = None
         self.mask = None
 
-    def set_frame(self, gt_image):
+    def set_frame(self, gt_image, gt_depth=None, grad_mask=None):
         self.gt = gt_image
         self.mask = (gt_image.sum(dim=0) > 0.01).view(1, *gt_image.shape[1:])
+        self.gt_depth, self.grad_mask = gt_depth, grad_mask
 
     def _camera(self):
         view = self.T.transpose(0, 1).contiguous()
@@ -88,10 +97,20 @@ class RefTracker:
         cam = self._camera()
         image, depth, opacity = _RefRasterize.apply(self.rot, self.trans, cam, self.bg, self.sc)
         image_ab = (torch.abs(self.a) + 1e-8) * image + self.b
-        res = opacity * (image_ab * self.mask - self.gt * self.mask)
-        loss = torch.norm(_Huber.apply(res, 0.01))
+        if self.mode == "huber":
+            res = opacity * (image_ab * self.mask - self.gt * self.mask)
+            loss = torch.norm(_Huber.apply(res, 0.01))
+        else:
+            m = self.mask * self.grad_mask if self.grad_mask is not None else self.mask
+            loss = (opacity * torch.abs(image_ab * m - self.gt * m)).mean()
+            if self.gt_depth is not None:
+                dm = (self.gt_depth > 0.01).view(*depth.shape) * (opacity > 0.95).view(*depth.shape)
+                loss = self.alpha * loss + (1 - self.alpha) * torch.abs(depth * dm - self.gt_depth * dm).mean()
         self.opt.zero_grad()
         loss.backward()
+        self.image, self.depth, self.opacity, self.loss = image.detach(), depth.detach(), opacity.detach(), loss.detach()
+        self.grads = (torch.cat([self.trans.grad.view(-1), self.rot.grad.view(-1)]).clone(),
+                      torch.cat([self.a.grad.view(-1), self.b.grad.view(-1)]).clone())
         with torch.no_grad():
             self.opt.step()
             tau = torch.cat([self.trans, self.rot], dim=0)

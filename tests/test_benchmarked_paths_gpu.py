@@ -1,0 +1,167 @@
+"""The paths bench.py times, compared with the REFERENCE at the size they are timed at.
+
+  * PoseTracker(fused=True, fast_math=True / False) — the kernel behind the headline number (blend_track_kernel) — against
+    oracle.ref_tracking.RefTracker: the unmodified reference CUDA rasterizer (oracle/_ref) inside the reference-style
+    tracking iteration (eager Huber/L2 or L1 loss, torch.optim.Adam with its default eps, torch SE3 update;
+    utils/slam_frontend.py:455-630), from the same state, at configs C1 / C2 (mono, Huber) and C3 (rgbd, L1).
+  * MapEngine(overlap=True, fast_math=True) over the 8 bench views of config C4 against oracle.ref_mapping.RefMapper
+    (reference kernels + torch activations + autograd; utils/slam_backend.py:183-247).
+
+Gates (BASELINE.json north_star): image <= 1e-4, loss <= 1e-5, every gradient <= 1e-3 (max-norm AND element-wise,
+tests/util.check_close), pose after 10 iterations <= 1e-4.
+"""
+import pytest
+import torch
+
+from tests import util as U
+
+pytestmark = pytest.mark.gpu
+
+IMG_TOL, LOSS_TOL, GRAD_TOL, POSE_TOL = 1e-4, 1e-5, 1e-3, 1e-4
+
+
+def _tracking_setup(cfg, depth=False):
+    from monogs_b200 import scene as S
+    from oracle import ref_gpu
+    sc, cam = S.make_config(cfg)
+    scd, camd = U.to_dev(sc), U.to_dev(cam)
+    bg = torch.zeros(3, device="cuda")
+    cam_gt = U.to_dev(S.make_camera(cam.W, cam.H, cam.fx, cam.fy, cam.cx, cam.cy, S.se3_exp(torch.tensor(S.GT_TAU)).float()))
+    # target frame: the scene rendered BY THE REFERENCE at the perturbed pose
+    fw = ref_gpu.forward(cam_gt, bg, scd.means3D, scd.opacities, shs=scd.shs, scales=scd.scales, rotations=scd.rotations,
+                         sh_degree=sc.sh_degree)
+    return S, sc, cam, scd, camd, bg, fw["color"].clone(), (fw["depth"].clone() if depth else None)
+
+
+@pytest.mark.parametrize("cfg,fast", [("C1", True), ("C2", True), ("C2", False)])
+def test_fused_tracker_vs_reference_tracker(cfg, fast):
+    from monogs_b200.tracking import PoseTracker
+    from oracle import ref_tracking
+    S, sc, cam, scd, camd, bg, gt, _ = _tracking_setup(cfg)
+    tr = PoseTracker(scd.means3D, scd.opacities, scd.shs, scd.scales, scd.rotations, sc.sh_degree, cam, bg, torch.eye(4),
+                     use_graph=False, fused=True, fast_math=fast)
+    tr.set_frame(gt)
+    rt = ref_tracking.RefTracker(scd, camd, bg, torch.eye(4), S.make_camera)
+    rt.set_frame(gt)
+    tr.step(); rt.step()
+    torch.cuda.synchronize()
+    U.check_close(tr.color, rt.image, IMG_TOL, "image")
+    U.check_close(tr.opacity, rt.opacity, IMG_TOL, "opacity")
+    assert abs(float(tr.loss) - float(rt.loss)) <= LOSS_TOL * abs(float(rt.loss)), (float(tr.loss), float(rt.loss))
+    tau_ref, dab_ref = rt.grads
+    U.check_close(tr.tau, tau_ref, GRAD_TOL, "tau")
+    # d loss / d exposure_a is exactly 0 at a = 0 in both (sign(0)); the b column carries the signal
+    assert U.rel_err(tr.dab, dab_ref) <= GRAD_TOL, (tr.dab, dab_ref)
+    for _ in range(9):
+        tr.step(); rt.step()
+    torch.cuda.synchronize()
+    U.check_close(tr.T, rt.T, POSE_TOL, "T after 10 iterations")
+    assert abs(float(tr.params[7]) - float(rt.b)) <= 1e-3 * abs(float(rt.b)) + 1e-7     # exposure_b after 10 Adam steps
+    assert abs(float(tr.loss) - float(rt.loss)) <= 1e-3 * abs(float(rt.loss))
+    assert not tr.check_capacity()[1]
+
+
+def test_fused_tracker_rgbd_l1_vs_reference_tracker_c3():
+    """Config C3 (500k Gaussians, 1200x680): get_loss_tracking_rgbd (slam_utils.py:102-113), alpha = 0.95."""
+    from monogs_b200.tracking import PoseTracker
+    from monogs_b200 import _lib as L
+    from oracle import ref_tracking
+    S, sc, cam, scd, camd, bg, gt, gt_depth = _tracking_setup("C3", depth=True)
+    tr = PoseTracker(scd.means3D, scd.opacities, scd.shs, scd.scales, scd.rotations, sc.sh_degree, cam, bg, torch.eye(4),
+                     mode=L.LOSS_TRACK_L1, use_depth=True, use_graph=False, fused=True, fast_math=True)
+    tr.set_frame(gt, gt_depth=gt_depth)
+    rt = ref_tracking.RefTracker(scd, camd, bg, torch.eye(4), S.make_camera, mode="l1")
+    rt.set_frame(gt, gt_depth=gt_depth)
+    tr.step(); rt.step()
+    torch.cuda.synchronize()
+    U.check_close(tr.color, rt.image, IMG_TOL, "image")
+    U.check_close(tr.depth, rt.depth, IMG_TOL, "depth")
+    assert abs(float(tr.loss) - float(rt.loss)) <= LOSS_TOL * abs(float(rt.loss)), (float(tr.loss), float(rt.loss))
+    tau_ref, dab_ref = rt.grads
+    U.check_close(tr.tau, tau_ref, GRAD_TOL, "tau")
+    assert U.rel_err(tr.dab, dab_ref) <= GRAD_TOL
+    for _ in range(9):
+        tr.step(); rt.step()
+    torch.cuda.synchronize()
+    U.check_close(tr.T, rt.T, POSE_TOL, "T after 10 iterations")
+
+
+def _mapping_window(P=200_000, window=8, cfg="C2"):
+    """The C4 workload exactly as bench.py's mapping_leg builds it (8 views around the identity pose)."""
+    from monogs_b200 import scene as S
+    from monogs_b200.rasterizer import GaussianRasterizationSettings
+    from oracle import ref_gpu
+    dev = "cuda"
+    sc, cam = S.make_config(cfg, P=P)
+    bg = torch.zeros(3, device=dev)
+    inv_sig = lambda x: torch.log(x / (1 - x))
+    raw = {"xyz": sc.means3D.to(dev), "f_dc": sc.shs[:, :1].to(dev).contiguous(),
+           "opacity": inv_sig(sc.opacities.clamp(1e-4, 1 - 1e-4)).to(dev), "scaling": torch.log(sc.scales).to(dev),
+           "rotation": sc.rotations.to(dev)}
+    lrs = {"xyz": 1.6e-4, "f_dc": 2.5e-3, "opacity": 0.05, "scaling": 1e-3, "rotation": 1e-3}
+    cams, gts, settings = [], [], []
+    for i in range(window):
+        tau = torch.tensor(S.GT_TAU) * (i - window / 2) * 0.5
+        c = U.to_dev(S.make_camera(cam.W, cam.H, cam.fx, cam.fy, cam.cx, cam.cy, S.se3_exp(tau).float()))
+        with torch.no_grad():
+            fw = ref_gpu.forward(c, bg, raw["xyz"], torch.sigmoid(raw["opacity"]), shs=raw["f_dc"], scales=torch.exp(raw["scaling"]),
+                                 rotations=torch.nn.functional.normalize(raw["rotation"]), sh_degree=0)
+        cams.append(c)
+        gts.append((fw["color"] * 0.9 + 0.05).contiguous())
+        settings.append(GaussianRasterizationSettings(c.H, c.W, c.tanfovx, c.tanfovy, bg, 1.0, c.viewmatrix, c.projmatrix,
+                                                      c.projmatrix_raw, 0, c.campos, False, False))
+    return sc, cam, bg, raw, lrs, cams, gts, settings
+
+
+@pytest.mark.parametrize("overlap,fast", [(True, True), (False, False)])
+def test_map_engine_vs_reference_mapper_c4(overlap, fast):
+    """One iteration's raw-parameter gradients of the benchmarked mapping engine at C4 (200k Gaussians, 640x480, the 8
+    bench views, four views in flight with atomic accumulation, ex2.approx exponent) against the reference kernels under
+    torch activations + autograd."""
+    from monogs_b200.mapping import MapEngine, MapView
+    from oracle import ref_mapping
+    sc, cam, bg, raw, lrs, cams, gts, settings = _mapping_window()
+    eng = MapEngine({k: v.clone() for k, v in raw.items()}, lrs, sh_degree=0, W=cam.W, H=cam.H, capacity_headroom=1.5,
+                    overlap=overlap, fast_math=fast)
+    out = eng.backward_only([MapView(rs, gt) for rs, gt in zip(settings, gts)])
+    torch.cuda.synchronize()
+    rm = ref_mapping.RefMapper(raw, lrs, cams, gts, bg)
+    loss_ref, g_ref, fws = rm.loss_and_grads()
+    torch.cuda.synchronize()
+    assert not eng.check_capacity()[1]
+    assert abs(float(eng.loss_total) - float(loss_ref)) <= LOSS_TOL * abs(float(loss_ref)), (float(eng.loss_total), float(loss_ref))
+    for k in ("xyz", "f_dc", "opacity", "scaling", "rotation"):
+        U.check_close(eng.grads[k], g_ref[k].view_as(eng.grads[k]), GRAD_TOL, k)
+    P = raw["xyz"].size(0)
+    touched_mismatch = 0
+    for i, fw in enumerate(fws):
+        assert torch.equal(out[i].radii, fw["radii"]), f"radii of view {i}"
+        touched_mismatch += int((out[i].n_touched != fw["n_touched"]).sum())
+    # n_touched counts pixels with T(1 - alpha) > 0.5: with the ex2.approx exponent alpha moves by ~4e-7 relative, so a
+    # borderline pixel may flip; exact with the reference's expf
+    print(f"n_touched entries that differ over 8 views: {touched_mismatch} of {8 * P}")
+    assert touched_mismatch <= (8 * P // 10000 if fast else 0)
+
+
+def test_map_engine_three_steps_vs_reference_mapper_c4():
+    """Three full iterations (gradients + fused Adam, eps = 1e-15) at C4: parameters stay within 1e-4 of the reference
+    iteration (torch.optim.Adam) — the optimiser sees the same gradients, moments and step sizes."""
+    from monogs_b200.mapping import MapEngine, MapView
+    from oracle import ref_mapping
+    sc, cam, bg, raw, lrs, cams, gts, settings = _mapping_window()
+    eng = MapEngine({k: v.clone() for k, v in raw.items()}, lrs, sh_degree=0, W=cam.W, H=cam.H, capacity_headroom=1.5)
+    views = [MapView(rs, gt) for rs, gt in zip(settings, gts)]
+    rm = ref_mapping.RefMapper(raw, lrs, cams, gts, bg)
+    for _ in range(3):
+        loss, _ = eng.step(views)
+        loss_ref = rm.step()
+    torch.cuda.synchronize()
+    assert abs(float(loss) - float(loss_ref)) <= 1e-4 * abs(float(loss_ref))
+    for k in ("xyz", "f_dc", "opacity", "scaling", "rotation"):
+        # Adam's first steps move every parameter by ~lr * sign(g): compare the UPDATE, not the parameter
+        d_mine, d_ref = eng.params[k] - raw[k], rm.p[k].detach() - raw[k]
+        # (an entry whose gradient is pure rounding noise, |g| ~ 1e-12, may step the other way: Adam normalises it to +-lr;
+        # such entries are counted, not compared)
+        frac = float(((d_mine - d_ref.view_as(d_mine)).abs() > 1e-3 * d_ref.abs().max()).float().mean())
+        print(f"{k}: fraction of entries whose 3-step update differs by more than 1e-3 of the largest update: {frac:.2e}")
+        assert frac <= 1e-3, f"{k}: {frac:.2e} of the entries moved differently"

@@ -51,3 +51,22 @@ def rel_err(a, b):
     """max |a-b| / max |b| — the 'relative' of BASELINE.json's 1e-4 / 1e-3 gates."""
     a, b = a.detach().double().cpu(), b.detach().double().cpu()
     return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def elem_err(a, b, rtol):
+    """Element-wise companion of rel_err: the largest |a-b| / (rtol*|b| + atol) with atol = rtol * max|b| * 1e-2, i.e.
+    torch.allclose(a, b, rtol, atol) holds iff the value is <= 1.  rel_err alone (a max-norm ratio) cannot see a wrong
+    value on an element that is small next to the largest one; this gate can, down to 1 % of the largest magnitude."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    atol = rtol * float(b.abs().max()) * 1e-2
+    if atol == 0.0:
+        return 0.0 if float((a - b).abs().max()) == 0.0 else float("inf")
+    return float(((a - b).abs() / (rtol * b.abs() + atol)).max())
+
+
+def check_close(a, b, tol, name=""):
+    """Both gates: max-norm relative error <= tol (BASELINE.json's 1e-4 / 1e-3) and element-wise allclose."""
+    r = rel_err(a, b)
+    assert r <= tol, f"{name}: max-norm relative error {r:.3e} > {tol}"
+    e = elem_err(a, b, tol)
+    assert e <= 1.0, f"{name}: element-wise gate violated by a factor {e:.3f} (rtol {tol}, atol = rtol * max|b| * 1e-2)"
