@@ -415,7 +415,7 @@ def e2e_dropin_leg(cfg, dev, steps, warmup, gt_host):
     T = torch.eye(4, device=dev)
     proj = cam.projmatrix_raw.to(dev)
     theta = torch.zeros(3, device=dev, requires_grad=True); rho = torch.zeros(3, device=dev, requires_grad=True)
-    a = torch.zeros(1, device=dev, requires_grad=True); b = torch.zeros(1, device=dev, requires_grad=True)
+    a = torch.ones(1, device=dev, requires_grad=True); b = torch.zeros(1, device=dev, requires_grad=True)   # camera_utils.py:56-61
     opt = ops.FusedAdam([{"params": [theta], "lr": 3e-3}, {"params": [rho], "lr": 1e-3}, {"params": [a], "lr": 2e-2},
                          {"params": [b], "lr": 2e-2}], eps=1e-15)
     gt_dev = torch.empty(3, cam.H, cam.W, device=dev)

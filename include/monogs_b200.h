@@ -243,9 +243,41 @@ typedef struct mgs_track_args {
   int32_t* converged;  /* i32[1], optional */
   void* workspace; size_t workspace_bytes; int64_t R_cap;
   void* scratch; size_t scratch_bytes;
+  /* optional.  lm_state: device f32[64], the tracker's cross-iteration record (layout below); with it the Huber
+   * iteration also keeps the reference's best_viewpoint_params (utils/slam_frontend.py:523-531).  status_out: pinned host
+   * i32[6], receives the workspace status words (see mgs_raster_status_async) as they stood when the call was enqueued,
+   * i.e. of the previous iteration — an overflow watch that costs one 24-byte copy node and no host wait. */
+  float* lm_state;
+  int32_t* status_out;
 } mgs_track_args;
 size_t mgs_track_scratch_bytes(int32_t P, int32_t W, int32_t H);
 int mgs_track_iteration(const mgs_track_args* args, void* stream);
+
+/* ---- one SECOND-ORDER tracking iteration, fused (the sketched Gauss-Newton / Levenberg-Marquardt phase of
+ *      FrontEnd.tracking, utils/slam_frontend.py:455-720 with in_second_order; gen_forward_sketch_args :269-338;
+ *      ApplyExposure, utils/slam_utils.py:115-185; the `stack_dim` calls of _C.rasterize_gaussians_backward_sketch_jacobian,
+ *      diff_gaussian_rasterization/__init__.py:216-253).  In the reference's order: apply the step left pending by the
+ *      previous iteration (TempCamera.step + update_pose), render, scalar loss ||r||_1, adapt lambda, form the sketched
+ *      Jacobian SJ[stack*sketch, 8] (rho, theta, exposure a, b) and residual Sf[stack*sketch] of
+ *      f = rand_weights * sum_c Huber(r_c) / (npix / (stack*sketch)), solve lstsq([SJ; sqrt(lambda) I], -[Sf; 0]) and leave x
+ *      pending.  One pass over the tile lists builds every pixel's row contribution (the per-pixel tangent is independent
+ *      of the routing), one reduction routes them for all stacks: no [P, sketch, ...] buffers, no per-stack backward.
+ *      Mono (rgb) objective and sh_degree 0 only, as the reference's own per-pixel rgbd loss raises NotImplementedError
+ *      (slam_utils.py:221).  No host synchronisation; CUDA-graph capturable.
+ *      lm_state layout (f32[64]): [0] lambda (set by the caller before the first iteration), [1] previous scalar loss,
+ *      [2] have-previous flag, [3] step-pending flag, [4..11] pending step x (rho, theta, a, b), [12] best scalar loss,
+ *      [13..28] best T_w2c, [29] best a, [30] best b, [31] converged (|x| < converged_threshold), [32] iterations done,
+ *      [33] scalar loss of the last iteration, [34] |x|, [35] have-best flag.  Zero it (except [0]) to start a frame. ---- */
+typedef struct mgs_track2_args {
+  mgs_track_args t;              /* loss_mode / use_depth / lr / Adam moments / tau / dab are not used; t.loss receives ||r||_1 */
+  int32_t n_stacks, sketch_dim;  /* stack_dim, sketch_dim (<= 64) */
+  const int32_t* sketch_indices; /* device i32[n_stacks,H,W]: row of the pixel in that stack, -1 = not in the stack */
+  const float* rand_weights;     /* device f32[H,W], +-1 */
+  float* rows;                   /* out, device f32[n_stacks*sketch_dim, 9]: columns 0..7 = SJ, column 8 = Sf */
+  float* lm_state;               /* device f32[64]; null = t.lm_state */
+  float min_lambda, max_lambda, increase_factor, decrease_factor, converged_threshold;
+} mgs_track2_args;
+int mgs_track_second_order(const mgs_track2_args* args, void* stream);
 
 /* ---- keyframe-window mapping iteration on the RAW Gaussian parameters (SURVEY.md §8 rows f1 + e).
  *      Replaces, per iteration of BackEnd.map (utils/slam_backend.py:157-333): the per-render parameter activations and

@@ -59,6 +59,16 @@ class MgsTrackArgs(C.Structure):
         ("loss", C.c_void_p), ("tau", C.c_void_p), ("dab", C.c_void_p), ("converged", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("R_cap", C.c_int64),
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
+        ("lm_state", C.c_void_p), ("status_out", C.c_void_p),
+    ]
+
+
+class MgsTrack2Args(C.Structure):
+    _fields_ = [
+        ("t", MgsTrackArgs), ("n_stacks", C.c_int32), ("sketch_dim", C.c_int32),
+        ("sketch_indices", C.c_void_p), ("rand_weights", C.c_void_p), ("rows", C.c_void_p), ("lm_state", C.c_void_p),
+        ("min_lambda", C.c_float), ("max_lambda", C.c_float), ("increase_factor", C.c_float), ("decrease_factor", C.c_float),
+        ("converged_threshold", C.c_float),
     ]
 
 
@@ -154,6 +164,7 @@ SIGNATURES = {
     "mgs_knn_dist2": (C.c_int, [_I32, _P, _P, _P, _SZ, _P]),
     "mgs_track_scratch_bytes": (_SZ, [_I32, _I32, _I32]),
     "mgs_track_iteration": (C.c_int, [C.POINTER(MgsTrackArgs), _P]),
+    "mgs_track_second_order": (C.c_int, [C.POINTER(MgsTrack2Args), _P]),
     "mgs_pose_update": (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _F, _P]),
     "mgs_median_scratch_bytes": (_SZ, []),
     "mgs_median": (C.c_int, [_P, _I64, _P, _P, _SZ, _P]),

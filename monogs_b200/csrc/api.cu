@@ -11,8 +11,8 @@ int prof_report(char* buf, size_t n);
 int launch_backward_full(const BackwardArgs& a, cudaStream_t s);
 int launch_backward_pose(const BackwardArgs& a, cudaStream_t s);
 size_t backward_pose_scratch_bytes(int P, int W, int H);
-int launch_sketch_reduce(const float* tau_image, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,
-                         float* sketch_dtau, cudaStream_t s);
+int launch_sketch_reduce(const float* rows, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,
+                         float* out, cudaStream_t s, int nv);
 }
 
 static int check_view(const mgs_view* v, bool need_raw) {
@@ -264,7 +264,7 @@ int mgs_sketch_reduce(const float* tau_image, int32_t H, int32_t W, int32_t n_st
     set_error("sketch_reduce: bad arguments"); return MGS_EINVAL;
   }
   if (sketch_dim > 64) { set_error("sketch_dim must be <= 64 (__init__.py:249)"); return MGS_EINVAL; }
-  return launch_sketch_reduce(tau_image, H, W, n_stacks, sketch_dim, sketch_indices, sketch_dtau, (cudaStream_t)stream);
+  return launch_sketch_reduce(tau_image, H, W, n_stacks, sketch_dim, sketch_indices, sketch_dtau, (cudaStream_t)stream, 6);
 }
 
 }  // extern "C"

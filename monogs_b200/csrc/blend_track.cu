@@ -35,13 +35,17 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // Pipeline per tile: records of batch i+2 in flight by bulk copy (TMA), pose Jacobians of batch i+1 gathered by cp.async
 // (their ids come from the records of i+1, already landed), batch i being blended: one CTA barrier (the early-out
 // vote) per batch and no load latency on the blend path.
-template <bool HAS_DEPTH, bool FAST>   // FAST: ex2.approx exponent, n_touched not produced
+// SKETCH: the epilogue evaluates the second-order (sketched Gauss-Newton) objective instead of the first-order loss and
+// writes this pixel's Jacobian row contribution (tau[6], d/d exposure_a, d/d exposure_b, f) to sk_image[9][H][W]; the rows
+// are formed afterwards by sketch_reduce_kernel, whatever the pixel -> row routing of the stacks (pose_backward.cu).
+template <bool HAS_DEPTH, bool FAST, bool SKETCH>   // FAST: ex2.approx exponent, n_touched not produced
 __global__ void __launch_bounds__(256, 3)
 blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __restrict__ tile_order, const uint2* __restrict__ ranges,
                    const SplatRec* __restrict__ recs, const float* __restrict__ jac, const float* __restrict__ bg,
                    float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
                    int32_t* __restrict__ n_touched, const LossK lk, const float loss_grad_scale,
-                   double* __restrict__ loss_partials, float* __restrict__ tau_sum) {
+                   double* __restrict__ loss_partials, float* __restrict__ tau_sum,
+                   const float* __restrict__ sk_weights, const float sk_scale, float* __restrict__ sk_image) {
   extern __shared__ __align__(128) unsigned char trk_smem[];
   SplatRec (*stage)[TRK_BATCH] = reinterpret_cast<SplatRec (*)[TRK_BATCH]>(trk_smem);
   float (*jstage)[TRK_BATCH * TRK_NF] =
@@ -206,8 +210,12 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     out_color[2 * plane + pix] = img[2];
     out_depth[pix] = D;
     out_opacity[pix] = 1 - T;
-    float gi[3], gd;
-    loss_pixel<true, true>(lk, (int)pix, img, D, 1 - T, loss_grad_scale, acc, gi, gd);
+    float gi[3], gd = 0.f, sk_da = 0.f, sk_db = 0.f, sk_f = 0.f;
+    if (SKETCH) {
+      float l1;
+      sk_f = sketch_pixel(lk, (int)pix, img, 1 - T, sk_weights[pix] * sk_scale, gi, sk_da, sk_db, l1);
+      acc[0] = l1;
+    } else loss_pixel<true, true>(lk, (int)pix, img, D, 1 - T, loss_grad_scale, acc, gi, gd);
     float E[6], A0[6], A1[6], A2[6], Ad[6];
 #pragma unroll
     for (int m = 0; m < 3; m++) {
@@ -224,8 +232,16 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
       tau[k] = t;
     }
     if (HAS_DEPTH) { tau[2] = fmaf(gd, F0, tau[2]); tau[3] = fmaf(gd, F1, tau[3]); tau[4] = fmaf(gd, F2, tau[4]); }
+    if (SKETCH) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) sk_image[k * plane + pix] = tau[k];
+      sk_image[6 * plane + pix] = sk_da;
+      sk_image[7 * plane + pix] = sk_db;
+      sk_image[8 * plane + pix] = sk_f;
+    }
   }
   loss_block_reduce(acc, loss_partials + (size_t)tile * 4);
+  if (SKETCH) return;
 #pragma unroll
   for (int k = 0; k < 6; k++) {
     float x = tau[k];
@@ -242,10 +258,11 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
   }
 }
 
-// tau_sum must be zeroed by the caller; jac holds the 6-column per-Gaussian maps (PoseJac<6>)
+// tau_sum must be zeroed by the caller; jac holds the 6-column per-Gaussian maps (PoseJac<6>).  sk_image != nullptr selects
+// the second-order epilogue (mono only): sk_weights f32[H,W] (+-1), sk_scale = stack_dim * sketch_dim / npix.
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
-                       float* tau_sum, cudaStream_t s) {
+                       float* tau_sum, cudaStream_t s, const float* sk_weights, float sk_scale, float* sk_image) {
   const int tiles = v.gx * v.gy;
   // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute
   static bool attr_set[64] = {};
@@ -253,21 +270,27 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
   MGS_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) { set_error("blend_track: device ordinal %d out of range", dev); return MGS_EINVAL; }
   if (!attr_set[dev]) {
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
     attr_set[dev] = true;
   }
+  if (sk_image != nullptr && (has_depth || sk_weights == nullptr)) { set_error("blend_track: the sketched epilogue is mono only and needs rand_weights"); return MGS_EINVAL; }
 #define MGS_TRK_ARGS v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color,   \
-      out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum
-  prof_begin("blend_track", s);
-  if (has_depth) {
-    if (fl.fast) blend_track_kernel<true, true><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
-    else blend_track_kernel<true, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+      out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum, sk_weights, sk_scale, sk_image
+  prof_begin(sk_image ? "blend_track_sketch" : "blend_track", s);
+  if (sk_image != nullptr) {
+    if (fl.fast) blend_track_kernel<false, true, true><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+    else blend_track_kernel<false, false, true><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+  } else if (has_depth) {
+    if (fl.fast) blend_track_kernel<true, true, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+    else blend_track_kernel<true, false, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
   } else {
-    if (fl.fast) blend_track_kernel<false, true><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
-    else blend_track_kernel<false, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+    if (fl.fast) blend_track_kernel<false, true, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
+    else blend_track_kernel<false, false, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
   }
   prof_end(s);
 #undef MGS_TRK_ARGS

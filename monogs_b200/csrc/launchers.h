@@ -22,7 +22,8 @@ int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float*
 // single-pass tracking blend (blend_track.cu): forward + loss + pose tangent; SH degree 0 / 6-column Jacobians only
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
-                       float* tau_sum, cudaStream_t s);
+                       float* tau_sum, cudaStream_t s, const float* sk_weights = nullptr, float sk_scale = 0.f,
+                       float* sk_image = nullptr);
 
 struct BackwardArgs {
   ViewConst v; int P; uint32_t grad_mask;

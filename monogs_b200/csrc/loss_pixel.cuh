@@ -41,7 +41,7 @@ __device__ __forceinline__ void loss_pixel(const LossK& k, const int p, const fl
       float h, dh;
       if (ar < k.delta) { h = r; dh = 1.f; }
       else { const float sq = sqrtf(2.f * k.delta * ar - k.delta * k.delta); h = sq * sgn(r); dh = k.delta / sq; }
-      if (REDUCE) acc[0] += h * h;
+      if (REDUCE) { acc[0] += h * h; acc[3] += ar; }   // [3]: ||r||_1, the scalar the reference keeps for its best-pose test
       dr = h * dh;
     } else {
       if (REDUCE) acc[0] += fabsf(r);
@@ -63,6 +63,43 @@ __device__ __forceinline__ void loss_pixel(const LossK& k, const int p, const fl
     if (REDUCE) acc[3] += fabsf(rd);
     if (WRITE_GRADS) g_depth = k.scale * (1.f - k.alpha) / (float)k.npix * sgn(rd) * dm;
   }
+}
+
+// One pixel of the SECOND-ORDER (sketched Gauss-Newton) tracking objective, MonoGS utils/slam_frontend.py:637-665 with
+// ApplyExposure.backward (utils/slam_utils.py:132-185):
+//     r_c = opacity * (image_ab_c * m - gt_c * m),  h_c = Huber_delta(r_c),  f = w * sum_c h_c / (npix / d_total)
+// where w = rand_weights[p] (+-1) and d_total = stack_dim * sketch_dim.  d f / d image_ab_c = g_ab_c; the gradient that
+// reaches the rasterizer is |a| * g_ab_c — the reference's ApplyExposure.backward multiplies by torch.abs(exposure_a)
+// WITHOUT the eps of the forward — and its sketched exposure columns are sum_c g_ab_c * image_c (no sign(a) factor) and
+// sum_c g_ab_c.  Quirks reproduced, not fixed.
+// Returns f; g_img[3] = gradient for the rasterizer; da, db = this pixel's exposure columns; l1 = sum_c |r_c| (the
+// un-Hubered scalar the LM accept test uses, slam_frontend.py:510).
+__device__ __forceinline__ float sketch_pixel(const LossK& k, const int p, const float (&img)[3], const float op,
+                                              const float wscale /* w * d_total / npix */, float (&g_img)[3],
+                                              float& da, float& db, float& l1) {
+  const float a_raw = k.a[0], eb = k.b[0];
+  const float aa = fabsf(a_raw), ea = aa + k.eps;
+  const float gt3[3] = {k.gt[p], k.gt[k.npix + p], k.gt[2 * k.npix + p]};
+  float m = (gt3[0] + gt3[1] + gt3[2]) > k.thr ? 1.f : 0.f;
+  if (k.mask) m *= k.mask[p];
+  float f = 0.f;
+  da = 0.f; db = 0.f; l1 = 0.f;
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    const float iab = ea * img[c] + eb;
+    const float r = op * (iab * m - gt3[c] * m);
+    const float ar = fabsf(r);
+    float h, dh;
+    if (ar < k.delta) { h = r; dh = 1.f; }
+    else { const float sq = sqrtf(2.f * k.delta * ar - k.delta * k.delta); h = sq * sgn(r); dh = k.delta / sq; }
+    f += h;
+    l1 += ar;
+    const float g_ab = wscale * dh * op * m;
+    g_img[c] = aa * g_ab;
+    da += g_ab * img[c];
+    db += g_ab;
+  }
+  return f * wscale;
 }
 
 // block-level reduction of acc[4] into one double4 slot (deterministic: shuffle tree -> shared -> fixed order)

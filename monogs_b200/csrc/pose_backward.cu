@@ -186,29 +186,31 @@ blend_backward_pose_kernel(const int W, const int H, const int gx, const uint2* 
   }
 }
 
-// SJ[j, i, :] = sum over pixels with sketch_indices[j, pix] == i of tau_image[:, pix]
+// SJ[j, i, :] = sum over pixels with sketch_indices[j, pix] == i of rows[:, pix]   (NV values per pixel: 6 = the pose
+// tangent image of the drop-in sketch backward; 9 = tangent + the two exposure columns + f of the fused second-order step)
+template <int NV>
 __global__ void __launch_bounds__(256)
-sketch_reduce_kernel(const float* __restrict__ tau_image, const int npix, const int d,
-                     const int32_t* __restrict__ sketch_indices, float* __restrict__ sketch_dtau) {
-  extern __shared__ float acc[];  // [d][6]
+sketch_reduce_kernel(const float* __restrict__ rows, const int npix, const int d,
+                     const int32_t* __restrict__ sketch_indices, float* __restrict__ out) {
+  extern __shared__ float acc[];  // [d][NV]
   const int stack = blockIdx.y;
-  for (int k = threadIdx.x; k < d * 6; k += blockDim.x) acc[k] = 0.f;
+  for (int k = threadIdx.x; k < d * NV; k += blockDim.x) acc[k] = 0.f;
   __syncthreads();
   const int32_t* idx = sketch_indices + (size_t)stack * npix;
   for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < npix; p += gridDim.x * blockDim.x) {
     const int row = idx[p];
     if (row < 0 || row >= d) continue;
 #pragma unroll
-    for (int k = 0; k < 6; k++) {
-      const float x = tau_image[(size_t)k * npix + p];
-      if (x != 0.f) atomicAdd(&acc[row * 6 + k], x);
+    for (int k = 0; k < NV; k++) {
+      const float x = rows[(size_t)k * npix + p];
+      if (x != 0.f) atomicAdd(&acc[row * NV + k], x);
     }
   }
   __syncthreads();
-  float* out = sketch_dtau + (size_t)stack * d * 6;
-  for (int k = threadIdx.x; k < d * 6; k += blockDim.x) {
+  float* o = out + (size_t)stack * d * NV;
+  for (int k = threadIdx.x; k < d * NV; k += blockDim.x) {
     const float x = acc[k];
-    if (x != 0.f) atomicAdd(&out[k], x);
+    if (x != 0.f) atomicAdd(&o[k], x);
   }
 }
 
@@ -264,12 +266,17 @@ int launch_backward_pose(const BackwardArgs& a, cudaStream_t s) {
   return launch_blend_backward_pose(a, jac, with_color, s);
 }
 
-int launch_sketch_reduce(const float* tau_image, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,
-                         float* sketch_dtau, cudaStream_t s) {
-  MGS_CUDA_TRY(cudaMemsetAsync(sketch_dtau, 0, (size_t)n_stacks * d * 6 * sizeof(float), s));
+int launch_sketch_reduce(const float* rows, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,
+                         float* out, cudaStream_t s, int nv) {
+  MGS_CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)n_stacks * d * nv * sizeof(float), s));
   const int npix = W * H;
-  dim3 grid(min((npix + 255) / 256, 148 * 2), n_stacks);
-  sketch_reduce_kernel<<<grid, 256, (size_t)d * 6 * sizeof(float), s>>>(tau_image, npix, d, sketch_indices, sketch_dtau);
+  // every CTA ends with d * nv global atomics, so the grid stays small: ~4 CTAs per SM over all stacks
+  const int per_stack = max(1, min((npix + 255) / 256, (148 * 4 + n_stacks - 1) / n_stacks));
+  dim3 grid(per_stack, n_stacks);
+  prof_begin("sketch_reduce", s);
+  if (nv == 9) sketch_reduce_kernel<9><<<grid, 256, (size_t)d * 9 * sizeof(float), s>>>(rows, npix, d, sketch_indices, out);
+  else sketch_reduce_kernel<6><<<grid, 256, (size_t)d * 6 * sizeof(float), s>>>(rows, npix, d, sketch_indices, out);
+  prof_end(s);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

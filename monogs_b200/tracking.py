@@ -46,6 +46,7 @@ class PoseTracker:
         assert self.view.viewmatrix == self.viewmatrix.data_ptr() and self.view.campos == self.viewmatrix.data_ptr()
         # optimiser state: params = [rho(3), theta(3), a(1), b(1)], grads = [tau(6), dab(2)]
         self.params = torch.zeros(8, **f)
+        self.params[6] = 1.0            # exposure_a starts at 1 (utils/camera_utils.py:56-58)
         self.tau = torch.zeros(6, **f)
         self.dab = torch.zeros(2, **f)
         self.exp_avg, self.exp_avg_sq = torch.zeros(8, **f), torch.zeros(8, **f)
@@ -75,6 +76,11 @@ class PoseTracker:
         self._status = torch.zeros(8, dtype=torch.int32).pin_memory()
         self._status_ev = torch.cuda.Event()
         self._status_pending = False
+        # cross-iteration record of the tracker on the device (include/monogs_b200.h, lm_state): LM damping, pending
+        # second-order step, best pose by scalar loss
+        self.lm_state = torch.zeros(64, **f)
+        self._sk = None             # second-order sketch buffers (set_sketch)
+        self._graph2 = None
         self._host_bind = None
         self.overflow_frames = 0     # frames during which at least one iteration dropped instances (see poll_capacity)
         self._size_workspace()
@@ -133,6 +139,7 @@ class PoseTracker:
         t.loss, t.tau, t.dab, t.converged = self.loss.data_ptr(), self.tau.data_ptr(), self.dab.data_ptr(), self.converged.data_ptr()
         t.workspace, t.workspace_bytes, t.R_cap = self.ws.data_ptr(), self.ws.numel(), self.R_cap
         t.scratch, t.scratch_bytes = self.track_scratch.data_ptr(), self.track_scratch.numel()
+        t.lm_state, t.status_out = self.lm_state.data_ptr(), None
         return t
 
     def _enqueue(self):
@@ -196,11 +203,11 @@ class PoseTracker:
             self._status_pending = True
         return regrown
 
-    def set_frame(self, gt_image, gt_depth=None, grad_mask=None, non_blocking=True, exposure=(0.0, 0.0)):
+    def set_frame(self, gt_image, gt_depth=None, grad_mask=None, non_blocking=True, exposure=(1.0, 0.0)):
         """New target frame (host pinned or device tensors); resets the per-frame optimiser state like the
         reference, which builds a fresh Adam per frame (slam_frontend.py:364-392,453) and a fresh Camera whose exposure
-        starts at a = b = 0 (utils/camera_utils.py:56-61); only the pose is carried over.  exposure=None keeps the
-        previous frame's (a, b)."""
+        starts at a = 1, b = 0 (utils/camera_utils.py:55-61: image_ab = (|a| + 1e-8) * image + b); only the pose is
+        carried over.  exposure=None keeps the previous frame's (a, b)."""
         self.poll_capacity()
         self.gt_image.copy_(gt_image, non_blocking=non_blocking)
         if self.gt_depth is not None and gt_depth is not None:
@@ -211,6 +218,7 @@ class PoseTracker:
                 self.graph = None
             self.grad_mask.copy_(grad_mask, non_blocking=non_blocking)
         self.exp_avg.zero_(); self.exp_avg_sq.zero_(); self.params[:6].zero_(); self.step_dev.zero_()
+        self.lm_state.zero_()
         if exposure is not None:
             self.params[6].fill_(float(exposure[0])); self.params[7].fill_(float(exposure[1]))
 
@@ -226,6 +234,98 @@ class PoseTracker:
             with torch.cuda.graph(self.graph):
                 self._enqueue()
         self.graph.replay()
+
+    # ---- second-order (sketched Gauss-Newton / LM) phase: utils/slam_frontend.py:455-720, in_second_order ----------------
+    LM_FIELDS = dict(lam=0, prev_scalar=1, have_prev=2, pending=3, x=slice(4, 12), best_scalar=12, best_T=slice(13, 29),
+                     best_a=29, best_b=30, converged=31, iters=32, scalar=33, step_norm=34, have_best=35)
+
+    @staticmethod
+    def gen_sketch_args(H, W, stack_dim=16, sketch_dim=64, device="cuda", generator=None):
+        """One repeat of FrontEnd.gen_forward_sketch_args (utils/slam_frontend.py:269-338): a random permutation of the
+        pixels cut into stack_dim x sketch_dim buckets of m // (stack_dim*sketch_dim) pixels -> sketch_indices
+        i32[stack,H,W] (-1 = pixel not in that stack), and Rademacher rand_weights f32[H,W]."""
+        m, d = H * W, stack_dim * sketch_dim
+        chunk = m // d
+        perm = torch.randperm(m, device=device, generator=generator)[:chunk * d]
+        idx = torch.full((stack_dim * m,), -1, dtype=torch.int32, device=device)
+        bucket = torch.arange(d, device=device).repeat_interleave(chunk)          # bucket of the k-th drawn pixel
+        idx[(bucket // sketch_dim) * m + perm] = (bucket % sketch_dim).to(torch.int32)
+        w = torch.randint(0, 2, (H, W), device=device, generator=generator, dtype=torch.float32) * 2 - 1
+        return idx.view(stack_dim, H, W), w
+
+    def begin_second_order(self, initial_lambda=1e-3, use_first_order_best=True):
+        """Switch of FrontEnd.tracking to the second-order phase (:468-473): optionally go back to the best first-order
+        pose / exposure (best_viewpoint_params.assign), reset the LM record, lambda = initial_lambda."""
+        st = self.lm_state
+        if use_first_order_best:
+            have = st[35:36]                     # device-side select, no host read
+            Tb = st[13:29].view(4, 4)
+            self.T.copy_(torch.where(have.bool(), Tb, self.T))
+            self.params[6:7].copy_(torch.where(have.bool(), st[29:30], self.params[6:7]))
+            self.params[7:8].copy_(torch.where(have.bool(), st[30:31], self.params[7:8]))
+            self.params[:6].zero_()
+            self.viewmatrix.copy_(self.T.t())
+            self.projmatrix.copy_(self.viewmatrix @ self.proj_raw)
+        st[0] = float(initial_lambda)
+        st[1:12].zero_(); st[31:35].zero_()
+
+    def set_sketch(self, sketch_indices, rand_weights, sketch_dim):
+        """This iteration's sketch (device tensors; copied into fixed buffers so that the captured graph stays valid)."""
+        idx = sketch_indices.to(torch.int32)
+        if self._sk is None or self._sk[0].shape != idx.shape or self._sk[3] != sketch_dim:
+            n_stacks = idx.shape[0]
+            self._sk = (torch.empty_like(idx).contiguous(), torch.empty(self.H, self.W, device=self.dev),
+                        torch.zeros(n_stacks * sketch_dim, 9, device=self.dev), sketch_dim)
+            self._graph2 = None
+        self._sk[0].copy_(idx, non_blocking=True)
+        self._sk[1].copy_(rand_weights, non_blocking=True)
+
+    def _enqueue_second_order(self, min_lambda, max_lambda, increase_factor, decrease_factor, converged_threshold):
+        a = L.MgsTrack2Args()
+        a.t = self._track_args()
+        idx, w, rows, d = self._sk
+        a.n_stacks, a.sketch_dim = idx.shape[0], d
+        a.sketch_indices, a.rand_weights, a.rows = idx.data_ptr(), w.data_ptr(), rows.data_ptr()
+        a.lm_state = self.lm_state.data_ptr()
+        a.min_lambda, a.max_lambda, a.increase_factor, a.decrease_factor = min_lambda, max_lambda, increase_factor, decrease_factor
+        a.converged_threshold = converged_threshold
+        L.check(self.lib.mgs_track_second_order(C.byref(a), _stream(self.dev)), "mgs_track_second_order")
+
+    def second_order_step(self, min_lambda=1e-6, max_lambda=1e7, increase_factor=5.0, decrease_factor=5.0,
+                          converged_threshold=1e-5):
+        """One second-order iteration with the sketch given by set_sketch(): apply the pending step, render, scalar loss,
+        lambda, SJ / Sf, damped solve, new pending step (defaults: configs/mono/tum/base_config.yaml RGN.second_order).
+        Captured once into a CUDA graph and replayed.  Results on the device: self.sketch_rows [stack*sketch, 9] (SJ | Sf),
+        self.lm_state (see LM_FIELDS), self.loss (the scalar ||r||_1)."""
+        assert self._sk is not None, "set_sketch() first"
+        args = (min_lambda, max_lambda, increase_factor, decrease_factor, converged_threshold)
+        if not self.use_graph:
+            self._enqueue_second_order(*args)
+            return
+        if self._graph2 is None or self._graph2[1] != args or self._graph2[2] is not self.ws:
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._enqueue_second_order(*args)
+            self._graph2 = (g, args, self.ws)
+        self._graph2[0].replay()
+
+    @property
+    def sketch_rows(self):
+        return self._sk[2]
+
+    def finish_second_order(self, use_best_loss=True):
+        """End of the frame (slam_frontend.py:741-790): the last pending step is NOT applied by the reference's loop; with
+        use_best_loss the pose / exposure of the best scalar loss seen in either phase are restored."""
+        if use_best_loss:
+            st = self.lm_state
+            have = st[35:36].bool()
+            self.T.copy_(torch.where(have, st[13:29].view(4, 4), self.T))
+            self.params[6:7].copy_(torch.where(have, st[29:30], self.params[6:7]))
+            self.params[7:8].copy_(torch.where(have, st[30:31], self.params[7:8]))
+            self.viewmatrix.copy_(self.T.t())
+            self.projmatrix.copy_(self.viewmatrix @ self.proj_raw)
+        self.lm_state[3] = 0.0
 
     def bind_host(self, gt_host, loss_host, tau_host):
         """Host-resident frame in, loss + pose tangent out, one graph launch per iteration (step_host()).

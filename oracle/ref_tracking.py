@@ -77,7 +77,7 @@ class RefTracker:
         self.T = T_w2c.clone().to(bg.device)
         self.rot = torch.zeros(3, device=bg.device, requires_grad=True)
         self.trans = torch.zeros(3, device=bg.device, requires_grad=True)
-        self.a = torch.zeros(1, device=bg.device, requires_grad=True)
+        self.a = torch.ones(1, device=bg.device, requires_grad=True)      # utils/camera_utils.py:56-58
         self.b = torch.zeros(1, device=bg.device, requires_grad=True)
         self.opt = torch.optim.Adam([{"params": [self.rot], "lr": 3e-3}, {"params": [self.trans], "lr": 1e-3},
                                      {"params": [self.a], "lr": 2e-2}, {"params": [self.b], "lr": 2e-2}])
@@ -121,3 +121,53 @@ class RefTracker:
             self.rot.data.fill_(0)
             self.trans.data.fill_(0)
         return loss
+
+
+    # ---- second-order (sketched Gauss-Newton / LM) iteration, utils/slam_frontend.py:455-720 with in_second_order ----
+    def begin_second_order(self, initial_lambda=1e-3):
+        self.lm = dict(lam=float(initial_lambda), prev=None, x=None)
+
+    def second_order_step(self, sketch_indices, rand_weights, sketch_dim, min_lambda=1e-6, max_lambda=1e7, inc=5.0, dec=5.0):
+        """One iteration in the reference's order: apply the pending step (TempCamera.step + update_pose, :474-480), render
+        with the reference kernels, scalar loss, lambda (:541-548), Sf and the gradient images through
+        oracle.golden.sketch_loss_ref (pinned to the reference's slam_utils by tests/test_oracle_cpu.py), the pose columns
+        of SJ through `stack_dim` calls of the reference's own sketch-Jacobian kernel (__init__.py:216-253), and
+        torch.linalg.lstsq([SJ; sqrt(lambda) I], -[Sf; 0]) (:668-679) in float64.  Returns (SJ [rows,8], Sf [rows], scalar, x)."""
+        from oracle import golden as G
+        lm = self.lm
+        with torch.no_grad():
+            if lm["x"] is not None:
+                x = lm["x"]
+                tau = x[:6].float()
+                R, V = _so3_exp(tau[3:])
+                E = torch.eye(4, device=tau.device)
+                E[:3, :3], E[:3, 3] = R, V @ tau[:3]
+                self.T = E @ self.T
+                self.a.data += x[6].float(); self.b.data += x[7].float()
+            cam = self._camera()
+            sc = self.sc
+            fw = ref_gpu.forward(cam, self.bg, sc.means3D, sc.opacities, shs=sc.shs, scales=sc.scales, rotations=sc.rotations,
+                                 sh_degree=sc.sh_degree)
+            n_stacks = sketch_indices.shape[0]
+            res = G.sketch_loss_ref(fw["color"], fw["opacity"], self.gt, self.a.detach(), self.b.detach(), sketch_indices,
+                                    rand_weights, sketch_dim)
+            scalar = float(res["scalar_l1"])
+            if lm["prev"] is not None:
+                lm["lam"] = max(lm["lam"] / dec, min_lambda) if scalar < lm["prev"] else min(lm["lam"] * inc, max_lambda)
+            lm["prev"] = scalar
+            g_img = res["g_image"].contiguous()
+            g_dep = torch.zeros_like(fw["depth"])
+            SJ = torch.zeros(n_stacks, sketch_dim, 8, device=g_img.device)
+            for j in range(n_stacks):
+                tau_j = ref_gpu.backward_sketch(cam, self.bg, fw, sc.means3D, g_img, g_dep, sketch_indices[j].contiguous(), sketch_dim,
+                                                shs=sc.shs, scales=sc.scales, rotations=sc.rotations, sh_degree=sc.sh_degree)
+                SJ[j, :, :6] = tau_j.double().sum(0).float()
+                del tau_j
+            SJ[:, :, 6:] = res["dexposure"]
+            SJ, Sf = SJ.view(-1, 8).double().cpu(), res["Sf"].reshape(-1).double().cpu()
+            A = torch.cat((SJ, torch.eye(8, dtype=torch.float64) * lm["lam"] ** 0.5), dim=0)
+            rhs = torch.cat((Sf, torch.zeros(8, dtype=torch.float64)), dim=0)
+            x = torch.linalg.lstsq(A, -rhs[:, None]).solution[:, 0]
+            lm["x"] = x.to(self.T.device)
+            self.image, self.opacity = fw["color"], fw["opacity"]
+        return SJ, Sf, scalar, x
