@@ -29,7 +29,14 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 METRIC = "tracking fwd+bwd iters/sec @640x480 200k Gaussians"
-WORKLOAD = "C2: mono TUM fr3_office-shaped tracking loop, synthetic frames, 200k Gaussians, 640x480, SH degree 0"
+WORKLOADS = {
+    "C1": "C1: mono tracking loop on the 50k-Gaussian scene of the rasterizer fwd+bwd config, 640x480, SH degree 0",
+    "C2": "C2: mono TUM fr3_office-shaped tracking loop, synthetic frames, 200k Gaussians, 640x480, SH degree 0",
+    "C3": "C3: RGB-D Replica office0-shaped tracking loop with depth loss (alpha 0.95), 500k Gaussians, 1200x680, SH degree 0",
+    "C5": "C5: stress, 2M Gaussians at 1920x1080, SH degree 3: tracking loop (forward + fused loss + pose-only backward)",
+}
+WORKLOAD = WORKLOADS["C2"]
+ISSUE_PEAK_WARP_INST_PER_S = 148 * 4 * 1.965e9      # one warp instruction per SM sub-partition per clock at sm_max_mhz
 
 
 def parse():
@@ -92,9 +99,12 @@ def build_tracker(cfg, dev, use_graph=True, rank=0):
     rs = RZ.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, bg, 1.0, cam_gt.viewmatrix,
                                           cam_gt.projmatrix, cam_gt.projmatrix_raw, sc.sh_degree, cam_gt.campos, False, False)
     gt, _, gt_depth, _, _, _ = RZ.raster_forward(rs, scd.means3D, scd.opacities, scd.shs, None, scd.scales, scd.rotations, None)
+    rgbd = cfg == "C3"       # config 3 tracks with the depth loss (get_loss_tracking_rgbd), the others with the mono Huber objective
+    from monogs_b200 import _lib as L
     tr = PoseTracker(scd.means3D, scd.opacities, scd.shs, scd.scales, scd.rotations, sc.sh_degree, cam, bg,
-                     torch.eye(4), use_graph=use_graph)
-    tr.set_frame(gt)
+                     torch.eye(4), use_graph=use_graph, mode=L.LOSS_TRACK_L1 if rgbd else L.LOSS_TRACK_HUBER, use_depth=rgbd)
+    tr.bench_gt_depth = gt_depth if rgbd else None
+    tr.set_frame(gt, gt_depth=tr.bench_gt_depth)
     return tr, scd, cam, gt
 
 
@@ -140,16 +150,61 @@ def kernel_profile(cfg, dev, steps):
     return prof, n_rendered, p_vis, tr.R_cap
 
 
+PROFILE_FILE = "profiles/r02_kernel_metrics.txt"     # ncu per-kernel metric table of the committed code (scripts/summarise_profiles.py)
+
+
+def profile_row(kernel_prefix):
+    """Row of the committed ncu metric table for the kernel whose name starts with `kernel_prefix` (tracking section), as a
+    dict {column: float}, plus whether the capture still describes the code that is running: the table's header records
+    the sha1 of every csrc file at capture time; a kernel source that changed since makes the row STALE and the caller
+    reports no traffic rather than an old number."""
+    import hashlib
+    import re
+    path = os.path.join(ROOT, PROFILE_FILE)
+    if not os.path.exists(path):
+        return None, "missing " + PROFILE_FILE
+    lines = open(path).read().splitlines()
+    shas = {}
+    for ln in lines:
+        if ln.startswith("# source-sha1:"):
+            for tok in ln.split(":", 1)[1].split():
+                f, _, h = tok.partition("=")
+                shas[f] = h
+    stale = []
+    for f, h in shas.items():
+        fp = os.path.join(ROOT, "monogs_b200", "csrc", f)
+        if not os.path.exists(fp) or hashlib.sha1(open(fp, "rb").read()).hexdigest()[:12] != h:
+            stale.append(f)
+    header, row = None, None
+    for ln in lines:
+        if ln.startswith("kernel ") and header is None:
+            header = ln.split()
+        elif header is not None and ln.startswith(kernel_prefix):
+            m = re.match(r"^(.*?)\s+(\d+)((?:\s+[-0-9.eE+]+){%d})\s*$" % (len(header) - 2), ln)
+            if m:
+                row = dict(zip(header[1:], [float(m.group(2))] + [float(x) for x in m.group(3).split()]))
+                row["kernel"] = m.group(1).strip()
+                break
+        elif ln.startswith("## mapping"):
+            break
+    if row is None:
+        return None, f"{kernel_prefix} not in {PROFILE_FILE}"
+    if not shas:
+        return row, "capture does not record source hashes"
+    return row, ("stale: changed since the capture: " + ", ".join(stale)) if stale else None
+
+
 def algorithmic_bytes(P, P_vis, R, R_cap, W, H, M=1):
     """Per-launch algorithmic bytes of every kernel of the fused tracking iteration."""
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     return {
         "preprocess": 12 * P + 8 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8 + 16 + 16) + P_vis * 144,
+        "preprocess+scan": 12 * P + 8 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8 + 16 + 16) + P_vis * 128 + 16 * tiles,
         "tile_scan": 16 * tiles,
         "emit": 4 * P + P_vis * 12 + 8 * R,
         "tile_sort_records": R * (8 + 44 + 48) + 8 * tiles,
         "tile_sort_records_large": 8 * tiles,
-        "blend_track": R * (48 + 144) + (20 + 12) * W * H + 40 * tiles,
+        "blend_track": R * (48 + 128) + (20 + 12) * W * H + 40 * tiles,
         "blend_forward": R * 48 + (28 + 12 + 12) * W * H + 40 * tiles,
         "blend_backward_pose": R * (48 + 144) + 20 * W * H + 8 * tiles,
         "track_update": 32 * tiles,
@@ -289,6 +344,58 @@ def ref_cuda_leg(cfg, dev, steps, warmup, flush):
     return out
 
 
+def second_order_leg(cfg, dev, steps, warmup, flush, with_reference=True):
+    """One second-order (sketched Gauss-Newton / LM) tracking iteration, stack_dim 16 x sketch_dim 64 (the shipped
+    configs/mono/tum/base_config.yaml RGN.second_order): here = mgs_track_second_order replayed from a CUDA graph
+    (the new sketch of every iteration is copied into the graph's buffers inside the timed region); reference = the same
+    iteration assembled from the reference's pieces (oracle.ref_tracking.RefTracker.second_order_step: reference forward,
+    16 x the reference's renderSketchJacobian kernel with its [P, 64, ...] buffers, float64 lstsq), on the same GPU."""
+    from monogs_b200.tracking import PoseTracker
+    from monogs_b200 import scene as S
+    from oracle import ref_gpu, ref_tracking
+    stacks, d = 16, 64
+    tr, scd, cam, gt = build_tracker(cfg, dev, use_graph=True)
+    for _ in range(40):                       # first-order phase (first_order.max_iter: 40)
+        tr.step()
+    tr.begin_second_order(1e-3)
+    g = torch.Generator(device=dev).manual_seed(0)
+    sketches = [PoseTracker.gen_sketch_args(cam.H, cam.W, stacks, d, device=dev, generator=g) for _ in range(4)]
+    k = [0]
+
+    def ours():
+        if k[0] % 10 == 0:                    # second_order.max_iter: 10 iterations per frame
+            tr.begin_second_order(1e-3, use_first_order_best=False)
+        idx, w = sketches[k[0] % 4]
+        k[0] += 1
+        tr.set_sketch(idx, w, d)
+        tr.second_order_step()
+    ms = timed_steps(ours, steps, warmup, flush, lambda: None)
+    out = {"iters_per_s": 1e3 * steps / ms, "ms_per_iter": ms / steps, "stack_dim": stacks, "sketch_dim": d,
+           "lambda": float(tr.lm_state[0]), "step_norm": float(tr.lm_state[34]), "overflow": tr.check_capacity()[1],
+           "api": "PoseTracker.set_sketch + second_order_step (mgs_track_second_order, CUDA graph)"}
+    if with_reference and ref_gpu.available():
+        sc, camc = S.make_config(cfg)
+        camd = S.Camera(*[x.to(dev) if isinstance(x, torch.Tensor) else x for x in camc])
+        rt = ref_tracking.RefTracker(scd, camd, torch.zeros(3, device=dev), torch.eye(4), S.make_camera)
+        rt.set_frame(gt)
+        for _ in range(3):
+            rt.step()
+        rt.begin_second_order(1e-3)
+        n_ref, j = 3, [0]
+
+        def ref():
+            idx, w = sketches[j[0] % 4]
+            j[0] += 1
+            rt.second_order_step(idx, w, d)
+        ms_ref = timed_steps(ref, n_ref, 1, flush, lambda: None)
+        out["ref_cuda_iters_per_s"] = 1e3 * n_ref / ms_ref
+        out["ref_cuda_ms_per_iter"] = ms_ref / n_ref
+        out["speedup_vs_ref_cuda"] = (ms_ref / n_ref) / (ms / steps)
+        out["ref_what"] = ("reference forward + 16 x _C.rasterize_gaussians_backward_sketch_jacobian (each with its zero-filled "
+                           "[P,64,...] gradient buffers, rasterize_points.cu:308-318) + eager sketched objective + lstsq")
+    return out
+
+
 def ref_mapping_leg(dev, flush, P=200_000, window=8, iters=6, warmup=2):
     """Config C4 through oracle/ref_mapping.py (the reference CUDA rasterizer inside the reference-style iteration)."""
     from oracle import ref_gpu, ref_mapping
@@ -315,7 +422,8 @@ def ref_mapping_leg(dev, flush, P=200_000, window=8, iters=6, warmup=2):
     return 1e3 * iters / ms
 
 
-def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engine=True, exchange="nccl", cfg="C2"):
+def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engine=True, exchange="nccl", cfg="C2",
+                ref_params=None, keep_params=None):
     """Config C4: 8-keyframe mapping window, views round-robin over ranks, one allreduce of the gradient arena,
     fused Adam on every rank (exchange="peer": reduce-scatter + Adam + parameter all-gather as ONE kernel over NVLink peer
     mappings, mgs_peer_reduce_adam).  engine=True: monogs_b200.mapping.MapEngine (mgs_map_*: raw parameters, activations once
@@ -391,6 +499,19 @@ def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engin
            "what": "8-keyframe window: per-view render+mapping loss+full backward, isotropic regulariser, one "
                    "sum-allreduce of the gradient arena, fused Adam on every rank"}
     if engine:
+        # cross-GPU parity inside the timed job: every rank ends with the same parameters (bit for bit: the checksums are
+        # exact float64 sums of the same float32 values), and the fused exchanges end where the NCCL path ends
+        flat = torch.cat([p.detach().reshape(-1) for p in eng.params.values()])
+        chk = torch.stack([flat.double().sum(), flat.double().abs().max(), flat.double().pow(2).sum()])
+        if world > 1:
+            allc = [torch.zeros_like(chk) for _ in range(world)]
+            dist.all_gather(allc, chk)
+            out["params_identical_across_ranks"] = all(bool(torch.equal(c, allc[0])) for c in allc)
+        out["param_checksum"] = [float(x) for x in chk]
+        if ref_params is not None:
+            out["max_rel_diff_vs_nccl_path"] = float((flat - ref_params).abs().max() / ref_params.abs().max())
+        if keep_params is not None:
+            keep_params.append(flat.clone())
         out["overflow"] = eng.check_capacity()[1]
         out["exchange"] = ("mgs_peer_reduce_adam: gradient reduce-scatter + Adam + parameter all-gather in one kernel over "
                            "NVLink peer mappings" if exchange == "peer" else "NCCL all_reduce of the gradient arena, then fused Adam")
@@ -464,7 +585,7 @@ def main():
     def step():
         # 100 pose iterations per frame (BASELINE.json config 2): re-arm the frame every 100 steps
         if step_count[0] % 100 == 0:
-            tr.set_frame(gt)
+            tr.set_frame(gt, gt_depth=tr.bench_gt_depth)
         step_count[0] += 1
         tr.step()
     clocks = ClockSampler(local)
@@ -491,12 +612,13 @@ def main():
     # its loss + tangent device -> host inside the timed region.  e2e: step_host_lagged() (iteration k is launched before
     # the host waits for the results of k-1, two result slots); e2e_sync: a full synchronize after every launch.
     loss_host = torch.zeros(2).pin_memory(); tau_host = torch.zeros(2, 6).pin_memory()
-    tr.bind_host(gt_host, loss_host, tau_host)
+    depth_host = tr.bench_gt_depth.cpu().pin_memory() if tr.bench_gt_depth is not None else None
+    tr.bind_host(gt_host, loss_host, tau_host, depth_host)
     sink = [0.0]
 
     def arm():
         if step_count[0] % 100 == 0:
-            tr.set_frame(tr._stage)                      # new frame: fresh Adam state (slam_frontend.py:453)
+            tr.set_frame(tr._stage, gt_depth=tr._stage_depth)     # new frame: fresh Adam state (slam_frontend.py:453)
         step_count[0] += 1
 
     def e2e_lagged():
@@ -519,7 +641,8 @@ def main():
         if world > 1: dist.all_reduce(te, op=dist.ReduceOp.MAX)
         return world * args.steps / float(te)
     e2e_sync = run_e2e(e2e_sync_step)
-    e2e = {"value": run_e2e(e2e_lagged), "unit": "iters/s", "h2d_bytes_per_step": gt_host.numel() * 4,
+    e2e = {"value": run_e2e(e2e_lagged), "unit": "iters/s",
+           "h2d_bytes_per_step": gt_host.numel() * 4 + (depth_host.numel() * 4 if depth_host is not None else 0),
            "d2h_bytes_per_step": 28, "value_sync_every_step": e2e_sync,
            "api": "monogs_b200.tracking.PoseTracker.bind_host/step_host_lagged over the C-ABI: one CUDA-graph launch per "
                   "iteration, the next frame's H2D copy beside the kernels, the host waits for iteration k-1 after launching k "
@@ -527,9 +650,11 @@ def main():
     line = {"metric": METRIC, "value": value, "unit": "iters/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "gaussians": scd.means3D.size(0), "visible": int((tr.radii > 0).sum()),
+            "config": {"workload": WORKLOADS[args.config], "gaussians": scd.means3D.size(0), "visible": int((tr.radii > 0).sum()),
                        "tile_instances": n_rendered, "instance_capacity": tr.R_cap, "overflow": overflow,
-                       "iters_per_frame": 100, "loss": "Huber(0.01)+L2 per-pixel residual (slam_frontend.py:596-598)",
+                       "iters_per_frame": 100,
+                       "loss": ("L1 rgb + depth, alpha 0.95 (slam_utils.py:102-113)" if args.config == "C3" else
+                                "Huber(0.01)+L2 per-pixel residual (slam_frontend.py:596-598)"),
                        "l2": "256 MiB buffer written between steps, outside the per-step event pairs",
                        "multi_gpu": "replicas only (tracking does not shard); see mapping"},
             "clocks": clk, "e2e": e2e, "gpu_launches": KERNELS_PER_ITER * args.steps,
@@ -551,15 +676,26 @@ def main():
                     v["alg_bytes"] = ab[k]; v["gbs"] = ab[k] / (v["avg_us"] * 1e-6) / 1e9
             top = max(prof, key=lambda k: prof[k]["avg_us"])
             step_us = sum(v["avg_us"] for v in prof.values())
-            # dram__bytes_read + write of one launch from the committed ncu --set full capture (profiles/), C2 only
-            traffic = {"blend_track": 56.9e6}.get(top) if args.config == "C2" else None
+            # dram bytes / warp instructions / lanes of one launch: parsed from the committed ncu table of THIS code (C2 only);
+            # a table captured before the kernel's source last changed is reported as stale, not used
+            row, problem = profile_row(top + "_kernel") if args.config == "C2" else (None, "the ncu table is captured at C2")
+            usable = row is not None and problem is None
+            traffic = (row["rdMB"] + row["wrMB"]) * 1e6 if usable else None
             line["roofline"] = {"kernel": top, "bound": "hbm", "achieved": prof[top].get("gbs"), "peak": peak, "unit": "GB/s",
                                 "frac": (prof[top].get("gbs") or 0) / peak, "traffic": traffic,
-                                "traffic_source": "profiles/r01e_ncu_full_blend_kernels.txt", "peak_source": src,
-                                "issue_slot_utilisation": {"blend_track": 0.677}.get(top),
+                                "traffic_source": PROFILE_FILE + (f" ({problem})" if problem else ""), "peak_source": src,
                                 "share_of_step": prof[top]["avg_us"] / step_us,
-                                "note": "the blend kernels are issue/SFU-bound (one 48-B record feeds 256 pixel "
-                                        "evaluations), so their HBM fraction is small by construction; see DESIGN.md"}
+                                "note": "HBM roofline of the dominant kernel.  The blend kernels are bound by warp-instruction "
+                                        "issue and the fp32 pipe, not by HBM (one 48-B record feeds up to 256 pixel evaluations), "
+                                        "so this fraction is small by construction; issue_roofline is the binding one"}
+            if usable:
+                inst = row["Minst"] * 1e6
+                rate = inst / (prof[top]["avg_us"] * 1e-6)
+                line["issue_roofline"] = {"kernel": row["kernel"], "warp_inst_per_launch": inst, "achieved_warp_inst_per_s": rate,
+                                          "peak_warp_inst_per_s": ISSUE_PEAK_WARP_INST_PER_S, "frac": rate / ISSUE_PEAK_WARP_INST_PER_S,
+                                          "lanes_active_of_32": row["lanes"], "lane_frac": rate / ISSUE_PEAK_WARP_INST_PER_S * row["lanes"] / 32.0,
+                                          "issue_active_pct_ncu": row["issue%"], "fma_pipe_pct_ncu": row["fma%"],
+                                          "source": PROFILE_FILE + ": instruction count and lanes from ncu, time measured live"}
             line["kernels"] = {k: {"avg_us": round(v["avg_us"], 2), "gbs": round(v.get("gbs", 0), 1)} for k, v in prof.items()}
             iter_bytes = sum(ab[k] for k in prof if k in ab)
             line["iteration_roofline"] = {"alg_bytes": iter_bytes, "achieved_gbs": iter_bytes / (ms / args.steps * 1e-3) / 1e9,
@@ -568,20 +704,27 @@ def main():
                 line["ref_cuda"] = ref_cuda_leg(args.config, dev, min(args.steps, 50), 5, flush)
             except Exception as ex:
                 line["ref_cuda"] = {"error": repr(ex)[:200]}
+            if args.config in ("C1", "C2"):
+                try:
+                    line["second_order"] = second_order_leg(args.config, dev, min(args.steps, 100), 5, flush)
+                except Exception as ex:
+                    line["second_order"] = {"error": repr(ex)[:300]}
             cpu_oracle_rate(args.config, 8, 8)       # untimed: builds the scene + tile lists, warms the allocator
             v, info = cpu_oracle_rate(args.config, 1, 1)
             line["cpu_baseline"] = {"value": v, "unit": "iters/s", "cores": os.cpu_count(), "kind": "port", "sample": _sample_text(info)}
+        nccl_params = []
         try:
-            line["mapping"] = mapping_leg(dev, rank, world)
+            line["mapping"] = mapping_leg(dev, rank, world, keep_params=nccl_params)
         except Exception as ex:
             line["mapping"] = {"error": repr(ex)[:300]}
         if world > 1:
+            refp = nccl_params[0] if nccl_params else None
             try:
-                line["mapping_peer"] = mapping_leg(dev, rank, world, exchange="peer")
+                line["mapping_peer"] = mapping_leg(dev, rank, world, exchange="peer", ref_params=refp)
             except Exception as ex:
                 line["mapping_peer"] = {"error": repr(ex)[:300]}
             try:
-                line["mapping_nvls"] = mapping_leg(dev, rank, world, exchange="nvls")
+                line["mapping_nvls"] = mapping_leg(dev, rank, world, exchange="nvls", ref_params=refp)
             except Exception as ex:
                 line["mapping_nvls"] = {"error": repr(ex)[:300]}
         if world == 1:

@@ -221,6 +221,10 @@ int mgs_pose_update(float* T_w2c, float* rho, float* theta, const float* proj_ra
  *      -> Adam on (rho lr[0], theta lr[1], exposure_a lr[2], exposure_b lr[3]) -> T <- Exp(rho,theta) T.
  *      No host synchronisation; CUDA-graph capturable.  view.viewmatrix / view.projmatrix (and view.campos when it
  *      aliases the view matrix, as in MonoGS) are device buffers that the call UPDATES IN PLACE with the new pose.
+ *      `workspace` and `scratch` must be ZERO-FILLED ONCE by their owner before the first iteration (and belong to this
+ *      loop alone): tile counters, tickets and the tangent accumulator are left zero by every iteration for the next one —
+ *      the tile scan runs in the last CTA of the preprocess kernel and the update in the last CTA of the blend kernel, so
+ *      an iteration is five kernel launches and no memset.
  *      params = f32[8] (rho, theta, a, b); exp_avg / exp_avg_sq = f32[8]; step_counter = device i32[1]. ---- */
 typedef struct mgs_track_args {
   mgs_view view;
@@ -331,7 +335,9 @@ typedef struct mgs_map_view {
   float* tau;               /* f32[6]: pose tangent (rho, theta) of this view's loss, optional */
   float* dab;               /* f32[2]: dL/d(exposure_a, exposure_b), optional */
   float* loss;              /* f32[1]: this view's loss, optional */
-  void* workspace; size_t workspace_bytes; int64_t R_cap;
+  void* workspace; size_t workspace_bytes; int64_t R_cap;   /* zero-filled once by its owner before the first view
+                             * rendered into it, and used by mgs_map_view_* only (tile counters and the scan ticket are left
+                             * zero by every view for the next one) */
 } mgs_map_view;
 
 size_t mgs_map_scratch_bytes(int32_t P, int32_t sh_coeffs, int32_t W_max, int32_t H_max);

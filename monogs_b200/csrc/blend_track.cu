@@ -13,15 +13,26 @@
 //     tau_pixel = sum_ch g_ch * (A_ch - out_ch * E)        (+ the same for depth, + g_d * sum_i alpha_i T_i dz_i/dtau).
 // The local Jacobians are exactly the reference's (clamp ignored, Q6; FoV quirk inside B_i, Q8), only the order of
 // the sum differs.  One pass instead of two: no second exp per pair, no g / final_T / n_contrib round trip.
+//
+// vp_i is evaluated from the folded per-Gaussian basis of pose_jac.cuh (32 floats, one 128-byte line):
+//     vp = s * (dx * (U + dx * A + dy * Bm) + dy * (V + dy * Cm)),   s = opacity * G / (1 - alpha)
+// 15 packed multiply-adds; s is folded into the four weights of the accumulation (1, w_r, w_g, w_b).
 #include "launchers.h"
 #include "tma.cuh"
 #include "loss_pixel.cuh"
 #include "pose_jac.cuh"
+#include "track_update.cuh"
+#include <cstdlib>
+#include <cstring>
+
+#ifndef MGS_TRK_SPLIT_DEFAULT
+#define MGS_TRK_SPLIT_DEFAULT 1
+#endif
 
 namespace mgs {
 
 constexpr int TRK_BATCH = 128;
-constexpr int TRK_NF = PoseJac<6>::kFloats;   // 36
+constexpr int TRK_NF = POSE_BASIS_FLOATS;   // 32
 
 constexpr int TRK_STAGES = 3;
 constexpr size_t TRK_SMEM = (size_t)TRK_STAGES * TRK_BATCH * sizeof(SplatRec) + 2 * (size_t)TRK_BATCH * TRK_NF * sizeof(float);
@@ -32,36 +43,56 @@ __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
-// Pipeline per tile: records of batch i+2 in flight by bulk copy (TMA), pose Jacobians of batch i+1 gathered by cp.async
+struct TrackTail {            // the folded update (FOLD): last CTA of the grid runs track_update_body
+  TrackUpdateK k;
+  uint32_t* ticket;           // device u32, zero before the first launch; reset by the last CTA
+  float* tau_raw;             // zeroed by the last CTA after it has consumed it
+};
+
+// Pipeline per tile: records of batch i+2 in flight by bulk copy (TMA), pose bases of batch i+1 gathered by cp.async
 // (their ids come from the records of i+1, already landed), batch i being blended: one CTA barrier (the early-out
 // vote) per batch and no load latency on the blend path.
+//
+// SPLIT = 1: the warp owns an 8x4 pixel patch and walks ONE list of the splats that can reach it.
+// SPLIT = 2: the warp's two half-warps own a 4x4 block each and walk their OWN lists side by side in the same
+//   instruction stream (lanes 0-15 at splat jL, lanes 16-31 at splat jR; shared-memory reads see two addresses instead
+//   of one).  A splat of a few pixels' radius reaches far fewer 4x4 blocks than 8x4 patches per covered pixel (Steiner:
+//   area + R * perimeter + block), so the number of list steps of a warp drops to max(nL, nR) of the two tighter lists
+//   and fewer lanes idle inside a step.
 // SKETCH: the epilogue evaluates the second-order (sketched Gauss-Newton) objective instead of the first-order loss and
-// writes this pixel's Jacobian row contribution (tau[6], d/d exposure_a, d/d exposure_b, f) to sk_image[9][H][W]; the rows
-// are formed afterwards by sketch_reduce_kernel, whatever the pixel -> row routing of the stacks (pose_backward.cu).
-template <bool HAS_DEPTH, bool FAST, bool SKETCH>   // FAST: ex2.approx exponent, n_touched not produced
+//   writes this pixel's Jacobian row contribution (tau[6], d/d exposure_a, d/d exposure_b, f) to sk_image[9][H][W]; the rows
+//   are formed afterwards by sketch_reduce_kernel, whatever the pixel -> row routing of the stacks (pose_backward.cu).
+// FOLD: the last CTA to finish (ticket) runs the iteration's serial tail (track_update_body) instead of a separate launch.
+template <bool HAS_DEPTH, bool FAST, bool SKETCH, int SPLIT, bool FOLD>   // FAST: ex2.approx exponent, n_touched not produced
 __global__ void __launch_bounds__(256, 3)
 blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __restrict__ tile_order, const uint2* __restrict__ ranges,
                    const SplatRec* __restrict__ recs, const float* __restrict__ jac, const float* __restrict__ bg,
                    float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
                    int32_t* __restrict__ n_touched, const LossK lk, const float loss_grad_scale,
                    double* __restrict__ loss_partials, float* __restrict__ tau_sum,
-                   const float* __restrict__ sk_weights, const float sk_scale, float* __restrict__ sk_image) {
+                   const float* __restrict__ sk_weights, const float sk_scale, float* __restrict__ sk_image,
+                   const TrackTail tail) {
   extern __shared__ __align__(128) unsigned char trk_smem[];
   SplatRec (*stage)[TRK_BATCH] = reinterpret_cast<SplatRec (*)[TRK_BATCH]>(trk_smem);
   float (*jstage)[TRK_BATCH * TRK_NF] =
       reinterpret_cast<float (*)[TRK_BATCH * TRK_NF]>(trk_smem + (size_t)TRK_STAGES * TRK_BATCH * sizeof(SplatRec));
   __shared__ __align__(8) uint64_t full_bar[TRK_STAGES];
   __shared__ float s_part[8][6];
+  __shared__ int s_last;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int tile = (int)tile_order[(size_t)blockIdx.x * TILE_CTR_STRIDE + 3];   // heavy tiles first (tile_scan_kernel)
   const int tx = tile % gx, ty = tile / gx;
-  const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
-  const int py = ty * TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+  // pixel of this lane inside the warp's 8x4 patch: row-major for SPLIT = 1; for SPLIT = 2 the half-warps are the left
+  // and the right 4x4 block
+  const int half = lane >> 4;
+  const int lx = SPLIT == 2 ? half * 4 + (lane & 3) : (lane & 7);
+  const int ly = SPLIT == 2 ? ((lane >> 2) & 3) : (lane >> 3);
+  const int px = tx * TILE_X + (warp & 1) * 8 + lx;
+  const int py = ty * TILE_Y + (warp >> 1) * 4 + ly;
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
   const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 4);
-  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
@@ -80,7 +111,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     bulk_g2s(&stage[i % TRK_STAGES][0], src + (size_t)i * TRK_BATCH, bytes, &full_bar[i % TRK_STAGES]);
   };
   auto wait_records = [&](int i) { mbar_wait(&full_bar[i % TRK_STAGES], (i / TRK_STAGES) & 1); };
-  auto gather = [&](int i) {  // pose Jacobians of batch i (L2-resident per-Gaussian array) -> jstage[i & 1], 16 B per cp.async
+  auto gather = [&](int i) {  // pose bases of batch i (L2-resident per-Gaussian array) -> jstage[i & 1], 16 B per cp.async
     const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
     const float4* rec4 = reinterpret_cast<const float4*>(&stage[i % TRK_STAGES][0]);
     float4* dst = reinterpret_cast<float4*>(&jstage[i & 1][0]);
@@ -96,17 +127,16 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
 
   bool done = !inside;
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
-  // The 6-vector accumulators live as three f32x2 register pairs each: the 54 multiply-adds per hit that build vp and
-  // fold it into E / A_ch issue as 27 packed FMUL2 / FFMA2 / FADD2 (sm_100 packed fp32; same IEEE operation per half,
-  // so the sums keep their bits).
+  // The 6-vector accumulators live as three f32x2 register pairs each: every multiply-add that builds vp and folds it
+  // into E / A_ch is a packed FMUL2 / FFMA2 (sm_100 packed fp32; same IEEE operation per half).
   float2 E2[3], A02[3], A12[3], A22[3], Ad2[3];
   float F0 = 0.f, F1 = 0.f, F2 = 0.f;
 #pragma unroll
   for (int k = 0; k < 3; k++) { E2[k] = A02[k] = A12[k] = A22[k] = Ad2[k] = make_float2(0.f, 0.f); }
 
   for (int i = 0; i < rounds; i++) {
-    cp_async_wait_all();   // this thread's share of the Jacobians of batch i has landed
-    // CTA vote; publishes the Jacobians of batch i and guarantees every warp left the buffers reused below
+    cp_async_wait_all();   // this thread's share of the bases of batch i has landed
+    // CTA vote; publishes the bases of batch i and guarantees every warp left the buffers reused below
     if (__syncthreads_count(done) == TILE_PIX) {
       if (tid == 0 && i + 1 < rounds) wait_records(i + 1);   // never exit with a bulk copy in flight
       break;
@@ -118,18 +148,27 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     const float* recf = reinterpret_cast<const float*>(&stage[i % TRK_STAGES][0]);
     const float* jst = &jstage[i & 1][0];
     for (int c0 = 0; c0 < cnt; c0 += 32) {
-      // lane-parallel exact cull of 32 splats against this warp's 8x4 patch (see splat_extent)
+      // lane-parallel exact cull of 32 splats against this warp's patch (SPLIT = 2: against each of its two 4x4 blocks)
       const int jj = c0 + lane;
-      unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+      unsigned mine;
+      if (SPLIT == 2) {
+        const bool ok = jj < cnt;
+        const unsigned hl = __ballot_sync(0xffffffffu, ok && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 3.f, patch_y0, patch_y0 + 3.f));
+        const unsigned hr = __ballot_sync(0xffffffffu, ok && splat_hits(recf + 12 * jj, patch_x0 + 4.f, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+        mine = half ? hr : hl;
+      } else {
+        mine = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+      }
       if (__ballot_sync(0xffffffffu, !done) == 0u) break;
-      while (hits) {
-        const int j = c0 + __ffs(hits) - 1;
-        hits &= hits - 1;
+      while (SPLIT == 2 ? __any_sync(0xffffffffu, mine != 0u) : (mine != 0u)) {
+        const bool act = SPLIT == 2 ? (mine != 0u) : true;
+        const int j = c0 + (act ? __ffs(mine) - 1 : 0);
+        mine &= mine - 1;
         const float4 g0 = rec4[3 * j + 0];  // x, y, depth, id
         const float4 g1 = rec4[3 * j + 1];  // conic xyz, opacity
         const float dx = g0.x - pxf, dy = g0.y - pyf;
         const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
-        bool valid = !done && !(power > 0.0f);
+        bool valid = act && !done && !(power > 0.0f);
         const float G = blend_exp<FAST>(power);
         const float alpha = min(0.99f, g1.w * G);
         valid = valid && !(alpha < 1.0f / 255.0f);
@@ -137,56 +176,50 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
         if (valid && test_T < 0.0001f) { done = true; valid = false; }
         if (!FAST) {
           const unsigned touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
-          if (touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
+          if (SPLIT == 2) {
+            const unsigned th = half ? (touch >> 16) : (touch & 0xffffu);
+            if (th != 0u && (lane & 15) == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(th));
+          } else if (touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
         }
         if (__ballot_sync(0xffffffffu, valid) == 0u) continue;
         if (valid) {
           const float4 g2 = rec4[3 * j + 2];
-          // vp = r * opacity * B^T geom  (geom: d alpha / d (mean2D, conic) up to the opacity factor, backward.cu:986-1010)
-          const float f = g1.w * rcp_unit(1.f - alpha);   // 1-alpha in [0.01,1]
-          const float gdx = G * dx, gdy = G * dy;
-          float q[5];
-          q[0] = f * (-gdx * g1.x - gdy * g1.y) * ddelx_dx;
-          q[1] = f * (-gdy * g1.z - gdx * g1.y) * ddely_dy;
-          q[2] = -0.5f * gdx * dx * f;
-          q[3] = -0.5f * gdx * dy * f;
-          q[4] = -0.5f * gdy * dy * f;
           const float4* J4 = reinterpret_cast<const float4*>(jst + j * TRK_NF);
-          float2 B2[TRK_NF / 2];   // row c of B = pairs 3c .. 3c+2
+          // folded basis rows: U = f[0..5], V = f[6..11], A = f[12..17], Bm = f[18..23], Cm = f[24..29], yC, -xC
+          const float4 b0 = J4[0], b1 = J4[1], b2 = J4[2], b3 = J4[3], b4 = J4[4], b5 = J4[5], b6 = J4[6], b7 = J4[7];
+          const float2 dx2 = make_float2(dx, dx), dy2 = make_float2(dy, dy);
+          float2 t1[3], t2[3], vp2[3];
+          // t1 = U + dx * A + dy * Bm ; t2 = V + dy * Cm ; vp = dx * t1 + dy * t2
+          t1[0] = __ffma2_rn(dx2, make_float2(b3.x, b3.y), make_float2(b0.x, b0.y));
+          t1[1] = __ffma2_rn(dx2, make_float2(b3.z, b3.w), make_float2(b0.z, b0.w));
+          t1[2] = __ffma2_rn(dx2, make_float2(b4.x, b4.y), make_float2(b1.x, b1.y));
+          t1[0] = __ffma2_rn(dy2, make_float2(b4.z, b4.w), t1[0]);
+          t1[1] = __ffma2_rn(dy2, make_float2(b5.x, b5.y), t1[1]);
+          t1[2] = __ffma2_rn(dy2, make_float2(b5.z, b5.w), t1[2]);
+          t2[0] = __ffma2_rn(dy2, make_float2(b6.x, b6.y), make_float2(b1.z, b1.w));
+          t2[1] = __ffma2_rn(dy2, make_float2(b6.z, b6.w), make_float2(b2.x, b2.y));
+          t2[2] = __ffma2_rn(dy2, make_float2(b7.x, b7.y), make_float2(b2.z, b2.w));
 #pragma unroll
-          for (int k = 0; k < TRK_NF / 4; k++) {
-            const float4 t4 = J4[k];
-            B2[2 * k] = make_float2(t4.x, t4.y); B2[2 * k + 1] = make_float2(t4.z, t4.w);
-          }
-          float2 vp2[3];
-          {
-            const float2 qq = make_float2(q[0], q[0]);
-#pragma unroll
-            for (int m = 0; m < 3; m++) vp2[m] = __fmul2_rn(qq, B2[m]);
-          }
-#pragma unroll
-          for (int c = 1; c < 5; c++) {
-            const float2 qq = make_float2(q[c], q[c]);
-#pragma unroll
-            for (int m = 0; m < 3; m++) vp2[m] = __ffma2_rn(qq, B2[c * 3 + m], vp2[m]);
-          }
-          const float w0 = fmaf(T, g2.x, C0), w1 = fmaf(T, g2.y, C1), w2 = fmaf(T, g2.z, C2);
-          const float2 w02 = make_float2(w0, w0), w12 = make_float2(w1, w1), w22 = make_float2(w2, w2);
+          for (int m = 0; m < 3; m++) vp2[m] = __ffma2_rn(dy2, t2[m], __fmul2_rn(dx2, t1[m]));
+          // s = opacity * G / (1 - alpha): d alpha / d(geometry) up to the polynomial, times r_i (1-alpha in [0.01,1])
+          const float sE = g1.w * G * rcp_unit(1.f - alpha);
+          const float s0 = sE * fmaf(T, g2.x, C0), s1 = sE * fmaf(T, g2.y, C1), s2 = sE * fmaf(T, g2.z, C2);
+          const float2 sE2 = make_float2(sE, sE), s02 = make_float2(s0, s0), s12 = make_float2(s1, s1), s22 = make_float2(s2, s2);
 #pragma unroll
           for (int m = 0; m < 3; m++) {
-            E2[m] = __fadd2_rn(E2[m], vp2[m]);
-            A02[m] = __ffma2_rn(w02, vp2[m], A02[m]);
-            A12[m] = __ffma2_rn(w12, vp2[m], A12[m]);
-            A22[m] = __ffma2_rn(w22, vp2[m], A22[m]);
+            E2[m] = __ffma2_rn(sE2, vp2[m], E2[m]);
+            A02[m] = __ffma2_rn(s02, vp2[m], A02[m]);
+            A12[m] = __ffma2_rn(s12, vp2[m], A12[m]);
+            A22[m] = __ffma2_rn(s22, vp2[m], A22[m]);
           }
           if (HAS_DEPTH) {
             const float aT = alpha * T;
-            const float wd = fmaf(T, g0.z, D);
-            const float2 wd2 = make_float2(wd, wd);
+            const float sd = sE * fmaf(T, g0.z, D);
+            const float2 sd2 = make_float2(sd, sd);
 #pragma unroll
-            for (int m = 0; m < 3; m++) Ad2[m] = __ffma2_rn(wd2, vp2[m], Ad2[m]);
+            for (int m = 0; m < 3; m++) Ad2[m] = __ffma2_rn(sd2, vp2[m], Ad2[m]);
             // depth column of B: dz/dtau = (0, 0, 1, y_C, -x_C, 0)
-            F0 += aT; F1 = fmaf(aT, B2[16].y, F1); F2 = fmaf(aT, B2[17].x, F2);
+            F0 += aT; F1 = fmaf(aT, b7.z, F1); F2 = fmaf(aT, b7.w, F2);
           }
           C0 += g2.x * alpha * T;   // same expression as forward.cu:364-367 / blend_forward.cu: identical image bits
           C1 += g2.y * alpha * T;
@@ -241,59 +274,101 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     }
   }
   loss_block_reduce(acc, loss_partials + (size_t)tile * 4);
-  if (SKETCH) return;
+  if (!SKETCH) {
 #pragma unroll
-  for (int k = 0; k < 6; k++) {
-    float x = tau[k];
+    for (int k = 0; k < 6; k++) {
+      float x = tau[k];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
-    if (lane == 0) s_part[warp][k] = x;
-  }
-  __syncthreads();
-  if (tid < 6) {
-    float x = 0.f;
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+      if (lane == 0) s_part[warp][k] = x;
+    }
+    __syncthreads();
+    if (tid < 6) {
+      float x = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; w++) x += s_part[w][tid];
-    if (x != 0.f) atomicAdd(&tau_sum[tid], x);
+      for (int w = 0; w < 8; w++) x += s_part[w][tid];
+      if (x != 0.f) atomicAdd(&tau_sum[tid], x);
+    }
+    if (FOLD) {
+      // ticket: this CTA's partial sums and tangent atomics are ordered before its increment, so whoever draws the last
+      // ticket sees the sums of every tile and runs the iteration's serial tail in place of a separate launch
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) {
+        const uint32_t t = atomicAdd(tail.ticket, 1u);
+        s_last = (t == gridDim.x - 1) ? 1 : 0;
+      }
+      __syncthreads();
+      if (s_last) {
+        __threadfence();
+        track_update_body(tail.k);
+        if (tid < 6) tail.tau_raw[tid] = 0.f;      // track_update_body has read tau_raw (its first barrier is behind us)
+        if (tid == 0) *tail.ticket = 0u;
+      }
+    }
   }
 }
 
-// tau_sum must be zeroed by the caller; jac holds the 6-column per-Gaussian maps (PoseJac<6>).  sk_image != nullptr selects
-// the second-order epilogue (mono only): sk_weights f32[H,W] (+-1), sk_scale = stack_dim * sketch_dim / npix.
-int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
-                       float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
-                       float* tau_sum, cudaStream_t s, const float* sk_weights, float sk_scale, float* sk_image) {
-  const int tiles = v.gx * v.gy;
+template <bool HAS_DEPTH, bool FAST, bool SKETCH, int SPLIT, bool FOLD>
+static int launch_trk_t(int tiles, cudaStream_t s, const int W, const int H, const int gx, const uint32_t* tile_order,
+                        const uint2* ranges, const SplatRec* recs, const float* jac, const float* bg, float* out_color,
+                        float* out_depth, float* out_opacity, int32_t* n_touched, const LossK& lk, float grad_scale,
+                        double* partials, float* tau_sum, const float* sk_weights, float sk_scale, float* sk_image,
+                        const TrackTail& tail) {
   // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute
   static bool attr_set[64] = {};
   int dev = 0;
   MGS_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) { set_error("blend_track: device ordinal %d out of range", dev); return MGS_EINVAL; }
+  auto kern = blend_track_kernel<HAS_DEPTH, FAST, SKETCH, SPLIT, FOLD>;
   if (!attr_set[dev]) {
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
-    MGS_CUDA_TRY(cudaFuncSetAttribute(blend_track_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
     attr_set[dev] = true;
   }
+  kern<<<tiles, 256, TRK_SMEM, s>>>(W, H, gx, tile_order, ranges, recs, jac, bg, out_color, out_depth, out_opacity, n_touched, lk,
+                                    grad_scale, partials, tau_sum, sk_weights, sk_scale, sk_image, tail);
+  return MGS_OK;
+}
+
+int blend_track_split() {
+  // MGS_TRK_SPLIT=1|2 overrides the built-in choice (read once; a tuning knob, like MGS_PEER_VARIANT)
+  static int split = [] {
+    const char* e = getenv("MGS_TRK_SPLIT");
+    return (e && e[0] == '1') ? 1 : ((e && e[0] == '2') ? 2 : MGS_TRK_SPLIT_DEFAULT);
+  }();
+  return split;
+}
+
+// tau_sum must be zero on entry (the folded tail re-zeroes it); jac holds the folded per-Gaussian bases
+// (POSE_BASIS_FLOATS).  sk_image != nullptr selects the second-order epilogue (mono only): sk_weights f32[H,W] (+-1),
+// sk_scale = stack_dim * sketch_dim / npix.  upd != nullptr folds the iteration's update tail into the kernel's last CTA.
+int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
+                       float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
+                       float* tau_sum, cudaStream_t s, const float* sk_weights, float sk_scale, float* sk_image,
+                       const TrackUpdateK* upd, uint32_t* ticket) {
+  const int tiles = v.gx * v.gy;
   if (sk_image != nullptr && (has_depth || sk_weights == nullptr)) { set_error("blend_track: the sketched epilogue is mono only and needs rand_weights"); return MGS_EINVAL; }
-#define MGS_TRK_ARGS v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color,   \
-      out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum, sk_weights, sk_scale, sk_image
+  if (upd != nullptr && (ticket == nullptr || sk_image != nullptr)) { set_error("blend_track: folded tail needs a ticket and the first-order epilogue"); return MGS_EINVAL; }
+  TrackTail tail;
+  memset(&tail, 0, sizeof(tail));
+  if (upd) { tail.k = *upd; tail.ticket = ticket; tail.tau_raw = tau_sum; }
+  const int split = blend_track_split();
+#define MGS_TRK_ARGS tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), \
+      jac, v.bg, out_color, out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum, sk_weights, sk_scale, sk_image, tail
+#define MGS_TRK_DISPATCH(HD, SK, FO)                                                                                                   \
+  do {                                                                                                                                 \
+    if (split == 2) rc = fl.fast ? launch_trk_t<HD, true, SK, 2, FO>(MGS_TRK_ARGS) : launch_trk_t<HD, false, SK, 2, FO>(MGS_TRK_ARGS); \
+    else rc = fl.fast ? launch_trk_t<HD, true, SK, 1, FO>(MGS_TRK_ARGS) : launch_trk_t<HD, false, SK, 1, FO>(MGS_TRK_ARGS);            \
+  } while (0)
+  int rc = MGS_OK;
   prof_begin(sk_image ? "blend_track_sketch" : "blend_track", s);
-  if (sk_image != nullptr) {
-    if (fl.fast) blend_track_kernel<false, true, true><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
-    else blend_track_kernel<false, false, true><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
-  } else if (has_depth) {
-    if (fl.fast) blend_track_kernel<true, true, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
-    else blend_track_kernel<true, false, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
-  } else {
-    if (fl.fast) blend_track_kernel<false, true, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
-    else blend_track_kernel<false, false, false><<<tiles, 256, TRK_SMEM, s>>>(MGS_TRK_ARGS);
-  }
+  if (sk_image != nullptr) MGS_TRK_DISPATCH(false, true, false);
+  else if (has_depth) { if (upd) MGS_TRK_DISPATCH(true, false, true); else MGS_TRK_DISPATCH(true, false, false); }
+  else { if (upd) MGS_TRK_DISPATCH(false, false, true); else MGS_TRK_DISPATCH(false, false, false); }
   prof_end(s);
+#undef MGS_TRK_DISPATCH
 #undef MGS_TRK_ARGS
+  if (rc) return rc;
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

@@ -54,7 +54,8 @@ struct WsHeader {
   // while instead of after every render, and still learns about ANY render that did not fit.
   uint32_t overflow_sticky;   // 1 once any binning into this workspace saw num_rendered > R_cap
   uint32_t max_rendered;      // largest num_rendered any binning into this workspace saw
-  uint32_t pad[58];
+  uint32_t ticket;            // CTA ticket of the folded scan (preprocess_kernel<.., FOLD_SCAN>); zero between launches
+  uint32_t pad[57];
 };
 static_assert(sizeof(WsHeader) == 256, "header is one 256-B slot");
 

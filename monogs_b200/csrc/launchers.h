@@ -6,13 +6,16 @@ namespace mgs {
 
 const char* get_error();
 
+// fused loops: the tile scan runs in the last CTA of the preprocess kernel, no counter memset (see raster_forward.cu)
+struct FoldScan { int64_t R_cap; bool heavy_first; };
 int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
-                      float* jac = nullptr, int jac_ncol = 0, const float* sh_rest = nullptr);
+                      float* jac = nullptr, int jac_ncol = 0, const float* sh_rest = nullptr, const FoldScan* fold = nullptr);
 int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false);
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
-                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false, bool scan_done = false);
+                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false, bool scan_done = false,
+                   bool clear_counts = false);
 struct LossK;
 // optional fused loss epilogue of the forward blend (tracking path): per-pixel loss + un-normalised gradient images
 struct FusedLoss { const LossK* k; float grad_scale; float* g_img; float* g_depth; double* partials; bool fast; };
@@ -23,7 +26,7 @@ int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float*
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s, const float* sk_weights = nullptr, float sk_scale = 0.f,
-                       float* sk_image = nullptr);
+                       float* sk_image = nullptr, const struct TrackUpdateK* upd = nullptr, uint32_t* ticket = nullptr);
 
 struct BackwardArgs {
   ViewConst v; int P; uint32_t grad_mask;

@@ -237,10 +237,13 @@ int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* st
   const mgs_gaussians& g = a->g;
   const MapScratch& m = c.m;
   void* ws = mv->workspace;
+  // the workspace of a mapping engine is zero-filled once by its owner: the scan runs in the last CTA of the preprocess
+  // kernel and the sort kernel leaves the tile counters zero for the next view (raster_forward.cu, FoldScan)
+  const FoldScan fs{mv->R_cap, false};
   if ((rc = launch_preprocess(c.v, c.P, g.xyz, m.act_opacity, c.shs, nullptr, m.act_scales, m.act_rot, nullptr, mv->radii, ws, c.L, s,
-                              nullptr, 0, c.M > 1 ? g.f_rest : nullptr))) return rc;
+                              nullptr, 0, c.M > 1 ? g.f_rest : nullptr, &fs))) return rc;
   MGS_CUDA_TRY(cudaMemsetAsync(mv->n_touched, 0, (size_t)c.P * sizeof(int32_t), s));
-  if ((rc = launch_binning(c.v, c.P, nullptr, mv->radii, ws, c.L, mv->R_cap, s))) return rc;
+  if ((rc = launch_binning(c.v, c.P, nullptr, mv->radii, ws, c.L, mv->R_cap, s, false, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
 
   LossK lk;
   lk.mode = MGS_LOSS_MAP_L1; lk.npix = (int)c.npix; lk.use_depth = c.use_depth;

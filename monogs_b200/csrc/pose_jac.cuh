@@ -7,13 +7,50 @@ namespace mgs {
 // B_g layout: NCOL columns (mx, my, cxx, cxy, cyy, depth[, r, g, b]) of 6 floats each, padded to float4s.
 template <int NCOL> struct PoseJac { static constexpr int kFloats = (NCOL * 6 + 3) / 4 * 4; };
 
+// The single-pass tracking blend (blend_track.cu) consumes the map in a folded form: 32 floats = one 128-byte line per
+// Gaussian.  With d = mean2D - pixel, G = exp(power) and s = opacity * G / (1 - alpha), a pixel's pose-tangent
+// contribution through this splat is (backward.cu:986-1010 chained with the columns of B)
+//     vp = s * ( d.x * (U + d.x * A + d.y * Bm)  +  d.y * (V + d.y * Cm) )
+//     U  = -(conic.xx * W/2 * Bx + conic.xy * H/2 * By)      V  = -(conic.xy * W/2 * Bx + conic.yy * H/2 * By)
+//     A  = -1/2 Bxx        Bm = -1/2 Bxy        Cm = -1/2 Byy
+// so the five per-pixel scalars q_k of the column form never have to be formed: 15 packed multiply-adds instead of
+// 15 + ~14 scalar instructions per (pixel, splat).  Floats 30, 31 = y_C, -x_C: the depth column (0, 0, 1, y_C, -x_C, 0).
+constexpr int POSE_BASIS_FLOATS = 32;
+
 template <int NCOL>
-__device__ __forceinline__ void build_pose_jac(const ViewConst& v, const int idx, const float3& p,
+__device__ __forceinline__ void compute_pose_B(const ViewConst& v, const int idx, const float3& p,
                                                const float* __restrict__ shs, const float* __restrict__ scales,
                                                const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
-                                               const uint32_t clamp_mask, float* __restrict__ jac) {
+                                               const uint32_t clamp_mask, float (&B)[PoseJac<NCOL>::kFloats]);
+
+__device__ __forceinline__ void build_pose_basis(const ViewConst& v, const int idx, const float3& p, const float3& conic,
+                                                 const float* __restrict__ scales, const float* __restrict__ rotations,
+                                                 const float* __restrict__ cov3D_precomp, float* __restrict__ basis) {
+  float B[PoseJac<6>::kFloats];
+  compute_pose_B<6>(v, idx, p, nullptr, scales, rotations, cov3D_precomp, 0u, B);
+  const float wx = 0.5f * (float)v.W, wy = 0.5f * (float)v.H;
+  float o[POSE_BASIS_FLOATS];
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    const float bx = wx * B[0 * 6 + k], by = wy * B[1 * 6 + k];
+    o[k] = -(conic.x * bx + conic.y * by);
+    o[6 + k] = -(conic.y * bx + conic.z * by);
+    o[12 + k] = -0.5f * B[2 * 6 + k];
+    o[18 + k] = -0.5f * B[3 * 6 + k];
+    o[24 + k] = -0.5f * B[4 * 6 + k];
+  }
+  o[30] = B[5 * 6 + 3]; o[31] = B[5 * 6 + 4];
+  float4* out = reinterpret_cast<float4*>(basis + (size_t)idx * POSE_BASIS_FLOATS);
+#pragma unroll
+  for (int k = 0; k < POSE_BASIS_FLOATS / 4; k++) out[k] = make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+}
+
+template <int NCOL>
+__device__ __forceinline__ void compute_pose_B(const ViewConst& v, const int idx, const float3& p,
+                                               const float* __restrict__ shs, const float* __restrict__ scales,
+                                               const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
+                                               const uint32_t clamp_mask, float (&B)[PoseJac<NCOL>::kFloats]) {
   constexpr int NF = PoseJac<NCOL>::kFloats;
-  float B[NF];
 #pragma unroll
   for (int k = 0; k < NF; k++) B[k] = 0.f;
   GaussCtx g;
@@ -45,6 +82,16 @@ __device__ __forceinline__ void build_pose_jac(const ViewConst& v, const int idx
       B[(6 + c) * 6 + 0] = -dm.x; B[(6 + c) * 6 + 1] = -dm.y; B[(6 + c) * 6 + 2] = -dm.z;
     }
   }
+}
+
+template <int NCOL>
+__device__ __forceinline__ void build_pose_jac(const ViewConst& v, const int idx, const float3& p,
+                                               const float* __restrict__ shs, const float* __restrict__ scales,
+                                               const float* __restrict__ rotations, const float* __restrict__ cov3D_precomp,
+                                               const uint32_t clamp_mask, float* __restrict__ jac) {
+  constexpr int NF = PoseJac<NCOL>::kFloats;
+  float B[NF];
+  compute_pose_B<NCOL>(v, idx, p, shs, scales, rotations, cov3D_precomp, clamp_mask, B);
   float4* out = reinterpret_cast<float4*>(jac + (size_t)idx * NF);
 #pragma unroll
   for (int k = 0; k < NF / 4; k++) out[k] = make_float4(B[4 * k], B[4 * k + 1], B[4 * k + 2], B[4 * k + 3]);

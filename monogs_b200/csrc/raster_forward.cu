@@ -213,10 +213,110 @@ __device__ __forceinline__ void for_each_tile(const uint2 rmin, const uint2 rmax
   }
 }
 
-// JAC_NCOL 0: plain; 6 / 9: also build the pose Jacobian of visible Gaussians (tracking path).
+// ------------------------------------------------------------------------------------------------
+// Binning.  The reference sorts R 64-bit (tile | depth) keys globally (rasterizer_impl.cu:70-111, 306-311).  Tile ids
+// are a small dense range, so the tile half is a COUNTING sort: per-tile counts (preprocess_kernel) -> exclusive scan
+// (tile ranges, rasterizer_impl.cu:116-138, fall out of it directly) -> scatter of (depth bits << 32 | Gaussian id) into
+// the tile's segment -> per-tile sort of that 64-bit word in shared memory.  The reference's radix sort is stable and its
+// instances are emitted in Gaussian-index order, so ties on (tile, depth) are ordered by index there too: the result
+// is the same permutation, bit for bit.
+// ------------------------------------------------------------------------------------------------
+constexpr int SCAN_THREADS = 1024, LARGE_LIST = 1024;
+// Whole-CTA scan of the per-tile instance counts: tile ranges (clipped to R_cap), scatter cursors, header, the compact
+// list of large tiles and (heavy_first) the launch order of the multi-wave blend kernel.  THREADS = 1024 for the
+// stand-alone tile_scan_kernel; the fused paths run it with the CTA size of preprocess_kernel in that kernel's LAST CTA
+// (FOLD_SCAN), which saves a launch.  Counts are read with ld.global.cg: they were accumulated by L2 atomics of other CTAs.
+template <int THREADS>
+__device__ __noinline__ void tile_scan_body(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_t R_cap,
+                                               uint2* __restrict__ ranges, WsHeader* __restrict__ hdr, const int heavy_first) {
+  constexpr int IPT = 4;                   // THREADS * 4 tiles per sweep; few registers: the body also runs as the tail of preprocess_kernel
+  using Scan = cub::BlockScan<uint32_t, THREADS>;
+  __shared__ typename Scan::TempStorage tmp;
+  __shared__ uint32_t n_large, max_count;
+  if (threadIdx.x == 0) { n_large = 0u; max_count = 0u; }
+  __syncthreads();
+  uint32_t carry = 0;
+  for (int base = 0; base < tiles; base += THREADS * IPT) {
+    const int t0 = base + threadIdx.x * IPT;
+    uint32_t c[IPT], sum = 0u, m = 0u;
+#pragma unroll
+    for (int i = 0; i < IPT; i++) c[i] = t0 + i < tiles ? __ldcg(&tile_ctr[(size_t)(t0 + i) * TILE_CTR_STRIDE]) : 0u;
+#pragma unroll
+    for (int i = 0; i < IPT; i++) { sum += c[i]; m = max(m, c[i]); }
+    m = __reduce_max_sync(0xffffffffu, m);
+    if ((threadIdx.x & 31) == 0 && m > 0u) atomicMax(&max_count, m);
+    uint32_t excl, total;
+    Scan(tmp).ExclusiveSum(sum, excl, total);
+    uint32_t start = carry + excl;
+#pragma unroll
+    for (int i = 0; i < IPT; i++) {
+      const int t = t0 + i;
+      if (t < tiles) {
+        const uint32_t lo = min(start, R_cap), hi = min(start + c[i], R_cap);
+        ranges[t] = (c[i] == 0u) ? make_uint2(0u, 0u) : make_uint2(lo, hi);            // untouched tiles keep {0,0}
+        tile_ctr[(size_t)t * TILE_CTR_STRIDE + 1] = start;
+        if (hi - lo > (uint32_t)LARGE_LIST)
+          tile_ctr[(size_t)atomicAdd(&n_large, 1u) * TILE_CTR_STRIDE + 2] = (uint32_t)t;
+        start += c[i];
+      }
+    }
+    carry += total;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    hdr->num_rendered = carry;
+    hdr->overflow = carry > R_cap ? 1u : 0u;
+    hdr->r_used = carry > R_cap ? R_cap : carry;
+    hdr->n_large = n_large;
+    if (carry > R_cap) hdr->overflow_sticky = 1u;
+    if (carry > hdr->max_rendered) hdr->max_rendered = carry;
+  }
+  // Heavy-first launch order for per-tile kernels that run in several waves (blend_track_kernel: 3 CTAs per SM): a
+  // counting sort of the tiles into 64 buckets of list length, longest lists first, written to
+  // tile_ctr[i * TILE_CTR_STRIDE + 3].  CTAs are dispatched in blockIdx order, so the long tiles start at once and the
+  // short ones fill the tail of the grid instead of the other way round.
+  if (!heavy_first) return;   // only the single-pass tracking blend reads the order (neutral at C3, +1 % at C1 / C2)
+  __shared__ uint32_t bucket[64];
+  if (threadIdx.x < 64) bucket[threadIdx.x] = 0u;
+  __syncthreads();
+  const uint32_t scale = max_count > 0u ? max_count : 1u;
+  for (int t = threadIdx.x; t < tiles; t += THREADS) {
+    const uint32_t c = __ldcg(&tile_ctr[(size_t)t * TILE_CTR_STRIDE]);
+    atomicAdd(&bucket[63u - (uint32_t)(((unsigned long long)c * 63ull) / scale)], 1u);
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {   // exclusive scan of the 64 bucket sizes
+    const uint32_t a = bucket[2 * threadIdx.x], b = bucket[2 * threadIdx.x + 1];
+    uint32_t incl = a + b;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)threadIdx.x >= o) incl += up;
+    }
+    bucket[2 * threadIdx.x] = incl - a - b;
+    bucket[2 * threadIdx.x + 1] = incl - b;
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < tiles; t += THREADS) {
+    const uint32_t c = __ldcg(&tile_ctr[(size_t)t * TILE_CTR_STRIDE]);
+    const uint32_t pos = atomicAdd(&bucket[63u - (uint32_t)(((unsigned long long)c * 63ull) / scale)], 1u);
+    tile_ctr[(size_t)pos * TILE_CTR_STRIDE + 3] = (uint32_t)t;
+  }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_t R_cap,
+                 uint2* __restrict__ ranges, WsHeader* __restrict__ hdr, const int heavy_first) {
+  tile_scan_body<SCAN_THREADS>(tile_ctr, tiles, R_cap, ranges, hdr, heavy_first);
+}
+
+// JAC_NCOL 0: plain; 6 / 9: also build the pose Jacobian of visible Gaussians (two-pass tracking path); 32: the folded
+// 32-float basis of the single-pass tracking blend (pose_jac.cuh).
+// FOLD_SCAN: the last CTA to finish (ticket in the workspace header, which must have been zero-filled once) runs the tile
+// scan in place of a separate tile_scan_kernel launch.
 // STAGE: SH rows of the warp's 32 Gaussians go through shared memory with coalesced 16-byte loads (sh_stage.cuh);
 // sh_rest != nullptr selects the split layout (shs = f_dc [P,1,3], sh_rest = f_rest [P,M-1,3]).
-template <int JAC_NCOL, bool STAGE>
+template <int JAC_NCOL, bool STAGE, bool FOLD_SCAN>
 __global__ void __launch_bounds__(256)
 preprocess_kernel(const ViewConst v, const int P,
                   const float* __restrict__ means3D, const float* __restrict__ opacities,
@@ -226,7 +326,8 @@ preprocess_kernel(const ViewConst v, const int P,
                   int32_t* __restrict__ radii, float* __restrict__ depths, float2* __restrict__ means2D,
                   float4* __restrict__ conic_opacity, float4* __restrict__ rgb4,
                   uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ tile_ctr,
-                  float* __restrict__ jac) {
+                  float* __restrict__ jac, const uint32_t R_cap, uint2* __restrict__ ranges, WsHeader* __restrict__ hdr,
+                  const int heavy_first) {
   extern __shared__ __align__(16) float sh_tile[];
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   int my_radius_i = 0;
@@ -294,7 +395,8 @@ preprocess_kernel(const ViewConst v, const int P,
       const float3 c = sh_to_rgb(v.D, p, v.campos, sh_row, cm);
       rgb4[idx] = make_float4(c.x, c.y, c.z, __uint_as_float(cm));
     }
-    if (JAC_NCOL > 0) build_pose_jac<(JAC_NCOL > 0 ? JAC_NCOL : 6)>(v, idx, p, shs, scales, rotations, cov3D_precomp, cm, jac);
+    if (JAC_NCOL == 32) build_pose_basis(v, idx, p, conic, scales, rotations, cov3D_precomp, jac);
+    else if (JAC_NCOL > 0) build_pose_jac<(JAC_NCOL == 9 ? 9 : 6)>(v, idx, p, shs, scales, rotations, cov3D_precomp, cm, jac);
     depths[idx] = view_z;
     means2D[idx] = pix;
     conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
@@ -312,97 +414,22 @@ preprocess_kernel(const ViewConst v, const int P,
     for (int u = 0; u < 4; u++)
       if (u < cnt) atomicAdd(&tile_ctr[tile[u] * TILE_CTR_STRIDE], 1u);
   });
-}
-
-// ------------------------------------------------------------------------------------------------
-// Binning.  The reference sorts R 64-bit (tile | depth) keys globally (rasterizer_impl.cu:70-111, 306-311).  Tile ids
-// are a small dense range, so the tile half is a COUNTING sort: per-tile counts (above) -> exclusive scan (tile
-// ranges, rasterizer_impl.cu:116-138, fall out of it directly) -> scatter of (depth bits << 32 | Gaussian id) into the
-// tile's segment -> per-tile sort of that 64-bit word in shared memory.  The reference's radix sort is stable and its
-// instances are emitted in Gaussian-index order, so ties on (tile, depth) are ordered by index there too: the result
-// is the same permutation, bit for bit.
-// ------------------------------------------------------------------------------------------------
-constexpr int SCAN_THREADS = 1024, SCAN_IPT = 4, LARGE_LIST = 1024;
-__global__ void __launch_bounds__(SCAN_THREADS)
-tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_t R_cap,
-                 uint2* __restrict__ ranges, WsHeader* __restrict__ hdr, const int heavy_first) {
-  using Scan = cub::BlockScan<uint32_t, SCAN_THREADS>;
-  __shared__ typename Scan::TempStorage tmp;
-  __shared__ uint32_t n_large, max_count;
-  if (threadIdx.x == 0) { n_large = 0u; max_count = 0u; }
-  __syncthreads();
-  uint32_t carry = 0;
-  for (int base = 0; base < tiles; base += SCAN_THREADS * SCAN_IPT) {
-    const int t0 = base + threadIdx.x * SCAN_IPT;
-    uint32_t c[SCAN_IPT], sum = 0u;
-#pragma unroll
-    for (int i = 0; i < SCAN_IPT; i++) c[i] = t0 + i < tiles ? tile_ctr[(size_t)(t0 + i) * TILE_CTR_STRIDE] : 0u;
-#pragma unroll
-    for (int i = 0; i < SCAN_IPT; i++) sum += c[i];
-    {
-      uint32_t m = max(max(c[0], c[1]), max(c[2], c[3]));
-      m = __reduce_max_sync(0xffffffffu, m);
-      if ((threadIdx.x & 31) == 0 && m > 0u) atomicMax(&max_count, m);
-    }
-    uint32_t excl, total;
-    Scan(tmp).ExclusiveSum(sum, excl, total);
-    uint32_t start = carry + excl;
-#pragma unroll
-    for (int i = 0; i < SCAN_IPT; i++) {
-      const int t = t0 + i;
-      if (t < tiles) {
-        const uint32_t lo = min(start, R_cap), hi = min(start + c[i], R_cap);
-        ranges[t] = (c[i] == 0u) ? make_uint2(0u, 0u) : make_uint2(lo, hi);            // untouched tiles keep {0,0}
-        tile_ctr[(size_t)t * TILE_CTR_STRIDE + 1] = start;
-        if (hi - lo > (uint32_t)LARGE_LIST)
-          tile_ctr[(size_t)atomicAdd(&n_large, 1u) * TILE_CTR_STRIDE + 2] = (uint32_t)t;
-        start += c[i];
-      }
-    }
-    carry += total;
+  if constexpr (FOLD_SCAN) {
+    __shared__ int s_last;
+    __threadfence();            // this thread's counter atomics are ordered before the CTA's ticket
     __syncthreads();
-  }
-  if (threadIdx.x == 0) {
-    hdr->num_rendered = carry;
-    hdr->overflow = carry > R_cap ? 1u : 0u;
-    hdr->r_used = carry > R_cap ? R_cap : carry;
-    hdr->n_large = n_large;
-    if (carry > R_cap) hdr->overflow_sticky = 1u;
-    if (carry > hdr->max_rendered) hdr->max_rendered = carry;
-  }
-  // Heavy-first launch order for per-tile kernels that run in several waves (blend_track_kernel: 3 CTAs per SM): a
-  // counting sort of the tiles into 64 buckets of list length, longest lists first, written to
-  // tile_ctr[i * TILE_CTR_STRIDE + 3].  CTAs are dispatched in blockIdx order, so the long tiles start at once and the
-  // short ones fill the tail of the grid instead of the other way round.
-  if (!heavy_first) return;   // only the single-pass tracking blend reads the order (neutral at C3, +1 % at C1 / C2)
-  __shared__ uint32_t bucket[64];
-  if (threadIdx.x < 64) bucket[threadIdx.x] = 0u;
-  __syncthreads();
-  const uint32_t scale = max_count > 0u ? max_count : 1u;
-  for (int t = threadIdx.x; t < tiles; t += SCAN_THREADS) {
-    const uint32_t c = tile_ctr[(size_t)t * TILE_CTR_STRIDE];
-    atomicAdd(&bucket[63u - (uint32_t)(((unsigned long long)c * 63ull) / scale)], 1u);
-  }
-  __syncthreads();
-  if (threadIdx.x < 32) {   // exclusive scan of the 64 bucket sizes
-    const uint32_t a = bucket[2 * threadIdx.x], b = bucket[2 * threadIdx.x + 1];
-    uint32_t incl = a + b;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
-      if ((int)threadIdx.x >= o) incl += up;
+    if (threadIdx.x == 0) s_last = (atomicAdd(&hdr->ticket, 1u) == gridDim.x - 1) ? 1 : 0;
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      if constexpr (STAGE) tile_scan_body<128>(tile_ctr, v.gx * v.gy, R_cap, ranges, hdr, heavy_first);
+      else tile_scan_body<256>(tile_ctr, v.gx * v.gy, R_cap, ranges, hdr, heavy_first);
+      if (threadIdx.x == 0) hdr->ticket = 0u;
     }
-    bucket[2 * threadIdx.x] = incl - a - b;
-    bucket[2 * threadIdx.x + 1] = incl - b;
-  }
-  __syncthreads();
-  for (int t = threadIdx.x; t < tiles; t += SCAN_THREADS) {
-    const uint32_t c = tile_ctr[(size_t)t * TILE_CTR_STRIDE];
-    const uint32_t pos = atomicAdd(&bucket[63u - (uint32_t)(((unsigned long long)c * 63ull) / scale)], 1u);
-    tile_ctr[(size_t)pos * TILE_CTR_STRIDE + 3] = (uint32_t)t;
   }
 }
 
+// (tile_scan_body / tile_scan_kernel are defined above preprocess_kernel, whose last CTA may run the scan itself)
 // scatter: one (depth bits << 32 | id) word per (Gaussian, tile) into the tile's segment, slot taken atomically
 __global__ void __launch_bounds__(256)
 emit_kernel(const int P, const uint32_t R_cap, const int gx, const int gy,
@@ -482,11 +509,14 @@ __global__ void __launch_bounds__(256)
 tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ list,
                          const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                          const float4* __restrict__ rgb4, const float* __restrict__ colors_precomp,
-                         SplatRec* __restrict__ recs, const uint32_t* __restrict__ tile_ctr,
-                         const WsHeader* __restrict__ hdr) {
+                         SplatRec* __restrict__ recs, uint32_t* __restrict__ tile_ctr,
+                         const WsHeader* __restrict__ hdr, const int clear_counts) {
   using Temp = typename cub::BlockMergeSort<unsigned long long, 256, LARGE ? 16 : 4>::TempStorage;
   __shared__ Temp temp;
   if (!LARGE) {
+    // fused loops (tracker, mapping engine) render into the same workspace again and again: the tile's instance counter
+    // is dead once the scan has run, so this CTA leaves it zero for the next preprocess instead of a memset per render
+    if (clear_counts && threadIdx.x == 0) tile_ctr[(size_t)blockIdx.x * TILE_CTR_STRIDE] = 0u;
     const uint2 range = ranges[blockIdx.x];
     const int n = (int)(range.y - range.x);
     if (n == 0 || n > LARGE_LIST) return;
@@ -541,26 +571,41 @@ int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_
 int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
-                      float* jac, int jac_ncol, const float* sh_rest) {
+                      float* jac, int jac_ncol, const float* sh_rest, const FoldScan* fold) {
   if (P == 0) return MGS_OK;
-  MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(ws, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
+  // fold != nullptr: the workspace is one a fused loop renders into repeatedly — its tile counters were left zero by the
+  // previous render's sort kernel (clear_counts) and its header ticket is zero, so no memset and no separate scan launch
+  if (fold == nullptr)
+    MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(ws, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
+  const uint32_t R_cap = fold ? (uint32_t)fold->R_cap : 0u;
+  const int heavy = fold ? (fold->heavy_first ? 1 : 0) : 0;
 #define MGS_PRE_ARGS v, P, means3D, opacities, shs, sh_rest, colors_precomp, scales, rotations, cov3D_precomp, radii,  \
       ws_ptr<float>(ws, L.depths), ws_ptr<float2>(ws, L.means2D), ws_ptr<float4>(ws, L.conic_opacity),               \
-      ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched), ws_ptr<uint32_t>(ws, L.tile_ctr), jac
+      ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched), ws_ptr<uint32_t>(ws, L.tile_ctr), jac, R_cap, \
+      ws_ptr<uint2>(ws, L.ranges), ws_ptr<WsHeader>(ws, L.header), heavy
   // SH rows of more than one coefficient are staged through shared memory (128 threads: 4 tiles of [32][3M | 1] floats)
-  const bool stage = shs != nullptr && colors_precomp == nullptr && v.M > 1;
+  const bool stage = shs != nullptr && colors_precomp == nullptr && v.M > 1 && !(jac != nullptr && jac_ncol == 32);
   if (sh_rest != nullptr && !stage) { set_error("preprocess: split SH layout needs sh_coeffs > 1 and no colors_precomp"); return MGS_EINVAL; }
-  prof_begin("preprocess", s);
+  if (jac != nullptr && jac_ncol == 32 && fold == nullptr) { set_error("preprocess: the folded pose basis is built by the fused SH-degree-0 tracker only"); return MGS_EINVAL; }
+  prof_begin(fold ? "preprocess+scan" : "preprocess", s);
   if (stage) {
     const int T = 128;
     const size_t smem = (size_t)T * sh_row_stride(v.M) * sizeof(float);
-    if (jac == nullptr) preprocess_kernel<0, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
-    else if (jac_ncol == 9) preprocess_kernel<9, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
-    else preprocess_kernel<6, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+    if (fold) {
+      if (jac == nullptr) preprocess_kernel<0, true, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+      else if (jac_ncol == 9) preprocess_kernel<9, true, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+      else { set_error("preprocess: unsupported fused variant"); return MGS_EINVAL; }
+    } else if (jac == nullptr) preprocess_kernel<0, true, false><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+    else if (jac_ncol == 9) preprocess_kernel<9, true, false><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+    else preprocess_kernel<6, true, false><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
   } else {
-    if (jac == nullptr) preprocess_kernel<0, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-    else if (jac_ncol == 9) preprocess_kernel<9, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-    else preprocess_kernel<6, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+    if (fold) {
+      if (jac == nullptr) preprocess_kernel<0, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+      else if (jac_ncol == 32) preprocess_kernel<32, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+      else { set_error("preprocess: unsupported fused variant"); return MGS_EINVAL; }
+    } else if (jac == nullptr) preprocess_kernel<0, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+    else if (jac_ncol == 9) preprocess_kernel<9, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+    else preprocess_kernel<6, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
   }
   prof_end(s);
 #undef MGS_PRE_ARGS
@@ -569,7 +614,7 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
 }
 
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
-                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first, bool scan_done) {
+                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first, bool scan_done, bool clear_counts) {
   const int tiles = v.gx * v.gy;
   if (!scan_done) {
     int rc = launch_tile_scan(v, ws, L, R_cap, s, heavy_first);   // ranges (clipped to R_cap), scatter cursors, header
@@ -582,7 +627,7 @@ int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const
   MGS_LAUNCH_CHECK();
 #define MGS_SORT_ARGS ws_ptr<uint2>(ws, L.ranges), ws_ptr<unsigned long long>(ws, L.list), ws_ptr<float2>(ws, L.means2D), \
       ws_ptr<float4>(ws, L.conic_opacity), ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<SplatRec>(ws, L.records),     \
-      ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<WsHeader>(ws, L.header)
+      ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<WsHeader>(ws, L.header), clear_counts ? 1 : 0
   MGS_PROF("tile_sort_records", s, tile_sort_records_kernel<false><<<tiles, 256, 0, s>>>(MGS_SORT_ARGS));
   MGS_LAUNCH_CHECK();
   MGS_PROF("tile_sort_records_large", s,

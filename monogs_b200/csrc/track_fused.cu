@@ -18,6 +18,7 @@
 #include "loss_pixel.cuh"
 #include "pose_jac.cuh"
 #include "pose_update.cuh"
+#include "track_update.cuh"
 #include <cstring>
 
 namespace mgs {
@@ -25,126 +26,7 @@ namespace mgs {
 int launch_sketch_reduce(const float* rows, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,
                          float* out, cudaStream_t s, int nv);
 
-struct TrackUpdateK {
-  int mode, use_depth, npix, tiles;
-  float alpha, scale;
-  const double* partials; const float* tau_raw;
-  float *loss, *tau, *dab;
-  float *params, *exp_avg, *exp_avg_sq; int* step; float lr[4]; float beta1, beta2, eps;
-  float *T, *view_out, *proj_out; const float* proj_raw; int* converged; float thr;
-  float* lm_state;   // optional (mgs_track_args.lm_state): scalar ||r||_1 and the best-pose record
-};
-
-// lm_state (device f32[64]) — the tracker's cross-iteration record, shared by the first- and second-order iterations
-enum : int {
-  LM_LAMBDA = 0, LM_PREV_SCALAR = 1, LM_HAVE_PREV = 2, LM_PENDING = 3, LM_X = 4 /* 8 floats */, LM_BEST_SCALAR = 12,
-  LM_BEST_T = 13 /* 16 floats */, LM_BEST_A = 29, LM_BEST_B = 30, LM_CONVERGED = 31, LM_ITERS = 32, LM_SCALAR = 33,
-  LM_STEP_NORM = 34, LM_HAVE_BEST = 35
-};
-
-// best_viewpoint_params of the reference (utils/slam_frontend.py:523-531): the pose and exposure the frame was RENDERED
-// with whenever the scalar ||residual||_1 improves.  T: pre-update pose; a, b: pre-update exposure.
-__device__ __forceinline__ void lm_track_best(float* __restrict__ st, const float scalar, const float* __restrict__ T,
-                                              const float a, const float b) {
-  st[LM_SCALAR] = scalar;
-  if (st[LM_HAVE_BEST] == 0.f || scalar < st[LM_BEST_SCALAR]) {
-    st[LM_HAVE_BEST] = 1.f; st[LM_BEST_SCALAR] = scalar;
-#pragma unroll
-    for (int i = 0; i < 16; i++) st[LM_BEST_T + i] = T[i];
-    st[LM_BEST_A] = a; st[LM_BEST_B] = b;
-  }
-}
-
-// One CTA.  Everything the serial tail needs is staged in shared memory by separate threads while the per-tile partials
-// are being reduced (a single thread chasing ~60 dependent global loads and stores costs an L2 round trip each), the
-// double-precision bias corrections are computed by another warp meanwhile, and the results go out in parallel.
-__global__ void __launch_bounds__(256) track_update_kernel(const TrackUpdateK k) {
-  __shared__ double red[8][4];
-  __shared__ float s_in[64];     // [0,6) tau_raw  [8,16) exp_avg  [16,24) exp_avg_sq  [24,32) params  [32,48) T  [48,64) proj_raw
-  __shared__ float s_out[72];    // [0,6) tau [6,8) dab [8,16) exp_avg [16,24) exp_avg_sq [24,32) params [32,48) T [48,64) view [64] loss
-  __shared__ float s_proj[16];
-  __shared__ float s_bc[2];
-  __shared__ int s_conv;
-  const int tid = threadIdx.x;
-  if (tid < 6) s_in[tid] = k.tau_raw[tid];
-  else if (tid >= 8 && tid < 16) s_in[tid] = k.exp_avg[tid - 8];
-  else if (tid >= 16 && tid < 24) s_in[tid] = k.exp_avg_sq[tid - 16];
-  else if (tid >= 24 && tid < 32) s_in[tid] = k.params[tid - 24];
-  else if (tid >= 32 && tid < 48) s_in[tid] = k.T[tid - 32];
-  else if (tid >= 48 && tid < 64) s_in[tid] = k.proj_raw ? k.proj_raw[tid - 48] : 0.f;
-  else if (tid == 64) {
-    const double t = (double)(k.step[0] + 1);
-    k.step[0] += 1;
-    s_bc[0] = (float)(1.0 - pow((double)k.beta1, t));
-    s_bc[1] = (float)sqrt(1.0 - pow((double)k.beta2, t));
-  }
-  double acc[4] = {0, 0, 0, 0};
-  const double2* p2 = reinterpret_cast<const double2*>(k.partials);
-#pragma unroll 4
-  for (int i = tid; i < k.tiles; i += 256) {
-    const double2 a = p2[2 * i], b = p2[2 * i + 1];
-    acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y;
-  }
-#pragma unroll
-  for (int q = 0; q < 4; q++) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc[q] += __shfl_xor_sync(0xffffffffu, acc[q], o);
-    if ((tid & 31) == 0) red[tid >> 5][q] = acc[q];
-  }
-  __syncthreads();
-  if (tid == 0) {
-    double tot[4];
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-      double t = 0;
-#pragma unroll
-      for (int w = 0; w < 8; w++) t += red[w][q];
-      tot[q] = t;
-    }
-    float gscale = 1.f;
-    if (k.mode == MGS_LOSS_TRACK_HUBER) {
-      const float nrm = (float)sqrt(tot[0]);
-      s_out[64] = k.scale * nrm;
-      gscale = nrm > 0.f ? k.scale / nrm : 0.f;
-    } else {
-      const double rgb = tot[0] / (3.0 * k.npix), dep = tot[3] / (double)k.npix;
-      s_out[64] = (float)(k.scale * (k.use_depth ? k.alpha * rgb + (1.0 - k.alpha) * dep : rgb));
-    }
-    if (k.lm_state != nullptr && k.mode == MGS_LOSS_TRACK_HUBER) lm_track_best(k.lm_state, (float)tot[3], s_in + 32, s_in[30], s_in[31]);
-    float g[8];
-#pragma unroll
-    for (int i = 0; i < 6; i++) { g[i] = s_in[i] * gscale; s_out[i] = g[i]; }
-    g[6] = (float)tot[1] * gscale; g[7] = (float)tot[2] * gscale;
-    s_out[6] = g[6]; s_out[7] = g[7];
-    // Adam (torch.optim.Adam, eps outside the bias-corrected sqrt) on [rho(3), theta(3), a, b]
-    const float bc1 = s_bc[0], bc2s = s_bc[1];
-#pragma unroll
-    for (int i = 0; i < 8; i++) {
-      const float lr = k.lr[i < 3 ? 0 : (i < 6 ? 1 : i - 4)];
-      float m = s_in[8 + i], v = s_in[16 + i];
-      m = m + (g[i] - m) * (1.f - k.beta1);
-      v = v * k.beta2 + (1.f - k.beta2) * g[i] * g[i];
-      const float denom = sqrtf(v) / bc2s + k.eps;
-      s_out[24 + i] = s_in[24 + i] - (lr / bc1) * (m / denom);
-      s_out[8 + i] = m; s_out[16 + i] = v;
-    }
-#pragma unroll
-    for (int i = 0; i < 16; i++) s_out[32 + i] = s_in[32 + i];
-    pose_update_dev(s_out + 32, s_out + 24, s_out + 27, k.proj_raw ? s_in + 48 : nullptr, k.view_out ? s_out + 48 : nullptr,
-                    k.proj_out ? s_proj : nullptr, k.converged ? &s_conv : nullptr, k.thr);
-  }
-  __syncthreads();
-  if (tid < 6) k.tau[tid] = s_out[tid];
-  else if (tid < 8) k.dab[tid - 6] = s_out[tid];
-  else if (tid < 16) k.exp_avg[tid - 8] = s_out[tid];
-  else if (tid < 24) k.exp_avg_sq[tid - 16] = s_out[tid];
-  else if (tid < 32) k.params[tid - 24] = s_out[tid];
-  else if (tid < 48) k.T[tid - 32] = s_out[tid];
-  else if (tid < 64) { if (k.view_out) k.view_out[tid - 48] = s_out[tid]; }
-  else if (tid < 80) { if (k.view_out && k.proj_out && k.proj_raw) k.proj_out[tid - 64] = s_proj[tid - 64]; }
-  else if (tid == 80) k.loss[0] = s_out[64];
-  else if (tid == 81) { if (k.converged) k.converged[0] = s_conv; }
-}
+__global__ void __launch_bounds__(256) track_update_kernel(const TrackUpdateK k) { track_update_body(k); }
 
 // ---- second-order (sketched Gauss-Newton / Levenberg-Marquardt) iteration, utils/slam_frontend.py:455-720 with
 //      in_second_order == True.  The reference applies the step of iteration k at the START of iteration k+1
@@ -299,12 +181,16 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   void* ws = t->workspace;
   if (t->status_out) MGS_CUDA_TRY(cudaMemcpyAsync(t->status_out, ws, 6 * sizeof(uint32_t), cudaMemcpyDefault, s));   // of the PREVIOUS iteration
 
+  // The workspace and the scratch of a tracker are zero-filled ONCE by their owner: tile counters, the scan ticket, the
+  // tangent accumulator and the update ticket are all left zero by the iteration that used them (the sort kernel clears
+  // its tile's counter, the folded tails reset their tickets and tau_raw), so an iteration is 5 kernels and no memset.
+  const FoldScan fs{t->R_cap, /*heavy_first=*/!with_color};
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
-                              ws, L, s, jac, with_color ? 9 : 6)))
+                              ws, L, s, jac, with_color ? 9 : 32, nullptr, &fs)))
     return rc;
   if (!t->fast_math) MGS_CUDA_TRY(cudaMemsetAsync(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
-  MGS_CUDA_TRY(cudaMemsetAsync(tau_raw, 0, 6 * sizeof(float), s));
-  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, /*heavy_first=*/!with_color))) return rc;
+  if (with_color) MGS_CUDA_TRY(cudaMemsetAsync(tau_raw, 0, 6 * sizeof(float), s));
+  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, fs.heavy_first, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
 
   LossK lk;
   lk.mode = t->loss_mode; lk.npix = (int)npix; lk.use_depth = use_depth;
@@ -315,20 +201,6 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   fl.k = &lk;
   fl.grad_scale = (t->loss_mode == MGS_LOSS_TRACK_HUBER) ? 1.f : (use_depth ? t->alpha : 1.f) / (3.f * (float)npix);
   fl.g_img = g_img; fl.g_depth = use_depth ? g_depth : nullptr; fl.partials = partials; fl.fast = t->fast_math != 0;
-  if (!with_color) {
-    // SH degree 0: colours do not depend on the pose -> forward, loss and pose tangent in one pass over the tile lists
-    if ((rc = launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
-                                 tau_raw, s)))
-      return rc;
-  } else {
-    if ((rc = launch_blend_forward(v, ws, L, t->out_color, t->out_depth, t->out_opacity, t->fast_math ? nullptr : t->n_touched, s, &fl))) return rc;
-    BackwardArgs a;
-    memset(&a, 0, sizeof(a));
-    a.v = v; a.P = P; a.grad_mask = MGS_GRAD_TAU; a.ws = ws; a.L = L;
-    a.dL_dcolor_img = g_img; a.dL_ddepth_img = use_depth ? g_depth : nullptr; a.dL_dtau_sum = tau_raw;
-    if ((rc = launch_blend_backward_pose(a, jac, with_color, s, t->fast_math != 0))) return rc;
-  }
-
   TrackUpdateK k;
   k.mode = t->loss_mode; k.use_depth = use_depth; k.npix = (int)npix; k.tiles = tiles; k.alpha = t->alpha; k.scale = 1.f;
   k.partials = partials; k.tau_raw = tau_raw; k.loss = t->loss; k.tau = t->tau; k.dab = t->dab;
@@ -338,6 +210,19 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   k.T = t->T_w2c; k.view_out = const_cast<float*>(view->viewmatrix); k.proj_out = const_cast<float*>(view->projmatrix);
   k.proj_raw = view->projmatrix_raw; k.converged = t->converged; k.thr = t->converged_threshold;
   k.lm_state = t->lm_state;
+  if (!with_color) {
+    // SH degree 0: colours do not depend on the pose -> forward, loss and pose tangent in one pass over the tile lists,
+    // and the iteration's serial tail (loss norm, Adam, pose update) in that kernel's last CTA
+    uint32_t* ticket = reinterpret_cast<uint32_t*>(tau_raw + 8);
+    return launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
+                              tau_raw, s, nullptr, 0.f, nullptr, &k, ticket);
+  }
+  if ((rc = launch_blend_forward(v, ws, L, t->out_color, t->out_depth, t->out_opacity, t->fast_math ? nullptr : t->n_touched, s, &fl))) return rc;
+  BackwardArgs a;
+  memset(&a, 0, sizeof(a));
+  a.v = v; a.P = P; a.grad_mask = MGS_GRAD_TAU; a.ws = ws; a.L = L;
+  a.dL_dcolor_img = g_img; a.dL_ddepth_img = use_depth ? g_depth : nullptr; a.dL_dtau_sum = tau_raw;
+  if ((rc = launch_blend_backward_pose(a, jac, with_color, s, t->fast_math != 0))) return rc;
   MGS_PROF("track_update", s, track_update_kernel<<<1, 256, 0, s>>>(k));
   MGS_LAUNCH_CHECK();
   return MGS_OK;
@@ -386,11 +271,12 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   k.conv_thr = a->converged_threshold; k.loss_out = t->loss;
   MGS_PROF("track2_begin", s, track2_begin_kernel<<<1, 32, 0, s>>>(k));
   MGS_LAUNCH_CHECK();
+  const FoldScan fs{t->R_cap, /*heavy_first=*/true};
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
-                              ws, L, s, jac, 6)))
+                              ws, L, s, jac, 32, nullptr, &fs)))
     return rc;
   if (!t->fast_math) MGS_CUDA_TRY(cudaMemsetAsync(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
-  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, /*heavy_first=*/true))) return rc;
+  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
   LossK lk;
   lk.mode = MGS_LOSS_TRACK_HUBER; lk.npix = (int)npix; lk.use_depth = 0;
   lk.thr = t->rgb_boundary_threshold; lk.alpha = t->alpha; lk.delta = t->huber_delta; lk.scale = 1.f; lk.eps = 1e-8f;

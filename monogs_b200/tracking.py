@@ -15,8 +15,9 @@ import torch
 from . import _lib as L
 from .rasterizer import make_view, GaussianRasterizationSettings, _stream
 
-KERNELS_PER_ITER = 7    # own kernels per fused iteration (SH degree 0): preprocess(+jac, +tile counts), tile_scan, emit,
-                        # tile_sort_records x2 (short / long lists), blend_track (forward+loss+pose tangent), track_update
+KERNELS_PER_ITER = 5    # own kernels per fused iteration (SH degree 0): preprocess (+ pose basis, tile counts and, in its last
+                        # CTA, the tile scan), emit, tile_sort_records x2 (short / long lists), blend_track (forward + loss +
+                        # pose tangent and, in its last CTA, loss norm + Adam + pose update)
 KERNELS_PER_ITER_COMPOSED = 14
 
 
@@ -68,7 +69,8 @@ class PoseTracker:
         self.bwd_scratch = torch.empty(max(lib.mgs_raster_backward_pose_scratch_bytes(self.P, self.W, self.H), 256),
                                        device=dev, dtype=torch.uint8)
         self.fused, self.fast_math = fused, fast_math
-        self.track_scratch = torch.empty(lib.mgs_track_scratch_bytes(self.P, self.W, self.H), device=dev, dtype=torch.uint8)
+        # zero-filled once: holds the tangent accumulator and the update ticket, which every iteration leaves zero again
+        self.track_scratch = torch.zeros(lib.mgs_track_scratch_bytes(self.P, self.W, self.H), device=dev, dtype=torch.uint8)
         self.headroom = capacity_headroom
         self.R_cap, self.ws = 0, None
         self.use_graph, self.graph = use_graph, None
@@ -327,7 +329,7 @@ class PoseTracker:
             self.projmatrix.copy_(self.viewmatrix @ self.proj_raw)
         self.lm_state[3] = 0.0
 
-    def bind_host(self, gt_host, loss_host, tau_host):
+    def bind_host(self, gt_host, loss_host, tau_host, gt_depth_host=None):
         """Host-resident frame in, loss + pose tangent out, one graph launch per iteration (step_host()).
         gt_host [3,H,W], loss_host [S] and tau_host [S,6] (or [6] when S = 1) are pinned host tensors.  The captured graph is
             gt_image <- staging;  { the iteration's kernels  ||  staging <- gt_host on a second stream };
@@ -339,11 +341,17 @@ class PoseTracker:
         S = 2 result slots enable step_host_lagged(): iteration k is launched before the host waits for iteration
         k-1, so the GPU never idles while the host turns around (one graph per slot, used alternately)."""
         assert gt_host.is_pinned() and loss_host.is_pinned() and tau_host.is_pinned()
-        self._host_bind = (gt_host, loss_host, tau_host)
+        assert (gt_depth_host is not None) == (self.gt_depth is not None), "a depth tracker takes a pinned depth frame too"
+        self._host_bind = (gt_host, loss_host, tau_host, gt_depth_host)
         S = loss_host.numel()
         tau_slots = tau_host.view(S, 6)
         self._stage = torch.empty_like(self.gt_image)
         self._stage.copy_(gt_host, non_blocking=True)
+        self._stage_depth = None
+        if gt_depth_host is not None:
+            assert gt_depth_host.is_pinned()
+            self._stage_depth = torch.empty_like(self.gt_depth)
+            self._stage_depth.copy_(gt_depth_host, non_blocking=True)
         torch.cuda.synchronize()
         side = torch.cuda.Stream(device=self.dev)
         self.host_graphs, self._host_ev, self._host_k = [], [torch.cuda.Event() for _ in range(S)], 0
@@ -352,9 +360,13 @@ class PoseTracker:
             with torch.cuda.graph(g):
                 main = torch.cuda.current_stream(self.dev)
                 self.gt_image.copy_(self._stage, non_blocking=True)
+                if self._stage_depth is not None:
+                    self.gt_depth.copy_(self._stage_depth, non_blocking=True)
                 side.wait_stream(main)
                 with torch.cuda.stream(side):
                     self._stage.copy_(gt_host, non_blocking=True)
+                    if self._stage_depth is not None:
+                        self._stage_depth.copy_(gt_depth_host, non_blocking=True)
                 self._enqueue()
                 loss_host[slot:slot + 1].copy_(self.loss, non_blocking=True)
                 tau_slots[slot].copy_(self.tau, non_blocking=True)
