@@ -195,6 +195,9 @@ size_t mgs_loss_scratch_bytes(int32_t H, int32_t W);
 typedef struct mgs_adam_group {
   float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
   int64_t numel; float lr;
+  const float* lr_device;   /* optional device f32[1]: when non-null the learning rate is read from it at run time instead
+                             * of `lr`, so a schedule (GaussianModel.update_learning_rate, gaussian_model.py:298-312: the xyz
+                             * rate changes every iteration) works under CUDA-graph replay */
 } mgs_adam_group;
 int mgs_adam_step(const mgs_adam_group* groups /* host array */, int32_t n_groups, int32_t step /* t>=1 */,
                   float beta1, float beta2, float eps, void* stream);
@@ -354,6 +357,30 @@ int mgs_map_view_backward(const mgs_map_args* args, const mgs_map_view* view, vo
  * weight * mean|s - mean(s)| once (weight = 10 in the reference). */
 int mgs_map_end(const mgs_map_args* args, int32_t add_regulariser, float regulariser_weight, void* stream);
 
+/* Window poses of a mapping iteration: keyframe_optimizers.step() followed by update_pose(viewpoint) for the keyframes
+ * being optimised (utils/slam_backend.py:325-332; optimiser built at :437-489 — torch.optim.Adam with its default eps,
+ * cam_rot_delta / cam_trans_delta at half the tracking rates, exposure a / b at 0.01).  One call handles all the views a
+ * rank owns (n <= 16): Adam on (rho, theta, a, b) with the view's tau / dab of mgs_map_view_backward, T <- Exp(rho, theta) T,
+ * rho = theta = 0, and the view's viewmatrix / projmatrix rewritten in place so that the next iteration renders from the
+ * new pose without a host round trip.  gather_out (optional, f32[20] = T | a | b | 0 | 0) is the owner's contribution to
+ * the pose all-gather of a sharded window: it points into the trailing sum-only segment of the gradient arena, the other
+ * ranks contribute zeros there, and the one exchange of the iteration (NCCL all-reduce or mgs_peer_reduce_adam) leaves
+ * every pose on every rank.  frozen = 1 (the first keyframe, uid 0): no step, matrices and gather_out still written. */
+typedef struct mgs_pose_slot {
+  float* T_w2c;             /* f32[4,4] row-major, in/out */
+  float* params;            /* f32[8]: rho, theta, exposure a, b; in/out */
+  float* exp_avg; float* exp_avg_sq;   /* f32[8] each */
+  int32_t* step;            /* device i32[1]: Adam step count of this view's optimiser */
+  const float* tau;         /* f32[6]: d loss / d (rho, theta) of this iteration */
+  const float* dab;         /* f32[2]: d loss / d (a, b) */
+  float* viewmatrix; float* projmatrix;   /* f32[16] each, optional */
+  float* gather_out;        /* f32[20], optional */
+  float lr[4];              /* rho, theta, a, b */
+  int32_t frozen;
+} mgs_pose_slot;
+int mgs_window_pose_step(const mgs_pose_slot* slots /* host array */, int32_t n, const float* proj_raw /* device f32[16] */,
+                         float beta1, float beta2, float eps, void* stream);
+
 /* ---- peer-memory exchange of the data-parallel mapping step.  The reference has no multi-GPU path
  *      (BackEnd.map, utils/slam_backend.py:157-333, renders the whole window on one GPU and calls
  *      torch.optim.Adam.step, gaussian_model.py:285); in the sharded window every rank holds gradients of its own views
@@ -378,13 +405,15 @@ typedef struct mgs_peer_exchange {
   int32_t world, rank;                      /* 1..MGS_PEER_MAX ranks; entries [0, world) of the tables are used */
   float* param_arena[MGS_PEER_MAX];         /* f32[numel] of every rank, as mapped in THIS process; [rank] is local */
   const float* grad_arena[MGS_PEER_MAX];    /* f32[numel], same layout */
-  float* loss_out[MGS_PEER_MAX];            /* f32[4] per rank: receives the summed loss segment */
+  float* loss_out[MGS_PEER_MAX];            /* per rank, as many floats as the trailing sum-only segment(s) hold (>= 4):
+                                             * receives their sums — the iteration's loss, and whatever else rides along
+                                             * (the window poses each owner contributes, zeros elsewhere) */
   uint32_t* flags[MGS_PEER_MAX];            /* mgs_peer_flags_bytes() per rank */
   float* exp_avg; float* exp_avg_sq;        /* local f32[numel]; only this rank's slice is read and written */
   int64_t numel;                            /* arena length in floats, multiple of 4 */
   int32_t n_segments;                       /* consecutive segments covering [0, numel): one per parameter tensor */
   int64_t segment_end[MGS_PEER_MAX_SEGMENTS];   /* exclusive ends in floats, multiples of 4 */
-  float segment_lr[MGS_PEER_MAX_SEGMENTS];      /* learning rate of the segment; < 0: sum only (the loss element) */
+  float segment_lr[MGS_PEER_MAX_SEGMENTS];      /* learning rate of the segment; < 0: sum only (trailing segments only) */
   /* Optional NVSwitch multicast (NVLS) mappings of the same memory — one address that reaches the arena of EVERY rank
    * (cuMulticast* objects; torch.distributed._symmetric_memory provides them).  All three or none.  When given, the
    * gradients are read with multimem.ld_reduce (summed inside the switch, association order unspecified) and the

@@ -39,7 +39,7 @@ class MgsLossArgs(C.Structure):
 class MgsAdamGroup(C.Structure):
     _fields_ = [
         ("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
-        ("numel", C.c_int64), ("lr", C.c_float),
+        ("numel", C.c_int64), ("lr", C.c_float), ("lr_device", C.c_void_p),
     ]
 
 
@@ -99,6 +99,14 @@ class MgsMapView(C.Structure):
         ("radii", C.c_void_p), ("n_touched", C.c_void_p),
         ("tau", C.c_void_p), ("dab", C.c_void_p), ("loss", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("R_cap", C.c_int64),
+    ]
+
+
+class MgsPoseSlot(C.Structure):
+    _fields_ = [
+        ("T_w2c", C.c_void_p), ("params", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+        ("step", C.c_void_p), ("tau", C.c_void_p), ("dab", C.c_void_p), ("viewmatrix", C.c_void_p),
+        ("projmatrix", C.c_void_p), ("gather_out", C.c_void_p), ("lr", C.c_float * 4), ("frozen", C.c_int32),
     ]
 
 
@@ -183,6 +191,7 @@ SIGNATURES = {
     "mgs_map_view_forward": (C.c_int, [C.POINTER(MgsMapArgs), C.POINTER(MgsMapView), _P]),
     "mgs_map_view_backward": (C.c_int, [C.POINTER(MgsMapArgs), C.POINTER(MgsMapView), _P]),
     "mgs_map_end": (C.c_int, [C.POINTER(MgsMapArgs), _I32, _F, _P]),
+    "mgs_window_pose_step": (C.c_int, [C.POINTER(MgsPoseSlot), _I32, _P, _F, _F, _F, _P]),
     "mgs_peer_alloc": (C.c_int, [_SZ, C.POINTER(C.c_void_p)]),
     "mgs_peer_free": (C.c_int, [_P]),
     "mgs_peer_export": (C.c_int, [_P, C.c_char_p]),

@@ -19,7 +19,7 @@ constexpr int FWD_THREADS = 128;
 
 template <bool FUSED_LOSS, bool FAST, bool TOUCH>   // FAST: ex2.approx exponent; TOUCH: n_touched produced
 __global__ void __launch_bounds__(FWD_THREADS)
-blend_forward_kernel(const int W, const int H, const int gx,
+blend_forward_kernel(const int W, const int H, const int gx, const uint32_t* __restrict__ tile_order,
                      const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
                      const float* __restrict__ bg,
                      float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
@@ -31,7 +31,9 @@ blend_forward_kernel(const int W, const int H, const int gx,
   __shared__ __align__(8) uint64_t full_bar[FWD_STAGES];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tile = blockIdx.x;
+  // tile_order != null: longest tile lists first (tile_scan_body, heavy_first) — the grid of a single view is ~1.4 waves,
+  // and the partial last wave then holds the SHORTEST lists instead of whatever the raster order left for it
+  const int tile = tile_order != nullptr ? (int)tile_order[(size_t)blockIdx.x * TILE_CTR_STRIDE + 3] : (int)blockIdx.x;
   const int tx = tile % gx, ty = tile / gx;
   const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
   const int py0 = ty * TILE_Y + (warp >> 1) * 8 + (lane >> 3), py1 = py0 + 4;
@@ -142,16 +144,17 @@ blend_forward_kernel(const int W, const int H, const int gx,
 }
 
 int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
-                         float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl) {
+                         float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl, bool heavy_first) {
   const int tiles = v.gx * v.gy;
+  const uint32_t* order = heavy_first ? ws_ptr<uint32_t>(ws, L.tile_ctr) : nullptr;
   prof_begin("blend_forward", s);
   if (fl == nullptr) {
     LossK none{};
     blend_forward_kernel<false, false, true><<<tiles, FWD_THREADS, 0, s>>>(
-        v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
+        v.W, v.H, v.gx, order, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
         ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, none, 0.f, nullptr, nullptr, nullptr);
   } else {
-#define MGS_FWD_ARGS v.W, v.H, v.gx, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg,                  \
+#define MGS_FWD_ARGS v.W, v.H, v.gx, order, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg,           \
         ws_ptr<float>(ws, L.final_T), ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, \
         *fl->k, fl->grad_scale, fl->g_img, fl->g_depth, fl->partials
     if (fl->fast && n_touched == nullptr) blend_forward_kernel<true, true, false><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);

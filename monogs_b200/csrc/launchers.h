@@ -20,7 +20,8 @@ struct LossK;
 // optional fused loss epilogue of the forward blend (tracking path): per-pixel loss + un-normalised gradient images
 struct FusedLoss { const LossK* k; float grad_scale; float* g_img; float* g_depth; double* partials; bool fast; };
 int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
-                         float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl = nullptr);
+                         float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl = nullptr,
+                         bool heavy_first = false);
 
 // single-pass tracking blend (blend_track.cu): forward + loss + pose tangent; SH degree 0 / 6-column Jacobians only
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
@@ -44,6 +45,7 @@ struct BackwardArgs {
   // ([P,1,3]) and dL_dsh_rest ([P,M-1,3]).  Null = one array [P,M,3].
   const float* sh_rest = nullptr; float* dL_dsh_rest = nullptr;
   bool fast = false;   // blend_backward_full only: exponent variant of the forward that produced ws (blend_exp<FAST>)
+  bool heavy_first = false;   // blend_backward_full only: walk the tiles in the scan's heavy-first order (tile_ctr[.. + 3])
   // sketch mode (sketch_dim > 0): per-pixel row routing, output sketch_dtau[d,6]
   int sketch_dim; const int32_t* sketch_indices; float* sketch_dtau;
 };

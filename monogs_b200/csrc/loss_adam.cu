@@ -4,6 +4,7 @@
 // Adam semantics: torch.optim.Adam(eps=1e-15, betas=(0.9,0.999)) as set up in
 // gaussian_splatting/scene/gaussian_model.py:285 and utils/slam_frontend.py:453.
 #include "launchers.h"
+#include <cstring>
 #include "loss_pixel.cuh"
 #include "adam_elem.cuh"
 
@@ -74,6 +75,7 @@ constexpr int ADAM_CHUNK = 2048;   // elements per block (256 threads x 2 float4
 struct AdamPack {
   float* p[ADAM_MAX_GROUPS]; const float* g[ADAM_MAX_GROUPS]; float* m[ADAM_MAX_GROUPS]; float* v[ADAM_MAX_GROUPS];
   long long numel[ADAM_MAX_GROUPS]; float lr[ADAM_MAX_GROUPS]; int chunk_start[ADAM_MAX_GROUPS + 1];
+  const float* lr_dev[ADAM_MAX_GROUPS];   // non-null: the group's learning rate is read from device memory at run time
   int n;
   float beta1, beta2, eps, bc1, bc2_sqrt;
   const int* step_dev;   // when non-null the step number is *step_dev + 1 and bc1/bc2_sqrt are derived on device
@@ -100,7 +102,7 @@ __global__ void __launch_bounds__(256) adam_kernel(const __grid_constant__ AdamP
   const long long n = a.numel[gi];
   float* __restrict__ p = a.p[gi]; const float* __restrict__ g = a.g[gi];
   float* __restrict__ m = a.m[gi]; float* __restrict__ v = a.v[gi];
-  const float step_size = a.lr[gi] / bc1;
+  const float step_size = (a.lr_dev[gi] != nullptr ? __ldg(a.lr_dev[gi]) : a.lr[gi]) / bc1;
   const bool vec = ((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0);
 #pragma unroll
   for (int it = 0; it < ADAM_CHUNK / 1024; it++) {
@@ -193,6 +195,7 @@ static int adam_impl(const mgs_adam_group* groups, int32_t n_groups, int32_t ste
   cudaStream_t s = (cudaStream_t)stream;
   for (int g0 = 0; g0 < n_groups; g0 += ADAM_MAX_GROUPS) {
     AdamPack a;
+    memset(&a, 0, sizeof(a));
     a.n = 0; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.step_dev = step_dev;
     a.bc1 = (float)(1.0 - pow((double)beta1, (double)step));
     a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
@@ -202,7 +205,7 @@ static int adam_impl(const mgs_adam_group* groups, int32_t n_groups, int32_t ste
       if (G.numel < 0 || (G.numel > 0 && (!G.param || !G.grad || !G.exp_avg || !G.exp_avg_sq))) { set_error("adam: group %d has null pointers", gi); return MGS_EINVAL; }
       if (G.numel == 0) continue;
       const int j = a.n++;
-      a.p[j] = G.param; a.g[j] = G.grad; a.m[j] = G.exp_avg; a.v[j] = G.exp_avg_sq; a.numel[j] = G.numel; a.lr[j] = G.lr;
+      a.p[j] = G.param; a.g[j] = G.grad; a.m[j] = G.exp_avg; a.v[j] = G.exp_avg_sq; a.numel[j] = G.numel; a.lr[j] = G.lr; a.lr_dev[j] = G.lr_device;
       a.chunk_start[j] = chunks;
       chunks += (int)((G.numel + ADAM_CHUNK - 1) / ADAM_CHUNK);
     }

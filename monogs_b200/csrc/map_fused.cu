@@ -13,6 +13,7 @@
 // iteration instead of O(P) torch kernels per view.
 #include "launchers.h"
 #include "loss_pixel.cuh"
+#include "pose_update.cuh"
 #include <cstring>
 
 namespace mgs {
@@ -148,6 +149,54 @@ map_end_kernel(const mgs_gaussians g, const MapScratch m, float* __restrict__ gr
   }
 }
 
+// Window poses: keyframe_optimizers.step() + update_pose() of BackEnd.map (utils/slam_backend.py:325-332) for the views a
+// rank owns.  One CTA per view; thread 0 runs the 8-parameter Adam (torch.optim.Adam, eps outside the bias-corrected
+// sqrt) and T <- Exp(rho, theta) T, then the view / projection matrices go out in parallel.
+constexpr int POSE_SLOTS_MAX = 16;
+struct PoseSlots { mgs_pose_slot s[POSE_SLOTS_MAX]; const float* proj_raw; float beta1, beta2, eps; };
+
+__global__ void __launch_bounds__(32) window_pose_step_kernel(const PoseSlots k) {
+  const mgs_pose_slot& p = k.s[blockIdx.x];
+  __shared__ float sT[16], sP[8], sView[16], sProj[16], sPr[16];
+  const int tid = threadIdx.x;
+  if (tid < 16) { sT[tid] = p.T_w2c[tid]; sPr[tid] = k.proj_raw[tid]; }
+  if (tid < 8) sP[tid] = p.params[tid];
+  __syncwarp();
+  if (tid == 0 && !p.frozen) {
+    const double t = (double)(p.step[0] + 1);
+    p.step[0] += 1;
+    const float bc1 = (float)(1.0 - pow((double)k.beta1, t)), bc2s = (float)sqrt(1.0 - pow((double)k.beta2, t));
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const float g = i < 6 ? p.tau[i] : p.dab[i - 6];
+      const float lr = p.lr[i < 3 ? 0 : (i < 6 ? 1 : i - 4)];
+      float m = p.exp_avg[i], v = p.exp_avg_sq[i];
+      m = m + (g - m) * (1.f - k.beta1);
+      v = v * k.beta2 + (1.f - k.beta2) * g * g;
+      const float denom = sqrtf(v) / bc2s + k.eps;
+      sP[i] = sP[i] - (lr / bc1) * (m / denom);
+      p.exp_avg[i] = m; p.exp_avg_sq[i] = v;
+    }
+    pose_update_dev(sT, sP, sP + 3, sPr, sView, sProj, nullptr, 0.f);
+  } else if (tid == 0) {
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) sView[4 * i + j] = sT[4 * j + i];
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) {
+      float acc = 0.f;
+      for (int q = 0; q < 4; q++) acc += sT[4 * q + i] * sPr[4 * q + j];
+      sProj[4 * i + j] = acc;
+    }
+  }
+  __syncwarp();
+  if (tid < 16) {
+    p.T_w2c[tid] = sT[tid];
+    if (p.viewmatrix) p.viewmatrix[tid] = sView[tid];
+    if (p.projmatrix) p.projmatrix[tid] = sProj[tid];
+    if (p.gather_out) p.gather_out[tid] = sT[tid];
+  }
+  if (tid < 8) p.params[tid] = sP[tid];
+  if (p.gather_out && tid >= 16 && tid < 20) p.gather_out[tid] = tid == 16 ? sP[6] : (tid == 17 ? sP[7] : 0.f);
+}
+
 }  // namespace mgs
 
 using namespace mgs;
@@ -239,11 +288,11 @@ int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* st
   void* ws = mv->workspace;
   // the workspace of a mapping engine is zero-filled once by its owner: the scan runs in the last CTA of the preprocess
   // kernel and the sort kernel leaves the tile counters zero for the next view (raster_forward.cu, FoldScan)
-  const FoldScan fs{mv->R_cap, false};
+  const FoldScan fs{mv->R_cap, /*heavy_first=*/true};
   if ((rc = launch_preprocess(c.v, c.P, g.xyz, m.act_opacity, c.shs, nullptr, m.act_scales, m.act_rot, nullptr, mv->radii, ws, c.L, s,
                               nullptr, 0, c.M > 1 ? g.f_rest : nullptr, &fs))) return rc;
   MGS_CUDA_TRY(cudaMemsetAsync(mv->n_touched, 0, (size_t)c.P * sizeof(int32_t), s));
-  if ((rc = launch_binning(c.v, c.P, nullptr, mv->radii, ws, c.L, mv->R_cap, s, false, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
+  if ((rc = launch_binning(c.v, c.P, nullptr, mv->radii, ws, c.L, mv->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
 
   LossK lk;
   lk.mode = MGS_LOSS_MAP_L1; lk.npix = (int)c.npix; lk.use_depth = c.use_depth;
@@ -253,7 +302,7 @@ int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* st
   FusedLoss fl;
   fl.k = &lk; fl.grad_scale = (c.use_depth ? mv->alpha : 1.f) / (3.f * (float)c.npix);
   fl.g_img = m.g_img[c.slot]; fl.g_depth = m.g_depth[c.slot]; fl.partials = m.partials[c.slot]; fl.fast = mv->fast_math != 0;
-  if ((rc = launch_blend_forward(c.v, ws, c.L, mv->out_color, mv->out_depth, mv->out_opacity, mv->n_touched, s, &fl))) return rc;
+  if ((rc = launch_blend_forward(c.v, ws, c.L, mv->out_color, mv->out_depth, mv->out_opacity, mv->n_touched, s, &fl, /*heavy_first=*/true))) return rc;
   MGS_PROF("map_loss_finalize", s, map_loss_finalize_kernel<<<1, 256, 0, s>>>(m.partials[c.slot], c.tiles, (int)c.npix, c.use_depth, mv->alpha,
                                                                              mv->loss, a->loss_total, mv->dab));
   MGS_LAUNCH_CHECK();
@@ -280,12 +329,33 @@ int mgs_map_view_backward(const mgs_map_args* a, const mgs_map_view* mv, void* s
   b.accumulate = mv->concurrent_backward ? 2 : 1;
   if (mv->update_stats) { b.stat_grad_accum = a->xyz_gradient_accum; b.stat_denom = a->denom; b.stat_max_radii = a->max_radii2D; }
   b.fast = mv->fast_math != 0;
+  b.heavy_first = true;     // the order the view's scan left in its workspace
   return launch_backward_full(b, (cudaStream_t)stream);
 }
 
 int mgs_map_view_fwd_bwd(const mgs_map_args* a, const mgs_map_view* mv, void* stream) {
   const int rc = mgs_map_view_forward(a, mv, stream);
   return rc ? rc : mgs_map_view_backward(a, mv, stream);
+}
+
+int mgs_window_pose_step(const mgs_pose_slot* slots, int32_t n, const float* proj_raw, float beta1, float beta2, float eps,
+                         void* stream) {
+  if (n == 0) return MGS_OK;
+  if (!slots || n < 0 || n > POSE_SLOTS_MAX || !proj_raw) { set_error("window_pose_step: 1..%d slots and a projection matrix", POSE_SLOTS_MAX); return MGS_EINVAL; }
+  PoseSlots k;
+  memset(&k, 0, sizeof(k));
+  for (int i = 0; i < n; i++) {
+    const mgs_pose_slot& p = slots[i];
+    if (!p.T_w2c || !p.params || (!p.frozen && (!p.exp_avg || !p.exp_avg_sq || !p.step || !p.tau || !p.dab))) {
+      set_error("window_pose_step: slot %d has null pointers", i); return MGS_EINVAL;
+    }
+    k.s[i] = p;
+  }
+  k.proj_raw = proj_raw; k.beta1 = beta1; k.beta2 = beta2; k.eps = eps;
+  cudaStream_t s = (cudaStream_t)stream;
+  MGS_PROF("window_pose_step", s, window_pose_step_kernel<<<n, 32, 0, s>>>(k));
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
 }
 
 int mgs_map_end(const mgs_map_args* a, int32_t add_regulariser, float regulariser_weight, void* stream) {

@@ -36,7 +36,9 @@ struct PeerPack {
   const float* grad_mc; float* param_mc; float* loss_mc;   // NVSwitch multicast mappings of the same arenas (null: unicast path)
   long long q_begin, q_end;                       // this rank's slice of the arena, in float4 units
   long long seg_end4[MGS_PEER_MAX_SEGMENTS];      // segment ends, float4 units
-  float seg_lr[MGS_PEER_MAX_SEGMENTS];            // < 0: sum only (the loss element)
+  float seg_lr[MGS_PEER_MAX_SEGMENTS];            // < 0: sum only (the trailing side segment: loss, window poses)
+  long long sum_begin4;                           // first float4 of the trailing sum-only segment(s); its sums land at
+                                                  // loss_out + (q - sum_begin4) * 4 on every rank
   float seg_step[MGS_PEER_MAX_SEGMENTS];          // lr / bias correction 1, the step size of the segment
   int n_seg, world, rank;
   uint32_t epoch;
@@ -155,8 +157,8 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_kernel(const __grid_cons
       int sg = 0;
       while (sg + 1 < a.n_seg && q >= a.seg_end4[sg]) sg++;
       const float lr = a.seg_lr[sg];
-      if (lr < 0.f) {                        // the loss element: every rank gets the sum; its parameter slot is unused
-        for (int r = 0; r < a.world; r++) *reinterpret_cast<float4*>(a.loss_out[r]) = S;
+      if (lr < 0.f) {                        // side segment: every rank gets the sum; its parameter slots are unused
+        for (int r = 0; r < a.world; r++) *reinterpret_cast<float4*>(a.loss_out[r] + (q - a.sum_begin4) * 4) = S;
       } else {
         const float step_size = a.seg_step[sg];
         adam_elem(P4[it].x, S.x, M4[it].x, V4[it].x, step_size, co); adam_elem(P4[it].y, S.y, M4[it].y, V4[it].y, step_size, co);
@@ -239,7 +241,7 @@ __global__ void __launch_bounds__(256) peer_reduce_adam_mc_kernel(const __grid_c
       int sg = 0;
       while (sg + 1 < a.n_seg && q >= a.seg_end4[sg]) sg++;
       const float lr = a.seg_lr[sg];
-      if (lr < 0.f) { multimem_st(a.loss_mc, S[u]); continue; }   // the loss element: every rank gets the sum
+      if (lr < 0.f) { multimem_st(a.loss_mc + (q - a.sum_begin4) * 4, S[u]); continue; }   // side segment: every rank gets the sum
       const float step_size = lr / a.bc1;
       adam_elem(P4[u].x, S[u].x, M4[u].x, V4[u].x, step_size, co); adam_elem(P4[u].y, S[u].y, M4[u].y, V4[u].y, step_size, co);
       adam_elem(P4[u].z, S[u].z, M4[u].z, V4[u].z, step_size, co); adam_elem(P4[u].w, S[u].w, M4[u].w, V4[u].w, step_size, co);
@@ -393,6 +395,10 @@ int mgs_peer_reduce_adam(const mgs_peer_exchange* x, int32_t step, uint32_t epoc
     a.seg_end4[sgi] = e / 4; a.seg_lr[sgi] = x->segment_lr[sgi]; prev = e;
   }
   if (prev != x->numel) { set_error("peer_reduce_adam: the segments must cover the arena"); return MGS_EINVAL; }
+  a.sum_begin4 = x->numel / 4;
+  for (int sgi = x->n_segments - 1; sgi >= 0 && x->segment_lr[sgi] < 0.f; sgi--) a.sum_begin4 = sgi > 0 ? x->segment_end[sgi - 1] / 4 : 0;
+  for (int sgi = 0; sgi < x->n_segments; sgi++)
+    if (x->segment_lr[sgi] < 0.f && x->segment_end[sgi] / 4 <= a.sum_begin4) { set_error("peer_reduce_adam: sum-only segments must be the trailing ones"); return MGS_EINVAL; }
   a.n_seg = x->n_segments; a.world = x->world; a.rank = x->rank; a.epoch = epoch;
   a.timeout_ns = (unsigned long long)(x->timeout_ms ? x->timeout_ms : 60000u) * 1000000ull;
   a.m = x->exp_avg; a.v = x->exp_avg_sq;

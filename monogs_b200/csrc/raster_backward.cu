@@ -75,7 +75,7 @@ __device__ __forceinline__ int reduce10_slot(const int lane) {
 // the colour of the previous record the warp processed: warp-uniform, not per-pixel state.
 template <bool FAST>   // FAST: the ex2.approx exponent of a FAST forward (T is recovered with the same alpha)
 __global__ void __launch_bounds__(BWD_THREADS)
-blend_backward_full_kernel(const int W, const int H, const int gx,
+blend_backward_full_kernel(const int W, const int H, const int gx, const uint32_t* __restrict__ tile_order,
                            const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
                            const float* __restrict__ bg, const float* __restrict__ final_T,
                            const uint32_t* __restrict__ n_contrib,
@@ -87,7 +87,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx,
   __shared__ int s_max_contrib;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tile = blockIdx.x;
+  const int tile = tile_order != nullptr ? (int)tile_order[(size_t)blockIdx.x * TILE_CTR_STRIDE + 3] : (int)blockIdx.x;   // heavy first
   const int tx = tile % gx, ty = tile / gx;
   const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
   const int py0 = ty * TILE_Y + (warp >> 1) * 8 + (lane >> 3), py1 = py0 + 4;
@@ -408,7 +408,8 @@ int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   if (a.dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
   const int tiles = v.gx * v.gy;
   prof_begin("blend_backward_full", s);
-#define MGS_BWD_ARGS v.W, v.H, v.gx, ws_ptr<uint2>(a.ws, a.L.ranges), ws_ptr<SplatRec>(a.ws, a.L.records), v.bg,          \
+  const uint32_t* order = a.heavy_first ? ws_ptr<uint32_t>(a.ws, a.L.tile_ctr) : nullptr;
+#define MGS_BWD_ARGS v.W, v.H, v.gx, order, ws_ptr<uint2>(a.ws, a.L.ranges), ws_ptr<SplatRec>(a.ws, a.L.records), v.bg,   \
       ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img, a.dL_ddepth_img, g2d
   if (a.fast) blend_backward_full_kernel<true><<<tiles, BWD_THREADS, 0, s>>>(MGS_BWD_ARGS);
   else blend_backward_full_kernel<false><<<tiles, BWD_THREADS, 0, s>>>(MGS_BWD_ARGS);

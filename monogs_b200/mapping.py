@@ -17,9 +17,37 @@ import torch
 import torch.distributed as dist
 
 
-def shard_views(n_views: int, world: int, rank: int) -> List[int]:
-    """Round-robin assignment of view indices to ranks (8-keyframe window -> 4/2/1 views per rank at 2/4/8)."""
-    return list(range(rank, n_views, world))
+def assign_views(n_views: int, world: int, n_window: Optional[int] = None) -> List[List[int]]:
+    """View indices per rank: the first n_window views — the keyframe window — go round-robin (8-keyframe
+    window -> 4/2/1 views per rank at 2/4/8 ranks); the remaining ones — the two random keyframes outside the window that
+    BackEnd.map renders beside it (utils/slam_backend.py:215-242) — go one by one to the least-loaded rank (ties: the
+    highest rank, away from rank 0, which also carries the regulariser)."""
+    n_window = n_views if n_window is None else min(n_window, n_views)
+    per = [list(range(r, n_window, world)) for r in range(world)]
+    for i in range(n_window, n_views):
+        r = min(range(world), key=lambda q: (len(per[q]), -q))
+        per[r].append(i)
+    return per
+
+
+def shard_views(n_views: int, world: int, rank: int, n_window: Optional[int] = None) -> List[int]:
+    """This rank's share of assign_views()."""
+    return assign_views(n_views, world, n_window)[rank]
+
+
+def expon_lr(step, lr_init, lr_final, lr_delay_steps=0, lr_delay_mult=1.0, max_steps=1000000):
+    """gaussian_splatting/utils/general_utils.py:80-95 (`helper`): log-linear decay from lr_init to lr_final over max_steps
+    with an optional sine warm-up — the xyz learning rate GaussianModel.update_learning_rate installs every iteration
+    (gaussian_model.py:298-312)."""
+    import math
+    if step < 0 or (lr_init == 0.0 and lr_final == 0.0):
+        return 0.0
+    if lr_delay_steps > 0:
+        delay_rate = lr_delay_mult + (1 - lr_delay_mult) * math.sin(0.5 * math.pi * min(max(step / lr_delay_steps, 0.0), 1.0))
+    else:
+        delay_rate = 1.0
+    t = min(max(step / max_steps, 0.0), 1.0)
+    return delay_rate * math.exp(math.log(lr_init) * (1 - t) + math.log(lr_final) * t)
 
 
 class GradArena:
@@ -153,7 +181,7 @@ class MapEngine:
     def __init__(self, params: Dict[str, torch.Tensor], lrs: Dict[str, float], sh_degree: int = 0, W: int = 640, H: int = 480,
                  capacity_headroom: float = 2.0, group=None, regulariser_weight: float = 10.0,
                  rgb_boundary_threshold: float = 0.01, alpha: float = 0.95, fast_math: bool = True, overlap: bool = True,
-                 exchange: str = "nccl"):
+                 exchange: str = "nccl", max_views: int = 16, use_graph: bool = False):
         from . import _lib as L
         from .ops import FusedAdam
         self.fast_math = fast_math   # ex2.approx exponent in the blend kernels (relative error ~4e-7), like PoseTracker
@@ -171,14 +199,24 @@ class MapEngine:
         self.isotropic = self.params["scaling"].size(-1) == 1
         for p in self.params.values():
             assert p.is_contiguous() and p.dtype == torch.float32 and p.device == self.dev
-        self.arena = GradArena(list(self.params.values()), extra=1)   # + the iteration's loss: one all-reduce for both
+        # Side segment behind the gradients, riding in the same exchange (sum over ranks): [0] the iteration's loss,
+        # [4 + 20 i ..] the pose record (T_w2c 16, exposure a, b, 0, 0) of window view i, written by its owner only —
+        # the all-gather of the window poses at no extra collective
+        self.max_views = max_views
+        self.side = 4 + 20 * max_views
+        self.arena = GradArena(list(self.params.values()), extra=self.side)
         self.grads = dict(zip(self.params.keys(), self.arena.views))
         self.lrs = dict(lrs)
-        self.opt = FusedAdam([{"params": [p], "lr": lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15)
+        # use_graph: step() of a window installed with set_window() is captured once into a CUDA graph and replayed (the
+        # Adam step number and learning rates then live on the device)
+        self.use_graph = use_graph
+        self.opt = FusedAdam([{"params": [p], "lr": lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15,
+                             capturable=use_graph)
+        self._win = None            # set_window(): views, per-view pose / optimiser state
         f = dict(device=self.dev, dtype=torch.float32)
         self.xyz_gradient_accum, self.denom = torch.zeros(self.P, **f), torch.zeros(self.P, **f)
         self.max_radii2D = torch.zeros(self.P, **f)
-        self.loss_total = self.arena.extra
+        self.loss_total = self.arena.extra[:1]
         self.W, self.H = W, H
         self.scratch = torch.empty(self.lib.mgs_map_scratch_bytes(self.P, self.M, W, H), device=self.dev, dtype=torch.uint8)
         self.color, self.depth, self.opacity = torch.empty(3, H, W, **f), torch.empty(1, H, W, **f), torch.empty(1, H, W, **f)
@@ -225,10 +263,10 @@ class MapEngine:
         from .ops import FusedAdam
         old = self.block
         assert self.exchange == "peer" or (self.distributed and self.world > 1), "exchange=\"nvls\" needs a process group"
-        block = PeerBlock(self.arena.numel, self.dev, backend="symm" if self.exchange == "nvls" else "ipc")
+        block = PeerBlock(self.arena.numel, self.dev, backend="symm" if self.exchange == "nvls" else "ipc", side_floats=self.side)
         if self.distributed and self.world > 1:
             block.connect(self.group)
-        arena = GradArena(list(self.params.values()), extra=1, flat=block.grads)
+        arena = GradArena(list(self.params.values()), extra=self.side, flat=block.grads)
         with torch.no_grad():
             pviews = arena.views_over(block.params)
             for v, p in zip(pviews, self.params.values()):
@@ -237,10 +275,11 @@ class MapEngine:
         arena.params = list(self.params.values())
         self.arena, self.block = arena, block
         self.grads = dict(zip(self.params.keys(), arena.views))
-        self.loss_total = arena.extra            # where mgs_map_end adds this rank's share
+        self.loss_total = arena.extra[:1]        # where mgs_map_end adds this rank's share
         self._m_flat, self._v_flat = torch.zeros_like(block.params), torch.zeros_like(block.params)
         mv, vv = arena.views_over(self._m_flat), arena.views_over(self._v_flat)
-        self.opt = FusedAdam([{"params": [p], "lr": self.lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15)
+        self.opt = FusedAdam([{"params": [p], "lr": self.lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15,
+                             capturable=False)     # peer mode: the optimiser object only carries the moments
         for i, (k, p) in enumerate(self.params.items()):
             if moments is not None:
                 mv[i].copy_(moments[0][k]); vv[i].copy_(moments[1][k])
@@ -412,20 +451,153 @@ class MapEngine:
         for ev in bwd_done[-2:]:
             main.wait_event(ev)
 
-    def backward_only(self, views: Sequence[MapView]) -> Dict[int, MapViewResult]:
-        """Everything of an iteration up to the raw-parameter gradients of THIS rank's views (no exchange, no Adam)."""
+    # ---- the keyframe window: placement, window poses, learning-rate schedule ----------------------------------------
+    def set_window(self, views: Sequence[MapView], T_w2c: Optional[Sequence[torch.Tensor]] = None,
+                   frozen: Optional[Sequence[bool]] = None, n_window: Optional[int] = None,
+                   pose_lrs=(5e-4, 1.5e-3, 0.01, 0.01)):
+        """Install the views of the coming iterations (identical on every rank): the first n_window are the keyframe window,
+        the rest the extra keyframes BackEnd.map renders beside it (utils/slam_backend.py:215-242); see assign_views().
+
+        T_w2c (one f32[4,4] world-to-camera matrix per view) switches on the window-pose side of the iteration
+        (slam_backend.py:325-332): every view gets (rho, theta, exposure a, b) + Adam moments on the device, the engine owns
+        the view / projection matrices the kernels read, and after the backward of an iteration the rank that rendered a
+        view takes its Adam step (lrs = cam_trans_delta, cam_rot_delta, exposure_a, exposure_b: the backend builds the
+        window optimiser at half the tracking rates, :437-489), updates T <- Exp(rho, theta) T and rewrites the matrices in
+        place.  frozen[i] keeps view i fixed (the first keyframe; views outside the window are never optimised).  The
+        owners' poses ride in the side segment of the gradient exchange, so window_poses() is complete on every rank."""
+        V = len(views)
+        assert 0 < V <= self.max_views, f"at most max_views={self.max_views} views per iteration"
+        n_window = V if n_window is None else min(n_window, V)
+        win = dict(views=list(views), n_window=n_window, per_rank=assign_views(V, self.world, n_window), poses=None)
+        win["mine"] = win["per_rank"][self.rank]
+        if T_w2c is not None:
+            assert len(T_w2c) == V
+            f = dict(device=self.dev, dtype=torch.float32)
+            st = dict(T=torch.zeros(V, 4, 4, **f), view=torch.zeros(V, 4, 4, **f), proj=torch.zeros(V, 4, 4, **f),
+                      params=torch.zeros(V, 8, **f), m=torch.zeros(V, 8, **f), v=torch.zeros(V, 8, **f),
+                      step=torch.zeros(V, device=self.dev, dtype=torch.int32),
+                      proj_raw=views[0].settings.projmatrix_raw.to(**f).contiguous().clone(), lrs=tuple(float(x) for x in pose_lrs),
+                      frozen=[bool(frozen[i]) if frozen is not None else False for i in range(V)])
+            new_views = []
+            for i, v in enumerate(views):
+                st["T"][i].copy_(T_w2c[i])
+                st["view"][i].copy_(st["T"][i].t())
+                st["proj"][i].copy_(st["view"][i] @ st["proj_raw"])
+                st["params"][i, 6] = 1.0
+                if v.exposure_a is not None:
+                    st["params"][i, 6:7].copy_(v.exposure_a.detach().reshape(1)); st["params"][i, 7:8].copy_(v.exposure_b.detach().reshape(1))
+                rs = v.settings
+                alias = rs.campos is not None and rs.campos.data_ptr() == rs.viewmatrix.data_ptr()
+                rs = rs._replace(viewmatrix=st["view"][i], projmatrix=st["proj"][i], projmatrix_raw=st["proj_raw"],
+                                 campos=st["view"][i] if (alias or rs.campos is None or rs.campos.numel() >= 16) else rs.campos)
+                new_views.append(v._replace(settings=rs,
+                                            exposure_a=st["params"][i, 6:7] if v.exposure_a is not None else None,
+                                            exposure_b=st["params"][i, 7:8] if v.exposure_a is not None else None))
+                if i >= n_window:
+                    st["frozen"][i] = True
+            win["views"], win["poses"] = new_views, st
+        self._win, self._graph = win, None
+        self.arena.extra[4:].zero_()
+        return win["mine"]
+
+    def reset_pose_optimizer(self):
+        """A new keyframe_optimizers object (the backend rebuilds it for every map() call, slam_backend.py:437-489)."""
+        st = self._win["poses"]
+        st["m"].zero_(); st["v"].zero_(); st["step"].zero_()
+
+    def window_poses(self):
+        """(T_w2c [V,4,4], exposure [V,2]) of every view of the window.  Views this rank rendered are live; the others come
+        out of the side segment of the last exchange (zeros before the first iteration of a window on a multi-rank group)."""
+        st = self._win["poses"]
+        T, ab = st["T"].clone(), st["params"][:, 6:8].clone()
+        if self.world > 1:
+            side = self.block.loss_out if self.exchange != "nccl" else self.arena.extra
+            rec = side[4:4 + 20 * T.size(0)].view(-1, 20)
+            for r, idxs in enumerate(self._win["per_rank"]):
+                if r != self.rank:
+                    for i in idxs:
+                        T[i].copy_(rec[i, :16].view(4, 4)); ab[i].copy_(rec[i, 16:18])
+        return T, ab
+
+    def _pose_step(self, out):
+        """keyframe_optimizers.step() + update_pose for the views this rank rendered (one launch)."""
+        from .rasterizer import _stream
+        st, L = self._win["poses"], self.L
+        mine = self._win["mine"]
+        if not mine:
+            return
+        arr = (L.MgsPoseSlot * len(mine))()
+        for k, i in enumerate(mine):
+            s = arr[k]
+            s.T_w2c, s.params = st["T"][i].data_ptr(), st["params"][i].data_ptr()
+            s.exp_avg, s.exp_avg_sq, s.step = st["m"][i].data_ptr(), st["v"][i].data_ptr(), st["step"][i:i + 1].data_ptr()
+            s.tau, s.dab = out[i].tau.data_ptr(), out[i].dab.data_ptr()
+            s.viewmatrix, s.projmatrix = st["view"][i].data_ptr(), st["proj"][i].data_ptr()
+            s.gather_out = self.arena.extra[4 + 20 * i:].data_ptr()
+            for q in range(4):
+                s.lr[q] = st["lrs"][q]
+            s.frozen = int(st["frozen"][i])
+        L.check(self.lib.mgs_window_pose_step(arr, len(mine), L.ptr(st["proj_raw"]), 0.9, 0.999, 1e-8, _stream()),
+                "mgs_window_pose_step")
+
+    def set_learning_rates(self, lrs: Dict[str, float]):
+        """New learning rates for some parameter groups, effective from the next step — also under CUDA-graph replay (the
+        rates live on the device) and on the fused exchanges (the segment table of mgs_peer_reduce_adam is rewritten; the
+        block is not re-installed)."""
+        names = list(self.params.keys())
+        for k, lr in lrs.items():
+            if k not in self.params:
+                continue
+            self.lrs[k] = float(lr)
+            self.opt.set_lr(names.index(k), float(lr))
+            if self.exchange != "nccl":
+                self._peer_x.segment_lr[names.index(k)] = float(lr)
+
+    def update_learning_rate(self, iteration, lr_init, lr_final, lr_delay_mult=1.0, max_steps=1000000):
+        """GaussianModel.update_learning_rate (gaussian_model.py:298-312): the xyz rate of this iteration; returns it."""
+        lr = expon_lr(iteration, lr_init, lr_final, lr_delay_mult=lr_delay_mult, max_steps=max_steps)
+        self.set_learning_rates({"xyz": lr})
+        return lr
+
+    def reset_opacity(self, value: float = 0.01, visibility_filters: Optional[Sequence[torch.Tensor]] = None):
+        """GaussianModel.reset_opacity (gaussian_model.py:364-367, value 0.01) and reset_opacity_nonvisible (:369-377,
+        value 0.4: Gaussians seen by any of `visibility_filters` — bool[P] or radii i32[P] per view — keep their opacity),
+        with replace_tensor_to_optimizer (:470-481): the opacity moments are zeroed, the step count stays.  In a sharded
+        window every rank passes the filters of ITS views; they are OR-ed over the group."""
+        import math
+        raw = math.log(value / (1.0 - value))          # inverse_sigmoid
+        op = self.params["opacity"]
+        with torch.no_grad():
+            if visibility_filters is None:
+                op.fill_(raw)
+            else:
+                seen = torch.zeros(self.P, device=self.dev, dtype=torch.int32)
+                for fl in visibility_filters:
+                    seen |= (fl.reshape(-1) > 0).to(torch.int32) if fl.dtype != torch.bool else fl.reshape(-1).to(torch.int32)
+                if self.distributed and self.world > 1:
+                    dist.all_reduce(seen, op=dist.ReduceOp.MAX, group=self.group)
+                op.copy_(torch.where(seen.view_as(op) > 0, op, torch.full_like(op, raw)))
+            st = self.opt.state.get(op)
+            if st is not None:
+                st["exp_avg"].zero_(); st["exp_avg_sq"].zero_()
+
+    # ---- one iteration ----------------------------------------------------------------------------------------------
+    def backward_only(self, views: Optional[Sequence[MapView]] = None) -> Dict[int, MapViewResult]:
+        """Everything of an iteration up to the raw-parameter gradients of THIS rank's views (no exchange, no Adam).
+        views=None: the window installed with set_window()."""
         from .rasterizer import _stream
         L = self.L
+        if views is None:
+            views, mine = self._win["views"], list(self._win["mine"])
+        else:
+            mine = list(shard_views(len(views), self.world, self.rank))
         for p, v in zip(self.arena.params, self.arena.views):
             p.grad = v
         self._keep = []
         args = self._args()
-        mine = list(shard_views(len(views), self.world, self.rank))
-        self._since_poll += 1
-        if self._since_poll >= self.poll_every:
-            self._since_poll = 0
-            self.poll_capacity()
         self._ensure_capacity([views[i] for i in mine])
+        if self._win is not None and self._win["poses"] is not None and self.exchange == "nccl" and self.world > 1:
+            self.arena.extra[4:].zero_()      # the all-reduce left the sums here; only owners write their slots again
         L.check(self.lib.mgs_map_begin(C.byref(args), _stream()), "mgs_map_begin")
         out = {}
         for i in mine:
@@ -438,24 +610,59 @@ class MapEngine:
         L.check(self.lib.mgs_map_end(C.byref(args), int(self.rank == 0), self.reg_weight, _stream()), "mgs_map_end")
         return out
 
-    def step(self, views: Sequence[MapView]):
-        """One data-parallel mapping iteration.  Returns (total loss f32[1] on the device, {view index: MapViewResult})."""
+    def _iteration(self, views):
+        """backward of this rank's views, window poses, the exchange, Adam — the launch sequence of one iteration."""
         out = self.backward_only(views)
+        if views is None and self._win["poses"] is not None:
+            self._pose_step(out)
         if self.exchange != "nccl":
-            # gradient reduce-scatter + Adam on this rank's slice + parameter all-gather, one kernel over peer memory
-            from .rasterizer import _stream
-            self._peer_step += 1
-            self._epoch += 1
-            for st in self.opt.state.values():
-                st["step"] = self._peer_step
-            self.L.check(self.lib.mgs_peer_reduce_adam(C.byref(self._peer_x), self._peer_step, self._epoch, 0.9, 0.999, 1e-15,
-                                                       _stream()), "mgs_peer_reduce_adam")
-            return self.block.loss_out[:1], out
+            return out          # the fused exchange carries host-side step / epoch numbers: launched by step(), never captured
         if self.distributed and self.world > 1:
             dist.all_reduce(self.arena.flat, op=dist.ReduceOp.SUM, group=self.group)   # the single exchange of the path
-                                                                                     # (gradients + loss_total, its last element)
+                                                                                     # (gradients + the side segment)
         self.opt.step()
+        return out
+
+    def step(self, views: Optional[Sequence[MapView]] = None):
+        """One data-parallel mapping iteration.  Returns (total loss f32[1] on the device, {view index: MapViewResult}).
+        views=None runs the window installed with set_window(); with use_graph the launch sequence of that window is
+        captured once (after one eager iteration that sizes every buffer) and replayed."""
+        self._since_poll += 1
+        if self._since_poll >= self.poll_every:
+            self._since_poll = 0
+            self.poll_capacity()        # may drop the workspaces: the captured graph is then rebuilt
+        if views is None and self.use_graph:
+            g = self._graph
+            if g is None or g["win"] is not self._win or g["ws"] is not self.ws:
+                # first iteration of this window (or after a regrow): eager — it sizes the workspaces, the resource sets,
+                # the per-view slots and the optimiser state the captured sequence will point at
+                out = self._iteration(None)
+                self._graph = dict(win=self._win, ws=self.ws, graph=None, out=out)
+            else:
+                if g["graph"] is None:
+                    torch.cuda.synchronize(self.dev)
+                    cg = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(cg):
+                        g["out"] = self._iteration(None)
+                    g["graph"] = cg
+                g["graph"].replay()
+                out = g["out"]
+        else:
+            out = self._iteration(views)
+        if self.exchange != "nccl":
+            self._launch_peer_exchange()
+            return self.block.loss_out[:1], out
         return self.loss_total, out
+
+    def _launch_peer_exchange(self):
+        """Gradient reduce-scatter + Adam on this rank's slice + parameter all-gather, one kernel over peer memory."""
+        from .rasterizer import _stream
+        self._peer_step += 1
+        self._epoch += 1
+        for st in self.opt.state.values():
+            st["step"] = self._peer_step
+        self.L.check(self.lib.mgs_peer_reduce_adam(C.byref(self._peer_x), self._peer_step, self._epoch, 0.9, 0.999, 1e-15,
+                                                   _stream()), "mgs_peer_reduce_adam")
 
     def sync_stats(self):
         """Side channels needed only before densify / prune: sum of the locally accumulated
@@ -509,15 +716,21 @@ class MapEngine:
         (densification_postfix, gaussian_model.py:592-594), re-sized scratch; the instance capacity is re-estimated."""
         from .ops import FusedAdam
         steps = {k: (self.opt.state[p]["step"] if p in self.opt.state else 0) for k, p in self.params.items()}
+        if self.opt.capturable and self.opt.device_step() is not None:      # the live count is on the device
+            steps = {k: int(self.opt.device_step()) for k in self.params}
         self.params = {k: out["params"][k] for k in self.params}
         self.P = self.params["xyz"].size(0)
-        self.arena = GradArena(list(self.params.values()), extra=1)
-        self.loss_total = self.arena.extra
+        self.arena = GradArena(list(self.params.values()), extra=self.side)
+        self.loss_total = self.arena.extra[:1]
         self.grads = dict(zip(self.params.keys(), self.arena.views))
-        self.opt = FusedAdam([{"params": [p], "lr": self.lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15)
+        self.opt = FusedAdam([{"params": [p], "lr": self.lrs[k]} for k, p in self.params.items()], lr=0.0, eps=1e-15,
+                             capturable=self.use_graph and self.exchange == "nccl")
         for k, p in self.params.items():
             if steps[k] > 0:
                 self.opt.state[p] = dict(step=steps[k], exp_avg=out["exp_avg"][k], exp_avg_sq=out["exp_avg_sq"][k])
+        if self.opt.capturable:
+            self.opt.set_step(max(steps.values()))
+        self._graph = None
         f = dict(device=self.dev, dtype=torch.float32)
         self.xyz_gradient_accum, self.denom = torch.zeros(self.P, **f), torch.zeros(self.P, **f)
         self.max_radii2D = torch.zeros(self.P, **f)

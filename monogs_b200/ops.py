@@ -22,7 +22,7 @@ def distCUDA2(points: torch.Tensor) -> torch.Tensor:
         return out
     lib = L.lib()
     ws = torch.empty(lib.mgs_knn_workspace_bytes(P), device=points.device, dtype=torch.uint8)
-    L.check(lib.mgs_knn_dist2(P, L.ptr(pts), L.ptr(out), L.ptr(ws), ws.numel(), _stream()), "mgs_knn_dist2")
+    L.check(lib.mgs_knn_dist2(P, L.ptr(pts), L.ptr(out), L.ptr(ws), ws.numel(), _stream(points.device)), "mgs_knn_dist2")
     return out
 
 
@@ -51,7 +51,7 @@ class FusedLoss(torch.autograd.Function):
         g_dep = torch.empty(1, H, W, device=dev)
         scratch = torch.empty(lib.mgs_loss_scratch_bytes(H, W), device=dev, dtype=torch.uint8)
         L.check(lib.mgs_loss_fwd_bwd(C.byref(a), L.ptr(loss), L.ptr(dab), L.ptr(g_img), L.ptr(g_dep), L.ptr(scratch),
-                                     scratch.numel(), _stream()), "mgs_loss_fwd_bwd")
+                                     scratch.numel(), _stream(dev)), "mgs_loss_fwd_bwd")
         ctx.save_for_backward(g_img, g_dep, dab)
         ctx.has = (depth is not None, exposure_a is not None, exposure_b is not None)
         return loss.squeeze(0)
@@ -87,9 +87,14 @@ def mapping_loss(image, depth, gt_image, exposure_a=None, exposure_b=None, gt_de
 
 class FusedAdam:
     """torch.optim.Adam-compatible subset (param_groups with per-group lr, betas, eps; no weight decay /
-    amsgrad) executed as one multi-tensor kernel launch per step."""
+    amsgrad) executed as one multi-tensor kernel launch per step.
 
-    def __init__(self, params, lr=0.0, betas=(0.9, 0.999), eps=1e-8):
+    capturable=True: the step number and the learning rates live in device memory (mgs_adam_step_device, the
+    lr_device field of mgs_adam_group), so step() can be captured into a CUDA graph once and replayed while
+    set_lr() keeps a schedule going (GaussianModel.update_learning_rate changes the xyz rate every iteration,
+    gaussian_model.py:298-312).  All parameters then share one step counter."""
+
+    def __init__(self, params, lr=0.0, betas=(0.9, 0.999), eps=1e-8, capturable=False):
         groups = list(params)
         if groups and not isinstance(groups[0], dict):
             groups = [{"params": groups}]
@@ -101,6 +106,8 @@ class FusedAdam:
             self.param_groups.append(g)
         self.state = {}
         self.betas, self.eps = betas, eps
+        self.capturable = capturable
+        self._step_dev = self._lr_dev = None
 
     def zero_grad(self, set_to_none=True):
         for g in self.param_groups:
@@ -109,18 +116,63 @@ class FusedAdam:
                     if set_to_none: p.grad = None
                     else: p.grad.zero_()
 
+    def set_lr(self, group_index: int, lr: float):
+        """Install a new learning rate for one group (host value and, when capturable, its device copy)."""
+        self.param_groups[group_index]["lr"] = float(lr)
+        if self._lr_dev is not None:
+            self._lr_dev[group_index].fill_(float(lr))
+
+    def device_step(self):
+        """The device-side step counter of a capturable optimiser (i32[1]); None before the first step."""
+        return self._step_dev
+
+    def set_step(self, n: int):
+        for g in self.param_groups:
+            for p in g["params"]:
+                if p in self.state:
+                    self.state[p]["step"] = int(n)
+        if self._step_dev is not None:
+            self._step_dev.fill_(int(n))
+        self._pending_step = int(n)
+
+    def _state_of(self, p):
+        st = self.state.get(p)
+        if st is None:
+            st = self.state[p] = dict(step=0, exp_avg=torch.zeros_like(p, memory_format=torch.contiguous_format),
+                                      exp_avg_sq=torch.zeros_like(p, memory_format=torch.contiguous_format))
+        return st
+
     @torch.no_grad()
     def step(self):
         lib = L.lib()
+        if self.capturable:
+            items = [(gi, g, p) for gi, g in enumerate(self.param_groups) for p in g["params"] if p.grad is not None]
+            if not items:
+                return
+            dev = items[0][2].device
+            if self._step_dev is None:      # created outside any capture: the first step of a capturable optimiser is eager
+                start = max([self._state_of(p)["step"] for _, _, p in items] + [getattr(self, "_pending_step", 0)])
+                self._step_dev = torch.full((1,), start, device=dev, dtype=torch.int32)
+                self._lr_dev = torch.tensor([g["lr"] for g in self.param_groups], device=dev, dtype=torch.float32)
+            arr = (L.MgsAdamGroup * len(items))()
+            for i, (gi, g, p) in enumerate(items):
+                st = self._state_of(p)
+                grad = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
+                assert p.is_contiguous() and p.dtype == torch.float32
+                arr[i].param, arr[i].grad = p.data_ptr(), grad.data_ptr()
+                arr[i].exp_avg, arr[i].exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
+                arr[i].numel, arr[i].lr = p.numel(), float(g["lr"])
+                arr[i].lr_device = self._lr_dev[gi:gi + 1].data_ptr()
+            b1, b2 = self.param_groups[0]["betas"]
+            L.check(lib.mgs_adam_step_device(arr, len(items), L.ptr(self._step_dev), b1, b2, self.param_groups[0]["eps"],
+                                             _stream(dev)), "mgs_adam_step_device")
+            return
         by_step = {}
         for g in self.param_groups:
             for p in g["params"]:
                 if p.grad is None:
                     continue
-                st = self.state.get(p)
-                if st is None:
-                    st = self.state[p] = dict(step=0, exp_avg=torch.zeros_like(p, memory_format=torch.contiguous_format),
-                                              exp_avg_sq=torch.zeros_like(p, memory_format=torch.contiguous_format))
+                st = self._state_of(p)
                 st["step"] += 1
                 grad = p.grad if p.grad.is_contiguous() else p.grad.contiguous()
                 by_step.setdefault((st["step"], g["betas"], g["eps"]), []).append((p, grad, st, g["lr"]))
@@ -131,7 +183,7 @@ class FusedAdam:
                 arr[i].param, arr[i].grad = p.data_ptr(), grad.data_ptr()
                 arr[i].exp_avg, arr[i].exp_avg_sq = st["exp_avg"].data_ptr(), st["exp_avg_sq"].data_ptr()
                 arr[i].numel, arr[i].lr = p.numel(), float(lr)
-            L.check(lib.mgs_adam_step(arr, len(items), step, betas[0], betas[1], eps, _stream()), "mgs_adam_step")
+            L.check(lib.mgs_adam_step(arr, len(items), step, betas[0], betas[1], eps, _stream(items[0][0].device)), "mgs_adam_step")
 
 
 def pose_update(T_w2c, rho, theta, proj_raw=None, want_matrices=False, converged_threshold=1e-4):
@@ -143,5 +195,5 @@ def pose_update(T_w2c, rho, theta, proj_raw=None, want_matrices=False, converged
     view = torch.empty(4, 4, device=dev) if want_matrices else None
     proj = torch.empty(4, 4, device=dev) if (want_matrices and proj_raw is not None) else None
     L.check(lib.mgs_pose_update(L.ptr(T_w2c), L.ptr(rho), L.ptr(theta), L.ptr(_f32c(proj_raw)), L.ptr(view), L.ptr(proj),
-                                L.ptr(conv), converged_threshold, _stream()), "mgs_pose_update")
+                                L.ptr(conv), converged_threshold, _stream(dev)), "mgs_pose_update")
     return conv, view, proj

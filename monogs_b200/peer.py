@@ -30,13 +30,15 @@ class PeerBlock:
     multicast mapping of the same memory: mgs_peer_reduce_adam then reduces inside the switch (multimem.ld_reduce) and
     broadcasts the parameters with multimem.st."""
 
-    def __init__(self, numel: int, dev: torch.device, backend: str = "ipc"):
+    def __init__(self, numel: int, dev: torch.device, backend: str = "ipc", side_floats: int = 4):
         assert numel > 0 and numel % 4 == 0, "arena length must be a positive multiple of 4 floats"
         assert backend in ("ipc", "symm")
         self.lib = L.lib()
         self.numel, self.dev, self.backend = numel, dev, backend
         self.flag_bytes = int(self.lib.mgs_peer_flags_bytes())
-        self.nbytes = 2 * numel * 4 + 16 + self.flag_bytes
+        assert side_floats >= 4 and side_floats % 4 == 0
+        self.side = side_floats        # floats of loss_out: the sums of the arena's trailing sum-only segment
+        self.nbytes = 2 * numel * 4 + 4 * side_floats + self.flag_bytes
         self._opened: List[int] = []
         self.mc_base = 0
         if backend == "symm":
@@ -46,8 +48,8 @@ class PeerBlock:
             torch.cuda.synchronize(dev)
             self.ptr = self._symm.data_ptr()
             self.params, self.grads = self._symm[:numel], self._symm[numel:2 * numel]
-            self.loss_out = self._symm[2 * numel:2 * numel + 4]
-            self.flags = self._symm[2 * numel + 4:].view(torch.int32)
+            self.loss_out = self._symm[2 * numel:2 * numel + side_floats]
+            self.flags = self._symm[2 * numel + side_floats:].view(torch.int32)
         else:
             p = C.c_void_p()
             with torch.cuda.device(dev):
@@ -55,8 +57,8 @@ class PeerBlock:
             self.ptr = p.value
             self.params = torch.as_tensor(_Raw(self.ptr, numel, "<f4", self), device=dev)
             self.grads = torch.as_tensor(_Raw(self.ptr + 4 * numel, numel, "<f4", self), device=dev)
-            self.loss_out = torch.as_tensor(_Raw(self.ptr + 8 * numel, 4, "<f4", self), device=dev)
-            self.flags = torch.as_tensor(_Raw(self.ptr + 8 * numel + 16, self.flag_bytes // 4, "<i4", self), device=dev)
+            self.loss_out = torch.as_tensor(_Raw(self.ptr + 8 * numel, side_floats, "<f4", self), device=dev)
+            self.flags = torch.as_tensor(_Raw(self.ptr + 8 * numel + 4 * side_floats, self.flag_bytes // 4, "<i4", self), device=dev)
         self.world, self.rank = 1, 0
         self.bases = [self.ptr]
         self._group, self._connected = None, False
@@ -101,9 +103,9 @@ class PeerBlock:
         return self
 
     @staticmethod
-    def local_group(numel: int, world: int, dev: torch.device) -> List["PeerBlock"]:
+    def local_group(numel: int, world: int, dev: torch.device, side_floats: int = 4) -> List["PeerBlock"]:
         """`world` blocks in THIS process on one device, wired to each other by their plain pointers."""
-        blocks = [PeerBlock(numel, dev) for _ in range(world)]
+        blocks = [PeerBlock(numel, dev, side_floats=side_floats) for _ in range(world)]
         for r, b in enumerate(blocks):
             b.world, b.rank, b.bases = world, r, [x.ptr for x in blocks]
         return blocks
@@ -116,7 +118,7 @@ class PeerBlock:
         x.world, x.rank, x.numel = self.world, self.rank, self.numel
         for r, b in enumerate(self.bases):
             x.param_arena[r], x.grad_arena[r] = b, b + 4 * self.numel
-            x.loss_out[r], x.flags[r] = b + 8 * self.numel, b + 8 * self.numel + 16
+            x.loss_out[r], x.flags[r] = b + 8 * self.numel, b + 8 * self.numel + 4 * self.side
         assert exp_avg.numel() == self.numel and exp_avg_sq.numel() == self.numel
         x.exp_avg, x.exp_avg_sq = exp_avg.data_ptr(), exp_avg_sq.data_ptr()
         assert len(segment_ends) == len(segment_lrs) <= L.PEER_MAX_SEGMENTS

@@ -97,7 +97,7 @@ def test_struct_layouts_match_header(tmp_path):
     L = _lib()
     pairs = {"mgs_view": L.MgsView, "mgs_loss_args": L.MgsLossArgs, "mgs_adam_group": L.MgsAdamGroup,
              "mgs_track_args": L.MgsTrackArgs, "mgs_track2_args": L.MgsTrack2Args, "mgs_gaussians": L.MgsGaussians,
-             "mgs_map_args": L.MgsMapArgs, "mgs_map_view": L.MgsMapView, "mgs_peer_exchange": L.MgsPeerExchange, "mgs_densify_cfg": L.MgsDensifyCfg,
+             "mgs_map_args": L.MgsMapArgs, "mgs_map_view": L.MgsMapView, "mgs_pose_slot": L.MgsPoseSlot, "mgs_peer_exchange": L.MgsPeerExchange, "mgs_densify_cfg": L.MgsDensifyCfg,
              "mgs_gaussian_state": L.MgsGaussianState}
     declared = set(re.findall(r"^}\s*(mgs_\w+);", open(HEADER).read(), flags=re.M))
     assert declared == set(pairs), declared ^ set(pairs)

@@ -201,3 +201,141 @@ def test_map_engine_pipeline_matches_single_stream(name):
         assert U.rel_err(o1[i].loss, o0[i].loss) <= 1e-6 and U.rel_err(o1[i].tau, o0[i].tau) <= 1e-5
     assert U.rel_err(e1.xyz_gradient_accum, e0.xyz_gradient_accum) <= 1e-5
     assert torch.equal(e1.denom, e0.denom) and torch.equal(e1.max_radii2D, e0.max_radii2D)
+
+
+def _lrs():
+    return {"xyz": 1.6e-4, "f_dc": 2.5e-3, "f_rest": 2.5e-3 / 20, "opacity": 0.05, "scaling": 1e-3, "rotation": 1e-3}
+
+
+def _window_T(views):
+    return [v.settings.viewmatrix.t().contiguous() for v in views]
+
+
+def test_window_pose_step_matches_torch_adam_and_se3_exp():
+    """The window-pose side of a mapping iteration (slam_backend.py:325-332): keyframe_optimizers.step() + update_pose on
+    the device for the views the engine rendered, against torch.optim.Adam (default eps) + the float64 SE3 exponential, from
+    the tau / dab the same engine reports without pose optimisation.  A frozen view keeps its pose."""
+    from monogs_b200.mapping import MapEngine
+    from monogs_b200 import scene as S
+    sc, cam = U.small_case("dense")
+    p = {k: v.detach().clone() for k, v in _raw_params(sc).items()}
+    views = _views(sc, cam, 3, False, True)
+    lr0 = {k: 0.0 for k in p}             # Gaussians fixed: the two engines see the same scene in both iterations
+    plain = MapEngine({k: v.clone() for k, v in p.items()}, lr0, sh_degree=sc.sh_degree, W=cam.W, H=cam.H, fast_math=False)
+    ref_out = plain.backward_only(views)
+    T0 = _window_T(views)
+    pose_lrs = (5e-4, 1.5e-3, 0.01, 0.01)
+    eng = MapEngine({k: v.clone() for k, v in p.items()}, lr0, sh_degree=sc.sh_degree, W=cam.W, H=cam.H, fast_math=False)
+    eng.set_window(views, T_w2c=T0, frozen=[True, False, False], pose_lrs=pose_lrs)
+    eng.step()
+    torch.cuda.synchronize()
+    T1, ab1 = eng.window_poses()
+    assert torch.equal(T1[0], T0[0])                              # the first keyframe is never moved
+    for i in (1, 2):
+        tau, dab = ref_out[i].tau.cpu().double(), ref_out[i].dab.cpu().double()
+        x = torch.zeros(8, dtype=torch.float64, requires_grad=True)
+        x.grad = torch.cat([tau, dab])
+        groups = [{"params": [x], "lr": 1.0}]
+        m, v = 0.1 * x.grad, 0.001 * x.grad ** 2                  # first Adam step in closed form: -lr * g / (|g| + eps)
+        upd = -(m / 0.1) / ((v / 0.001).sqrt() + 1e-8)
+        lrs8 = torch.tensor([pose_lrs[0]] * 3 + [pose_lrs[1]] * 3 + [pose_lrs[2], pose_lrs[3]], dtype=torch.float64)
+        delta = upd * lrs8
+        T_ref = (S.se3_exp(delta[:6]) @ T0[i].cpu().double()).float()
+        assert U.rel_err(T1[i], T_ref) <= 1e-5, i
+        if views[i].exposure_a is not None:
+            a0, b0 = float(views[i].exposure_a), float(views[i].exposure_b)
+            assert abs(float(ab1[i, 0]) - (a0 + float(delta[6]))) <= 1e-6 and abs(float(ab1[i, 1]) - (b0 + float(delta[7]))) <= 1e-6
+    # the engine's own matrices follow the new pose: the next iteration renders from it
+    st = eng._win["poses"]
+    assert U.rel_err(st["view"][1], T1[1].t()) <= 1e-6 and U.rel_err(st["proj"][1], T1[1].t() @ st["proj_raw"]) <= 1e-5
+    l0 = float(eng.step()[0])
+    for _ in range(20):
+        l1 = float(eng.step()[0])
+    assert l1 < l0            # pose + exposure optimisation alone lowers the window loss
+
+
+def test_map_engine_graph_replay_matches_eager_and_follows_the_lr_schedule():
+    """use_graph: the iteration of an installed window is captured once and replayed.  Same parameters as the eager
+    engine after several iterations (up to the order of the float atomics), including a learning-rate change between
+    replays (the rates live on the device: GaussianModel.update_learning_rate, gaussian_model.py:298-312)."""
+    from monogs_b200.mapping import MapEngine, expon_lr
+    sc, cam = U.small_case("dense")
+    p = {k: v.detach().clone() for k, v in _raw_params(sc).items()}
+    views = _views(sc, cam, 5, False, False)
+    engs = []
+    for use_graph in (False, True):
+        eng = MapEngine({k: v.clone() for k, v in p.items()}, _lrs(), sh_degree=sc.sh_degree, W=cam.W, H=cam.H, fast_math=False,
+                        use_graph=use_graph)
+        eng.set_window(views)
+        losses = []
+        for it in range(6):
+            lr = eng.update_learning_rate(it * 5000, 1.6e-4 * 6, 1.6e-6 * 6, lr_delay_mult=0.01, max_steps=30000)
+            assert abs(lr - expon_lr(it * 5000, 1.6e-4 * 6, 1.6e-6 * 6, lr_delay_mult=0.01, max_steps=30000)) < 1e-12
+            losses.append(float(eng.step()[0]))
+        torch.cuda.synchronize()
+        engs.append((eng, losses))
+    (e0, l0), (e1, l1) = engs
+    assert e1._graph is not None and e1._graph["graph"] is not None, "the window was replayed from a captured graph"
+    for a, b in zip(l0, l1):
+        assert abs(a - b) <= 1e-5 * abs(a)
+    for k in p:
+        d0, d1 = e0.params[k] - p[k], e1.params[k] - p[k]
+        frac = float(((d0 - d1).abs() > 1e-3 * d0.abs().max()).float().mean())
+        assert frac <= 1e-3, (k, frac)
+    # and the schedule really reached the kernel: the xyz update of a step shrinks with the rate
+    e = MapEngine({k: v.clone() for k, v in p.items()}, _lrs(), sh_degree=sc.sh_degree, W=cam.W, H=cam.H, use_graph=True)
+    e.set_window(views)
+    for _ in range(3):
+        e.step()
+    x0 = e.params["xyz"].clone(); e.step(); d_big = float((e.params["xyz"] - x0).abs().max())
+    e.set_learning_rates({"xyz": 1.6e-6})
+    x0 = e.params["xyz"].clone(); e.step(); d_small = float((e.params["xyz"] - x0).abs().max())
+    assert d_small < 0.05 * d_big
+
+
+def test_reset_opacity_on_the_arena():
+    """GaussianModel.reset_opacity / reset_opacity_nonvisible (gaussian_model.py:364-377) + replace_tensor_to_optimizer:
+    values and zeroed opacity moments, step counts kept."""
+    import math
+    from monogs_b200.mapping import MapEngine
+    sc, cam = U.small_case("dense")
+    p = {k: v.detach().clone() for k, v in _raw_params(sc).items()}
+    views = _views(sc, cam, 3, False, False)
+    eng = MapEngine(p, _lrs(), sh_degree=sc.sh_degree, W=cam.W, H=cam.H)
+    outs = None
+    for _ in range(2):
+        _, outs = eng.step(views)
+    op_before = eng.params["opacity"].clone()
+    filters = [outs[i].radii > 0 for i in outs]
+    seen = torch.stack(filters).any(dim=0)
+    eng.reset_opacity(0.4, visibility_filters=filters)
+    inv = math.log(0.4 / 0.6)
+    assert torch.equal(eng.params["opacity"][seen], op_before[seen])
+    assert torch.allclose(eng.params["opacity"][~seen], torch.full_like(op_before[~seen], inv))
+    st = eng.opt.state[eng.params["opacity"]]
+    assert float(st["exp_avg"].abs().max()) == 0.0 and float(st["exp_avg_sq"].abs().max()) == 0.0 and st["step"] == 2
+    eng.reset_opacity()
+    assert torch.allclose(eng.params["opacity"], torch.full_like(op_before, math.log(0.01 / 0.99)))
+    eng.step(views)     # mapping continues
+
+
+def test_assign_views_and_capacity_poll():
+    from monogs_b200.mapping import MapEngine, assign_views
+    assert assign_views(8, 4) == [[0, 4], [1, 5], [2, 6], [3, 7]]
+    assert assign_views(10, 8, 8) == [[0], [1], [2], [3], [4], [5], [6, 9], [7, 8]]      # extras to the least-loaded ranks
+    assert sorted(sum(assign_views(10, 4, 8), [])) == list(range(10))
+    sc, cam = U.small_case("dense")
+    p = {k: v.detach().clone() for k, v in _raw_params(sc).items()}
+    views = _views(sc, cam, 3, False, False)
+    eng = MapEngine(p, _lrs(), sh_degree=sc.sh_degree, W=cam.W, H=cam.H, capacity_headroom=1.05)
+    eng.poll_every = 2
+    eng.step(views)
+    cap0 = eng.R_cap
+    with torch.no_grad():
+        eng.params["scaling"] += 1.2          # every splat 3.3x larger: far more tile instances than the capacity
+    for _ in range(8):
+        eng.step(views)
+    torch.cuda.synchronize()
+    eng.poll_capacity(); eng.step(views)
+    assert eng.overflow_polls >= 1 and eng.R_cap > cap0, "the sticky overflow word was seen and the workspaces regrown"
+    assert not eng.check_capacity()[1]
