@@ -153,6 +153,28 @@ int mgs_raster_backward_pose(const mgs_view* view, int32_t P,
                              float* tau_image, float* dL_dtau_sum, void* stream);
 size_t mgs_raster_backward_pose_scratch_bytes(int32_t P, int32_t W, int32_t H);
 
+/* Single-pass variant of the two calls above for the DROP-IN surface (what MonoGS's tracking actually calls: only theta / rho
+ * require a gradient, utils/slam_frontend.py:1799-1800, and SH degree 0 so that no colour depends on the pose).  The pose
+ * tangent of a pixel is tau = sum_ch g_ch (A_ch - out_ch E) (+ the depth terms) where E and A_ch are sums over the pixel's
+ * splats that do NOT depend on the loss; mgs_raster_forward_pose is mgs_raster_forward that also accumulates them during
+ * its one walk over the tile lists and leaves them in pose_state, and mgs_raster_backward_pose_deferred contracts them with
+ * the dL/d out of whatever loss the caller evaluated in between — one pass over the pixels, no second walk over the lists,
+ * no final_T / n_contrib round trip.  Same status_out / ready_event protocol as mgs_raster_forward; on overflow the caller
+ * re-renders with mgs_raster_render and uses the two-pass mgs_raster_backward_pose. */
+size_t mgs_raster_pose_state_bytes(int32_t P, int32_t W, int32_t H);
+int mgs_raster_forward_pose(const mgs_view* view, int32_t P,
+                            const float* means3D, const float* opacities,
+                            const float* shs, const float* colors_precomp,
+                            const float* scales, const float* rotations, const float* cov3D_precomp,
+                            int32_t* radii, void* workspace, size_t workspace_bytes, int64_t R_cap,
+                            float* out_color, float* out_depth, float* out_opacity, int32_t* n_touched,
+                            void* pose_state, size_t pose_state_bytes,
+                            int32_t* status_out, void* ready_event, void* stream);
+int mgs_raster_backward_pose_deferred(int32_t W, int32_t H, const void* pose_state,
+                                      const float* dL_dout_color, const float* dL_dout_depth /* may be null */,
+                                      float* tau_image /* f32[6,H,W], optional */, float* dL_dtau_sum /* f32[6], optional */,
+                                      void* stream);
+
 /* Sketch rows from a tau image: sketch_dtau[j,i,:] = sum over pixels with sketch_indices[j,y,x] == i of
  * tau_image[:,y,x]; indices outside [0, sketch_dim) (the reference uses -1) are ignored.  This equals
  * sum over Gaussians of df_dtau[P,d,6] that the reference wrapper forms per stack j (__init__.py:216-253);

@@ -154,6 +154,9 @@ SIGNATURES = {
     "mgs_raster_render": (C.c_int, [_VP, _I32, _P, _P, _P, _SZ, _I64, _P, _P, _P, _P, _P]),
     "mgs_raster_query": (C.c_int, [_P, C.POINTER(_I32), C.POINTER(_I32), _P]),
     "mgs_raster_forward": (C.c_int, [_VP, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _I64, _P, _P, _P, _P, _P, _P, _P]),
+    "mgs_raster_pose_state_bytes": (_SZ, [_I32, _I32, _I32]),
+    "mgs_raster_forward_pose": (C.c_int, [_VP, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _I64, _P, _P, _P, _P, _P, _SZ, _P, _P, _P]),
+    "mgs_raster_backward_pose_deferred": (C.c_int, [_I32, _I32, _P, _P, _P, _P, _P, _P]),
     "mgs_raster_status_async": (C.c_int, [_P, _P, _P]),
     "mgs_raster_status_reset": (C.c_int, [_P, _P]),
     "mgs_raster_backward": (C.c_int, [_VP, _I32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _P,

@@ -171,6 +171,56 @@ int mgs_raster_forward(const mgs_view* view, int32_t P, const float* means3D, co
   return launch_blend_forward(v, workspace, L, out_color, out_depth, out_opacity, n_touched, s);
 }
 
+size_t mgs_raster_pose_state_bytes(int32_t P, int32_t W, int32_t H) {
+  if (P < 0 || W <= 0 || H <= 0) return 0;
+  return pose_deferred_bytes(W, H) + ((size_t)(P > 0 ? P : 1) * 32 * sizeof(float) + 255) / 256 * 256;
+}
+
+int mgs_raster_forward_pose(const mgs_view* view, int32_t P, const float* means3D, const float* opacities,
+                            const float* shs, const float* colors_precomp, const float* scales, const float* rotations,
+                            const float* cov3D_precomp, int32_t* radii, void* workspace, size_t workspace_bytes, int64_t R_cap,
+                            float* out_color, float* out_depth, float* out_opacity, int32_t* n_touched,
+                            void* pose_state, size_t pose_state_bytes, int32_t* status_out, void* ready_event, void* stream) {
+  int rc = check_view(view, true);
+  if (rc) return rc;
+  if (P <= 0 || R_cap <= 0 || R_cap > 0x7fffffffLL) { set_error("forward_pose: bad P or R_cap"); return MGS_EINVAL; }
+  if (view->sh_degree != 0) { set_error("forward_pose: sh_degree must be 0 (the colour of a splat must not depend on the pose)"); return MGS_EINVAL; }
+  if (!workspace || !out_color || !out_depth || !out_opacity || !means3D || !opacities || !radii || !n_touched || !pose_state) {
+    set_error("forward_pose: null argument"); return MGS_EINVAL;
+  }
+  if ((rc = check_options(view, shs, colors_precomp, scales, rotations, cov3D_precomp))) return rc;
+  const int W = view->image_width, H = view->image_height;
+  if (pose_state_bytes < mgs_raster_pose_state_bytes(P, W, H)) { set_error("forward_pose: pose_state too small"); return MGS_ENOSPC; }
+  cudaStream_t s = (cudaStream_t)stream;
+  WsLayout L;
+  if ((rc = ws_layout(P, W, H, R_cap, &L))) return rc;
+  if (workspace_bytes < L.total) { set_error("workspace too small: %zu < %zu", workspace_bytes, L.total); return MGS_ENOSPC; }
+  const ViewConst v = make_view_const(view);
+  float* ea = reinterpret_cast<float*>(pose_state);
+  float* basis = reinterpret_cast<float*>(reinterpret_cast<char*>(pose_state) + pose_deferred_bytes(W, H));
+  // a fresh workspace: the folded scan wants a zero header (ticket) and zero tile counters
+  MGS_CUDA_TRY(cudaMemsetAsync(workspace, 0, sizeof(WsHeader), s));
+  MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(workspace, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
+  const FoldScan fs{R_cap, /*heavy_first=*/true};
+  if ((rc = launch_preprocess(v, P, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
+                              workspace, L, s, basis, 32, nullptr, &fs)))
+    return rc;
+  if (status_out) MGS_CUDA_TRY(cudaMemcpyAsync(status_out, workspace, 6 * sizeof(uint32_t), cudaMemcpyDefault, s));
+  if (ready_event) MGS_CUDA_TRY(cudaEventRecord((cudaEvent_t)ready_event, s));
+  MGS_CUDA_TRY(cudaMemsetAsync(n_touched, 0, (size_t)P * sizeof(int32_t), s));
+  if ((rc = launch_binning(v, P, colors_precomp, radii, workspace, L, R_cap, s, true, /*scan_done=*/true))) return rc;
+  FusedLoss none{};
+  return launch_blend_track(v, workspace, L, basis, out_color, out_depth, out_opacity, n_touched, none, true, nullptr, s,
+                            nullptr, 0.f, ea, nullptr, nullptr, /*deferred=*/true);
+}
+
+int mgs_raster_backward_pose_deferred(int32_t W, int32_t H, const void* pose_state, const float* dL_dout_color,
+                                      const float* dL_dout_depth, float* tau_image, float* dL_dtau_sum, void* stream) {
+  if (W <= 0 || H <= 0 || !pose_state || !dL_dout_color || (!tau_image && !dL_dtau_sum)) { set_error("backward_pose_deferred: bad arguments"); return MGS_EINVAL; }
+  return launch_pose_contract(reinterpret_cast<const float*>(pose_state), W, H, dL_dout_color, dL_dout_depth, tau_image, dL_dtau_sum,
+                              (cudaStream_t)stream);
+}
+
 // test hook: byte offsets of the workspace regions, in WsLayout order (tests read keys/ranges through it)
 int mgs_debug_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, size_t* out /* >= 17 */) {
   WsLayout L;

@@ -59,11 +59,17 @@ struct TrackTail {            // the folded update (FOLD): last CTA of the grid 
 //   of one).  A splat of a few pixels' radius reaches far fewer 4x4 blocks than 8x4 patches per covered pixel (Steiner:
 //   area + R * perimeter + block), so the number of list steps of a warp drops to max(nL, nR) of the two tighter lists
 //   and fewer lanes idle inside a step.
-// SKETCH: the epilogue evaluates the second-order (sketched Gauss-Newton) objective instead of the first-order loss and
-//   writes this pixel's Jacobian row contribution (tau[6], d/d exposure_a, d/d exposure_b, f) to sk_image[9][H][W]; the rows
-//   are formed afterwards by sketch_reduce_kernel, whatever the pixel -> row routing of the stacks (pose_backward.cu).
+// EPI = 0: the epilogue evaluates the first-order tracking loss and contracts the pose tangent.
+// EPI = 1 (sketch): it evaluates the second-order (sketched Gauss-Newton) objective instead and writes this pixel's
+//   Jacobian row contribution (tau[6], d/d exposure_a, d/d exposure_b, f) to sk_image[9][H][W]; the rows are formed
+//   afterwards by sketch_reduce_kernel, whatever the pixel -> row routing of the stacks (pose_backward.cu).
+// EPI = 2 (deferred): no loss in the kernel — the accumulators themselves go to sk_image[EA_PLANES][H][W] (E, A_r, A_g,
+//   A_b, A_depth, the depth-column sums F and the final colour / depth), and pose_contract_kernel forms
+//   tau = sum_ch g_ch (A_ch - out_ch E) once the caller's loss has produced dL/d out.  This is how the DROP-IN autograd
+//   surface gets the single pass: E and A do not depend on the loss, so forward(theta, rho) can build them before any
+//   loss exists and backward is one cheap pass over the pixels.
 // FOLD: the last CTA to finish (ticket) runs the iteration's serial tail (track_update_body) instead of a separate launch.
-template <bool HAS_DEPTH, bool FAST, bool SKETCH, int SPLIT, bool FOLD>   // FAST: ex2.approx exponent, n_touched not produced
+template <bool HAS_DEPTH, bool FAST, int EPI, int SPLIT, bool FOLD>   // FAST: ex2.approx exponent, n_touched not produced
 __global__ void __launch_bounds__(256, 3)
 blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __restrict__ tile_order, const uint2* __restrict__ ranges,
                    const SplatRec* __restrict__ recs, const float* __restrict__ jac, const float* __restrict__ bg,
@@ -72,6 +78,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
                    double* __restrict__ loss_partials, float* __restrict__ tau_sum,
                    const float* __restrict__ sk_weights, const float sk_scale, float* __restrict__ sk_image,
                    const TrackTail tail) {
+  constexpr bool SKETCH = EPI == 1, DEFER = EPI == 2;
   extern __shared__ __align__(128) unsigned char trk_smem[];
   SplatRec (*stage)[TRK_BATCH] = reinterpret_cast<SplatRec (*)[TRK_BATCH]>(trk_smem);
   float (*jstage)[TRK_BATCH * TRK_NF] =
@@ -243,8 +250,23 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     out_color[2 * plane + pix] = img[2];
     out_depth[pix] = D;
     out_opacity[pix] = 1 - T;
-    float gi[3], gd = 0.f, sk_da = 0.f, sk_db = 0.f, sk_f = 0.f;
-    if (SKETCH) {
+    if (DEFER) {
+      // planes: E 0..5 | A_r 6..11 | A_g 12..17 | A_b 18..23 | A_d 24..29 | F 30..32 | out r g b 33..35 | D 36
+#pragma unroll
+      for (int m = 0; m < 3; m++) {
+        sk_image[(2 * m) * plane + pix] = E2[m].x; sk_image[(2 * m + 1) * plane + pix] = E2[m].y;
+        sk_image[(6 + 2 * m) * plane + pix] = A02[m].x; sk_image[(7 + 2 * m) * plane + pix] = A02[m].y;
+        sk_image[(12 + 2 * m) * plane + pix] = A12[m].x; sk_image[(13 + 2 * m) * plane + pix] = A12[m].y;
+        sk_image[(18 + 2 * m) * plane + pix] = A22[m].x; sk_image[(19 + 2 * m) * plane + pix] = A22[m].y;
+        sk_image[(24 + 2 * m) * plane + pix] = Ad2[m].x; sk_image[(25 + 2 * m) * plane + pix] = Ad2[m].y;
+      }
+      sk_image[30 * plane + pix] = F0; sk_image[31 * plane + pix] = F1; sk_image[32 * plane + pix] = F2;
+      sk_image[33 * plane + pix] = img[0]; sk_image[34 * plane + pix] = img[1]; sk_image[35 * plane + pix] = img[2];
+      sk_image[36 * plane + pix] = D;
+    }
+    float gi[3] = {0.f, 0.f, 0.f}, gd = 0.f, sk_da = 0.f, sk_db = 0.f, sk_f = 0.f;
+    if (DEFER) {
+    } else if (SKETCH) {
       float l1;
       sk_f = sketch_pixel(lk, (int)pix, img, 1 - T, sk_weights[pix] * sk_scale, gi, sk_da, sk_db, l1);
       acc[0] = l1;
@@ -273,6 +295,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
       sk_image[8 * plane + pix] = sk_f;
     }
   }
+  if (DEFER) return;
   loss_block_reduce(acc, loss_partials + (size_t)tile * 4);
   if (!SKETCH) {
 #pragma unroll
@@ -309,7 +332,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
   }
 }
 
-template <bool HAS_DEPTH, bool FAST, bool SKETCH, int SPLIT, bool FOLD>
+template <bool HAS_DEPTH, bool FAST, int EPI, int SPLIT, bool FOLD>
 static int launch_trk_t(int tiles, cudaStream_t s, const int W, const int H, const int gx, const uint32_t* tile_order,
                         const uint2* ranges, const SplatRec* recs, const float* jac, const float* bg, float* out_color,
                         float* out_depth, float* out_opacity, int32_t* n_touched, const LossK& lk, float grad_scale,
@@ -320,13 +343,73 @@ static int launch_trk_t(int tiles, cudaStream_t s, const int W, const int H, con
   int dev = 0;
   MGS_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) { set_error("blend_track: device ordinal %d out of range", dev); return MGS_EINVAL; }
-  auto kern = blend_track_kernel<HAS_DEPTH, FAST, SKETCH, SPLIT, FOLD>;
+  auto kern = blend_track_kernel<HAS_DEPTH, FAST, EPI, SPLIT, FOLD>;
   if (!attr_set[dev]) {
     MGS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
     attr_set[dev] = true;
   }
   kern<<<tiles, 256, TRK_SMEM, s>>>(W, H, gx, tile_order, ranges, recs, jac, bg, out_color, out_depth, out_opacity, n_touched, lk,
                                     grad_scale, partials, tau_sum, sk_weights, sk_scale, sk_image, tail);
+  return MGS_OK;
+}
+
+// Deferred contraction (EPI = 2): tau_pixel = sum_ch g_ch (A_ch - out_ch E) + g_d (A_d - D E) + g_d F, per pixel, from the
+// accumulator planes of the forward; summed over the image (tau_sum) and / or kept per pixel (tau_image, the sketch path).
+constexpr int EA_PLANES = 37;
+__global__ void __launch_bounds__(256)
+pose_contract_kernel(const float* __restrict__ ea, const int npix, const float* __restrict__ g_color,
+                     const float* __restrict__ g_depth, float* __restrict__ tau_image, float* __restrict__ tau_sum) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  float tau[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (p < npix) {
+    const float g0 = g_color[p], g1 = g_color[npix + p], g2 = g_color[2 * (size_t)npix + p];
+    const float gd = g_depth != nullptr ? g_depth[p] : 0.f;
+    const float o0 = ea[33 * (size_t)npix + p], o1 = ea[34 * (size_t)npix + p], o2 = ea[35 * (size_t)npix + p], D = ea[36 * (size_t)npix + p];
+#pragma unroll
+    for (int k = 0; k < 6; k++) {
+      const float E = ea[k * (size_t)npix + p];
+      float t = g0 * (ea[(6 + k) * (size_t)npix + p] - o0 * E);
+      t = fmaf(g1, ea[(12 + k) * (size_t)npix + p] - o1 * E, t);
+      t = fmaf(g2, ea[(18 + k) * (size_t)npix + p] - o2 * E, t);
+      if (g_depth != nullptr) t = fmaf(gd, ea[(24 + k) * (size_t)npix + p] - D * E, t);
+      tau[k] = t;
+    }
+    if (g_depth != nullptr) {
+      tau[2] = fmaf(gd, ea[30 * (size_t)npix + p], tau[2]); tau[3] = fmaf(gd, ea[31 * (size_t)npix + p], tau[3]);
+      tau[4] = fmaf(gd, ea[32 * (size_t)npix + p], tau[4]);
+    }
+    if (tau_image != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) tau_image[k * (size_t)npix + p] = tau[k];
+    }
+  }
+  if (tau_sum == nullptr) return;
+  __shared__ float s_part[8][6];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    float x = tau[k];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+    if (lane == 0) s_part[warp][k] = x;
+  }
+  __syncthreads();
+  if (threadIdx.x < 6) {
+    float x = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; w++) x += s_part[w][threadIdx.x];
+    if (x != 0.f) atomicAdd(&tau_sum[threadIdx.x], x);
+  }
+}
+
+size_t pose_deferred_bytes(int W, int H) { return (size_t)EA_PLANES * W * H * sizeof(float); }
+
+int launch_pose_contract(const float* ea, int W, int H, const float* g_color, const float* g_depth, float* tau_image,
+                         float* tau_sum, cudaStream_t s) {
+  const int npix = W * H;
+  if (tau_sum) MGS_CUDA_TRY(cudaMemsetAsync(tau_sum, 0, 6 * sizeof(float), s));
+  MGS_PROF("pose_contract", s, pose_contract_kernel<<<(npix + 255) / 256, 256, 0, s>>>(ea, npix, g_color, g_depth, tau_image, tau_sum));
+  MGS_LAUNCH_CHECK();
   return MGS_OK;
 }
 
@@ -345,8 +428,29 @@ int blend_track_split() {
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s, const float* sk_weights, float sk_scale, float* sk_image,
-                       const TrackUpdateK* upd, uint32_t* ticket) {
+                       const TrackUpdateK* upd, uint32_t* ticket, bool deferred) {
   const int tiles = v.gx * v.gy;
+  if (deferred) {
+    // drop-in forward: exact exponent (n_touched produced), depth accumulators always (the loss is not known yet)
+    if (sk_image == nullptr || n_touched == nullptr) { set_error("blend_track: deferred mode needs the accumulator planes and n_touched"); return MGS_EINVAL; }
+    TrackTail none;
+    memset(&none, 0, sizeof(none));
+    LossK lk0{};
+    int rc0;
+    prof_begin("blend_track_deferred", s);
+    if (blend_track_split() == 2)
+      rc0 = launch_trk_t<true, false, 2, 2, false>(tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges),
+                                                  ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color, out_depth, out_opacity, n_touched,
+                                                  lk0, 0.f, nullptr, nullptr, nullptr, 0.f, sk_image, none);
+    else
+      rc0 = launch_trk_t<true, false, 2, 1, false>(tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges),
+                                                  ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color, out_depth, out_opacity, n_touched,
+                                                  lk0, 0.f, nullptr, nullptr, nullptr, 0.f, sk_image, none);
+    prof_end(s);
+    if (rc0) return rc0;
+    MGS_LAUNCH_CHECK();
+    return MGS_OK;
+  }
   if (sk_image != nullptr && (has_depth || sk_weights == nullptr)) { set_error("blend_track: the sketched epilogue is mono only and needs rand_weights"); return MGS_EINVAL; }
   if (upd != nullptr && (ticket == nullptr || sk_image != nullptr)) { set_error("blend_track: folded tail needs a ticket and the first-order epilogue"); return MGS_EINVAL; }
   TrackTail tail;
@@ -362,9 +466,9 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
   } while (0)
   int rc = MGS_OK;
   prof_begin(sk_image ? "blend_track_sketch" : "blend_track", s);
-  if (sk_image != nullptr) MGS_TRK_DISPATCH(false, true, false);
-  else if (has_depth) { if (upd) MGS_TRK_DISPATCH(true, false, true); else MGS_TRK_DISPATCH(true, false, false); }
-  else { if (upd) MGS_TRK_DISPATCH(false, false, true); else MGS_TRK_DISPATCH(false, false, false); }
+  if (sk_image != nullptr) MGS_TRK_DISPATCH(false, 1, false);
+  else if (has_depth) { if (upd) MGS_TRK_DISPATCH(true, 0, true); else MGS_TRK_DISPATCH(true, 0, false); }
+  else { if (upd) MGS_TRK_DISPATCH(false, 0, true); else MGS_TRK_DISPATCH(false, 0, false); }
   prof_end(s);
 #undef MGS_TRK_DISPATCH
 #undef MGS_TRK_ARGS

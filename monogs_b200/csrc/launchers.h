@@ -27,7 +27,12 @@ int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float*
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s, const float* sk_weights = nullptr, float sk_scale = 0.f,
-                       float* sk_image = nullptr, const struct TrackUpdateK* upd = nullptr, uint32_t* ticket = nullptr);
+                       float* sk_image = nullptr, const struct TrackUpdateK* upd = nullptr, uint32_t* ticket = nullptr,
+                       bool deferred = false);
+// deferred single pass of the drop-in surface: accumulator planes of blend_track<EPI = 2> and their contraction
+size_t pose_deferred_bytes(int W, int H);
+int launch_pose_contract(const float* ea, int W, int H, const float* g_color, const float* g_depth, float* tau_image,
+                         float* tau_sum, cudaStream_t s);
 
 struct BackwardArgs {
   ViewConst v; int P; uint32_t grad_mask;

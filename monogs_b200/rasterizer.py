@@ -97,7 +97,7 @@ def make_view(rs: GaussianRasterizationSettings, sh_coeffs: int, keep: list) -> 
 
 class RasterState:
     """What forward leaves for backward: the workspace and the sizes it was carved for."""
-    __slots__ = ("workspace", "num_rendered", "P", "sh_coeffs")
+    __slots__ = ("workspace", "num_rendered", "P", "sh_coeffs", "pose_state")
 
 
 class _DevCache(threading.local):
@@ -118,6 +118,10 @@ class _DevCache(threading.local):
 
 _cache = _DevCache()
 CAPACITY_HEADROOM = 1.25     # workspace capacity of a speculative forward = previous num_rendered of that size x this
+# Tracking through the drop-in surface (only theta / rho require a gradient, SH degree 0): the forward also accumulates the
+# loss-independent sums the pose tangent is made of, and backward is one pass over the pixels (mgs_raster_forward_pose /
+# mgs_raster_backward_pose_deferred) instead of a second walk over every tile list.
+SINGLE_PASS_TRACKING = True
 
 
 def _debug_guard(rs, s, what, args_fn, dump):
@@ -149,8 +153,10 @@ def _cpu_deep_copy(args):
     return tuple(a.detach().cpu().clone() if isinstance(a, torch.Tensor) else a for a in args)
 
 
-def raster_forward(rs, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp):
+def raster_forward(rs, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, single_pass=False):
     """Forward of the drop-in surface.  Returns (color, radii, depth, opacity, n_touched, state).
+    single_pass: the caller will only ask for the pose tangent (tracking) — state.pose_state then holds the per-pixel
+    sums for mgs_raster_backward_pose_deferred (None when the capacity guess missed, or on the first call of a size).
 
     The reference blocks the host in the middle of every forward to read num_rendered (rasterizer_impl.cu:284) before it
     can size the binning buffers.  Here the first forward of a (P, W, H) problem does the same (two stages, one read);
@@ -175,7 +181,7 @@ def raster_forward(rs, means3D, opacities, shs, colors_precomp, scales, rotation
     radii = torch.empty(P, device=dev, dtype=torch.int32)
     n_touched = torch.empty(P, device=dev, dtype=torch.int32)
     st = RasterState()
-    st.P, st.sh_coeffs = P, M
+    st.P, st.sh_coeffs, st.pose_state = P, M, None
     if P == 0:  # rasterize_points.cu:90 — legal, zero-filled outputs
         color.zero_(); depth.zero_(); opacity.zero_()
         st.workspace, st.num_rendered = torch.empty(0, device=dev, dtype=torch.uint8), 0
@@ -198,6 +204,19 @@ def raster_forward(rs, means3D, opacities, shs, colors_precomp, scales, rotation
                         "mgs_raster_preprocess")
                 L.check(lib.mgs_stream_synchronize(s), "mgs_stream_synchronize")
                 R, rerun = int(status[0]), True
+            elif single_pass and int(rs.sh_degree) == 0:
+                R_cap = int(guess * CAPACITY_HEADROOM) + 4096
+                ws = torch.empty(lib.mgs_raster_workspace_bytes(P, W, H, R_cap), device=dev, dtype=torch.uint8)
+                ps = torch.empty(lib.mgs_raster_pose_state_bytes(P, W, H), device=dev, dtype=torch.uint8)
+                L.check(lib.mgs_raster_forward_pose(C.byref(view), P, L.ptr(means3D), L.ptr(opacities), L.ptr(shs),
+                                                    L.ptr(colors_precomp), L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp),
+                                                    L.ptr(radii), L.ptr(ws), ws.numel(), R_cap, L.ptr(color), L.ptr(depth),
+                                                    L.ptr(opacity), L.ptr(n_touched), L.ptr(ps), ps.numel(),
+                                                    C.c_void_p(status.data_ptr()), C.c_void_p(cache["event"].cuda_event), s),
+                        "mgs_raster_forward_pose")
+                cache["event"].synchronize()
+                R, rerun = int(status[0]), bool(status[1])
+                st.pose_state = None if rerun else ps
             else:
                 R_cap = int(guess * CAPACITY_HEADROOM) + 4096
                 ws = torch.empty(lib.mgs_raster_workspace_bytes(P, W, H, R_cap), device=dev, dtype=torch.uint8)
@@ -297,6 +316,21 @@ def raster_backward_pose(rs, st, means3D, shs, colors_precomp, scales, rotations
     return tau, tau_image
 
 
+def raster_backward_pose_deferred(rs, st, grad_color, grad_depth, want_image=False):
+    """Pose tangent from the per-pixel sums a single-pass forward left in st.pose_state: (tau_sum[6], tau_image or None)."""
+    lib = L.lib()
+    H, W = int(rs.image_height), int(rs.image_width)
+    dev = st.pose_state.device
+    grad_color, grad_depth = _f32c(grad_color), _f32c(grad_depth)
+    tau = torch.empty(6, device=dev, dtype=torch.float32)
+    tau_image = torch.empty(6, H, W, device=dev, dtype=torch.float32) if want_image else None
+    with _on(dev):
+        L.check(lib.mgs_raster_backward_pose_deferred(W, H, L.ptr(st.pose_state), L.ptr(grad_color), L.ptr(grad_depth),
+                                                      L.ptr(tau_image), L.ptr(tau), _stream(dev)),
+                "mgs_raster_backward_pose_deferred")
+    return tau, tau_image
+
+
 def sketch_reduce(tau_image, sketch_indices, sketch_dim):
     """sketch_indices i32[stack,H,W] -> f32[stack, sketch_dim, 6]."""
     lib = L.lib()
@@ -322,9 +356,12 @@ class _RasterizeGaussians(torch.autograd.Function):
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, theta, rho,
                 raster_settings, num_backward_gaussians, sketch_mode, sketch_dim, stack_dim, sketch_dtau,
                 sketch_indices):
+        need = ctx.needs_input_grad
+        # tracking: nothing but the pose tangent (or its sketched rows) will be asked for
+        pose_only = (SINGLE_PASS_TRACKING and not any(need[:8]) and (need[8] or need[9] or (sketch_mode != 0 and need[15])))
         color, radii, depth, opacity, n_touched, st = raster_forward(
             raster_settings, means3D, opacities, _opt(sh), _opt(colors_precomp), _opt(scales), _opt(rotations),
-            _opt(cov3Ds_precomp))
+            _opt(cov3Ds_precomp), single_pass=pose_only)
         ctx.raster_settings = raster_settings
         ctx.state = st
         ctx.sketch_mode, ctx.sketch_dim, ctx.stack_dim = sketch_mode, sketch_dim, stack_dim
@@ -344,16 +381,20 @@ class _RasterizeGaussians(torch.autograd.Function):
         dev = means3D.device
         if grad_out_color is None:
             grad_out_color = torch.zeros(3, H, W, device=dev)
-        if grad_out_depth is None:
+        depth_grad = grad_out_depth          # None (mono tracking): the deferred contraction then skips the depth planes
+        if grad_out_depth is None and st.pose_state is None:
             grad_out_depth = torch.zeros(1, H, W, device=dev)
         need = ctx.needs_input_grad
         g = [None] * 17
         if ctx.sketch_mode != 0:
             # sketched Jacobian rows for stack j = 0..stack_dim-1 of repeat `repeat_iter` (__init__.py:216-253)
             assert ctx.sketch_dim <= 64
-            _, tau_image = raster_backward_pose(rs, st, means3D, _opt(sh), _opt(colors_precomp), _opt(scales),
-                                                _opt(rotations), _opt(cov3Ds_precomp), radii, grad_out_color,
-                                                grad_out_depth, want_image=True)
+            if st.pose_state is not None:
+                _, tau_image = raster_backward_pose_deferred(rs, st, grad_out_color, depth_grad, want_image=True)
+            else:
+                _, tau_image = raster_backward_pose(rs, st, means3D, _opt(sh), _opt(colors_precomp), _opt(scales),
+                                                    _opt(rotations), _opt(cov3Ds_precomp), radii, grad_out_color,
+                                                    grad_out_depth, want_image=True)
             idx = sketch_indices[ctx.repeat_iter][: ctx.stack_dim]
             g[15] = sketch_reduce(tau_image, idx, ctx.sketch_dim).to(sketch_dtau.dtype).view(sketch_dtau.shape)
             ctx.repeat_iter += 1
@@ -365,7 +406,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         if need[4]: mask |= L.GRAD_OPACITY
         if need[5] or need[6] or need[7]: mask |= L.GRAD_COV
         want_tau = need[8] or need[9]
-        if mask == 0 and want_tau:
+        if mask == 0 and want_tau and st.pose_state is not None:
+            tau, _ = raster_backward_pose_deferred(rs, st, grad_out_color, depth_grad)
+        elif mask == 0 and want_tau:
             tau, _ = raster_backward_pose(rs, st, means3D, _opt(sh), _opt(colors_precomp), _opt(scales),
                                           _opt(rotations), _opt(cov3Ds_precomp), radii, grad_out_color,
                                           grad_out_depth)

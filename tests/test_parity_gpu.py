@@ -394,3 +394,61 @@ def test_speculative_forward_recovers_from_a_wrong_capacity_guess():
     gr = ref_gpu.backward(camd, bg.cuda(), fw, scd.means3D, gc.cuda(), gd.cuda(), shs=scd.shs, scales=scd.scales * 3.0,
                           rotations=scd.rotations, sh_degree=sc.sh_degree)
     U.check_close(g["means3D"], gr["means3D"], GRAD_TOL, "means3D")
+
+
+@pytest.mark.parametrize("name,use_depth", [("ragged", True), ("dense", False), ("packed8", True)])
+def test_dropin_single_pass_tracking_matches_reference(name, use_depth):
+    """Tracking through the drop-in surface (only theta / rho require a gradient): from the second call of a size on, the
+    forward is mgs_raster_forward_pose and the backward the deferred per-pixel contraction — images bit-identical to the
+    standard forward, tangent <= 1e-3 against the reference's backward, with and without a depth gradient, and through the
+    sketch branch."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    from monogs_b200 import rasterizer as RZ
+    from oracle import ref_gpu
+    sc, cam, bg, gc, gd = _setup(name)
+    if sc.sh_degree != 0:
+        sc = sc._replace(shs=sc.shs[:, :1].contiguous(), sh_degree=0)
+    scd, camd = U.to_dev(sc), U.to_dev(cam)
+    rs = GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, bg.cuda(), 1.0, camd.viewmatrix,
+                                       camd.projmatrix, camd.projmatrix_raw, 0, camd.campos, False, False)
+    fw = ref_gpu.forward(camd, bg.cuda(), scd.means3D, scd.opacities, shs=scd.shs, scales=scd.scales, rotations=scd.rotations, sh_degree=0)
+    gdz = gd.cuda() if use_depth else torch.zeros_like(gd).cuda()
+    gr = ref_gpu.backward(camd, bg.cuda(), fw, scd.means3D, gc.cuda(), gdz, shs=scd.shs, scales=scd.scales, rotations=scd.rotations, sh_degree=0)
+    tau_ref = gr["tau"].double().sum(0).float()
+    for call in range(3):          # call 0 primes the capacity guess (two-stage forward); 1 and 2 take the single pass
+        theta, rho = torch.zeros(3, device="cuda", requires_grad=True), torch.zeros(3, device="cuda", requires_grad=True)
+        color, radii, depth, opacity, n_touched = GaussianRasterizer(rs)(
+            means3D=scd.means3D, means2D=torch.zeros_like(scd.means3D), shs=scd.shs, opacities=scd.opacities, scales=scd.scales,
+            rotations=scd.rotations, theta=theta, rho=rho)
+        if call > 0:
+            assert color.grad_fn.state.pose_state is not None, "the single-pass forward was taken"
+        loss = (color * gc.cuda()).sum() + ((depth * gd.cuda()).sum() if use_depth else 0.0)
+        loss.backward()
+        assert torch.equal(radii, fw["radii"]) and torch.equal(n_touched, fw["n_touched"])
+        U.check_close(color, fw["color"], IMG_TOL, "color"); U.check_close(depth, fw["depth"], IMG_TOL, "depth")
+        U.check_close(opacity, fw["opacity"], IMG_TOL, "opacity")
+        U.check_close(torch.cat([rho.grad, theta.grad]), tau_ref, GRAD_TOL, f"tau, call {call}")
+    # sketch branch on the single-pass state
+    d, stacks = 8, 2
+    idx = torch.randint(-1, d, (1, stacks, cam.H, cam.W), generator=torch.Generator().manual_seed(3), dtype=torch.int32).cuda()
+    sketch_dtau = torch.empty(stacks, d, 6, device="cuda", requires_grad=True)
+    color, _, depth, _, _ = GaussianRasterizer(rs)(
+        means3D=scd.means3D, means2D=torch.zeros_like(scd.means3D), shs=scd.shs, opacities=scd.opacities, scales=scd.scales,
+        rotations=scd.rotations, theta=torch.zeros(3, device="cuda", requires_grad=True), rho=torch.zeros(3, device="cuda", requires_grad=True),
+        sketch_mode=1, sketch_dim=d, stack_dim=stacks, sketch_dtau=sketch_dtau, sketch_indices=idx)
+    assert color.grad_fn.state.pose_state is not None
+    ((color * gc.cuda()).sum() + ((depth * gd.cuda()).sum() if use_depth else 0.0)).backward()
+    for j in range(stacks):
+        ref_tau = ref_gpu.backward_sketch(camd, bg.cuda(), fw, scd.means3D, gc.cuda(), gdz, idx[0, j].contiguous(), d, shs=scd.shs,
+                                          scales=scd.scales, rotations=scd.rotations, sh_degree=0)
+        U.check_close(sketch_dtau.grad[j], ref_tau.double().sum(0).float(), GRAD_TOL, f"sketch stack {j}")
+    # the switch: with SINGLE_PASS_TRACKING off the same call takes the two-pass backward
+    RZ.SINGLE_PASS_TRACKING = False
+    try:
+        theta = torch.zeros(3, device="cuda", requires_grad=True)
+        color, _, _, _, _ = GaussianRasterizer(rs)(means3D=scd.means3D, means2D=torch.zeros_like(scd.means3D), shs=scd.shs,
+                                                  opacities=scd.opacities, scales=scd.scales, rotations=scd.rotations, theta=theta,
+                                                  rho=torch.zeros(3, device="cuda", requires_grad=True))
+        assert color.grad_fn.state.pose_state is None
+    finally:
+        RZ.SINGLE_PASS_TRACKING = True
