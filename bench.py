@@ -170,9 +170,21 @@ def profile_row(kernel_prefix):
             for tok in ln.split(":", 1)[1].split():
                 f, _, h = tok.partition("=")
                 shas[f] = h
+    # only the translation unit that defines the kernel and the headers it includes (transitively) decide staleness
+    csrc = os.path.join(ROOT, "monogs_b200", "csrc")
+    relevant, todo = set(), [f for f in os.listdir(csrc) if f.endswith(".cu") and (kernel_prefix + "(") in open(os.path.join(csrc, f)).read()
+                             or f.endswith(".cu") and ("\n" + kernel_prefix) in open(os.path.join(csrc, f)).read()]
+    while todo:
+        f = todo.pop()
+        if f in relevant or not os.path.exists(os.path.join(csrc, f)):
+            continue
+        relevant.add(f)
+        todo += re.findall(r'#include "([\w.]+)"', open(os.path.join(csrc, f)).read())
     stale = []
     for f, h in shas.items():
-        fp = os.path.join(ROOT, "monogs_b200", "csrc", f)
+        if relevant and f not in relevant:
+            continue
+        fp = os.path.join(csrc, f)
         if not os.path.exists(fp) or hashlib.sha1(open(fp, "rb").read()).hexdigest()[:12] != h:
             stale.append(f)
     header, row = None, None
@@ -423,7 +435,7 @@ def ref_mapping_leg(dev, flush, P=200_000, window=8, iters=6, warmup=2):
 
 
 def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engine=True, exchange="nccl", cfg="C2",
-                ref_params=None, keep_params=None):
+                ref_params=None, keep_params=None, n_extra=0, use_graph=True, scaling="strong", profile=False):
     """Config C4: 8-keyframe mapping window, views round-robin over ranks, one allreduce of the gradient arena,
     fused Adam on every rank (exchange="peer": reduce-scatter + Adam + parameter all-gather as ONE kernel over NVLink peer
     mappings, mgs_peer_reduce_adam).  engine=True: monogs_b200.mapping.MapEngine (mgs_map_*: raw parameters, activations once
@@ -444,6 +456,8 @@ def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engin
     if sc.shs.size(1) > 1:      # config C5: SH degree 3 (gaussian_model.py:281: the rest coefficients train at lr / 20)
         raw["f_rest"], lrs["f_rest"] = sc.shs[:, 1:].to(dev).contiguous(), 2.5e-3 / 20
     shs_all = sc.shs.to(dev).contiguous()
+    n_window = window
+    window = window + n_extra          # the reference renders two random keyframes from outside the window beside it
     views = []
     for i in range(window):
         tau = torch.tensor(S.GT_TAU) * (i - window / 2) * 0.5
@@ -459,9 +473,10 @@ def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engin
     if engine:
         del shs_all
         eng = MapEngine({k: v.clone() for k, v in raw.items()}, lrs, sh_degree=deg, W=cam.W, H=cam.H, capacity_headroom=1.5,
-                        exchange=exchange)
+                        exchange=exchange, use_graph=use_graph)
         mviews = [MapView(rs, gt) for rs, gt in views]
-        run = lambda: eng.step(mviews)
+        mine = eng.set_window(mviews, n_window=n_window)      # placement: window round-robin, extras to the least-loaded ranks
+        run = lambda: eng.step()                              # the installed window, replayed from a CUDA graph (NCCL path)
         nbytes = eng.arena.nbytes()
     else:
         params = {k: v.clone().requires_grad_(True) for k, v in raw.items()}
@@ -493,11 +508,35 @@ def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engin
     if world > 1: dist.barrier()
     t = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1: dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    out = {"iters_per_s": 1e3 * iters / float(t), "n_gpus": world, "window": window, "gaussians": sc.means3D.size(0), "config": cfg,
-           "views_per_rank": len(range(rank, window, world)), "allreduce_bytes": nbytes if world > 1 else 0,
-           "scaling": "strong", "api": "MapEngine (mgs_map_*)" if engine else "drop-in autograd surface (MappingStep)",
-           "what": "8-keyframe window: per-view render+mapping loss+full backward, isotropic regulariser, one "
-                   "sum-allreduce of the gradient arena, fused Adam on every rank"}
+    from monogs_b200.mapping import assign_views
+    per_rank = assign_views(window, world, n_window)
+    out = {"iters_per_s": 1e3 * iters / float(t), "views_per_s": 1e3 * iters * window / float(t), "n_gpus": world, "window": n_window,
+           "extra_views": n_extra, "gaussians": sc.means3D.size(0), "config": cfg,
+           "views_per_rank": [len(x) for x in per_rank], "allreduce_bytes": nbytes if world > 1 else 0,
+           "scaling": scaling, "cuda_graph": bool(engine and use_graph and exchange == "nccl"),
+           "api": "MapEngine (mgs_map_*)" if engine else "drop-in autograd surface (MappingStep)",
+           "what": f"{n_window}-keyframe window{' + %d extra keyframes' % n_extra if n_extra else ''}: per-view render+mapping "
+                   "loss+full backward, isotropic regulariser, one sum-allreduce of the gradient arena, fused Adam on every rank"}
+    if engine and profile:
+        # which kernel bounds this rank's iteration: library-side CUDA events over three eager iterations (rank 0's views)
+        import ctypes as C
+        from monogs_b200 import _lib as L
+        eng.use_graph = False
+        lib = L.lib()
+        lib.mgs_profile_enable(1)
+        for _ in range(3):
+            eng.step()
+        buf = C.create_string_buffer(8192)
+        lib.mgs_profile_report(buf, 8192)
+        lib.mgs_profile_enable(0)
+        ker = {}
+        for ln in buf.value.decode().strip().splitlines():
+            name, k, ms = ln.split()
+            ker[name] = round(1e3 * float(ms) / 3, 1)
+        top = max(ker, key=ker.get)
+        out["kernels_us_per_iteration_rank0"] = ker
+        out["bound_by"] = {"kernel": top, "us_per_iteration": ker[top], "sum_of_kernels_us": round(sum(ker.values()), 1),
+                           "iteration_us": round(float(t) / iters * 1e3, 1)}
     if engine:
         # cross-GPU parity inside the timed job: every rank ends with the same parameters (bit for bit: the checksums are
         # exact float64 sums of the same float32 values), and the fused exchanges end where the NCCL path ends
@@ -714,9 +753,17 @@ def main():
             line["cpu_baseline"] = {"value": v, "unit": "iters/s", "cores": os.cpu_count(), "kind": "port", "sample": _sample_text(info)}
         nccl_params = []
         try:
-            line["mapping"] = mapping_leg(dev, rank, world, keep_params=nccl_params)
+            line["mapping"] = mapping_leg(dev, rank, world, keep_params=nccl_params, profile=True)
         except Exception as ex:
             line["mapping"] = {"error": repr(ex)[:300]}
+        try:    # the reference-shaped iteration: the window plus two random keyframes from outside it (slam_backend.py:215-242)
+            line["mapping_window_plus_2"] = mapping_leg(dev, rank, world, n_extra=2, iters=20, warmup=3)
+        except Exception as ex:
+            line["mapping_window_plus_2"] = {"error": repr(ex)[:300]}
+        try:    # weak scaling: two views per rank whatever the number of ranks (compare views_per_s across N)
+            line["mapping_weak"] = mapping_leg(dev, rank, world, window=2 * world, iters=20, warmup=3, scaling="weak")
+        except Exception as ex:
+            line["mapping_weak"] = {"error": repr(ex)[:300]}
         if world > 1:
             refp = nccl_params[0] if nccl_params else None
             try:

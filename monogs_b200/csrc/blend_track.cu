@@ -25,17 +25,27 @@
 #include <cstdlib>
 #include <cstring>
 
-#ifndef MGS_TRK_SPLIT_DEFAULT
-#define MGS_TRK_SPLIT_DEFAULT 1
-#endif
 
 namespace mgs {
 
-constexpr int TRK_BATCH = 128;
 constexpr int TRK_NF = POSE_BASIS_FLOATS;   // 32
-
 constexpr int TRK_STAGES = 3;
-constexpr size_t TRK_SMEM = (size_t)TRK_STAGES * TRK_BATCH * sizeof(SplatRec) + 2 * (size_t)TRK_BATCH * TRK_NF * sizeof(float);
+// One CTA (8 warps) per 16x16 tile; records and bases are staged per batch of 128 splats by the whole CTA (50 KB of
+// shared memory), one CTA barrier per batch.  MGS_TRK_MIN_CTAS = resident CTAs per SM the kernel is compiled for: 3 (80
+// registers, no spill) or 4 (64 registers, a few spilled words, 32 warps per SM instead of 24).
+// Variants that were built, measured on the B200 and dropped (profiles/r02_notes.txt): half-warp cursors over 4x4 blocks,
+// two pixels per thread, half-tile CTAs, and per-warp record rings without any CTA barrier.
+#ifndef MGS_TRK_MIN_CTAS
+#define MGS_TRK_MIN_CTAS 3
+#endif
+#ifndef MGS_TRK_MIN_CTAS_DEPTH
+#define MGS_TRK_MIN_CTAS_DEPTH 3   // the RGB-D variants carry 9 more accumulators
+#endif
+template <int NW> struct TrkCfg {
+  static constexpr int kThreads = NW * 32;
+  static constexpr int kBatch = 128;
+  static constexpr size_t kSmem = (size_t)TRK_STAGES * kBatch * sizeof(SplatRec) + 2 * (size_t)kBatch * TRK_NF * sizeof(float);
+};
 
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
@@ -53,12 +63,7 @@ struct TrackTail {            // the folded update (FOLD): last CTA of the grid 
 // (their ids come from the records of i+1, already landed), batch i being blended: one CTA barrier (the early-out
 // vote) per batch and no load latency on the blend path.
 //
-// SPLIT = 1: the warp owns an 8x4 pixel patch and walks ONE list of the splats that can reach it.
-// SPLIT = 2: the warp's two half-warps own a 4x4 block each and walk their OWN lists side by side in the same
-//   instruction stream (lanes 0-15 at splat jL, lanes 16-31 at splat jR; shared-memory reads see two addresses instead
-//   of one).  A splat of a few pixels' radius reaches far fewer 4x4 blocks than 8x4 patches per covered pixel (Steiner:
-//   area + R * perimeter + block), so the number of list steps of a warp drops to max(nL, nR) of the two tighter lists
-//   and fewer lanes idle inside a step.
+// A warp owns an 8x4 pixel patch and walks the splats of the batch that can reach it (lane-parallel exact cull).
 // EPI = 0: the epilogue evaluates the first-order tracking loss and contracts the pose tangent.
 // EPI = 1 (sketch): it evaluates the second-order (sketched Gauss-Newton) objective instead and writes this pixel's
 //   Jacobian row contribution (tau[6], d/d exposure_a, d/d exposure_b, f) to sk_image[9][H][W]; the rows are formed
@@ -69,8 +74,8 @@ struct TrackTail {            // the folded update (FOLD): last CTA of the grid 
 //   surface gets the single pass: E and A do not depend on the loss, so forward(theta, rho) can build them before any
 //   loss exists and backward is one cheap pass over the pixels.
 // FOLD: the last CTA to finish (ticket) runs the iteration's serial tail (track_update_body) instead of a separate launch.
-template <bool HAS_DEPTH, bool FAST, int EPI, int SPLIT, bool FOLD>   // FAST: ex2.approx exponent, n_touched not produced
-__global__ void __launch_bounds__(256, 3)
+template <bool HAS_DEPTH, bool FAST, int EPI, int NW, bool FOLD>   // FAST: ex2.approx exponent, n_touched not produced
+__global__ void __launch_bounds__(NW * 32, HAS_DEPTH ? MGS_TRK_MIN_CTAS_DEPTH : MGS_TRK_MIN_CTAS)
 blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __restrict__ tile_order, const uint2* __restrict__ ranges,
                    const SplatRec* __restrict__ recs, const float* __restrict__ jac, const float* __restrict__ bg,
                    float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
@@ -79,58 +84,29 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
                    const float* __restrict__ sk_weights, const float sk_scale, float* __restrict__ sk_image,
                    const TrackTail tail) {
   constexpr bool SKETCH = EPI == 1, DEFER = EPI == 2;
+  constexpr int TRK_BATCH = TrkCfg<NW>::kBatch, THREADS = NW * 32;
   extern __shared__ __align__(128) unsigned char trk_smem[];
   SplatRec (*stage)[TRK_BATCH] = reinterpret_cast<SplatRec (*)[TRK_BATCH]>(trk_smem);
   float (*jstage)[TRK_BATCH * TRK_NF] =
       reinterpret_cast<float (*)[TRK_BATCH * TRK_NF]>(trk_smem + (size_t)TRK_STAGES * TRK_BATCH * sizeof(SplatRec));
   __shared__ __align__(8) uint64_t full_bar[TRK_STAGES];
-  __shared__ float s_part[8][6];
+  __shared__ float s_part[NW][6];
   __shared__ int s_last;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int tile = (int)tile_order[(size_t)blockIdx.x * TILE_CTR_STRIDE + 3];   // heavy tiles first (tile_scan_kernel)
+  const int tile = (int)tile_order[(size_t)blockIdx.x * TILE_CTR_STRIDE + 3];   // heavy tiles first (tile_scan_body)
   const int tx = tile % gx, ty = tile / gx;
-  // pixel of this lane inside the warp's 8x4 patch: row-major for SPLIT = 1; for SPLIT = 2 the half-warps are the left
-  // and the right 4x4 block
-  const int half = lane >> 4;
-  const int lx = SPLIT == 2 ? half * 4 + (lane & 3) : (lane & 7);
-  const int ly = SPLIT == 2 ? ((lane >> 2) & 3) : (lane >> 3);
-  const int px = tx * TILE_X + (warp & 1) * 8 + lx;
-  const int py = ty * TILE_Y + (warp >> 1) * 4 + ly;
+  const int wrow = warp >> 1;   // which 4-row band of the tile
+  const int px = tx * TILE_X + (warp & 1) * 8 + (lane & 7);
+  const int py = ty * TILE_Y + wrow * 4 + (lane >> 3);
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
-  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + (warp >> 1) * 4);
+  const float patch_x0 = (float)(tx * TILE_X + (warp & 1) * 8), patch_y0 = (float)(ty * TILE_Y + wrow * 4);
 
   const uint2 range = ranges[tile];
   const int n = (int)(range.y - range.x);
   const int rounds = (n + TRK_BATCH - 1) / TRK_BATCH;
   const SplatRec* src = recs + range.x;
-
-  if (tid == 0) {
-#pragma unroll
-    for (int s = 0; s < TRK_STAGES; s++) mbar_init(&full_bar[s], 1);
-    mbar_init_fence();
-  }
-  __syncthreads();
-  auto issue = [&](int i) {   // records of batch i -> stage[i % 3]
-    const uint32_t bytes = (uint32_t)min(n - i * TRK_BATCH, TRK_BATCH) * sizeof(SplatRec);
-    mbar_expect_tx(&full_bar[i % TRK_STAGES], bytes);
-    bulk_g2s(&stage[i % TRK_STAGES][0], src + (size_t)i * TRK_BATCH, bytes, &full_bar[i % TRK_STAGES]);
-  };
-  auto wait_records = [&](int i) { mbar_wait(&full_bar[i % TRK_STAGES], (i / TRK_STAGES) & 1); };
-  auto gather = [&](int i) {  // pose bases of batch i (L2-resident per-Gaussian array) -> jstage[i & 1], 16 B per cp.async
-    const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
-    const float4* rec4 = reinterpret_cast<const float4*>(&stage[i % TRK_STAGES][0]);
-    float4* dst = reinterpret_cast<float4*>(&jstage[i & 1][0]);
-    for (int e = tid; e < cnt * (TRK_NF / 4); e += 256) {
-      const int slot = e / (TRK_NF / 4), k = e - slot * (TRK_NF / 4);
-      const uint32_t id = __float_as_uint(rec4[3 * slot + 0].w);
-      cp_async16(dst + e, reinterpret_cast<const float4*>(jac + (size_t)id * TRK_NF) + k);
-    }
-    cp_async_commit();
-  };
-  if (tid == 0 && rounds > 0) { issue(0); if (rounds > 1) issue(1); }
-  if (rounds > 0) { wait_records(0); gather(0); }
 
   bool done = !inside;
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
@@ -141,98 +117,119 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
 #pragma unroll
   for (int k = 0; k < 3; k++) { E2[k] = A02[k] = A12[k] = A22[k] = Ad2[k] = make_float2(0.f, 0.f); }
 
-  for (int i = 0; i < rounds; i++) {
-    cp_async_wait_all();   // this thread's share of the bases of batch i has landed
-    // CTA vote; publishes the bases of batch i and guarantees every warp left the buffers reused below
-    if (__syncthreads_count(done) == TILE_PIX) {
-      if (tid == 0 && i + 1 < rounds) wait_records(i + 1);   // never exit with a bulk copy in flight
-      break;
+  // one (warp, splat) step: rec4 = the staged records, j = the splat's slot in them, jrow = its 32-float basis
+  auto hit = [&](const float4* __restrict__ rec4, const int j, const float* __restrict__ jrow) {
+    const float4 g0 = rec4[3 * j + 0], g1 = rec4[3 * j + 1];   // x, y, depth, id | conic xyz, opacity
+    const float dx = g0.x - pxf, dy = g0.y - pyf;
+    const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
+    bool valid = !done && !(power > 0.0f);
+    const float G = blend_exp<FAST>(power);
+    const float alpha = min(0.99f, g1.w * G);
+    valid = valid && !(alpha < 1.0f / 255.0f);
+    const float test_T = T * (1 - alpha);
+    if (valid && test_T < 0.0001f) { done = true; valid = false; }
+    if (!FAST) {
+      const unsigned touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
+      if (touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
     }
-    if (tid == 0 && i + 2 < rounds) issue(i + 2);
-    if (i + 1 < rounds) { wait_records(i + 1); gather(i + 1); }
-    const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
-    const float4* rec4 = reinterpret_cast<const float4*>(&stage[i % TRK_STAGES][0]);
-    const float* recf = reinterpret_cast<const float*>(&stage[i % TRK_STAGES][0]);
-    const float* jst = &jstage[i & 1][0];
-    for (int c0 = 0; c0 < cnt; c0 += 32) {
-      // lane-parallel exact cull of 32 splats against this warp's patch (SPLIT = 2: against each of its two 4x4 blocks)
-      const int jj = c0 + lane;
-      unsigned mine;
-      if (SPLIT == 2) {
-        const bool ok = jj < cnt;
-        const unsigned hl = __ballot_sync(0xffffffffu, ok && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 3.f, patch_y0, patch_y0 + 3.f));
-        const unsigned hr = __ballot_sync(0xffffffffu, ok && splat_hits(recf + 12 * jj, patch_x0 + 4.f, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
-        mine = half ? hr : hl;
-      } else {
-        mine = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+    if (__ballot_sync(0xffffffffu, valid) == 0u) return;
+    if (valid) {
+      const float4* J4 = reinterpret_cast<const float4*>(jrow);
+      const float4 b0 = J4[0], b1 = J4[1], b2 = J4[2], b3 = J4[3], b4 = J4[4], b5 = J4[5], b6 = J4[6], b7 = J4[7];
+      const float4 g2 = rec4[3 * j + 2];
+      // folded basis rows: U = f[0..5], V = f[6..11], A = f[12..17], Bm = f[18..23], Cm = f[24..29], yC, -xC
+      const float2 dx2 = make_float2(dx, dx), dy2 = make_float2(dy, dy);
+      float2 t1[3], t2[3], vp2[3];
+      // t1 = U + dx * A + dy * Bm ; t2 = V + dy * Cm ; vp = dx * t1 + dy * t2
+      t1[0] = __ffma2_rn(dx2, make_float2(b3.x, b3.y), make_float2(b0.x, b0.y));
+      t1[1] = __ffma2_rn(dx2, make_float2(b3.z, b3.w), make_float2(b0.z, b0.w));
+      t1[2] = __ffma2_rn(dx2, make_float2(b4.x, b4.y), make_float2(b1.x, b1.y));
+      t1[0] = __ffma2_rn(dy2, make_float2(b4.z, b4.w), t1[0]);
+      t1[1] = __ffma2_rn(dy2, make_float2(b5.x, b5.y), t1[1]);
+      t1[2] = __ffma2_rn(dy2, make_float2(b5.z, b5.w), t1[2]);
+      t2[0] = __ffma2_rn(dy2, make_float2(b6.x, b6.y), make_float2(b1.z, b1.w));
+      t2[1] = __ffma2_rn(dy2, make_float2(b6.z, b6.w), make_float2(b2.x, b2.y));
+      t2[2] = __ffma2_rn(dy2, make_float2(b7.x, b7.y), make_float2(b2.z, b2.w));
+#pragma unroll
+      for (int m = 0; m < 3; m++) vp2[m] = __ffma2_rn(dy2, t2[m], __fmul2_rn(dx2, t1[m]));
+      // s = opacity * G / (1 - alpha): d alpha / d(geometry) up to the polynomial, times r_i (1-alpha in [0.01,1])
+      const float sE = g1.w * G * rcp_unit(1.f - alpha);
+      const float s0 = sE * fmaf(T, g2.x, C0), s1 = sE * fmaf(T, g2.y, C1), s2 = sE * fmaf(T, g2.z, C2);
+      const float2 sE2 = make_float2(sE, sE), s02 = make_float2(s0, s0), s12 = make_float2(s1, s1), s22 = make_float2(s2, s2);
+#pragma unroll
+      for (int m = 0; m < 3; m++) {
+        E2[m] = __ffma2_rn(sE2, vp2[m], E2[m]);
+        A02[m] = __ffma2_rn(s02, vp2[m], A02[m]);
+        A12[m] = __ffma2_rn(s12, vp2[m], A12[m]);
+        A22[m] = __ffma2_rn(s22, vp2[m], A22[m]);
       }
-      if (__ballot_sync(0xffffffffu, !done) == 0u) break;
-      while (SPLIT == 2 ? __any_sync(0xffffffffu, mine != 0u) : (mine != 0u)) {
-        const bool act = SPLIT == 2 ? (mine != 0u) : true;
-        const int j = c0 + (act ? __ffs(mine) - 1 : 0);
-        mine &= mine - 1;
-        const float4 g0 = rec4[3 * j + 0];  // x, y, depth, id
-        const float4 g1 = rec4[3 * j + 1];  // conic xyz, opacity
-        const float dx = g0.x - pxf, dy = g0.y - pyf;
-        const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
-        bool valid = act && !done && !(power > 0.0f);
-        const float G = blend_exp<FAST>(power);
-        const float alpha = min(0.99f, g1.w * G);
-        valid = valid && !(alpha < 1.0f / 255.0f);
-        const float test_T = T * (1 - alpha);
-        if (valid && test_T < 0.0001f) { done = true; valid = false; }
-        if (!FAST) {
-          const unsigned touch = __ballot_sync(0xffffffffu, valid && test_T > 0.5f);
-          if (SPLIT == 2) {
-            const unsigned th = half ? (touch >> 16) : (touch & 0xffffu);
-            if (th != 0u && (lane & 15) == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(th));
-          } else if (touch != 0u && lane == 0) atomicAdd(&n_touched[__float_as_uint(g0.w)], __popc(touch));
-        }
-        if (__ballot_sync(0xffffffffu, valid) == 0u) continue;
-        if (valid) {
-          const float4 g2 = rec4[3 * j + 2];
-          const float4* J4 = reinterpret_cast<const float4*>(jst + j * TRK_NF);
-          // folded basis rows: U = f[0..5], V = f[6..11], A = f[12..17], Bm = f[18..23], Cm = f[24..29], yC, -xC
-          const float4 b0 = J4[0], b1 = J4[1], b2 = J4[2], b3 = J4[3], b4 = J4[4], b5 = J4[5], b6 = J4[6], b7 = J4[7];
-          const float2 dx2 = make_float2(dx, dx), dy2 = make_float2(dy, dy);
-          float2 t1[3], t2[3], vp2[3];
-          // t1 = U + dx * A + dy * Bm ; t2 = V + dy * Cm ; vp = dx * t1 + dy * t2
-          t1[0] = __ffma2_rn(dx2, make_float2(b3.x, b3.y), make_float2(b0.x, b0.y));
-          t1[1] = __ffma2_rn(dx2, make_float2(b3.z, b3.w), make_float2(b0.z, b0.w));
-          t1[2] = __ffma2_rn(dx2, make_float2(b4.x, b4.y), make_float2(b1.x, b1.y));
-          t1[0] = __ffma2_rn(dy2, make_float2(b4.z, b4.w), t1[0]);
-          t1[1] = __ffma2_rn(dy2, make_float2(b5.x, b5.y), t1[1]);
-          t1[2] = __ffma2_rn(dy2, make_float2(b5.z, b5.w), t1[2]);
-          t2[0] = __ffma2_rn(dy2, make_float2(b6.x, b6.y), make_float2(b1.z, b1.w));
-          t2[1] = __ffma2_rn(dy2, make_float2(b6.z, b6.w), make_float2(b2.x, b2.y));
-          t2[2] = __ffma2_rn(dy2, make_float2(b7.x, b7.y), make_float2(b2.z, b2.w));
+      if (HAS_DEPTH) {
+        const float aT = alpha * T;
+        const float sd = sE * fmaf(T, g0.z, D);
+        const float2 sd2 = make_float2(sd, sd);
 #pragma unroll
-          for (int m = 0; m < 3; m++) vp2[m] = __ffma2_rn(dy2, t2[m], __fmul2_rn(dx2, t1[m]));
-          // s = opacity * G / (1 - alpha): d alpha / d(geometry) up to the polynomial, times r_i (1-alpha in [0.01,1])
-          const float sE = g1.w * G * rcp_unit(1.f - alpha);
-          const float s0 = sE * fmaf(T, g2.x, C0), s1 = sE * fmaf(T, g2.y, C1), s2 = sE * fmaf(T, g2.z, C2);
-          const float2 sE2 = make_float2(sE, sE), s02 = make_float2(s0, s0), s12 = make_float2(s1, s1), s22 = make_float2(s2, s2);
+        for (int m = 0; m < 3; m++) Ad2[m] = __ffma2_rn(sd2, vp2[m], Ad2[m]);
+        // depth column of B: dz/dtau = (0, 0, 1, y_C, -x_C, 0)
+        F0 += aT; F1 = fmaf(aT, b7.z, F1); F2 = fmaf(aT, b7.w, F2);
+      }
+      C0 += g2.x * alpha * T;   // same expression as forward.cu:364-367 / blend_forward.cu: identical image bits
+      C1 += g2.y * alpha * T;
+      C2 += g2.z * alpha * T;
+      D += g0.z * alpha * T;
+      T = test_T;
+    }
+  };
+
+  {
+    // ---- one CTA per tile: records and bases of a batch are staged by the whole CTA, one barrier per batch ----
+    if (tid == 0) {
 #pragma unroll
-          for (int m = 0; m < 3; m++) {
-            E2[m] = __ffma2_rn(sE2, vp2[m], E2[m]);
-            A02[m] = __ffma2_rn(s02, vp2[m], A02[m]);
-            A12[m] = __ffma2_rn(s12, vp2[m], A12[m]);
-            A22[m] = __ffma2_rn(s22, vp2[m], A22[m]);
-          }
-          if (HAS_DEPTH) {
-            const float aT = alpha * T;
-            const float sd = sE * fmaf(T, g0.z, D);
-            const float2 sd2 = make_float2(sd, sd);
-#pragma unroll
-            for (int m = 0; m < 3; m++) Ad2[m] = __ffma2_rn(sd2, vp2[m], Ad2[m]);
-            // depth column of B: dz/dtau = (0, 0, 1, y_C, -x_C, 0)
-            F0 += aT; F1 = fmaf(aT, b7.z, F1); F2 = fmaf(aT, b7.w, F2);
-          }
-          C0 += g2.x * alpha * T;   // same expression as forward.cu:364-367 / blend_forward.cu: identical image bits
-          C1 += g2.y * alpha * T;
-          C2 += g2.z * alpha * T;
-          D += g0.z * alpha * T;
-          T = test_T;
+      for (int s = 0; s < TRK_STAGES; s++) mbar_init(&full_bar[s], 1);
+      mbar_init_fence();
+    }
+    __syncthreads();
+    auto issue = [&](int i) {   // records of batch i -> stage[i % 3]
+      const uint32_t bytes = (uint32_t)min(n - i * TRK_BATCH, TRK_BATCH) * sizeof(SplatRec);
+      mbar_expect_tx(&full_bar[i % TRK_STAGES], bytes);
+      bulk_g2s(&stage[i % TRK_STAGES][0], src + (size_t)i * TRK_BATCH, bytes, &full_bar[i % TRK_STAGES]);
+    };
+    auto wait_records = [&](int i) { mbar_wait(&full_bar[i % TRK_STAGES], (i / TRK_STAGES) & 1); };
+    auto gather = [&](int i) {  // pose bases of batch i (L2-resident per-Gaussian array) -> jstage[i & 1], 16 B per cp.async
+      const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
+      const float4* rec4 = reinterpret_cast<const float4*>(&stage[i % TRK_STAGES][0]);
+      float4* dst = reinterpret_cast<float4*>(&jstage[i & 1][0]);
+      for (int e = tid; e < cnt * (TRK_NF / 4); e += THREADS) {
+        const int slot = e / (TRK_NF / 4), k = e - slot * (TRK_NF / 4);
+        const uint32_t id = __float_as_uint(rec4[3 * slot + 0].w);
+        cp_async16(dst + e, reinterpret_cast<const float4*>(jac + (size_t)id * TRK_NF) + k);
+      }
+      cp_async_commit();
+    };
+    if (tid == 0 && rounds > 0) { issue(0); if (rounds > 1) issue(1); }
+    if (rounds > 0) { wait_records(0); gather(0); }
+    for (int i = 0; i < rounds; i++) {
+      cp_async_wait_all();   // this thread's share of the bases of batch i has landed
+      // CTA vote; publishes the bases of batch i and guarantees every warp left the buffers reused below
+      if (__syncthreads_count(done) == THREADS) {
+        if (tid == 0 && i + 1 < rounds) wait_records(i + 1);   // never exit with a bulk copy in flight
+        break;
+      }
+      if (tid == 0 && i + 2 < rounds) issue(i + 2);
+      if (i + 1 < rounds) { wait_records(i + 1); gather(i + 1); }
+      const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
+      const float4* rec4 = reinterpret_cast<const float4*>(&stage[i % TRK_STAGES][0]);
+      const float* recf = reinterpret_cast<const float*>(&stage[i % TRK_STAGES][0]);
+      const float* jst = &jstage[i & 1][0];
+      for (int c0 = 0; c0 < cnt; c0 += 32) {
+        // lane-parallel exact cull of 32 splats against this warp's 8x4 patch (see splat_extent)
+        const int jj = c0 + lane;
+        unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+        if (__ballot_sync(0xffffffffu, !done) == 0u) break;
+        if (hits == 0u) continue;
+        while (hits != 0u) {
+          const int j = c0 + __ffs(hits) - 1;
+          hits &= hits - 1;
+          hit(rec4, j, jst + j * TRK_NF);
         }
       }
     }
@@ -296,7 +293,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     }
   }
   if (DEFER) return;
-  loss_block_reduce(acc, loss_partials + (size_t)tile * 4);
+  loss_block_reduce(acc, loss_partials + (size_t)blockIdx.x * 4);      // one slot per CTA (two per tile when NW = 4)
   if (!SKETCH) {
 #pragma unroll
     for (int k = 0; k < 6; k++) {
@@ -309,7 +306,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     if (tid < 6) {
       float x = 0.f;
 #pragma unroll
-      for (int w = 0; w < 8; w++) x += s_part[w][tid];
+      for (int w = 0; w < NW; w++) x += s_part[w][tid];
       if (x != 0.f) atomicAdd(&tau_sum[tid], x);
     }
     if (FOLD) {
@@ -332,7 +329,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
   }
 }
 
-template <bool HAS_DEPTH, bool FAST, int EPI, int SPLIT, bool FOLD>
+template <bool HAS_DEPTH, bool FAST, int EPI, int NW, bool FOLD>
 static int launch_trk_t(int tiles, cudaStream_t s, const int W, const int H, const int gx, const uint32_t* tile_order,
                         const uint2* ranges, const SplatRec* recs, const float* jac, const float* bg, float* out_color,
                         float* out_depth, float* out_opacity, int32_t* n_touched, const LossK& lk, float grad_scale,
@@ -343,13 +340,14 @@ static int launch_trk_t(int tiles, cudaStream_t s, const int W, const int H, con
   int dev = 0;
   MGS_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) { set_error("blend_track: device ordinal %d out of range", dev); return MGS_EINVAL; }
-  auto kern = blend_track_kernel<HAS_DEPTH, FAST, EPI, SPLIT, FOLD>;
+  auto kern = blend_track_kernel<HAS_DEPTH, FAST, EPI, NW, FOLD>;
   if (!attr_set[dev]) {
-    MGS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TRK_SMEM));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TrkCfg<NW>::kSmem));
     attr_set[dev] = true;
   }
-  kern<<<tiles, 256, TRK_SMEM, s>>>(W, H, gx, tile_order, ranges, recs, jac, bg, out_color, out_depth, out_opacity, n_touched, lk,
-                                    grad_scale, partials, tau_sum, sk_weights, sk_scale, sk_image, tail);
+  kern<<<tiles, NW * 32, TrkCfg<NW>::kSmem, s>>>(W, H, gx, tile_order, ranges, recs, jac, bg, out_color, out_depth,
+                                                                     out_opacity, n_touched, lk, grad_scale, partials, tau_sum,
+                                                                     sk_weights, sk_scale, sk_image, tail);
   return MGS_OK;
 }
 
@@ -413,14 +411,7 @@ int launch_pose_contract(const float* ea, int W, int H, const float* g_color, co
   return MGS_OK;
 }
 
-int blend_track_split() {
-  // MGS_TRK_SPLIT=1|2 overrides the built-in choice (read once; a tuning knob, like MGS_PEER_VARIANT)
-  static int split = [] {
-    const char* e = getenv("MGS_TRK_SPLIT");
-    return (e && e[0] == '1') ? 1 : ((e && e[0] == '2') ? 2 : MGS_TRK_SPLIT_DEFAULT);
-  }();
-  return split;
-}
+int blend_track_warps() { return 8; }
 
 // tau_sum must be zero on entry (the folded tail re-zeroes it); jac holds the folded per-Gaussian bases
 // (POSE_BASIS_FLOATS).  sk_image != nullptr selects the second-order epilogue (mono only): sk_weights f32[H,W] (+-1),
@@ -438,12 +429,7 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
     LossK lk0{};
     int rc0;
     prof_begin("blend_track_deferred", s);
-    if (blend_track_split() == 2)
-      rc0 = launch_trk_t<true, false, 2, 2, false>(tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges),
-                                                  ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color, out_depth, out_opacity, n_touched,
-                                                  lk0, 0.f, nullptr, nullptr, nullptr, 0.f, sk_image, none);
-    else
-      rc0 = launch_trk_t<true, false, 2, 1, false>(tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges),
+      rc0 = launch_trk_t<true, false, 2, 8, false>(tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges),
                                                   ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color, out_depth, out_opacity, n_touched,
                                                   lk0, 0.f, nullptr, nullptr, nullptr, 0.f, sk_image, none);
     prof_end(s);
@@ -456,13 +442,11 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
   TrackTail tail;
   memset(&tail, 0, sizeof(tail));
   if (upd) { tail.k = *upd; tail.ticket = ticket; tail.tau_raw = tau_sum; }
-  const int split = blend_track_split();
 #define MGS_TRK_ARGS tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), \
       jac, v.bg, out_color, out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum, sk_weights, sk_scale, sk_image, tail
 #define MGS_TRK_DISPATCH(HD, SK, FO)                                                                                                   \
   do {                                                                                                                                 \
-    if (split == 2) rc = fl.fast ? launch_trk_t<HD, true, SK, 2, FO>(MGS_TRK_ARGS) : launch_trk_t<HD, false, SK, 2, FO>(MGS_TRK_ARGS); \
-    else rc = fl.fast ? launch_trk_t<HD, true, SK, 1, FO>(MGS_TRK_ARGS) : launch_trk_t<HD, false, SK, 1, FO>(MGS_TRK_ARGS);            \
+    rc = fl.fast ? launch_trk_t<HD, true, SK, 8, FO>(MGS_TRK_ARGS) : launch_trk_t<HD, false, SK, 8, FO>(MGS_TRK_ARGS);            \
   } while (0)
   int rc = MGS_OK;
   prof_begin(sk_image ? "blend_track_sketch" : "blend_track", s);

@@ -29,6 +29,7 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
                        float* tau_sum, cudaStream_t s, const float* sk_weights = nullptr, float sk_scale = 0.f,
                        float* sk_image = nullptr, const struct TrackUpdateK* upd = nullptr, uint32_t* ticket = nullptr,
                        bool deferred = false);
+int blend_track_warps();      // 8 or 4: CTAs per tile = 8 / warps; loss partial slots = tiles * 8 / warps
 // deferred single pass of the drop-in surface: accumulator planes of blend_track<EPI = 2> and their contraction
 size_t pose_deferred_bytes(int W, int H);
 int launch_pose_contract(const float* ea, int W, int H, const float* g_color, const float* g_depth, float* tau_image,

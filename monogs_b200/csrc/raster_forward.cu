@@ -416,9 +416,13 @@ preprocess_kernel(const ViewConst v, const int P,
   });
   if constexpr (FOLD_SCAN) {
     __shared__ int s_last;
-    __threadfence();            // this thread's counter atomics are ordered before the CTA's ticket
+    // the CTA barrier orders every thread's counter atomics before thread 0's fence (fences are cumulative), which orders
+    // them before the ticket: one MEMBAR per CTA instead of one per thread
     __syncthreads();
-    if (threadIdx.x == 0) s_last = (atomicAdd(&hdr->ticket, 1u) == gridDim.x - 1) ? 1 : 0;
+    if (threadIdx.x == 0) {
+      __threadfence();
+      s_last = (atomicAdd(&hdr->ticket, 1u) == gridDim.x - 1) ? 1 : 0;
+    }
     __syncthreads();
     if (s_last) {
       __threadfence();

@@ -143,7 +143,7 @@ size_t mgs_track_scratch_bytes(int32_t P, int32_t W, int32_t H) {
   const size_t Pp = P > 0 ? P : 1, npix = (size_t)W * H;
   const size_t tiles = (size_t)((W + TILE_X - 1) / TILE_X) * ((H + TILE_Y - 1) / TILE_Y);
   auto up = [](size_t x) { return (x + 255) / 256 * 256; };
-  return up(Pp * PoseJac<9>::kFloats * 4) + up(3 * npix * 4) + up(npix * 4) + up(tiles * 4 * 8) + 256 +
+  return up(Pp * PoseJac<9>::kFloats * 4) + up(3 * npix * 4) + up(npix * 4) + up(2 * tiles * 4 * 8) + 256 +
          up(9 * npix * 4);   // + the per-pixel Jacobian rows of the second-order iteration
 }
 
@@ -175,7 +175,7 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   float* jac = reinterpret_cast<float*>(sp); sp += up((size_t)P * PoseJac<9>::kFloats * 4);
   float* g_img = reinterpret_cast<float*>(sp); sp += up(3 * npix * 4);
   float* g_depth = reinterpret_cast<float*>(sp); sp += up(npix * 4);
-  double* partials = reinterpret_cast<double*>(sp); sp += up((size_t)tiles * 4 * 8);
+  double* partials = reinterpret_cast<double*>(sp); sp += up((size_t)2 * tiles * 4 * 8);
   float* tau_raw = reinterpret_cast<float*>(sp);
   const bool with_color = v.D > 0;
   void* ws = t->workspace;
@@ -202,7 +202,7 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   fl.grad_scale = (t->loss_mode == MGS_LOSS_TRACK_HUBER) ? 1.f : (use_depth ? t->alpha : 1.f) / (3.f * (float)npix);
   fl.g_img = g_img; fl.g_depth = use_depth ? g_depth : nullptr; fl.partials = partials; fl.fast = t->fast_math != 0;
   TrackUpdateK k;
-  k.mode = t->loss_mode; k.use_depth = use_depth; k.npix = (int)npix; k.tiles = tiles; k.alpha = t->alpha; k.scale = 1.f;
+  k.mode = t->loss_mode; k.use_depth = use_depth; k.npix = (int)npix; k.tiles = with_color ? tiles : tiles * (8 / blend_track_warps()); k.alpha = t->alpha; k.scale = 1.f;
   k.partials = partials; k.tau_raw = tau_raw; k.loss = t->loss; k.tau = t->tau; k.dab = t->dab;
   k.params = t->params; k.exp_avg = t->exp_avg; k.exp_avg_sq = t->exp_avg_sq; k.step = t->step_counter;
   for (int i = 0; i < 4; i++) k.lr[i] = t->lr[i];
@@ -256,14 +256,14 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   char* sp = reinterpret_cast<char*>(t->scratch);
   float* jac = reinterpret_cast<float*>(sp); sp += up((size_t)P * PoseJac<9>::kFloats * 4);
   sp += up(3 * npix * 4) + up(npix * 4);
-  double* partials = reinterpret_cast<double*>(sp); sp += up((size_t)tiles * 4 * 8);
+  double* partials = reinterpret_cast<double*>(sp); sp += up((size_t)2 * tiles * 4 * 8);
   sp += 256;
   float* sk_image = reinterpret_cast<float*>(sp);
   void* ws = t->workspace;
   if (t->status_out) MGS_CUDA_TRY(cudaMemcpyAsync(t->status_out, ws, 6 * sizeof(uint32_t), cudaMemcpyDefault, s));
 
   Track2K k;
-  k.npix = (int)npix; k.tiles = tiles; k.rows = a->n_stacks * a->sketch_dim;
+  k.npix = (int)npix; k.tiles = tiles * (8 / blend_track_warps()); k.rows = a->n_stacks * a->sketch_dim;
   k.partials = partials; k.sj = a->rows; k.params = t->params; k.T = t->T_w2c;
   k.view_out = const_cast<float*>(view->viewmatrix); k.proj_out = const_cast<float*>(view->projmatrix);
   k.proj_raw = view->projmatrix_raw; k.st = a->lm_state ? a->lm_state : t->lm_state;

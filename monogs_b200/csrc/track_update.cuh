@@ -40,7 +40,7 @@ static __device__ __forceinline__ void lm_track_best(float* __restrict__ st, con
 // One CTA.  Everything the serial tail needs is staged in shared memory by separate threads while the per-tile partials
 // are being reduced (a single thread chasing ~60 dependent global loads and stores costs an L2 round trip each), the
 // double-precision bias corrections are computed by another warp meanwhile, and the results go out in parallel.
-// Callable from a 256-thread CTA: the stand-alone track_update_kernel, or the LAST CTA of blend_track_kernel (ticket in
+// Callable from a CTA of 128 or 256 threads (the roles below use tid < 96): the stand-alone track_update_kernel, or the LAST CTA of blend_track_kernel (ticket in
 // blend_track.cu), which saves a launch and the tau / counter memsets.  Inputs produced by other CTAs (partials, tau_raw)
 // are read with ld.global.cg: they were written through L2 and this SM's L1 may not be trusted.
 static __device__ __noinline__ void track_update_body(const TrackUpdateK& k) {
@@ -66,7 +66,7 @@ static __device__ __noinline__ void track_update_body(const TrackUpdateK& k) {
   double acc[4] = {0, 0, 0, 0};
   const double2* p2 = reinterpret_cast<const double2*>(k.partials);
 #pragma unroll 4
-  for (int i = tid; i < k.tiles; i += 256) {
+  for (int i = tid; i < k.tiles; i += (int)blockDim.x) {
     const double2 a = __ldcg(p2 + 2 * i), b = __ldcg(p2 + 2 * i + 1);
     acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y;
   }
@@ -83,7 +83,7 @@ static __device__ __noinline__ void track_update_body(const TrackUpdateK& k) {
     for (int q = 0; q < 4; q++) {
       double t = 0;
 #pragma unroll
-      for (int w = 0; w < 8; w++) t += red[w][q];
+      for (int w = 0; w < (int)(blockDim.x >> 5); w++) t += red[w][q];
       tot[q] = t;
     }
     float gscale = 1.f;

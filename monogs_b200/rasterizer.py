@@ -82,7 +82,8 @@ def make_view(rs: GaussianRasterizationSettings, sh_coeffs: int, keep: list) -> 
     tens = {}
     for name in ("bg", "viewmatrix", "projmatrix", "projmatrix_raw", "campos"):
         t = getattr(rs, name)
-        t = _f32c(t.to(dev)) if t is not None else None
+        if t is not None and not (t.device == dev and t.dtype == torch.float32 and t.is_contiguous()):   # fast path: as MonoGS passes them
+            t = _f32c(t.to(dev))
         keep.append(t)
         tens[name] = t
     v = L.MgsView()
@@ -124,9 +125,20 @@ CAPACITY_HEADROOM = 1.25     # workspace capacity of a speculative forward = pre
 SINGLE_PASS_TRACKING = True
 
 
+class _NoGuard:
+    def __enter__(self): return self
+    def __exit__(self, *exc): return False
+
+
+_NO_GUARD = _NoGuard()
+
+
 def _debug_guard(rs, s, what, args_fn, dump):
     """debug=True (auxiliary.h:166-173 CHECK_CUDA, __init__.py:109-116,202-209): wait for the launches of `what` and
     raise on any CUDA error; on failure the inputs are written to `dump` before the exception propagates."""
+    if not rs.debug:
+        return _NO_GUARD
+
     class _G:
         def __enter__(self_g):
             self_g.snapshot = _cpu_deep_copy(args_fn()) if rs.debug else None   # copied before they can be corrupted

@@ -105,7 +105,12 @@ hdr = (f"# ncu --metrics gpu__time_duration.sum --clock-control none  python scr
        f"# config C4 (8-keyframe mapping window, 200k Gaussians, 640x480) through MapEngine: setup + 2 iterations; commit {commit}\n"
        "# per-launch times are cold-cache and serialised: compare SHARES, not absolutes\n")
 launch_list(f"gpurun_out/{tag}_launches_map.csv", f"profiles/{tag}_launches_mapping_c4.txt", f"profiles/{tag}_launches_mapping_c4.csv", hdr)
+import glob, hashlib, os
+shas = " ".join(f"{os.path.basename(p)}={hashlib.sha1(open(p, 'rb').read()).hexdigest()[:12]}"
+                for p in sorted(glob.glob("monogs_b200/csrc/*.cu") + glob.glob("monogs_b200/csrc/*.cuh")))
 with open(f"profiles/{tag}_kernel_metrics.txt", "w") as f:
+    # bench.py (profile_row) refuses numbers from this table for a kernel whose sources changed after the capture
+    f.write(f"# source-sha1: {shas}\n")
     f.write(f"# ncu --metrics <13 metrics> --clock-control none; commit {commit}; averages over the launches of each kernel\n"
             "# us = gpu__time_duration, Minst = warp instructions, issue% = smsp__issue_active, occ% = sm__warps_active, lanes = threads per\n"
             "# instruction, fma/alu/xu% = pipe utilisation, rd/wr MB = DRAM bytes, L2MB = lts__t_bytes, lld/lst = local-memory instructions\n\n")
@@ -113,6 +118,6 @@ with open(f"profiles/{tag}_kernel_metrics.txt", "w") as f:
     metric_table(f"gpurun_out/{tag}_metrics_map.csv", f, "## mapping iteration, config C4 (python scripts/prof_map.py 1)\n")
 with open(f"profiles/{tag}_ncu_full_blend_kernels.txt", "w") as f:
     f.write(f"# ncu --set full --clock-control none --import-source on; commit {commit}\n\n")
-    full_table(f"gpurun_out/{tag}_full_track.ncu-rep", f, "## blend_track_kernel<0,1> (tracking, C2): python scripts/prof_step.py 4, -k regex:blend_track -s 2 -c 1\n", KEEP)
+    full_table(f"gpurun_out/{tag}_full_track.ncu-rep", f, "## blend_track_kernel (tracking, C2): python scripts/prof_step.py 4, -k regex:blend_track -s 2 -c 1\n", KEEP)
     full_table(f"gpurun_out/{tag}_full_map.ncu-rep", f, "## mapping blend kernels (C4, MapEngine fast_math): python scripts/prof_map.py 1, -k regex:blend -s 10 -c 2\n", KEEP)
 print("written")
