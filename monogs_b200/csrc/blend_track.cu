@@ -56,7 +56,6 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 struct TrackTail {            // the folded update (FOLD): last CTA of the grid runs track_update_body
   TrackUpdateK k;
   uint32_t* ticket;           // device u32, zero before the first launch; reset by the last CTA
-  float* tau_raw;             // zeroed by the last CTA after it has consumed it
 };
 
 // Pipeline per tile: records of batch i+2 in flight by bulk copy (TMA), pose bases of batch i+1 gathered by cp.async
@@ -322,7 +321,6 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
       if (s_last) {
         __threadfence();
         track_update_body(tail.k);
-        if (tid < 6) tail.tau_raw[tid] = 0.f;      // track_update_body has read tau_raw (its first barrier is behind us)
         if (tid == 0) *tail.ticket = 0u;
       }
     }
@@ -441,7 +439,7 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
   if (upd != nullptr && (ticket == nullptr || sk_image != nullptr)) { set_error("blend_track: folded tail needs a ticket and the first-order epilogue"); return MGS_EINVAL; }
   TrackTail tail;
   memset(&tail, 0, sizeof(tail));
-  if (upd) { tail.k = *upd; tail.ticket = ticket; tail.tau_raw = tau_sum; }
+  if (upd) { tail.k = *upd; tail.ticket = ticket; }
 #define MGS_TRK_ARGS tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), \
       jac, v.bg, out_color, out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum, sk_weights, sk_scale, sk_image, tail
 #define MGS_TRK_DISPATCH(HD, SK, FO)                                                                                                   \

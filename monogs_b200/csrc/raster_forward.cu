@@ -583,6 +583,13 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
     MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(ws, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
   const uint32_t R_cap = fold ? (uint32_t)fold->R_cap : 0u;
   const int heavy = fold ? (fold->heavy_first ? 1 : 0) : 0;
+  // The scan runs as its own one-CTA launch by default: measured on the B200 the fused iteration is 6 us SHORTER that way
+  // than with the scan in the last CTA of this kernel (profiles/r02_notes.txt; the tail then runs at the occupancy and
+  // register budget of preprocess_kernel).  MGS_SCAN_FOLD=1 selects the folded tail.  Either way the workspace is the
+  // zero-maintained one of a fused loop: no memset.
+  static const bool scan_separate = [] { const char* e = getenv("MGS_SCAN_FOLD"); return !(e && e[0] == '1'); }();
+  const FoldScan* const fold_req = fold;
+  if (scan_separate) fold = nullptr;
 #define MGS_PRE_ARGS v, P, means3D, opacities, shs, sh_rest, colors_precomp, scales, rotations, cov3D_precomp, radii,  \
       ws_ptr<float>(ws, L.depths), ws_ptr<float2>(ws, L.means2D), ws_ptr<float4>(ws, L.conic_opacity),               \
       ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched), ws_ptr<uint32_t>(ws, L.tile_ctr), jac, R_cap, \
@@ -590,7 +597,7 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
   // SH rows of more than one coefficient are staged through shared memory (128 threads: 4 tiles of [32][3M | 1] floats)
   const bool stage = shs != nullptr && colors_precomp == nullptr && v.M > 1 && !(jac != nullptr && jac_ncol == 32);
   if (sh_rest != nullptr && !stage) { set_error("preprocess: split SH layout needs sh_coeffs > 1 and no colors_precomp"); return MGS_EINVAL; }
-  if (jac != nullptr && jac_ncol == 32 && fold == nullptr) { set_error("preprocess: the folded pose basis is built by the fused SH-degree-0 tracker only"); return MGS_EINVAL; }
+  if (jac != nullptr && jac_ncol == 32 && fold_req == nullptr) { set_error("preprocess: the folded pose basis is built by the fused SH-degree-0 tracker only"); return MGS_EINVAL; }
   prof_begin(fold ? "preprocess+scan" : "preprocess", s);
   if (stage) {
     const int T = 128;
@@ -609,11 +616,13 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
       else { set_error("preprocess: unsupported fused variant"); return MGS_EINVAL; }
     } else if (jac == nullptr) preprocess_kernel<0, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
     else if (jac_ncol == 9) preprocess_kernel<9, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+    else if (jac_ncol == 32) preprocess_kernel<32, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
     else preprocess_kernel<6, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
   }
   prof_end(s);
 #undef MGS_PRE_ARGS
   MGS_LAUNCH_CHECK();
+  if (fold_req != nullptr && fold == nullptr) return launch_tile_scan(v, ws, L, fold_req->R_cap, s, fold_req->heavy_first);
   return MGS_OK;
 }
 

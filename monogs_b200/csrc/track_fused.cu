@@ -183,7 +183,7 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
 
   // The workspace and the scratch of a tracker are zero-filled ONCE by their owner: tile counters, the scan ticket, the
   // tangent accumulator and the update ticket are all left zero by the iteration that used them (the sort kernel clears
-  // its tile's counter, the folded tails reset their tickets and tau_raw), so an iteration is 5 kernels and no memset.
+  // its tile's counter, the update kernel re-zeroes tau_raw), so an iteration is 7 kernels and no memset.
   const FoldScan fs{t->R_cap, /*heavy_first=*/!with_color};
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
                               ws, L, s, jac, with_color ? 9 : 32, nullptr, &fs)))
@@ -209,13 +209,24 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   k.beta1 = t->beta1; k.beta2 = t->beta2; k.eps = t->adam_eps;
   k.T = t->T_w2c; k.view_out = const_cast<float*>(view->viewmatrix); k.proj_out = const_cast<float*>(view->projmatrix);
   k.proj_raw = view->projmatrix_raw; k.converged = t->converged; k.thr = t->converged_threshold;
-  k.lm_state = t->lm_state;
+  k.lm_state = t->lm_state; k.tau_clear = nullptr;
   if (!with_color) {
     // SH degree 0: colours do not depend on the pose -> forward, loss and pose tangent in one pass over the tile lists,
     // and the iteration's serial tail (loss norm, Adam, pose update) in that kernel's last CTA
     uint32_t* ticket = reinterpret_cast<uint32_t*>(tau_raw + 8);
-    return launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
-                              tau_raw, s, nullptr, 0.f, nullptr, &k, ticket);
+    k.tau_clear = tau_raw;      // the update leaves the accumulator zero for the next iteration: no memset
+    // The serial tail (loss norm, Adam, pose update) runs as its own one-CTA launch by default: measured on the B200 the
+    // blend kernel is 24 us shorter without the per-CTA fence + ticket and the iteration 15 us shorter in total
+    // (profiles/r02_notes.txt).  MGS_UPDATE_FOLD=1 selects the variant that runs it in the blend kernel's last CTA.
+    static const bool update_fold = [] { const char* e = getenv("MGS_UPDATE_FOLD"); return e && e[0] == '1'; }();
+    if (update_fold)
+      return launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
+                                tau_raw, s, nullptr, 0.f, nullptr, &k, ticket);
+    if ((rc = launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
+                                 tau_raw, s, nullptr, 0.f, nullptr, nullptr, nullptr))) return rc;
+    MGS_PROF("track_update", s, track_update_kernel<<<1, 256, 0, s>>>(k));
+    MGS_LAUNCH_CHECK();
+    return MGS_OK;
   }
   if ((rc = launch_blend_forward(v, ws, L, t->out_color, t->out_depth, t->out_opacity, t->fast_math ? nullptr : t->n_touched, s, &fl))) return rc;
   BackwardArgs a;

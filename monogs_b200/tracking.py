@@ -15,9 +15,9 @@ import torch
 from . import _lib as L
 from .rasterizer import make_view, GaussianRasterizationSettings, _stream
 
-KERNELS_PER_ITER = 5    # own kernels per fused iteration (SH degree 0): preprocess (+ pose basis, tile counts and, in its last
-                        # CTA, the tile scan), emit, tile_sort_records x2 (short / long lists), blend_track (forward + loss +
-                        # pose tangent and, in its last CTA, loss norm + Adam + pose update)
+KERNELS_PER_ITER = 7    # own kernels per fused iteration (SH degree 0): preprocess (+ pose basis, tile counts), tile_scan, emit,
+                        # tile_sort_records x2 (short / long lists), blend_track (forward + loss + pose tangent),
+                        # track_update (loss norm + Adam + pose update)
 KERNELS_PER_ITER_COMPOSED = 14
 
 
