@@ -212,6 +212,20 @@ int mgs_loss_fwd_bwd(const mgs_loss_args* args, float* out_loss, float* out_dab,
                      float* dL_dimage, float* dL_ddepth, void* scratch, size_t scratch_bytes, void* stream);
 size_t mgs_loss_scratch_bytes(int32_t H, int32_t W);
 
+/* The same loss for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.  Inputs and
+ * outputs are the caller's as above; the per-block partial sums live in a file-scope device array inside the library
+ * (512 KB + 256 B, held by every GPU that loads the library until the process exits) whose device address the
+ * library fetches once per device with cudaGetSymbolAddress.  Nothing on the call path calls cudaMalloc, cudaFree or
+ * an allocating library routine.  Limit: H * W <= MGS_LOSS_STATIC_MAX_PIXELS, larger frames return MGS_ENOSPC with a
+ * message (use mgs_loss_fwd_bwd with caller-owned scratch for those).  All calls on a device SHARE the array, which
+ * keeps the previous call's contents: every slot a call reads it has written first, so calls ordered on one stream (or
+ * otherwise serialised) are independent, but two calls that overlap on the GPU (different streams, no dependency
+ * between them) race on it and return garbage.  Results are bit-identical to mgs_loss_fwd_bwd. */
+#define MGS_LOSS_STATIC_MAX_PIXELS (2048 * 2048)
+int mgs_loss_fwd_bwd_static(const mgs_loss_args* args, float* out_loss, float* out_dab,
+                            float* dL_dimage, float* dL_ddepth, void* stream);
+
 /* ---- fused Adam (torch.optim.Adam as configured at gaussian_splatting/scene/gaussian_model.py:285,
  *      utils/slam_frontend.py:453): multi-tensor, per-group lr, eps outside the bias-corrected sqrt. ---- */
 typedef struct mgs_adam_group {

@@ -169,6 +169,7 @@ SIGNATURES = {
     "mgs_mark_visible": (C.c_int, [_I32, _P, _P, _P, _P, _P]),
     "mgs_loss_fwd_bwd": (C.c_int, [C.POINTER(MgsLossArgs), _P, _P, _P, _P, _P, _SZ, _P]),
     "mgs_loss_scratch_bytes": (_SZ, [_I32, _I32]),
+    "mgs_loss_fwd_bwd_static": (C.c_int, [C.POINTER(MgsLossArgs), _P, _P, _P, _P, _P]),
     "mgs_adam_step": (C.c_int, [C.POINTER(MgsAdamGroup), _I32, _I32, _F, _F, _F, _P]),
     "mgs_adam_step_device": (C.c_int, [C.POINTER(MgsAdamGroup), _I32, _P, _F, _F, _F, _P]),
     "mgs_knn_workspace_bytes": (_SZ, [_I32]),

@@ -5,6 +5,7 @@
 // gaussian_splatting/scene/gaussian_model.py:285 and utils/slam_frontend.py:453.
 #include "launchers.h"
 #include <cstring>
+#include <mutex>
 #include "loss_pixel.cuh"
 #include "adam_elem.cuh"
 
@@ -172,6 +173,49 @@ int mgs_loss_fwd_bwd(const mgs_loss_args* args, float* out_loss, float* out_dab,
   }
   prof_end(s);
   return MGS_OK;
+}
+
+// ---- mgs_loss_fwd_bwd_static: the same loss with its scratch in the library's own device memory (no allocation
+//      anywhere on the call path; see include/monogs_b200.h).  The array below is a file-scope device symbol: in HOST
+//      code its name is only a stand-in, so its device address is fetched once per device with cudaGetSymbolAddress,
+//      with that device current, and that pointer is what the kernels receive.
+constexpr size_t kLossStaticBlocks = ((size_t)MGS_LOSS_STATIC_MAX_PIXELS + 255) / 256;
+constexpr size_t kLossStaticBytes = kLossStaticBlocks * 4 * sizeof(double) + 256;
+static __device__ __align__(256) unsigned char g_loss_static_scratch[kLossStaticBytes];
+constexpr int kLossStaticMaxDevices = 64;
+static void* g_loss_static_ptr[kLossStaticMaxDevices];     // per device, null until that device's first call
+static std::mutex g_loss_static_mutex;
+
+int mgs_loss_fwd_bwd_static(const mgs_loss_args* args, float* out_loss, float* out_dab, float* dL_dimage,
+                            float* dL_ddepth, void* stream) {
+  if (!args) { set_error("loss_static: null argument"); return MGS_EINVAL; }
+  if (args->H <= 0 || args->W <= 0) { set_error("loss_static: bad image size %d x %d", args->W, args->H); return MGS_EINVAL; }
+  if ((long long)args->H * (long long)args->W > (long long)MGS_LOSS_STATIC_MAX_PIXELS) {
+    set_error("loss_static: %d x %d = %lld pixels exceed the built-in scratch (MGS_LOSS_STATIC_MAX_PIXELS = %d); use "
+              "mgs_loss_fwd_bwd with caller-owned scratch", args->W, args->H, (long long)args->H * args->W,
+              (int)MGS_LOSS_STATIC_MAX_PIXELS);
+    return MGS_ENOSPC;
+  }
+  int dev = -1;
+  MGS_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kLossStaticMaxDevices) { set_error("loss_static: device ordinal %d not supported (max %d)", dev, kLossStaticMaxDevices - 1); return MGS_EINVAL; }
+  void* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_loss_static_mutex);
+    if (g_loss_static_ptr[dev] == nullptr) {     // set-up, once per device, with that device current
+      void* p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(&p, g_loss_static_scratch);
+      if (e != cudaSuccess || p == nullptr) {
+        set_error("loss_static: cudaGetSymbolAddress failed on device %d: %s", dev, cudaGetErrorString(e));
+        return MGS_ECUDA;
+      }
+      g_loss_static_ptr[dev] = p;
+    }
+    scratch = g_loss_static_ptr[dev];
+  }
+  // Every per-block partial slot the finalize kernels read is written earlier in the SAME call (the Huber path without
+  // gradients clears its own second-stage slots), so the contents the previous call left behind are never read.
+  return mgs_loss_fwd_bwd(args, out_loss, out_dab, dL_dimage, dL_ddepth, scratch, kLossStaticBytes, stream);
 }
 
 static int adam_impl(const mgs_adam_group* groups, int32_t n_groups, int32_t step, int32_t* step_dev, float beta1,
