@@ -201,7 +201,7 @@ int mgs_raster_forward_pose(const mgs_view* view, int32_t P, const float* means3
   // a fresh workspace: the folded scan wants a zero header (ticket) and zero tile counters
   MGS_CUDA_TRY(cudaMemsetAsync(workspace, 0, sizeof(WsHeader), s));
   MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(workspace, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
-  const FoldScan fs{R_cap, /*heavy_first=*/true};
+  const FoldScan fs{R_cap, /*heavy_first=*/true, /*in_kernel=*/false};
   if ((rc = launch_preprocess(v, P, means3D, opacities, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
                               workspace, L, s, basis, 32, nullptr, &fs)))
     return rc;

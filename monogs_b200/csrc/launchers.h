@@ -7,7 +7,10 @@ namespace mgs {
 const char* get_error();
 
 // fused loops: the tile scan runs in the last CTA of the preprocess kernel, no counter memset (see raster_forward.cu)
-struct FoldScan { int64_t R_cap; bool heavy_first; };
+// in_kernel: run the scan in the last CTA of preprocess_kernel (true) or as its own one-CTA launch behind it (false).
+// Measured on the B200: the separate launch wins in the serial tracking iteration (+2 %), the folded tail wins in the mapping
+// engine, whose views overlap on several streams (+3 %); MGS_SCAN_FOLD=0|1 overrides both for measurements.
+struct FoldScan { int64_t R_cap; bool heavy_first; bool in_kernel; };
 int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,

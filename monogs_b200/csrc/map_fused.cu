@@ -288,7 +288,7 @@ int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* st
   void* ws = mv->workspace;
   // the workspace of a mapping engine is zero-filled once by its owner: the scan runs in the last CTA of the preprocess
   // kernel and the sort kernel leaves the tile counters zero for the next view (raster_forward.cu, FoldScan)
-  const FoldScan fs{mv->R_cap, /*heavy_first=*/true};
+  const FoldScan fs{mv->R_cap, /*heavy_first=*/true, /*in_kernel=*/true};
   if ((rc = launch_preprocess(c.v, c.P, g.xyz, m.act_opacity, c.shs, nullptr, m.act_scales, m.act_rot, nullptr, mv->radii, ws, c.L, s,
                               nullptr, 0, c.M > 1 ? g.f_rest : nullptr, &fs))) return rc;
   MGS_CUDA_TRY(cudaMemsetAsync(mv->n_touched, 0, (size_t)c.P * sizeof(int32_t), s));

@@ -583,11 +583,10 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
     MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(ws, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
   const uint32_t R_cap = fold ? (uint32_t)fold->R_cap : 0u;
   const int heavy = fold ? (fold->heavy_first ? 1 : 0) : 0;
-  // The scan runs as its own one-CTA launch by default: measured on the B200 the fused iteration is 6 us SHORTER that way
-  // than with the scan in the last CTA of this kernel (profiles/r02_notes.txt; the tail then runs at the occupancy and
-  // register budget of preprocess_kernel).  MGS_SCAN_FOLD=1 selects the folded tail.  Either way the workspace is the
+  // fold->in_kernel picks the folded tail or a separate tile_scan launch (launchers.h); either way the workspace is the
   // zero-maintained one of a fused loop: no memset.
-  static const bool scan_separate = [] { const char* e = getenv("MGS_SCAN_FOLD"); return !(e && e[0] == '1'); }();
+  static const int scan_env = [] { const char* e = getenv("MGS_SCAN_FOLD"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
+  const bool scan_separate = fold != nullptr && (scan_env >= 0 ? scan_env == 0 : !fold->in_kernel);
   const FoldScan* const fold_req = fold;
   if (scan_separate) fold = nullptr;
 #define MGS_PRE_ARGS v, P, means3D, opacities, shs, sh_rest, colors_precomp, scales, rotations, cov3D_precomp, radii,  \

@@ -184,7 +184,7 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   // The workspace and the scratch of a tracker are zero-filled ONCE by their owner: tile counters, the scan ticket, the
   // tangent accumulator and the update ticket are all left zero by the iteration that used them (the sort kernel clears
   // its tile's counter, the update kernel re-zeroes tau_raw), so an iteration is 7 kernels and no memset.
-  const FoldScan fs{t->R_cap, /*heavy_first=*/!with_color};
+  const FoldScan fs{t->R_cap, /*heavy_first=*/!with_color, /*in_kernel=*/false};
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
                               ws, L, s, jac, with_color ? 9 : 32, nullptr, &fs)))
     return rc;
@@ -282,7 +282,7 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   k.conv_thr = a->converged_threshold; k.loss_out = t->loss;
   MGS_PROF("track2_begin", s, track2_begin_kernel<<<1, 32, 0, s>>>(k));
   MGS_LAUNCH_CHECK();
-  const FoldScan fs{t->R_cap, /*heavy_first=*/true};
+  const FoldScan fs{t->R_cap, /*heavy_first=*/true, /*in_kernel=*/false};
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
                               ws, L, s, jac, 32, nullptr, &fs)))
     return rc;

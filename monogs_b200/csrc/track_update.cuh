@@ -126,9 +126,8 @@ static __device__ __noinline__ void track_update_body(const TrackUpdateK& k) {
       s_out[8 + i] = m; s_out[16 + i] = v;
     } else if (tid < 24) s_out[32 + tid - 8] = s_in[32 + tid - 8];
     __syncwarp();
-    if (tid == 0)
-      pose_update_dev(s_out + 32, s_out + 24, s_out + 27, k.proj_raw ? s_in + 48 : nullptr, k.view_out ? s_out + 48 : nullptr,
-                      k.proj_out ? s_proj : nullptr, k.converged ? &s_conv : nullptr, k.thr);
+    pose_update_warp(s_out + 32, s_out + 24, s_out + 27, k.proj_raw ? s_in + 48 : nullptr, k.view_out ? s_out + 48 : nullptr,
+                     k.proj_out ? s_proj : nullptr, k.converged ? &s_conv : nullptr, k.thr, tid);
   } else if (tid < 64 && track_best) {
     // warp 1: best_viewpoint_params (lm_track_best) beside the update — the PRE-update pose and exposure
     double t3 = 0;
