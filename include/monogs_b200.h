@@ -136,6 +136,26 @@ int mgs_raster_backward(const mgs_view* view, int32_t P, uint32_t grad_mask,
                         float* dL_dtau_sum, float* dL_dtau_per_gaussian, void* stream);
 size_t mgs_raster_backward_scratch_bytes(int32_t P);
 
+/* ---- pixel-sample backward: replaces the select_pixels = true branch of _C.rasterize_gaussians_backward
+ *      (rasterize_points.cu:174-189,233; rasterizer_impl.cu:369,424; renderPixelSampleCUDA, backward.cu:592-797, launched
+ *      with one block per listed pixel at backward.cu:1142).  Same outputs as mgs_raster_backward, but only the pixels in
+ *      selected_pixel_indices (device i32[n_selected], linear index y * W + x) send gradient; a pixel listed k times
+ *      sends it k times (the reference launches k blocks for it), indices outside [0, W*H) are ignored (its `inside`
+ *      test).  n_selected = 0 yields zero gradients (the reference falls back to the dense kernel for an EMPTY list
+ *      because it encodes "not selected" as size 0; callers wanting that use mgs_raster_backward).
+ *      scratch: mgs_raster_backward_pixels_scratch_bytes(P, W, H). ---- */
+int mgs_raster_backward_pixels(const mgs_view* view, int32_t P, uint32_t grad_mask,
+                               const float* means3D, const float* shs, const float* colors_precomp,
+                               const float* scales, const float* rotations, const float* cov3D_precomp,
+                               const int32_t* radii, const void* workspace, size_t workspace_bytes,
+                               void* scratch, size_t scratch_bytes,
+                               const int32_t* selected_pixel_indices, int32_t n_selected,
+                               const float* dL_dout_color, const float* dL_dout_depth,
+                               float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors_or_sh,
+                               float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                               float* dL_dtau_sum, float* dL_dtau_per_gaussian, void* stream);
+size_t mgs_raster_backward_pixels_scratch_bytes(int32_t P, int32_t W, int32_t H);
+
 /* ---- pose-only backward (tracking) and sketch-Jacobian backward.  Replaces the tracking use of
  *      _C.rasterize_gaussians_backward (only grad_theta / grad_rho are consumed there because the frontend's
  *      Gaussians are detached, utils/slam_frontend.py:1799-1800) and

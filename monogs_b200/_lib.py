@@ -162,6 +162,9 @@ SIGNATURES = {
     "mgs_raster_backward": (C.c_int, [_VP, _I32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _P,
                                       _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "mgs_raster_backward_scratch_bytes": (_SZ, [_I32]),
+    "mgs_raster_backward_pixels": (C.c_int, [_VP, _I32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _I32, _P, _P,
+                                             _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "mgs_raster_backward_pixels_scratch_bytes": (_SZ, [_I32, _I32, _I32]),
     "mgs_raster_backward_pose": (C.c_int, [_VP, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _P, _SZ, _P, _P,
                                            _P, _P, _P]),
     "mgs_raster_backward_pose_scratch_bytes": (_SZ, [_I32, _I32, _I32]),

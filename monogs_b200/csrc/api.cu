@@ -234,13 +234,13 @@ int mgs_debug_layout(int32_t P, int32_t W, int32_t H, int64_t R_cap, size_t* out
 
 size_t mgs_raster_backward_scratch_bytes(int32_t P) { return backward_scratch_bytes(P, 0); }
 
-int mgs_raster_backward(const mgs_view* view, int32_t P, uint32_t grad_mask, const float* means3D, const float* shs,
+static int raster_backward_impl(const mgs_view* view, int32_t P, uint32_t grad_mask, const float* means3D, const float* shs,
                         const float* colors_precomp, const float* scales, const float* rotations,
                         const float* cov3D_precomp, const int32_t* radii, const void* workspace,
                         size_t workspace_bytes, void* scratch, size_t scratch_bytes, const float* dL_dout_color,
                         const float* dL_dout_depth, float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors_or_sh,
                         float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
-                        float* dL_dtau_sum, float* dL_dtau_per_gaussian, void* stream) {
+                        float* dL_dtau_sum, float* dL_dtau_per_gaussian, const int32_t* pixel_mult, void* stream) {
   int rc = check_view(view, true);
   if (rc) return rc;
   cudaStream_t s = (cudaStream_t)stream;
@@ -271,7 +271,58 @@ int mgs_raster_backward(const mgs_view* view, int32_t P, uint32_t grad_mask, con
   a.dL_dopacity = dL_dopacity; a.dL_dscales = dL_dscales; a.dL_drotations = dL_drotations; a.dL_dcov3D = dL_dcov3D;
   a.dL_dtau_sum = (grad_mask & MGS_GRAD_TAU) ? dL_dtau_sum : nullptr;
   a.dL_dtau_pg = (grad_mask & MGS_GRAD_TAU) ? dL_dtau_per_gaussian : nullptr;
+  a.pixel_mult = pixel_mult;
   return launch_backward_full(a, s);
+}
+
+int mgs_raster_backward(const mgs_view* view, int32_t P, uint32_t grad_mask, const float* means3D, const float* shs,
+                        const float* colors_precomp, const float* scales, const float* rotations,
+                        const float* cov3D_precomp, const int32_t* radii, const void* workspace,
+                        size_t workspace_bytes, void* scratch, size_t scratch_bytes, const float* dL_dout_color,
+                        const float* dL_dout_depth, float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors_or_sh,
+                        float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                        float* dL_dtau_sum, float* dL_dtau_per_gaussian, void* stream) {
+  return raster_backward_impl(view, P, grad_mask, means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
+                              workspace, workspace_bytes, scratch, scratch_bytes, dL_dout_color, dL_dout_depth, dL_dmeans3D,
+                              dL_dmeans2D, dL_dcolors_or_sh, dL_dopacity, dL_dscales, dL_drotations, dL_dcov3D, dL_dtau_sum,
+                              dL_dtau_per_gaussian, nullptr, stream);
+}
+
+// ---- pixel-sample backward (renderPixelSampleCUDA, backward.cu:592-797; reached through select_pixels = true of
+//      _C.rasterize_gaussians_backward, rasterize_points.cu:174-189).  The reference runs one 128-thread block per listed
+//      pixel in which thread 0 alone walks the pixel's list.  Here the list becomes a multiplicity plane (one scatter
+//      kernel) and the regular tile-parallel backward runs with it: same arithmetic per (pixel, Gaussian) pair.
+size_t mgs_raster_backward_pixels_scratch_bytes(int32_t P, int32_t W, int32_t H) {
+  if (P < 0 || W <= 0 || H <= 0) return 0;
+  return ((mgs_raster_backward_scratch_bytes(P) + 255) & ~(size_t)255) + (size_t)W * H * sizeof(int32_t);
+}
+
+int mgs_raster_backward_pixels(const mgs_view* view, int32_t P, uint32_t grad_mask, const float* means3D, const float* shs,
+                               const float* colors_precomp, const float* scales, const float* rotations,
+                               const float* cov3D_precomp, const int32_t* radii, const void* workspace,
+                               size_t workspace_bytes, void* scratch, size_t scratch_bytes,
+                               const int32_t* selected_pixel_indices, int32_t n_selected, const float* dL_dout_color,
+                               const float* dL_dout_depth, float* dL_dmeans3D, float* dL_dmeans2D,
+                               float* dL_dcolors_or_sh, float* dL_dopacity, float* dL_dscales, float* dL_drotations,
+                               float* dL_dcov3D, float* dL_dtau_sum, float* dL_dtau_per_gaussian, void* stream) {
+  int rc = check_view(view, true);
+  if (rc) return rc;
+  if (n_selected < 0 || (n_selected > 0 && !selected_pixel_indices)) { set_error("backward_pixels: bad pixel list"); return MGS_EINVAL; }
+  if (P > 0 && !scratch) { set_error("backward_pixels: null scratch"); return MGS_EINVAL; }
+  const int W = view->image_width, H = view->image_height;
+  if (P > 0 && scratch_bytes < mgs_raster_backward_pixels_scratch_bytes(P, W, H)) { set_error("backward_pixels: scratch too small"); return MGS_ENOSPC; }
+  cudaStream_t s = (cudaStream_t)stream;
+  int32_t* mult = nullptr;
+  size_t inner = 0;
+  if (P > 0) {
+    inner = (mgs_raster_backward_scratch_bytes(P) + 255) & ~(size_t)255;
+    mult = reinterpret_cast<int32_t*>(static_cast<unsigned char*>(scratch) + inner);
+    if ((rc = launch_pixel_multiplicity(selected_pixel_indices, n_selected, W * H, mult, s))) return rc;
+  }
+  return raster_backward_impl(view, P, grad_mask, means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
+                              workspace, workspace_bytes, scratch, inner, dL_dout_color, dL_dout_depth, dL_dmeans3D,
+                              dL_dmeans2D, dL_dcolors_or_sh, dL_dopacity, dL_dscales, dL_drotations, dL_dcov3D, dL_dtau_sum,
+                              dL_dtau_per_gaussian, mult, stream);
 }
 
 

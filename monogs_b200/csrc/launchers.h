@@ -55,10 +55,13 @@ struct BackwardArgs {
   const float* sh_rest = nullptr; float* dL_dsh_rest = nullptr;
   bool fast = false;   // blend_backward_full only: exponent variant of the forward that produced ws (blend_exp<FAST>)
   bool heavy_first = false;   // blend_backward_full only: walk the tiles in the scan's heavy-first order (tile_ctr[.. + 3])
+  const int32_t* pixel_mult = nullptr;   // blend_backward_full only: i32[H*W] multiplicity of each pixel in the selected-pixel
+                                         // list of mgs_raster_backward_pixels (null: every pixel once)
   // sketch mode (sketch_dim > 0): per-pixel row routing, output sketch_dtau[d,6]
   int sketch_dim; const int32_t* sketch_indices; float* sketch_dtau;
 };
 int launch_backward(const BackwardArgs& a, cudaStream_t s);
+int launch_pixel_multiplicity(const int32_t* indices, int n, int npix, int32_t* mult, cudaStream_t s);   // mult[p] = #occurrences of p
 int launch_backward_full(const BackwardArgs& a, cudaStream_t s);
 int launch_blend_backward_pose(const BackwardArgs& a, const float* jac, bool with_color, cudaStream_t s, bool fast = false);
 size_t backward_scratch_bytes(int P, int sketch_dim);

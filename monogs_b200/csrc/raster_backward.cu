@@ -80,7 +80,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx, const uint32_
                            const float* __restrict__ bg, const float* __restrict__ final_T,
                            const uint32_t* __restrict__ n_contrib,
                            const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth,
-                           G2DGrad* __restrict__ g2d) {
+                           const int32_t* __restrict__ pixel_mult, G2DGrad* __restrict__ g2d) {
   __shared__ __align__(128) SplatRec stage[2][BWD_BATCH];
   __shared__ __align__(16) float acc[BWD_BATCH * 12];
   __shared__ __align__(8) uint64_t full_bar[2];
@@ -98,10 +98,22 @@ blend_backward_full_kernel(const int W, const int H, const int gx, const uint32_
   const uint2 range = ranges[tile];
 
   const float2 T_final = make_float2(in0 ? final_T[pix0] : 0.f, in1 ? final_T[pix1] : 0.f);
-  const int last0 = in0 ? (int)n_contrib[pix0] : 0, last1 = in1 ? (int)n_contrib[pix1] : 0;
+  int last0 = in0 ? (int)n_contrib[pix0] : 0, last1 = in1 ? (int)n_contrib[pix1] : 0;
   float2 dp0 = make_float2(0.f, 0.f), dp1 = dp0, dp2 = dp0, dpd = dp0;
   if (in0) { dp0.x = dL_dpix[pix0]; dp1.x = dL_dpix[plane + pix0]; dp2.x = dL_dpix[2 * plane + pix0]; dpd.x = dL_dpix_depth[pix0]; }
   if (in1) { dp0.y = dL_dpix[pix1]; dp1.y = dL_dpix[plane + pix1]; dp2.y = dL_dpix[2 * plane + pix1]; dpd.y = dL_dpix_depth[pix1]; }
+  if (pixel_mult != nullptr) {
+    // pixel-sample backward (the reference's renderPixelSampleCUDA, backward.cu:592-797): only the listed pixels send
+    // gradient, a pixel listed k times sends it k times.  A pixel that is not listed gets "no contributor" — every splat
+    // is then skipped for it by the test below, the tile's walk starts at the deepest contributor of its LISTED pixels,
+    // and a tile without any returns at once.
+    const int m0 = in0 ? pixel_mult[pix0] : 0, m1 = in1 ? pixel_mult[pix1] : 0;
+    last0 = m0 > 0 ? last0 : 0; last1 = m1 > 0 ? last1 : 0;
+    const float2 mf = make_float2((float)m0, (float)m1);
+    dp0 = __fmul2_rn(dp0, mf); dp1 = __fmul2_rn(dp1, mf); dp2 = __fmul2_rn(dp2, mf); dpd = __fmul2_rn(dpd, mf);
+  }
+  // a warp none of whose 64 pixels has a contributor (empty patch, or no listed pixel) has nothing to walk
+  const bool warp_live = __ballot_sync(0xffffffffu, last0 > 0 || last1 > 0) != 0u;
   if (tid == 0) {
     s_max_contrib = 0;
     mbar_init(&full_bar[0], 1); mbar_init(&full_bar[1], 1);
@@ -150,7 +162,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx, const uint32_
     const int cnt = hi - lo;
     const float4* rec4 = reinterpret_cast<const float4*>(&stage[i & 1][0]);
     const float* recf = reinterpret_cast<const float*>(&stage[i & 1][0]);
-    for (int c0 = ((cnt - 1) >> 5) << 5; c0 >= 0; c0 -= 32) {
+    for (int c0 = warp_live ? ((cnt - 1) >> 5) << 5 : -1; c0 >= 0; c0 -= 32) {
      // lane-parallel exact cull of 32 splats against this warp's 8x8 patch (see splat_extent)
      const int jj = c0 + lane;
      unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + 12 * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 7.f));
@@ -398,6 +410,24 @@ size_t backward_scratch_bytes(int P, int sketch_dim) {
   return ((size_t)(P > 0 ? P : 1) * sizeof(G2DGrad) + 255) / 256 * 256 + 256;
 }
 
+// selected-pixel list -> multiplicity plane (indices outside [0, npix) are ignored: the reference's `inside` test)
+__global__ void __launch_bounds__(256) pixel_multiplicity_kernel(const int32_t* __restrict__ idx, const int n, const int npix,
+                                                                 int32_t* __restrict__ mult) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int p = idx[i];
+  if (p >= 0 && p < npix) atomicAdd(&mult[p], 1);
+}
+
+int launch_pixel_multiplicity(const int32_t* indices, int n, int npix, int32_t* mult, cudaStream_t s) {
+  MGS_CUDA_TRY(cudaMemsetAsync(mult, 0, (size_t)npix * sizeof(int32_t), s));
+  if (n > 0) {
+    MGS_PROF("pixel_multiplicity", s, pixel_multiplicity_kernel<<<(n + 255) / 256, 256, 0, s>>>(indices, n, npix, mult));
+    MGS_LAUNCH_CHECK();
+  }
+  return MGS_OK;
+}
+
 int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   const ViewConst& v = a.v;
   const int P = a.P;
@@ -410,7 +440,8 @@ int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   prof_begin("blend_backward_full", s);
   const uint32_t* order = a.heavy_first ? ws_ptr<uint32_t>(a.ws, a.L.tile_ctr) : nullptr;
 #define MGS_BWD_ARGS v.W, v.H, v.gx, order, ws_ptr<uint2>(a.ws, a.L.ranges), ws_ptr<SplatRec>(a.ws, a.L.records), v.bg,   \
-      ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img, a.dL_ddepth_img, g2d
+      ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img, a.dL_ddepth_img,        \
+      a.pixel_mult, g2d
   if (a.fast) blend_backward_full_kernel<true><<<tiles, BWD_THREADS, 0, s>>>(MGS_BWD_ARGS);
   else blend_backward_full_kernel<false><<<tiles, BWD_THREADS, 0, s>>>(MGS_BWD_ARGS);
 #undef MGS_BWD_ARGS

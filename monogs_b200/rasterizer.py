@@ -254,8 +254,11 @@ def raster_forward(rs, means3D, opacities, shs, colors_precomp, scales, rotation
 
 
 def raster_backward(rs, st, grad_mask, means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, radii,
-                    grad_color, grad_depth, want_tau_per_gaussian=False):
-    """One call of mgs_raster_backward; returns a dict of the requested gradients."""
+                    grad_color, grad_depth, want_tau_per_gaussian=False, selected_pixel_indices=None):
+    """One call of mgs_raster_backward; returns a dict of the requested gradients.
+    selected_pixel_indices (int32 [n], linear pixel indices): the select_pixels = True branch of the reference's
+    _C.rasterize_gaussians_backward (rasterize_points.cu:174-189) — only those pixels send gradient
+    (mgs_raster_backward_pixels).  None = the dense backward."""
     lib = L.lib()
     dev, P = means3D.device, st.P
     means3D, shs, colors_precomp = _f32c(means3D), _f32c(shs), _f32c(colors_precomp)
@@ -283,7 +286,13 @@ def raster_backward(rs, st, grad_mask, means3D, shs, colors_precomp, scales, rot
     if P == 0:
         for t in out.values(): t.zero_()
         return out
-    scratch = torch.empty(lib.mgs_raster_backward_scratch_bytes(P), device=dev, dtype=torch.uint8)
+    sel = None
+    if selected_pixel_indices is not None:
+        sel = selected_pixel_indices.to(device=dev, dtype=torch.int32).contiguous()
+        H, W = int(rs.image_height), int(rs.image_width)
+        scratch = torch.empty(lib.mgs_raster_backward_pixels_scratch_bytes(P, W, H), device=dev, dtype=torch.uint8)
+    else:
+        scratch = torch.empty(lib.mgs_raster_backward_scratch_bytes(P), device=dev, dtype=torch.uint8)
     g = lambda k: L.ptr(out[k]) if k in out else None
     with _on(dev):
         s = _stream(dev)
@@ -291,6 +300,14 @@ def raster_backward(rs, st, grad_mask, means3D, shs, colors_precomp, scales, rot
                         rs.viewmatrix, rs.projmatrix, rs.projmatrix_raw, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, shs,
                         rs.sh_degree, rs.campos, st.workspace, st.num_rendered, rs.debug)
         with _debug_guard(rs, s, "backward", snap, "snapshot_bw.dump"):
+            if sel is not None:
+                L.check(lib.mgs_raster_backward_pixels(
+                    C.byref(view), P, grad_mask, L.ptr(means3D), L.ptr(shs), L.ptr(colors_precomp), L.ptr(scales),
+                    L.ptr(rotations), L.ptr(cov3D_precomp), L.ptr(radii), L.ptr(st.workspace), st.workspace.numel(),
+                    L.ptr(scratch), scratch.numel(), C.c_void_p(sel.data_ptr()) if sel.numel() else None, sel.numel(),
+                    L.ptr(grad_color), L.ptr(grad_depth), g("means3D"), g("means2D"), g("color"), g("opacity"), g("scales"),
+                    g("rotations"), g("cov3D"), g("tau"), g("tau_pg"), s), "mgs_raster_backward_pixels")
+                return out
             L.check(lib.mgs_raster_backward(C.byref(view), P, grad_mask, L.ptr(means3D), L.ptr(shs), L.ptr(colors_precomp),
                                             L.ptr(scales), L.ptr(rotations), L.ptr(cov3D_precomp), L.ptr(radii),
                                             L.ptr(st.workspace), st.workspace.numel(), L.ptr(scratch), scratch.numel(),

@@ -49,12 +49,25 @@ def forward(cam, bg, means3D, opacities, shs=None, colors_precomp=None, scales=N
 
 
 def backward(cam, bg, fw, means3D, grad_color, grad_depth, shs=None, colors_precomp=None, scales=None, rotations=None,
-             cov3D_precomp=None, sh_degree=0, scale_modifier=1.0, slot=0):
+             cov3D_precomp=None, sh_degree=0, scale_modifier=1.0, slot=0, selected_pixel_indices=None):
+    """selected_pixel_indices (int32 [n] on the device, n > 0): the reference's select_pixels branch
+    (renderPixelSampleCUDA) instead of the dense renderCUDA."""
     dev = means3D.device
     P, M, W, H = fw["P"], fw["M"], cam.W, cam.H
     z = lambda *s: torch.zeros(*s, device=dev)
     g = dict(means2D=z(P, 3), conic=z(P, 2, 2), opacity=z(P, 1), color=z(P, 3), depth=z(P, 1), means3D=z(P, 3),
              cov3D=z(P, 6), sh=z(P, max(M, 1), 3), scales=z(P, 3), rotations=z(P, 4), tau=z(P, 6))
+    if selected_pixel_indices is not None:
+        sel = selected_pixel_indices.to(device=dev, dtype=torch.int32).contiguous()
+        lib().ref_backward_pixels(slot, sel.numel(), _p(sel), P, sh_degree, M, fw["R"], _p(bg), W, H, _p(means3D), _p(shs),
+                                  _p(colors_precomp), _p(scales), C.c_float(scale_modifier), _p(rotations),
+                                  _p(cov3D_precomp), _p(cam.viewmatrix), _p(cam.projmatrix), _p(cam.projmatrix_raw),
+                                  _p(cam.campos), C.c_float(cam.tanfovx), C.c_float(cam.tanfovy), _p(fw["radii"]),
+                                  _p(grad_color), _p(grad_depth), _p(g["means2D"]), _p(g["conic"]), _p(g["opacity"]),
+                                  _p(g["color"]), _p(g["depth"]), _p(g["means3D"]), _p(g["cov3D"]), _p(g["sh"]),
+                                  _p(g["scales"]), _p(g["rotations"]), _p(g["tau"]))
+        torch.cuda.synchronize()
+        return g
     lib().ref_backward(slot, P, sh_degree, M, fw["R"], _p(bg), W, H, _p(means3D), _p(shs), _p(colors_precomp), _p(scales),
                        C.c_float(scale_modifier), _p(rotations), _p(cov3D_precomp), _p(cam.viewmatrix),
                        _p(cam.projmatrix), _p(cam.projmatrix_raw), _p(cam.campos), C.c_float(cam.tanfovx),

@@ -61,6 +61,24 @@ void ref_backward(int slot, int P, int D, int M, int R, const float* bg, int W, 
                                        dL_drot, dL_dtau, false);
 }
 
+// The select_pixels = true branch of the reference wrapper (rasterize_points.cu:189,233): same call with the pixel list,
+// which makes BACKWARD::render launch renderPixelSampleCUDA (backward.cu:1139-1165) instead of renderCUDA.
+void ref_backward_pixels(int slot, int n_selected, int* selected_pixel_indices, int P, int D, int M, int R, const float* bg,
+                         int W, int H, const float* means3D, const float* shs, const float* colors_precomp,
+                         const float* scales, float scale_modifier, const float* rotations, const float* cov3D_precomp,
+                         const float* viewmatrix, const float* projmatrix, const float* projmatrix_raw,
+                         const float* campos, float tan_fovx, float tan_fovy, const int* radii, const float* dL_dpix,
+                         const float* dL_dpix_depth, float* dL_dmean2D, float* dL_dconic, float* dL_dopacity,
+                         float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                         float* dL_dscale, float* dL_drot, float* dL_dtau) {
+  CudaRasterizer::Rasterizer::backward(P, D, M, R, bg, W, H, means3D, shs, colors_precomp, scales, scale_modifier,
+                                       rotations, cov3D_precomp, viewmatrix, projmatrix, projmatrix_raw, campos,
+                                       tan_fovx, tan_fovy, radii, g_geom[slot].ptr, g_bin[slot].ptr, g_img[slot].ptr,
+                                       n_selected, selected_pixel_indices, 0, nullptr, nullptr, dL_dpix, dL_dpix_depth,
+                                       dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth, dL_dmean3D, dL_dcov3D,
+                                       dL_dsh, dL_dscale, dL_drot, dL_dtau, false);
+}
+
 // Sketch-Jacobian backward; all df_* buffers are [P, sketch_dim, ...] and zero-filled by the caller.
 void ref_backward_sketch(int slot, int sketch_mode, int sketch_dim, const int* sketch_indices, int P, int D, int M,
                          int R, const float* bg, int W, int H, const float* means3D, const float* shs,
