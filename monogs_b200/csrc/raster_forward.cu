@@ -130,6 +130,8 @@ __device__ __forceinline__ Cov2DOut cov2d_project(const float3& mean, const View
 __device__ __forceinline__ float3 sh_to_rgb(int deg, const float3& pos, const float* __restrict__ campos,
                                             const float* __restrict__ sh /* this Gaussian's row [M,3] */, uint32_t& clamp_mask) {
   float w[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) w[k] = 0.f;
   w[0] = kSH0;
   if (deg > 0) {
     float dx = pos.x - campos[0], dy = pos.y - campos[1], dz = pos.z - campos[2];
@@ -155,9 +157,14 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float3& pos, const fl
   float c[3];
 #pragma unroll
   for (int ch = 0; ch < 3; ch++) c[ch] = w[0] * sh[ch];
-  for (int k = 1; k < n; k++) {
+  // fully unrolled with a predicate, so that w[] is indexed by constants and stays in registers (a loop to n indexes it
+  // dynamically: local memory); same multiply-adds in the same order
 #pragma unroll
-    for (int ch = 0; ch < 3; ch++) c[ch] = fmaf(w[k], sh[3 * k + ch], c[ch]);
+  for (int k = 1; k < 16; k++) {
+    if (k < n) {
+#pragma unroll
+      for (int ch = 0; ch < 3; ch++) c[ch] = fmaf(w[k], sh[3 * k + ch], c[ch]);
+    }
   }
   clamp_mask = 0;
 #pragma unroll
@@ -351,10 +358,13 @@ preprocess_kernel(const ViewConst v, const int P,
       if (v.prefiltered) { printf("Point is filtered although prefiltered is set. This shouldn't happen!"); __trap(); }
       break;
     }
-    float cov6_local[6];
-    const float* cov6;
-    if (cov3D_precomp != nullptr) cov6 = cov3D_precomp + 6 * (size_t)idx;
-    else { cov3d_from_scale_rot(scales, rotations, idx, v.scale_modifier, cov6_local); cov6 = cov6_local; }
+    // the six covariance entries live in registers either way (a pointer that selects between the global array and a
+    // local one forces the local one into local memory: 6250 local stores per launch in the round-1 profile)
+    float cov6[6];
+    if (cov3D_precomp != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 6; k++) cov6[k] = cov3D_precomp[6 * (size_t)idx + k];
+    } else cov3d_from_scale_rot(scales, rotations, idx, v.scale_modifier, cov6);
     const Cov2DOut cv = cov2d_project(p, v, cov6);
     const float det = (cv.a * cv.c - cv.b * cv.b);
     if (det == 0.0f) break;
