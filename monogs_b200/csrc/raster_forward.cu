@@ -220,6 +220,58 @@ __device__ __forceinline__ void for_each_tile(const uint2 rmin, const uint2 rmax
   }
 }
 
+#ifndef MGS_EMIT_COOP
+#define MGS_EMIT_COOP 4          // emit_kernel: chunks per step of the warp-cooperative rect walk (0: per-lane walk)
+#endif
+// The same visit, distributed over the warp: the rects of the warp's 32 splats are laid end to end (prefix sum of their
+// areas) and lane l takes instance base + l of every 32-instance chunk — whoever owns it (binary search over the prefix,
+// five shuffles).  Every lane is busy whatever the mix of rect sizes (the per-lane walk above ran emit_kernel at 11 of 32
+// lanes, and its time was the dependent atomic chain of the lane with the largest rect), and U chunks are handed to the
+// callback together so that it can keep U atomics per lane in flight.  fn(tile[U], ok[U], payload[U]).
+// Must be reached by all 32 lanes.
+template <int U, typename F>
+__device__ __forceinline__ void for_each_tile_coop(const uint2 rmin, const uint2 rmax, const int gx,
+                                                   const unsigned long long payload, F&& fn) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t w = rmax.x - rmin.x, area = w * (rmax.y - rmin.y);
+  uint32_t incl = area;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += up;
+  }
+  const uint32_t excl = incl - area, total = __shfl_sync(0xffffffffu, incl, 31);
+  const float inv_w = w > 0u ? 1.0f / (float)w : 0.f;
+  const uint32_t pl_lo = (uint32_t)payload, pl_hi = (uint32_t)(payload >> 32);
+  for (uint32_t base = 0; base < total; base += 32u * U) {
+    uint32_t tile[U];
+    bool ok[U];
+    unsigned long long pl[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const uint32_t q = base + 32u * u + lane;
+      // owner = the last lane whose first instance is <= q (lanes without a rect share their successor's start and lose)
+      int lo = 0;
+#pragma unroll
+      for (int step = 16; step > 0; step >>= 1) {
+        const uint32_t e = __shfl_sync(0xffffffffu, excl, (lo + step) & 31);
+        if (e <= q) lo += step;       // lo + step <= 31 by construction
+      }
+      const uint32_t x0 = __shfl_sync(0xffffffffu, rmin.x, lo), y0 = __shfl_sync(0xffffffffu, rmin.y, lo);
+      const uint32_t ww = __shfl_sync(0xffffffffu, w, lo), e0 = __shfl_sync(0xffffffffu, excl, lo);
+      const float iw = __shfl_sync(0xffffffffu, inv_w, lo);
+      const uint32_t plo = __shfl_sync(0xffffffffu, pl_lo, lo), phi = __shfl_sync(0xffffffffu, pl_hi, lo);
+      const uint32_t k = q - e0;
+      // k / ww for k < 2^20: (k + 0.5) / ww is never within 0.5 / ww of an integer, far outside the float error
+      const uint32_t ty = (uint32_t)__float2int_rz(((float)k + 0.5f) * iw);
+      ok[u] = q < total;
+      tile[u] = (y0 + ty) * gx + x0 + (k - ty * ww);
+      pl[u] = ((unsigned long long)phi << 32) | plo;
+    }
+    fn(tile, ok, pl);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Binning.  The reference sorts R 64-bit (tile | depth) keys globally (rasterizer_impl.cu:70-111, 306-311).  Tile ids
 // are a small dense range, so the tile half is a COUNTING sort: per-tile counts (preprocess_kernel) -> exclusive scan
@@ -460,6 +512,18 @@ emit_kernel(const int P, const uint32_t R_cap, const int gx, const int gy,
       word = ((unsigned long long)__float_as_uint(depths[idx]) << 32) | (uint32_t)idx;
     }
   }
+#if MGS_EMIT_COOP
+  for_each_tile_coop<MGS_EMIT_COOP>(rmin, rmax, gx, word, [&](const uint32_t (&tile)[MGS_EMIT_COOP], const bool (&ok)[MGS_EMIT_COOP],
+                                                              const unsigned long long (&w)[MGS_EMIT_COOP]) {
+    uint32_t slot[MGS_EMIT_COOP];
+#pragma unroll
+    for (int u = 0; u < MGS_EMIT_COOP; u++)
+      if (ok[u]) slot[u] = atomicAdd(&tile_ctr[tile[u] * TILE_CTR_STRIDE + 1], 1u);
+#pragma unroll
+    for (int u = 0; u < MGS_EMIT_COOP; u++)
+      if (ok[u] && slot[u] < R_cap) list[slot[u]] = w[u];
+  });
+#else
   for_each_tile(rmin, rmax, gx, word, [&](const uint32_t (&tile)[4], int cnt, unsigned long long w) {
     uint32_t slot[4];
 #pragma unroll
@@ -469,6 +533,7 @@ emit_kernel(const int P, const uint32_t R_cap, const int gx, const int gy,
     for (int u = 0; u < 4; u++)
       if (u < cnt && slot[u] < R_cap) list[slot[u]] = w;
   });
+#endif
 }
 
 // Per-tile sort of the 64-bit words + record packing.  Lists of up to SORT_CAP words are merge-sorted from registers
@@ -494,12 +559,15 @@ __device__ __forceinline__ void write_record(const unsigned long long w, SplatRe
   out[2] = make_float4(c.x, c.y, c.z, __uint_as_float(splat_extent(co.x, co.y, co.z, co.w)));
 }
 
-template <int IPT, typename Temp>
+#ifndef MGS_SORT_THREADS
+#define MGS_SORT_THREADS 256     // CTA size of the short-list sort kernel; measured at C2: 256 -> 33 us, 128 -> 44 us, 64 -> 48 us
+#endif
+template <int IPT, int THREADS, typename Temp>
 __device__ __noinline__ void sort_tile_regs(Temp& temp, const unsigned long long* __restrict__ seg, const int n,
                                             SplatRec* __restrict__ dst, const float2* __restrict__ means2D,
                                             const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
                                             const float* __restrict__ colors_precomp) {
-  using Sort = cub::BlockMergeSort<unsigned long long, 256, IPT>;
+  using Sort = cub::BlockMergeSort<unsigned long long, THREADS, IPT>;
   unsigned long long k[IPT];
 #pragma unroll
   for (int i = 0; i < IPT; i++) {
@@ -519,13 +587,14 @@ __device__ __noinline__ void sort_tile_regs(Temp& temp, const unsigned long long
 // kernel compacted (tile_ctr[i * TILE_CTR_STRIDE + 2], i < header.n_large); with no large tile it costs an empty wave
 // of a few hundred CTAs instead of one CTA per tile.
 template <bool LARGE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(LARGE ? 256 : MGS_SORT_THREADS)
 tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* __restrict__ list,
                          const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                          const float4* __restrict__ rgb4, const float* __restrict__ colors_precomp,
                          SplatRec* __restrict__ recs, uint32_t* __restrict__ tile_ctr,
                          const WsHeader* __restrict__ hdr, const int clear_counts) {
-  using Temp = typename cub::BlockMergeSort<unsigned long long, 256, LARGE ? 16 : 4>::TempStorage;
+  constexpr int ST = LARGE ? 256 : MGS_SORT_THREADS, SI = 1024 / MGS_SORT_THREADS;   // SI words per thread cover LARGE_LIST
+  using Temp = typename cub::BlockMergeSort<unsigned long long, ST, LARGE ? 16 : SI>::TempStorage;
   __shared__ Temp temp;
   if (!LARGE) {
     // fused loops (tracker, mapping engine) render into the same workspace again and again: the tile's instance counter
@@ -536,8 +605,8 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
     if (n == 0 || n > LARGE_LIST) return;
     unsigned long long* seg = list + range.x;
     SplatRec* dst = recs + range.x;
-    if (n <= 512) sort_tile_regs<2>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
-    else sort_tile_regs<4>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+    if (n <= 512) sort_tile_regs<SI / 2, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+    else sort_tile_regs<SI, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
     return;
   }
   const uint32_t n_large = hdr->n_large;
@@ -547,8 +616,8 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
     unsigned long long* seg = list + range.x;
     SplatRec* dst = recs + range.x;
     if (n <= SORT_CAP) {
-      if (n <= 2048) sort_tile_regs<8>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
-      else sort_tile_regs<16>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+      if (n <= 2048) sort_tile_regs<8, 256>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+      else sort_tile_regs<16, 256>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
       __syncthreads();          // temp is reused by the next tile
       continue;
     }
@@ -650,7 +719,7 @@ int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const
 #define MGS_SORT_ARGS ws_ptr<uint2>(ws, L.ranges), ws_ptr<unsigned long long>(ws, L.list), ws_ptr<float2>(ws, L.means2D), \
       ws_ptr<float4>(ws, L.conic_opacity), ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<SplatRec>(ws, L.records),     \
       ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<WsHeader>(ws, L.header), clear_counts ? 1 : 0
-  MGS_PROF("tile_sort_records", s, tile_sort_records_kernel<false><<<tiles, 256, 0, s>>>(MGS_SORT_ARGS));
+  MGS_PROF("tile_sort_records", s, tile_sort_records_kernel<false><<<tiles, MGS_SORT_THREADS, 0, s>>>(MGS_SORT_ARGS));
   MGS_LAUNCH_CHECK();
   MGS_PROF("tile_sort_records_large", s,
            tile_sort_records_kernel<true><<<tiles < 592 ? tiles : 592, 256, 0, s>>>(MGS_SORT_ARGS));
