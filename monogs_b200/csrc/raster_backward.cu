@@ -74,7 +74,10 @@ __device__ __forceinline__ int reduce10_slot(const int lane) {
 // fold with last_alpha = 0.  So the per-pixel updates run unconditionally for both halves, and the "last colour" is
 // the colour of the previous record the warp processed: warp-uniform, not per-pixel state.
 template <bool FAST>   // FAST: the ex2.approx exponent of a FAST forward (T is recovered with the same alpha)
-__global__ void __launch_bounds__(BWD_THREADS)
+#ifndef MGS_BWD_MIN_CTAS
+#define MGS_BWD_MIN_CTAS 9     // 56 registers, no spills: 9 CTAs per SM instead of 8 (+1 % on the mapping iteration; 10 spills, 12 is 10 % slower)
+#endif
+__global__ void __launch_bounds__(BWD_THREADS, MGS_BWD_MIN_CTAS)
 blend_backward_full_kernel(const int W, const int H, const int gx, const uint32_t* __restrict__ tile_order,
                            const uint2* __restrict__ ranges, const SplatRec* __restrict__ recs,
                            const float* __restrict__ bg, const float* __restrict__ final_T,

@@ -126,12 +126,48 @@ __device__ __forceinline__ Cov2DOut cov2d_project(const float3& mean, const View
   return o;
 }
 
+#ifndef MGS_SH_INLINE
+#define MGS_SH_INLINE 1      // 0: the weight-array form (64 B of stack per thread)
+#endif
+#ifndef MGS_COV6_REGS
+#define MGS_COV6_REGS 1
+#endif
 // SH -> RGB (forward.cu:22-73).  Returns the clamped colour and a 3-bit mask of channels clamped at 0.
 __device__ __forceinline__ float3 sh_to_rgb(int deg, const float3& pos, const float* __restrict__ campos,
                                             const float* __restrict__ sh /* this Gaussian's row [M,3] */, uint32_t& clamp_mask) {
-  float w[16];
+#if MGS_SH_INLINE
+  // Each basis weight is folded into the colour as soon as it is known — c += w_k * sh[k], k = 0, 1, 2, ... in that order,
+  // the same multiply-adds as a loop over a weight array — so that no array of 16 weights exists (indexed dynamically it
+  // lived in local memory, fully unrolled it cost 12 registers and a resident CTA per SM).
+  float c[3];
 #pragma unroll
-  for (int k = 0; k < 16; k++) w[k] = 0.f;
+  for (int ch = 0; ch < 3; ch++) c[ch] = kSH0 * sh[ch];
+  auto acc = [&](const int k, const float wk) {
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) c[ch] = fmaf(wk, sh[3 * k + ch], c[ch]);
+  };
+  if (deg > 0) {
+    float dx = pos.x - campos[0], dy = pos.y - campos[1], dz = pos.z - campos[2];
+    const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+    const float x = dx / len, y = dy / len, z = dz / len;
+    acc(1, -(kSH1 * y)); acc(2, kSH1 * z); acc(3, -(kSH1 * x));
+    if (deg > 1) {
+      const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+      acc(4, kSH2[0] * xy); acc(5, kSH2[1] * yz); acc(6, kSH2[2] * (2.0f * zz - xx - yy));
+      acc(7, kSH2[3] * xz); acc(8, kSH2[4] * (xx - yy));
+      if (deg > 2) {
+        acc(9, kSH3[0] * y * (3.0f * xx - yy));
+        acc(10, kSH3[1] * xy * z);
+        acc(11, kSH3[2] * y * (4.0f * zz - xx - yy));
+        acc(12, kSH3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy));
+        acc(13, kSH3[4] * x * (4.0f * zz - xx - yy));
+        acc(14, kSH3[5] * z * (xx - yy));
+        acc(15, kSH3[6] * x * (xx - 3.0f * yy));
+      }
+    }
+  }
+#else
+  float w[16];
   w[0] = kSH0;
   if (deg > 0) {
     float dx = pos.x - campos[0], dy = pos.y - campos[1], dz = pos.z - campos[2];
@@ -157,15 +193,11 @@ __device__ __forceinline__ float3 sh_to_rgb(int deg, const float3& pos, const fl
   float c[3];
 #pragma unroll
   for (int ch = 0; ch < 3; ch++) c[ch] = w[0] * sh[ch];
-  // fully unrolled with a predicate, so that w[] is indexed by constants and stays in registers (a loop to n indexes it
-  // dynamically: local memory); same multiply-adds in the same order
+  for (int k = 1; k < n; k++) {
 #pragma unroll
-  for (int k = 1; k < 16; k++) {
-    if (k < n) {
-#pragma unroll
-      for (int ch = 0; ch < 3; ch++) c[ch] = fmaf(w[k], sh[3 * k + ch], c[ch]);
-    }
+    for (int ch = 0; ch < 3; ch++) c[ch] = fmaf(w[k], sh[3 * k + ch], c[ch]);
   }
+#endif
   clamp_mask = 0;
 #pragma unroll
   for (int ch = 0; ch < 3; ch++) {
@@ -376,7 +408,7 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
 // STAGE: SH rows of the warp's 32 Gaussians go through shared memory with coalesced 16-byte loads (sh_stage.cuh);
 // sh_rest != nullptr selects the split layout (shs = f_dc [P,1,3], sh_rest = f_rest [P,M-1,3]).
 template <int JAC_NCOL, bool STAGE, bool FOLD_SCAN>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, (JAC_NCOL == 0 && !STAGE) ? 5 : ((JAC_NCOL == 32 && !STAGE) ? 3 : 0))   // plain: 48 registers, 5 CTAs per SM; pose basis: 80, 3 CTAs
 preprocess_kernel(const ViewConst v, const int P,
                   const float* __restrict__ means3D, const float* __restrict__ opacities,
                   const float* __restrict__ shs, const float* __restrict__ sh_rest, const float* __restrict__ colors_precomp,
@@ -410,6 +442,7 @@ preprocess_kernel(const ViewConst v, const int P,
       if (v.prefiltered) { printf("Point is filtered although prefiltered is set. This shouldn't happen!"); __trap(); }
       break;
     }
+#if MGS_COV6_REGS
     // the six covariance entries live in registers either way (a pointer that selects between the global array and a
     // local one forces the local one into local memory: 6250 local stores per launch in the round-1 profile)
     float cov6[6];
@@ -417,6 +450,12 @@ preprocess_kernel(const ViewConst v, const int P,
 #pragma unroll
       for (int k = 0; k < 6; k++) cov6[k] = cov3D_precomp[6 * (size_t)idx + k];
     } else cov3d_from_scale_rot(scales, rotations, idx, v.scale_modifier, cov6);
+#else
+    float cov6_local[6];
+    const float* cov6;
+    if (cov3D_precomp != nullptr) cov6 = cov3D_precomp + 6 * (size_t)idx;
+    else { cov3d_from_scale_rot(scales, rotations, idx, v.scale_modifier, cov6_local); cov6 = cov6_local; }
+#endif
     const Cov2DOut cv = cov2d_project(p, v, cov6);
     const float det = (cv.a * cv.c - cv.b * cv.b);
     if (det == 0.0f) break;
