@@ -513,7 +513,10 @@ def mapping_leg(dev, rank, world, iters=40, warmup=5, P=200_000, window=8, engin
     out = {"iters_per_s": 1e3 * iters / float(t), "views_per_s": 1e3 * iters * window / float(t), "n_gpus": world, "window": n_window,
            "extra_views": n_extra, "gaussians": sc.means3D.size(0), "config": cfg,
            "views_per_rank": [len(x) for x in per_rank], "allreduce_bytes": nbytes if world > 1 else 0,
-           "scaling": scaling, "cuda_graph": bool(engine and use_graph and exchange == "nccl"),
+           "scaling": scaling,
+           # NCCL path: the whole iteration is one replayed graph; fused exchanges: views + window-pose step are the graph,
+           # mgs_peer_reduce_adam (host-side step / epoch numbers) is launched behind it
+           "cuda_graph": (True if exchange == "nccl" else "compute part; exchange launched eagerly") if (engine and use_graph) else False,
            "api": "MapEngine (mgs_map_*)" if engine else "drop-in autograd surface (MappingStep)",
            "what": f"{n_window}-keyframe window{' + %d extra keyframes' % n_extra if n_extra else ''}: per-view render+mapping "
                    "loss+full backward, isotropic regulariser, one sum-allreduce of the gradient arena, fused Adam on every rank"}
