@@ -407,8 +407,11 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
 // scan in place of a separate tile_scan_kernel launch.
 // STAGE: SH rows of the warp's 32 Gaussians go through shared memory with coalesced 16-byte loads (sh_stage.cuh);
 // sh_rest != nullptr selects the split layout (shs = f_dc [P,1,3], sh_rest = f_rest [P,M-1,3]).
+#ifndef MGS_PRE_BASIS_MIN_CTAS
+#define MGS_PRE_BASIS_MIN_CTAS 3
+#endif
 template <int JAC_NCOL, bool STAGE, bool FOLD_SCAN>
-__global__ void __launch_bounds__(256, (JAC_NCOL == 0 && !STAGE) ? 5 : ((JAC_NCOL == 32 && !STAGE) ? 3 : 0))   // plain: 48 registers, 5 CTAs per SM; pose basis: 80, 3 CTAs
+__global__ void __launch_bounds__(256, (JAC_NCOL == 0 && !STAGE) ? 5 : ((JAC_NCOL == 32 && !STAGE) ? MGS_PRE_BASIS_MIN_CTAS : 0))   // plain: 48 registers, 5 CTAs per SM; pose basis: 80, 3 CTAs
 preprocess_kernel(const ViewConst v, const int P,
                   const float* __restrict__ means3D, const float* __restrict__ opacities,
                   const float* __restrict__ shs, const float* __restrict__ sh_rest, const float* __restrict__ colors_precomp,
