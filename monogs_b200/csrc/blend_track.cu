@@ -45,8 +45,12 @@ template <int NW> struct TrkCfg {
   static constexpr int kThreads = NW * 32;
   static constexpr int kBatch = 128;
   static constexpr size_t kSmem = (size_t)TRK_STAGES * kBatch * sizeof(SplatRec) + 2 * (size_t)kBatch * TRK_NF * sizeof(float);
+  static constexpr size_t kSmemRows = 2 * (size_t)kBatch * sizeof(uint32_t) + 2 * (size_t)kBatch * TRACK_ROW_FLOATS * sizeof(float);
 };
 
+__device__ __forceinline__ void cp_async4(void* dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
+}
 __device__ __forceinline__ void cp_async16(void* dst, const void* src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(dst)), "l"(src) : "memory");
 }
@@ -73,7 +77,9 @@ struct TrackTail {            // the folded update (FOLD): last CTA of the grid 
 //   surface gets the single pass: E and A do not depend on the loss, so forward(theta, rho) can build them before any
 //   loss exists and backward is one cheap pass over the pixels.
 // FOLD: the last CTA to finish (ticket) runs the iteration's serial tail (track_update_body) instead of a separate launch.
-template <bool HAS_DEPTH, bool FAST, int EPI, int NW, bool FOLD>   // FAST: ex2.approx exponent, n_touched not produced
+// ROWS: `recs` holds the sorted Gaussian ids (u32) and `jac` the packed per-Gaussian rows (TRACK_ROW_FLOATS: record + basis);
+//   a batch is then ONE gather by id (cp.async) instead of a bulk copy of per-instance records plus the basis gather.
+template <bool HAS_DEPTH, bool FAST, int EPI, int NW, bool FOLD, bool ROWS>   // FAST: ex2.approx exponent, n_touched not produced
 __global__ void __launch_bounds__(NW * 32, HAS_DEPTH ? MGS_TRK_MIN_CTAS_DEPTH : MGS_TRK_MIN_CTAS)
 blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __restrict__ tile_order, const uint2* __restrict__ ranges,
                    const SplatRec* __restrict__ recs, const float* __restrict__ jac, const float* __restrict__ bg,
@@ -117,8 +123,8 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
   for (int k = 0; k < 3; k++) { E2[k] = A02[k] = A12[k] = A22[k] = Ad2[k] = make_float2(0.f, 0.f); }
 
   // one (warp, splat) step: rec4 = the staged records, j = the splat's slot in them, jrow = its 32-float basis
-  auto hit = [&](const float4* __restrict__ rec4, const int j, const float* __restrict__ jrow) {
-    const float4 g0 = rec4[3 * j + 0], g1 = rec4[3 * j + 1];   // x, y, depth, id | conic xyz, opacity
+  auto hit = [&](const float4* __restrict__ r4 /* the splat's record: 3 quads */, const float* __restrict__ jrow) {
+    const float4 g0 = r4[0], g1 = r4[1];   // x, y, depth, id | conic xyz, opacity
     const float dx = g0.x - pxf, dy = g0.y - pyf;
     const float power = -0.5f * (g1.x * dx * dx + g1.z * dy * dy) - g1.y * dx * dy;
     bool valid = !done && !(power > 0.0f);
@@ -135,7 +141,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     if (valid) {
       const float4* J4 = reinterpret_cast<const float4*>(jrow);
       const float4 b0 = J4[0], b1 = J4[1], b2 = J4[2], b3 = J4[3], b4 = J4[4], b5 = J4[5], b6 = J4[6], b7 = J4[7];
-      const float4 g2 = rec4[3 * j + 2];
+      const float4 g2 = r4[2];
       // folded basis rows: U = f[0..5], V = f[6..11], A = f[12..17], Bm = f[18..23], Cm = f[24..29], yC, -xC
       const float2 dx2 = make_float2(dx, dx), dy2 = make_float2(dy, dy);
       float2 t1[3], t2[3], vp2[3];
@@ -179,7 +185,54 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     }
   };
 
-  {
+  if constexpr (ROWS) {
+    // ---- ids + packed rows: ids of batch i+2 and rows of batch i+1 in flight (cp.async) while batch i is blended ----
+    constexpr int RF = TRACK_ROW_FLOATS, RC = RF / 4;
+    uint32_t (*idstage)[TRK_BATCH] = reinterpret_cast<uint32_t (*)[TRK_BATCH]>(trk_smem);
+    float* rowstage = reinterpret_cast<float*>(trk_smem + 2 * TRK_BATCH * sizeof(uint32_t));
+    const uint32_t* ids = reinterpret_cast<const uint32_t*>(recs) + range.x;
+    auto load_ids = [&](int i) {
+      const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
+      if (tid < cnt) cp_async4(&idstage[i & 1][tid], ids + (size_t)i * TRK_BATCH + tid);
+    };
+    auto gather = [&](int i) {   // rows of batch i (L2-resident per-Gaussian array) -> rowstage[i & 1], 16 B per cp.async
+      const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
+      float4* dst = reinterpret_cast<float4*>(rowstage + (size_t)(i & 1) * TRK_BATCH * RF);
+      for (int e = tid; e < cnt * RC; e += THREADS) {
+        const int slot = e / RC, k = e - slot * RC;
+        cp_async16(dst + e, reinterpret_cast<const float4*>(jac + (size_t)idstage[i & 1][slot] * RF) + k);
+      }
+    };
+    if (rounds > 0) {
+      load_ids(0); cp_async_commit(); cp_async_wait_all();
+      __syncthreads();
+      gather(0);
+      if (rounds > 1) load_ids(1);
+      cp_async_commit();
+    }
+    for (int i = 0; i < rounds; i++) {
+      cp_async_wait_all();   // this thread's share of the rows of batch i (and of the ids of batch i+1) has landed
+      if (__syncthreads_count(done) == THREADS) break;   // CTA vote + publication; nothing is in flight here
+      if (i + 1 < rounds) {
+        gather(i + 1);
+        if (i + 2 < rounds) load_ids(i + 2);
+        cp_async_commit();
+      }
+      const int cnt = min(TRK_BATCH, n - i * TRK_BATCH);
+      const float* recf = rowstage + (size_t)(i & 1) * TRK_BATCH * RF;
+      const float4* row4 = reinterpret_cast<const float4*>(recf);
+      for (int c0 = 0; c0 < cnt; c0 += 32) {
+        const int jj = c0 + lane;
+        unsigned hits = __ballot_sync(0xffffffffu, jj < cnt && splat_hits(recf + RF * jj, patch_x0, patch_x0 + 7.f, patch_y0, patch_y0 + 3.f));
+        if (__ballot_sync(0xffffffffu, !done) == 0u) break;
+        while (hits != 0u) {
+          const int j = c0 + __ffs(hits) - 1;
+          hits &= hits - 1;
+          hit(row4 + RC * j, recf + RF * j + 12);
+        }
+      }
+    }
+  } else {
     // ---- one CTA per tile: records and bases of a batch are staged by the whole CTA, one barrier per batch ----
     if (tid == 0) {
 #pragma unroll
@@ -228,7 +281,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
         while (hits != 0u) {
           const int j = c0 + __ffs(hits) - 1;
           hits &= hits - 1;
-          hit(rec4, j, jst + j * TRK_NF);
+          hit(rec4 + 3 * j, jst + j * TRK_NF);
         }
       }
     }
@@ -327,7 +380,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
   }
 }
 
-template <bool HAS_DEPTH, bool FAST, int EPI, int NW, bool FOLD>
+template <bool HAS_DEPTH, bool FAST, int EPI, int NW, bool FOLD, bool ROWS = false>
 static int launch_trk_t(int tiles, cudaStream_t s, const int W, const int H, const int gx, const uint32_t* tile_order,
                         const uint2* ranges, const SplatRec* recs, const float* jac, const float* bg, float* out_color,
                         float* out_depth, float* out_opacity, int32_t* n_touched, const LossK& lk, float grad_scale,
@@ -338,12 +391,12 @@ static int launch_trk_t(int tiles, cudaStream_t s, const int W, const int H, con
   int dev = 0;
   MGS_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) { set_error("blend_track: device ordinal %d out of range", dev); return MGS_EINVAL; }
-  auto kern = blend_track_kernel<HAS_DEPTH, FAST, EPI, NW, FOLD>;
+  auto kern = blend_track_kernel<HAS_DEPTH, FAST, EPI, NW, FOLD, ROWS>;
   if (!attr_set[dev]) {
-    MGS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TrkCfg<NW>::kSmem));
+    MGS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ROWS ? TrkCfg<NW>::kSmemRows : TrkCfg<NW>::kSmem)));
     attr_set[dev] = true;
   }
-  kern<<<tiles, NW * 32, TrkCfg<NW>::kSmem, s>>>(W, H, gx, tile_order, ranges, recs, jac, bg, out_color, out_depth,
+  kern<<<tiles, NW * 32, ROWS ? TrkCfg<NW>::kSmemRows : TrkCfg<NW>::kSmem, s>>>(W, H, gx, tile_order, ranges, recs, jac, bg, out_color, out_depth,
                                                                      out_opacity, n_touched, lk, grad_scale, partials, tau_sum,
                                                                      sk_weights, sk_scale, sk_image, tail);
   return MGS_OK;
@@ -417,8 +470,9 @@ int blend_track_warps() { return 8; }
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s, const float* sk_weights, float sk_scale, float* sk_image,
-                       const TrackUpdateK* upd, uint32_t* ticket, bool deferred) {
+                       const TrackUpdateK* upd, uint32_t* ticket, bool deferred, bool rows) {
   const int tiles = v.gx * v.gy;
+  if (rows && (deferred || upd != nullptr)) { set_error("blend_track: the packed-row staging serves the fused tracker's un-folded kernels only"); return MGS_EINVAL; }
   if (deferred) {
     // drop-in forward: exact exponent (n_touched produced), depth accumulators always (the loss is not known yet)
     if (sk_image == nullptr || n_touched == nullptr) { set_error("blend_track: deferred mode needs the accumulator planes and n_touched"); return MGS_EINVAL; }
@@ -448,9 +502,19 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
   } while (0)
   int rc = MGS_OK;
   prof_begin(sk_image ? "blend_track_sketch" : "blend_track", s);
-  if (sk_image != nullptr) MGS_TRK_DISPATCH(false, 1, false);
+#define MGS_TRK_DISPATCH_ROWS(HD, SK)                                                                                                  \
+  do {                                                                                                                                 \
+    rc = fl.fast ? launch_trk_t<HD, true, SK, 8, false, true>(MGS_TRK_ARGS) : launch_trk_t<HD, false, SK, 8, false, true>(MGS_TRK_ARGS); \
+  } while (0)
+  if (rows) {
+    if (sk_image != nullptr) MGS_TRK_DISPATCH_ROWS(false, 1);
+    else if (has_depth) MGS_TRK_DISPATCH_ROWS(true, 0);
+    else MGS_TRK_DISPATCH_ROWS(false, 0);
+  }
+  else if (sk_image != nullptr) MGS_TRK_DISPATCH(false, 1, false);
   else if (has_depth) { if (upd) MGS_TRK_DISPATCH(true, 0, true); else MGS_TRK_DISPATCH(true, 0, false); }
   else { if (upd) MGS_TRK_DISPATCH(false, 0, true); else MGS_TRK_DISPATCH(false, 0, false); }
+#undef MGS_TRK_DISPATCH_ROWS
   prof_end(s);
 #undef MGS_TRK_DISPATCH
 #undef MGS_TRK_ARGS

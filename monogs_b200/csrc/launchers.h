@@ -18,7 +18,7 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
 int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false);
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
                    const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first = false, bool scan_done = false,
-                   bool clear_counts = false);
+                   bool clear_counts = false, bool ids_only = false);   // ids_only: sorted Gaussian ids (u32) instead of records
 struct LossK;
 // optional fused loss epilogue of the forward blend (tracking path): per-pixel loss + un-normalised gradient images
 struct FusedLoss { const LossK* k; float grad_scale; float* g_img; float* g_depth; double* partials; bool fast; };
@@ -31,7 +31,7 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s, const float* sk_weights = nullptr, float sk_scale = 0.f,
                        float* sk_image = nullptr, const struct TrackUpdateK* upd = nullptr, uint32_t* ticket = nullptr,
-                       bool deferred = false);
+                       bool deferred = false, bool rows = false);   // rows: ids + packed per-Gaussian rows (fused tracker)
 int blend_track_warps();      // 8 or 4: CTAs per tile = 8 / warps; loss partial slots = tiles * 8 / warps
 // deferred single pass of the drop-in surface: accumulator planes of blend_track<EPI = 2> and their contraction
 size_t pose_deferred_bytes(int W, int H);

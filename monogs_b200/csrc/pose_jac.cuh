@@ -16,6 +16,10 @@ template <int NCOL> struct PoseJac { static constexpr int kFloats = (NCOL * 6 + 
 // so the five per-pixel scalars q_k of the column form never have to be formed: 15 packed multiply-adds instead of
 // 15 + ~14 scalar instructions per (pixel, splat).  Floats 30, 31 = y_C, -x_C: the depth column (0, 0, 1, y_C, -x_C, 0).
 constexpr int POSE_BASIS_FLOATS = 32;
+// Packed per-Gaussian row of the fused tracker (blend_track_kernel<ROWS>): the 12 floats of a SplatRec (x, y, depth, id |
+// conic xyz, opacity | r, g, b, extent) followed by the 32-float basis — one 176-byte gather by id replaces the per-instance
+// 48-byte record copy of the sort kernel plus the separate basis gather.
+constexpr int TRACK_ROW_FLOATS = 12 + POSE_BASIS_FLOATS;
 
 template <int NCOL>
 __device__ __forceinline__ void compute_pose_B(const ViewConst& v, const int idx, const float3& p,
@@ -25,7 +29,8 @@ __device__ __forceinline__ void compute_pose_B(const ViewConst& v, const int idx
 
 __device__ __forceinline__ void build_pose_basis(const ViewConst& v, const int idx, const float3& p, const float3& conic,
                                                  const float* __restrict__ scales, const float* __restrict__ rotations,
-                                                 const float* __restrict__ cov3D_precomp, float* __restrict__ basis) {
+                                                 const float* __restrict__ cov3D_precomp, float* __restrict__ basis,
+                                                 const int row_floats = POSE_BASIS_FLOATS, const int row_offset = 0) {
   float B[PoseJac<6>::kFloats];
   compute_pose_B<6>(v, idx, p, nullptr, scales, rotations, cov3D_precomp, 0u, B);
   const float wx = 0.5f * (float)v.W, wy = 0.5f * (float)v.H;
@@ -40,7 +45,7 @@ __device__ __forceinline__ void build_pose_basis(const ViewConst& v, const int i
     o[24 + k] = -0.5f * B[4 * 6 + k];
   }
   o[30] = B[5 * 6 + 3]; o[31] = B[5 * 6 + 4];
-  float4* out = reinterpret_cast<float4*>(basis + (size_t)idx * POSE_BASIS_FLOATS);
+  float4* out = reinterpret_cast<float4*>(basis + (size_t)idx * row_floats + row_offset);
 #pragma unroll
   for (int k = 0; k < POSE_BASIS_FLOATS / 4; k++) out[k] = make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
 }

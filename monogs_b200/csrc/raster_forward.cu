@@ -411,7 +411,7 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
 #define MGS_PRE_BASIS_MIN_CTAS 3
 #endif
 template <int JAC_NCOL, bool STAGE, bool FOLD_SCAN>
-__global__ void __launch_bounds__(256, (JAC_NCOL == 0 && !STAGE) ? 5 : ((JAC_NCOL == 32 && !STAGE) ? MGS_PRE_BASIS_MIN_CTAS : 0))   // plain: 48 registers, 5 CTAs per SM; pose basis: 80, 3 CTAs
+__global__ void __launch_bounds__(256, (JAC_NCOL == 0 && !STAGE) ? 5 : (((JAC_NCOL == 32 || JAC_NCOL == TRACK_ROW_FLOATS) && !STAGE) ? MGS_PRE_BASIS_MIN_CTAS : 0))   // plain: 48 registers, 5 CTAs per SM; pose basis: 80, 3 CTAs
 preprocess_kernel(const ViewConst v, const int P,
                   const float* __restrict__ means3D, const float* __restrict__ opacities,
                   const float* __restrict__ shs, const float* __restrict__ sh_rest, const float* __restrict__ colors_precomp,
@@ -495,15 +495,27 @@ preprocess_kernel(const ViewConst v, const int P,
   } else if (shs != nullptr) sh_row = shs + (size_t)idx * v.M * 3;
   if (alive) {
     uint32_t cm = 0;
+    float3 col = {0.f, 0.f, 0.f};
     if (colors_precomp == nullptr) {
-      const float3 c = sh_to_rgb(v.D, p, v.campos, sh_row, cm);
-      rgb4[idx] = make_float4(c.x, c.y, c.z, __uint_as_float(cm));
+      col = sh_to_rgb(v.D, p, v.campos, sh_row, cm);
+      // (packed-row mode: colour, conic and opacity live in the row; nothing reads the separate arrays, and the kernel
+      // is bound by its strided stores)
+      if (JAC_NCOL != TRACK_ROW_FLOATS) rgb4[idx] = make_float4(col.x, col.y, col.z, __uint_as_float(cm));
     }
     if (JAC_NCOL == 32) build_pose_basis(v, idx, p, conic, scales, rotations, cov3D_precomp, jac);
+    else if (JAC_NCOL == TRACK_ROW_FLOATS) {
+      // the packed row of the fused tracker: record part (what write_record assembles per instance) + basis
+      build_pose_basis(v, idx, p, conic, scales, rotations, cov3D_precomp, jac, TRACK_ROW_FLOATS, 12);
+      const float op = opacities[idx];
+      float4* row = reinterpret_cast<float4*>(jac + (size_t)idx * TRACK_ROW_FLOATS);
+      row[0] = make_float4(pix.x, pix.y, view_z, __uint_as_float((uint32_t)idx));
+      row[1] = make_float4(conic.x, conic.y, conic.z, op);
+      row[2] = make_float4(col.x, col.y, col.z, __uint_as_float(splat_extent(conic.x, conic.y, conic.z, op)));
+    }
     else if (JAC_NCOL > 0) build_pose_jac<(JAC_NCOL == 9 ? 9 : 6)>(v, idx, p, shs, scales, rotations, cov3D_precomp, cm, jac);
     depths[idx] = view_z;
     means2D[idx] = pix;
-    conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
+    if (JAC_NCOL != TRACK_ROW_FLOATS) conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
     my_radius_i = (int)my_radius;
     touched = area;
     rmin = r0; rmax = r1;
@@ -586,9 +598,13 @@ emit_kernel(const int P, const uint32_t R_cap, const int gx, const int gy,
 constexpr int SORT_CAP = 4096;
 struct U64Less { __device__ __forceinline__ bool operator()(unsigned long long a, unsigned long long b) const { return a < b; } };
 
-__device__ __forceinline__ void write_record(const unsigned long long w, SplatRec* __restrict__ dst,
+// means2D == nullptr: ids-only mode of the fused tracker — the sorted Gaussian ids (u32) are all that is written, into the
+// same workspace region; blend_track_kernel<ROWS> gathers the packed per-Gaussian rows by id (pose_jac.cuh).
+__device__ __forceinline__ void write_record(const unsigned long long w, void* __restrict__ dst_base, const int e,
                                              const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                                              const float4* __restrict__ rgb4, const float* __restrict__ colors_precomp) {
+  if (means2D == nullptr) { reinterpret_cast<uint32_t*>(dst_base)[e] = (uint32_t)w; return; }
+  SplatRec* dst = reinterpret_cast<SplatRec*>(dst_base) + e;
   const uint32_t id = (uint32_t)w;
   const float2 xy = means2D[id];
   const float4 co = conic_opacity[id];
@@ -606,7 +622,7 @@ __device__ __forceinline__ void write_record(const unsigned long long w, SplatRe
 #endif
 template <int IPT, int THREADS, typename Temp>
 __device__ __noinline__ void sort_tile_regs(Temp& temp, const unsigned long long* __restrict__ seg, const int n,
-                                            SplatRec* __restrict__ dst, const float2* __restrict__ means2D,
+                                            void* __restrict__ dst, const float2* __restrict__ means2D,
                                             const float4* __restrict__ conic_opacity, const float4* __restrict__ rgb4,
                                             const float* __restrict__ colors_precomp) {
   using Sort = cub::BlockMergeSort<unsigned long long, THREADS, IPT>;
@@ -620,7 +636,7 @@ __device__ __noinline__ void sort_tile_regs(Temp& temp, const unsigned long long
 #pragma unroll
   for (int i = 0; i < IPT; i++) {
     const int e = threadIdx.x * IPT + i;
-    if (e < n) write_record(k[i], dst + e, means2D, conic_opacity, rgb4, colors_precomp);
+    if (e < n) write_record(k[i], dst, e, means2D, conic_opacity, rgb4, colors_precomp);
   }
 }
 
@@ -646,7 +662,7 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
     const int n = (int)(range.y - range.x);
     if (n == 0 || n > LARGE_LIST) return;
     unsigned long long* seg = list + range.x;
-    SplatRec* dst = recs + range.x;
+    void* dst = means2D == nullptr ? (void*)(reinterpret_cast<uint32_t*>(recs) + range.x) : (void*)(recs + range.x);
     if (n <= 512) sort_tile_regs<SI / 2, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
     else sort_tile_regs<SI, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
     return;
@@ -656,7 +672,7 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
     const uint2 range = ranges[tile_ctr[(size_t)li * TILE_CTR_STRIDE + 2]];
     const int n = (int)(range.y - range.x);
     unsigned long long* seg = list + range.x;
-    SplatRec* dst = recs + range.x;
+    void* dst = means2D == nullptr ? (void*)(reinterpret_cast<uint32_t*>(recs) + range.x) : (void*)(recs + range.x);
     if (n <= SORT_CAP) {
       if (n <= 2048) sort_tile_regs<8, 256>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
       else sort_tile_regs<16, 256>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
@@ -681,7 +697,7 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
       }
     }
     for (int e = threadIdx.x; e < n; e += blockDim.x)
-      write_record(__ldcg(seg + e), dst + e, means2D, conic_opacity, rgb4, colors_precomp);
+      write_record(__ldcg(seg + e), dst, e, means2D, conic_opacity, rgb4, colors_precomp);
   }
 }
 
@@ -715,9 +731,9 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
       ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched), ws_ptr<uint32_t>(ws, L.tile_ctr), jac, R_cap, \
       ws_ptr<uint2>(ws, L.ranges), ws_ptr<WsHeader>(ws, L.header), heavy
   // SH rows of more than one coefficient are staged through shared memory (128 threads: 4 tiles of [32][3M | 1] floats)
-  const bool stage = shs != nullptr && colors_precomp == nullptr && v.M > 1 && !(jac != nullptr && jac_ncol == 32);
+  const bool stage = shs != nullptr && colors_precomp == nullptr && v.M > 1 && !(jac != nullptr && (jac_ncol == 32 || jac_ncol == TRACK_ROW_FLOATS));
   if (sh_rest != nullptr && !stage) { set_error("preprocess: split SH layout needs sh_coeffs > 1 and no colors_precomp"); return MGS_EINVAL; }
-  if (jac != nullptr && jac_ncol == 32 && fold_req == nullptr) { set_error("preprocess: the folded pose basis is built by the fused SH-degree-0 tracker only"); return MGS_EINVAL; }
+  if (jac != nullptr && (jac_ncol == 32 || jac_ncol == TRACK_ROW_FLOATS) && fold_req == nullptr) { set_error("preprocess: the folded pose basis is built by the fused SH-degree-0 tracker only"); return MGS_EINVAL; }
   prof_begin(fold ? "preprocess+scan" : "preprocess", s);
   if (stage) {
     const int T = 128;
@@ -733,10 +749,12 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
     if (fold) {
       if (jac == nullptr) preprocess_kernel<0, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
       else if (jac_ncol == 32) preprocess_kernel<32, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+      else if (jac_ncol == TRACK_ROW_FLOATS) preprocess_kernel<TRACK_ROW_FLOATS, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
       else { set_error("preprocess: unsupported fused variant"); return MGS_EINVAL; }
     } else if (jac == nullptr) preprocess_kernel<0, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
     else if (jac_ncol == 9) preprocess_kernel<9, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
     else if (jac_ncol == 32) preprocess_kernel<32, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+    else if (jac_ncol == TRACK_ROW_FLOATS) preprocess_kernel<TRACK_ROW_FLOATS, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
     else preprocess_kernel<6, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
   }
   prof_end(s);
@@ -747,7 +765,8 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
 }
 
 int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const int32_t* radii, void* ws,
-                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first, bool scan_done, bool clear_counts) {
+                   const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first, bool scan_done, bool clear_counts,
+                   bool ids_only) {
   const int tiles = v.gx * v.gy;
   if (!scan_done) {
     int rc = launch_tile_scan(v, ws, L, R_cap, s, heavy_first);   // ranges (clipped to R_cap), scatter cursors, header
@@ -758,7 +777,8 @@ int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const
       P, (uint32_t)R_cap, v.gx, v.gy, ws_ptr<float2>(ws, L.means2D), ws_ptr<float>(ws, L.depths), radii,
       ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<unsigned long long>(ws, L.list)));
   MGS_LAUNCH_CHECK();
-#define MGS_SORT_ARGS ws_ptr<uint2>(ws, L.ranges), ws_ptr<unsigned long long>(ws, L.list), ws_ptr<float2>(ws, L.means2D), \
+#define MGS_SORT_ARGS ws_ptr<uint2>(ws, L.ranges), ws_ptr<unsigned long long>(ws, L.list),                                   \
+      (ids_only ? (const float2*)nullptr : ws_ptr<float2>(ws, L.means2D)),                                                       \
       ws_ptr<float4>(ws, L.conic_opacity), ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<SplatRec>(ws, L.records),     \
       ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<WsHeader>(ws, L.header), clear_counts ? 1 : 0
   MGS_PROF("tile_sort_records", s, tile_sort_records_kernel<false><<<tiles, MGS_SORT_THREADS, 0, s>>>(MGS_SORT_ARGS));

@@ -147,6 +147,18 @@ size_t mgs_track_scratch_bytes(int32_t P, int32_t W, int32_t H) {
          up(9 * npix * 4);   // + the per-pixel Jacobian rows of the second-order iteration
 }
 
+// Packed-row staging of the single-pass blend (blend_track_kernel<ROWS>, pose_jac.cuh): preprocess writes one 176-byte row per
+// Gaussian, the sort kernel writes sorted ids only, the blend gathers rows by id.  MGS_TRACK_ROWS=0 selects the per-instance
+// 48-byte records + separate basis gather (the comparison is in profiles/r02_notes.txt).
+static bool track_update_fold() {
+  static const bool on = [] { const char* e = getenv("MGS_UPDATE_FOLD"); return e && e[0] == '1'; }();
+  return on;
+}
+static bool track_rows() {
+  static const bool on = [] { const char* e = getenv("MGS_TRACK_ROWS"); return !(e && e[0] == '0'); }();
+  return on;
+}
+
 int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   if (!t) { set_error("track: args is null"); return MGS_EINVAL; }
   const mgs_view* view = &t->view;
@@ -184,13 +196,15 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   // The workspace and the scratch of a tracker are zero-filled ONCE by their owner: tile counters, the scan ticket, the
   // tangent accumulator and the update ticket are all left zero by the iteration that used them (the sort kernel clears
   // its tile's counter, the update kernel re-zeroes tau_raw), so an iteration is 7 kernels and no memset.
+  const bool rows = !with_color && track_rows() && !track_update_fold();   // (the folded-update kernels keep the record staging)
   const FoldScan fs{t->R_cap, /*heavy_first=*/!with_color, /*in_kernel=*/false};
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
-                              ws, L, s, jac, with_color ? 9 : 32, nullptr, &fs)))
+                              ws, L, s, jac, with_color ? 9 : (rows ? TRACK_ROW_FLOATS : 32), nullptr, &fs)))
     return rc;
   if (!t->fast_math) MGS_CUDA_TRY(cudaMemsetAsync(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
   if (with_color) MGS_CUDA_TRY(cudaMemsetAsync(tau_raw, 0, 6 * sizeof(float), s));
-  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, fs.heavy_first, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
+  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, fs.heavy_first, /*scan_done=*/true, /*clear_counts=*/true,
+                           /*ids_only=*/rows))) return rc;
 
   LossK lk;
   lk.mode = t->loss_mode; lk.npix = (int)npix; lk.use_depth = use_depth;
@@ -218,12 +232,12 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
     // The serial tail (loss norm, Adam, pose update) runs as its own one-CTA launch by default: measured on the B200 the
     // blend kernel is 24 us shorter without the per-CTA fence + ticket and the iteration 15 us shorter in total
     // (profiles/r02_notes.txt).  MGS_UPDATE_FOLD=1 selects the variant that runs it in the blend kernel's last CTA.
-    static const bool update_fold = [] { const char* e = getenv("MGS_UPDATE_FOLD"); return e && e[0] == '1'; }();
+    const bool update_fold = track_update_fold();
     if (update_fold)
       return launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
                                 tau_raw, s, nullptr, 0.f, nullptr, &k, ticket);
     if ((rc = launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
-                                 tau_raw, s, nullptr, 0.f, nullptr, nullptr, nullptr))) return rc;
+                                 tau_raw, s, nullptr, 0.f, nullptr, nullptr, nullptr, false, rows))) return rc;
     MGS_PROF("track_update", s, track_update_kernel<<<1, 256, 0, s>>>(k));
     MGS_LAUNCH_CHECK();
     return MGS_OK;
@@ -282,12 +296,13 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   k.conv_thr = a->converged_threshold; k.loss_out = t->loss;
   MGS_PROF("track2_begin", s, track2_begin_kernel<<<1, 32, 0, s>>>(k));
   MGS_LAUNCH_CHECK();
+  const bool rows = track_rows();
   const FoldScan fs{t->R_cap, /*heavy_first=*/true, /*in_kernel=*/false};
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
-                              ws, L, s, jac, 32, nullptr, &fs)))
+                              ws, L, s, jac, rows ? TRACK_ROW_FLOATS : 32, nullptr, &fs)))
     return rc;
   if (!t->fast_math) MGS_CUDA_TRY(cudaMemsetAsync(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
-  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
+  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true, /*ids_only=*/rows))) return rc;
   LossK lk;
   lk.mode = MGS_LOSS_TRACK_HUBER; lk.npix = (int)npix; lk.use_depth = 0;
   lk.thr = t->rgb_boundary_threshold; lk.alpha = t->alpha; lk.delta = t->huber_delta; lk.scale = 1.f; lk.eps = 1e-8f;
@@ -297,7 +312,7 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   fl.k = &lk; fl.grad_scale = 1.f; fl.g_img = nullptr; fl.g_depth = nullptr; fl.partials = partials; fl.fast = t->fast_math != 0;
   const float sk_scale = (float)((double)k.rows / (double)npix);     // 1 / (m / (stack_dim * sketch_dim)), slam_frontend.py:642
   if ((rc = launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, false, nullptr, s,
-                               a->rand_weights, sk_scale, sk_image)))
+                               a->rand_weights, sk_scale, sk_image, nullptr, nullptr, false, rows)))
     return rc;
   if ((rc = launch_sketch_reduce(sk_image, H, W, a->n_stacks, a->sketch_dim, a->sketch_indices, a->rows, s, 9))) return rc;
   MGS_PROF("track2_solve", s, track2_solve_kernel<<<1, 256, 0, s>>>(k));

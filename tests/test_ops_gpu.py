@@ -109,7 +109,11 @@ def test_fused_track_iteration_matches_composed_entry_points(mode, use_depth):
             losses.append(float(tr.loss))
         runs.append((losses, tr.T.clone(), tr.tau.clone(), tr.params.clone(), tr.color.clone()))
     (l0, T0, tau0, p0, c0), (l1, T1, tau1, p1, c1) = runs
-    assert all(abs(a - b) <= 1e-4 * abs(b) + 1e-7 for a, b in zip(l0, l1)), (l0, l1)
+    # the first iterations start from identical states: tight.  Later ones inherit the rounding-level differences of the two
+    # paths through Adam, which turns a sign flip of a near-zero gradient (float atomics sum in a different order from run
+    # to run) into a full learning-rate step: compared at the trajectory tolerance
+    assert all(abs(a - b) <= (1e-4 if i < 3 else 1e-3) * abs(b) + 1e-7 for i, (a, b) in enumerate(zip(l0, l1))), \
+        [(i, a, b) for i, (a, b) in enumerate(zip(l0, l1))]
     # 12 Adam steps amplify the rounding-level differences of the two paths (ex2.approx vs expf, atomic summation order):
     # the trajectories are compared at 1e-3, the per-call parity gates live in test_parity_gpu.py
     assert U.rel_err(T0, T1) <= 1e-4 and U.rel_err(p0, p1) <= 1e-3 and U.rel_err(c0, c1) <= 1e-3
