@@ -30,7 +30,8 @@ __device__ __forceinline__ void compute_pose_B(const ViewConst& v, const int idx
 __device__ __forceinline__ void build_pose_basis(const ViewConst& v, const int idx, const float3& p, const float3& conic,
                                                  const float* __restrict__ scales, const float* __restrict__ rotations,
                                                  const float* __restrict__ cov3D_precomp, float* __restrict__ basis,
-                                                 const int row_floats = POSE_BASIS_FLOATS, const int row_offset = 0) {
+                                                 const int row_floats = POSE_BASIS_FLOATS, const int row_offset = 0,
+                                                 const int out_row = -1 /* row to write; default: idx */) {
   float B[PoseJac<6>::kFloats];
   compute_pose_B<6>(v, idx, p, nullptr, scales, rotations, cov3D_precomp, 0u, B);
   const float wx = 0.5f * (float)v.W, wy = 0.5f * (float)v.H;
@@ -45,7 +46,7 @@ __device__ __forceinline__ void build_pose_basis(const ViewConst& v, const int i
     o[24 + k] = -0.5f * B[4 * 6 + k];
   }
   o[30] = B[5 * 6 + 3]; o[31] = B[5 * 6 + 4];
-  float4* out = reinterpret_cast<float4*>(basis + (size_t)idx * row_floats + row_offset);
+  float4* out = reinterpret_cast<float4*>(basis + (size_t)(out_row >= 0 ? out_row : idx) * row_floats + row_offset);
 #pragma unroll
   for (int k = 0; k < POSE_BASIS_FLOATS / 4; k++) out[k] = make_float4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
 }

@@ -505,9 +505,12 @@ preprocess_kernel(const ViewConst v, const int P,
     if (JAC_NCOL == 32) build_pose_basis(v, idx, p, conic, scales, rotations, cov3D_precomp, jac);
     else if (JAC_NCOL == TRACK_ROW_FLOATS) {
       // the packed row of the fused tracker: record part (what write_record assembles per instance) + basis
-      build_pose_basis(v, idx, p, conic, scales, rotations, cov3D_precomp, jac, TRACK_ROW_FLOATS, 12);
+      // ... assembled in the CTA's shared-memory tile [256][44] and written out below by the whole CTA: the rows of a CTA's
+      // 256 consecutive Gaussians are one contiguous 45 KB block, so the copy is coalesced 16-byte stores, whereas a thread
+      // writing its own row issues eleven 16-byte stores at a 176-byte lane stride (the kernel was bound by those)
+      build_pose_basis(v, idx, p, conic, scales, rotations, cov3D_precomp, sh_tile, TRACK_ROW_FLOATS, 12, (int)threadIdx.x);
       const float op = opacities[idx];
-      float4* row = reinterpret_cast<float4*>(jac + (size_t)idx * TRACK_ROW_FLOATS);
+      float4* row = reinterpret_cast<float4*>(sh_tile + (size_t)threadIdx.x * TRACK_ROW_FLOATS);
       row[0] = make_float4(pix.x, pix.y, view_z, __uint_as_float((uint32_t)idx));
       row[1] = make_float4(conic.x, conic.y, conic.z, op);
       row[2] = make_float4(col.x, col.y, col.z, __uint_as_float(splat_extent(conic.x, conic.y, conic.z, op)));
@@ -523,6 +526,20 @@ preprocess_kernel(const ViewConst v, const int P,
   if (idx < P) {
     radii[idx] = my_radius_i;
     tiles_touched[idx] = touched;
+  }
+  if constexpr (JAC_NCOL == TRACK_ROW_FLOATS) {
+    __shared__ uint32_t s_alive[8];
+    const unsigned am = __ballot_sync(0xffffffffu, alive);
+    if ((threadIdx.x & 31) == 0) s_alive[threadIdx.x >> 5] = am;
+    __syncthreads();
+    constexpr int RC = TRACK_ROW_FLOATS / 4;
+    const float4* src4 = reinterpret_cast<const float4*>(sh_tile);
+    float4* dst4 = reinterpret_cast<float4*>(jac + (size_t)blockIdx.x * 256 * TRACK_ROW_FLOATS);
+#pragma unroll
+    for (int q = 0; q < RC; q++) {
+      const int e = q * 256 + (int)threadIdx.x, r = e / RC;
+      if ((s_alive[r >> 5] >> (r & 31)) & 1u) dst4[e] = src4[e];
+    }
   }
   // instances per tile (the histogram of the counting sort that replaces the reference's global key sort)
   for_each_tile(rmin, rmax, v.gx, 0ull, [&](const uint32_t (&tile)[4], int cnt, unsigned long long) {
@@ -749,12 +766,12 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
     if (fold) {
       if (jac == nullptr) preprocess_kernel<0, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
       else if (jac_ncol == 32) preprocess_kernel<32, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-      else if (jac_ncol == TRACK_ROW_FLOATS) preprocess_kernel<TRACK_ROW_FLOATS, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+      else if (jac_ncol == TRACK_ROW_FLOATS) preprocess_kernel<TRACK_ROW_FLOATS, false, true><<<(P + 255) / 256, 256, 256 * TRACK_ROW_FLOATS * sizeof(float), s>>>(MGS_PRE_ARGS);
       else { set_error("preprocess: unsupported fused variant"); return MGS_EINVAL; }
     } else if (jac == nullptr) preprocess_kernel<0, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
     else if (jac_ncol == 9) preprocess_kernel<9, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
     else if (jac_ncol == 32) preprocess_kernel<32, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-    else if (jac_ncol == TRACK_ROW_FLOATS) preprocess_kernel<TRACK_ROW_FLOATS, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+    else if (jac_ncol == TRACK_ROW_FLOATS) preprocess_kernel<TRACK_ROW_FLOATS, false, false><<<(P + 255) / 256, 256, 256 * TRACK_ROW_FLOATS * sizeof(float), s>>>(MGS_PRE_ARGS);
     else preprocess_kernel<6, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
   }
   prof_end(s);
