@@ -210,13 +210,14 @@ def algorithmic_bytes(P, P_vis, R, R_cap, W, H, M=1):
     """Per-launch algorithmic bytes of every kernel of the fused tracking iteration."""
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     return {
-        "preprocess": 12 * P + 8 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8 + 16 + 16) + P_vis * 144,
+        # fused tracker, packed-row mode (DESIGN.md redesign 22): per visible Gaussian depth + mean2D (12 B) and one 176-B row
+        "preprocess": 12 * P + 8 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8) + P_vis * 176,
         "preprocess+scan": 12 * P + 8 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8 + 16 + 16) + P_vis * 128 + 16 * tiles,
         "tile_scan": 16 * tiles,
         "emit": 4 * P + P_vis * 12 + 8 * R,
-        "tile_sort_records": R * (8 + 44 + 48) + 8 * tiles,
+        "tile_sort_records": R * (8 + 4) + 8 * tiles,          # 64-bit words in, sorted ids out
         "tile_sort_records_large": 8 * tiles,
-        "blend_track": R * (48 + 128) + (20 + 12) * W * H + 40 * tiles,
+        "blend_track": R * (4 + 176) + (20 + 12) * W * H + 40 * tiles,   # id + gathered row per instance
         "blend_forward": R * 48 + (28 + 12 + 12) * W * H + 40 * tiles,
         "blend_backward_pose": R * (48 + 144) + 20 * W * H + 8 * tiles,
         "track_update": 32 * tiles,
