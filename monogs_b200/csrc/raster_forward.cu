@@ -327,11 +327,12 @@ __device__ __noinline__ void tile_scan_body(uint32_t* __restrict__ tile_ctr, con
   if (threadIdx.x == 0) { n_large = 0u; max_count = 0u; }
   __syncthreads();
   uint32_t carry = 0;
+  uint32_t ck[IPT] = {0u, 0u, 0u, 0u};     // the counts of the (usually only) sweep, kept for the heavy-first passes below
   for (int base = 0; base < tiles; base += THREADS * IPT) {
     const int t0 = base + threadIdx.x * IPT;
     uint32_t c[IPT], sum = 0u, m = 0u;
 #pragma unroll
-    for (int i = 0; i < IPT; i++) c[i] = t0 + i < tiles ? __ldcg(&tile_ctr[(size_t)(t0 + i) * TILE_CTR_STRIDE]) : 0u;
+    for (int i = 0; i < IPT; i++) { c[i] = t0 + i < tiles ? __ldcg(&tile_ctr[(size_t)(t0 + i) * TILE_CTR_STRIDE]) : 0u; ck[i] = c[i]; }
 #pragma unroll
     for (int i = 0; i < IPT; i++) { sum += c[i]; m = max(m, c[i]); }
     m = __reduce_max_sync(0xffffffffu, m);
@@ -370,10 +371,18 @@ __device__ __noinline__ void tile_scan_body(uint32_t* __restrict__ tile_ctr, con
   __shared__ uint32_t bucket[64];
   if (threadIdx.x < 64) bucket[threadIdx.x] = 0u;
   __syncthreads();
-  const uint32_t scale = max_count > 0u ? max_count : 1u;
-  for (int t = threadIdx.x; t < tiles; t += THREADS) {
-    const uint32_t c = __ldcg(&tile_ctr[(size_t)t * TILE_CTR_STRIDE]);
-    atomicAdd(&bucket[63u - (uint32_t)(((unsigned long long)c * 63ull) / scale)], 1u);
+  // bucket = 63 - floor(63 c / max) in float: any monotone map of the count will do (a 64-bit integer division per tile
+  // and pass cost more than the rest of the pass).  With one sweep (tiles <= THREADS * 4: every frame up to 1920x1080 at
+  // 1024 threads) the counts are still in registers; otherwise they are read again.
+  const float inv = 63.0f / (float)(max_count > 0u ? max_count : 1u);
+  auto bucket_of = [&](const uint32_t c) { return 63u - min(63u, (uint32_t)((float)c * inv)); };
+  const bool single = tiles <= THREADS * IPT;
+  if (single) {
+#pragma unroll
+    for (int i = 0; i < IPT; i++)
+      if ((int)threadIdx.x * IPT + i < tiles) atomicAdd(&bucket[bucket_of(ck[i])], 1u);
+  } else {
+    for (int t = threadIdx.x; t < tiles; t += THREADS) atomicAdd(&bucket[bucket_of(__ldcg(&tile_ctr[(size_t)t * TILE_CTR_STRIDE]))], 1u);
   }
   __syncthreads();
   if (threadIdx.x < 32) {   // exclusive scan of the 64 bucket sizes
@@ -388,10 +397,17 @@ __device__ __noinline__ void tile_scan_body(uint32_t* __restrict__ tile_ctr, con
     bucket[2 * threadIdx.x + 1] = incl - b;
   }
   __syncthreads();
-  for (int t = threadIdx.x; t < tiles; t += THREADS) {
-    const uint32_t c = __ldcg(&tile_ctr[(size_t)t * TILE_CTR_STRIDE]);
-    const uint32_t pos = atomicAdd(&bucket[63u - (uint32_t)(((unsigned long long)c * 63ull) / scale)], 1u);
-    tile_ctr[(size_t)pos * TILE_CTR_STRIDE + 3] = (uint32_t)t;
+  if (single) {
+#pragma unroll
+    for (int i = 0; i < IPT; i++) {
+      const int t = (int)threadIdx.x * IPT + i;
+      if (t < tiles) tile_ctr[(size_t)atomicAdd(&bucket[bucket_of(ck[i])], 1u) * TILE_CTR_STRIDE + 3] = (uint32_t)t;
+    }
+  } else {
+    for (int t = threadIdx.x; t < tiles; t += THREADS) {
+      const uint32_t pos = atomicAdd(&bucket[bucket_of(__ldcg(&tile_ctr[(size_t)t * TILE_CTR_STRIDE]))], 1u);
+      tile_ctr[(size_t)pos * TILE_CTR_STRIDE + 3] = (uint32_t)t;
+    }
   }
 }
 
