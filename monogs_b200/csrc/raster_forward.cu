@@ -696,7 +696,8 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
     if (n == 0 || n > LARGE_LIST) return;
     unsigned long long* seg = list + range.x;
     void* dst = means2D == nullptr ? (void*)(reinterpret_cast<uint32_t*>(recs) + range.x) : (void*)(recs + range.x);
-    if (n <= 512) sort_tile_regs<SI / 2, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+    if (n <= 256) sort_tile_regs<SI / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
+    else if (n <= 512) sort_tile_regs<SI / 2, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
     else if (n <= 768) sort_tile_regs<SI * 3 / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);   // lists just over 512 are common at 640x480 / 200k
     else sort_tile_regs<SI, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
     return;
