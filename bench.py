@@ -206,9 +206,18 @@ def profile_row(kernel_prefix):
     return row, ("stale: changed since the capture: " + ", ".join(stale)) if stale else None
 
 
-def algorithmic_bytes(P, P_vis, R, R_cap, W, H, M=1):
+def algorithmic_bytes(P, P_vis, R, R_cap, W, H, M=1, segments=False):
     """Per-launch algorithmic bytes of every kernel of the fused tracking iteration."""
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    if segments:
+        # fixed tile segments (DESIGN.md redesign 23): the preprocess kernel scatters one 8-byte word per instance (no depth /
+        # mean2D arrays), one kernel sorts the segments (words in, ids out, counts in, ranges + order out)
+        return {
+            "preprocess": 12 * P + 8 * P + P_vis * (32 + 12 * M) + P_vis * 176 + 8 * R,
+            "tile_sort_segments": R * (8 + 4) + (4 + 8 + 4) * tiles,
+            "blend_track": R * (4 + 176) + (20 + 12) * W * H + 44 * tiles,
+            "track_update": 32 * tiles,
+        }
     return {
         # fused tracker, packed-row mode (DESIGN.md redesign 22): per visible Gaussian depth + mean2D (12 B) and one 176-B row
         "preprocess": 12 * P + 8 * P + P_vis * (32 + 12 * M) + P_vis * (4 + 8) + P_vis * 176,
@@ -683,8 +692,11 @@ def main():
         te = torch.tensor([time.perf_counter() - t0], device=dev)
         if world > 1: dist.all_reduce(te, op=dist.ReduceOp.MAX)
         return world * args.steps / float(te)
-    e2e_sync = run_e2e(e2e_sync_step)
-    e2e = {"value": run_e2e(e2e_lagged), "unit": "iters/s",
+    # host-timed and short (K steps of ~0.27 ms): one hiccup of the host moves a single run by 10 %, so each variant is run
+    # three times (K steps each) and the median is reported
+    median3 = lambda fn: sorted(run_e2e(fn) for _ in range(3))[1]
+    e2e_sync = median3(e2e_sync_step)
+    e2e = {"value": median3(e2e_lagged), "unit": "iters/s", "runs": "median of 3 runs of K steps",
            "h2d_bytes_per_step": gt_host.numel() * 4 + (depth_host.numel() * 4 if depth_host is not None else 0),
            "d2h_bytes_per_step": 28, "value_sync_every_step": e2e_sync,
            "api": "monogs_b200.tracking.PoseTracker.bind_host/step_host_lagged over the C-ABI: one CUDA-graph launch per "
@@ -700,7 +712,7 @@ def main():
                                 "Huber(0.01)+L2 per-pixel residual (slam_frontend.py:596-598)"),
                        "l2": "256 MiB buffer written between steps, outside the per-step event pairs",
                        "multi_gpu": "replicas only (tracking does not shard); see mapping"},
-            "clocks": clk, "e2e": e2e, "gpu_launches": KERNELS_PER_ITER * args.steps,
+            "clocks": clk, "e2e": e2e, "gpu_launches": tr.kernels_per_iter * args.steps,
             "value_l2_warm": world * args.steps / (warm_ms * 1e-3)}
     if not args.no_extras:
         if world == 1:
@@ -711,7 +723,7 @@ def main():
                 line["e2e_dropin"] = {"error": repr(ex)[:200]}
             prof, R, p_vis, R_cap = kernel_profile(args.config, dev, min(args.steps, 50))
             P = scd.means3D.size(0)
-            ab = algorithmic_bytes(P, p_vis, R, R_cap, cam.W, cam.H)
+            ab = algorithmic_bytes(P, p_vis, R, R_cap, cam.W, cam.H, segments=tr.tile_segments)
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
             peak, src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
             for k, v in prof.items():

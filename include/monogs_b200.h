@@ -112,12 +112,14 @@ int mgs_raster_forward(const mgs_view* view, int32_t P,
                        float* out_color, float* out_depth, float* out_opacity, int32_t* n_touched,
                        int32_t* status_out, void* ready_event, void* stream);
 
-/* Asynchronous copy of the first six header words of a workspace (see status_out above) to pinned host or device
- * memory.  The two sticky words are only ever raised by the kernels: a loop that renders many views into one workspace
+/* Asynchronous copy of the first EIGHT header words of a workspace to pinned host or device memory: the six status
+ * words (see status_out above), then [6] an internal ticket (zero between launches) and [7] max_tile_count, sticky like
+ * max_rendered: the longest tile list (instances of one tile) any binning into this workspace saw — what a caller of
+ * mgs_track_args.tile_segments compares with MGS_TILE_SEGMENT.  The two sticky words are only ever raised by the kernels: a loop that renders many views into one workspace
  * (mgs_track_iteration, mgs_map_view_*) polls them once in a while — no host wait inside the loop — and still learns
  * about ANY render that did not fit.  mgs_raster_status_reset clears the header (also required once before the first
  * use of a workspace whose sticky words are going to be read: the library never clears them itself). */
-int mgs_raster_status_async(const void* workspace, int32_t* status_out /* i32[6] */, void* stream);
+int mgs_raster_status_async(const void* workspace, int32_t* status_out /* i32[8] */, void* stream);
 int mgs_raster_status_reset(void* workspace, void* stream);
 
 /* ---- rasterizer backward: replaces _C.rasterize_gaussians_backward (ext.cpp:47,
@@ -313,7 +315,18 @@ typedef struct mgs_track_args {
    * i.e. of the previous iteration — an overflow watch that costs one 24-byte copy node and no host wait. */
   float* lm_state;
   int32_t* status_out;
+  /* tile_segments = 1 (sh_degree 0 only): fixed-segment binning.  Every tile owns MGS_TILE_SEGMENT instance slots of the
+   * workspace; the preprocess kernel scatters each (Gaussian, tile) instance into its tile's segment as it counts it, one
+   * kernel sorts the segments, and the iteration is FOUR kernels (preprocess, tile_sort_segments, blend_track, track_update)
+   * instead of seven — no tile scan and no emit pass between counting and sorting (the reference's duplicateWithKeys +
+   * SortPairs + identifyTileRanges, rasterizer_impl.cu:288-321, as one scatter + one in-place sort).  Needs
+   * R_cap >= tiles * MGS_TILE_SEGMENT.  Results are those of tile_segments = 0 as long as no tile holds more than
+   * MGS_TILE_SEGMENT instances; a longer list loses its excess and raises the status words `overflow` / `overflow_sticky`
+   * (mgs_raster_status_async), on which the caller falls back to tile_segments = 0. */
+  int32_t tile_segments;
+  int32_t reserved0;
 } mgs_track_args;
+#define MGS_TILE_SEGMENT 1024
 size_t mgs_track_scratch_bytes(int32_t P, int32_t W, int32_t H);
 int mgs_track_iteration(const mgs_track_args* args, void* stream);
 

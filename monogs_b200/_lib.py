@@ -60,6 +60,7 @@ class MgsTrackArgs(C.Structure):
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("R_cap", C.c_int64),
         ("scratch", C.c_void_p), ("scratch_bytes", C.c_size_t),
         ("lm_state", C.c_void_p), ("status_out", C.c_void_p),
+        ("tile_segments", C.c_int32), ("reserved0", C.c_int32),
     ]
 
 

@@ -123,7 +123,7 @@ int mgs_raster_query(const void* workspace, int32_t* num_rendered, int32_t* over
 
 int mgs_raster_status_async(const void* workspace, int32_t* status_out, void* stream) {
   if (!workspace || !status_out) { set_error("raster_status: null argument"); return MGS_EINVAL; }
-  MGS_CUDA_TRY(cudaMemcpyAsync(status_out, workspace, 6 * sizeof(uint32_t), cudaMemcpyDefault, (cudaStream_t)stream));
+  MGS_CUDA_TRY(cudaMemcpyAsync(status_out, workspace, 8 * sizeof(uint32_t), cudaMemcpyDefault, (cudaStream_t)stream));
   return MGS_OK;
 }
 

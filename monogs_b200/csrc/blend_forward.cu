@@ -33,6 +33,7 @@ blend_forward_kernel(const int W, const int H, const int gx, const uint32_t* __r
   __shared__ __align__(128) SplatRec stage[FWD_STAGES][FWD_BATCH];
   __shared__ __align__(8) uint64_t full_bar[FWD_STAGES];
 
+  pdl_enter<PDL_FWD>();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   // tile_order != null: longest tile lists first (tile_scan_body, heavy_first) — the grid of a single view is ~1.4 waves,
   // and the partial last wave then holds the SHORTEST lists instead of whatever the raster order left for it
@@ -150,22 +151,24 @@ int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float*
                          float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl, bool heavy_first) {
   const int tiles = v.gx * v.gy;
   const uint32_t* order = heavy_first ? ws_ptr<uint32_t>(ws, L.tile_ctr) : nullptr;
+  cudaError_t e;
   prof_begin("blend_forward", s);
   if (fl == nullptr) {
     LossK none{};
-    blend_forward_kernel<false, false, true><<<tiles, FWD_THREADS, 0, s>>>(
+    e = launch_chain(blend_forward_kernel<false, false, true>, tiles, FWD_THREADS, 0, s,
         v.W, v.H, v.gx, order, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
         ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, none, 0.f, nullptr, nullptr, nullptr);
   } else {
 #define MGS_FWD_ARGS v.W, v.H, v.gx, order, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg,           \
         ws_ptr<float>(ws, L.final_T), ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, \
         *fl->k, fl->grad_scale, fl->g_img, fl->g_depth, fl->partials
-    if (fl->fast && n_touched == nullptr) blend_forward_kernel<true, true, false><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
-    else if (fl->fast) blend_forward_kernel<true, true, true><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
-    else blend_forward_kernel<true, false, true><<<tiles, FWD_THREADS, 0, s>>>(MGS_FWD_ARGS);
+    if (fl->fast && n_touched == nullptr) e = launch_chain(blend_forward_kernel<true, true, false>, tiles, FWD_THREADS, 0, s, MGS_FWD_ARGS);
+    else if (fl->fast) e = launch_chain(blend_forward_kernel<true, true, true>, tiles, FWD_THREADS, 0, s, MGS_FWD_ARGS);
+    else e = launch_chain(blend_forward_kernel<true, false, true>, tiles, FWD_THREADS, 0, s, MGS_FWD_ARGS);
 #undef MGS_FWD_ARGS
   }
   prof_end(s);
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

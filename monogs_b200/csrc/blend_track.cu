@@ -87,7 +87,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
                    int32_t* __restrict__ n_touched, const LossK lk, const float loss_grad_scale,
                    double* __restrict__ loss_partials, float* __restrict__ tau_sum,
                    const float* __restrict__ sk_weights, const float sk_scale, float* __restrict__ sk_image,
-                   const TrackTail tail) {
+                   const TrackTail tail, uint32_t* __restrict__ clear_ctr) {
   constexpr bool SKETCH = EPI == 1, DEFER = EPI == 2;
   constexpr int TRK_BATCH = TrkCfg<NW>::kBatch, THREADS = NW * 32;
   extern __shared__ __align__(128) unsigned char trk_smem[];
@@ -98,6 +98,7 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
   __shared__ float s_part[NW][6];
   __shared__ int s_last;
 
+  pdl_enter<PDL_TRK>();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int tile = (int)tile_order[(size_t)blockIdx.x * TILE_CTR_STRIDE + 3];   // heavy tiles first (tile_scan_body)
   const int tx = tile % gx, ty = tile / gx;
@@ -112,6 +113,9 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
   const int n = (int)(range.y - range.x);
   const int rounds = (n + TRK_BATCH - 1) / TRK_BATCH;
   const SplatRec* src = recs + range.x;
+  // fixed-segment binning: the tile's instance counter is dead once its range has been read, and this grid visits every
+  // tile exactly once, so it leaves the counters zero for the next iteration's preprocess (tile_sort_segments_kernel)
+  if (clear_ctr != nullptr && tid == 0) clear_ctr[(size_t)tile * TILE_CTR_STRIDE] = 0u;
 
   bool done = !inside;
   float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f;
@@ -385,7 +389,7 @@ static int launch_trk_t(int tiles, cudaStream_t s, const int W, const int H, con
                         const uint2* ranges, const SplatRec* recs, const float* jac, const float* bg, float* out_color,
                         float* out_depth, float* out_opacity, int32_t* n_touched, const LossK& lk, float grad_scale,
                         double* partials, float* tau_sum, const float* sk_weights, float sk_scale, float* sk_image,
-                        const TrackTail& tail) {
+                        const TrackTail& tail, uint32_t* clear_ctr) {
   // the opt-in to > 48 KB of dynamic shared memory is a per-device function attribute
   static bool attr_set[64] = {};
   int dev = 0;
@@ -396,9 +400,9 @@ static int launch_trk_t(int tiles, cudaStream_t s, const int W, const int H, con
     MGS_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(ROWS ? TrkCfg<NW>::kSmemRows : TrkCfg<NW>::kSmem)));
     attr_set[dev] = true;
   }
-  kern<<<tiles, NW * 32, ROWS ? TrkCfg<NW>::kSmemRows : TrkCfg<NW>::kSmem, s>>>(W, H, gx, tile_order, ranges, recs, jac, bg, out_color, out_depth,
-                                                                     out_opacity, n_touched, lk, grad_scale, partials, tau_sum,
-                                                                     sk_weights, sk_scale, sk_image, tail);
+  MGS_CUDA_TRY(launch_chain(kern, tiles, NW * 32, ROWS ? TrkCfg<NW>::kSmemRows : TrkCfg<NW>::kSmem, s, W, H, gx, tile_order, ranges, recs, jac, bg,
+                            out_color, out_depth, out_opacity, n_touched, lk, grad_scale, partials, tau_sum, sk_weights, sk_scale,
+                            sk_image, tail, clear_ctr));
   return MGS_OK;
 }
 
@@ -456,7 +460,7 @@ size_t pose_deferred_bytes(int W, int H) { return (size_t)EA_PLANES * W * H * si
 int launch_pose_contract(const float* ea, int W, int H, const float* g_color, const float* g_depth, float* tau_image,
                          float* tau_sum, cudaStream_t s) {
   const int npix = W * H;
-  if (tau_sum) MGS_CUDA_TRY(cudaMemsetAsync(tau_sum, 0, 6 * sizeof(float), s));
+  if (tau_sum) MGS_CUDA_TRY(memset_async(tau_sum, 0, 6 * sizeof(float), s));
   MGS_PROF("pose_contract", s, pose_contract_kernel<<<(npix + 255) / 256, 256, 0, s>>>(ea, npix, g_color, g_depth, tau_image, tau_sum));
   MGS_LAUNCH_CHECK();
   return MGS_OK;
@@ -470,8 +474,9 @@ int blend_track_warps() { return 8; }
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s, const float* sk_weights, float sk_scale, float* sk_image,
-                       const TrackUpdateK* upd, uint32_t* ticket, bool deferred, bool rows) {
+                       const TrackUpdateK* upd, uint32_t* ticket, bool deferred, bool rows, bool clear_counts) {
   const int tiles = v.gx * v.gy;
+  if (clear_counts && !rows) { set_error("blend_track: clear_counts belongs to the fixed-segment (packed-row) mode"); return MGS_EINVAL; }
   if (rows && (deferred || upd != nullptr)) { set_error("blend_track: the packed-row staging serves the fused tracker's un-folded kernels only"); return MGS_EINVAL; }
   if (deferred) {
     // drop-in forward: exact exponent (n_touched produced), depth accumulators always (the loss is not known yet)
@@ -483,7 +488,7 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
     prof_begin("blend_track_deferred", s);
       rc0 = launch_trk_t<true, false, 2, 8, false>(tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges),
                                                   ws_ptr<SplatRec>(ws, L.records), jac, v.bg, out_color, out_depth, out_opacity, n_touched,
-                                                  lk0, 0.f, nullptr, nullptr, nullptr, 0.f, sk_image, none);
+                                                  lk0, 0.f, nullptr, nullptr, nullptr, 0.f, sk_image, none, nullptr);
     prof_end(s);
     if (rc0) return rc0;
     MGS_LAUNCH_CHECK();
@@ -495,7 +500,8 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
   memset(&tail, 0, sizeof(tail));
   if (upd) { tail.k = *upd; tail.ticket = ticket; }
 #define MGS_TRK_ARGS tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), \
-      jac, v.bg, out_color, out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum, sk_weights, sk_scale, sk_image, tail
+      jac, v.bg, out_color, out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum, sk_weights, sk_scale, sk_image, tail, \
+      (clear_counts ? ws_ptr<uint32_t>(ws, L.tile_ctr) : (uint32_t*)nullptr)
 #define MGS_TRK_DISPATCH(HD, SK, FO)                                                                                                   \
   do {                                                                                                                                 \
     rc = fl.fast ? launch_trk_t<HD, true, SK, 8, FO>(MGS_TRK_ARGS) : launch_trk_t<HD, false, SK, 8, FO>(MGS_TRK_ARGS);            \

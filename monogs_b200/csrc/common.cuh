@@ -55,7 +55,8 @@ struct WsHeader {
   uint32_t overflow_sticky;   // 1 once any binning into this workspace saw num_rendered > R_cap
   uint32_t max_rendered;      // largest num_rendered any binning into this workspace saw
   uint32_t ticket;            // CTA ticket of the folded scan (preprocess_kernel<.., FOLD_SCAN>); zero between launches
-  uint32_t pad[57];
+  uint32_t max_tile_count;    // sticky: longest tile list (instances of one tile) any binning into this workspace saw
+  uint32_t pad[56];
 };
 static_assert(sizeof(WsHeader) == 256, "header is one 256-B slot");
 
@@ -245,6 +246,57 @@ inline ViewConst make_view_const(const mgs_view* v) {
   c.bg = v->bg; c.view = v->viewmatrix; c.proj = v->projmatrix; c.proj_raw = v->projmatrix_raw;
   c.campos = v->campos;
   return c;
+}
+
+// ---- programmatic dependent launch (PDL) along the fixed kernel chains of the fused entry points -----------------------
+// A tracking iteration is seven dependent kernels of 7-200 us, a mapping view eleven: the drain + launch latency between
+// two of them is a measurable share.  Every kernel of those chains starts with pdl_enter(): it lets the NEXT kernel of
+// the stream be scheduled as soon as all CTAs of this one have started (griddepcontrol.launch_dependents), then blocks
+// until the PREVIOUS kernel has completed and its writes are visible (griddepcontrol.wait) — the dependency itself is the
+// full stream-order one, only the launch latency of the successor is hidden behind the predecessor.  Both instructions
+// are no-ops in a kernel that was launched without the attribute.  Completion is transitive: kernel k+1 completes only
+// after its CTAs passed their wait, i.e. after kernel k completed, so a wait on k+1 also orders everything before it.
+// Host side: a fused entry point opens a PdlScope; launch_chain() adds the attribute when the previous operation the
+// scope put on the stream was one of its own kernels (state 2) and launches normally otherwise (first kernel, or after
+// a memset / copy, which call pdl_break() through the wrappers below).  launch_chain() must only ever launch kernels
+// that begin with pdl_enter().  MGS_PDL=0 switches the attribute off (A/B measurements); the event profiler does too.
+// MGS_PDL_MASK: which kernels release their successor at their START (bits below); the others release it when they exit.
+// Measured on the B200 (profiles/r02_notes.txt item 14): releasing early pays only where the successor is small or the
+// stream is alone on the GPU — CTAs of a large successor that sit in their wait hold registers and shared memory that the
+// mapping engine's other streams need (all bits set: mapping window of 8 views 441 -> 371 it/s).
+#ifndef MGS_PDL_MASK
+#define MGS_PDL_MASK (PDL_PRE | PDL_SCAN | PDL_EMIT | PDL_TRK)
+#endif
+enum : int { PDL_PRE = 1, PDL_SCAN = 2, PDL_EMIT = 4, PDL_SORT = 8, PDL_SORTL = 16, PDL_TRK = 32, PDL_UPD = 64, PDL_FWD = 128,
+             PDL_LOSSF = 256, PDL_BWD = 512, PDL_PBWD = 1024 };
+template <int BIT> __device__ __forceinline__ void pdl_enter() {
+  if (MGS_PDL_MASK & BIT) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+extern thread_local int g_pdl;      // 0: no scope; 1: in a scope, the last operation was not a chained kernel; 2: it was
+bool pdl_allowed();
+struct PdlScope {
+  bool outer;
+  PdlScope() : outer(g_pdl == 0) { if (outer) g_pdl = pdl_allowed() ? 1 : 0; }
+  ~PdlScope() { if (outer) g_pdl = 0; }
+};
+inline void pdl_break() { if (g_pdl == 2) g_pdl = 1; }
+inline cudaError_t memset_async(void* p, int value, size_t bytes, cudaStream_t s) { pdl_break(); return cudaMemsetAsync(p, value, bytes, s); }
+inline cudaError_t memcpy_async(void* dst, const void* src, size_t bytes, cudaMemcpyKind kind, cudaStream_t s) {
+  pdl_break();
+  return cudaMemcpyAsync(dst, src, bytes, kind, s);
+}
+template <typename... P, typename... A>
+inline cudaError_t launch_chain(void (*kern)(P...), const dim3 grid, const dim3 block, const size_t smem, cudaStream_t s, A&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at = {};
+  at.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at.val.programmaticStreamSerializationAllowed = 1;
+  if (g_pdl == 2) { cfg.attrs = &at; cfg.numAttrs = 1; }
+  const cudaError_t e = cudaLaunchKernelEx(&cfg, kern, static_cast<P>(args)...);
+  if (g_pdl == 1) g_pdl = 2;
+  return e;
 }
 
 // number of significant bits of the tile id (rasterizer_impl.cu:35-50)

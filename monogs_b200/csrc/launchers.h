@@ -10,7 +10,11 @@ const char* get_error();
 // in_kernel: run the scan in the last CTA of preprocess_kernel (true) or as its own one-CTA launch behind it (false).
 // Measured on the B200: the separate launch wins in the serial tracking iteration (+2 %), the folded tail wins in the mapping
 // engine, whose views overlap on several streams (+3 %); MGS_SCAN_FOLD=0|1 overrides both for measurements.
-struct FoldScan { int64_t R_cap; bool heavy_first; bool in_kernel; };
+// segment_cap != 0 (fused tracker, packed-row mode): fixed segments of that many instances per tile, scattered by the
+// preprocess kernel itself; no scan and no emit — launch_sort_segments() follows instead of launch_binning().
+struct FoldScan { int64_t R_cap; bool heavy_first; bool in_kernel; int segment_cap = 0; };
+constexpr int TILE_SEGMENT = 1024;      // instances per tile segment (= the longest list the one-CTA-per-tile sort takes)
+int launch_sort_segments(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s);
 int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
@@ -31,7 +35,8 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s, const float* sk_weights = nullptr, float sk_scale = 0.f,
                        float* sk_image = nullptr, const struct TrackUpdateK* upd = nullptr, uint32_t* ticket = nullptr,
-                       bool deferred = false, bool rows = false);   // rows: ids + packed per-Gaussian rows (fused tracker)
+                       bool deferred = false, bool rows = false,    // rows: ids + packed per-Gaussian rows (fused tracker)
+                       bool clear_counts = false);                  // fixed-segment binning: zero each tile's instance counter
 int blend_track_warps();      // 8 or 4: CTAs per tile = 8 / warps; loss partial slots = tiles * 8 / warps
 // deferred single pass of the drop-in surface: accumulator planes of blend_track<EPI = 2> and their contraction
 size_t pose_deferred_bytes(int W, int H);
@@ -53,6 +58,7 @@ struct BackwardArgs {
   // split SH layout (mapping engine): shs = f_dc [P,1,3], sh_rest = f_rest [P,M-1,3]; gradients go to dL_dcolors_or_sh
   // ([P,1,3]) and dL_dsh_rest ([P,M-1,3]).  Null = one array [P,M,3].
   const float* sh_rest = nullptr; float* dL_dsh_rest = nullptr;
+  bool pre_cleared = false;   // launch_backward_full: the caller has already zeroed the scratch accumulator and dL_dtau_sum on this stream
   bool fast = false;   // blend_backward_full only: exponent variant of the forward that produced ws (blend_exp<FAST>)
   bool heavy_first = false;   // blend_backward_full only: walk the tiles in the scan's heavy-first order (tile_ctr[.. + 3])
   const int32_t* pixel_mult = nullptr;   // blend_backward_full only: i32[H*W] multiplicity of each pixel in the selected-pixel
@@ -65,5 +71,6 @@ int launch_pixel_multiplicity(const int32_t* indices, int n, int npix, int32_t* 
 int launch_backward_full(const BackwardArgs& a, cudaStream_t s);
 int launch_blend_backward_pose(const BackwardArgs& a, const float* jac, bool with_color, cudaStream_t s, bool fast = false);
 size_t backward_scratch_bytes(int P, int sketch_dim);
+size_t backward_g2d_bytes();      // bytes per Gaussian of the accumulator launch_backward_full zero-fills at the head of its scratch
 
 }  // namespace mgs

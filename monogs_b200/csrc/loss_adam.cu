@@ -161,7 +161,7 @@ int mgs_loss_fwd_bwd(const mgs_loss_args* args, float* out_loss, float* out_dab,
     if (grads) {
       loss_kernel<true, false><<<nblocks, 256, 0, s>>>(k, out_loss, partials, dL_dimage, dL_ddepth);
       MGS_LAUNCH_CHECK();
-    } else MGS_CUDA_TRY(cudaMemsetAsync(partials, 0, (size_t)nblocks * 4 * sizeof(double), s));
+    } else MGS_CUDA_TRY(memset_async(partials, 0, (size_t)nblocks * 4 * sizeof(double), s));
     loss_finalize_kernel<<<1, 256, 0, s>>>(k, partials, nblocks, 1, out_loss, out_dab);
     MGS_LAUNCH_CHECK();
   } else {

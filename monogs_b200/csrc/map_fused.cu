@@ -81,6 +81,7 @@ map_loss_finalize_kernel(const double* __restrict__ partials, const int tiles, c
                          const float alpha, float* __restrict__ loss_view, float* __restrict__ loss_total,
                          float* __restrict__ dab) {
   __shared__ double sh[256][4];
+  pdl_enter<PDL_LOSSF>();
   double acc[4] = {0, 0, 0, 0};
   for (int i = threadIdx.x; i < tiles; i += 256)
 #pragma unroll
@@ -231,13 +232,13 @@ int mgs_map_begin(const mgs_map_args* a, void* stream) {
   // sizes of the image-dependent tail do not matter here: only the per-Gaussian head is touched
   const MapScratch m = carve_map_scratch(a->scratch, P, a->g.sh_coeffs, 16, 16);
   if (a->scratch_bytes < m.total) { set_error("map: scratch too small"); return MGS_ENOSPC; }
-  if (P == 0) { MGS_CUDA_TRY(cudaMemsetAsync(a->loss_total, 0, sizeof(float), s)); return MGS_OK; }
+  if (P == 0) { MGS_CUDA_TRY(memset_async(a->loss_total, 0, sizeof(float), s)); return MGS_OK; }
   MGS_PROF("map_activate", s, map_activate_kernel<<<(P + 255) / 256, 256, 0, s>>>(a->g, m, a->grad_xyz, a->grad_f_dc, a->loss_total));
   MGS_LAUNCH_CHECK();
   const int M = a->g.sh_coeffs;
   if (M > 1) {   // SH gradients accumulate straight into the raw-parameter gradients (features have no activation)
-    MGS_CUDA_TRY(cudaMemsetAsync(a->grad_f_dc, 0, (size_t)P * 3 * sizeof(float), s));
-    MGS_CUDA_TRY(cudaMemsetAsync(a->grad_f_rest, 0, (size_t)P * (M - 1) * 3 * sizeof(float), s));
+    MGS_CUDA_TRY(memset_async(a->grad_f_dc, 0, (size_t)P * 3 * sizeof(float), s));
+    MGS_CUDA_TRY(memset_async(a->grad_f_rest, 0, (size_t)P * (M - 1) * 3 * sizeof(float), s));
   }
   return MGS_OK;
 }
@@ -283,15 +284,17 @@ int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* st
   if (rc) return rc;
   if (c.P == 0) return MGS_OK;
   cudaStream_t s = (cudaStream_t)stream;
+  PdlScope pdl_scope;    // preprocess .. loss finalize chained by programmatic dependent launch (common.cuh)
   const mgs_gaussians& g = a->g;
   const MapScratch& m = c.m;
   void* ws = mv->workspace;
+  // n_touched is written by the forward blend only: cleared ahead of the chain so that no memset sits between its kernels
+  MGS_CUDA_TRY(memset_async(mv->n_touched, 0, (size_t)c.P * sizeof(int32_t), s));
   // the workspace of a mapping engine is zero-filled once by its owner: the scan runs in the last CTA of the preprocess
   // kernel and the sort kernel leaves the tile counters zero for the next view (raster_forward.cu, FoldScan)
   const FoldScan fs{mv->R_cap, /*heavy_first=*/true, /*in_kernel=*/true};
   if ((rc = launch_preprocess(c.v, c.P, g.xyz, m.act_opacity, c.shs, nullptr, m.act_scales, m.act_rot, nullptr, mv->radii, ws, c.L, s,
                               nullptr, 0, c.M > 1 ? g.f_rest : nullptr, &fs))) return rc;
-  MGS_CUDA_TRY(cudaMemsetAsync(mv->n_touched, 0, (size_t)c.P * sizeof(int32_t), s));
   if ((rc = launch_binning(c.v, c.P, nullptr, mv->radii, ws, c.L, mv->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
 
   LossK lk;
@@ -303,17 +306,20 @@ int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* st
   fl.k = &lk; fl.grad_scale = (c.use_depth ? mv->alpha : 1.f) / (3.f * (float)c.npix);
   fl.g_img = m.g_img[c.slot]; fl.g_depth = m.g_depth[c.slot]; fl.partials = m.partials[c.slot]; fl.fast = mv->fast_math != 0;
   if ((rc = launch_blend_forward(c.v, ws, c.L, mv->out_color, mv->out_depth, mv->out_opacity, mv->n_touched, s, &fl, /*heavy_first=*/true))) return rc;
-  MGS_PROF("map_loss_finalize", s, map_loss_finalize_kernel<<<1, 256, 0, s>>>(m.partials[c.slot], c.tiles, (int)c.npix, c.use_depth, mv->alpha,
-                                                                             mv->loss, a->loss_total, mv->dab));
+  cudaError_t e;
+  MGS_PROF("map_loss_finalize", s, e = launch_chain(map_loss_finalize_kernel, 1, 256, 0, s, m.partials[c.slot], c.tiles, (int)c.npix, c.use_depth,
+                                                    mv->alpha, mv->loss, a->loss_total, mv->dab));
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }
 
-int mgs_map_view_backward(const mgs_map_args* a, const mgs_map_view* mv, void* stream) {
+static int map_view_backward(const mgs_map_args* a, const mgs_map_view* mv, void* stream, bool pre_cleared) {
   MapViewCtx c;
   int rc = map_view_ctx(a, mv, &c);
   if (rc) return rc;
   if (c.P == 0) return MGS_OK;
+  PdlScope pdl_scope;
   const mgs_gaussians& g = a->g;
   const MapScratch& m = c.m;
   BackwardArgs b;
@@ -330,12 +336,26 @@ int mgs_map_view_backward(const mgs_map_args* a, const mgs_map_view* mv, void* s
   if (mv->update_stats) { b.stat_grad_accum = a->xyz_gradient_accum; b.stat_denom = a->denom; b.stat_max_radii = a->max_radii2D; }
   b.fast = mv->fast_math != 0;
   b.heavy_first = true;     // the order the view's scan left in its workspace
+  b.pre_cleared = pre_cleared;
   return launch_backward_full(b, (cudaStream_t)stream);
 }
 
+int mgs_map_view_backward(const mgs_map_args* a, const mgs_map_view* mv, void* stream) { return map_view_backward(a, mv, stream, false); }
+
+// Forward and backward of one view back to back on one stream (a rank that owns a single view of the window: the whole
+// iteration is this dependent chain).  The backward's accumulators are cleared AHEAD of the forward, so the view is eight
+// kernels with nothing between them, chained by programmatic dependent launch.
 int mgs_map_view_fwd_bwd(const mgs_map_args* a, const mgs_map_view* mv, void* stream) {
-  const int rc = mgs_map_view_forward(a, mv, stream);
-  return rc ? rc : mgs_map_view_backward(a, mv, stream);
+  MapViewCtx c;
+  int rc = map_view_ctx(a, mv, &c);
+  if (rc) return rc;
+  if (c.P == 0) return MGS_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  PdlScope pdl_scope;
+  MGS_CUDA_TRY(memset_async(c.m.bwd[c.slot], 0, (size_t)c.P * backward_g2d_bytes(), s));
+  if (mv->tau) MGS_CUDA_TRY(memset_async(mv->tau, 0, 6 * sizeof(float), s));
+  rc = mgs_map_view_forward(a, mv, stream);
+  return rc ? rc : map_view_backward(a, mv, stream, true);
 }
 
 int mgs_window_pose_step(const mgs_pose_slot* slots, int32_t n, const float* proj_raw, float beta1, float beta2, float eps,

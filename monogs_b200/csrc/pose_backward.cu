@@ -252,7 +252,7 @@ int launch_backward_pose(const BackwardArgs& a, cudaStream_t s) {
   const size_t need = backward_pose_scratch_bytes(P, v.W, v.H);
   if (a.scratch == nullptr || a.scratch_bytes < need) { set_error("pose backward scratch too small: %zu < %zu", a.scratch_bytes, need); return MGS_ENOSPC; }
   float* jac = reinterpret_cast<float*>(a.scratch);
-  if (a.dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
+  if (a.dL_dtau_sum) MGS_CUDA_TRY(memset_async(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
   const bool with_color = (a.shs != nullptr && v.D > 0);
   prof_begin("pose_jacobian", s);
   if (with_color)
@@ -268,7 +268,7 @@ int launch_backward_pose(const BackwardArgs& a, cudaStream_t s) {
 
 int launch_sketch_reduce(const float* rows, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,
                          float* out, cudaStream_t s, int nv) {
-  MGS_CUDA_TRY(cudaMemsetAsync(out, 0, (size_t)n_stacks * d * nv * sizeof(float), s));
+  MGS_CUDA_TRY(memset_async(out, 0, (size_t)n_stacks * d * nv * sizeof(float), s));
   const int npix = W * H;
   // every CTA ends with d * nv global atomics, so the grid stays small: ~4 CTAs per SM over all stacks
   const int per_stack = max(1, min((npix + 255) / 256, (148 * 4 + n_stacks - 1) / n_stacks));

@@ -89,6 +89,7 @@ blend_backward_full_kernel(const int W, const int H, const int gx, const uint32_
   __shared__ __align__(8) uint64_t full_bar[2];
   __shared__ int s_max_contrib;
 
+  pdl_enter<PDL_BWD>();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int tile = tile_order != nullptr ? (int)tile_order[(size_t)blockIdx.x * TILE_CTR_STRIDE + 3] : (int)blockIdx.x;   // heavy first
   const int tx = tile % gx, ty = tile / gx;
@@ -276,6 +277,7 @@ preprocess_backward_kernel(const ViewConst v, const int P, const uint32_t mask,
                            const int accumulate, float* __restrict__ stat_grad_accum, float* __restrict__ stat_denom,
                            float* __restrict__ stat_max_radii) {
   extern __shared__ __align__(16) float sh_tile[];
+  pdl_enter<PDL_PBWD>();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
   const int RS = sh_row_stride(v.M);
@@ -423,7 +425,7 @@ __global__ void __launch_bounds__(256) pixel_multiplicity_kernel(const int32_t* 
 }
 
 int launch_pixel_multiplicity(const int32_t* indices, int n, int npix, int32_t* mult, cudaStream_t s) {
-  MGS_CUDA_TRY(cudaMemsetAsync(mult, 0, (size_t)npix * sizeof(int32_t), s));
+  MGS_CUDA_TRY(memset_async(mult, 0, (size_t)npix * sizeof(int32_t), s));
   if (n > 0) {
     MGS_PROF("pixel_multiplicity", s, pixel_multiplicity_kernel<<<(n + 255) / 256, 256, 0, s>>>(indices, n, npix, mult));
     MGS_LAUNCH_CHECK();
@@ -431,24 +433,30 @@ int launch_pixel_multiplicity(const int32_t* indices, int n, int npix, int32_t* 
   return MGS_OK;
 }
 
+size_t backward_g2d_bytes() { return sizeof(G2DGrad); }
+
 int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   const ViewConst& v = a.v;
   const int P = a.P;
   const size_t need = backward_scratch_bytes(P, 0);
   if (a.scratch == nullptr || a.scratch_bytes < need) { set_error("backward scratch too small: %zu < %zu", a.scratch_bytes, need); return MGS_ENOSPC; }
   G2DGrad* g2d = reinterpret_cast<G2DGrad*>(a.scratch);
-  MGS_CUDA_TRY(cudaMemsetAsync(g2d, 0, (size_t)P * sizeof(G2DGrad), s));
-  if (a.dL_dtau_sum) MGS_CUDA_TRY(cudaMemsetAsync(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
+  if (!a.pre_cleared) {   // (mgs_map_view_fwd_bwd clears both ahead of the view's forward, so that no memset sits between the kernels)
+    MGS_CUDA_TRY(memset_async(g2d, 0, (size_t)P * sizeof(G2DGrad), s));
+    if (a.dL_dtau_sum) MGS_CUDA_TRY(memset_async(a.dL_dtau_sum, 0, 6 * sizeof(float), s));
+  }
   const int tiles = v.gx * v.gy;
+  cudaError_t e;
   prof_begin("blend_backward_full", s);
   const uint32_t* order = a.heavy_first ? ws_ptr<uint32_t>(a.ws, a.L.tile_ctr) : nullptr;
 #define MGS_BWD_ARGS v.W, v.H, v.gx, order, ws_ptr<uint2>(a.ws, a.L.ranges), ws_ptr<SplatRec>(a.ws, a.L.records), v.bg,   \
       ws_ptr<float>(a.ws, a.L.final_T), ws_ptr<uint32_t>(a.ws, a.L.n_contrib), a.dL_dcolor_img, a.dL_ddepth_img,        \
       a.pixel_mult, g2d
-  if (a.fast) blend_backward_full_kernel<true><<<tiles, BWD_THREADS, 0, s>>>(MGS_BWD_ARGS);
-  else blend_backward_full_kernel<false><<<tiles, BWD_THREADS, 0, s>>>(MGS_BWD_ARGS);
+  if (a.fast) e = launch_chain(blend_backward_full_kernel<true>, tiles, BWD_THREADS, 0, s, MGS_BWD_ARGS);
+  else e = launch_chain(blend_backward_full_kernel<false>, tiles, BWD_THREADS, 0, s, MGS_BWD_ARGS);
 #undef MGS_BWD_ARGS
   prof_end(s);
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   prof_begin("preprocess_backward", s);
 #define MGS_PB_ARGS v, P, a.grad_mask, a.means3D, a.shs, a.sh_rest, a.dL_dsh_rest, a.colors_precomp, a.scales, a.rotations,        \
@@ -461,10 +469,11 @@ int launch_backward_full(const BackwardArgs& a, cudaStream_t s) {
   }
   if (stage) {
     const int T = 128;
-    preprocess_backward_kernel<true><<<(P + T - 1) / T, T, (size_t)T * sh_row_stride(v.M) * sizeof(float), s>>>(MGS_PB_ARGS);
-  } else preprocess_backward_kernel<false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PB_ARGS);
+    e = launch_chain(preprocess_backward_kernel<true>, (P + T - 1) / T, T, (size_t)T * sh_row_stride(v.M) * sizeof(float), s, MGS_PB_ARGS);
+  } else e = launch_chain(preprocess_backward_kernel<false>, (P + 255) / 256, 256, 0, s, MGS_PB_ARGS);
 #undef MGS_PB_ARGS
   prof_end(s);
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

@@ -36,6 +36,11 @@ void prof_end(cudaStream_t s) {
   cudaEventRecord(g_cur.e1, s);
   g_prof.push_back(g_cur);
 }
+thread_local int g_pdl = 0;
+bool pdl_allowed() {
+  static const bool env_on = [] { const char* e = getenv("MGS_PDL"); return !(e && e[0] == '0'); }();
+  return env_on && !g_prof_on;    // the profiler's event records sit between the kernels: nothing to chain
+}
 void prof_enable(bool on) {
   for (auto& r : g_prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
   g_prof.clear();
@@ -362,6 +367,7 @@ __device__ __noinline__ void tile_scan_body(uint32_t* __restrict__ tile_ctr, con
     hdr->n_large = n_large;
     if (carry > R_cap) hdr->overflow_sticky = 1u;
     if (carry > hdr->max_rendered) hdr->max_rendered = carry;
+    if (max_count > hdr->max_tile_count) hdr->max_tile_count = max_count;
   }
   // Heavy-first launch order for per-tile kernels that run in several waves (blend_track_kernel: 3 CTAs per SM): a
   // counting sort of the tiles into 64 buckets of list length, longest lists first, written to
@@ -414,6 +420,7 @@ __device__ __noinline__ void tile_scan_body(uint32_t* __restrict__ tile_ctr, con
 __global__ void __launch_bounds__(SCAN_THREADS)
 tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_t R_cap,
                  uint2* __restrict__ ranges, WsHeader* __restrict__ hdr, const int heavy_first) {
+  pdl_enter<PDL_SCAN>();
   tile_scan_body<SCAN_THREADS>(tile_ctr, tiles, R_cap, ranges, hdr, heavy_first);
 }
 
@@ -426,7 +433,11 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
 #ifndef MGS_PRE_BASIS_MIN_CTAS
 #define MGS_PRE_BASIS_MIN_CTAS 3
 #endif
-template <int JAC_NCOL, bool STAGE, bool FOLD_SCAN>
+// SEGMENTS (fused tracker, packed-row mode): the counting sort's scatter happens HERE — every tile owns a fixed segment of
+// `seg_cap` words of `list`, and an instance takes slot = atomicAdd(tile counter) of its tile at once, so there is no scan
+// between counting and scattering and no emit pass at all (tile_sort_segments_kernel sorts the segments in place of
+// tile_scan + emit + tile_sort_records x 2).  Instances beyond seg_cap are dropped; the count still says so (overflow).
+template <int JAC_NCOL, bool STAGE, bool FOLD_SCAN, bool SEGMENTS = false>
 __global__ void __launch_bounds__(256, (JAC_NCOL == 0 && !STAGE) ? 5 : (((JAC_NCOL == 32 || JAC_NCOL == TRACK_ROW_FLOATS) && !STAGE) ? MGS_PRE_BASIS_MIN_CTAS : 0))   // plain: 48 registers, 5 CTAs per SM; pose basis: 80, 3 CTAs
 preprocess_kernel(const ViewConst v, const int P,
                   const float* __restrict__ means3D, const float* __restrict__ opacities,
@@ -437,8 +448,9 @@ preprocess_kernel(const ViewConst v, const int P,
                   float4* __restrict__ conic_opacity, float4* __restrict__ rgb4,
                   uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ tile_ctr,
                   float* __restrict__ jac, const uint32_t R_cap, uint2* __restrict__ ranges, WsHeader* __restrict__ hdr,
-                  const int heavy_first) {
+                  const int heavy_first, unsigned long long* __restrict__ list, const uint32_t seg_cap) {
   extern __shared__ __align__(16) float sh_tile[];
+  pdl_enter<PDL_PRE>();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   int my_radius_i = 0;
   uint32_t touched = 0;
@@ -532,8 +544,10 @@ preprocess_kernel(const ViewConst v, const int P,
       row[2] = make_float4(col.x, col.y, col.z, __uint_as_float(splat_extent(conic.x, conic.y, conic.z, op)));
     }
     else if (JAC_NCOL > 0) build_pose_jac<(JAC_NCOL == 9 ? 9 : 6)>(v, idx, p, shs, scales, rotations, cov3D_precomp, cm, jac);
-    depths[idx] = view_z;
-    means2D[idx] = pix;
+    if (!SEGMENTS) {   // (segment mode: emit_kernel, their only reader on the fused tracking path, does not run)
+      depths[idx] = view_z;
+      means2D[idx] = pix;
+    }
     if (JAC_NCOL != TRACK_ROW_FLOATS) conic_opacity[idx] = make_float4(conic.x, conic.y, conic.z, opacities[idx]);
     my_radius_i = (int)my_radius;
     touched = area;
@@ -541,7 +555,7 @@ preprocess_kernel(const ViewConst v, const int P,
   }
   if (idx < P) {
     radii[idx] = my_radius_i;
-    tiles_touched[idx] = touched;
+    if (!SEGMENTS) tiles_touched[idx] = touched;
   }
   if constexpr (JAC_NCOL == TRACK_ROW_FLOATS) {
     __shared__ uint32_t s_alive[8];
@@ -556,6 +570,21 @@ preprocess_kernel(const ViewConst v, const int P,
       const int e = q * 256 + (int)threadIdx.x, r = e / RC;
       if ((s_alive[r >> 5] >> (r & 31)) & 1u) dst4[e] = src4[e];
     }
+  }
+  if constexpr (SEGMENTS) {
+    // count AND scatter: (depth bits << 32 | id) straight into the tile's fixed segment, warp-cooperative walk of the 32
+    // rects with four returning atomics per lane in flight (the walk of emit_kernel)
+    const unsigned long long word = alive ? (((unsigned long long)__float_as_uint(view_z) << 32) | (uint32_t)idx) : 0ull;
+    for_each_tile_coop<4>(rmin, rmax, v.gx, word, [&](const uint32_t (&tile)[4], const bool (&ok)[4], const unsigned long long (&w)[4]) {
+      uint32_t slot[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (ok[u]) slot[u] = atomicAdd(&tile_ctr[tile[u] * TILE_CTR_STRIDE], 1u);
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (ok[u] && slot[u] < seg_cap) list[(size_t)tile[u] * seg_cap + slot[u]] = w[u];
+    });
+    return;
   }
   // instances per tile (the histogram of the counting sort that replaces the reference's global key sort)
   for_each_tile(rmin, rmax, v.gx, 0ull, [&](const uint32_t (&tile)[4], int cnt, unsigned long long) {
@@ -588,6 +617,7 @@ __global__ void __launch_bounds__(256)
 emit_kernel(const int P, const uint32_t R_cap, const int gx, const int gy,
             const float2* __restrict__ means2D, const float* __restrict__ depths, const int32_t* __restrict__ radii,
             uint32_t* __restrict__ tile_ctr, unsigned long long* __restrict__ list) {
+  pdl_enter<PDL_EMIT>();
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   uint2 rmin = {0u, 0u}, rmax = {0u, 0u};
   unsigned long long word = 0ull;
@@ -687,6 +717,7 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
   constexpr int ST = LARGE ? 256 : MGS_SORT_THREADS, SI = 1024 / MGS_SORT_THREADS;   // SI words per thread cover LARGE_LIST
   using Temp = typename cub::BlockMergeSort<unsigned long long, ST, LARGE ? 16 : SI>::TempStorage;
   __shared__ Temp temp;
+  pdl_enter<LARGE ? PDL_SORTL : PDL_SORT>();
   if (!LARGE) {
     // fused loops (tracker, mapping engine) render into the same workspace again and again: the tile's instance counter
     // is dead once the scan has run, so this CTA leaves it zero for the next preprocess instead of a memset per render
@@ -736,10 +767,100 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
   }
 }
 
+// Fixed-segment binning of the fused tracker (preprocess_kernel<.., SEGMENTS>): tile t's instances sit unsorted in
+// list[t * cap .. t * cap + min(count, cap)).  CTA b >= 1 sorts the segment of tile b - 1 and writes the sorted Gaussian ids
+// (u32) at the same offsets of the record region; CTA 0 meanwhile does what is left of the scan: ranges, the status header
+// and the heavy-first launch order of the blend kernel (tile_ctr[i * TILE_CTR_STRIDE + 3]) — no prefix sum, the segment
+// starts are a multiplication.  The tile counters are NOT cleared here (CTA 0 reads all of them while the others run); the
+// blend kernel, which visits every tile exactly once, leaves them zero for the next iteration.
+__global__ void __launch_bounds__(MGS_SORT_THREADS)
+tile_sort_segments_kernel(const int tiles, const uint32_t cap, const unsigned long long* __restrict__ list,
+                          uint32_t* __restrict__ ids, uint32_t* __restrict__ tile_ctr, uint2* __restrict__ ranges,
+                          WsHeader* __restrict__ hdr) {
+  constexpr int ST = MGS_SORT_THREADS, SI = 1024 / MGS_SORT_THREADS;
+  using Temp = typename cub::BlockMergeSort<unsigned long long, ST, SI>::TempStorage;
+  __shared__ Temp temp;
+  pdl_enter<PDL_SORT>();
+  if (blockIdx.x != 0) {
+    const int tile = (int)blockIdx.x - 1;
+    const int n = (int)min(__ldcg(&tile_ctr[(size_t)tile * TILE_CTR_STRIDE]), cap);
+    if (n == 0) return;
+    const unsigned long long* seg = list + (size_t)tile * cap;
+    void* dst = ids + (size_t)tile * cap;
+    if (n <= 256) sort_tile_regs<SI / 4, ST>(temp, seg, n, dst, nullptr, nullptr, nullptr, nullptr);
+    else if (n <= 512) sort_tile_regs<SI / 2, ST>(temp, seg, n, dst, nullptr, nullptr, nullptr, nullptr);
+    else if (n <= 768) sort_tile_regs<SI * 3 / 4, ST>(temp, seg, n, dst, nullptr, nullptr, nullptr, nullptr);
+    else sort_tile_regs<SI, ST>(temp, seg, n, dst, nullptr, nullptr, nullptr, nullptr);
+    return;
+  }
+  __shared__ uint32_t s_sum, s_used, s_max, bucket[64];
+  if (threadIdx.x == 0) { s_sum = 0u; s_used = 0u; s_max = 0u; }
+  if (threadIdx.x < 64) bucket[threadIdx.x] = 0u;
+  __syncthreads();
+  uint32_t sum = 0u, used = 0u, m = 0u;
+  for (int t = threadIdx.x; t < tiles; t += ST) {
+    const uint32_t c = __ldcg(&tile_ctr[(size_t)t * TILE_CTR_STRIDE]), n = min(c, cap);
+    ranges[t] = (c == 0u) ? make_uint2(0u, 0u) : make_uint2((uint32_t)t * cap, (uint32_t)t * cap + n);
+    sum += c; used += n; m = max(m, c);
+  }
+  sum = __reduce_add_sync(0xffffffffu, sum); used = __reduce_add_sync(0xffffffffu, used); m = __reduce_max_sync(0xffffffffu, m);
+  if ((threadIdx.x & 31) == 0) { atomicAdd(&s_sum, sum); atomicAdd(&s_used, used); atomicMax(&s_max, m); }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const bool over = s_max > cap;
+    hdr->num_rendered = s_sum;
+    hdr->overflow = over ? 1u : 0u;
+    hdr->r_used = s_used;
+    hdr->n_large = 0u;
+    if (over) hdr->overflow_sticky = 1u;
+    if (s_sum > hdr->max_rendered) hdr->max_rendered = s_sum;
+    if (s_max > hdr->max_tile_count) hdr->max_tile_count = s_max;
+  }
+  // heavy-first order: counting sort of the tiles into 64 buckets of list length, longest first (as tile_scan_body)
+  const float inv = 63.0f / (float)(s_max > 0u ? s_max : 1u);
+  auto bucket_of = [&](const uint32_t c) { return 63u - min(63u, (uint32_t)((float)c * inv)); };
+  for (int t = threadIdx.x; t < tiles; t += ST) atomicAdd(&bucket[bucket_of(__ldcg(&tile_ctr[(size_t)t * TILE_CTR_STRIDE]))], 1u);
+  __syncthreads();
+  if (threadIdx.x < 32) {   // exclusive scan of the 64 bucket sizes
+    const uint32_t a = bucket[2 * threadIdx.x], b = bucket[2 * threadIdx.x + 1];
+    uint32_t incl = a + b;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)threadIdx.x >= o) incl += up;
+    }
+    bucket[2 * threadIdx.x] = incl - a - b;
+    bucket[2 * threadIdx.x + 1] = incl - b;
+  }
+  __syncthreads();
+  for (int t = threadIdx.x; t < tiles; t += ST) {
+    const uint32_t pos = atomicAdd(&bucket[bucket_of(__ldcg(&tile_ctr[(size_t)t * TILE_CTR_STRIDE]))], 1u);
+    tile_ctr[(size_t)pos * TILE_CTR_STRIDE + 3] = (uint32_t)t;
+  }
+}
+
+int launch_sort_segments(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s) {
+  const int tiles = v.gx * v.gy;
+  if ((int64_t)tiles * TILE_SEGMENT > R_cap) {
+    set_error("tile segments: R_cap %lld < tiles x %d = %lld", (long long)R_cap, TILE_SEGMENT, (long long)tiles * TILE_SEGMENT);
+    return MGS_ENOSPC;
+  }
+  cudaError_t e;
+  MGS_PROF("tile_sort_segments", s, e = launch_chain(tile_sort_segments_kernel, tiles + 1, MGS_SORT_THREADS, 0, s, tiles, (uint32_t)TILE_SEGMENT,
+                                                     ws_ptr<unsigned long long>(ws, L.list), ws_ptr<uint32_t>(ws, L.records),
+                                                     ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges),
+                                                     ws_ptr<WsHeader>(ws, L.header)));
+  MGS_CUDA_TRY(e);
+  MGS_LAUNCH_CHECK();
+  return MGS_OK;
+}
+
 int launch_tile_scan(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s, bool heavy_first) {
-  MGS_PROF("tile_scan", s, tile_scan_kernel<<<1, SCAN_THREADS, 0, s>>>(
+  cudaError_t e;
+  MGS_PROF("tile_scan", s, e = launch_chain(tile_scan_kernel, 1, SCAN_THREADS, 0, s,
       ws_ptr<uint32_t>(ws, L.tile_ctr), v.gx * v.gy, (uint32_t)R_cap, ws_ptr<uint2>(ws, L.ranges),
       ws_ptr<WsHeader>(ws, L.header), heavy_first ? 1 : 0));
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }
@@ -752,49 +873,57 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
   // fold != nullptr: the workspace is one a fused loop renders into repeatedly — its tile counters were left zero by the
   // previous render's sort kernel (clear_counts) and its header ticket is zero, so no memset and no separate scan launch
   if (fold == nullptr)
-    MGS_CUDA_TRY(cudaMemsetAsync(ws_ptr<void>(ws, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
+    MGS_CUDA_TRY(memset_async(ws_ptr<void>(ws, L.tile_ctr), 0, (size_t)v.gx * v.gy * TILE_CTR_STRIDE * sizeof(uint32_t), s));
   const uint32_t R_cap = fold ? (uint32_t)fold->R_cap : 0u;
   const int heavy = fold ? (fold->heavy_first ? 1 : 0) : 0;
+  const uint32_t seg_cap = fold ? (uint32_t)fold->segment_cap : 0u;
+  if (seg_cap != 0u && !(jac != nullptr && jac_ncol == TRACK_ROW_FLOATS && !fold->in_kernel)) {
+    set_error("preprocess: fixed tile segments serve the fused tracker's packed-row mode only"); return MGS_EINVAL;
+  }
   // fold->in_kernel picks the folded tail or a separate tile_scan launch (launchers.h); either way the workspace is the
   // zero-maintained one of a fused loop: no memset.
   static const int scan_env = [] { const char* e = getenv("MGS_SCAN_FOLD"); return e ? (e[0] == '1' ? 1 : 0) : -1; }();
-  const bool scan_separate = fold != nullptr && (scan_env >= 0 ? scan_env == 0 : !fold->in_kernel);
+  const bool scan_separate = fold != nullptr && (seg_cap != 0u || (scan_env >= 0 ? scan_env == 0 : !fold->in_kernel));
   const FoldScan* const fold_req = fold;
   if (scan_separate) fold = nullptr;
 #define MGS_PRE_ARGS v, P, means3D, opacities, shs, sh_rest, colors_precomp, scales, rotations, cov3D_precomp, radii,  \
       ws_ptr<float>(ws, L.depths), ws_ptr<float2>(ws, L.means2D), ws_ptr<float4>(ws, L.conic_opacity),               \
       ws_ptr<float4>(ws, L.rgb4), ws_ptr<uint32_t>(ws, L.tiles_touched), ws_ptr<uint32_t>(ws, L.tile_ctr), jac, R_cap, \
-      ws_ptr<uint2>(ws, L.ranges), ws_ptr<WsHeader>(ws, L.header), heavy
+      ws_ptr<uint2>(ws, L.ranges), ws_ptr<WsHeader>(ws, L.header), heavy, ws_ptr<unsigned long long>(ws, L.list), seg_cap
   // SH rows of more than one coefficient are staged through shared memory (128 threads: 4 tiles of [32][3M | 1] floats)
   const bool stage = shs != nullptr && colors_precomp == nullptr && v.M > 1 && !(jac != nullptr && (jac_ncol == 32 || jac_ncol == TRACK_ROW_FLOATS));
   if (sh_rest != nullptr && !stage) { set_error("preprocess: split SH layout needs sh_coeffs > 1 and no colors_precomp"); return MGS_EINVAL; }
   if (jac != nullptr && (jac_ncol == 32 || jac_ncol == TRACK_ROW_FLOATS) && fold_req == nullptr) { set_error("preprocess: the folded pose basis is built by the fused SH-degree-0 tracker only"); return MGS_EINVAL; }
+  cudaError_t pe = cudaSuccess;
   prof_begin(fold ? "preprocess+scan" : "preprocess", s);
   if (stage) {
     const int T = 128;
     const size_t smem = (size_t)T * sh_row_stride(v.M) * sizeof(float);
     if (fold) {
-      if (jac == nullptr) preprocess_kernel<0, true, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
-      else if (jac_ncol == 9) preprocess_kernel<9, true, true><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+      if (jac == nullptr) pe = launch_chain(preprocess_kernel<0, true, true>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
+      else if (jac_ncol == 9) pe = launch_chain(preprocess_kernel<9, true, true>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
       else { set_error("preprocess: unsupported fused variant"); return MGS_EINVAL; }
-    } else if (jac == nullptr) preprocess_kernel<0, true, false><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
-    else if (jac_ncol == 9) preprocess_kernel<9, true, false><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
-    else preprocess_kernel<6, true, false><<<(P + T - 1) / T, T, smem, s>>>(MGS_PRE_ARGS);
+    } else if (jac == nullptr) pe = launch_chain(preprocess_kernel<0, true, false>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
+    else if (jac_ncol == 9) pe = launch_chain(preprocess_kernel<9, true, false>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
+    else pe = launch_chain(preprocess_kernel<6, true, false>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
   } else {
     if (fold) {
-      if (jac == nullptr) preprocess_kernel<0, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-      else if (jac_ncol == 32) preprocess_kernel<32, false, true><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-      else if (jac_ncol == TRACK_ROW_FLOATS) preprocess_kernel<TRACK_ROW_FLOATS, false, true><<<(P + 255) / 256, 256, 256 * TRACK_ROW_FLOATS * sizeof(float), s>>>(MGS_PRE_ARGS);
+      if (jac == nullptr) pe = launch_chain(preprocess_kernel<0, false, true>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
+      else if (jac_ncol == 32) pe = launch_chain(preprocess_kernel<32, false, true>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
+      else if (jac_ncol == TRACK_ROW_FLOATS) pe = launch_chain(preprocess_kernel<TRACK_ROW_FLOATS, false, true>, (P + 255) / 256, 256, 256 * TRACK_ROW_FLOATS * sizeof(float), s, MGS_PRE_ARGS);
       else { set_error("preprocess: unsupported fused variant"); return MGS_EINVAL; }
-    } else if (jac == nullptr) preprocess_kernel<0, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-    else if (jac_ncol == 9) preprocess_kernel<9, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-    else if (jac_ncol == 32) preprocess_kernel<32, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
-    else if (jac_ncol == TRACK_ROW_FLOATS) preprocess_kernel<TRACK_ROW_FLOATS, false, false><<<(P + 255) / 256, 256, 256 * TRACK_ROW_FLOATS * sizeof(float), s>>>(MGS_PRE_ARGS);
-    else preprocess_kernel<6, false, false><<<(P + 255) / 256, 256, 0, s>>>(MGS_PRE_ARGS);
+    } else if (jac == nullptr) pe = launch_chain(preprocess_kernel<0, false, false>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
+    else if (jac_ncol == 9) pe = launch_chain(preprocess_kernel<9, false, false>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
+    else if (jac_ncol == 32) pe = launch_chain(preprocess_kernel<32, false, false>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
+    else if (jac_ncol == TRACK_ROW_FLOATS && seg_cap != 0u) pe = launch_chain(preprocess_kernel<TRACK_ROW_FLOATS, false, false, true>, (P + 255) / 256, 256, 256 * TRACK_ROW_FLOATS * sizeof(float), s, MGS_PRE_ARGS);
+    else if (jac_ncol == TRACK_ROW_FLOATS) pe = launch_chain(preprocess_kernel<TRACK_ROW_FLOATS, false, false>, (P + 255) / 256, 256, 256 * TRACK_ROW_FLOATS * sizeof(float), s, MGS_PRE_ARGS);
+    else pe = launch_chain(preprocess_kernel<6, false, false>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
   }
   prof_end(s);
 #undef MGS_PRE_ARGS
+  MGS_CUDA_TRY(pe);
   MGS_LAUNCH_CHECK();
+  if (seg_cap != 0u) return MGS_OK;     // no scan: launch_sort_segments() follows
   if (fold_req != nullptr && fold == nullptr) return launch_tile_scan(v, ws, L, fold_req->R_cap, s, fold_req->heavy_first);
   return MGS_OK;
 }
@@ -808,18 +937,22 @@ int launch_binning(const ViewConst& v, int P, const float* colors_precomp, const
     if (rc) return rc;
   }
   if (R_cap == 0 || P == 0) return MGS_OK;
-  MGS_PROF("emit", s, emit_kernel<<<(P + 255) / 256, 256, 0, s>>>(
+  cudaError_t e;
+  MGS_PROF("emit", s, e = launch_chain(emit_kernel, (P + 255) / 256, 256, 0, s,
       P, (uint32_t)R_cap, v.gx, v.gy, ws_ptr<float2>(ws, L.means2D), ws_ptr<float>(ws, L.depths), radii,
       ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<unsigned long long>(ws, L.list)));
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
 #define MGS_SORT_ARGS ws_ptr<uint2>(ws, L.ranges), ws_ptr<unsigned long long>(ws, L.list),                                   \
       (ids_only ? (const float2*)nullptr : ws_ptr<float2>(ws, L.means2D)),                                                       \
       ws_ptr<float4>(ws, L.conic_opacity), ws_ptr<float4>(ws, L.rgb4), colors_precomp, ws_ptr<SplatRec>(ws, L.records),     \
       ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<WsHeader>(ws, L.header), clear_counts ? 1 : 0
-  MGS_PROF("tile_sort_records", s, tile_sort_records_kernel<false><<<tiles, MGS_SORT_THREADS, 0, s>>>(MGS_SORT_ARGS));
+  MGS_PROF("tile_sort_records", s, e = launch_chain(tile_sort_records_kernel<false>, tiles, MGS_SORT_THREADS, 0, s, MGS_SORT_ARGS));
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   MGS_PROF("tile_sort_records_large", s,
-           tile_sort_records_kernel<true><<<tiles < 592 ? tiles : 592, 256, 0, s>>>(MGS_SORT_ARGS));
+           e = launch_chain(tile_sort_records_kernel<true>, tiles < 592 ? tiles : 592, 256, 0, s, MGS_SORT_ARGS));
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
 #undef MGS_SORT_ARGS
   return MGS_OK;

@@ -26,7 +26,7 @@ namespace mgs {
 int launch_sketch_reduce(const float* rows, int H, int W, int n_stacks, int d, const int32_t* sketch_indices,
                          float* out, cudaStream_t s, int nv);
 
-__global__ void __launch_bounds__(256) track_update_kernel(const TrackUpdateK k) { track_update_body(k); }
+__global__ void __launch_bounds__(256) track_update_kernel(const TrackUpdateK k) { pdl_enter<PDL_UPD>(); track_update_body(k); }
 
 // ---- second-order (sketched Gauss-Newton / Levenberg-Marquardt) iteration, utils/slam_frontend.py:455-720 with
 //      in_second_order == True.  The reference applies the step of iteration k at the START of iteration k+1
@@ -46,6 +46,7 @@ struct Track2K {
 
 __global__ void __launch_bounds__(32) track2_begin_kernel(const Track2K k) {
   __shared__ float s_T[16], s_p[8], s_view[16], s_proj[16], s_pr[16];
+  pdl_enter<PDL_UPD>();
   const int tid = threadIdx.x;
   if (k.st[LM_PENDING] == 0.f) return;     // uniform
   if (tid < 16) { s_T[tid] = k.T[tid]; s_pr[tid] = k.proj_raw[tid]; }
@@ -62,6 +63,7 @@ __global__ void __launch_bounds__(256) track2_solve_kernel(const Track2K k) {
   constexpr int NA = 36 + 8;                  // upper triangle of J^T J, then J^T f
   __shared__ double red[8][NA + 1];
   __shared__ double tot[NA + 1];
+  pdl_enter<PDL_UPD>();
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double acc[NA + 1];
 #pragma unroll
@@ -175,6 +177,7 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   if (t->R_cap <= 0 || t->R_cap > 0x7fffffffLL) { set_error("track: bad R_cap"); return MGS_EINVAL; }
   if (t->scratch_bytes < mgs_track_scratch_bytes(P, W, H)) { set_error("track: scratch too small"); return MGS_ENOSPC; }
   cudaStream_t s = (cudaStream_t)stream;
+  PdlScope pdl_scope;     // the iteration's kernels are chained by programmatic dependent launch (common.cuh)
   WsLayout L;
   int rc = ws_layout(P, W, H, t->R_cap, &L);
   if (rc) return rc;
@@ -191,20 +194,26 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   float* tau_raw = reinterpret_cast<float*>(sp);
   const bool with_color = v.D > 0;
   void* ws = t->workspace;
-  if (t->status_out) MGS_CUDA_TRY(cudaMemcpyAsync(t->status_out, ws, 6 * sizeof(uint32_t), cudaMemcpyDefault, s));   // of the PREVIOUS iteration
+  if (t->status_out) MGS_CUDA_TRY(memcpy_async(t->status_out, ws, 6 * sizeof(uint32_t), cudaMemcpyDefault, s));   // of the PREVIOUS iteration
 
   // The workspace and the scratch of a tracker are zero-filled ONCE by their owner: tile counters, the scan ticket, the
   // tangent accumulator and the update ticket are all left zero by the iteration that used them (the sort kernel clears
   // its tile's counter, the update kernel re-zeroes tau_raw), so an iteration is 7 kernels and no memset.
   const bool rows = !with_color && track_rows() && !track_update_fold();   // (the folded-update kernels keep the record staging)
-  const FoldScan fs{t->R_cap, /*heavy_first=*/!with_color, /*in_kernel=*/false};
+  // tile_segments: fixed 1024-instance segment per tile, scattered by the preprocess kernel and sorted in place — the
+  // iteration is preprocess, tile_sort_segments, blend_track, track_update (four kernels instead of seven)
+  const bool segments = t->tile_segments != 0;
+  if (segments && !rows) { set_error("track: tile_segments needs sh_degree 0 and the packed-row staging (MGS_TRACK_ROWS, MGS_UPDATE_FOLD unset)"); return MGS_EINVAL; }
+  if (segments && (int64_t)tiles * TILE_SEGMENT > t->R_cap) { set_error("track: tile_segments needs R_cap >= tiles x %d", TILE_SEGMENT); return MGS_ENOSPC; }
+  const FoldScan fs{t->R_cap, /*heavy_first=*/!with_color, /*in_kernel=*/false, segments ? TILE_SEGMENT : 0};
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
                               ws, L, s, jac, with_color ? 9 : (rows ? TRACK_ROW_FLOATS : 32), nullptr, &fs)))
     return rc;
-  if (!t->fast_math) MGS_CUDA_TRY(cudaMemsetAsync(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
-  if (with_color) MGS_CUDA_TRY(cudaMemsetAsync(tau_raw, 0, 6 * sizeof(float), s));
-  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, fs.heavy_first, /*scan_done=*/true, /*clear_counts=*/true,
-                           /*ids_only=*/rows))) return rc;
+  if (!t->fast_math) MGS_CUDA_TRY(memset_async(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
+  if (with_color) MGS_CUDA_TRY(memset_async(tau_raw, 0, 6 * sizeof(float), s));
+  if (segments) { if ((rc = launch_sort_segments(v, ws, L, t->R_cap, s))) return rc; }
+  else if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, fs.heavy_first, /*scan_done=*/true, /*clear_counts=*/true,
+                                /*ids_only=*/rows))) return rc;
 
   LossK lk;
   lk.mode = t->loss_mode; lk.npix = (int)npix; lk.use_depth = use_depth;
@@ -237,8 +246,10 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
       return launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
                                 tau_raw, s, nullptr, 0.f, nullptr, &k, ticket);
     if ((rc = launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, use_depth != 0,
-                                 tau_raw, s, nullptr, 0.f, nullptr, nullptr, nullptr, false, rows))) return rc;
-    MGS_PROF("track_update", s, track_update_kernel<<<1, 256, 0, s>>>(k));
+                                 tau_raw, s, nullptr, 0.f, nullptr, nullptr, nullptr, false, rows, segments))) return rc;
+    cudaError_t e;
+    MGS_PROF("track_update", s, e = launch_chain(track_update_kernel, 1, 256, 0, s, k));
+    MGS_CUDA_TRY(e);
     MGS_LAUNCH_CHECK();
     return MGS_OK;
   }
@@ -248,7 +259,9 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
   a.v = v; a.P = P; a.grad_mask = MGS_GRAD_TAU; a.ws = ws; a.L = L;
   a.dL_dcolor_img = g_img; a.dL_ddepth_img = use_depth ? g_depth : nullptr; a.dL_dtau_sum = tau_raw;
   if ((rc = launch_blend_backward_pose(a, jac, with_color, s, t->fast_math != 0))) return rc;
-  MGS_PROF("track_update", s, track_update_kernel<<<1, 256, 0, s>>>(k));
+  cudaError_t e;
+  MGS_PROF("track_update", s, e = launch_chain(track_update_kernel, 1, 256, 0, s, k));
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }
@@ -270,6 +283,7 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   if (t->R_cap <= 0 || t->R_cap > 0x7fffffffLL) { set_error("track2: bad R_cap"); return MGS_EINVAL; }
   if (t->scratch_bytes < mgs_track_scratch_bytes(P, W, H)) { set_error("track2: scratch too small"); return MGS_ENOSPC; }
   cudaStream_t s = (cudaStream_t)stream;
+  PdlScope pdl_scope;
   WsLayout L;
   int rc = ws_layout(P, W, H, t->R_cap, &L);
   if (rc) return rc;
@@ -285,7 +299,7 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   sp += 256;
   float* sk_image = reinterpret_cast<float*>(sp);
   void* ws = t->workspace;
-  if (t->status_out) MGS_CUDA_TRY(cudaMemcpyAsync(t->status_out, ws, 6 * sizeof(uint32_t), cudaMemcpyDefault, s));
+  if (t->status_out) MGS_CUDA_TRY(memcpy_async(t->status_out, ws, 6 * sizeof(uint32_t), cudaMemcpyDefault, s));
 
   Track2K k;
   k.npix = (int)npix; k.tiles = tiles * (8 / blend_track_warps()); k.rows = a->n_stacks * a->sketch_dim;
@@ -294,15 +308,21 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   k.proj_raw = view->projmatrix_raw; k.st = a->lm_state ? a->lm_state : t->lm_state;
   k.min_lambda = a->min_lambda; k.max_lambda = a->max_lambda; k.inc = a->increase_factor; k.dec = a->decrease_factor;
   k.conv_thr = a->converged_threshold; k.loss_out = t->loss;
-  MGS_PROF("track2_begin", s, track2_begin_kernel<<<1, 32, 0, s>>>(k));
+  cudaError_t e;
+  MGS_PROF("track2_begin", s, e = launch_chain(track2_begin_kernel, 1, 32, 0, s, k));
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   const bool rows = track_rows();
-  const FoldScan fs{t->R_cap, /*heavy_first=*/true, /*in_kernel=*/false};
+  const bool segments = t->tile_segments != 0;
+  if (segments && !rows) { set_error("track2: tile_segments needs the packed-row staging"); return MGS_EINVAL; }
+  if (segments && (int64_t)tiles * TILE_SEGMENT > t->R_cap) { set_error("track2: tile_segments needs R_cap >= tiles x %d", TILE_SEGMENT); return MGS_ENOSPC; }
+  const FoldScan fs{t->R_cap, /*heavy_first=*/true, /*in_kernel=*/false, segments ? TILE_SEGMENT : 0};
   if ((rc = launch_preprocess(v, P, t->means3D, t->opacities, t->shs, nullptr, t->scales, t->rotations, nullptr, t->radii,
                               ws, L, s, jac, rows ? TRACK_ROW_FLOATS : 32, nullptr, &fs)))
     return rc;
-  if (!t->fast_math) MGS_CUDA_TRY(cudaMemsetAsync(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
-  if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true, /*ids_only=*/rows))) return rc;
+  if (!t->fast_math) MGS_CUDA_TRY(memset_async(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
+  if (segments) { if ((rc = launch_sort_segments(v, ws, L, t->R_cap, s))) return rc; }
+  else if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true, /*ids_only=*/rows))) return rc;
   LossK lk;
   lk.mode = MGS_LOSS_TRACK_HUBER; lk.npix = (int)npix; lk.use_depth = 0;
   lk.thr = t->rgb_boundary_threshold; lk.alpha = t->alpha; lk.delta = t->huber_delta; lk.scale = 1.f; lk.eps = 1e-8f;
@@ -312,10 +332,11 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   fl.k = &lk; fl.grad_scale = 1.f; fl.g_img = nullptr; fl.g_depth = nullptr; fl.partials = partials; fl.fast = t->fast_math != 0;
   const float sk_scale = (float)((double)k.rows / (double)npix);     // 1 / (m / (stack_dim * sketch_dim)), slam_frontend.py:642
   if ((rc = launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, false, nullptr, s,
-                               a->rand_weights, sk_scale, sk_image, nullptr, nullptr, false, rows)))
+                               a->rand_weights, sk_scale, sk_image, nullptr, nullptr, false, rows, segments)))
     return rc;
   if ((rc = launch_sketch_reduce(sk_image, H, W, a->n_stacks, a->sketch_dim, a->sketch_indices, a->rows, s, 9))) return rc;
-  MGS_PROF("track2_solve", s, track2_solve_kernel<<<1, 256, 0, s>>>(k));
+  MGS_PROF("track2_solve", s, e = launch_chain(track2_solve_kernel, 1, 256, 0, s, k));
+  MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
 }

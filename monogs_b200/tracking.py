@@ -9,6 +9,7 @@ replayed (the reference blocks on cudaMemcpy of num_rendered every forward, rast
 Python + autograd round trip per stage).  torch provides memory, streams and the graph object only.
 """
 import ctypes as C
+import os
 
 import torch
 
@@ -18,14 +19,19 @@ from .rasterizer import make_view, GaussianRasterizationSettings, _stream
 KERNELS_PER_ITER = 7    # own kernels per fused iteration (SH degree 0): preprocess (+ pose basis, tile counts), tile_scan, emit,
                         # tile_sort_records x2 (short / long lists), blend_track (forward + loss + pose tangent),
                         # track_update (loss norm + Adam + pose update)
+KERNELS_PER_ITER_SEGMENTS = 4   # fixed tile segments: preprocess (+ scatter), tile_sort_segments, blend_track, track_update
 KERNELS_PER_ITER_COMPOSED = 14
+TILE_SEGMENT = 1024     # MGS_TILE_SEGMENT (include/monogs_b200.h)
 
 
 class PoseTracker:
     def __init__(self, means3D, opacities, shs, scales, rotations, sh_degree, cam, bg, T_w2c, mode=L.LOSS_TRACK_HUBER,
                  use_depth=False, lr=(1e-3, 3e-3, 2e-2, 2e-2), capacity_headroom=1.3, use_graph=True, fused=True, fast_math=True,
-                 adam_eps=1e-8):
-        """adam_eps: the reference builds the pose / exposure optimiser as torch.optim.Adam(opt_params) with torch's default
+                 adam_eps=1e-8, tile_segments=True):
+        """tile_segments: fixed-segment binning of the fused SH-degree-0 iteration (mgs_track_args.tile_segments: four kernels
+        per iteration instead of seven; the workspace holds tiles x 1024 instance slots).  A tile list beyond 1024 instances
+        raises the overflow status; poll_capacity() / check_capacity() then switch the tracker back to the general binning.
+        adam_eps: the reference builds the pose / exposure optimiser as torch.optim.Adam(opt_params) with torch's default
         eps = 1e-8 (utils/slam_frontend.py:453); only the Gaussian optimiser uses 1e-15 (gaussian_model.py:285)."""
         lib = self.lib = L.lib()
         dev = self.dev = means3D.device
@@ -69,12 +75,14 @@ class PoseTracker:
         self.bwd_scratch = torch.empty(max(lib.mgs_raster_backward_pose_scratch_bytes(self.P, self.W, self.H), 256),
                                        device=dev, dtype=torch.uint8)
         self.fused, self.fast_math = fused, fast_math
+        self.tile_segments = bool(tile_segments) and fused and sh_degree == 0 and os.environ.get("MGS_TILE_SEGMENTS", "1") != "0"
+        self.tiles = ((self.W + 15) // 16) * ((self.H + 15) // 16)
         # zero-filled once: holds the tangent accumulator and the update ticket, which every iteration leaves zero again
         self.track_scratch = torch.zeros(lib.mgs_track_scratch_bytes(self.P, self.W, self.H), device=dev, dtype=torch.uint8)
         self.headroom = capacity_headroom
         self.R_cap, self.ws = 0, None
         self.use_graph, self.graph = use_graph, None
-        self._seen_max = 0
+        self._seen_max, self._tile_max = 0, 0
         self._status = torch.zeros(8, dtype=torch.int32).pin_memory()
         self._status_ev = torch.cuda.Event()
         self._status_pending = False
@@ -92,15 +100,21 @@ class PoseTracker:
         """One synchronous preprocess to learn num_rendered, then capacity = headroom x that."""
         lib = self.lib
         base = lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, 0)
-        tmp = torch.empty(base, device=self.dev, dtype=torch.uint8)
+        tmp = torch.zeros(base, device=self.dev, dtype=torch.uint8)     # zero: the sticky header words are read below
         n_host = torch.zeros(1, dtype=torch.int32).pin_memory()
         L.check(lib.mgs_raster_preprocess(C.byref(self.view), self.P, L.ptr(self.means3D), L.ptr(self.opacities),
                                           L.ptr(self.shs), None, L.ptr(self.scales), L.ptr(self.rotations), None,
                                           L.ptr(self.radii), L.ptr(tmp), tmp.numel(), C.c_void_p(n_host.data_ptr()),
                                           _stream(self.dev)), "mgs_raster_preprocess")
+        L.check(lib.mgs_raster_status_async(L.ptr(tmp), C.c_void_p(self._status.data_ptr()), _stream(self.dev)), "mgs_raster_status_async")
         torch.cuda.current_stream(self.dev).synchronize()
         R = int(n_host.item())
         self.R_cap = max(int(max(R, self._seen_max) * self.headroom) + 4096, 4096)
+        self._tile_max = max(self._tile_max, int(self._status[7]))
+        if self.tile_segments and self._tile_max * self.headroom > TILE_SEGMENT:
+            self.tile_segments = False      # a tile list is (close to) longer than a segment: general binning
+        if self.tile_segments:
+            self.R_cap = max(self.R_cap, self.tiles * TILE_SEGMENT)     # every tile owns a fixed segment
         # zero-filled: the sticky header words (overflow_sticky, max_rendered) are read by poll_capacity()
         self.ws = torch.zeros(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev,
                               dtype=torch.uint8)
@@ -142,7 +156,12 @@ class PoseTracker:
         t.workspace, t.workspace_bytes, t.R_cap = self.ws.data_ptr(), self.ws.numel(), self.R_cap
         t.scratch, t.scratch_bytes = self.track_scratch.data_ptr(), self.track_scratch.numel()
         t.lm_state, t.status_out = self.lm_state.data_ptr(), None
+        t.tile_segments = int(self.tile_segments)
         return t
+
+    @property
+    def kernels_per_iter(self):
+        return KERNELS_PER_ITER_SEGMENTS if self.tile_segments else (KERNELS_PER_ITER if self.fused else KERNELS_PER_ITER_COMPOSED)
 
     def _enqueue(self):
         """The whole iteration on the current stream, no host sync anywhere: one fused C-ABI call
@@ -192,9 +211,13 @@ class PoseTracker:
             self._status_pending = False
             over, seen = bool(self._status[4]), int(self._status[5])
             self._seen_max = max(self._seen_max, seen)
+            self._tile_max = max(self._tile_max, int(self._status[7]))
+            leave = self.tile_segments and (over or self._tile_max * 1.1 > TILE_SEGMENT)
             if over:
                 self.overflow_frames += 1
-            if over or seen * 1.1 > self.R_cap:
+            if leave:
+                self.tile_segments = False      # in segment mode overflow = a tile list beyond 1024 instances
+            if over or leave or seen * 1.1 > self.R_cap:
                 self._size_workspace()
                 regrown = True
         if not self._status_pending:
@@ -400,5 +423,6 @@ class PoseTracker:
         L.check(self.lib.mgs_raster_query(L.ptr(self.ws), C.byref(n), C.byref(ov), _stream(self.dev)), "mgs_raster_query")
         self._seen_max = max(self._seen_max, n.value)
         if ov.value:
+            self.tile_segments = False
             self._size_workspace()
         return n.value, bool(ov.value)
