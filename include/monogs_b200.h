@@ -411,6 +411,10 @@ typedef struct mgs_map_view {
   void* workspace; size_t workspace_bytes; int64_t R_cap;   /* zero-filled once by its owner before the first view
                              * rendered into it, and used by mgs_map_view_* only (tile counters and the scan ticket are left
                              * zero by every view for the next one) */
+  int32_t tile_segments;    /* 1: fixed-segment binning as in mgs_track_args.tile_segments (R_cap >= tiles * MGS_TILE_SEGMENT;
+                             * a tile list beyond a segment raises the workspace's overflow words): per view preprocess,
+                             * tile_sort_segments, blend, ... instead of preprocess + scan, emit, two sort kernels, blend, ... */
+  int32_t reserved0;
 } mgs_map_view;
 
 size_t mgs_map_scratch_bytes(int32_t P, int32_t sh_coeffs, int32_t W_max, int32_t H_max);

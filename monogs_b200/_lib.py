@@ -100,6 +100,7 @@ class MgsMapView(C.Structure):
         ("radii", C.c_void_p), ("n_touched", C.c_void_p),
         ("tau", C.c_void_p), ("dab", C.c_void_p), ("loss", C.c_void_p),
         ("workspace", C.c_void_p), ("workspace_bytes", C.c_size_t), ("R_cap", C.c_int64),
+        ("tile_segments", C.c_int32), ("reserved0", C.c_int32),
     ]
 
 

@@ -29,7 +29,7 @@ blend_forward_kernel(const int W, const int H, const int gx, const uint32_t* __r
                      float* __restrict__ out_color, float* __restrict__ out_depth, float* __restrict__ out_opacity,
                      int32_t* __restrict__ n_touched,
                      const LossK lk, const float loss_grad_scale, float* __restrict__ g_img, float* __restrict__ g_depth,
-                     double* __restrict__ loss_partials) {
+                     double* __restrict__ loss_partials, uint32_t* __restrict__ clear_ctr) {
   __shared__ __align__(128) SplatRec stage[FWD_STAGES][FWD_BATCH];
   __shared__ __align__(8) uint64_t full_bar[FWD_STAGES];
 
@@ -49,6 +49,8 @@ blend_forward_kernel(const int W, const int H, const int gx, const uint32_t* __r
   const int n = (int)(range.y - range.x);
   const int rounds = (n + FWD_BATCH - 1) / FWD_BATCH;
   const SplatRec* src = recs + range.x;
+  // fixed-segment binning: this grid visits every tile once and leaves the instance counters zero for the next view
+  if (clear_ctr != nullptr && tid == 0) clear_ctr[(size_t)tile * TILE_CTR_STRIDE] = 0u;
 
   if (tid == 0) {
 #pragma unroll
@@ -148,8 +150,9 @@ blend_forward_kernel(const int W, const int H, const int gx, const uint32_t* __r
 }
 
 int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
-                         float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl, bool heavy_first) {
+                         float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl, bool heavy_first, bool clear_counts) {
   const int tiles = v.gx * v.gy;
+  uint32_t* clear_ctr = clear_counts ? ws_ptr<uint32_t>(ws, L.tile_ctr) : nullptr;
   const uint32_t* order = heavy_first ? ws_ptr<uint32_t>(ws, L.tile_ctr) : nullptr;
   cudaError_t e;
   prof_begin("blend_forward", s);
@@ -157,11 +160,11 @@ int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float*
     LossK none{};
     e = launch_chain(blend_forward_kernel<false, false, true>, tiles, FWD_THREADS, 0, s,
         v.W, v.H, v.gx, order, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg, ws_ptr<float>(ws, L.final_T),
-        ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, none, 0.f, nullptr, nullptr, nullptr);
+        ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, none, 0.f, nullptr, nullptr, nullptr, clear_ctr);
   } else {
 #define MGS_FWD_ARGS v.W, v.H, v.gx, order, ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), v.bg,           \
         ws_ptr<float>(ws, L.final_T), ws_ptr<uint32_t>(ws, L.n_contrib), out_color, out_depth, out_opacity, n_touched, \
-        *fl->k, fl->grad_scale, fl->g_img, fl->g_depth, fl->partials
+        *fl->k, fl->grad_scale, fl->g_img, fl->g_depth, fl->partials, clear_ctr
     if (fl->fast && n_touched == nullptr) e = launch_chain(blend_forward_kernel<true, true, false>, tiles, FWD_THREADS, 0, s, MGS_FWD_ARGS);
     else if (fl->fast) e = launch_chain(blend_forward_kernel<true, true, true>, tiles, FWD_THREADS, 0, s, MGS_FWD_ARGS);
     else e = launch_chain(blend_forward_kernel<true, false, true>, tiles, FWD_THREADS, 0, s, MGS_FWD_ARGS);

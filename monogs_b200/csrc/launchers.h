@@ -14,7 +14,7 @@ const char* get_error();
 // preprocess kernel itself; no scan and no emit — launch_sort_segments() follows instead of launch_binning().
 struct FoldScan { int64_t R_cap; bool heavy_first; bool in_kernel; int segment_cap = 0; };
 constexpr int TILE_SEGMENT = 1024;      // instances per tile segment (= the longest list the one-CTA-per-tile sort takes)
-int launch_sort_segments(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s);
+int launch_sort_segments(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s, bool ids_only);
 int launch_preprocess(const ViewConst& v, int P, const float* means3D, const float* opacities, const float* shs,
                       const float* colors_precomp, const float* scales, const float* rotations,
                       const float* cov3D_precomp, int32_t* radii, void* ws, const WsLayout& L, cudaStream_t s,
@@ -28,7 +28,7 @@ struct LossK;
 struct FusedLoss { const LossK* k; float grad_scale; float* g_img; float* g_depth; double* partials; bool fast; };
 int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float* out_color, float* out_depth,
                          float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl = nullptr,
-                         bool heavy_first = false);
+                         bool heavy_first = false, bool clear_counts = false);   // clear_counts: fixed-segment binning (zero each tile's counter)
 
 // single-pass tracking blend (blend_track.cu): forward + loss + pose tangent; SH degree 0 / 6-column Jacobians only
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,

@@ -292,10 +292,14 @@ int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* st
   MGS_CUDA_TRY(memset_async(mv->n_touched, 0, (size_t)c.P * sizeof(int32_t), s));
   // the workspace of a mapping engine is zero-filled once by its owner: the scan runs in the last CTA of the preprocess
   // kernel and the sort kernel leaves the tile counters zero for the next view (raster_forward.cu, FoldScan)
-  const FoldScan fs{mv->R_cap, /*heavy_first=*/true, /*in_kernel=*/true};
+  // tile_segments: fixed 1024-slot segment per tile, scattered by the preprocess kernel (no scan, no emit, one sort kernel)
+  const bool segments = mv->tile_segments != 0;
+  if (segments && (int64_t)c.tiles * TILE_SEGMENT > mv->R_cap) { set_error("map: tile_segments needs R_cap >= tiles x %d", TILE_SEGMENT); return MGS_ENOSPC; }
+  const FoldScan fs{mv->R_cap, /*heavy_first=*/true, /*in_kernel=*/!segments, segments ? TILE_SEGMENT : 0};
   if ((rc = launch_preprocess(c.v, c.P, g.xyz, m.act_opacity, c.shs, nullptr, m.act_scales, m.act_rot, nullptr, mv->radii, ws, c.L, s,
                               nullptr, 0, c.M > 1 ? g.f_rest : nullptr, &fs))) return rc;
-  if ((rc = launch_binning(c.v, c.P, nullptr, mv->radii, ws, c.L, mv->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
+  if (segments) { if ((rc = launch_sort_segments(c.v, ws, c.L, mv->R_cap, s, /*ids_only=*/false))) return rc; }
+  else if ((rc = launch_binning(c.v, c.P, nullptr, mv->radii, ws, c.L, mv->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true))) return rc;
 
   LossK lk;
   lk.mode = MGS_LOSS_MAP_L1; lk.npix = (int)c.npix; lk.use_depth = c.use_depth;
@@ -305,7 +309,7 @@ int mgs_map_view_forward(const mgs_map_args* a, const mgs_map_view* mv, void* st
   FusedLoss fl;
   fl.k = &lk; fl.grad_scale = (c.use_depth ? mv->alpha : 1.f) / (3.f * (float)c.npix);
   fl.g_img = m.g_img[c.slot]; fl.g_depth = m.g_depth[c.slot]; fl.partials = m.partials[c.slot]; fl.fast = mv->fast_math != 0;
-  if ((rc = launch_blend_forward(c.v, ws, c.L, mv->out_color, mv->out_depth, mv->out_opacity, mv->n_touched, s, &fl, /*heavy_first=*/true))) return rc;
+  if ((rc = launch_blend_forward(c.v, ws, c.L, mv->out_color, mv->out_depth, mv->out_opacity, mv->n_touched, s, &fl, /*heavy_first=*/true, /*clear_counts=*/segments))) return rc;
   cudaError_t e;
   MGS_PROF("map_loss_finalize", s, e = launch_chain(map_loss_finalize_kernel, 1, 256, 0, s, m.partials[c.slot], c.tiles, (int)c.npix, c.use_depth,
                                                     mv->alpha, mv->loss, a->loss_total, mv->dab));

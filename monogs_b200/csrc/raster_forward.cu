@@ -544,7 +544,7 @@ preprocess_kernel(const ViewConst v, const int P,
       row[2] = make_float4(col.x, col.y, col.z, __uint_as_float(splat_extent(conic.x, conic.y, conic.z, op)));
     }
     else if (JAC_NCOL > 0) build_pose_jac<(JAC_NCOL == 9 ? 9 : 6)>(v, idx, p, shs, scales, rotations, cov3D_precomp, cm, jac);
-    if (!SEGMENTS) {   // (segment mode: emit_kernel, their only reader on the fused tracking path, does not run)
+    if (!(SEGMENTS && JAC_NCOL == TRACK_ROW_FLOATS)) {   // (packed-row segment mode: emit_kernel, their only reader there, does not run)
       depths[idx] = view_z;
       means2D[idx] = pix;
     }
@@ -773,9 +773,12 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
 // and the heavy-first launch order of the blend kernel (tile_ctr[i * TILE_CTR_STRIDE + 3]) — no prefix sum, the segment
 // starts are a multiplication.  The tile counters are NOT cleared here (CTA 0 reads all of them while the others run); the
 // blend kernel, which visits every tile exactly once, leaves them zero for the next iteration.
+// IDS: sorted Gaussian ids (fused tracker, packed rows); otherwise 48-byte records gathered by id (mapping engine).
+template <bool IDS>
 __global__ void __launch_bounds__(MGS_SORT_THREADS)
 tile_sort_segments_kernel(const int tiles, const uint32_t cap, const unsigned long long* __restrict__ list,
-                          uint32_t* __restrict__ ids, uint32_t* __restrict__ tile_ctr, uint2* __restrict__ ranges,
+                          void* __restrict__ out, const float2* __restrict__ means2D_in, const float4* __restrict__ conic_opacity,
+                          const float4* __restrict__ rgb4, uint32_t* __restrict__ tile_ctr, uint2* __restrict__ ranges,
                           WsHeader* __restrict__ hdr) {
   constexpr int ST = MGS_SORT_THREADS, SI = 1024 / MGS_SORT_THREADS;
   using Temp = typename cub::BlockMergeSort<unsigned long long, ST, SI>::TempStorage;
@@ -786,11 +789,12 @@ tile_sort_segments_kernel(const int tiles, const uint32_t cap, const unsigned lo
     const int n = (int)min(__ldcg(&tile_ctr[(size_t)tile * TILE_CTR_STRIDE]), cap);
     if (n == 0) return;
     const unsigned long long* seg = list + (size_t)tile * cap;
-    void* dst = ids + (size_t)tile * cap;
-    if (n <= 256) sort_tile_regs<SI / 4, ST>(temp, seg, n, dst, nullptr, nullptr, nullptr, nullptr);
-    else if (n <= 512) sort_tile_regs<SI / 2, ST>(temp, seg, n, dst, nullptr, nullptr, nullptr, nullptr);
-    else if (n <= 768) sort_tile_regs<SI * 3 / 4, ST>(temp, seg, n, dst, nullptr, nullptr, nullptr, nullptr);
-    else sort_tile_regs<SI, ST>(temp, seg, n, dst, nullptr, nullptr, nullptr, nullptr);
+    void* dst = IDS ? (void*)(reinterpret_cast<uint32_t*>(out) + (size_t)tile * cap) : (void*)(reinterpret_cast<SplatRec*>(out) + (size_t)tile * cap);
+    const float2* means2D = IDS ? nullptr : means2D_in;      // write_record: null = ids only
+    if (n <= 256) sort_tile_regs<SI / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, nullptr);
+    else if (n <= 512) sort_tile_regs<SI / 2, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, nullptr);
+    else if (n <= 768) sort_tile_regs<SI * 3 / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, nullptr);
+    else sort_tile_regs<SI, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, nullptr);
     return;
   }
   __shared__ uint32_t s_sum, s_used, s_max, bucket[64];
@@ -839,17 +843,19 @@ tile_sort_segments_kernel(const int tiles, const uint32_t cap, const unsigned lo
   }
 }
 
-int launch_sort_segments(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s) {
+int launch_sort_segments(const ViewConst& v, void* ws, const WsLayout& L, int64_t R_cap, cudaStream_t s, bool ids_only) {
   const int tiles = v.gx * v.gy;
   if ((int64_t)tiles * TILE_SEGMENT > R_cap) {
     set_error("tile segments: R_cap %lld < tiles x %d = %lld", (long long)R_cap, TILE_SEGMENT, (long long)tiles * TILE_SEGMENT);
     return MGS_ENOSPC;
   }
   cudaError_t e;
-  MGS_PROF("tile_sort_segments", s, e = launch_chain(tile_sort_segments_kernel, tiles + 1, MGS_SORT_THREADS, 0, s, tiles, (uint32_t)TILE_SEGMENT,
-                                                     ws_ptr<unsigned long long>(ws, L.list), ws_ptr<uint32_t>(ws, L.records),
-                                                     ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges),
-                                                     ws_ptr<WsHeader>(ws, L.header)));
+#define MGS_SEG_ARGS tiles + 1, MGS_SORT_THREADS, 0, s, tiles, (uint32_t)TILE_SEGMENT, ws_ptr<unsigned long long>(ws, L.list),          \
+      ws_ptr<void>(ws, L.records), ws_ptr<float2>(ws, L.means2D), ws_ptr<float4>(ws, L.conic_opacity), ws_ptr<float4>(ws, L.rgb4),  \
+      ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<WsHeader>(ws, L.header)
+  MGS_PROF("tile_sort_segments", s, e = ids_only ? launch_chain(tile_sort_segments_kernel<true>, MGS_SEG_ARGS)
+                                                 : launch_chain(tile_sort_segments_kernel<false>, MGS_SEG_ARGS));
+#undef MGS_SEG_ARGS
   MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
   return MGS_OK;
@@ -877,8 +883,8 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
   const uint32_t R_cap = fold ? (uint32_t)fold->R_cap : 0u;
   const int heavy = fold ? (fold->heavy_first ? 1 : 0) : 0;
   const uint32_t seg_cap = fold ? (uint32_t)fold->segment_cap : 0u;
-  if (seg_cap != 0u && !(jac != nullptr && jac_ncol == TRACK_ROW_FLOATS && !fold->in_kernel)) {
-    set_error("preprocess: fixed tile segments serve the fused tracker's packed-row mode only"); return MGS_EINVAL;
+  if (seg_cap != 0u && !((jac == nullptr || jac_ncol == TRACK_ROW_FLOATS) && !fold->in_kernel)) {
+    set_error("preprocess: fixed tile segments serve the fused tracker's packed-row mode and the mapping engine"); return MGS_EINVAL;
   }
   // fold->in_kernel picks the folded tail or a separate tile_scan launch (launchers.h); either way the workspace is the
   // zero-maintained one of a fused loop: no memset.
@@ -903,7 +909,8 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
       if (jac == nullptr) pe = launch_chain(preprocess_kernel<0, true, true>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
       else if (jac_ncol == 9) pe = launch_chain(preprocess_kernel<9, true, true>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
       else { set_error("preprocess: unsupported fused variant"); return MGS_EINVAL; }
-    } else if (jac == nullptr) pe = launch_chain(preprocess_kernel<0, true, false>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
+    } else if (jac == nullptr && seg_cap != 0u) pe = launch_chain(preprocess_kernel<0, true, false, true>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
+    else if (jac == nullptr) pe = launch_chain(preprocess_kernel<0, true, false>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
     else if (jac_ncol == 9) pe = launch_chain(preprocess_kernel<9, true, false>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
     else pe = launch_chain(preprocess_kernel<6, true, false>, (P + T - 1) / T, T, smem, s, MGS_PRE_ARGS);
   } else {
@@ -912,7 +919,8 @@ int launch_preprocess(const ViewConst& v, int P, const float* means3D, const flo
       else if (jac_ncol == 32) pe = launch_chain(preprocess_kernel<32, false, true>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
       else if (jac_ncol == TRACK_ROW_FLOATS) pe = launch_chain(preprocess_kernel<TRACK_ROW_FLOATS, false, true>, (P + 255) / 256, 256, 256 * TRACK_ROW_FLOATS * sizeof(float), s, MGS_PRE_ARGS);
       else { set_error("preprocess: unsupported fused variant"); return MGS_EINVAL; }
-    } else if (jac == nullptr) pe = launch_chain(preprocess_kernel<0, false, false>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
+    } else if (jac == nullptr && seg_cap != 0u) pe = launch_chain(preprocess_kernel<0, false, false, true>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
+    else if (jac == nullptr) pe = launch_chain(preprocess_kernel<0, false, false>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
     else if (jac_ncol == 9) pe = launch_chain(preprocess_kernel<9, false, false>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
     else if (jac_ncol == 32) pe = launch_chain(preprocess_kernel<32, false, false>, (P + 255) / 256, 256, 0, s, MGS_PRE_ARGS);
     else if (jac_ncol == TRACK_ROW_FLOATS && seg_cap != 0u) pe = launch_chain(preprocess_kernel<TRACK_ROW_FLOATS, false, false, true>, (P + 255) / 256, 256, 256 * TRACK_ROW_FLOATS * sizeof(float), s, MGS_PRE_ARGS);

@@ -211,7 +211,7 @@ int mgs_track_iteration(const mgs_track_args* t, void* stream) {
     return rc;
   if (!t->fast_math) MGS_CUDA_TRY(memset_async(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
   if (with_color) MGS_CUDA_TRY(memset_async(tau_raw, 0, 6 * sizeof(float), s));
-  if (segments) { if ((rc = launch_sort_segments(v, ws, L, t->R_cap, s))) return rc; }
+  if (segments) { if ((rc = launch_sort_segments(v, ws, L, t->R_cap, s, /*ids_only=*/true))) return rc; }
   else if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, fs.heavy_first, /*scan_done=*/true, /*clear_counts=*/true,
                                 /*ids_only=*/rows))) return rc;
 
@@ -321,7 +321,7 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
                               ws, L, s, jac, rows ? TRACK_ROW_FLOATS : 32, nullptr, &fs)))
     return rc;
   if (!t->fast_math) MGS_CUDA_TRY(memset_async(t->n_touched, 0, (size_t)P * sizeof(int32_t), s));
-  if (segments) { if ((rc = launch_sort_segments(v, ws, L, t->R_cap, s))) return rc; }
+  if (segments) { if ((rc = launch_sort_segments(v, ws, L, t->R_cap, s, /*ids_only=*/true))) return rc; }
   else if ((rc = launch_binning(v, P, nullptr, t->radii, ws, L, t->R_cap, s, true, /*scan_done=*/true, /*clear_counts=*/true, /*ids_only=*/rows))) return rc;
   LossK lk;
   lk.mode = MGS_LOSS_TRACK_HUBER; lk.npix = (int)npix; lk.use_depth = 0;

@@ -11,10 +11,13 @@ All Gaussian gradients live in ONE contiguous fp32 arena (`grad_arena`): each pa
 it, autograd accumulates in place, and the collective is a single all_reduce over 4*(11+3M)*P bytes.
 """
 import ctypes as C
+import os
 from typing import Callable, Dict, List, NamedTuple, Optional, Sequence
 
 import torch
 import torch.distributed as dist
+
+TILE_SEGMENT = 1024     # MGS_TILE_SEGMENT (include/monogs_b200.h)
 
 
 def assign_views(n_views: int, world: int, n_window: Optional[int] = None) -> List[List[int]]:
@@ -181,9 +184,15 @@ class MapEngine:
     def __init__(self, params: Dict[str, torch.Tensor], lrs: Dict[str, float], sh_degree: int = 0, W: int = 640, H: int = 480,
                  capacity_headroom: float = 2.0, group=None, regulariser_weight: float = 10.0,
                  rgb_boundary_threshold: float = 0.01, alpha: float = 0.95, fast_math: bool = True, overlap: bool = True,
-                 exchange: str = "nccl", max_views: int = 16, use_graph: bool = False):
+                 exchange: str = "nccl", max_views: int = 16, use_graph: bool = False, tile_segments: bool = True):
         from . import _lib as L
         from .ops import FusedAdam
+        # tile_segments: fixed-segment binning of every view (mgs_map_view.tile_segments: the preprocess kernel scatters
+        # the instances into per-tile segments of 1024 slots, one kernel sorts them; no scan, emit or long-list sort).
+        # Used while the longest tile list of the window leaves 1.3x headroom; an overflow or a list within 10 % of a
+        # segment switches the engine back to the general binning at the next poll_capacity().
+        self.tile_segments = bool(tile_segments) and os.environ.get("MGS_TILE_SEGMENTS", "1") != "0"
+        self._tile_max = 0
         self.fast_math = fast_math   # ex2.approx exponent in the blend kernels (relative error ~4e-7), like PoseTracker
         # overlap: the forward half of view k+1 (preprocess, binning, blend + loss) runs on the caller's stream beside the
         # backward half of view k on a second stream; two workspaces and two loss-gradient slots alternate
@@ -239,7 +248,6 @@ class MapEngine:
         if exchange == "auto":
             # the measured choice: the unicast kernel up to 4 ranks, the multicast kernel at 8, NCCL whenever
             # the group is not one NVLink domain of at most 8 CUDA ranks of this node
-            import os
             one_node = int(os.environ.get("LOCAL_WORLD_SIZE", self.world)) == self.world
             fused = (self.distributed and 1 < self.world <= 8 and one_node and self.dev.type == "cuda"
                      and dist.get_backend(group) == "nccl")
@@ -323,7 +331,7 @@ class MapEngine:
             shs = (torch.cat((self.params["f_dc"], self.params["f_rest"]), dim=1).contiguous() if "f_rest" in self.params
                    else self.params["f_dc"])
         base = lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, 0)
-        tmp = torch.empty(base, device=self.dev, dtype=torch.uint8)
+        tmp = torch.zeros(base, device=self.dev, dtype=torch.uint8)     # zero: the sticky max_tile_count is read below
         radii = torch.zeros(self.P, device=self.dev, dtype=torch.int32)
         n_host = torch.zeros(max(len(views), 1), dtype=torch.int32).pin_memory()
         for k, view in enumerate(views):
@@ -332,9 +340,15 @@ class MapEngine:
             L.check(lib.mgs_raster_preprocess(C.byref(v), self.P, L.ptr(self.params["xyz"]), L.ptr(op), L.ptr(shs), None, L.ptr(sc),
                                               L.ptr(rot), None, L.ptr(radii), L.ptr(tmp), tmp.numel(),
                                               C.c_void_p(n_host[k:].data_ptr()), _stream(self.dev)), "mgs_raster_preprocess")
+        L.check(lib.mgs_raster_status_async(L.ptr(tmp), C.c_void_p(self._status.data_ptr()), _stream(self.dev)), "mgs_raster_status_async")
         torch.cuda.current_stream(self.dev).synchronize()
         seen = max(int(n_host.max()), self._seen_max)
         self.R_cap = max(int(seen * self.headroom) + 4096, 4096)
+        self._tile_max = max(self._tile_max, int(self._status[0, 7]))
+        if self.tile_segments and self._tile_max * 1.3 > TILE_SEGMENT:
+            self.tile_segments = False
+        if self.tile_segments:
+            self.R_cap = max(self.R_cap, ((self.W + 15) // 16) * ((self.H + 15) // 16) * TILE_SEGMENT)
         # zero-filled: the sticky header words are read by poll_capacity()
         self.ws = torch.zeros(lib.mgs_raster_workspace_bytes(self.P, self.W, self.H, self.R_cap), device=self.dev, dtype=torch.uint8)
         self.ws_extra, self._out_extra = [], []
@@ -355,9 +369,13 @@ class MapEngine:
             n = self._status_n
             over = bool(self._status[:n, 4].any())
             self._seen_max = max(self._seen_max, int(self._status[:n, 5].max()))
+            self._tile_max = max(self._tile_max, int(self._status[:n, 7].max()))
+            leave = self.tile_segments and (over or self._tile_max * 1.1 > TILE_SEGMENT)
             if over:
                 self.overflow_polls += 1
-            if over or self._seen_max * 1.1 > self.R_cap:
+            if leave:
+                self.tile_segments = False       # a tile list reached the segment size: general binning from here on
+            if over or leave or self._seen_max * 1.1 > self.R_cap:
                 self.ws, self.ws_extra = None, []
                 dropped = True
         if not self._status_pending and self.ws is not None:
@@ -397,6 +415,7 @@ class MapEngine:
         ws = self.ws if r == 0 else self.ws_extra[r - 1]
         color, depth, opacity = (self.color, self.depth, self.opacity) if r == 0 else self._out_extra[r - 1]
         mv.fast_math, mv.slot, mv.concurrent_backward = int(self.fast_math), r, int(self.overlap and self._concurrent)
+        mv.tile_segments = int(self.tile_segments)
         mv.out_color, mv.out_depth, mv.out_opacity = color.data_ptr(), depth.data_ptr(), opacity.data_ptr()
         mv.radii, mv.n_touched = slot.radii.data_ptr(), slot.n_touched.data_ptr()
         mv.tau, mv.dab, mv.loss = slot.tau.data_ptr(), slot.dab.data_ptr(), slot.loss.data_ptr()
@@ -692,7 +711,9 @@ class MapEngine:
             # sticky words: ANY view rendered into these workspaces since they were allocated, not only the last one
             n_max, over = int(st[:, 5].max()), bool(st[:, 4].any())
             self._seen_max = max(self._seen_max, n_max)
+            self._tile_max = max(self._tile_max, int(st[:, 7].max()))
         if over:
+            self.tile_segments = False
             self.ws, self.ws_extra = None, []
         if self.block is not None:
             epoch = self.block.error_epoch(_stream())

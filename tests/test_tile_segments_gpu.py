@@ -121,3 +121,38 @@ def test_segment_overflow_is_reported_and_tracker_falls_back():
     torch.cuda.synchronize()
     assert torch.equal(tr2.color, ref_color) and U.rel_err(tr2.tau, ref_tau) <= 1e-5
     assert not tr2.check_capacity()[1]
+
+
+@pytest.mark.parametrize("name,with_depth,isotropic,overlap", [("dense", True, False, True), ("sh3", False, False, True),
+                                                               ("ragged", True, True, False), ("tiny", False, False, False)])
+def test_map_engine_segments_match_general_binning(name, with_depth, isotropic, overlap):
+    """mgs_map_view.tile_segments (preprocess_kernel<0, ., ., SEGMENTS> + tile_sort_segments_kernel<records>) against the
+    general binning of the same engine: identical radii / n_touched / images, gradients to the order of the float atomics;
+    two passes over the window, so the second runs on the counters the first left behind."""
+    from monogs_b200.mapping import MapEngine
+    from tests.test_map_engine_gpu import _raw_params, _views
+    sc, cam = U.small_case(name)
+    p0 = _raw_params(sc, isotropic)
+    views = _views(sc, cam, 3, with_depth, True)
+    out = []
+    for seg in (True, False):
+        p = {k: v.detach().clone() for k, v in p0.items()}
+        eng = MapEngine(p, {k: 0.0 for k in p}, sh_degree=sc.sh_degree, W=cam.W, H=cam.H, fast_math=False, overlap=overlap,
+                        tile_segments=seg)
+        eng.backward_only(views)
+        res = eng.backward_only(views)
+        torch.cuda.synchronize()
+        assert eng.tile_segments == seg
+        n, ov = eng.check_capacity()
+        assert not ov and 0 < eng._tile_max <= 1024
+        out.append(({k: g.clone() for k, g in eng.grads.items()}, [(r.radii.clone(), r.n_touched.clone(), r.tau.clone(), r.loss.clone()) for r in (res[i] for i in range(len(views)))],
+                    eng.loss_total.clone(), eng.xyz_gradient_accum.clone(), n))
+    (g0, r0, l0, a0, n0), (g1, r1, l1, a1, n1) = out
+    assert n0 == n1 and U.rel_err(l0, l1) <= 1e-6
+    for (ra, na, ta, la), (rb, nb, tb, lb) in zip(r0, r1):
+        assert torch.equal(ra, rb) and torch.equal(na, nb) and U.rel_err(la, lb) <= 1e-6 and U.rel_err(ta, tb) <= 1e-4
+    for k in g0:
+        if isotropic and k == "rotation":
+            continue
+        assert U.rel_err(g0[k], g1[k]) <= 1e-5, k
+    assert U.rel_err(a0, a1) <= 1e-5
