@@ -437,6 +437,9 @@ tile_scan_kernel(uint32_t* __restrict__ tile_ctr, const int tiles, const uint32_
 // `seg_cap` words of `list`, and an instance takes slot = atomicAdd(tile counter) of its tile at once, so there is no scan
 // between counting and scattering and no emit pass at all (tile_sort_segments_kernel sorts the segments in place of
 // tile_scan + emit + tile_sort_records x 2).  Instances beyond seg_cap are dropped; the count still says so (overflow).
+#ifndef MGS_SEG_COOP
+#define MGS_SEG_COOP 4           // chunks (returning atomics per lane in flight) of the segment scatter's warp-cooperative walk
+#endif
 template <int JAC_NCOL, bool STAGE, bool FOLD_SCAN, bool SEGMENTS = false>
 __global__ void __launch_bounds__(256, (JAC_NCOL == 0 && !STAGE) ? 5 : (((JAC_NCOL == 32 || JAC_NCOL == TRACK_ROW_FLOATS) && !STAGE) ? MGS_PRE_BASIS_MIN_CTAS : 0))   // plain: 48 registers, 5 CTAs per SM; pose basis: 80, 3 CTAs
 preprocess_kernel(const ViewConst v, const int P,
@@ -575,13 +578,14 @@ preprocess_kernel(const ViewConst v, const int P,
     // count AND scatter: (depth bits << 32 | id) straight into the tile's fixed segment, warp-cooperative walk of the 32
     // rects with four returning atomics per lane in flight (the walk of emit_kernel)
     const unsigned long long word = alive ? (((unsigned long long)__float_as_uint(view_z) << 32) | (uint32_t)idx) : 0ull;
-    for_each_tile_coop<4>(rmin, rmax, v.gx, word, [&](const uint32_t (&tile)[4], const bool (&ok)[4], const unsigned long long (&w)[4]) {
-      uint32_t slot[4];
+    for_each_tile_coop<MGS_SEG_COOP>(rmin, rmax, v.gx, word, [&](const uint32_t (&tile)[MGS_SEG_COOP], const bool (&ok)[MGS_SEG_COOP],
+                                                                 const unsigned long long (&w)[MGS_SEG_COOP]) {
+      uint32_t slot[MGS_SEG_COOP];
 #pragma unroll
-      for (int u = 0; u < 4; u++)
+      for (int u = 0; u < MGS_SEG_COOP; u++)
         if (ok[u]) slot[u] = atomicAdd(&tile_ctr[tile[u] * TILE_CTR_STRIDE], 1u);
 #pragma unroll
-      for (int u = 0; u < 4; u++)
+      for (int u = 0; u < MGS_SEG_COOP; u++)
         if (ok[u] && slot[u] < seg_cap) list[(size_t)tile[u] * seg_cap + slot[u]] = w[u];
     });
     return;
