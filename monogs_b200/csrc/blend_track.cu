@@ -60,6 +60,7 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 struct TrackTail {            // the folded update (FOLD): last CTA of the grid runs track_update_body
   TrackUpdateK k;
   uint32_t* ticket;           // device u32, zero before the first launch; reset by the last CTA
+  SketchRoute route;          // EPI = 1: route.idx != null sends the pixel's row contribution straight to the sketch rows
 };
 
 // Pipeline per tile: records of batch i+2 in flight by bulk copy (TMA), pose bases of batch i+1 gathered by cp.async
@@ -341,11 +342,32 @@ blend_track_kernel(const int W, const int H, const int gx, const uint32_t* __res
     }
     if (HAS_DEPTH) { tau[2] = fmaf(gd, F0, tau[2]); tau[3] = fmaf(gd, F1, tau[3]); tau[4] = fmaf(gd, F2, tau[4]); }
     if (SKETCH) {
+      if (tail.route.idx != nullptr) {
+        // Routed here: the pixel's nine values go to row sketch_indices[j][pix] of every stack j that holds the pixel, as
+        // fire-and-forget float reductions in L2 (RED.ADD.F32) spread over the whole run of the kernel, behind the other
+        // CTAs' blending.  This replaces the [9][H][W] planes and the reduction kernel that re-read them (52 us at C2, bound
+        // by its shared-memory float atomics, which are compare-and-swap loops; profiles/r02_notes.txt item 16).
+        const float val[9] = {tau[0], tau[1], tau[2], tau[3], tau[4], tau[5], sk_da, sk_db, sk_f};
+        for (int j0 = 0; j0 < tail.route.n_stacks; j0 += 8) {
+          int row[8];
 #pragma unroll
-      for (int k = 0; k < 6; k++) sk_image[k * plane + pix] = tau[k];
-      sk_image[6 * plane + pix] = sk_da;
-      sk_image[7 * plane + pix] = sk_db;
-      sk_image[8 * plane + pix] = sk_f;
+          for (int u = 0; u < 8; u++) row[u] = j0 + u < tail.route.n_stacks ? __ldg(tail.route.idx + (size_t)(j0 + u) * plane + pix) : -1;
+#pragma unroll
+          for (int u = 0; u < 8; u++) {
+            if (row[u] < 0 || row[u] >= tail.route.d) continue;
+            float* o = tail.route.rows + ((size_t)(j0 + u) * tail.route.d + row[u]) * 9;
+#pragma unroll
+            for (int k = 0; k < 9; k++)
+              if (val[k] != 0.f) atomicAdd(o + k, val[k]);
+          }
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 6; k++) sk_image[k * plane + pix] = tau[k];
+        sk_image[6 * plane + pix] = sk_da;
+        sk_image[7 * plane + pix] = sk_db;
+        sk_image[8 * plane + pix] = sk_f;
+      }
     }
   }
   if (DEFER) return;
@@ -474,7 +496,7 @@ int blend_track_warps() { return 8; }
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s, const float* sk_weights, float sk_scale, float* sk_image,
-                       const TrackUpdateK* upd, uint32_t* ticket, bool deferred, bool rows, bool clear_counts) {
+                       const TrackUpdateK* upd, uint32_t* ticket, bool deferred, bool rows, bool clear_counts, const SketchRoute* route) {
   const int tiles = v.gx * v.gy;
   if (clear_counts && !rows) { set_error("blend_track: clear_counts belongs to the fixed-segment (packed-row) mode"); return MGS_EINVAL; }
   if (rows && (deferred || upd != nullptr)) { set_error("blend_track: the packed-row staging serves the fused tracker's un-folded kernels only"); return MGS_EINVAL; }
@@ -499,6 +521,10 @@ int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const fl
   TrackTail tail;
   memset(&tail, 0, sizeof(tail));
   if (upd) { tail.k = *upd; tail.ticket = ticket; }
+  if (route != nullptr) {
+    if (sk_image == nullptr) { set_error("blend_track: a sketch route belongs to the second-order epilogue"); return MGS_EINVAL; }
+    tail.route = *route;
+  }
 #define MGS_TRK_ARGS tiles, s, v.W, v.H, v.gx, ws_ptr<uint32_t>(ws, L.tile_ctr), ws_ptr<uint2>(ws, L.ranges), ws_ptr<SplatRec>(ws, L.records), \
       jac, v.bg, out_color, out_depth, out_opacity, n_touched, *fl.k, fl.grad_scale, fl.partials, tau_sum, sk_weights, sk_scale, sk_image, tail, \
       (clear_counts ? ws_ptr<uint32_t>(ws, L.tile_ctr) : (uint32_t*)nullptr)

@@ -30,13 +30,17 @@ int launch_blend_forward(const ViewConst& v, void* ws, const WsLayout& L, float*
                          float* out_opacity, int32_t* n_touched, cudaStream_t s, const FusedLoss* fl = nullptr,
                          bool heavy_first = false, bool clear_counts = false);   // clear_counts: fixed-segment binning (zero each tile's counter)
 
+// second-order epilogue of the single-pass blend: where a pixel's Jacobian-row contribution goes (sketch_indices i32[n_stacks,H,W],
+// rows f32[n_stacks * d, 9], zero on entry)
+struct SketchRoute { const int32_t* idx; float* rows; int n_stacks, d; };
 // single-pass tracking blend (blend_track.cu): forward + loss + pose tangent; SH degree 0 / 6-column Jacobians only
 int launch_blend_track(const ViewConst& v, void* ws, const WsLayout& L, const float* jac, float* out_color,
                        float* out_depth, float* out_opacity, int32_t* n_touched, const FusedLoss& fl, bool has_depth,
                        float* tau_sum, cudaStream_t s, const float* sk_weights = nullptr, float sk_scale = 0.f,
                        float* sk_image = nullptr, const struct TrackUpdateK* upd = nullptr, uint32_t* ticket = nullptr,
                        bool deferred = false, bool rows = false,    // rows: ids + packed per-Gaussian rows (fused tracker)
-                       bool clear_counts = false);                  // fixed-segment binning: zero each tile's instance counter
+                       bool clear_counts = false,                   // fixed-segment binning: zero each tile's instance counter
+                       const SketchRoute* route = nullptr);
 int blend_track_warps();      // 8 or 4: CTAs per tile = 8 / warps; loss partial slots = tiles * 8 / warps
 // deferred single pass of the drop-in surface: accumulator planes of blend_track<EPI = 2> and their contraction
 size_t pose_deferred_bytes(int W, int H);

@@ -20,6 +20,7 @@
 #include "pose_update.cuh"
 #include "track_update.cuh"
 #include <cstring>
+#include <cstdlib>
 
 namespace mgs {
 
@@ -309,6 +310,10 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   k.min_lambda = a->min_lambda; k.max_lambda = a->max_lambda; k.inc = a->increase_factor; k.dec = a->decrease_factor;
   k.conv_thr = a->converged_threshold; k.loss_out = t->loss;
   cudaError_t e;
+  // the sketch rows are accumulated by the blend kernel's epilogue (SketchRoute): cleared ahead of the chain's first kernel
+  static const bool route_env = [] { const char* e = getenv("MGS_SKETCH_IN_BLEND"); return !(e && e[0] == '0'); }();
+  const SketchRoute route{a->sketch_indices, a->rows, a->n_stacks, a->sketch_dim};
+  if (route_env) MGS_CUDA_TRY(memset_async(a->rows, 0, (size_t)k.rows * 9 * sizeof(float), s));
   MGS_PROF("track2_begin", s, e = launch_chain(track2_begin_kernel, 1, 32, 0, s, k));
   MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
@@ -332,9 +337,9 @@ int mgs_track_second_order(const mgs_track2_args* a, void* stream) {
   fl.k = &lk; fl.grad_scale = 1.f; fl.g_img = nullptr; fl.g_depth = nullptr; fl.partials = partials; fl.fast = t->fast_math != 0;
   const float sk_scale = (float)((double)k.rows / (double)npix);     // 1 / (m / (stack_dim * sketch_dim)), slam_frontend.py:642
   if ((rc = launch_blend_track(v, ws, L, jac, t->out_color, t->out_depth, t->out_opacity, t->n_touched, fl, false, nullptr, s,
-                               a->rand_weights, sk_scale, sk_image, nullptr, nullptr, false, rows, segments)))
+                               a->rand_weights, sk_scale, sk_image, nullptr, nullptr, false, rows, segments, route_env ? &route : nullptr)))
     return rc;
-  if ((rc = launch_sketch_reduce(sk_image, H, W, a->n_stacks, a->sketch_dim, a->sketch_indices, a->rows, s, 9))) return rc;
+  if (!route_env && (rc = launch_sketch_reduce(sk_image, H, W, a->n_stacks, a->sketch_dim, a->sketch_indices, a->rows, s, 9))) return rc;
   MGS_PROF("track2_solve", s, e = launch_chain(track2_solve_kernel, 1, 256, 0, s, k));
   MGS_CUDA_TRY(e);
   MGS_LAUNCH_CHECK();
