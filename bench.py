@@ -77,6 +77,10 @@ class ClockSampler:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.25)
         self.proc.terminate()
+        try:                       # make sure the poller is gone before anything else is timed (it queries the driver every 200 ms)
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
         sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
         mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
@@ -694,9 +698,13 @@ def main():
         return world * args.steps / float(te)
     # host-timed and short (K steps of ~0.27 ms): one hiccup of the host moves a single run by 10 %, so each variant is run
     # three times (K steps each) and the median is reported
-    median3 = lambda fn: sorted(run_e2e(fn) for _ in range(3))[1]
-    e2e_sync = median3(e2e_sync_step)
-    e2e = {"value": median3(e2e_lagged), "unit": "iters/s", "runs": "median of 3 runs of K steps",
+    e2e_runs = {}
+
+    def median3(name, fn):
+        e2e_runs[name] = [round(run_e2e(fn), 1) for _ in range(3)]
+        return sorted(e2e_runs[name])[1]
+    e2e_sync = median3("sync_every_step", e2e_sync_step)
+    e2e = {"value": median3("lagged", e2e_lagged), "unit": "iters/s", "runs": "median of 3 runs of K steps", "all_runs": e2e_runs,
            "h2d_bytes_per_step": gt_host.numel() * 4 + (depth_host.numel() * 4 if depth_host is not None else 0),
            "d2h_bytes_per_step": 28, "value_sync_every_step": e2e_sync,
            "api": "monogs_b200.tracking.PoseTracker.bind_host/step_host_lagged over the C-ABI: one CUDA-graph launch per "
