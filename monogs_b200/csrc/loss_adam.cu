@@ -89,9 +89,13 @@ __global__ void __launch_bounds__(256) adam_kernel(const __grid_constant__ AdamP
   if (a.step_dev != nullptr) {   // uniform branch: device-side step counter (CUDA-graph friendly)
     __shared__ float s_bc[2];
     if (threadIdx.x == 0) {
-      const double t = (double)(a.step_dev[0] + 1);
-      s_bc[0] = (float)(1.0 - pow((double)a.beta1, t));
-      s_bc[1] = (float)sqrt(1.0 - pow((double)a.beta2, t));
+      // beta^t for the integer step number by repeated squaring (every CTA waits for this thread: the generic double pow()
+      // is several hundred dependent instructions, twice)
+      const int t = a.step_dev[0] + 1;
+      double p1 = 1.0, p2 = 1.0, b1 = (double)a.beta1, b2 = (double)a.beta2;
+      for (int e = t; e > 0; e >>= 1) { if (e & 1) { p1 *= b1; p2 *= b2; } b1 *= b1; b2 *= b2; }
+      s_bc[0] = (float)(1.0 - p1);
+      s_bc[1] = (float)sqrt(1.0 - p2);
     }
     __syncthreads();
     bc1 = s_bc[0]; bc2_sqrt = s_bc[1];
