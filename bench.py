@@ -705,6 +705,11 @@ def main():
     def median3(name, fn):
         e2e_runs[name] = [round(run_e2e(fn), 1) for _ in range(5)]
         return sorted(e2e_runs[name])[2]
+    # host warm-up: the timed loops above leave the host thread mostly waiting, and the first few hundred milliseconds of a
+    # host-driven loop then run slower than its steady state (observed: five consecutive 55 ms runs climbing from 3130 to
+    # 3700 it/s); ~0.5 s of untimed steps first
+    for _ in range(max(8 * args.steps, 1000)): e2e_sync_step()
+    torch.cuda.synchronize()
     e2e_sync = median3("sync_every_step", e2e_sync_step)
     e2e = {"value": median3("lagged", e2e_lagged), "unit": "iters/s", "runs": "median of 5 runs of K steps", "all_runs": e2e_runs,
            "h2d_bytes_per_step": gt_host.numel() * 4 + (depth_host.numel() * 4 if depth_host is not None else 0),
