@@ -284,7 +284,7 @@ int mgs_pose_update(float* T_w2c, float* rho, float* theta, const float* proj_ra
  *      aliases the view matrix, as in MonoGS) are device buffers that the call UPDATES IN PLACE with the new pose.
  *      `workspace` and `scratch` must be ZERO-FILLED ONCE by their owner before the first iteration (and belong to this
  *      loop alone): tile counters, tickets and the tangent accumulator are left zero by every iteration for the next one
- *      (the sort kernel clears its tile's counter, the update kernel re-zeroes the accumulator), so an iteration is seven
+ *      (the sort kernel clears its tile's counter, the update kernel re-zeroes the accumulator), so an iteration is seven (four with tile_segments, below)
  *      kernel launches and no memset.  (MGS_SCAN_FOLD=1 / MGS_UPDATE_FOLD=1 in the environment run the tile scan / the
  *      update in the last CTA of the preceding kernel instead of as their own launches: measured slower, kept for comparison.)
  *      params = f32[8] (rho, theta, a, b); exp_avg / exp_avg_sq = f32[8]; step_counter = device i32[1]. ---- */
