@@ -356,7 +356,7 @@ class MapEngine:
         self._graph = None
 
     def poll_capacity(self):
-        """Overflow watch without a host wait (called by step() every `poll_every` iterations): enqueue a 24-byte copy of
+        """Overflow watch without a host wait (called by step() every `poll_every` iterations): enqueue a 32-byte copy of
         every workspace header to pinned memory, and look at the copies enqueued at the previous poll (event.query(), never
         a synchronize).  Any view of any iteration in between that exceeded R_cap has raised overflow_sticky in its
         workspace: the engine counts it (`overflow_polls`), drops the workspaces and re-estimates the capacity from the

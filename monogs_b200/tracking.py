@@ -202,7 +202,7 @@ class PoseTracker:
     def poll_capacity(self):
         """Overflow watch without a host wait.  The scan kernel raises two sticky words in the workspace header
         (overflow_sticky, max_rendered) whenever an iteration's tile instances exceed R_cap; once per frame the tracker
-        enqueues a 24-byte copy of the header to pinned memory and looks at the copy it enqueued one frame earlier (long
+        enqueues a 32-byte copy of the header to pinned memory and looks at the copy it enqueued one frame earlier (long
         complete: event.query(), never synchronize).  An overflow regrows the workspace (and re-captures the graph) before
         the next frame and is counted in `overflow_frames`; a count that merely approaches the capacity regrows it
         proactively.  Returns True when the workspace was regrown."""
