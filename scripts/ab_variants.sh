@@ -1,8 +1,7 @@
-# A/B of build variants: variants/<name>.so copied over the product library, tracking + mapping rates taken
+# A/B of build variants: variants/<name>.so copied over the product library, tracking (+ optionally mapping) rates taken
 for m in $VARIANTS; do
   cp variants/$m.so monogs_b200/lib/libmonogs_b200.so
   echo "== $m"
   python bench.py --no-extras 2>/dev/null | python -c "import json,sys; d=json.loads([l for l in sys.stdin if l.startswith('{')][0]); print('track %.1f warm %.1f e2e %.1f' % (d['value'], d['value_l2_warm'], d['e2e']['value']))"
-  python scripts/map_rate.py 1 | tail -1
-  python scripts/map_rate.py 8 | tail -1
+  if [ -n "$WITH_MAP" ]; then python scripts/map_rate.py 1 | tail -1; python scripts/map_rate.py 8 | tail -1; fi
 done 2>&1 | tee gpurun_out/ab_variants.log
