@@ -778,8 +778,11 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
 // starts are a multiplication.  The tile counters are NOT cleared here (CTA 0 reads all of them while the others run); the
 // blend kernel, which visits every tile exactly once, leaves them zero for the next iteration.
 // IDS: sorted Gaussian ids (fused tracker, packed rows); otherwise 48-byte records gathered by id (mapping engine).
+#ifndef MGS_SEG_SORT_MIN_CTAS
+#define MGS_SEG_SORT_MIN_CTAS 8   // record variant: 32 registers instead of 40 -> 8 CTAs per SM (mapping C4, 8 views: 457.3 -> 459.1 it/s)
+#endif
 template <bool IDS>
-__global__ void __launch_bounds__(MGS_SORT_THREADS)
+__global__ void __launch_bounds__(MGS_SORT_THREADS, IDS ? 0 : MGS_SEG_SORT_MIN_CTAS)
 tile_sort_segments_kernel(const int tiles, const uint32_t cap, const unsigned long long* __restrict__ list,
                           void* __restrict__ out, const float2* __restrict__ means2D_in, const float4* __restrict__ conic_opacity,
                           const float4* __restrict__ rgb4, uint32_t* __restrict__ tile_ctr, uint2* __restrict__ ranges,
