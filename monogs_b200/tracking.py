@@ -161,7 +161,12 @@ class PoseTracker:
 
     @property
     def kernels_per_iter(self):
-        return KERNELS_PER_ITER_SEGMENTS if self.tile_segments else (KERNELS_PER_ITER if self.fused else KERNELS_PER_ITER_COMPOSED)
+        if not self.fused:
+            return KERNELS_PER_ITER_COMPOSED
+        if self.tile_segments:
+            return KERNELS_PER_ITER_SEGMENTS
+        # SH degree > 0: the colours depend on the pose, so the blend is two kernels (forward + loss, pose-only backward)
+        return KERNELS_PER_ITER + (1 if self.view.sh_degree > 0 else 0)
 
     def _enqueue(self):
         """The whole iteration on the current stream, no host sync anywhere: one fused C-ABI call
