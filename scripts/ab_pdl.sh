@@ -1,4 +1,6 @@
 # A/B of the programmatic-dependent-launch trigger placement: variants/pdl_<mask>.so are builds with -DMGS_PDL_MASK=<mask>
+#   for m in 0 2047 39; do MGS_NVCC_EXTRA="-DMGS_PDL_MASK=$m" bash monogs_b200/csrc/build.sh && cp monogs_b200/lib/libmonogs_b200.so variants/pdl_$m.so; done
+#   gpurun -- 'MASKS="0 2047 39" PDLS="0 1" bash scripts/ab_pdl.sh'   (rebuild the default library afterwards)
 # (bits: common.cuh PDL_*); each is copied over the product library and the tracking / mapping rates are taken.
 run() {
   python bench.py --no-extras > gpurun_out/ab_tmp.json 2> gpurun_out/ab_tmp.err

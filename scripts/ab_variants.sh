@@ -1,4 +1,6 @@
-# A/B of build variants: variants/<name>.so copied over the product library, tracking (+ optionally mapping) rates taken
+# A/B of build variants: variants/<name>.so (builds with MGS_NVCC_EXTRA=-D<macro>=<value>, copied from monogs_b200/lib/) are
+# copied over the product library in turn and the tracking (+ with WITH_MAP=1 the mapping) rates are taken:
+#   gpurun -- 'VARIANTS="base coop2" bash scripts/ab_variants.sh'   (rebuild the default library afterwards)
 for m in $VARIANTS; do
   cp variants/$m.so monogs_b200/lib/libmonogs_b200.so
   echo "== $m"
