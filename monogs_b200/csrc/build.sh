@@ -16,3 +16,5 @@ done
 for p in "${pids[@]}"; do wait "$p"; done
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../lib/libmonogs_b200.so $OBJS
 rm -f $OBJS
+# stand-alone checker of the block bitonic sort (tests/test_ops_gpu.py runs it on the GPU box)
+nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o ../../scripts/tools/bitonic_check ../../scripts/tools/bitonic_check.cu

@@ -4,6 +4,7 @@
 #include "launchers.h"
 #include "pose_jac.cuh"
 #include "sh_stage.cuh"
+#include "bitonic_sort.cuh"
 #include <cub/block/block_scan.cuh>
 #include <cub/block/block_merge_sort.cuh>
 #include <cstdarg>
@@ -699,7 +700,11 @@ __device__ __noinline__ void sort_tile_regs(Temp& temp, const unsigned long long
     const int e = threadIdx.x * IPT + i;
     k[i] = e < n ? seg[e] : ~0ull;
   }
-  Sort(reinterpret_cast<typename Sort::TempStorage&>(temp)).Sort(k, U64Less());
+  // (the exchange buffer lives in the sort's shared storage; an instantiation whose storage is too small is the dead
+  // LARGE branch of the short-list kernel and keeps the merge sort)
+  if constexpr (MGS_SORT_BITONIC && (IPT & (IPT - 1)) == 0 && sizeof(Temp) >= (size_t)THREADS * IPT * sizeof(unsigned long long)) {
+    block_bitonic_sort<IPT, THREADS>(k, reinterpret_cast<unsigned long long*>(&temp));
+  } else Sort(reinterpret_cast<typename Sort::TempStorage&>(temp)).Sort(k, U64Less());
 #pragma unroll
   for (int i = 0; i < IPT; i++) {
     const int e = threadIdx.x * IPT + i;

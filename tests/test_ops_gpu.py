@@ -257,3 +257,15 @@ def test_lagged_host_pipeline_returns_previous_iteration():
             got.append((float(loss_host[slot]), tau_host[slot].clone()))
     for (l0, t0), (l1, t1) in zip(ref, got):
         assert abs(l0 - l1) <= 1e-5 * abs(l0) + 1e-8 and U.rel_err(t1, t0) <= 1e-3
+
+
+def test_block_bitonic_sort_against_std_sort():
+    """block_bitonic_sort (csrc/bitonic_sort.cuh: the per-tile depth sort of every binning path) for 1 / 2 / 4 / 8 / 16 words
+    per thread on random unique words with ~0 padding, against std::sort (scripts/tools/bitonic_check.cu, built by
+    csrc/build.sh).  The sorted tile lists are also compared bit for bit with the reference's in test_parity_gpu.py."""
+    import os
+    import subprocess
+    exe = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts", "tools", "bitonic_check")
+    assert os.path.exists(exe), "scripts/tools/bitonic_check missing: run monogs_b200/csrc/build.sh"
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip().endswith("OK"), r.stdout + r.stderr
