@@ -685,6 +685,9 @@ __device__ __forceinline__ void write_record(const unsigned long long w, void* _
   out[2] = make_float4(c.x, c.y, c.z, __uint_as_float(splat_extent(co.x, co.y, co.z, co.w)));
 }
 
+#ifndef MGS_SORT_768_AS_1024
+#define MGS_SORT_768_AS_1024 0    // 1: lists of 513..768 words take the 1024-word bitonic network instead of the 3-words-per-thread merge sort
+#endif
 #ifndef MGS_SORT_THREADS
 #define MGS_SORT_THREADS 256     // CTA size of the short-list sort kernel; measured at C2: 256 -> 33 us, 128 -> 44 us, 64 -> 48 us
 #endif
@@ -738,7 +741,7 @@ tile_sort_records_kernel(const uint2* __restrict__ ranges, unsigned long long* _
     void* dst = means2D == nullptr ? (void*)(reinterpret_cast<uint32_t*>(recs) + range.x) : (void*)(recs + range.x);
     if (n <= 256) sort_tile_regs<SI / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
     else if (n <= 512) sort_tile_regs<SI / 2, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
-    else if (n <= 768) sort_tile_regs<SI * 3 / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);   // lists just over 512 are common at 640x480 / 200k
+    else if (n <= 768 && !MGS_SORT_768_AS_1024) sort_tile_regs<SI * 3 / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);   // lists just over 512 are common at 640x480 / 200k
     else sort_tile_regs<SI, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, colors_precomp);
     return;
   }
@@ -805,7 +808,7 @@ tile_sort_segments_kernel(const int tiles, const uint32_t cap, const unsigned lo
     const float2* means2D = IDS ? nullptr : means2D_in;      // write_record: null = ids only
     if (n <= 256) sort_tile_regs<SI / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, nullptr);
     else if (n <= 512) sort_tile_regs<SI / 2, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, nullptr);
-    else if (n <= 768) sort_tile_regs<SI * 3 / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, nullptr);
+    else if (n <= 768 && !MGS_SORT_768_AS_1024) sort_tile_regs<SI * 3 / 4, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, nullptr);
     else sort_tile_regs<SI, ST>(temp, seg, n, dst, means2D, conic_opacity, rgb4, nullptr);
     return;
   }
