@@ -109,3 +109,29 @@ def test_grad_arena_layout_and_peer_slices():
             assert cuts[0][0] == 0 and cuts[-1][1] == numel
             for (b0, e0), (b1, e1) in zip(cuts, cuts[1:]):
                 assert e0 == b1 and b0 <= e0 and b0 % 4 == 0
+
+
+def test_committed_profile_table_describes_the_committed_kernels():
+    """bench.py takes `roofline.traffic` and the issue-roofline inputs of the dominant kernel from the committed ncu table
+    (profiles/r02_kernel_metrics.txt) and refuses a row whose kernel sources changed after the capture (the table's
+    header records their sha1).  A kernel edit without a fresh capture would silently drop those numbers from the bench
+    line; this test makes it loud."""
+    import bench
+    row, why = bench.profile_row("blend_track_kernel")
+    assert row is not None, why
+    assert why is None, why
+    assert row["us"] > 0 and row["Minst"] > 0 and 0 < row["lanes"] <= 32
+
+
+def test_algorithmic_bytes_of_the_segment_iteration():
+    """The four kernels of the fixed-segment tracking iteration and the seven of the general binning are both accounted
+    for; the segment iteration moves fewer algorithmic bytes (no depth / mean2D arrays, no emit pass)."""
+    import bench
+    P, P_vis, R, R_cap, W, H = 200_000, 145_000, 546_000, 1_228_800, 640, 480
+    seg = bench.algorithmic_bytes(P, P_vis, R, R_cap, W, H, segments=True)
+    gen = bench.algorithmic_bytes(P, P_vis, R, R_cap, W, H, segments=False)
+    assert set(seg) == {"preprocess", "tile_sort_segments", "blend_track", "track_update"}
+    assert {"preprocess", "tile_scan", "emit", "tile_sort_records", "blend_track", "track_update"} <= set(gen)
+    fused_gen = sum(gen[k] for k in ("preprocess", "tile_scan", "emit", "tile_sort_records", "tile_sort_records_large", "blend_track", "track_update"))
+    assert sum(seg.values()) < fused_gen
+    assert seg["preprocess"] == gen["preprocess"] - 12 * P_vis + 8 * R      # + scattered words, - depth / mean2D arrays
